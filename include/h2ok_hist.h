@@ -1,0 +1,204 @@
+/*
+ * h2ok_hist.h — C ABI of the B200-native GBM histogram path ("hist" layer).
+ *
+ * The reference (isgasho/h2o-kubernetes, crate `h2ok`) has NO FFI, plugin or operator interface
+ * and no numeric code: the GBM it stands up runs inside the unvendored H2O-3 jar started by
+ * src/k8s/templates.rs:29-30 (`java ... -jar /opt/h2oai/h2o-3/h2o.jar`, image pinned only as
+ * `latest` at src/k8s/mod.rs:115).  This header therefore DEFINES the boundary; each entry point
+ * names the H2O-3 unit it stands in for (package hex.tree, recalled from H2O-3's public source,
+ * not present under /root/reference — see DESIGN.md "parity unpinned") and the reference line
+ * through which that unit is reached today.
+ *
+ * Conventions inherited from the reference:
+ *  - fallible operations return a status instead of aborting (Result<..> everywhere, e.g.
+ *    src/k8s/mod.rs:85-93, src/main.rs:54-59): every function returns int32_t, 0 == H2OK_OK;
+ *    the message is fetched with h2ok_last_error() (thread-local).
+ *  - callers are single-threaded and blocking (fresh Runtime + block_on per op,
+ *    src/k8s/mod.rs:86,130,167): a context is used from one thread; the *_dev entry points
+ *    enqueue on the context's stream and return, the host-buffer entry points are complete on return.
+ *  - no hidden state beyond the opaque context (state in the reference is an explicit file,
+ *    src/main.rs:72-101).
+ *
+ * Data layout: X is column-major fp32, column c at X + c*ld (ld >= rows, ld % 4 == 0, base
+ * 16-byte aligned) — one contiguous vector per column like an H2O Vec/Chunk.  Row-indexed arrays
+ * (y, w, nid, quantised targets) have `rows` entries.  nid[r] is the index of the row's node in
+ * the current level's active-node list, or a negative value if the row already sits in a leaf.
+ *
+ * Histogram layout: [n_nodes][cols][max_bins+1][3], channels {w, wY, wYY}; slot nbin of a
+ * (node,col) is the NA bucket (DHistogram._vals, hex/tree/DHistogram.java), slots above nbin unused.
+ */
+#ifndef H2OK_HIST_H
+#define H2OK_HIST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define H2OK_OK 0
+#define H2OK_ERR_ARG 1         /* bad argument (null, size, alignment) */
+#define H2OK_ERR_CUDA 2        /* a CUDA call failed; message has the CUDA error string */
+#define H2OK_ERR_STATE 3       /* call sequence violated (e.g. build_level before set_data) */
+#define H2OK_ERR_UNSUPPORTED 4 /* categorical columns, > H2OK_MAX_BINS bins, ... */
+
+#define H2OK_MAX_BINS 1024
+#define H2OK_MAX_LEVEL_NODES 4096
+
+/* NA direction of a split (DHistogram.NASplitDir). */
+#define H2OK_NA_NONE 0
+#define H2OK_NA_VS_REST 1 /* non-NA left, NA right */
+#define H2OK_NA_LEFT 2
+#define H2OK_NA_RIGHT 3
+
+/* Synthetic shapes of SURVEY.md §8(d). */
+#define H2OK_SHAPE_HIGGS28 2 /* config 2: 28 HIGGS-shaped columns */
+#define H2OK_SHAPE_WIDE64 3  /* config 3: the 28-column recipe tiled to any width with affine offsets */
+#define H2OK_SHAPE_SPARSE 4  /* config 4: 90 % exact zeros, else u */
+
+typedef struct h2ok_ctx h2ok_ctx;
+
+/* a1 — one DHistogram's constructor fields for one (node, column).  nbin == 0 means the column is
+ * not tracked for this node (constant / all-NA there) and contributes nothing. */
+typedef struct h2ok_col_desc {
+  double min;     /* inclusive lower bound (_min) */
+  double maxex;   /* exclusive upper bound (_maxEx) */
+  double step;    /* _step: nbin/(maxex-min), or 1.0 for integer columns with few values */
+  int32_t nbin;   /* _nbin <= max_bins */
+  int32_t is_int; /* _isInt: 0 real, 1 integer; 2 (categorical) is rejected */
+} h2ok_col_desc;
+
+/* a7 — DTree.Split as chosen by UndecidedNode.bestCol.  col < 0: the node does not split. */
+typedef struct h2ok_split {
+  int32_t col;
+  int32_t bin;    /* bins [0,bin) left, [bin,nbin) right */
+  int32_t na_dir; /* H2OK_NA_* */
+  float splat;    /* row routing threshold: x >= splat goes right (Split.splat) */
+  double se_before, se_left, se_right;
+  double n_left, n_right;       /* weighted row counts */
+  double pred_left, pred_right; /* wY/w of each side */
+} h2ok_split;
+
+/* Fixed-point scales for the integer accumulators.  All three are powers of two so that the
+ * conversion back to double is exact.  weighted == 0: w is absent (== 1) and channel 0 counts rows. */
+typedef struct h2ok_quant {
+  double scale_w, scale_wy, scale_wyy;
+  int32_t weighted;
+  int32_t qbits; /* |quantised value| <= 2^qbits */
+} h2ok_quant;
+
+typedef struct h2ok_params {
+  int32_t nbins;           /* 256 in BASELINE configs 2/3, 64 in config 4 */
+  int32_t nbins_top_level; /* H2O halves this per level down to nbins; set == nbins to keep it fixed */
+  int32_t max_depth;
+  int32_t pad;
+  double min_rows;              /* 10 */
+  double min_split_improvement; /* 1e-5 */
+} h2ok_params;
+
+typedef struct h2ok_stats {
+  float build_ms;   /* device time of the last build_level's kernels */
+  int32_t launches; /* kernels launched by the last build_level */
+  int32_t passes;   /* node-group passes over X */
+  int32_t copies;   /* privatised sub-histograms per (node,col) */
+  double algo_bytes;
+} h2ok_stats;
+
+/* ---- lifecycle ------------------------------------------------------------------------------ */
+int32_t h2ok_hist_create(int32_t device, h2ok_ctx** out);
+int32_t h2ok_hist_destroy(h2ok_ctx* ctx);
+const char* h2ok_last_error(void);
+int32_t h2ok_hist_abi_version(void);
+/* Use `stream` (a cudaStream_t) for every *_dev call instead of the context's own stream. */
+int32_t h2ok_hist_set_stream(h2ok_ctx* ctx, void* stream);
+int32_t h2ok_hist_sync(h2ok_ctx* ctx);
+
+/* ---- device-resident entry points (pointers are device pointers; asynchronous) -------------- */
+
+/* Counter-based generator of SURVEY.md §8(d); fills rows [row0,row0+rows) of the global matrix.
+ * d_w may be NULL.  na_permille: per-mille of cells set to NaN.  weight_mode: 0 w=1, 1 w=0.5+u with 2% zeros. */
+int32_t h2ok_hist_synth_fill_dev(h2ok_ctx* ctx, int32_t shape, uint64_t seed, int64_t row0, int64_t rows,
+                                 int32_t cols, int64_t ld, int32_t na_permille, int32_t weight_mode,
+                                 float* d_X, float* d_y, float* d_w);
+
+/* Root ranges (DHistogram.initialHist reads Vec.min()/max()): finite-or-inf min and max per column, NaN skipped.
+ * Output is the order-preserving uint32 encoding (see h2ok_hist_decode_f32) so ranks can be combined with integer min/max. */
+int32_t h2ok_hist_col_ranges_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, int64_t rows, int32_t cols,
+                                 uint32_t* d_min_enc, uint32_t* d_max_enc);
+
+/* max |w|, |w*y|, |w*y*y| over rows → d_absmax[3] (doubles); used to choose h2ok_quant scales. */
+int32_t h2ok_hist_target_absmax_dev(h2ok_ctx* ctx, const float* d_y, const float* d_w, int64_t rows, double* d_absmax);
+
+/* Per-row fixed-point targets: wq = rint(w*scale_w) (absent when !weighted), wyq = rint(w*y*scale_wy),
+ * wyyq = rint(w*y*y*scale_wyy), all computed in fp64, round-half-even. */
+int32_t h2ok_hist_quantize_rows_dev(h2ok_ctx* ctx, const float* d_y, const float* d_w, int64_t rows,
+                                    const h2ok_quant* q, int32_t* d_wq, int32_t* d_wyq, int32_t* d_wyyq);
+
+/* a2 — DHistogram.bin for n values against one descriptor (test hook for bit-exact bin indices). */
+int32_t h2ok_hist_bin_dev(h2ok_ctx* ctx, const float* d_x, int64_t n, const h2ok_col_desc* desc, int32_t* d_bins);
+
+/* a3/a4 — ScoreBuildHistogram local phase: accumulate every active row into its (node,col) histogram.
+ * d_acc: int64 [n_nodes][cols][max_bins+1][3] fixed-point sums, zeroed here when clear != 0.
+ * d_min2_enc/d_maxin_enc: uint32 [n_nodes][cols] encoded observed min / max (DHistogram._min2/_maxIn), reset when clear != 0.
+ * d_descs: device array [n_nodes][cols]. d_wq may be NULL (unweighted). */
+int32_t h2ok_hist_build_level_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, int64_t rows, int32_t cols,
+                                  const int32_t* d_nid, const int32_t* d_wq, const int32_t* d_wyq,
+                                  const int32_t* d_wyyq, int32_t n_nodes, const h2ok_col_desc* d_descs,
+                                  int32_t max_bins, int32_t clear, int64_t* d_acc, uint32_t* d_min2_enc,
+                                  uint32_t* d_maxin_enc);
+
+/* a5 tail — after the cross-rank reduce (MRTask.reduce / DHistogram.add, done by the caller on d_acc with an
+ * integer sum and on the encoded ranges with integer min/max): fixed-point → double, encoded → float. */
+int32_t h2ok_hist_finalize_level_dev(h2ok_ctx* ctx, const int64_t* d_acc, const uint32_t* d_min2_enc,
+                                     const uint32_t* d_maxin_enc, int32_t n_nodes, int32_t cols, int32_t max_bins,
+                                     const h2ok_quant* q, double* d_hist, float* d_min2, float* d_maxin);
+
+/* a7 — DTree.findBestSplitPoint per (node,col) + UndecidedNode.bestCol per node. */
+int32_t h2ok_hist_find_splits_dev(h2ok_ctx* ctx, const double* d_hist, const h2ok_col_desc* d_descs, int32_t n_nodes,
+                                  int32_t cols, int32_t max_bins, double min_rows, double min_split_improvement,
+                                  h2ok_split* d_splits);
+
+/* a8 — DTree.Split.nextLevelHistos for both children of every split node.  d_child_ids[2*i+way] receives the
+ * child's index in the next level's active list or -1; d_child_descs is [2*n_nodes][cols] (compacted, first
+ * *d_n_children entries valid).  depth = level of the parents. */
+int32_t h2ok_hist_next_level_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, const h2ok_col_desc* d_descs,
+                                 const float* d_min2, const float* d_maxin, int32_t n_nodes, int32_t cols,
+                                 const h2ok_params* params, int32_t depth, h2ok_col_desc* d_child_descs,
+                                 int32_t* d_child_ids, int32_t* d_n_children);
+
+/* a6 — ScoreBuildHistogram.score_decide / DecidedNode.getChildNodeID: move each active row to its child.
+ * A row that retires gets nid -1 and d_leaf[r] = 3*(gid_base+node) + k, k = 0 node did not split, 1 / 2 the left /
+ * right side has no child (gid_base: tree-wide id of this level's node 0; d_leaf may be NULL). */
+int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, int64_t rows, const h2ok_split* d_splits,
+                                   const int32_t* d_child_ids, int32_t gid_base, int32_t n_nodes, int32_t* d_nid,
+                                   int32_t* d_leaf);
+
+/* ---- host-buffer entry points (what an H2O-side caller binds; synchronous) ------------------ */
+
+/* Library copies the columns (cols_host[c] points at `rows` floats). */
+int32_t h2ok_hist_set_data_host(h2ok_ctx* ctx, const float* const* cols_host, int64_t rows, int32_t cols);
+/* New tree: copy y (and w, may be NULL), choose scales, quantise, put every row in node 0. */
+int32_t h2ok_hist_set_targets_host(h2ok_ctx* ctx, const float* y_host, const float* w_host);
+/* Root descriptors from the resident data (DHistogram.initialHist). */
+int32_t h2ok_hist_root_descs(h2ok_ctx* ctx, const h2ok_params* params, const int32_t* is_int /*[cols] or NULL*/,
+                             h2ok_col_desc* descs_out /*[cols]*/);
+/* One level: histogram + observed ranges to host buffers. */
+int32_t h2ok_hist_build_level(h2ok_ctx* ctx, int32_t n_nodes, const h2ok_col_desc* descs, int32_t max_bins,
+                              double* hist_out, float* min2_out, float* maxin_out);
+/* Split search on the level just built; splits to host. */
+int32_t h2ok_hist_find_splits(h2ok_ctx* ctx, double min_rows, double min_split_improvement, h2ok_split* splits_out);
+/* Children of the level just searched: descriptors + child ids to host; *n_children_out active nodes next. */
+int32_t h2ok_hist_next_level(h2ok_ctx* ctx, const h2ok_params* params, int32_t depth, h2ok_col_desc* child_descs_out,
+                             int32_t* child_ids_out, int32_t* n_children_out);
+/* Route rows with the splits found (device-resident copies are used; nothing crosses the bus). */
+int32_t h2ok_hist_apply_splits(h2ok_ctx* ctx);
+/* Copy the row→node map / leaf assignment back (tests). */
+int32_t h2ok_hist_get_nid_host(h2ok_ctx* ctx, int32_t* nid_out, int32_t* leaf_out);
+int32_t h2ok_hist_get_quant(h2ok_ctx* ctx, h2ok_quant* out);
+int32_t h2ok_hist_last_level_stats(h2ok_ctx* ctx, h2ok_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* H2OK_HIST_H */

@@ -1,0 +1,226 @@
+"""ctypes binding of oracle/liboracle.so — TEST INFRASTRUCTURE ONLY (tests/, smoke(), bench cpu_baseline).
+
+Builds the library with `make -C oracle` if it is missing (gcc only, no GPU needed).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from h2ok_hist import abi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB = None
+
+i32, i64, u64, f64 = C.c_int32, C.c_int64, C.c_uint64, C.c_double
+vp = C.c_void_p
+
+
+def _build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+
+
+class Oracle:
+    def __init__(self, lib):
+        self.lib = lib
+        L = lib
+        L.h2ok_oracle_splitmix64.restype = u64
+        L.h2ok_oracle_splitmix64.argtypes = [u64]
+        L.h2ok_oracle_gen_x.restype = C.c_float
+        L.h2ok_oracle_gen_x.argtypes = [i32, u64, i64, i32, i32]
+        L.h2ok_oracle_synth_fill.restype = None
+        L.h2ok_oracle_synth_fill.argtypes = [i32, u64, i64, i64, i32, i64, i32, i32, vp, vp, vp]
+        L.h2ok_oracle_make_desc.restype = i32
+        L.h2ok_oracle_make_desc.argtypes = [f64, f64, i32, i32, vp]
+        L.h2ok_oracle_find_maxex.restype = f64
+        L.h2ok_oracle_find_maxex.argtypes = [f64, i32]
+        L.h2ok_oracle_col_ranges.restype = None
+        L.h2ok_oracle_col_ranges.argtypes = [vp, i64, i64, i32, vp, vp]
+        L.h2ok_oracle_root_descs.restype = i32
+        L.h2ok_oracle_root_descs.argtypes = [vp, i64, i64, i32, C.POINTER(abi.Params), vp, vp]
+        L.h2ok_oracle_bin.restype = i32
+        L.h2ok_oracle_bin.argtypes = [C.c_float, vp]
+        L.h2ok_oracle_bin_many.restype = None
+        L.h2ok_oracle_bin_many.argtypes = [vp, i64, vp, vp]
+        L.h2ok_oracle_target_absmax.restype = None
+        L.h2ok_oracle_target_absmax.argtypes = [vp, vp, i64, vp]
+        L.h2ok_oracle_choose_quant.restype = None
+        L.h2ok_oracle_choose_quant.argtypes = [vp, i32, i32, C.POINTER(abi.Quant)]
+        L.h2ok_oracle_quantize_rows.restype = None
+        L.h2ok_oracle_quantize_rows.argtypes = [vp, vp, i64, C.POINTER(abi.Quant), vp, vp, vp]
+        L.h2ok_oracle_build_level.restype = None
+        L.h2ok_oracle_build_level.argtypes = [vp, i64, i64, i32, vp, vp, vp, i32, vp, i32, vp, vp, vp, vp, i32]
+        L.h2ok_oracle_build_level_q.restype = None
+        L.h2ok_oracle_build_level_q.argtypes = [vp, i64, i64, i32, vp, vp, vp, vp, i32, vp, i32, vp, vp, vp]
+        L.h2ok_oracle_finalize.restype = None
+        L.h2ok_oracle_finalize.argtypes = [vp, i64, i32, C.POINTER(abi.Quant), vp]
+        L.h2ok_oracle_find_splits.restype = None
+        L.h2ok_oracle_find_splits.argtypes = [vp, vp, i32, i32, i32, f64, f64, vp]
+        L.h2ok_oracle_next_level.restype = None
+        L.h2ok_oracle_next_level.argtypes = [vp, vp, vp, vp, i32, i32, C.POINTER(abi.Params), i32, vp, vp, vp]
+        L.h2ok_oracle_apply_splits.restype = None
+        L.h2ok_oracle_apply_splits.argtypes = [vp, i64, i64, vp, vp, i32, i32, vp, vp]
+        L.h2ok_oracle_max_threads.restype = i32
+
+    # ---- generator ----
+    def synth(self, shape, seed, row0, rows, cols, na_permille=0, weight_mode=0, ld=None):
+        ld = ld or ((rows + 3) // 4 * 4)
+        X = np.zeros((cols, ld), np.float32)
+        y = np.zeros(rows, np.float32)
+        w = np.zeros(rows, np.float32) if weight_mode else None
+        self.lib.h2ok_oracle_synth_fill(shape, seed, row0, rows, cols, ld, na_permille, weight_mode,
+                                        abi.ptr(X), abi.ptr(y), abi.ptr(w))
+        return X, y, w
+
+    # ---- descriptors ----
+    def make_desc(self, mn, maxex, is_int, nbins):
+        d = np.zeros(1, abi.COL_DESC)
+        ok = self.lib.h2ok_oracle_make_desc(mn, maxex, is_int, nbins, abi.ptr(d))
+        return d[0], ok
+
+    def find_maxex(self, maxin, is_int):
+        return self.lib.h2ok_oracle_find_maxex(maxin, is_int)
+
+    def col_ranges(self, X, rows):
+        cols, ld = X.shape
+        mn = np.zeros(cols, np.float32)
+        mx = np.zeros(cols, np.float32)
+        self.lib.h2ok_oracle_col_ranges(abi.ptr(X), ld, rows, cols, abi.ptr(mn), abi.ptr(mx))
+        return mn, mx
+
+    def root_descs(self, X, rows, params, is_int=None):
+        cols, ld = X.shape
+        out = np.zeros(cols, abi.COL_DESC)
+        ii = None if is_int is None else np.ascontiguousarray(is_int, np.int32)
+        rc = self.lib.h2ok_oracle_root_descs(abi.ptr(X), ld, rows, cols, C.byref(params), abi.ptr(ii), abi.ptr(out))
+        assert rc == 0
+        return out
+
+    def bin(self, x, desc):
+        d = np.array([desc], abi.COL_DESC)
+        return self.lib.h2ok_oracle_bin(C.c_float(x), abi.ptr(d))
+
+    def bin_many(self, x, desc):
+        x = np.ascontiguousarray(x, np.float32)
+        d = np.array([desc], abi.COL_DESC)
+        out = np.zeros(x.size, np.int32)
+        self.lib.h2ok_oracle_bin_many(abi.ptr(x), x.size, abi.ptr(d), abi.ptr(out))
+        return out
+
+    # ---- quantisation ----
+    def choose_quant(self, y, w, qbits=26):
+        m = np.zeros(3, np.float64)
+        self.lib.h2ok_oracle_target_absmax(abi.ptr(y), abi.ptr(w), y.size, abi.ptr(m))
+        q = abi.Quant()
+        self.lib.h2ok_oracle_choose_quant(abi.ptr(m), 1 if w is not None else 0, qbits, C.byref(q))
+        return q, m
+
+    def quantize_rows(self, y, w, q):
+        n = y.size
+        wq = np.zeros(n, np.int32) if q.weighted else None
+        wyq = np.zeros(n, np.int32)
+        wyyq = np.zeros(n, np.int32)
+        self.lib.h2ok_oracle_quantize_rows(abi.ptr(y), abi.ptr(w), n, C.byref(q), abi.ptr(wq), abi.ptr(wyq), abi.ptr(wyyq))
+        return wq, wyq, wyyq
+
+    # ---- level ----
+    def build_level(self, X, rows, y, w, nid, descs, max_bins, threads=1, want_abs=True):
+        cols, ld = X.shape
+        descs = np.ascontiguousarray(descs, abi.COL_DESC).reshape(-1, cols)
+        n_nodes = descs.shape[0]
+        hist = np.zeros((n_nodes, cols, max_bins + 1, 3), np.float64)
+        absy = np.zeros((n_nodes, cols, max_bins + 1), np.float64) if want_abs else None
+        min2 = np.zeros((n_nodes, cols), np.float32)
+        maxin = np.zeros((n_nodes, cols), np.float32)
+        self.lib.h2ok_oracle_build_level(abi.ptr(X), ld, rows, cols, abi.ptr(y), abi.ptr(w), abi.ptr(nid), n_nodes,
+                                         abi.ptr(descs), max_bins, abi.ptr(hist), abi.ptr(absy), abi.ptr(min2),
+                                         abi.ptr(maxin), threads)
+        return hist, absy, min2, maxin
+
+    def build_level_q(self, X, rows, nid, wq, wyq, wyyq, descs, max_bins):
+        cols, ld = X.shape
+        descs = np.ascontiguousarray(descs, abi.COL_DESC).reshape(-1, cols)
+        n_nodes = descs.shape[0]
+        acc = np.zeros((n_nodes, cols, max_bins + 1, 3), np.int64)
+        min2 = np.zeros((n_nodes, cols), np.float32)
+        maxin = np.zeros((n_nodes, cols), np.float32)
+        self.lib.h2ok_oracle_build_level_q(abi.ptr(X), ld, rows, cols, abi.ptr(nid), abi.ptr(wq), abi.ptr(wyq),
+                                           abi.ptr(wyyq), n_nodes, abi.ptr(descs), max_bins, abi.ptr(acc),
+                                           abi.ptr(min2), abi.ptr(maxin))
+        return acc, min2, maxin
+
+    def finalize(self, acc, q, max_bins):
+        hist = np.zeros(acc.shape, np.float64)
+        self.lib.h2ok_oracle_finalize(abi.ptr(acc), acc.size, max_bins, C.byref(q), abi.ptr(hist))
+        return hist
+
+    def find_splits(self, hist, descs, min_rows=10.0, msi=1e-5):
+        n_nodes, cols, nb1, _ = hist.shape
+        hist = np.ascontiguousarray(hist, np.float64)
+        descs = np.ascontiguousarray(descs, abi.COL_DESC).reshape(n_nodes, cols)
+        out = np.zeros(n_nodes, abi.SPLIT)
+        self.lib.h2ok_oracle_find_splits(abi.ptr(hist), abi.ptr(descs), n_nodes, cols, nb1 - 1, min_rows, msi, abi.ptr(out))
+        return out
+
+    def next_level(self, splits, descs, min2, maxin, params, depth=0):
+        descs = np.ascontiguousarray(descs, abi.COL_DESC)
+        n_nodes, cols = descs.shape
+        splits = np.ascontiguousarray(splits, abi.SPLIT)
+        child = np.zeros((2 * n_nodes, cols), abi.COL_DESC)
+        ids = np.zeros(2 * n_nodes, np.int32)
+        n = C.c_int32(0)
+        min2 = np.ascontiguousarray(min2, np.float32)
+        maxin = np.ascontiguousarray(maxin, np.float32)
+        self.lib.h2ok_oracle_next_level(abi.ptr(splits), abi.ptr(descs), abi.ptr(min2), abi.ptr(maxin), n_nodes, cols,
+                                        C.byref(params), depth, abi.ptr(child), abi.ptr(ids), C.byref(n))
+        return child[: n.value].copy(), ids, n.value
+
+    def apply_splits(self, X, rows, splits, child_ids, gid_base, nid, leaf=None):
+        cols, ld = X.shape
+        splits = np.ascontiguousarray(splits, abi.SPLIT)
+        child_ids = np.ascontiguousarray(child_ids, np.int32)
+        self.lib.h2ok_oracle_apply_splits(abi.ptr(X), ld, rows, abi.ptr(splits), abi.ptr(child_ids), gid_base,
+                                          splits.size, abi.ptr(nid), abi.ptr(leaf))
+
+    def max_threads(self):
+        return self.lib.h2ok_oracle_max_threads()
+
+    # ---- whole tree on the CPU (used as the checker for the level loop) ----
+    def train_tree(self, X, rows, y, w, params, is_int=None, threads=1, on_level=None):
+        cols = X.shape[0]
+        descs = self.root_descs(X, rows, params, is_int).reshape(1, cols)
+        nid = np.zeros(rows, np.int32)
+        leaf = np.full(rows, -1, np.int32)
+        gid_base = 0
+        levels = []
+        max_bins = max(params.nbins, params.nbins_top_level)
+        for depth in range(params.max_depth):
+            n_nodes = descs.shape[0]
+            hist, absy, min2, maxin = self.build_level(X, rows, y, w, nid, descs, max_bins, threads)
+            splits = self.find_splits(hist, descs, params.min_rows, params.min_split_improvement)
+            if depth + 1 < params.max_depth:
+                child, ids, nch = self.next_level(splits, descs, min2, maxin, params, depth)
+            else:
+                child, ids, nch = np.zeros((0, cols), abi.COL_DESC), np.full(2 * n_nodes, -1, np.int32), 0
+            levels.append(dict(descs=descs, hist=hist, abs_wy=absy, min2=min2, maxin=maxin, splits=splits,
+                               child_ids=ids, nid=nid.copy(), gid_base=gid_base))
+            if on_level:
+                on_level(depth, levels[-1])
+            self.apply_splits(X, rows, splits, ids, gid_base, nid, leaf)
+            gid_base += n_nodes
+            descs = child
+            if nch == 0:
+                break
+        return levels, nid, leaf
+
+
+def load():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(ROOT, "oracle", "liboracle.so")
+        src = os.path.join(ROOT, "oracle", "hist_oracle.c")
+        if not os.path.exists(path) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(path)):
+            _build()
+        _LIB = Oracle(C.CDLL(path))
+    return _LIB
