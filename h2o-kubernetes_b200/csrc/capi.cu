@@ -1,0 +1,511 @@
+// capi.cu — the extern "C" boundary declared in include/h2ok_hist.h.  No torch types, plain pointers and sizes.
+// There is no CPU fallback: every entry point drives the sm_100a kernels or fails with a status.
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace h2ok;
+
+static thread_local char g_err[512] = "";
+
+static int32_t fail(int32_t code, const char* fmt, const char* a = "", const char* b = "") {
+  snprintf(g_err, sizeof(g_err), fmt, a, b);
+  return code;
+}
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t _e = (call);                                                             \
+    if (_e != cudaSuccess) return fail(H2OK_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_e)); \
+  } while (0)
+
+#define REQUIRE(cond, msg) \
+  do {                     \
+    if (!(cond)) return fail(H2OK_ERR_ARG, "%s (%s)", msg, #cond); \
+  } while (0)
+
+template <typename T>
+struct DevBuf {  // grow-only device buffer
+  T* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+    if (e == cudaSuccess) cap = n;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct h2ok_ctx {
+  int device = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // scratch of next_level (a8)
+  DevBuf<h2ok_col_desc> tmp_descs;
+  DevBuf<int32_t> tmp_valid;
+  // resident data of the host-buffer API
+  DevBuf<float> X, y, w;
+  DevBuf<int32_t> nid, leaf, wq, wyq, wyyq;
+  DevBuf<double> absmax;
+  DevBuf<uint32_t> cmin, cmax;
+  int64_t rows = 0, ld = 0;
+  int cols = 0;
+  bool have_data = false, have_targets = false, weighted = false;
+  h2ok_quant q{};
+  // level state
+  DevBuf<h2ok_col_desc> descs, child_descs;
+  DevBuf<int64_t> acc;
+  DevBuf<uint32_t> mn, mx;
+  DevBuf<double> hist;
+  DevBuf<float> min2, maxin;
+  DevBuf<h2ok_split> splits;
+  DevBuf<int32_t> child_ids, n_children;
+  int n_nodes = 0, max_bins = 0, gid_base = 0;
+  bool level_built = false, splits_found = false, children_made = false;
+  h2ok_stats stats{};
+};
+
+// ---- host copies of the a1 rules (DHistogram.<init> / find_maxEx) for root descriptors -------------------
+static double h_ulp(double x) {
+  x = fabs(x);
+  if (isinf(x)) return x;
+  if (x == 1.7976931348623157e308) return x - nextafter(x, 0.0);
+  return nextafter(x, INFINITY) - x;
+}
+static double h_find_maxex(double maxin, int is_int) {
+  double ulp = h_ulp(maxin);
+  if (is_int > 0 && 1 > ulp) ulp = 1;
+  double res = maxin + ulp;
+  return isinf(res) ? maxin : res;
+}
+static int h_make_desc(double mn, double maxex, int is_int, int nbins, h2ok_col_desc* out) {
+  out->min = mn;
+  out->maxex = maxex;
+  out->is_int = is_int;
+  out->nbin = 0;
+  out->step = 0.0;
+  if (!(maxex > mn)) return 0;
+  int xbins = nbins;
+  double step;
+  if (is_int > 0 && maxex - mn <= (double)xbins) {
+    xbins = (int)((long long)maxex - (long long)mn);
+    step = 1.0;
+  } else {
+    volatile double range = maxex - mn;  // keep the two roundings separate (no contraction on the host either)
+    step = (double)xbins / range;
+    if (!(step > 0.0) || isinf(step)) return 0;
+  }
+  if (xbins < 1) return 0;
+  out->step = step;
+  out->nbin = xbins;
+  return 1;
+}
+static double pow2_scale(double absmax, int qbits) {
+  if (!(absmax > 0.0) || isinf(absmax)) return 1.0;
+  int ex;
+  frexp(absmax, &ex);
+  return ldexp(1.0, qbits - ex);
+}
+
+extern "C" {
+
+const char* h2ok_last_error(void) { return g_err; }
+int32_t h2ok_hist_abi_version(void) { return 1; }
+
+int32_t h2ok_hist_create(int32_t device, h2ok_ctx** out) {
+  REQUIRE(out != nullptr, "null out pointer");
+  int n = 0;
+  CK(cudaGetDeviceCount(&n));
+  if (device < 0 || device >= n) return fail(H2OK_ERR_ARG, "%s", "device index out of range");
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return fail(H2OK_ERR_UNSUPPORTED, "%s", "this library is built for sm_100a (B200) only");
+  h2ok_ctx* c = new h2ok_ctx();
+  c->device = device;
+  CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  CK(cudaEventCreate(&c->ev0));
+  CK(cudaEventCreate(&c->ev1));
+  *out = c;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_destroy(h2ok_ctx* c) {
+  if (!c) return H2OK_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->tmp_descs.release(); c->tmp_valid.release(); c->X.release(); c->y.release(); c->w.release();
+  c->nid.release(); c->leaf.release(); c->wq.release(); c->wyq.release(); c->wyyq.release(); c->absmax.release();
+  c->cmin.release(); c->cmax.release(); c->descs.release(); c->child_descs.release(); c->acc.release();
+  c->mn.release(); c->mx.release(); c->hist.release(); c->min2.release(); c->maxin.release(); c->splits.release();
+  c->child_ids.release(); c->n_children.release();
+  cudaEventDestroy(c->ev0);
+  cudaEventDestroy(c->ev1);
+  cudaStreamDestroy(c->own_stream);
+  delete c;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_set_stream(h2ok_ctx* c, void* stream) {
+  REQUIRE(c != nullptr, "null context");
+  c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_sync(h2ok_ctx* c) {
+  REQUIRE(c != nullptr, "null context");
+  CK(cudaStreamSynchronize(c->stream));
+  return H2OK_OK;
+}
+
+// ---------------------------------------------------------------------------------------- device-resident
+int32_t h2ok_hist_synth_fill_dev(h2ok_ctx* c, int32_t shape, uint64_t seed, int64_t row0, int64_t rows, int32_t cols,
+                                 int64_t ld, int32_t na_permille, int32_t weight_mode, float* d_X, float* d_y, float* d_w) {
+  REQUIRE(c != nullptr, "null context");
+  REQUIRE(rows >= 0 && cols > 0 && ld >= rows, "bad shape");
+  REQUIRE(shape == H2OK_SHAPE_HIGGS28 || shape == H2OK_SHAPE_WIDE64 || shape == H2OK_SHAPE_SPARSE, "unknown shape id");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_synth(shape, seed, row0, rows, cols, ld, na_permille, weight_mode, d_X, d_y, d_w, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_col_ranges_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int64_t rows, int32_t cols,
+                                 uint32_t* d_min_enc, uint32_t* d_max_enc) {
+  REQUIRE(c && d_X && d_min_enc && d_max_enc, "null pointer");
+  REQUIRE(rows >= 0 && cols > 0 && ld >= rows, "bad shape");
+  CK(launch_col_ranges(d_X, ld, rows, cols, d_min_enc, d_max_enc, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_target_absmax_dev(h2ok_ctx* c, const float* d_y, const float* d_w, int64_t rows, double* d_absmax) {
+  REQUIRE(c && d_y && d_absmax, "null pointer");
+  CK(launch_target_absmax(d_y, d_w, rows, d_absmax, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_quantize_rows_dev(h2ok_ctx* c, const float* d_y, const float* d_w, int64_t rows, const h2ok_quant* q,
+                                    int32_t* d_wq, int32_t* d_wyq, int32_t* d_wyyq) {
+  REQUIRE(c && d_y && q && d_wyq && d_wyyq, "null pointer");
+  REQUIRE(!q->weighted || (d_w && d_wq), "weighted quantisation needs w and wq");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_quantize_rows(d_y, d_w, rows, *q, d_wq, d_wyq, d_wyyq, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_bin_dev(h2ok_ctx* c, const float* d_x, int64_t n, const h2ok_col_desc* desc, int32_t* d_bins) {
+  REQUIRE(c && d_x && desc && d_bins, "null pointer");
+  if (n == 0) return H2OK_OK;
+  CK(launch_bin(d_x, n, *desc, d_bins, c->stream));
+  return H2OK_OK;
+}
+
+static int32_t check_level_shape(int32_t n_nodes, int32_t cols, int32_t max_bins) {
+  if (n_nodes < 1 || n_nodes > H2OK_MAX_LEVEL_NODES) return fail(H2OK_ERR_ARG, "%s", "n_nodes out of range");
+  if (cols < 1) return fail(H2OK_ERR_ARG, "%s", "cols < 1");
+  if (max_bins < 1 || max_bins > H2OK_MAX_BINS) return fail(H2OK_ERR_UNSUPPORTED, "%s", "max_bins outside [1, H2OK_MAX_BINS]");
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_build_level_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int64_t rows, int32_t cols,
+                                  const int32_t* d_nid, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq,
+                                  int32_t n_nodes, const h2ok_col_desc* d_descs, int32_t max_bins, int32_t clear,
+                                  int64_t* d_acc, uint32_t* d_min2_enc, uint32_t* d_maxin_enc) {
+  REQUIRE(c && d_X && d_nid && d_wyq && d_wyyq && d_descs && d_acc && d_min2_enc && d_maxin_enc, "null pointer");
+  int32_t rc = check_level_shape(n_nodes, cols, max_bins);
+  if (rc) return rc;
+  REQUIRE(rows >= 0 && ld >= rows && ld % 4 == 0, "ld must be >= rows and a multiple of 4");
+  REQUIRE(((uintptr_t)d_X % 16) == 0 && ((uintptr_t)d_nid % 16) == 0 && ((uintptr_t)d_wyq % 16) == 0 &&
+              ((uintptr_t)d_wyyq % 16) == 0 && ((uintptr_t)d_wq % 16) == 0,
+          "row arrays must be 16-byte aligned");
+  const int nb1 = max_bins + 1;
+  const int64_t ncell = (int64_t)n_nodes * cols;
+  if (clear) {
+    CK(cudaMemsetAsync(d_acc, 0, sizeof(int64_t) * (size_t)(ncell * nb1 * 3), c->stream));
+    CK(launch_init_enc(d_min2_enc, d_maxin_enc, ncell, c->stream));
+  }
+  HistPlan plan = plan_hist(n_nodes, cols, rows, nb1);
+  c->stats.passes = plan.passes;
+  c->stats.copies = plan.copies;
+  c->stats.launches = plan.passes + (clear ? 2 : 0);
+  c->stats.algo_bytes = (double)rows * cols * 4.0 + (double)rows * (4.0 + 4.0 + 4.0 + (d_wq ? 4.0 : 0.0)) +
+                        (double)ncell * nb1 * 3 * 8.0;
+  if (rows == 0) return H2OK_OK;
+  HistArgs a{};
+  a.X = d_X; a.ld = ld; a.rows = rows; a.cols = cols; a.nid = d_nid; a.wq = d_wq; a.wyq = d_wyq; a.wyyq = d_wyyq;
+  a.descs = d_descs; a.nb1 = nb1; a.acc = d_acc; a.min2_enc = d_min2_enc; a.maxin_enc = d_maxin_enc;
+  CK(launch_hist_build(a, plan, n_nodes, d_wq != nullptr, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_finalize_level_dev(h2ok_ctx* c, const int64_t* d_acc, const uint32_t* d_min2_enc,
+                                     const uint32_t* d_maxin_enc, int32_t n_nodes, int32_t cols, int32_t max_bins,
+                                     const h2ok_quant* q, double* d_hist, float* d_min2, float* d_maxin) {
+  REQUIRE(c && q, "null pointer");
+  REQUIRE((d_hist == nullptr) == (d_acc == nullptr), "acc and hist go together");
+  REQUIRE((d_min2 == nullptr) == (d_min2_enc == nullptr) && (d_min2 == nullptr) == (d_maxin == nullptr) &&
+              (d_min2 == nullptr) == (d_maxin_enc == nullptr),
+          "encoded and decoded ranges go together");
+  int32_t rc = check_level_shape(n_nodes, cols, max_bins);
+  if (rc) return rc;
+  CK(launch_finalize(d_acc, d_min2_enc, d_maxin_enc, (int64_t)n_nodes * cols, max_bins + 1, *q, d_hist, d_min2, d_maxin,
+                     c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_find_splits_dev(h2ok_ctx* c, const double* d_hist, const h2ok_col_desc* d_descs, int32_t n_nodes,
+                                  int32_t cols, int32_t max_bins, double min_rows, double min_split_improvement,
+                                  h2ok_split* d_splits) {
+  REQUIRE(c && d_hist && d_descs && d_splits, "null pointer");
+  int32_t rc = check_level_shape(n_nodes, cols, max_bins);
+  if (rc) return rc;
+  CK(launch_find_splits(d_hist, d_descs, n_nodes, cols, max_bins + 1, min_rows, min_split_improvement, d_splits, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_next_level_dev(h2ok_ctx* c, const h2ok_split* d_splits, const h2ok_col_desc* d_descs,
+                                 const float* d_min2, const float* d_maxin, int32_t n_nodes, int32_t cols,
+                                 const h2ok_params* params, int32_t depth, h2ok_col_desc* d_child_descs,
+                                 int32_t* d_child_ids, int32_t* d_n_children) {
+  (void)depth;
+  REQUIRE(c && d_splits && d_descs && d_min2 && d_maxin && params && d_child_descs && d_child_ids && d_n_children,
+          "null pointer");
+  int32_t rc = check_level_shape(n_nodes, cols, params->nbins);
+  if (rc) return rc;
+  CK(c->tmp_descs.ensure((size_t)2 * n_nodes * cols));
+  CK(c->tmp_valid.ensure((size_t)2 * n_nodes));
+  CK(launch_next_level(d_splits, d_descs, d_min2, d_maxin, n_nodes, cols, *params, c->tmp_descs.p, c->tmp_valid.p,
+                       d_child_descs, d_child_ids, d_n_children, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int64_t rows, const h2ok_split* d_splits,
+                                   const int32_t* d_child_ids, int32_t gid_base, int32_t n_nodes, int32_t* d_nid,
+                                   int32_t* d_leaf) {
+  REQUIRE(c && d_X && d_splits && d_child_ids && d_nid, "null pointer");
+  REQUIRE(n_nodes >= 1 && rows >= 0, "bad shape");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_apply_splits(d_X, ld, rows, d_splits, d_child_ids, gid_base, n_nodes, d_nid, d_leaf, c->stream));
+  return H2OK_OK;
+}
+
+// ---------------------------------------------------------------------------------------- host-buffer API
+int32_t h2ok_hist_set_data_host(h2ok_ctx* c, const float* const* cols_host, int64_t rows, int32_t cols) {
+  REQUIRE(c && cols_host, "null pointer");
+  REQUIRE(rows > 0 && cols > 0, "empty data");
+  CK(cudaSetDevice(c->device));
+  int64_t ld = (rows + 63) / 64 * 64;
+  CK(c->X.ensure((size_t)ld * cols));
+  for (int32_t j = 0; j < cols; j++) {
+    REQUIRE(cols_host[j] != nullptr, "null column");
+    CK(cudaMemcpyAsync(c->X.p + (int64_t)j * ld, cols_host[j], sizeof(float) * (size_t)rows, cudaMemcpyHostToDevice, c->stream));
+    if (ld > rows) CK(cudaMemsetAsync(c->X.p + (int64_t)j * ld + rows, 0, sizeof(float) * (size_t)(ld - rows), c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  c->rows = rows;
+  c->ld = ld;
+  c->cols = cols;
+  c->have_data = true;
+  c->have_targets = false;
+  c->level_built = c->splits_found = c->children_made = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_set_targets_host(h2ok_ctx* c, const float* y_host, const float* w_host) {
+  REQUIRE(c && y_host, "null pointer");
+  if (!c->have_data) return fail(H2OK_ERR_STATE, "%s", "set_targets_host before set_data_host");
+  CK(cudaSetDevice(c->device));
+  const int64_t n = c->rows;
+  const size_t pad = (size_t)(n + 3) / 4 * 4;
+  CK(c->y.ensure(pad)); CK(c->nid.ensure(pad)); CK(c->leaf.ensure(pad)); CK(c->wyq.ensure(pad)); CK(c->wyyq.ensure(pad));
+  CK(c->absmax.ensure(3));
+  c->weighted = w_host != nullptr;
+  if (c->weighted) { CK(c->w.ensure(pad)); CK(c->wq.ensure(pad)); }
+  CK(cudaMemcpyAsync(c->y.p, y_host, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  if (c->weighted) CK(cudaMemcpyAsync(c->w.p, w_host, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  CK(launch_target_absmax(c->y.p, c->weighted ? c->w.p : nullptr, n, c->absmax.p, c->stream));
+  double m[3];
+  CK(cudaMemcpyAsync(m, c->absmax.p, sizeof(m), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  h2ok_hist_choose_quant(m, c->weighted ? 1 : 0, 26, &c->q);
+  CK(launch_quantize_rows(c->y.p, c->weighted ? c->w.p : nullptr, n, c->q, c->weighted ? c->wq.p : nullptr, c->wyq.p,
+                          c->wyyq.p, c->stream));
+  CK(cudaMemsetAsync(c->nid.p, 0, sizeof(int32_t) * (size_t)n, c->stream));
+  CK(cudaMemsetAsync(c->leaf.p, 0xFF, sizeof(int32_t) * (size_t)n, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->gid_base = 0;
+  c->have_targets = true;
+  c->level_built = c->splits_found = c->children_made = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_root_descs_from_ranges(const float* col_min, const float* col_max, int32_t cols,
+                                         const h2ok_params* params, const int32_t* is_int, h2ok_col_desc* descs_out) {
+  REQUIRE(col_min && col_max && params && descs_out && cols > 0, "null pointer");
+  for (int j = 0; j < cols; j++) {
+    float lo = col_min[j] + 0.0f, hi = col_max[j] + 0.0f;
+    int ii = is_int ? is_int[j] : 0;
+    if (ii > 1) return fail(H2OK_ERR_UNSUPPORTED, "%s", "categorical columns (is_int == 2) are not supported");
+    h2ok_col_desc* o = &descs_out[j];
+    memset(o, 0, sizeof(*o));
+    o->is_int = ii;
+    if (!(lo < hi) || isinf(lo) || isinf(hi)) continue;  // DHistogram.initialHist: constant / all-NA columns
+    h_make_desc((double)lo, h_find_maxex((double)hi, ii), ii, params->nbins_top_level, o);
+  }
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_choose_quant(const double* m, int32_t weighted, int32_t qbits, h2ok_quant* q) {
+  REQUIRE(m && q, "null pointer");
+  REQUIRE(qbits >= 8 && qbits <= 30, "qbits outside [8,30]");
+  q->weighted = weighted ? 1 : 0;
+  q->qbits = qbits;
+  q->scale_w = weighted ? pow2_scale(m[0], qbits) : 1.0;
+  q->scale_wy = pow2_scale(m[1], qbits);
+  q->scale_wyy = pow2_scale(m[2], qbits);
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_root_descs(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int, h2ok_col_desc* descs_out) {
+  REQUIRE(c && params && descs_out, "null pointer");
+  if (!c->have_data) return fail(H2OK_ERR_STATE, "%s", "root_descs before set_data_host");
+  CK(cudaSetDevice(c->device));
+  CK(c->cmin.ensure(c->cols)); CK(c->cmax.ensure(c->cols));
+  CK(launch_col_ranges(c->X.p, c->ld, c->rows, c->cols, c->cmin.p, c->cmax.p, c->stream));
+  std::vector<uint32_t> mn(c->cols), mx(c->cols);
+  CK(cudaMemcpyAsync(mn.data(), c->cmin.p, sizeof(uint32_t) * c->cols, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(mx.data(), c->cmax.p, sizeof(uint32_t) * c->cols, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  std::vector<float> lo(c->cols), hi(c->cols);
+  for (int j = 0; j < c->cols; j++) {
+    uint32_t lo_b = dec_f32_bits(mn[j]), hi_b = dec_f32_bits(mx[j]);
+    memcpy(&lo[j], &lo_b, 4);
+    memcpy(&hi[j], &hi_b, 4);
+  }
+  return h2ok_hist_root_descs_from_ranges(lo.data(), hi.data(), c->cols, params, is_int, descs_out);
+}
+
+int32_t h2ok_hist_build_level(h2ok_ctx* c, int32_t n_nodes, const h2ok_col_desc* descs, int32_t max_bins,
+                              double* hist_out, float* min2_out, float* maxin_out) {
+  REQUIRE(c && descs, "null pointer");
+  if (!c->have_targets) return fail(H2OK_ERR_STATE, "%s", "build_level before set_targets_host");
+  int32_t rc = check_level_shape(n_nodes, c->cols, max_bins);
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device));
+  const int nb1 = max_bins + 1;
+  const size_t ncell = (size_t)n_nodes * c->cols;
+  CK(c->descs.ensure(ncell)); CK(c->acc.ensure(ncell * nb1 * 3)); CK(c->hist.ensure(ncell * nb1 * 3));
+  CK(c->mn.ensure(ncell)); CK(c->mx.ensure(ncell)); CK(c->min2.ensure(ncell)); CK(c->maxin.ensure(ncell));
+  CK(cudaMemcpyAsync(c->descs.p, descs, sizeof(h2ok_col_desc) * ncell, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaEventRecord(c->ev0, c->stream));
+  rc = h2ok_hist_build_level_dev(c, c->X.p, c->ld, c->rows, c->cols, c->nid.p, c->weighted ? c->wq.p : nullptr, c->wyq.p,
+                                 c->wyyq.p, n_nodes, c->descs.p, max_bins, 1, c->acc.p, c->mn.p, c->mx.p);
+  if (rc) return rc;
+  rc = h2ok_hist_finalize_level_dev(c, c->acc.p, c->mn.p, c->mx.p, n_nodes, c->cols, max_bins, &c->q, c->hist.p,
+                                    c->min2.p, c->maxin.p);
+  if (rc) return rc;
+  c->stats.launches += 2;
+  CK(cudaEventRecord(c->ev1, c->stream));
+  if (hist_out) CK(cudaMemcpyAsync(hist_out, c->hist.p, sizeof(double) * ncell * nb1 * 3, cudaMemcpyDeviceToHost, c->stream));
+  if (min2_out) CK(cudaMemcpyAsync(min2_out, c->min2.p, sizeof(float) * ncell, cudaMemcpyDeviceToHost, c->stream));
+  if (maxin_out) CK(cudaMemcpyAsync(maxin_out, c->maxin.p, sizeof(float) * ncell, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaEventElapsedTime(&c->stats.build_ms, c->ev0, c->ev1));
+  c->n_nodes = n_nodes;
+  c->max_bins = max_bins;
+  c->level_built = true;
+  c->splits_found = c->children_made = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_find_splits(h2ok_ctx* c, double min_rows, double min_split_improvement, h2ok_split* splits_out) {
+  REQUIRE(c != nullptr, "null context");
+  if (!c->level_built) return fail(H2OK_ERR_STATE, "%s", "find_splits before build_level");
+  CK(cudaSetDevice(c->device));
+  CK(c->splits.ensure(c->n_nodes));
+  int32_t rc = h2ok_hist_find_splits_dev(c, c->hist.p, c->descs.p, c->n_nodes, c->cols, c->max_bins, min_rows,
+                                         min_split_improvement, c->splits.p);
+  if (rc) return rc;
+  if (splits_out) CK(cudaMemcpyAsync(splits_out, c->splits.p, sizeof(h2ok_split) * c->n_nodes, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->splits_found = true;
+  c->children_made = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_next_level(h2ok_ctx* c, const h2ok_params* params, int32_t depth, h2ok_col_desc* child_descs_out,
+                             int32_t* child_ids_out, int32_t* n_children_out) {
+  REQUIRE(c && params && n_children_out, "null pointer");
+  if (!c->splits_found) return fail(H2OK_ERR_STATE, "%s", "next_level before find_splits");
+  CK(cudaSetDevice(c->device));
+  const size_t slots = (size_t)2 * c->n_nodes;
+  CK(c->child_descs.ensure(slots * c->cols)); CK(c->child_ids.ensure(slots)); CK(c->n_children.ensure(1));
+  int32_t rc = h2ok_hist_next_level_dev(c, c->splits.p, c->descs.p, c->min2.p, c->maxin.p, c->n_nodes, c->cols, params,
+                                        depth, c->child_descs.p, c->child_ids.p, c->n_children.p);
+  if (rc) return rc;
+  int32_t n = 0;
+  CK(cudaMemcpyAsync(&n, c->n_children.p, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  if (child_ids_out) CK(cudaMemcpyAsync(child_ids_out, c->child_ids.p, sizeof(int32_t) * slots, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (child_descs_out && n > 0)
+    CK(cudaMemcpy(child_descs_out, c->child_descs.p, sizeof(h2ok_col_desc) * (size_t)n * c->cols, cudaMemcpyDeviceToHost));
+  *n_children_out = n;
+  c->children_made = true;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_apply_splits(h2ok_ctx* c) {
+  REQUIRE(c != nullptr, "null context");
+  if (!c->splits_found) return fail(H2OK_ERR_STATE, "%s", "apply_splits before find_splits");
+  CK(cudaSetDevice(c->device));
+  if (!c->children_made) {  // last level of the tree: every side becomes a leaf
+    CK(c->child_ids.ensure((size_t)2 * c->n_nodes));
+    CK(cudaMemsetAsync(c->child_ids.p, 0xFF, sizeof(int32_t) * 2 * (size_t)c->n_nodes, c->stream));
+  }
+  int32_t rc = h2ok_hist_apply_splits_dev(c, c->X.p, c->ld, c->rows, c->splits.p, c->child_ids.p, c->gid_base, c->n_nodes,
+                                          c->nid.p, c->leaf.p);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(c->stream));
+  c->gid_base += c->n_nodes;
+  c->level_built = c->splits_found = c->children_made = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_get_nid_host(h2ok_ctx* c, int32_t* nid_out, int32_t* leaf_out) {
+  REQUIRE(c != nullptr, "null context");
+  if (!c->have_targets) return fail(H2OK_ERR_STATE, "%s", "get_nid_host before set_targets_host");
+  CK(cudaSetDevice(c->device));
+  if (nid_out) CK(cudaMemcpyAsync(nid_out, c->nid.p, sizeof(int32_t) * (size_t)c->rows, cudaMemcpyDeviceToHost, c->stream));
+  if (leaf_out) CK(cudaMemcpyAsync(leaf_out, c->leaf.p, sizeof(int32_t) * (size_t)c->rows, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_get_quant(h2ok_ctx* c, h2ok_quant* out) {
+  REQUIRE(c && out, "null pointer");
+  if (!c->have_targets) return fail(H2OK_ERR_STATE, "%s", "get_quant before set_targets_host");
+  *out = c->q;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_last_level_stats(h2ok_ctx* c, h2ok_stats* out) {
+  REQUIRE(c && out, "null pointer");
+  *out = c->stats;
+  return H2OK_OK;
+}
+
+}  // extern "C"

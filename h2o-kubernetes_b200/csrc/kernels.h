@@ -1,0 +1,61 @@
+// kernels.h — host-side launch interface between capi.cu and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/h2ok_hist.h"
+
+namespace h2ok {
+
+constexpr int kHistThreads = 1024;
+
+struct HistArgs {
+  const float* X;
+  int64_t ld, rows;
+  int cols;
+  const int32_t* nid;
+  const int32_t* wq;  // NULL when unweighted
+  const int32_t* wyq;
+  const int32_t* wyyq;
+  const h2ok_col_desc* descs;  // [n_nodes][cols]
+  int nb1;                     // max_bins + 1
+  int node_base, node_cnt;     // node group handled by this launch
+  int copies;                  // privatised sub-histograms per (node,bin), power of two <= 32
+  int64_t chunk_rows;          // rows per CTA, multiple of 4*kHistThreads
+  int64_t* acc;                // [n_nodes][cols][nb1][3]
+  uint32_t* min2_enc;          // [n_nodes][cols]
+  uint32_t* maxin_enc;
+};
+
+struct HistPlan {
+  int group = 1, passes = 1, copies = 1, chunks = 1;
+  int64_t chunk_rows = 0;
+  size_t smem = 0;
+};
+
+HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1);
+size_t hist_smem_bytes(int node_cnt, int nb1, int copies);
+
+cudaError_t launch_synth(int shape, uint64_t seed, int64_t row0, int64_t rows, int cols, int64_t ld, int na_permille,
+                         int weight_mode, float* X, float* y, float* w, cudaStream_t s);
+cudaError_t launch_init_enc(uint32_t* mn, uint32_t* mx, int64_t n, cudaStream_t s);
+cudaError_t launch_col_ranges(const float* X, int64_t ld, int64_t rows, int cols, uint32_t* mn, uint32_t* mx, cudaStream_t s);
+cudaError_t launch_target_absmax(const float* y, const float* w, int64_t rows, double* out, cudaStream_t s);
+cudaError_t launch_quantize_rows(const float* y, const float* w, int64_t rows, const h2ok_quant& q, int32_t* wq,
+                                 int32_t* wyq, int32_t* wyyq, cudaStream_t s);
+cudaError_t launch_bin(const float* x, int64_t n, const h2ok_col_desc& d, int32_t* out, cudaStream_t s);
+cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_nodes, bool weighted, cudaStream_t s);
+cudaError_t launch_finalize(const int64_t* acc, const uint32_t* mn, const uint32_t* mx, int64_t n_node_cols, int nb1,
+                            const h2ok_quant& q, double* hist, float* min2, float* maxin, cudaStream_t s);
+
+cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
+                               double min_rows, double msi, h2ok_split* splits, cudaStream_t s);
+// tmp_descs: [2*n_nodes][cols] scratch; tmp_valid: [2*n_nodes] scratch
+cudaError_t launch_next_level(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2, const float* maxin,
+                              int n_nodes, int cols, const h2ok_params& p, h2ok_col_desc* tmp_descs, int32_t* tmp_valid,
+                              h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children, cudaStream_t s);
+cudaError_t launch_apply_splits(const float* X, int64_t ld, int64_t rows, const h2ok_split* splits,
+                                const int32_t* child_ids, int gid_base, int n_nodes, int32_t* nid, int32_t* leaf,
+                                cudaStream_t s);
+
+}  // namespace h2ok

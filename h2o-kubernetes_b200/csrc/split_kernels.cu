@@ -1,0 +1,477 @@
+// split_kernels.cu — sm_100a kernels for SURVEY.md §8 rows a6 (score_decide), a7 (findBestSplitPoint + bestCol)
+// and a8 (nextLevelHistos).  Arithmetic mirrors oracle/hist_oracle.c operation for operation with explicit
+// round-to-nearest intrinsics (no FMA contraction), so results are bit-identical to the oracle.
+//
+// a7 exactness note: the oracle's running prefix/suffix sums are sequential fp64 additions.  Histograms produced
+// by this library are exact multiples of a power of two with |sum| < 2^53 quanta, so every partial sum is exact and
+// the warp-shuffle scan below returns the same bits as the sequential loop (and suffix == total - prefix).
+#include <math.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace h2ok {
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kSplitWarps = 8;
+
+struct Cand {  // running best of DTree.findBestSplitPoint
+  double key;  // se_left + se_right
+  double seL, seR, nL, nR, pL, pR;
+  int dist;   // |b - nbins/2|
+  int order;  // position in the sequential scan: 2*b + option; -1 = initial state
+  int bin;
+  int na;
+};
+
+__device__ __forceinline__ bool cand_better(double key, int dist, int order, const Cand& b) {
+  // sequential rule: strictly smaller error, or equal error and strictly closer to the middle; on full ties the
+  // earlier candidate stays
+  if (key < b.key) return true;
+  if (key == b.key) {
+    if (dist < b.dist) return true;
+    if (dist == b.dist && order < b.order) return true;
+  }
+  return false;
+}
+
+__device__ __forceinline__ double se_of(double wyy, double wy, double w) {
+  double se = __dsub_rn(wyy, __ddiv_rn(__dmul_rn(wy, wy), w));
+  return se < 0 ? 0 : se;  // NaN stays NaN, like the Java/C comparison
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+  for (int o = 16; o; o >>= 1) v = __dadd_rn(v, __shfl_xor_sync(kFull, v, o));
+  return v;
+}
+
+__device__ __forceinline__ double warp_incl_scan(double v, int lane) {
+  for (int o = 1; o < 32; o <<= 1) {
+    double t = __shfl_up_sync(kFull, v, o);
+    if (lane >= o) v = __dadd_rn(v, t);
+  }
+  return v;
+}
+
+// One warp evaluates one (node, column).  Returns found != 0 in every lane and the winning candidate in `out`.
+__device__ int warp_best_split_point(const double* __restrict__ vals, int nbins, double min_rows, double msi, int lane,
+                                     Cand& out, double& se_before_out) {
+  if (nbins <= 1) return 0;
+  double W = 0, WY = 0, WYY = 0;
+  for (int b = lane; b < nbins; b += 32) {
+    W = __dadd_rn(W, vals[3 * b]);
+    WY = __dadd_rn(WY, vals[3 * b + 1]);
+    WYY = __dadd_rn(WYY, vals[3 * b + 2]);
+  }
+  W = warp_sum(W);
+  WY = warp_sum(WY);
+  WYY = warp_sum(WYY);
+  const double wNA = vals[3 * nbins], wYNA = vals[3 * nbins + 1], wYYNA = vals[3 * nbins + 2];
+  const double tot = __dadd_rn(W, wNA);
+  if (tot < __dmul_rn(2.0, min_rows)) return 0;
+  const double sy = __dadd_rn(WY, wYNA);
+  const double var = __dsub_rn(__dmul_rn(__dadd_rn(WYY, wYYNA), tot), __dmul_rn(sy, sy));
+  if ((float)var == 0.0f) return 0;
+
+  Cand best;
+  best.key = __dadd_rn(1.7976931348623157e308, 1.7976931348623157e308);  // DBL_MAX + DBL_MAX
+  best.seL = best.seR = 1.7976931348623157e308;
+  best.nL = best.nR = best.pL = best.pR = 0;
+  const int mid = nbins >> 1;
+  best.dist = mid;  // |0 - mid|
+  best.order = -1;
+  best.bin = 0;
+  best.na = H2OK_NA_NONE;
+  const double seNonNA = se_of(WYY, WY, W);
+  double seBefore = seNonNA;
+  if (wNA >= min_rows) {
+    double sall = __dadd_rn(WY, wYNA);
+    double seAll = __dsub_rn(__dadd_rn(WYY, wYYNA), __ddiv_rn(__dmul_rn(sall, sall), __dadd_rn(W, wNA)));
+    double seNA = se_of(wYYNA, wYNA, wNA);
+    best.seL = seNonNA;
+    best.seR = seNA;
+    best.key = __dadd_rn(seNonNA, seNA);
+    best.na = H2OK_NA_VS_REST;
+    seBefore = seAll;
+    best.nL = W;
+    best.pL = WY;
+    best.nR = wNA;
+    best.pR = wYNA;
+  }
+  const Cand init = best;
+  const bool init_nan = !(init.key == init.key);
+
+  double cw = 0, cwy = 0, cwyy = 0;  // carries of the row-wise scan
+  const int nrows = (nbins + 31) / 32;
+  for (int k = 0; k < nrows; k++) {
+    const int b = 32 * k + lane;
+    double v0 = 0, v1 = 0, v2 = 0;
+    if (b < nbins) {
+      v0 = vals[3 * b];
+      v1 = vals[3 * b + 1];
+      v2 = vals[3 * b + 2];
+    }
+    double i0 = warp_incl_scan(v0, lane), i1 = warp_incl_scan(v1, lane), i2 = warp_incl_scan(v2, lane);
+    const double wlo = __dadd_rn(cw, __dsub_rn(i0, v0));  // exclusive prefix: bins [0,b)
+    const double wYlo = __dadd_rn(cwy, __dsub_rn(i1, v1));
+    const double wYYlo = __dadd_rn(cwyy, __dsub_rn(i2, v2));
+    cw = __dadd_rn(cw, __shfl_sync(kFull, i0, 31));
+    cwy = __dadd_rn(cwy, __shfl_sync(kFull, i1, 31));
+    cwyy = __dadd_rn(cwyy, __shfl_sync(kFull, i2, 31));
+    if (b < 1 || b > nbins - 1 || v0 == 0) continue;
+    const double whi = __dsub_rn(W, wlo), wYhi = __dsub_rn(WY, wYlo), wYYhi = __dsub_rn(WYY, wYYlo);
+    if (__dadd_rn(wlo, wNA) < min_rows) continue;
+    if (__dadd_rn(whi, wNA) < min_rows) continue;  // H2O breaks here; whi only shrinks, so skipping is the same
+    const int dist = abs(b - mid);
+    if (wNA == 0) {
+      double selo = se_of(wYYlo, wYlo, wlo), sehi = se_of(wYYhi, wYhi, whi);
+      double key = __dadd_rn(selo, sehi);
+      if (cand_better(key, dist, 2 * b, best) && wlo >= min_rows && whi >= min_rows) {
+        best.key = key; best.seL = selo; best.seR = sehi; best.dist = dist; best.order = 2 * b; best.bin = b;
+        best.nL = wlo; best.nR = whi; best.pL = wYlo; best.pR = wYhi; best.na = H2OK_NA_NONE;
+      }
+    } else {
+      {  // NAs to the left
+        double nl = __dadd_rn(wlo, wNA);
+        double selo = se_of(__dadd_rn(wYYlo, wYYNA), __dadd_rn(wYlo, wYNA), nl), sehi = se_of(wYYhi, wYhi, whi);
+        double key = __dadd_rn(selo, sehi);
+        if (cand_better(key, dist, 2 * b, best) && nl >= min_rows && whi >= min_rows) {
+          best.key = key; best.seL = selo; best.seR = sehi; best.dist = dist; best.order = 2 * b; best.bin = b;
+          best.nL = nl; best.nR = whi; best.pL = __dadd_rn(wYlo, wYNA); best.pR = wYhi; best.na = H2OK_NA_LEFT;
+        }
+      }
+      {  // NAs to the right
+        double nr = __dadd_rn(whi, wNA);
+        double selo = se_of(wYYlo, wYlo, wlo), sehi = se_of(__dadd_rn(wYYhi, wYYNA), __dadd_rn(wYhi, wYNA), nr);
+        double key = __dadd_rn(selo, sehi);
+        if (cand_better(key, dist, 2 * b + 1, best) && wlo >= min_rows && nr >= min_rows) {
+          best.key = key; best.seL = selo; best.seR = sehi; best.dist = dist; best.order = 2 * b + 1; best.bin = b;
+          best.nL = wlo; best.nR = nr; best.pL = wYlo; best.pR = __dadd_rn(wYhi, wYNA); best.na = H2OK_NA_RIGHT;
+        }
+      }
+    }
+  }
+  // cross-lane lexicographic minimum over (key, dist, order); lanes still holding the initial state carry order -1
+  // and the initial key, so the initial state wins every tie exactly as it does in the sequential scan
+  int winner = lane;
+  {
+    double k = best.key;
+    int d = best.dist, o = best.order, wl = lane;
+    for (int off = 16; off; off >>= 1) {
+      double k2 = __shfl_xor_sync(kFull, k, off);
+      int d2 = __shfl_xor_sync(kFull, d, off), o2 = __shfl_xor_sync(kFull, o, off), w2 = __shfl_xor_sync(kFull, wl, off);
+      bool take = (k2 < k) || (k2 == k && (d2 < d || (d2 == d && (o2 < o || (o2 == o && w2 < wl)))));
+      if (take) { k = k2; d = d2; o = o2; wl = w2; }
+    }
+    winner = wl;
+  }
+  if (init_nan) best = init;  // nothing compares better than NaN in the sequential scan
+  else {
+    Cand w;
+    w.key = __shfl_sync(kFull, best.key, winner);
+    w.seL = __shfl_sync(kFull, best.seL, winner);
+    w.seR = __shfl_sync(kFull, best.seR, winner);
+    w.nL = __shfl_sync(kFull, best.nL, winner);
+    w.nR = __shfl_sync(kFull, best.nR, winner);
+    w.pL = __shfl_sync(kFull, best.pL, winner);
+    w.pR = __shfl_sync(kFull, best.pR, winner);
+    w.dist = __shfl_sync(kFull, best.dist, winner);
+    w.order = __shfl_sync(kFull, best.order, winner);
+    w.bin = __shfl_sync(kFull, best.bin, winner);
+    w.na = __shfl_sync(kFull, best.na, winner);
+    best = w;
+  }
+  if (best.bin == 0 && best.na == H2OK_NA_NONE) return 0;
+  if (!(__dadd_rn(best.seL, best.seR) < __dmul_rn(seBefore, __dsub_rn(1.0, msi)))) return 0;
+  if (best.na == H2OK_NA_NONE) best.na = best.nL > best.nR ? H2OK_NA_LEFT : H2OK_NA_RIGHT;
+  best.pL = __ddiv_rn(best.pL, best.nL);
+  best.pR = __ddiv_rn(best.pR, best.nR);
+  out = best;
+  se_before_out = seBefore;
+  return 1;
+}
+
+// DTree.Split.splat for the chosen (node, col, bin): warp-parallel search of the neighbouring non-empty bins.
+__device__ float warp_splat(const double* __restrict__ vals, const h2ok_col_desc& d, int bin, int na, int lane) {
+  if (na == H2OK_NA_VS_REST) return -1.0f;
+  int x = -1, n = d.nbin;
+  for (int b = lane; b < d.nbin; b += 32) {
+    if (vals[3 * b] != 0) {
+      if (b < bin) x = max(x, b);
+      else n = min(n, b);
+    }
+  }
+  x = __reduce_max_sync(kFull, x);
+  n = __reduce_min_sync(kFull, n);
+  double lo = __dadd_rn(d.min, __ddiv_rn((double)(x + 1), d.step));
+  double hi = __dadd_rn(d.min, __ddiv_rn((double)n, d.step));
+  if (d.is_int > 0) lo = d.step == 1 ? __dsub_rn(lo, 1.0) : floor(lo);
+  if (d.is_int > 0) hi = d.step == 1 ? hi : ceil(hi);
+  return (float)__ddiv_rn(__dadd_rn(lo, hi), 2.0);
+}
+
+__global__ void __launch_bounds__(kSplitWarps * 32) find_splits_kernel(const double* __restrict__ hist,
+                                                                      const h2ok_col_desc* __restrict__ descs, int cols,
+                                                                      int nb1, double min_rows, double msi,
+                                                                      h2ok_split* __restrict__ splits) {
+  __shared__ Cand s_best[kSplitWarps];
+  __shared__ double s_se_before[kSplitWarps];
+  __shared__ int s_col[kSplitWarps];
+  __shared__ int s_win;
+  const int g = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  Cand wbest;
+  double wbefore = 0;
+  int wcol = -1;
+  for (int c = warp; c < cols; c += kSplitWarps) {
+    const h2ok_col_desc& d = descs[(int64_t)g * cols + c];
+    if (d.nbin <= 1) continue;
+    const double* vals = hist + ((int64_t)g * cols + c) * nb1 * 3;
+    Cand cand;
+    double before;
+    if (!warp_best_split_point(vals, d.nbin, min_rows, msi, lane, cand, before)) continue;
+    if (wcol < 0 || cand.key < wbest.key) {  // bestCol: strictly smaller se wins, lowest column on ties
+      wbest = cand;
+      wbefore = before;
+      wcol = c;
+    }
+  }
+  if (lane == 0) {
+    s_col[warp] = wcol;
+    if (wcol >= 0) {
+      s_best[warp] = wbest;
+      s_se_before[warp] = wbefore;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int win = -1;
+    for (int w = 0; w < kSplitWarps; w++) {
+      if (s_col[w] < 0) continue;
+      if (win < 0 || s_best[w].key < s_best[win].key || (s_best[w].key == s_best[win].key && s_col[w] < s_col[win])) win = w;
+    }
+    s_win = win;
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  const int win = s_win;
+  h2ok_split out;
+  out.col = -1;
+  out.bin = 0;
+  out.na_dir = 0;
+  out.splat = 0.0f;
+  out.se_before = out.se_left = out.se_right = out.n_left = out.n_right = out.pred_left = out.pred_right = 0;
+  if (win >= 0) {
+    const Cand b = s_best[win];
+    const int c = s_col[win];
+    const h2ok_col_desc d = descs[(int64_t)g * cols + c];
+    const double* vals = hist + ((int64_t)g * cols + c) * nb1 * 3;
+    out.col = c;
+    out.bin = b.bin;
+    out.na_dir = b.na;
+    out.splat = warp_splat(vals, d, b.bin, b.na, lane);
+    out.se_before = s_se_before[win];
+    out.se_left = b.seL;
+    out.se_right = b.seR;
+    out.n_left = b.nL;
+    out.n_right = b.nR;
+    out.pred_left = b.pL;
+    out.pred_right = b.pR;
+  }
+  if (lane == 0) splits[g] = out;
+}
+
+// ---- a8 ---------------------------------------------------------------------------------------------------
+__device__ inline double ulp_d(double x) {  // java.lang.Math.ulp(double)
+  x = fabs(x);
+  if (isinf(x)) return x;
+  if (x == 1.7976931348623157e308) return __dsub_rn(x, nextafter(x, 0.0));
+  return __dsub_rn(nextafter(x, (double)INFINITY), x);
+}
+
+__device__ inline double find_maxex(double maxin, int is_int) {  // DHistogram.find_maxEx
+  double ulp = ulp_d(maxin);
+  if (is_int > 0 && 1 > ulp) ulp = 1;
+  double res = __dadd_rn(maxin, ulp);
+  return isinf(res) ? maxin : res;
+}
+
+__device__ inline int make_desc(double mn, double maxex, int is_int, int nbins, h2ok_col_desc& out) {  // DHistogram.<init>
+  out.min = mn;
+  out.maxex = maxex;
+  out.is_int = is_int;
+  out.nbin = 0;
+  out.step = 0.0;
+  if (!(maxex > mn)) return 0;
+  int xbins = nbins;
+  double step;
+  if (is_int > 0 && __dsub_rn(maxex, mn) <= (double)xbins) {
+    xbins = (int)((long long)maxex - (long long)mn);
+    step = 1.0;
+  } else {
+    step = __ddiv_rn((double)xbins, __dsub_rn(maxex, mn));
+    if (!(step > 0.0) || isinf(step)) return 0;
+  }
+  if (xbins < 1) return 0;
+  out.step = step;
+  out.nbin = xbins;
+  return 1;
+}
+
+__device__ inline bool equals_within_one_small_ulp(double a, double b) {
+  if (isinf(a) || (isinf(b) && (a < b || b < a))) return false;
+  double ua = ulp_d(a), ub = ulp_d(b);
+  double su = ua < ub ? ua : ub;
+  return fabs(__dsub_rn(a, b)) <= su;
+}
+
+__global__ void next_level_descs_kernel(const h2ok_split* __restrict__ splits, const h2ok_col_desc* __restrict__ descs,
+                                        const float* __restrict__ min2, const float* __restrict__ maxin, int n_nodes,
+                                        int cols, h2ok_params p, h2ok_col_desc* __restrict__ tmp,
+                                        int32_t* __restrict__ valid) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)2 * n_nodes * cols) return;
+  const int j = (int)(i % cols);
+  const int slot = (int)(i / cols);
+  const int g = slot >> 1, way = slot & 1;
+  h2ok_col_desc o;
+  o.min = o.maxex = o.step = 0;
+  o.nbin = 0;
+  const h2ok_split s = splits[g];
+  const h2ok_col_desc h = descs[(int64_t)g * cols + j];
+  o.is_int = h.is_int;
+  bool ok = s.col >= 0;
+  if (ok) {
+    double n = way == 0 ? s.n_left : s.n_right;
+    double se = way == 0 ? s.se_left : s.se_right;
+    ok = !(n < p.min_rows) && !(se <= 1e-30) && h.nbin > 0;
+  }
+  if (ok) {
+    int adj_nbins = (h.nbin >> 1) > p.nbins ? (h.nbin >> 1) : p.nbins;
+    double mn = (double)min2[(int64_t)g * cols + j];
+    double mxin = (double)maxin[(int64_t)g * cols + j];
+    ok = !(mxin == mn) && (mn <= mxin);
+    if (ok) {
+      double maxex = find_maxex(mxin, h.is_int);
+      if (s.col == j) {
+        if (s.na_dir == H2OK_NA_VS_REST) {
+          if (way == 1) ok = false;
+        } else {
+          double split = (double)s.splat;
+          if (h.is_int > 0) split = (double)(float)ceil(split);
+          if (way == 0) maxex = split;
+          else mn = split;
+        }
+      }
+      if (ok) {
+        if (mn > maxex) ok = false;
+        else if (equals_within_one_small_ulp(mn, maxex)) ok = false;
+        else if (isinf(__ddiv_rn((double)adj_nbins, __dsub_rn(maxex, mn)))) ok = false;
+        else if (h.is_int > 0 && !(__dadd_rn(mn, 1.0) < maxex)) ok = false;
+        if (ok) {
+          h2ok_col_desc t;
+          if (make_desc(mn, maxex, h.is_int, adj_nbins, t)) {
+            o = t;
+            atomicOr(&valid[slot], 1);
+          }
+        }
+      }
+    }
+  }
+  tmp[i] = o;
+}
+
+__global__ void __launch_bounds__(1024) next_level_compact_kernel(const h2ok_col_desc* __restrict__ tmp,
+                                                                  const int32_t* __restrict__ valid, int n_nodes, int cols,
+                                                                  h2ok_col_desc* __restrict__ child_descs,
+                                                                  int32_t* __restrict__ child_ids,
+                                                                  int32_t* __restrict__ n_children) {
+  __shared__ int s_part[1024];
+  __shared__ int s_ids[2 * H2OK_MAX_LEVEL_NODES];
+  const int slots = 2 * n_nodes;
+  const int per = (slots + 1023) / 1024;
+  const int lo = threadIdx.x * per, hi = min(slots, lo + per);
+  int cnt = 0;
+  for (int sl = lo; sl < hi; sl++) cnt += valid[sl] ? 1 : 0;
+  s_part[threadIdx.x] = cnt;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {  // Hillis-Steele inclusive scan of the per-thread counts
+    int t = threadIdx.x >= o ? s_part[threadIdx.x - o] : 0;
+    __syncthreads();
+    s_part[threadIdx.x] += t;
+    __syncthreads();
+  }
+  int run = s_part[threadIdx.x] - cnt;
+  for (int sl = lo; sl < hi; sl++) {
+    int id = valid[sl] ? run++ : -1;
+    s_ids[sl] = id;
+    child_ids[sl] = id;
+  }
+  if (threadIdx.x == 1023) *n_children = s_part[1023];
+  __syncthreads();
+  const int64_t total = (int64_t)slots * cols;
+  for (int64_t i = threadIdx.x; i < total; i += 1024) {
+    int sl = (int)(i / cols), j = (int)(i % cols);
+    int id = s_ids[sl];
+    if (id >= 0) child_descs[(int64_t)id * cols + j] = tmp[i];
+  }
+}
+
+// ---- a6 ---------------------------------------------------------------------------------------------------
+__global__ void apply_splits_kernel(const float* __restrict__ X, int64_t ld, int64_t rows,
+                                    const h2ok_split* __restrict__ splits, const int32_t* __restrict__ child_ids,
+                                    int gid_base, int n_nodes, int32_t* __restrict__ nid, int32_t* __restrict__ leaf) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  int g = nid[r];
+  if (g < 0 || g >= n_nodes) return;
+  const int col = splits[g].col;
+  if (col < 0) {
+    nid[r] = -1;
+    if (leaf) leaf[r] = (gid_base + g) * 3;
+    return;
+  }
+  const int na = splits[g].na_dir;
+  const float splat = splits[g].splat;
+  const float d = X[(int64_t)col * ld + r];
+  int way;
+  if (d != d) way = (na == H2OK_NA_LEFT) ? 0 : 1;
+  else if (na == H2OK_NA_VS_REST) way = 0;
+  else way = d >= splat ? 1 : 0;
+  const int ch = child_ids[2 * g + way];
+  nid[r] = ch;
+  if (ch < 0 && leaf) leaf[r] = (gid_base + g) * 3 + 1 + way;
+}
+
+}  // namespace
+
+cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
+                               double min_rows, double msi, h2ok_split* splits, cudaStream_t s) {
+  find_splits_kernel<<<n_nodes, kSplitWarps * 32, 0, s>>>(hist, descs, cols, nb1, min_rows, msi, splits);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_next_level(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2, const float* maxin,
+                              int n_nodes, int cols, const h2ok_params& p, h2ok_col_desc* tmp_descs, int32_t* tmp_valid,
+                              h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children, cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(tmp_valid, 0, sizeof(int32_t) * 2 * (size_t)n_nodes, s);
+  if (e != cudaSuccess) return e;
+  int64_t n = (int64_t)2 * n_nodes * cols;
+  next_level_descs_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(splits, descs, min2, maxin, n_nodes, cols, p,
+                                                                      tmp_descs, tmp_valid);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  next_level_compact_kernel<<<1, 1024, 0, s>>>(tmp_descs, tmp_valid, n_nodes, cols, child_descs, child_ids, n_children);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_apply_splits(const float* X, int64_t ld, int64_t rows, const h2ok_split* splits,
+                                const int32_t* child_ids, int gid_base, int n_nodes, int32_t* nid, int32_t* leaf,
+                                cudaStream_t s) {
+  apply_splits_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(X, ld, rows, splits, child_ids, gid_base, n_nodes,
+                                                                    nid, leaf);
+  return cudaGetLastError();
+}
+
+}  // namespace h2ok

@@ -1,0 +1,283 @@
+"""Host-side mirror of the histogram path: one rank's resident shard (CudaShard) and the per-level loop
+(LevelDriver) that H2O-3 runs as SharedTree.buildLayer → ScoreBuildHistogram2 (map over rows) → MRTask.reduce
+(DHistogram.add) → DTree.findBestSplitPoint → Split.nextLevelHistos → score_decide.
+
+PyTorch is plumbing only: device memory, the CUDA stream, and torch.distributed for the one real exchange step
+(the histogram reduce).  All arithmetic happens in libh2ok_hist.so through the C ABI; there is no CPU path here.
+
+Rows are sharded across ranks; descriptors, splits and child ids are replicated.  Because the
+accumulators are integers, the all-reduce is exact and every rank derives bit-identical splits.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import abi, capi
+
+_I32_SIGN = -(2**31)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class CudaShard:
+    """One GPU's rows: column-major fp32 X [cols, ld], targets, row→node map, and the level buffers."""
+
+    def __init__(self, device=0, max_level_nodes=128):
+        self.lib = capi.load()
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        h = C.c_void_p()
+        self.lib.call("h2ok_hist_create", device, C.byref(h))
+        self.ctx = h
+        self.use_current_stream()
+        self.max_level_nodes = max_level_nodes
+        self.rows = self.cols = self.ld = 0
+        self.X = self.y = self.w = None
+        self.weighted = False
+        self.quant = None
+        self._level_cap = None
+
+    def close(self):
+        if self.ctx is not None:
+            self.lib.call("h2ok_hist_destroy", self.ctx)
+            self.ctx = None
+
+    def use_current_stream(self):
+        """Kernels go on torch's current stream so torch.cuda.Event timing and NCCL ordering see them."""
+        self.lib.call("h2ok_hist_set_stream", self.ctx, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+
+    # ---- data -------------------------------------------------------------------------------------------
+    def _alloc_rows(self, rows, cols, weighted):
+        self.rows, self.cols = rows, cols
+        self.ld = (rows + 63) // 64 * 64
+        dev = self.device
+        self.X = torch.empty((cols, self.ld), dtype=torch.float32, device=dev)
+        self.y = torch.empty(self.ld, dtype=torch.float32, device=dev)
+        self.w = torch.empty(self.ld, dtype=torch.float32, device=dev) if weighted else None
+        self.weighted = weighted
+        self.nid = torch.zeros(self.ld, dtype=torch.int32, device=dev)
+        self.leaf = torch.full((self.ld,), -1, dtype=torch.int32, device=dev)
+        self.wq = torch.empty(self.ld, dtype=torch.int32, device=dev) if weighted else None
+        self.wyq = torch.empty(self.ld, dtype=torch.int32, device=dev)
+        self.wyyq = torch.empty(self.ld, dtype=torch.int32, device=dev)
+
+    def set_data_synth(self, shape, seed, row0, rows, cols, na_permille=0, weight_mode=0):
+        """Counter-based generator: this rank fills rows [row0,row0+rows) of the global matrix."""
+        self._alloc_rows(rows, cols, weight_mode != 0)
+        self.lib.call("h2ok_hist_synth_fill_dev", self.ctx, shape, seed, row0, rows, cols, self.ld, na_permille,
+                      weight_mode, _ptr(self.X), _ptr(self.y), _ptr(self.w))
+
+    def set_data_tensors(self, X, y, w=None):
+        """X: [cols, rows] fp32 (host or device), copied into the padded column-major layout."""
+        cols, rows = X.shape
+        self._alloc_rows(rows, cols, w is not None)
+        self.X[:, :rows].copy_(X, non_blocking=True)
+        self.X[:, rows:].zero_()
+        self.set_targets(y, w)
+
+    def set_targets(self, y, w=None):
+        self.y[: self.rows].copy_(y, non_blocking=True)
+        if self.weighted:
+            self.w[: self.rows].copy_(w, non_blocking=True)
+
+    def synth_targets(self, seed, row0):
+        self.lib.call("h2ok_hist_synth_fill_dev", self.ctx, abi.SHAPE_HIGGS28, seed, row0, self.rows, self.cols, self.ld,
+                      0, 1 if self.weighted else 0, None, _ptr(self.y), _ptr(self.w))
+
+    # ---- per-tree set-up ---------------------------------------------------------------------------------
+    def col_ranges(self):
+        mn = torch.empty(self.cols, dtype=torch.int32, device=self.device)
+        mx = torch.empty(self.cols, dtype=torch.int32, device=self.device)
+        self.lib.call("h2ok_hist_col_ranges_dev", self.ctx, _ptr(self.X), self.ld, self.rows, self.cols, _ptr(mn), _ptr(mx))
+        return mn, mx
+
+    def target_absmax(self):
+        out = torch.empty(3, dtype=torch.float64, device=self.device)
+        self.lib.call("h2ok_hist_target_absmax_dev", self.ctx, _ptr(self.y), _ptr(self.w), self.rows, _ptr(out))
+        return out
+
+    def quantize(self, quant):
+        self.quant = quant
+        self.lib.call("h2ok_hist_quantize_rows_dev", self.ctx, _ptr(self.y), _ptr(self.w), self.rows, C.byref(quant),
+                      _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq))
+
+    def reset_nodes(self):
+        self.nid.zero_()
+        self.leaf.fill_(-1)
+
+    # ---- level buffers -----------------------------------------------------------------------------------
+    def ensure_level_buffers(self, max_nodes, max_bins):
+        key = (max_nodes, max_bins, self.cols)
+        if self._level_cap == key:
+            return
+        dev, cols, nb1 = self.device, self.cols, max_bins + 1
+        self.descs = torch.zeros((max_nodes, cols, abi.COL_DESC.itemsize), dtype=torch.uint8, device=dev)
+        self.child_descs = torch.zeros((2 * max_nodes, cols, abi.COL_DESC.itemsize), dtype=torch.uint8, device=dev)
+        self.acc = torch.zeros((max_nodes, cols, nb1, 3), dtype=torch.int64, device=dev)
+        self.hist = torch.zeros((max_nodes, cols, nb1, 3), dtype=torch.float64, device=dev)
+        self.mn = torch.zeros((max_nodes, cols), dtype=torch.int32, device=dev)
+        self.mx = torch.zeros((max_nodes, cols), dtype=torch.int32, device=dev)
+        self.min2 = torch.zeros((max_nodes, cols), dtype=torch.float32, device=dev)
+        self.maxin = torch.zeros((max_nodes, cols), dtype=torch.float32, device=dev)
+        self.splits = torch.zeros((max_nodes, abi.SPLIT.itemsize), dtype=torch.uint8, device=dev)
+        self.child_ids = torch.zeros(2 * max_nodes, dtype=torch.int32, device=dev)
+        self.n_children = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._level_cap = key
+        self.max_bins = max_bins
+
+    def upload_descs(self, descs_np):
+        d = np.ascontiguousarray(descs_np, abi.COL_DESC).reshape(-1, self.cols)
+        n = d.shape[0]
+        self.descs[:n].copy_(torch.from_numpy(d.view(np.uint8).reshape(n, self.cols, -1)))
+        return n
+
+    def adopt_children(self, n):
+        """The children computed by next_level become the next level's descriptors (device-to-device)."""
+        self.descs[:n].copy_(self.child_descs[:n])
+
+    # ---- a3/a4: local histogram --------------------------------------------------------------------------
+    def build_level(self, n_nodes):
+        self.lib.call("h2ok_hist_build_level_dev", self.ctx, _ptr(self.X), self.ld, self.rows, self.cols, _ptr(self.nid),
+                      _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), n_nodes, _ptr(self.descs), self.max_bins, 1,
+                      _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
+        return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
+
+    def finalize_level(self, n_nodes):
+        self.lib.call("h2ok_hist_finalize_level_dev", self.ctx, _ptr(self.acc), _ptr(self.mn), _ptr(self.mx), n_nodes,
+                      self.cols, self.max_bins, C.byref(self.quant), _ptr(self.hist), _ptr(self.min2), _ptr(self.maxin))
+
+    # ---- a7 / a8 / a6 ------------------------------------------------------------------------------------
+    def find_splits(self, n_nodes, min_rows, msi):
+        self.lib.call("h2ok_hist_find_splits_dev", self.ctx, _ptr(self.hist), _ptr(self.descs), n_nodes, self.cols,
+                      self.max_bins, float(min_rows), float(msi), _ptr(self.splits))
+
+    def next_level(self, n_nodes, params, depth):
+        self.lib.call("h2ok_hist_next_level_dev", self.ctx, _ptr(self.splits), _ptr(self.descs), _ptr(self.min2),
+                      _ptr(self.maxin), n_nodes, self.cols, C.byref(params), depth, _ptr(self.child_descs),
+                      _ptr(self.child_ids), _ptr(self.n_children))
+        return int(self.n_children.item())  # the one host sync per level: how many nodes the next level has
+
+    def no_children(self, n_nodes):
+        self.child_ids[: 2 * n_nodes].fill_(-1)
+
+    def apply_splits(self, n_nodes, gid_base):
+        self.lib.call("h2ok_hist_apply_splits_dev", self.ctx, _ptr(self.X), self.ld, self.rows, _ptr(self.splits),
+                      _ptr(self.child_ids), gid_base, n_nodes, _ptr(self.nid), _ptr(self.leaf))
+
+    # ---- host copies (tests, tree assembly) --------------------------------------------------------------
+    def splits_np(self, n):
+        return self.splits[:n].cpu().numpy().view(abi.SPLIT).reshape(n).copy()
+
+    def descs_np(self, n):
+        return self.descs[:n].cpu().numpy().view(abi.COL_DESC).reshape(n, self.cols).copy()
+
+    def stats(self):
+        s = abi.Stats()
+        self.lib.call("h2ok_hist_last_level_stats", self.ctx, C.byref(s))
+        return s
+
+
+def _world():
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def reduce_level(acc, mn, mx):
+    """a5 — MRTask.reduce / DHistogram.add across ranks: integer sum of the fixed-point histogram, integer min / max
+    of the encoded observed ranges.  The encodings are unsigned; flipping the top bit makes signed min/max agree."""
+    if _world() == 1:
+        return
+    dist.all_reduce(acc, op=dist.ReduceOp.SUM)
+    mn ^= _I32_SIGN
+    mx ^= _I32_SIGN
+    dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    mn ^= _I32_SIGN
+    mx ^= _I32_SIGN
+
+
+class LevelDriver:
+    """SharedTree.buildLayer loop over one shard per rank.  `shard` is a CudaShard (tests substitute a CPU double
+    with the same methods to exercise the reduce logic under gloo)."""
+
+    def __init__(self, shard, params, is_int=None, qbits=26):
+        self.shard = shard
+        self.params = params
+        self.is_int = None if is_int is None else np.ascontiguousarray(is_int, np.int32)
+        self.qbits = qbits
+        self.lib = shard.lib
+        self.max_bins = max(params.nbins, params.nbins_top_level)
+        self.root = None
+
+    # -- once per data set: root descriptors from the global column ranges
+    def prepare_data(self):
+        mn, mx = self.shard.col_ranges()
+        if _world() > 1:
+            mn ^= _I32_SIGN
+            mx ^= _I32_SIGN
+            dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            mn ^= _I32_SIGN
+            mx ^= _I32_SIGN
+        lo = abi.decode_f32(mn.cpu().numpy().view(np.uint32))
+        hi = abi.decode_f32(mx.cpu().numpy().view(np.uint32))
+        out = np.zeros(self.shard.cols, abi.COL_DESC)
+        self.lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi), self.shard.cols,
+                      C.byref(self.params), abi.ptr(self.is_int), abi.ptr(out))
+        self.root = out
+        max_nodes = min(2 ** max(self.params.max_depth - 1, 0), 4096)
+        self.shard.ensure_level_buffers(max_nodes, self.max_bins)
+        return out
+
+    # -- once per tree: common fixed-point scales, quantised targets, all rows at the root
+    def prepare_tree(self):
+        m = self.shard.target_absmax()
+        if _world() > 1:
+            dist.all_reduce(m, op=dist.ReduceOp.MAX)
+        q = abi.Quant()
+        mh = m.cpu().numpy()
+        self.lib.call("h2ok_hist_choose_quant", abi.ptr(mh), 1 if self.shard.weighted else 0, self.qbits, C.byref(q))
+        self.shard.quantize(q)
+        self.shard.reset_nodes()
+        self.n_nodes = self.shard.upload_descs(self.root.reshape(1, -1))
+        self.gid_base = 0
+        self.depth = 0
+        return q
+
+    # -- one level = one "step" of the benchmark
+    def level(self, last=None, inspect=None):
+        """Build, reduce, search, derive children, route.  `inspect(driver, n_nodes, n_children)` runs after the
+        children are known and before the row map and descriptors are overwritten (tests read the level there)."""
+        sh, p = self.shard, self.params
+        n = self.n_nodes
+        acc, mn, mx = sh.build_level(n)
+        reduce_level(acc, mn, mx)
+        sh.finalize_level(n)
+        sh.find_splits(n, p.min_rows, p.min_split_improvement)
+        last = (self.depth + 1 >= p.max_depth) if last is None else last
+        if last:
+            sh.no_children(n)
+            nch = 0
+        else:
+            nch = sh.next_level(n, p, self.depth)
+        if inspect:
+            inspect(self, n, nch)
+        sh.apply_splits(n, self.gid_base)
+        self.gid_base += n
+        self.depth += 1
+        done_nodes = n
+        if nch > 0:
+            sh.adopt_children(nch)
+        self.n_nodes = nch
+        return done_nodes, nch
+
+    def train_tree(self, inspect=None):
+        self.prepare_tree()
+        levels = 0
+        while self.n_nodes > 0 and self.depth < self.params.max_depth:
+            self.level(inspect=inspect)
+            levels += 1
+        return levels

@@ -174,6 +174,13 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
                                    const int32_t* d_child_ids, int32_t gid_base, int32_t n_nodes, int32_t* d_nid,
                                    int32_t* d_leaf);
 
+/* a1 — DHistogram.initialHist from column ranges that the caller has already combined across ranks (plain host
+ * arithmetic, no device work): constant / all-NA / infinite-range columns get nbin 0. */
+int32_t h2ok_hist_root_descs_from_ranges(const float* col_min, const float* col_max, int32_t cols,
+                                         const h2ok_params* params, const int32_t* is_int, h2ok_col_desc* descs_out);
+/* Power-of-two fixed-point scales from max|w|, max|w*y|, max|w*y*y| (host arithmetic). */
+int32_t h2ok_hist_choose_quant(const double* absmax3, int32_t weighted, int32_t qbits, h2ok_quant* out);
+
 /* ---- host-buffer entry points (what an H2O-side caller binds; synchronous) ------------------ */
 
 /* Library copies the columns (cols_host[c] points at `rows` floats). */

@@ -1,0 +1,452 @@
+"""GPU parity tests: every call goes through the C ABI (ctypes → libh2ok_hist.so) and is checked against the
+oracle on the same seeded inputs.  Integer / index work must be bit-exact; fp sums are checked two ways:
+ (1) against the oracle's fixed-point walk — every channel an exact integer, so equality is bit-for-bit;
+ (2) against the oracle's fp64 walk of the unquantised fp32 inputs with north_star's tolerance:
+     |got - ref| <= 1e-5 * sum|w*y| over the bin (+ rows_in_bin quanta of 2^-27 * max|w*y|, the documented
+     fixed-point allowance, 670x below the 1e-5 term for any bin whose mean |w*y| is within 1/1000 of the max).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+from h2ok_hist import abi, capi  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def shard():
+    from h2ok_hist.driver import CudaShard
+
+    s = CudaShard(0)
+    yield s
+    s.close()
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def P(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def gpu_build(shard, X, rows, nid, wq, wyq, wyyq, descs, max_bins):
+    """Raw h2ok_hist_build_level_dev on caller-made device buffers."""
+    cols, ld = X.shape
+    descs = np.ascontiguousarray(descs, abi.COL_DESC).reshape(-1, cols)
+    n = descs.shape[0]
+    dX, dnid, dwyq, dwyyq = dev(X), dev(nid), dev(wyq), dev(wyyq)
+    dwq = dev(wq) if wq is not None else None
+    dd = dev(descs.view(np.uint8))
+    acc = torch.full((n, cols, max_bins + 1, 3), 7, dtype=torch.int64, device="cuda")  # garbage: clear must reset it
+    mn = torch.zeros((n, cols), dtype=torch.int32, device="cuda")
+    mx = torch.zeros((n, cols), dtype=torch.int32, device="cuda")
+    shard.lib.call("h2ok_hist_build_level_dev", shard.ctx, P(dX), ld, rows, cols, P(dnid), P(dwq), P(dwyq), P(dwyyq), n,
+                   P(dd), max_bins, 1, P(acc), P(mn), P(mx))
+    torch.cuda.synchronize()
+    return acc.cpu().numpy(), mn.cpu().numpy().view(np.uint32), mx.cpu().numpy().view(np.uint32)
+
+
+def pad4(a):
+    n = (-a.shape[-1]) % 4
+    return np.ascontiguousarray(np.pad(a, [(0, 0)] * (a.ndim - 1) + [(0, n)]))
+
+
+# ------------------------------------------------------------------------------------------------ generator
+@pytest.mark.parametrize("shape,cols", [(abi.SHAPE_HIGGS28, 28), (abi.SHAPE_WIDE64, 64), (abi.SHAPE_SPARSE, 9)])
+def test_generator_bit_exact(shard, oracle, shape, cols):
+    rows, row0 = 3001, 123456789012
+    Xo, yo, wo = oracle.synth(shape, 20261106, row0, rows, cols, na_permille=10, weight_mode=1, ld=3008)
+    X = torch.zeros((cols, 3008), dtype=torch.float32, device="cuda")
+    y = torch.zeros(rows, dtype=torch.float32, device="cuda")
+    w = torch.zeros(rows, dtype=torch.float32, device="cuda")
+    shard.lib.call("h2ok_hist_synth_fill_dev", shard.ctx, shape, 20261106, row0, rows, cols, 3008, 10, 1, P(X), P(y), P(w))
+    torch.cuda.synchronize()
+    assert np.array_equal(X.cpu().numpy().view(np.uint32), Xo.view(np.uint32))  # NaNs included, bit for bit
+    assert np.array_equal(y.cpu().numpy(), yo) and np.array_equal(w.cpu().numpy(), wo)
+
+
+# ------------------------------------------------------------------------------------------------ a2
+def test_bin_indices_bit_exact(shard, oracle):
+    rng = np.random.default_rng(1)
+    specials = np.array([np.nan, np.inf, -np.inf, 0.0, -0.0, 1e-45, -1e-45, 3.4e38, -3.4e38], np.float32)
+    for mn, maxex, nb, is_int in [(0.1, 0.8, 256, 0), (-3.14159274, 3.1415929794311523, 256, 0), (0.0, 3.0, 256, 1),
+                                  (-1e30, 1e30, 1024, 0), (5.0, 5.0 + 1e-9, 64, 0), (0.25, 4.25, 20, 0)]:
+        d, ok = oracle.make_desc(mn, maxex, is_int, nb)
+        assert ok
+        x = np.concatenate([rng.uniform(mn - 0.1 * abs(mn) - 0.1, maxex + 0.1, 200000).astype(np.float32), specials,
+                            np.float32(mn) + np.arange(4096, dtype=np.float32) * np.float32((maxex - mn) / 4096)])
+        dx = dev(x)
+        out = torch.zeros(x.size, dtype=torch.int32, device="cuda")
+        dd = np.array([d], abi.COL_DESC)
+        shard.lib.call("h2ok_hist_bin_dev", shard.ctx, P(dx), x.size, abi.ptr(dd), P(out))
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), oracle.bin_many(x, d))
+
+
+# ------------------------------------------------------------------------------------------------ targets
+@pytest.mark.parametrize("weight_mode", [0, 1])
+def test_quantise_rows_bit_exact(shard, oracle, weight_mode):
+    rows = 100003
+    _, y, w = oracle.synth(abi.SHAPE_HIGGS28, 9, 0, rows, 28, weight_mode=weight_mode)
+    q, m = oracle.choose_quant(y, w, 26)
+    wq, wyq, wyyq = oracle.quantize_rows(y, w, q)
+    dy, dw = dev(y), (dev(w) if w is not None else None)
+    dm = torch.zeros(3, dtype=torch.float64, device="cuda")
+    shard.lib.call("h2ok_hist_target_absmax_dev", shard.ctx, P(dy), P(dw), rows, P(dm))
+    assert np.array_equal(dm.cpu().numpy(), m)
+    g_wq = torch.zeros(rows, dtype=torch.int32, device="cuda") if weight_mode else None
+    g_wyq = torch.zeros(rows, dtype=torch.int32, device="cuda")
+    g_wyyq = torch.zeros(rows, dtype=torch.int32, device="cuda")
+    shard.lib.call("h2ok_hist_quantize_rows_dev", shard.ctx, P(dy), P(dw), rows, C.byref(q), P(g_wq), P(g_wyq), P(g_wyyq))
+    torch.cuda.synchronize()
+    assert np.array_equal(g_wyq.cpu().numpy(), wyq) and np.array_equal(g_wyyq.cpu().numpy(), wyyq)
+    if weight_mode:
+        assert np.array_equal(g_wq.cpu().numpy(), wq)
+
+
+# ------------------------------------------------------------------------------------------------ a3/a4
+def check_level(shard, oracle, X, rows, y, w, nid, descs, nb, qbits=26):
+    q, m = oracle.choose_quant(y, w, qbits)
+    wq, wyq, wyyq = oracle.quantize_rows(y, w, q)
+    acc, mn, mx = gpu_build(shard, X, rows, nid, wq, wyq, wyyq, descs, nb)
+    ref_acc, min2, maxin = oracle.build_level_q(X, rows, nid, wq, wyq, wyyq, descs, nb)
+    assert np.array_equal(acc, ref_acc)  # (1) every channel, every bin, bit for bit
+    assert np.array_equal(abi.decode_f32(mn) + np.float32(0), min2)
+    assert np.array_equal(abi.decode_f32(mx) + np.float32(0), maxin)
+    hist, absy, _, _ = oracle.build_level(X, rows, y, w, nid, descs, nb)
+    got = oracle.finalize(acc, q, nb)
+    nrows = oracle.build_level(X, rows, np.ones(max(rows, 1), np.float32), None if w is None else (w != 0).astype(np.float32),
+                               nid, descs, nb, want_abs=False)[0][..., 0]
+    if w is None:
+        assert np.array_equal(got[..., 0], hist[..., 0])  # counts exact
+    else:
+        assert (np.abs(got[..., 0] - hist[..., 0]) <= REL_TOL * hist[..., 0] + nrows * m[0] * 2.0**-27).all()
+    assert (np.abs(got[..., 1] - hist[..., 1]) <= REL_TOL * absy + nrows * m[1] * 2.0**-27).all()  # (2)
+    assert (np.abs(got[..., 2] - hist[..., 2]) <= REL_TOL * hist[..., 2] + nrows * m[2] * 2.0**-27).all()
+    return acc
+
+
+@pytest.mark.parametrize("rows", [1, 3, 4, 5, 4095, 4097, 150001])
+def test_build_level_root_ragged_sizes(shard, oracle, rows):
+    cols, nb = 5, 256
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 31, 0, rows, cols)
+    root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb))
+    if rows == 1:
+        d, _ = oracle.make_desc(0.0, 8.0, 0, nb)
+        root[:] = d
+    check_level(shard, oracle, X, rows, y, None, np.zeros(pad4(np.zeros(rows)).size, np.int32), root.reshape(1, cols), nb)
+
+
+@pytest.mark.parametrize("n_nodes,weight_mode,na", [(2, 0, 0), (3, 1, 10), (8, 0, 10), (37, 1, 0), (64, 0, 0), (100, 0, 5), (130, 1, 5)])
+def test_build_level_many_nodes(shard, oracle, n_nodes, weight_mode, na):
+    rows, cols, nb = 60001, 6, 256
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 77 + n_nodes, 0, rows, cols, na_permille=na, weight_mode=weight_mode)
+    rng = np.random.default_rng(n_nodes)
+    nid = np.zeros(X.shape[1], np.int32)
+    nid[:rows] = rng.integers(-1, n_nodes, rows)  # -1: rows already in leaves
+    nid[rows:] = -1
+    root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb))
+    descs = np.stack([root] * n_nodes)
+    for g in range(n_nodes):  # per-node ranges differ; some values clamp; a few columns untracked
+        descs[g]["min"] += (g % 5) * 0.01
+        descs[g]["step"] *= 1.0 + (g % 3) * 0.125
+    descs[n_nodes // 2, 1]["nbin"] = 0
+    descs[0, 3]["nbin"] = 17
+    check_level(shard, oracle, X, rows, y, w, nid, descs, nb)
+
+
+def test_build_level_skewed_and_small_bins(shard, oracle):
+    # 3-valued and constant-ish columns: every lane of a warp hits the same few addresses
+    rows, cols, nb = 200000, 28, 64
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 5, 0, rows, cols)
+    X[1, :rows] = 2.5
+    X[2, :rows] = np.where(np.arange(rows) % 1000 == 0, np.nan, 1.0)
+    root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb))
+    d, _ = oracle.make_desc(0.0, 8.0, 0, nb)
+    root[1] = d
+    root[2] = d
+    nid = np.zeros(rows, np.int32)
+    check_level(shard, oracle, X, rows, y, None, nid, root.reshape(1, cols), nb)
+
+
+def test_build_level_carry_path(shard, oracle):
+    # qbits=30 with every row in one bin forces many carries/borrows out of the 32-bit shared words
+    rows, cols, nb = 300000, 2, 8
+    X, y, w = oracle.synth(abi.SHAPE_HIGGS28, 41, 0, rows, cols, weight_mode=1)
+    X[0, :rows] = 1.0
+    y[:rows] = np.where(np.arange(rows) % 7 < 5, y[:rows], -np.abs(y[:rows]))
+    d, _ = oracle.make_desc(0.0, 8.0, 0, nb)
+    descs = np.array([[d, d]], abi.COL_DESC)
+    acc = check_level(shard, oracle, X, rows, y, w, np.zeros(rows, np.int32), descs, nb, qbits=30)
+    assert np.abs(acc).max() > 2**40
+
+
+def test_build_level_rejects_bad_arguments(shard):
+    x = torch.zeros(64, dtype=torch.float32, device="cuda")
+    i = torch.zeros(64, dtype=torch.int32, device="cuda")
+    d = torch.zeros(32, dtype=torch.uint8, device="cuda")
+    acc = torch.zeros(3 * 257, dtype=torch.int64, device="cuda")
+    args = lambda **k: [shard.ctx, P(x), k.get("ld", 64), k.get("rows", 64), 1, P(i), None, P(i), P(i), k.get("n", 1), P(d),
+                        k.get("nb", 256), 1, P(acc), P(i), P(i)]
+    for bad, code in [(dict(ld=62), abi.ERR_ARG), (dict(rows=65), abi.ERR_ARG), (dict(n=0), abi.ERR_ARG),
+                      (dict(nb=2000), abi.ERR_UNSUPPORTED), (dict(n=5000), abi.ERR_ARG)]:
+        with pytest.raises(capi.H2okError) as e:
+            shard.lib.call("h2ok_hist_build_level_dev", *args(**bad))
+        assert e.value.code == code
+    a = args()
+    a[1] = None
+    with pytest.raises(capi.H2okError):
+        shard.lib.call("h2ok_hist_build_level_dev", *a)
+
+
+# ------------------------------------------------------------------------------------------------ a7 / a8 / a6
+def gpu_find_splits(shard, hist, descs, min_rows, msi):
+    n, cols, nb1, _ = hist.shape
+    dh, dd = dev(hist), dev(np.ascontiguousarray(descs, abi.COL_DESC).view(np.uint8))
+    out = torch.zeros((n, abi.SPLIT.itemsize), dtype=torch.uint8, device="cuda")
+    shard.lib.call("h2ok_hist_find_splits_dev", shard.ctx, P(dh), P(dd), n, cols, nb1 - 1, float(min_rows), float(msi), P(out))
+    torch.cuda.synchronize()
+    return out.cpu().numpy().view(abi.SPLIT).reshape(n)
+
+
+def test_find_splits_known_cases_bit_exact(shard, oracle):
+    from test_oracle import desc, hist_from
+
+    d4 = desc(0.0, 8.0, 0.5, 4)
+    cases = [
+        hist_from([10, 10, 10, 10], [0, 0, 10, 10], [0, 0, 10, 10]),
+        hist_from([10, 10, 10, 10], [0, 10, 10, 10], [0, 10, 10, 10]),
+        hist_from([10, 10, 10, 10], [10, 10, 10, 10], [10, 10, 10, 10]),
+        hist_from([10, 10, 10, 10], [10, 0, 0, 10], [10, 0, 0, 10]),
+        hist_from([10, 0, 0, 10], [0, 0, 0, 10], [0, 0, 0, 10]),
+        hist_from([10, 10, 10, 10], [0, 0, 10, 10], [0, 0, 10, 10], na=(10, 10, 10)),
+        hist_from([10, 10, 10, 10], [0, 0, 10, 10], [0, 0, 10, 10], na=(10, 0, 0)),
+        hist_from([10, 10, 10, 10], [0, 0, 0, 0], [0, 0, 0, 0], na=(20, 20, 20)),
+        hist_from([0, 0, 0, 0], [0, 0, 0, 0], [0, 0, 0, 0], na=(20, 5, 20)),
+    ]
+    hist = np.concatenate(cases, axis=0)
+    descs = np.array([[d4]] * len(cases), abi.COL_DESC)
+    for min_rows, msi in [(1.0, 0.0), (10.0, 1e-5), (15.0, 0.0), (5.0, 0.5)]:
+        want = oracle.find_splits(hist, descs, min_rows, msi)
+        got = gpu_find_splits(shard, hist, descs, min_rows, msi)
+        assert got.tobytes() == want.tobytes(), (min_rows, msi, got, want)
+
+
+@pytest.mark.parametrize("weight_mode,na,nb", [(0, 0, 256), (1, 20, 256), (0, 20, 37), (0, 0, 1024)])
+def test_find_splits_on_real_histograms_bit_exact(shard, oracle, weight_mode, na, nb):
+    rows, cols, n_nodes = 80000, 12, 5
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 3, 0, rows, cols, na_permille=na, weight_mode=weight_mode)
+    nid = (np.arange(X.shape[1]) % n_nodes).astype(np.int32)
+    root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb), is_int=None)
+    descs = np.stack([root] * n_nodes)
+    descs[1, 2]["nbin"] = 1
+    q, _ = oracle.choose_quant(y, w, 26)
+    wq, wyq, wyyq = oracle.quantize_rows(y, w, q)
+    acc, _, _ = gpu_build(shard, X, rows, nid, wq, wyq, wyyq, descs, nb)
+    hist = oracle.finalize(acc, q, nb)
+    for min_rows, msi in [(10.0, 1e-5), (1.0, 0.0), (3000.0, 1e-5)]:
+        want = oracle.find_splits(hist, descs, min_rows, msi)
+        got = gpu_find_splits(shard, hist, descs, min_rows, msi)
+        assert got.tobytes() == want.tobytes()
+        assert (want["col"] >= 0).any()
+
+
+def run_tree_both(shard, oracle, X, rows, y, w, params, is_int=None):
+    """LevelDriver on the GPU vs the oracle's fixed-point level loop: every level's accumulators, descriptors,
+    splits, child ids and row map must be identical."""
+    from h2ok_hist.driver import LevelDriver
+
+    cols = X.shape[0]
+    shard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()),
+                           None if w is None else torch.from_numpy(w[:rows].copy()))
+    drv = LevelDriver(shard, params, is_int=is_int)
+    root = drv.prepare_data()
+    assert root.tobytes() == oracle.root_descs(X, rows, params, is_int).tobytes()
+    q, _ = oracle.choose_quant(y[:rows], None if w is None else w[:rows], 26)
+    wq, wyq, wyyq = oracle.quantize_rows(y[:rows], None if w is None else w[:rows], q)
+    state = dict(descs=root.reshape(1, cols).copy(), nid=np.zeros(rows, np.int32), leaf=np.full(rows, -1, np.int32), gid=0,
+                 levels=0)
+    nb = drv.max_bins
+
+    def inspect(d, n, nch):
+        sh = d.shard
+        torch.cuda.synchronize()
+        assert n == state["descs"].shape[0]
+        assert sh.descs_np(n).tobytes() == state["descs"].tobytes()
+        assert np.array_equal(sh.nid[:rows].cpu().numpy(), state["nid"])
+        acc, min2, maxin = oracle.build_level_q(X, rows, state["nid"], wq, wyq, wyyq, state["descs"], nb)
+        assert np.array_equal(sh.acc[:n].cpu().numpy(), acc)
+        assert np.array_equal(sh.min2[:n].cpu().numpy(), min2) and np.array_equal(sh.maxin[:n].cpu().numpy(), maxin)
+        hist = oracle.finalize(acc, q, nb)
+        assert np.array_equal(sh.hist[:n].cpu().numpy(), hist)
+        splits = oracle.find_splits(hist, state["descs"], params.min_rows, params.min_split_improvement)
+        assert sh.splits_np(n).tobytes() == splits.tobytes()
+        last = d.depth + 1 >= params.max_depth
+        if last:
+            child, ids, nc = np.zeros((0, cols), abi.COL_DESC), np.full(2 * n, -1, np.int32), 0
+        else:
+            child, ids, nc = oracle.next_level(splits, state["descs"], min2, maxin, params, d.depth)
+        assert nc == nch
+        assert np.array_equal(sh.child_ids[: 2 * n].cpu().numpy(), ids)
+        if nc:
+            got_child = sh.child_descs[:nc].cpu().numpy().view(abi.COL_DESC).reshape(nc, cols)
+            assert got_child.tobytes() == child.tobytes()
+        oracle.apply_splits(X, rows, splits, ids, state["gid"], state["nid"], state["leaf"])
+        state["gid"] += n
+        state["descs"] = child
+        state["levels"] += 1
+
+    levels = drv.train_tree(inspect=inspect)
+    torch.cuda.synchronize()
+    assert levels == state["levels"]
+    assert np.array_equal(shard.nid[:rows].cpu().numpy(), state["nid"])
+    assert np.array_equal(shard.leaf[:rows].cpu().numpy(), state["leaf"])
+    return levels, state
+
+
+def test_tree_levels_match_oracle_config2_shape(shard, oracle):
+    rows, cols = 120000, 28
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 20261106, 0, rows, cols)
+    levels, st = run_tree_both(shard, oracle, X, rows, y, None, abi.Params.make(nbins=256, max_depth=6))
+    assert levels == 6 and (st["leaf"] >= 0).all()
+
+
+def test_tree_levels_match_oracle_weighted_na_int(shard, oracle):
+    rows, cols = 50001, 10
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 99, 0, rows, cols, na_permille=30, weight_mode=1)
+    X[4, :rows] = np.floor(X[4, :rows] * 3)  # integer column, few values → step-1 bins
+    X[7, :rows] = np.floor(X[7, :rows] * 1000)  # integer column, many values
+    is_int = [0, 0, 0, 0, 1, 0, 0, 1, 0, 0]
+    levels, _ = run_tree_both(shard, oracle, X, rows, y, w, abi.Params.make(nbins=64, max_depth=7, min_rows=5), is_int)
+    assert levels >= 4
+
+
+def test_tree_top_level_bins_shrink(shard, oracle):
+    rows, cols = 30000, 8
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 4, 0, rows, cols)
+    run_tree_both(shard, oracle, X, rows, y, None, abi.Params.make(nbins=20, nbins_top_level=160, max_depth=5))
+
+
+# ------------------------------------------------------------------------------------------------ host-buffer ABI
+def test_host_buffer_entry_points(oracle, lib):
+    rows, cols, nb = 40003, 7, 64
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 12, 0, rows, cols, na_permille=10, weight_mode=1)
+    p = abi.Params.make(nbins=nb, max_depth=3)
+    h = C.c_void_p()
+    lib.call("h2ok_hist_create", 0, C.byref(h))
+    try:
+        with pytest.raises(capi.H2okError) as e:
+            lib.call("h2ok_hist_set_targets_host", h, abi.ptr(y), None)
+        assert e.value.code == abi.ERR_STATE
+        colptrs = (C.c_void_p * cols)(*[X[c].ctypes.data for c in range(cols)])
+        lib.call("h2ok_hist_set_data_host", h, colptrs, rows, cols)
+        lib.call("h2ok_hist_set_targets_host", h, abi.ptr(y), abi.ptr(w))
+        descs = np.zeros((1, cols), abi.COL_DESC)
+        lib.call("h2ok_hist_root_descs", h, C.byref(p), None, abi.ptr(descs))
+        assert descs.tobytes() == oracle.root_descs(X, rows, p).tobytes()
+        q = abi.Quant()
+        lib.call("h2ok_hist_get_quant", h, C.byref(q))
+        qo, _ = oracle.choose_quant(y, w, 26)
+        assert (q.scale_w, q.scale_wy, q.scale_wyy) == (qo.scale_w, qo.scale_wy, qo.scale_wyy)
+        wq, wyq, wyyq = oracle.quantize_rows(y, w, qo)
+        nid = np.zeros(rows, np.int32)
+        leaf = np.full(rows, -1, np.int32)
+        gid = 0
+        with pytest.raises(capi.H2okError):
+            lib.call("h2ok_hist_find_splits", h, 10.0, 1e-5, None)
+        for depth in range(3):
+            n = descs.shape[0]
+            hist = np.zeros((n, cols, nb + 1, 3))
+            min2 = np.zeros((n, cols), np.float32)
+            maxin = np.zeros((n, cols), np.float32)
+            lib.call("h2ok_hist_build_level", h, n, abi.ptr(descs), nb, abi.ptr(hist), abi.ptr(min2), abi.ptr(maxin))
+            acc, rmin2, rmaxin = oracle.build_level_q(X, rows, nid, wq, wyq, wyyq, descs, nb)
+            assert np.array_equal(hist, oracle.finalize(acc, qo, nb))
+            assert np.array_equal(min2, rmin2) and np.array_equal(maxin, rmaxin)
+            splits = np.zeros(n, abi.SPLIT)
+            lib.call("h2ok_hist_find_splits", h, p.min_rows, p.min_split_improvement, abi.ptr(splits))
+            want = oracle.find_splits(hist, descs, p.min_rows, p.min_split_improvement)
+            assert splits.tobytes() == want.tobytes()
+            if depth < 2:
+                child = np.zeros((2 * n, cols), abi.COL_DESC)
+                ids = np.zeros(2 * n, np.int32)
+                nc = C.c_int32()
+                lib.call("h2ok_hist_next_level", h, C.byref(p), depth, abi.ptr(child), abi.ptr(ids), C.byref(nc))
+                wchild, wids, wn = oracle.next_level(want, descs, min2, maxin, p, depth)
+                assert nc.value == wn and np.array_equal(ids, wids) and child[:wn].tobytes() == wchild.tobytes()
+            else:
+                wchild, wids = None, np.full(2 * n, -1, np.int32)
+            lib.call("h2ok_hist_apply_splits", h)
+            oracle.apply_splits(X, rows, want, wids, gid, nid, leaf)
+            gid += n
+            gn = np.zeros(rows, np.int32)
+            gl = np.zeros(rows, np.int32)
+            lib.call("h2ok_hist_get_nid_host", h, abi.ptr(gn), abi.ptr(gl))
+            assert np.array_equal(gn, nid) and np.array_equal(gl, leaf)
+            st = abi.Stats()
+            lib.call("h2ok_hist_last_level_stats", h, C.byref(st))
+            assert st.build_ms > 0 and st.launches >= 3
+            if depth < 2:
+                descs = wchild
+    finally:
+        lib.call("h2ok_hist_destroy", h)
+
+
+# ------------------------------------------------------------------------------------------------ full-size properties
+def level_invariants(drv, n, nch):
+    """Size-independent properties (checksum of checksums): in every node each tracked column's bins must sum to the
+    same three integers — the node's row count and its sums of wyq and wyyq computed directly from the row arrays."""
+    sh = drv.shard
+    rows = sh.rows
+    nid = sh.nid[:rows].long()
+    act = nid >= 0
+    idx = nid[act]
+    cnt = torch.zeros(n, dtype=torch.int64, device=sh.device).index_add_(0, idx, torch.ones_like(idx))
+    s1 = torch.zeros(n, dtype=torch.int64, device=sh.device).index_add_(0, idx, sh.wyq[:rows][act].long())
+    s2 = torch.zeros(n, dtype=torch.int64, device=sh.device).index_add_(0, idx, sh.wyyq[:rows][act].long())
+    want = torch.stack([cnt, s1, s2], dim=1)  # [n,3]
+    sums = sh.acc[:n].sum(dim=2)  # [n, cols, 3]
+    nbin = torch.from_numpy(sh.descs_np(n)["nbin"].astype(np.int64)).to(sh.device)  # [n, cols]
+    tracked = nbin > 0
+    assert torch.equal(sums[tracked], want[:, None, :].expand(-1, sh.cols, -1)[tracked])
+    assert (sums[~tracked] == 0).all()
+    # nothing lands above a column's NA slot
+    ar = torch.arange(sh.acc.shape[2], device=sh.device)
+    above = ar[None, None, :] > nbin[:, :, None]
+    assert (sh.acc[:n][above] == 0).all()
+    drv._checked = getattr(drv, "_checked", 0) + 1
+
+
+def test_full_size_config2_invariants(shard):
+    from h2ok_hist.driver import LevelDriver
+
+    rows, cols = 1_000_000, 28  # BASELINE config 2 at full size
+    shard.set_data_synth(abi.SHAPE_HIGGS28, 20261106, 0, rows, cols)
+    drv = LevelDriver(shard, abi.Params.make(nbins=256, max_depth=6))
+    drv.prepare_data()
+    assert drv.train_tree(inspect=level_invariants) == 6 and drv._checked == 6
+    assert int((shard.leaf[:rows] < 0).sum()) == 0
+
+
+def test_full_size_config3_slice_invariants_and_idempotence(shard):
+    from h2ok_hist.driver import LevelDriver
+
+    free, _ = torch.cuda.mem_get_info()
+    rows = 100_000_000 if free > 60e9 else 10_000_000  # BASELINE config 3 full size when the device has room
+    cols = 64
+    shard.set_data_synth(abi.SHAPE_WIDE64, 20261106, 0, rows, cols)
+    drv = LevelDriver(shard, abi.Params.make(nbins=256, max_depth=8))
+    drv.prepare_data()
+    assert drv.train_tree(inspect=level_invariants) == 8
+    leaf1 = shard.leaf[:rows].clone()
+    acc1 = shard.acc.clone()
+    assert drv.train_tree() == 8  # same tree again: integer accumulation is order-independent → identical bits
+    assert torch.equal(shard.leaf[:rows], leaf1) and torch.equal(shard.acc, acc1)
+    shard.set_data_synth(abi.SHAPE_HIGGS28, 1, 0, 1024, 4)  # release the big buffers
+    torch.cuda.empty_cache()
