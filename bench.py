@@ -1,0 +1,479 @@
+#!/usr/bin/env python
+"""bench.py — GBM histogram rows*cols/s per tree level (BASELINE.json metric) on N B200s.
+
+A "step" is one tree level of the hot path on the 100M x 64, 256-bin, depth-8 workload (BASELINE config 3, the
+configuration the metric is quoted on): score_decide of the previous level's splits → histogram build (the
+dominant kernel) → cross-rank reduce (N>1) → split search → children descriptors.  Steps cycle through levels
+0..7 of real trees, so node counts and the row→node map are the ones the algorithm produces.  Rows are sharded
+across ranks (strong scaling: total rows fixed); launch under torchrun for N>1.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for the definition of every field.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "h2o-kubernetes_b200"), os.path.join(ROOT, "tests"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "gbm_histogram_rows_x_cols_per_s_per_tree_level"
+UNIT = "cells/s"
+SEED = 20261106
+WORKLOADS = {
+    "c3": dict(name="GBM histogram build 100M rows x 64 cols, 256 bins, depth 8 (BASELINE config 3)", rows=100_000_000,
+               cols=64, bins=256, depth=8, shape=3),
+    "c2": dict(name="GBM histogram build 1M rows x 28 cols (HIGGS-shaped), 256 bins, depth 6 (BASELINE config 2)",
+               rows=1_000_000, cols=28, bins=256, depth=6, shape=2),
+}
+CPU_SAMPLE_ROWS = 2_000_000
+
+
+def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False):
+    """every fp32 cell once, nid + y (+ w) once per row, the fp64 histogram written once."""
+    return rows * cols * 4.0 + rows * (4.0 + 4.0 + (4.0 if weighted else 0.0)) + n_nodes * cols * (bins + 1) * 3 * 8.0
+
+
+def measured_hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            out["reasons"] = ["nvidia-smi unavailable"]
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ CPU arms
+def cpu_levels(oracle, wl, sample_rows, threads, max_seconds, levels=None):
+    """The oracle's own level loop (fp64, column-parallel like H2O's LocalMR) on the first `sample_rows` rows of the
+    workload.  Returns per-level seconds of build_level + find_splits + next_level + apply_splits."""
+    from h2ok_hist import abi
+
+    cols, bins = wl["cols"], wl["bins"]
+    X, y, _ = oracle.synth(wl["shape"], SEED, 0, sample_rows, cols)
+    params = abi.Params.make(nbins=bins, max_depth=wl["depth"])
+    descs = oracle.root_descs(X, sample_rows, params).reshape(1, cols)
+    nid = np.zeros(sample_rows, np.int32)
+    gid, times, nodes = 0, [], []
+    t_all = time.perf_counter()
+    for depth in range(wl["depth"] if levels is None else levels):
+        n = descs.shape[0]
+        t0 = time.perf_counter()
+        hist, _, min2, maxin = oracle.build_level(X, sample_rows, y, None, nid, descs, bins, threads=threads, want_abs=False)
+        splits = oracle.find_splits(hist, descs, params.min_rows, params.min_split_improvement)
+        if depth + 1 < wl["depth"]:
+            child, ids, nch = oracle.next_level(splits, descs, min2, maxin, params, depth)
+        else:
+            child, ids, nch = None, np.full(2 * n, -1, np.int32), 0
+        oracle.apply_splits(X, sample_rows, splits, ids, gid, nid, None)
+        times.append(time.perf_counter() - t0)
+        nodes.append(n)
+        gid += n
+        descs = child
+        if nch == 0 or time.perf_counter() - t_all > max_seconds:
+            break
+    return times, nodes
+
+
+def run_reference(args, wl):
+    """--impl reference: the CPU implementation of the path on the host cores.  The reference tree has no code for
+    this path and H2O-3 cannot run here (no JVM, no jar), so this arm is the oracle port with every host thread."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle_lib
+
+    oracle = oracle_lib.load()
+    threads = oracle.max_threads()
+    rows = min(CPU_SAMPLE_ROWS, wl["rows"])
+    # every "step" is one level of a depth-`depth` tree over the sample; warm-up levels come first
+    need = args.steps + args.warmup
+    times = []
+    while len(times) < need:
+        t, _ = cpu_levels(oracle, wl, rows, threads, max_seconds=600)
+        times += t
+    timed = times[args.warmup: args.warmup + args.steps]
+    sec = float(np.sum(timed))
+    value = rows * wl["cols"] * len(timed) / sec
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * sec / len(timed), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl["name"], "rows": wl["rows"], "cols": wl["cols"], "bins": wl["bins"], "depth": wl["depth"],
+                   "sample_rows": rows, "note": "CPU oracle port (H2O-3 itself is not runnable here: no JVM/jar)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"levels of a depth-{wl['depth']} tree on the first {rows} rows x {wl['cols']} cols of the workload"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_gpu(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    from h2ok_hist import abi, capi
+    from h2ok_hist.driver import CudaShard, LevelDriver
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    rows_total, cols, bins, depth = wl["rows"], wl["cols"], wl["bins"], wl["depth"]
+    row0 = rows_total * rank // world
+    rows = rows_total * (rank + 1) // world - row0
+    shard = CudaShard(local)
+    shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
+    params = abi.Params.make(nbins=bins, max_depth=depth)
+    drv = LevelDriver(shard, params)
+    drv.prepare_data()
+    barrier()
+
+    # ---- resident path: inputs in HBM when the timed region starts ------------------------------------
+    rec = []  # per timed step: (level, n_nodes, hist_ms)
+
+    def run_steps(n_steps, record):
+        done = 0
+        while done < n_steps:
+            if drv.n_nodes_left() == 0:
+                drv.prepare_tree()
+            lvl, n = drv.depth, drv.n_nodes
+            drv.level()
+            if record:
+                rec.append((lvl, n, shard.last_hist_ms()))
+            done += 1
+
+    drv.prepare_tree()
+    run_steps(args.warmup, False)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = shard.launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    run_steps(args.steps, True)
+    ev1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    launches = shard.launches - launches0
+    value = rows_total * cols * args.steps / (total_ms * 1e-3)
+
+    # roofline of the dominant kernel (hist_build_kernel): algorithmic bytes of THIS rank's launches / their device time
+    hist_ms = float(sum(r[2] for r in rec))
+    abytes = float(sum(algo_bytes_level(rows, cols, r[1], bins) for r in rec))
+    peak, peak_src = measured_hbm_peak()
+    achieved = abytes / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
+    per_level = {}
+    for lvl, n, t in rec:
+        per_level.setdefault(lvl, []).append((n, t))
+    level_table = {str(k): {"nodes": v[0][0], "hist_ms": round(float(np.mean([x[1] for x in v])), 4),
+                            "frac": round(algo_bytes_level(rows, cols, v[0][0], bins) / (np.mean([x[1] for x in v]) * 1e-3) / 1e9 / peak, 4)}
+                   for k, v in sorted(per_level.items())}
+
+    # ---- e2e: host buffers in, host buffers out, copies inside the timed region ---------------------------
+    if args.no_e2e:
+        e2e = None
+    elif world == 1:
+        e2e = run_e2e_cabi(args, wl, shard, params)
+    else:
+        e2e = run_e2e(args, wl, shard, drv, world, rank, rows_total, rows, barrier)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle_lib
+
+        oracle = oracle_lib.load()
+        threads = oracle.max_threads()
+        srows = min(CPU_SAMPLE_ROWS, rows_total)
+        t, nodes = cpu_levels(oracle, wl, srows, threads, max_seconds=40)
+        cpu = {"value": srows * cols * len(t) / float(np.sum(t)), "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"{len(t)} levels of a depth-{depth} tree on the first {srows} rows x {cols} cols (slice, not extrapolated)"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64 binning, i32/i64 fixed-point sums", "data": "synthetic",
+            "config": {"workload": wl["name"], "rows": rows_total, "cols": cols, "bins": bins, "depth": depth,
+                       "rows_per_gpu": rows, "step": "one tree level (levels cycle 0..depth-1 of real trees)",
+                       "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
+                       "per_level": level_table},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "hist_build_kernel", "peak_source": peak_src,
+                         "note": "algorithmic bytes of the timed levels / CUDA-event time of their hist_build launches"},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    shard.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, wl, shard, drv, world, rank, rows_total, rows, barrier):
+    """Same metric through the public API with HOST buffers.  Per tree the targets y come from pinned host memory
+    (H2D inside the timed region); per level the histogram, observed ranges, splits and child ids are copied to
+    pinned host buffers (D2H inside the timed region).  X stays resident between levels, as it does in a training job;
+    its one-time upload is reported separately (set_data_ms) and not hidden."""
+    import torch
+    import torch.distributed as dist
+
+    from h2ok_hist import abi
+
+    cols, bins, depth = wl["cols"], wl["bins"], wl["depth"]
+    nb1 = bins + 1
+    max_nodes = shard.acc.shape[0]
+    y_host = shard.y[:rows].cpu().pin_memory()
+    # one-time upload of X through the host path (measured on a slice, scaled is NOT reported: we report the slice)
+    t0 = time.perf_counter()
+    slice_cols = min(cols, 4)
+    xs = shard.X[:slice_cols, :rows].cpu()
+    d2h_s = time.perf_counter() - t0
+    xs = xs.pin_memory()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    shard.X[:slice_cols, :rows].copy_(xs, non_blocking=True)
+    torch.cuda.synchronize()
+    h2d_s = time.perf_counter() - t0
+    upload_gbs = slice_cols * rows * 4 / h2d_s / 1e9
+    del xs
+    host = dict(hist=torch.empty((max_nodes, cols, nb1, 3), dtype=torch.float64).pin_memory(),
+                min2=torch.empty((max_nodes, cols), dtype=torch.float32).pin_memory(),
+                maxin=torch.empty((max_nodes, cols), dtype=torch.float32).pin_memory(),
+                splits=torch.empty((max_nodes, abi.SPLIT.itemsize), dtype=torch.uint8).pin_memory(),
+                child_ids=torch.empty(2 * max_nodes, dtype=torch.int32).pin_memory())
+    h2d = d2h = 0
+
+    def tree_start():
+        nonlocal h2d
+        shard.set_targets(y_host)  # H2D from pinned memory
+        drv.prepare_tree()
+        h2d += rows * 4 + cols * abi.COL_DESC.itemsize
+
+    def level_out(d, n, nch):
+        nonlocal d2h
+        sh = d.shard
+        host["hist"][:n].copy_(sh.hist[:n], non_blocking=True)
+        host["min2"][:n].copy_(sh.min2[:n], non_blocking=True)
+        host["maxin"][:n].copy_(sh.maxin[:n], non_blocking=True)
+        host["splits"][:n].copy_(sh.splits[:n], non_blocking=True)
+        host["child_ids"][: 2 * n].copy_(sh.child_ids[: 2 * n], non_blocking=True)
+        d2h += n * cols * nb1 * 24 + n * cols * 8 + n * abi.SPLIT.itemsize + 2 * n * 4
+
+    def steps(k):
+        done = 0
+        while done < k:
+            if drv.n_nodes_left() == 0:
+                tree_start()
+            drv.level(inspect=level_out)
+            torch.cuda.current_stream().synchronize()  # the caller owns the host buffers only after the copies land
+            done += 1
+
+    drv.n_nodes = 0
+    steps(min(args.warmup, depth))
+    drv.n_nodes = 0  # timed region starts at a tree boundary so the y upload is counted
+    h2d = d2h = 0
+    barrier()
+    t0 = time.perf_counter()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    steps(args.steps)
+    ev1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    ms = torch.tensor([max(ev0.elapsed_time(ev1), 0.0)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    return {"value": rows_total * cols * args.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d / args.steps,
+            "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": ms / args.steps, "wall_ms_per_step": wall * 1e3 / args.steps,
+            "path": "LevelDriver: y from pinned host memory per tree; hist/ranges/splits/child ids to pinned host buffers per level",
+            "x_upload": {"note": "one-time, outside the timed region (X is resident across levels like H2O's DKV chunks)",
+                         "measured_h2d_gbs": upload_gbs, "full_x_bytes_per_gpu": rows * cols * 4,
+                         "est_ms": rows * cols * 4 / upload_gbs / 1e6, "slice_d2h_s": d2h_s}}
+
+
+def run_e2e_cabi(args, wl, shard, params):
+    """N=1: the same metric through the host-buffer C-ABI entry points (what an H2O-side binding calls): every level
+    the descriptors go host→device and the histogram, observed ranges, splits, child descriptors and child ids come
+    device→host; every tree the targets y go host→device (h2ok_hist_set_targets_host).  X is uploaded once with
+    h2ok_hist_set_data_host before the timed region (reported as x_upload), exactly as a training job would."""
+    import torch
+
+    from h2ok_hist import abi, capi
+
+    lib = capi.load()
+    rows, cols, bins, depth = shard.rows, wl["cols"], wl["bins"], wl["depth"]
+    nb1 = bins + 1
+    max_nodes = 2 ** (depth - 1)
+    t0 = time.perf_counter()
+    Xh = torch.empty((cols, rows), dtype=torch.float32)
+    for c in range(cols):
+        Xh[c].copy_(shard.X[c, :rows])
+    yh = shard.y[:rows].cpu().pin_memory()
+    prep_s = time.perf_counter() - t0
+    # free the resident shard's big buffers: the library owns its own copy from here on
+    shard.X = shard.nid = shard.leaf = shard.wyq = shard.wyyq = None
+    torch.cuda.empty_cache()
+    h = C.c_void_p()
+    lib.call("h2ok_hist_create", 0, C.byref(h))
+    colptrs = (C.c_void_p * cols)(*[Xh[c].data_ptr() for c in range(cols)])
+    t0 = time.perf_counter()
+    lib.call("h2ok_hist_set_data_host", h, colptrs, rows, cols)
+    upload_s = time.perf_counter() - t0
+
+    def pinned(shape, dtype):
+        return torch.empty(shape, dtype=dtype).pin_memory().numpy()
+
+    hist = pinned((max_nodes, cols, nb1, 3), torch.float64)
+    min2 = pinned((max_nodes, cols), torch.float32)
+    maxin = pinned((max_nodes, cols), torch.float32)
+    splits = pinned((max_nodes, abi.SPLIT.itemsize), torch.uint8)
+    child = pinned((2 * max_nodes, cols, abi.COL_DESC.itemsize), torch.uint8)
+    ids = pinned((2 * max_nodes,), torch.int32)
+    root = np.zeros((1, cols), abi.COL_DESC)
+    lib.call("h2ok_hist_root_descs", h, C.byref(params), None, abi.ptr(root))
+    state = dict(n=0, depth=0, descs=None, h2d=0, d2h=0)
+    yp = C.c_void_p(yh.data_ptr())
+
+    def step():
+        if state["n"] == 0 or state["depth"] >= depth:
+            lib.call("h2ok_hist_set_targets_host", h, yp, None)
+            state.update(n=1, depth=0, descs=root)
+            state["h2d"] += rows * 4
+        n, d = state["n"], state["depth"]
+        lib.call("h2ok_hist_build_level", h, n, abi.ptr(state["descs"]), bins, abi.ptr(hist), abi.ptr(min2), abi.ptr(maxin))
+        lib.call("h2ok_hist_find_splits", h, params.min_rows, params.min_split_improvement, abi.ptr(splits))
+        state["h2d"] += n * cols * abi.COL_DESC.itemsize
+        state["d2h"] += n * cols * nb1 * 24 + n * cols * 8 + n * abi.SPLIT.itemsize
+        nch = 0
+        if d + 1 < depth:
+            nc = C.c_int32()
+            lib.call("h2ok_hist_next_level", h, C.byref(params), d, abi.ptr(child), abi.ptr(ids), C.byref(nc))
+            nch = nc.value
+            state["d2h"] += nch * cols * abi.COL_DESC.itemsize + 2 * n * 4 + 4
+        lib.call("h2ok_hist_apply_splits", h)
+        state.update(n=nch, depth=d + 1, descs=child.view(abi.COL_DESC).reshape(2 * max_nodes, cols)[:nch] if nch else None)
+
+    for _ in range(depth):  # warm-up: one whole tree
+        step()
+    state.update(n=0, h2d=0, d2h=0)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize()
+    sec = time.perf_counter() - t0  # every entry point is synchronous on return, so host time == end-to-end time
+    lib.call("h2ok_hist_destroy", h)
+    return {"value": rows * cols * args.steps / sec, "unit": UNIT, "h2d_bytes_per_step": state["h2d"] / args.steps,
+            "d2h_bytes_per_step": state["d2h"] / args.steps, "ms_per_step": sec * 1e3 / args.steps,
+            "path": "C ABI host-buffer entry points: set_targets_host per tree; build_level / find_splits / next_level / "
+                    "apply_splits per level with host descriptors in and host histogram, ranges, splits, children out",
+            "x_upload": {"note": "one-time h2ok_hist_set_data_host from pageable host memory, outside the timed region "
+                                 "(X stays resident across levels and trees, like H2O's in-memory chunks)",
+                         "ms": upload_s * 1e3, "bytes": rows * cols * 4, "host_copy_prep_s": prep_s}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override the workload's row count (debug only)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    wl = dict(WORKLOADS[args.workload])
+    if args.rows:
+        wl["rows"] = args.rows
+        wl["name"] += f" [rows overridden to {args.rows}]"
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_gpu(args, wl)
+
+
+if __name__ == "__main__":
+    main()

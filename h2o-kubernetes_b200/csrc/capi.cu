@@ -76,6 +76,7 @@ struct h2ok_ctx {
   DevBuf<int32_t> child_ids, n_children;
   int n_nodes = 0, max_bins = 0, gid_base = 0;
   bool level_built = false, splits_found = false, children_made = false;
+  bool timed = false;  // ev0/ev1 bracket the last hist_build launches
   h2ok_stats stats{};
 };
 
@@ -161,9 +162,10 @@ int32_t h2ok_hist_destroy(h2ok_ctx* c) {
   return H2OK_OK;
 }
 
-int32_t h2ok_hist_set_stream(h2ok_ctx* c, void* stream) {
+int32_t h2ok_hist_set_stream(h2ok_ctx* c, void* stream, int32_t use_own) {
   REQUIRE(c != nullptr, "null context");
-  c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+  // a NULL handle is a real stream (CUDA's legacy default stream, which is what torch uses by default)
+  c->stream = use_own ? c->own_stream : (cudaStream_t)stream;
   return H2OK_OK;
 }
 
@@ -248,7 +250,10 @@ int32_t h2ok_hist_build_level_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int
   HistArgs a{};
   a.X = d_X; a.ld = ld; a.rows = rows; a.cols = cols; a.nid = d_nid; a.wq = d_wq; a.wyq = d_wyq; a.wyyq = d_wyyq;
   a.descs = d_descs; a.nb1 = nb1; a.acc = d_acc; a.min2_enc = d_min2_enc; a.maxin_enc = d_maxin_enc;
+  CK(cudaEventRecord(c->ev0, c->stream));  // device time of the hist_build launches only (read by last_level_stats)
   CK(launch_hist_build(a, plan, n_nodes, d_wq != nullptr, c->stream));
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->timed = true;
   return H2OK_OK;
 }
 
@@ -411,7 +416,6 @@ int32_t h2ok_hist_build_level(h2ok_ctx* c, int32_t n_nodes, const h2ok_col_desc*
   CK(c->descs.ensure(ncell)); CK(c->acc.ensure(ncell * nb1 * 3)); CK(c->hist.ensure(ncell * nb1 * 3));
   CK(c->mn.ensure(ncell)); CK(c->mx.ensure(ncell)); CK(c->min2.ensure(ncell)); CK(c->maxin.ensure(ncell));
   CK(cudaMemcpyAsync(c->descs.p, descs, sizeof(h2ok_col_desc) * ncell, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaEventRecord(c->ev0, c->stream));
   rc = h2ok_hist_build_level_dev(c, c->X.p, c->ld, c->rows, c->cols, c->nid.p, c->weighted ? c->wq.p : nullptr, c->wyq.p,
                                  c->wyyq.p, n_nodes, c->descs.p, max_bins, 1, c->acc.p, c->mn.p, c->mx.p);
   if (rc) return rc;
@@ -419,12 +423,10 @@ int32_t h2ok_hist_build_level(h2ok_ctx* c, int32_t n_nodes, const h2ok_col_desc*
                                     c->min2.p, c->maxin.p);
   if (rc) return rc;
   c->stats.launches += 2;
-  CK(cudaEventRecord(c->ev1, c->stream));
   if (hist_out) CK(cudaMemcpyAsync(hist_out, c->hist.p, sizeof(double) * ncell * nb1 * 3, cudaMemcpyDeviceToHost, c->stream));
   if (min2_out) CK(cudaMemcpyAsync(min2_out, c->min2.p, sizeof(float) * ncell, cudaMemcpyDeviceToHost, c->stream));
   if (maxin_out) CK(cudaMemcpyAsync(maxin_out, c->maxin.p, sizeof(float) * ncell, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
-  CK(cudaEventElapsedTime(&c->stats.build_ms, c->ev0, c->ev1));
   c->n_nodes = n_nodes;
   c->max_bins = max_bins;
   c->level_built = true;
@@ -504,6 +506,11 @@ int32_t h2ok_hist_get_quant(h2ok_ctx* c, h2ok_quant* out) {
 
 int32_t h2ok_hist_last_level_stats(h2ok_ctx* c, h2ok_stats* out) {
   REQUIRE(c && out, "null pointer");
+  if (c->timed) {  // waits only for the histogram kernels, which callers have normally synchronised past already
+    CK(cudaEventSynchronize(c->ev1));
+    CK(cudaEventElapsedTime(&c->stats.build_ms, c->ev0, c->ev1));
+    c->timed = false;
+  }
   *out = c->stats;
   return H2OK_OK;
 }

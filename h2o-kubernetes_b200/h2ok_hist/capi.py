@@ -18,7 +18,7 @@ SIGNATURES = {
     "h2ok_hist_create": [i32, C.POINTER(vp)],
     "h2ok_hist_destroy": [vp],
     "h2ok_hist_abi_version": [],
-    "h2ok_hist_set_stream": [vp, vp],
+    "h2ok_hist_set_stream": [vp, vp, i32],
     "h2ok_hist_sync": [vp],
     "h2ok_hist_synth_fill_dev": [vp, i32, u64, i64, i64, i32, i64, i32, i32, vp, vp, vp],
     "h2ok_hist_col_ranges_dev": [vp, vp, i64, i64, i32, vp, vp],

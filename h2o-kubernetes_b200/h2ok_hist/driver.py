@@ -40,6 +40,7 @@ class CudaShard:
         self.weighted = False
         self.quant = None
         self._level_cap = None
+        self.launches = 0  # kernels of libh2ok_hist.so launched through this shard
 
     def close(self):
         if self.ctx is not None:
@@ -48,7 +49,7 @@ class CudaShard:
 
     def use_current_stream(self):
         """Kernels go on torch's current stream so torch.cuda.Event timing and NCCL ordering see them."""
-        self.lib.call("h2ok_hist_set_stream", self.ctx, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        self.lib.call("h2ok_hist_set_stream", self.ctx, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream), 0)
 
     # ---- data -------------------------------------------------------------------------------------------
     def _alloc_rows(self, rows, cols, weighted):
@@ -144,21 +145,32 @@ class CudaShard:
         self.lib.call("h2ok_hist_build_level_dev", self.ctx, _ptr(self.X), self.ld, self.rows, self.cols, _ptr(self.nid),
                       _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
+        slots = 1
+        while slots * 2 <= (227 * 1024 - 64 * 28) // ((self.max_bins + 1) * 12):
+            slots *= 2  # same rule as plan_hist() in csrc/hist_kernels.cu
+        self.launches += 1 + (n_nodes + slots - 1) // slots  # init_enc + one hist_build per node group
         return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
+
+    def last_hist_ms(self):
+        """Device time of the last build_level's hist_build launches (CUDA events inside the library)."""
+        return float(self.stats().build_ms)
 
     def finalize_level(self, n_nodes):
         self.lib.call("h2ok_hist_finalize_level_dev", self.ctx, _ptr(self.acc), _ptr(self.mn), _ptr(self.mx), n_nodes,
                       self.cols, self.max_bins, C.byref(self.quant), _ptr(self.hist), _ptr(self.min2), _ptr(self.maxin))
+        self.launches += 2
 
     # ---- a7 / a8 / a6 ------------------------------------------------------------------------------------
     def find_splits(self, n_nodes, min_rows, msi):
         self.lib.call("h2ok_hist_find_splits_dev", self.ctx, _ptr(self.hist), _ptr(self.descs), n_nodes, self.cols,
                       self.max_bins, float(min_rows), float(msi), _ptr(self.splits))
+        self.launches += 1
 
     def next_level(self, n_nodes, params, depth):
         self.lib.call("h2ok_hist_next_level_dev", self.ctx, _ptr(self.splits), _ptr(self.descs), _ptr(self.min2),
                       _ptr(self.maxin), n_nodes, self.cols, C.byref(params), depth, _ptr(self.child_descs),
                       _ptr(self.child_ids), _ptr(self.n_children))
+        self.launches += 2
         return int(self.n_children.item())  # the one host sync per level: how many nodes the next level has
 
     def no_children(self, n_nodes):
@@ -167,6 +179,7 @@ class CudaShard:
     def apply_splits(self, n_nodes, gid_base):
         self.lib.call("h2ok_hist_apply_splits_dev", self.ctx, _ptr(self.X), self.ld, self.rows, _ptr(self.splits),
                       _ptr(self.child_ids), gid_base, n_nodes, _ptr(self.nid), _ptr(self.leaf))
+        self.launches += 1
 
     # ---- host copies (tests, tree assembly) --------------------------------------------------------------
     def splits_np(self, n):
@@ -211,6 +224,9 @@ class LevelDriver:
         self.lib = shard.lib
         self.max_bins = max(params.nbins, params.nbins_top_level)
         self.root = None
+        self.n_nodes = 0
+        self.depth = 0
+        self.gid_base = 0
 
     # -- once per data set: root descriptors from the global column ranges
     def prepare_data(self):
@@ -273,6 +289,10 @@ class LevelDriver:
             sh.adopt_children(nch)
         self.n_nodes = nch
         return done_nodes, nch
+
+    def n_nodes_left(self):
+        """Active nodes waiting for the next level; 0 when the current tree is finished (or none was started)."""
+        return self.n_nodes if self.depth < self.params.max_depth else 0
 
     def train_tree(self, inspect=None):
         self.prepare_tree()

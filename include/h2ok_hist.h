@@ -110,8 +110,9 @@ int32_t h2ok_hist_create(int32_t device, h2ok_ctx** out);
 int32_t h2ok_hist_destroy(h2ok_ctx* ctx);
 const char* h2ok_last_error(void);
 int32_t h2ok_hist_abi_version(void);
-/* Use `stream` (a cudaStream_t) for every *_dev call instead of the context's own stream. */
-int32_t h2ok_hist_set_stream(h2ok_ctx* ctx, void* stream);
+/* use_own == 0: run every call on `stream` (a cudaStream_t; NULL is CUDA's legacy default stream, a valid choice).
+ * use_own != 0: go back to the context's own non-blocking stream (the state after create). */
+int32_t h2ok_hist_set_stream(h2ok_ctx* ctx, void* stream, int32_t use_own);
 int32_t h2ok_hist_sync(h2ok_ctx* ctx);
 
 /* ---- device-resident entry points (pointers are device pointers; asynchronous) -------------- */

@@ -245,7 +245,7 @@ def test_quantised_level_matches_fp64_level(oracle, weight_mode):
     n_in_bin = oracle.build_level(X, rows, np.ones(rows, np.float32), None, nid, descs, nb)[0][..., 0]
     assert (np.abs(hq[..., 1] - hist[..., 1]) <= n_in_bin * 0.5 / q.scale_wy + 1e-300).all()
     assert (np.abs(hq[..., 2] - hist[..., 2]) <= n_in_bin * 0.5 / q.scale_wyy + 1e-300).all()
-    assert (np.abs(hq[..., 1] - hist[..., 1]) <= 1e-5 * absy + n_in_bin * m[1] * 2.0**-27).all()
+    assert (np.abs(hq[..., 1] - hist[..., 1]) <= 1e-5 * absy + n_in_bin * 0.5 / q.scale_wy).all()
     del cnt
 
 
