@@ -298,6 +298,28 @@ int32_t h2ok_hist_next_level_dev(h2ok_ctx* c, const h2ok_split* d_splits, const 
   return H2OK_OK;
 }
 
+// Allocation-free a8 for callers that may not allocate device memory while running (see include/h2ok_hist.h).
+// Same kernels as h2ok_hist_next_level_dev; the scratch is the library's fixed device array instead of ctx buffers.
+int32_t h2ok_hist_next_level_noalloc_dev(h2ok_ctx* c, const h2ok_split* d_splits, const h2ok_col_desc* d_descs,
+                                         const float* d_min2, const float* d_maxin, int32_t n_nodes, int32_t cols,
+                                         const h2ok_params* params, int32_t depth, h2ok_col_desc* d_child_descs,
+                                         int32_t* d_child_ids, int32_t* d_n_children) {
+  (void)depth;
+  REQUIRE(c && d_splits && d_descs && d_min2 && d_maxin && params && d_child_descs && d_child_ids && d_n_children,
+          "null pointer");
+  int32_t rc = check_level_shape(n_nodes, cols, params->nbins);
+  if (rc) return rc;
+  if ((int64_t)2 * n_nodes * cols > H2OK_NOALLOC_MAX_SLOT_COLS)
+    return fail(H2OK_ERR_ARG, "%s", "next_level_noalloc: 2*n_nodes*cols exceeds H2OK_NOALLOC_MAX_SLOT_COLS (16384); "
+                                    "use h2ok_hist_next_level_dev for larger levels");
+  if (2 * n_nodes > H2OK_NOALLOC_MAX_SLOTS)
+    return fail(H2OK_ERR_ARG, "%s", "next_level_noalloc: 2*n_nodes exceeds H2OK_NOALLOC_MAX_SLOTS (2048); "
+                                    "use h2ok_hist_next_level_dev for larger levels");
+  CK(launch_next_level_noalloc(d_splits, d_descs, d_min2, d_maxin, n_nodes, cols, *params, d_child_descs, d_child_ids,
+                               d_n_children, c->stream));
+  return H2OK_OK;
+}
+
 int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int64_t rows, const h2ok_split* d_splits,
                                    const int32_t* d_child_ids, int32_t gid_base, int32_t n_nodes, int32_t* d_nid,
                                    int32_t* d_leaf) {

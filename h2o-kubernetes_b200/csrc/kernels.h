@@ -54,6 +54,10 @@ cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, i
 cudaError_t launch_next_level(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2, const float* maxin,
                               int n_nodes, int cols, const h2ok_params& p, h2ok_col_desc* tmp_descs, int32_t* tmp_valid,
                               h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children, cudaStream_t s);
+cudaError_t launch_next_level_noalloc(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2,
+                                      const float* maxin, int n_nodes, int cols, const h2ok_params& p,
+                                      h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children,
+                                      cudaStream_t s);
 cudaError_t launch_apply_splits(const float* X, int64_t ld, int64_t rows, const h2ok_split* splits,
                                 const int32_t* child_ids, int gid_base, int n_nodes, int32_t* nid, int32_t* leaf,
                                 cudaStream_t s);

@@ -466,6 +466,43 @@ cudaError_t launch_next_level(const h2ok_split* splits, const h2ok_col_desc* des
   return cudaGetLastError();
 }
 
+// ---- allocation-free variant of a8 ---------------------------------------------------------------------------
+// Some hosts of this library must never cause a device allocation while they run: an H2O node (or any embedding
+// process) that has handed all of the GPU's memory to a pool allocator cannot let a raw cudaMalloc compete with
+// that pool, and a service loop with a latency budget cannot accept the device-wide synchronisation cudaMalloc /
+// cudaFree imply.  For them the scratch of next_level (candidate child descriptors + one flag per child slot) lives
+// in this fixed array instead of a grow-on-demand buffer.  It costs kNoAllocScratchBytes (520 KiB) on every GPU that
+// loads the library, until the process exits.
+constexpr size_t kNoAllocDescBytes = (size_t)H2OK_NOALLOC_MAX_SLOT_COLS * sizeof(h2ok_col_desc);
+constexpr size_t kNoAllocScratchBytes = kNoAllocDescBytes + (size_t)H2OK_NOALLOC_MAX_SLOTS * sizeof(int32_t);
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// The array's name is only a host-side handle; the device address is looked up once per device (with that device
+// current) and cached.  The first call on a device therefore does a symbol lookup and should be made before any
+// stream capture begins.
+cudaError_t launch_next_level_noalloc(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2,
+                                      const float* maxin, int n_nodes, int cols, const h2ok_params& p,
+                                      h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children,
+                                      cudaStream_t s) {
+  constexpr int kMaxDevices = 64;
+  static unsigned char* dev_ptr[kMaxDevices] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  if (dev_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    dev_ptr[dev] = static_cast<unsigned char*>(ptr);
+  }
+  h2ok_col_desc* tmp_descs = reinterpret_cast<h2ok_col_desc*>(dev_ptr[dev]);
+  int32_t* tmp_valid = reinterpret_cast<int32_t*>(dev_ptr[dev] + kNoAllocDescBytes);
+  // the array still holds the previous call's flags: launch_next_level clears the ones this call uses
+  return launch_next_level(splits, descs, min2, maxin, n_nodes, cols, p, tmp_descs, tmp_valid, child_descs, child_ids,
+                           n_children, s);
+}
+
 cudaError_t launch_apply_splits(const float* X, int64_t ld, int64_t rows, const h2ok_split* splits,
                                 const int32_t* child_ids, int gid_base, int n_nodes, int32_t* nid, int32_t* leaf,
                                 cudaStream_t s) {

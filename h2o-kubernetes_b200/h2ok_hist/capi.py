@@ -29,6 +29,7 @@ SIGNATURES = {
     "h2ok_hist_finalize_level_dev": [vp, vp, vp, vp, i32, i32, i32, pQ, vp, vp, vp],
     "h2ok_hist_find_splits_dev": [vp, vp, vp, i32, i32, i32, f64, f64, vp],
     "h2ok_hist_next_level_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
+    "h2ok_hist_next_level_noalloc_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
     "h2ok_hist_apply_splits_dev": [vp, vp, i64, i64, vp, vp, i32, i32, vp, vp],
     "h2ok_hist_root_descs_from_ranges": [vp, vp, i32, pP, vp, vp],
     "h2ok_hist_choose_quant": [vp, i32, i32, pQ],

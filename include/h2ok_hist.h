@@ -45,6 +45,9 @@ extern "C" {
 
 #define H2OK_MAX_BINS 1024
 #define H2OK_MAX_LEVEL_NODES 4096
+/* limits of h2ok_hist_next_level_noalloc_dev: 2*n_nodes*cols and 2*n_nodes may not exceed these */
+#define H2OK_NOALLOC_MAX_SLOT_COLS 16384
+#define H2OK_NOALLOC_MAX_SLOTS 2048
 
 /* NA direction of a split (DHistogram.NASplitDir). */
 #define H2OK_NA_NONE 0
@@ -167,6 +170,23 @@ int32_t h2ok_hist_next_level_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, cons
                                  const float* d_min2, const float* d_maxin, int32_t n_nodes, int32_t cols,
                                  const h2ok_params* params, int32_t depth, h2ok_col_desc* d_child_descs,
                                  int32_t* d_child_ids, int32_t* d_n_children);
+
+/* a8 without any allocation — same inputs, outputs and results as h2ok_hist_next_level_dev.  No counterpart in the
+ * reference (nor in H2O-3): it exists for hosts that cannot allocate device memory while they run — a process whose
+ * GPU memory is wholly owned by a pool allocator, or a loop that cannot tolerate the device-wide synchronisation of
+ * cudaMalloc/cudaFree.  h2ok_hist_next_level_dev grows a scratch buffer inside the context on demand; this variant
+ * keeps that scratch in a fixed 520 KiB device array that is part of the library image (resident on every GPU that
+ * loads the library until the process exits) and calls no cudaMalloc, cudaFree or other allocating routine.
+ * Limits: 2*n_nodes*cols <= H2OK_NOALLOC_MAX_SLOT_COLS and 2*n_nodes <= H2OK_NOALLOC_MAX_SLOTS, otherwise
+ * H2OK_ERR_ARG with a message naming the limit (128 nodes x 64 columns fits exactly).
+ * The first call on each device looks up the array's device address (with that device current) and caches it; make
+ * that first call before starting any stream capture.  All calls on a device share the one array, which keeps the
+ * previous call's contents (the flags are cleared at the start of each call): two calls that overlap on the GPU —
+ * different streams or contexts — race on it, so serialise them. */
+int32_t h2ok_hist_next_level_noalloc_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, const h2ok_col_desc* d_descs,
+                                         const float* d_min2, const float* d_maxin, int32_t n_nodes, int32_t cols,
+                                         const h2ok_params* params, int32_t depth, h2ok_col_desc* d_child_descs,
+                                         int32_t* d_child_ids, int32_t* d_n_children);
 
 /* a6 — ScoreBuildHistogram.score_decide / DecidedNode.getChildNodeID: move each active row to its child.
  * A row that retires gets nid -1 and d_leaf[r] = 3*(gid_base+node) + k, k = 0 node did not split, 1 / 2 the left /
