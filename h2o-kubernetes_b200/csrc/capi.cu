@@ -57,6 +57,9 @@ struct h2ok_ctx {
   // scratch of next_level (a8)
   DevBuf<h2ok_col_desc> tmp_descs;
   DevBuf<int32_t> tmp_valid;
+  // scratch of build_level: packed row records + range-error flag
+  DevBuf<uint2> rec;
+  DevBuf<int32_t> rec_err;
   // resident data of the host-buffer API
   DevBuf<float> X, y, w;
   DevBuf<int32_t> nid, leaf, wq, wyq, wyyq;
@@ -150,7 +153,7 @@ int32_t h2ok_hist_destroy(h2ok_ctx* c) {
   if (!c) return H2OK_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  c->tmp_descs.release(); c->tmp_valid.release(); c->X.release(); c->y.release(); c->w.release();
+  c->tmp_descs.release(); c->tmp_valid.release(); c->rec.release(); c->rec_err.release(); c->X.release(); c->y.release(); c->w.release();
   c->nid.release(); c->leaf.release(); c->wq.release(); c->wyq.release(); c->wyyq.release(); c->absmax.release();
   c->cmin.release(); c->cmax.release(); c->descs.release(); c->child_descs.release(); c->acc.release();
   c->mn.release(); c->mx.release(); c->hist.release(); c->min2.release(); c->maxin.release(); c->splits.release();
@@ -243,14 +246,21 @@ int32_t h2ok_hist_build_level_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int
   HistPlan plan = plan_hist(n_nodes, cols, rows, nb1);
   c->stats.passes = plan.passes;
   c->stats.copies = plan.copies;
-  c->stats.launches = plan.passes + (clear ? 2 : 0);
+  c->stats.launches = plan.passes + 1 + (clear ? 1 : 0);  // hist passes + pack_rows + init_enc
   c->stats.algo_bytes = (double)rows * cols * 4.0 + (double)rows * (4.0 + 4.0 + 4.0 + (d_wq ? 4.0 : 0.0)) +
                         (double)ncell * nb1 * 3 * 8.0;
   if (rows == 0) return H2OK_OK;
+  const int64_t padded = (rows + 3) / 4 * 4;
+  CK(c->rec.ensure((size_t)padded));
+  if (!c->rec_err.p) {
+    CK(c->rec_err.ensure(1));
+    CK(cudaMemsetAsync(c->rec_err.p, 0, sizeof(int32_t), c->stream));
+  }
   HistArgs a{};
-  a.X = d_X; a.ld = ld; a.rows = rows; a.cols = cols; a.nid = d_nid; a.wq = d_wq; a.wyq = d_wyq; a.wyyq = d_wyyq;
+  a.X = d_X; a.ld = ld; a.rows = rows; a.cols = cols; a.rec = c->rec.p; a.wq = d_wq;
   a.descs = d_descs; a.nb1 = nb1; a.acc = d_acc; a.min2_enc = d_min2_enc; a.maxin_enc = d_maxin_enc;
-  CK(cudaEventRecord(c->ev0, c->stream));  // device time of the hist_build launches only (read by last_level_stats)
+  CK(cudaEventRecord(c->ev0, c->stream));  // device time of pack + hist_build launches (read by last_level_stats)
+  CK(launch_pack_rows(d_nid, d_wq, d_wyq, d_wyyq, rows, padded, n_nodes, c->rec.p, c->rec_err.p, c->stream));
   CK(launch_hist_build(a, plan, n_nodes, d_wq != nullptr, c->stream));
   CK(cudaEventRecord(c->ev1, c->stream));
   c->timed = true;
@@ -368,7 +378,7 @@ int32_t h2ok_hist_set_targets_host(h2ok_ctx* c, const float* y_host, const float
   double m[3];
   CK(cudaMemcpyAsync(m, c->absmax.p, sizeof(m), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
-  h2ok_hist_choose_quant(m, c->weighted ? 1 : 0, 26, &c->q);
+  h2ok_hist_choose_quant(m, c->weighted ? 1 : 0, 25, &c->q);
   CK(launch_quantize_rows(c->y.p, c->weighted ? c->w.p : nullptr, n, c->q, c->weighted ? c->wq.p : nullptr, c->wyq.p,
                           c->wyyq.p, c->stream));
   CK(cudaMemsetAsync(c->nid.p, 0, sizeof(int32_t) * (size_t)n, c->stream));
@@ -398,7 +408,7 @@ int32_t h2ok_hist_root_descs_from_ranges(const float* col_min, const float* col_
 
 int32_t h2ok_hist_choose_quant(const double* m, int32_t weighted, int32_t qbits, h2ok_quant* q) {
   REQUIRE(m && q, "null pointer");
-  REQUIRE(qbits >= 8 && qbits <= 30, "qbits outside [8,30]");
+  REQUIRE(qbits >= 8 && qbits <= 25, "qbits outside [8,25] (the packed row records hold 27-bit targets)");
   q->weighted = weighted ? 1 : 0;
   q->qbits = qbits;
   q->scale_w = weighted ? pow2_scale(m[0], qbits) : 1.0;
@@ -532,6 +542,12 @@ int32_t h2ok_hist_last_level_stats(h2ok_ctx* c, h2ok_stats* out) {
     CK(cudaEventSynchronize(c->ev1));
     CK(cudaEventElapsedTime(&c->stats.build_ms, c->ev0, c->ev1));
     c->timed = false;
+    if (c->rec_err.p) {
+      int32_t e = 0;
+      CK(cudaMemcpyAsync(&e, c->rec_err.p, sizeof(e), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      c->stats.range_errors = e;
+    }
   }
   *out = c->stats;
   return H2OK_OK;

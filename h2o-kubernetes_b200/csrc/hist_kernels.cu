@@ -110,111 +110,248 @@ __global__ void bin_kernel(const float* __restrict__ x, int64_t n, h2ok_col_desc
 }
 
 // ------------------------------------------------------------------------------------------------ a3/a4 build
-// 32-bit shared add with the carry/borrow out of bit 31 forwarded to the 64-bit global accumulator.
-__device__ __forceinline__ void add_lo_carry(int* slot, int v, unsigned long long* gslot) {
-  unsigned old = atomicAdd(reinterpret_cast<unsigned*>(slot), (unsigned)v);
-  unsigned nw = old + (unsigned)v;
-  int hi = (v >> 31) + (nw < (unsigned)v ? 1 : 0);  // sign extension of v plus carry-out: -1, 0 or +1
-  if (hi != 0) atomicAdd(gslot, (unsigned long long)(long long)hi << 32);
-}
+// Row records.  Once per level every row's node index and fixed-point targets are packed into one 8-byte word so
+// that the hot kernel reads 12 B per cell from L2 instead of 16 and needs no per-cell validity / weight test:
+//   lo = wyq  << 5 | node[4:0]     (wyq  signed,   |wyq|  < 2^26)
+//   hi = wyyq << 5 | node[9:5]     (wyyq unsigned,  wyyq  < 2^27)
+// node 0x3FF marks a row that takes no part in this level (already in a leaf, or zero weight).
+constexpr unsigned kNoNode = 0x3FFu;
 
-template <bool WEIGHTED>
-__device__ __forceinline__ void accumulate_row(const HistArgs& a, int col, float x, int nid, int wq, int wyq, int wyyq,
-                                               int sub, const double* s_min, const double* s_step, const int* s_nbin,
-                                               unsigned* s_mn, unsigned* s_mx, int* h0, int chstride) {
-  unsigned g = (unsigned)(nid - a.node_base);
-  if (g >= (unsigned)a.node_cnt) return;
-  int nb = s_nbin[g];
-  if (nb <= 0) return;
-  if (WEIGHTED && wq == 0) return;  // updateHisto: zero-weight rows are skipped before min/max
-  if (x == x) {                     // observed range (_min2/_maxIn); NaN never compares
-    unsigned e = enc_f32_bits(__float_as_uint(x));
-    if (e < s_mn[g]) atomicMin(&s_mn[g], e);
-    if (e > s_mx[g]) atomicMax(&s_mx[g], e);
+__global__ void pack_rows_kernel(const int32_t* __restrict__ nid, const int32_t* __restrict__ wq,
+                                 const int32_t* __restrict__ wyq, const int32_t* __restrict__ wyyq, int64_t rows,
+                                 int64_t padded, int n_nodes, uint2* __restrict__ rec, int32_t* __restrict__ err) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= padded) return;
+  unsigned node = kNoNode;
+  int y1 = 0, y2 = 0;
+  if (r < rows) {
+    int g = nid[r];
+    y1 = wyq[r];
+    y2 = wyyq[r];
+    if (g >= 0 && g < n_nodes && (!wq || wq[r] != 0)) node = (unsigned)g;
+    if (y1 >= (1 << 26) || y1 < -(1 << 26) || y2 < 0 || y2 >= (1 << 27) || (wq && (wq[r] < 0 || wq[r] >= (1 << 27)))) {
+      atomicOr(err, 1);  // targets outside the packed format's range (qbits > 25): reported by last_level_stats
+      node = kNoNode;
+    }
   }
-  int b = bin_of(x, s_min[g], s_step[g], nb);
-  int cell = (int)g * a.nb1 + b;
-  int idx = cell * a.copies + sub;
-  unsigned long long* gs =
-      reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(a.node_base + g) * a.cols + col) * a.nb1 + b) * 3;
-  if (WEIGHTED)
-    add_lo_carry(h0 + idx, wq, gs);
-  else
-    atomicAdd(reinterpret_cast<unsigned*>(h0 + idx), 1u);  // < 2^32 rows per CTA: never carries
-  add_lo_carry(h0 + chstride + idx, wyq, gs + 1);
-  add_lo_carry(h0 + 2 * chstride + idx, wyyq, gs + 2);
+  rec[r] = make_uint2(((unsigned)y1 << 5) | (node & 31u), ((unsigned)y2 << 5) | (node >> 5));
 }
 
-template <bool WEIGHTED>
+// Cold path: a 32-bit shared word wrapped; the carry / borrow goes to the 64-bit global accumulator.
+__device__ __noinline__ void carry_to_global(int64_t* acc, int64_t cell_index, int ch, int delta) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(acc) + cell_index * 3 + ch, (unsigned long long)(long long)delta << 32);
+}
+
+struct NodeMeta {  // shared-memory record per node of the group (16 B, read with one LDS.128)
+  int nbin;
+  int cellofs;        // byte offset of the node's first histogram word
+  unsigned emn, emx;  // encoded observed min / max so far; a row touches them only when it beats them
+};
+
+template <bool WEIGHTED, bool ONE_NODE>
+struct RowCtx {
+  const HistArgs& a;
+  unsigned char* hsub;  // histogram base + this lane's copy offset
+  const double2* s_desc;
+  NodeMeta* s_meta;
+  int cstride;  // bytes between consecutive bins of one node (copies * 12)
+  int col;
+  // ONE_NODE: the single descriptor and the thread's running extremes live in registers
+  double mn, step;
+  int nbin;
+  float fmn, fmx;
+};
+
+// a2 inside the hot loop: same value as bin_of() with fewer instructions — the saturating unsigned conversion sends
+// negative and NaN positions to 0 and huge ones to UINT_MAX, one unsigned min applies the round-off clamp.
+__device__ __forceinline__ int bin_fast(float x, double mn, double step, int nbin) {
+  const double pos = __dmul_rn(__dsub_rn((double)x, mn), step);
+  const unsigned idx = min(__double2uint_rz(pos), (unsigned)(nbin - 1));
+  return x != x ? nbin : (int)idx;
+}
+
+template <bool WEIGHTED, bool ONE_NODE>
+__device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, ONE_NODE>& c, float x, unsigned lo, unsigned hi, int wq) {
+  unsigned g = 0;
+  int nbin, cellofs = 0, b;
+  if (ONE_NODE) {
+    if ((lo | hi) & 31u) return;  // only node 0 exists at this level
+    nbin = c.nbin;
+    b = bin_fast(x, c.mn, c.step, nbin);
+    c.fmn = fminf(c.fmn, x);  // NaN-ignoring, exact: the thread's observed range stays in two registers
+    c.fmx = fmaxf(c.fmx, x);
+  } else {
+    g = ((lo & 31u) | ((hi & 31u) << 5)) - (unsigned)c.a.node_base;
+    if (g >= (unsigned)c.a.node_cnt) return;
+    const int4 m = *reinterpret_cast<const int4*>(&c.s_meta[g]);
+    nbin = m.x;
+    if (nbin <= 0) return;
+    cellofs = m.y;
+    const double2 d = c.s_desc[g];
+    b = bin_fast(x, d.x, d.y, nbin);
+    const unsigned xb = __float_as_uint(x);
+    const unsigned e = xb ^ ((unsigned)((int)xb >> 31) | 0x80000000u);  // == enc_f32_bits(xb)
+    if ((e < (unsigned)m.z) | (e > (unsigned)m.w)) {  // a new record (rare), or NaN (whose encoding sorts above +inf)
+      if (x == x) {
+        atomicMin(&c.s_meta[g].emn, e);
+        atomicMax(&c.s_meta[g].emx, e);
+      }
+    }
+  }
+  unsigned* p = reinterpret_cast<unsigned*>(c.hsub + cellofs + b * c.cstride);
+  const int v1 = (int)lo >> 5;
+  const unsigned v2 = hi >> 5;
+  bool ev = false;
+  if (WEIGHTED) {
+    unsigned o0 = atomicAdd(p, (unsigned)wq);
+    ev = o0 + (unsigned)wq < o0;
+  } else {
+    atomicAdd(p, 1u);  // < 2^32 rows per CTA: never wraps
+  }
+  const unsigned o1 = atomicAdd(p + 1, (unsigned)v1);
+  const unsigned n1 = o1 + (unsigned)v1;
+  const bool e1 = (n1 < o1) != (v1 < 0);  // carry when adding a positive value, borrow when adding a negative one
+  const unsigned o2 = atomicAdd(p + 2, v2);
+  const bool e2 = o2 + v2 < o2;
+  if (ev | e1 | e2) {
+    const int64_t cell = ((int64_t)(c.a.node_base + g) * c.a.cols + c.col) * c.a.nb1 + b;
+    if (ev) carry_to_global(c.a.acc, cell, 0, 1);
+    if (e1) carry_to_global(c.a.acc, cell, 1, v1 < 0 ? -1 : 1);
+    if (e2) carry_to_global(c.a.acc, cell, 2, 1);
+  }
+}
+
+constexpr unsigned kWyBias = 0x80000000u;  // wY words start mid-range so that sums hovering around zero never wrap
+
+template <bool WEIGHTED, bool ONE_NODE>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* s_min = reinterpret_cast<double*>(smem_raw);
-  double* s_step = s_min + a.node_cnt;
-  int* s_nbin = reinterpret_cast<int*>(s_step + a.node_cnt);
-  unsigned* s_mn = reinterpret_cast<unsigned*>(s_nbin + a.node_cnt);
-  unsigned* s_mx = s_mn + a.node_cnt;
-  int* h0 = reinterpret_cast<int*>(s_mx + a.node_cnt);
-  const int chstride = a.node_cnt * a.nb1 * a.copies;
+  const int cnt = a.node_cnt;
+  double2* s_desc = reinterpret_cast<double2*>(smem_raw);
+  NodeMeta* s_meta = reinterpret_cast<NodeMeta*>(s_desc + cnt);
+  unsigned* h = reinterpret_cast<unsigned*>(s_meta + cnt);
+  const int copies = a.copies, nb1 = a.nb1;
+  const int cells = cnt * nb1;
+  const int words = cells * copies * 3;
   const int col = blockIdx.x % a.cols;
   const int chunk = blockIdx.x / a.cols;
   const int tid = threadIdx.x;
 
-  for (int i = tid; i < 3 * chstride; i += kHistThreads) h0[i] = 0;
-  for (int g = tid; g < a.node_cnt; g += kHistThreads) {
+  for (int i = tid; i < words; i += kHistThreads) h[i] = (i % 3 == 1) ? kWyBias : 0u;
+  for (int g = tid; g < cnt; g += kHistThreads) {
     const h2ok_col_desc& d = a.descs[(int64_t)(a.node_base + g) * a.cols + col];
-    s_min[g] = d.min;
-    s_step[g] = d.step;
-    s_nbin[g] = d.nbin;
-    s_mn[g] = kEncPosInf;
-    s_mx[g] = kEncNegInf;
+    s_desc[g] = make_double2(d.min, d.step);
+    NodeMeta m;
+    m.nbin = d.nbin;
+    m.cellofs = g * nb1 * copies * 12;
+    m.emn = kEncPosInf;
+    m.emx = kEncNegInf;
+    s_meta[g] = m;
   }
   __syncthreads();
 
   const int64_t r0 = (int64_t)chunk * a.chunk_rows;
   const int64_t r1 = min(a.rows, r0 + a.chunk_rows);
-  const float* __restrict__ x = a.X + (int64_t)col * a.ld;
-  const int sub = tid & (a.copies - 1);
+  const int n = (int)(r1 - r0);
+  const int nvec = n & ~3;
+  const float* __restrict__ x = a.X + (int64_t)col * a.ld + r0;
+  const uint2* __restrict__ rec = a.rec + r0;
+  const int32_t* __restrict__ wq = WEIGHTED ? a.wq + r0 : nullptr;
 
-  for (int64_t base = r0 + (int64_t)tid * 4; base < r1; base += (int64_t)kHistThreads * 4) {
-    if (base + 4 <= r1) {
-      float4 xv = __ldcs(reinterpret_cast<const float4*>(x + base));  // streamed once: evict-first
-      int4 nv = __ldg(reinterpret_cast<const int4*>(a.nid + base));
-      int4 yv = __ldg(reinterpret_cast<const int4*>(a.wyq + base));
-      int4 zv = __ldg(reinterpret_cast<const int4*>(a.wyyq + base));
-      int4 wv = make_int4(1, 1, 1, 1);
-      if (WEIGHTED) wv = __ldg(reinterpret_cast<const int4*>(a.wq + base));
-      accumulate_row<WEIGHTED>(a, col, xv.x, nv.x, wv.x, yv.x, zv.x, sub, s_min, s_step, s_nbin, s_mn, s_mx, h0, chstride);
-      accumulate_row<WEIGHTED>(a, col, xv.y, nv.y, wv.y, yv.y, zv.y, sub, s_min, s_step, s_nbin, s_mn, s_mx, h0, chstride);
-      accumulate_row<WEIGHTED>(a, col, xv.z, nv.z, wv.z, yv.z, zv.z, sub, s_min, s_step, s_nbin, s_mn, s_mx, h0, chstride);
-      accumulate_row<WEIGHTED>(a, col, xv.w, nv.w, wv.w, yv.w, zv.w, sub, s_min, s_step, s_nbin, s_mn, s_mx, h0, chstride);
-    } else {
-      for (int64_t r = base; r < r1; r++)
-        accumulate_row<WEIGHTED>(a, col, x[r], a.nid[r], WEIGHTED ? a.wq[r] : 1, a.wyq[r], a.wyyq[r], sub, s_min, s_step,
-                                 s_nbin, s_mn, s_mx, h0, chstride);
+  RowCtx<WEIGHTED, ONE_NODE> c{a};
+  c.hsub = reinterpret_cast<unsigned char*>(h) + (tid & (copies - 1)) * 12;
+  c.s_desc = s_desc;
+  c.s_meta = s_meta;
+  c.cstride = copies * 12;
+  c.col = col;
+  c.mn = s_desc[0].x;
+  c.step = s_desc[0].y;
+  c.nbin = s_meta[0].nbin;
+  c.fmn = __int_as_float(0x7f800000);
+  c.fmx = __int_as_float(0xff800000);
+
+  if (!ONE_NODE || c.nbin > 0) {
+    // two register tiles in ping-pong: the next tile's loads are in flight while this tile's atomics issue
+    constexpr int kStep = kHistThreads * 4;
+    const float* xp = x + tid * 4;
+    const uint2* rp = rec + tid * 4;
+    const int32_t* wp = WEIGHTED ? wq + tid * 4 : nullptr;
+    int left = nvec - tid * 4;  // rows from this thread's position to the end of the vector part
+    float4 xa = make_float4(0, 0, 0, 0), xb = xa;
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0, b0 = a0, b1 = a0;
+    int4 wa = make_int4(0, 0, 0, 0), wb = wa;
+#define H2OK_LOAD_TILE(XV, R0, R1, WV, OFF)                                        \
+  {                                                                                \
+    XV = __ldcs(reinterpret_cast<const float4*>(xp + (OFF))); /* streamed once */  \
+    R0 = __ldg(reinterpret_cast<const uint4*>(rp + (OFF)));                        \
+    R1 = __ldg(reinterpret_cast<const uint4*>(rp + (OFF) + 2));                    \
+    if (WEIGHTED) WV = __ldg(reinterpret_cast<const int4*>(wp + (OFF)));           \
+  }
+#define H2OK_DO_TILE(XV, R0, R1, WV)                 \
+  {                                                  \
+    accumulate_row(c, XV.x, R0.x, R0.y, WV.x);       \
+    accumulate_row(c, XV.y, R0.z, R0.w, WV.y);       \
+    accumulate_row(c, XV.z, R1.x, R1.y, WV.z);       \
+    accumulate_row(c, XV.w, R1.z, R1.w, WV.w);       \
+  }
+    if (left > 0) {
+      H2OK_LOAD_TILE(xa, a0, a1, wa, 0);
+      while (true) {
+        if (left > kStep) H2OK_LOAD_TILE(xb, b0, b1, wb, kStep);
+        H2OK_DO_TILE(xa, a0, a1, wa);
+        left -= kStep;
+        if (left <= 0) break;
+        xp += 2 * kStep;
+        rp += 2 * kStep;
+        if (WEIGHTED) wp += 2 * kStep;
+        if (left > kStep) H2OK_LOAD_TILE(xa, a0, a1, wa, 0);
+        H2OK_DO_TILE(xb, b0, b1, wb);
+        left -= kStep;
+        if (left <= 0) break;
+      }
+    }
+#undef H2OK_LOAD_TILE
+#undef H2OK_DO_TILE
+    if (tid < n - nvec) {  // at most 3 rows at the very end of the shard
+      const int r = nvec + tid;
+      const uint2 q = rec[r];
+      accumulate_row(c, x[r], q.x, q.y, WEIGHTED ? wq[r] : 1);
+    }
+  }
+  if (ONE_NODE) {
+    unsigned emn = __reduce_min_sync(0xffffffffu, enc_f32_bits(__float_as_uint(c.fmn)));
+    unsigned emx = __reduce_max_sync(0xffffffffu, enc_f32_bits(__float_as_uint(c.fmx)));
+    if ((tid & 31) == 0) {
+      atomicMin(&s_meta[0].emn, emn);
+      atomicMax(&s_meta[0].emx, emx);
     }
   }
   __syncthreads();
 
-  // flush: low words of every copy (zero-extended) → global 64-bit accumulators; lane-rotated copy order keeps the
-  // shared reads conflict-free when copies == 32
-  const int cells = a.node_cnt * a.nb1;
+  // flush: low words of every copy → global 64-bit accumulators (zero-extended; the wY bias is taken back out).
+  // The copy order is rotated by lane so that the reads stay conflict-free.
   const int lane = tid & 31;
   for (int i = tid; i < cells; i += kHistThreads) {
-    int g = i / a.nb1, b = i - g * a.nb1;
+    const int g = i / nb1, b = i - g * nb1;
     unsigned long long* gs =
-        reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(a.node_base + g) * a.cols + col) * a.nb1 + b) * 3;
-#pragma unroll
-    for (int ch = 0; ch < 3; ch++) {
-      const int* h = h0 + ch * chstride + i * a.copies;
-      unsigned long long s = 0;
-      for (int k = 0; k < a.copies; k++) s += (unsigned)h[(k + lane) & (a.copies - 1)];
-      if (s) atomicAdd(gs + ch, s);
+        reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(a.node_base + g) * a.cols + col) * nb1 + b) * 3;
+    const unsigned* hc = h + (size_t)i * copies * 3;
+    unsigned long long s0 = 0, s1 = 0, s2 = 0;
+    for (int k = 0; k < copies; k++) {
+      const unsigned* w = hc + ((k + lane) & (copies - 1)) * 3;
+      s0 += w[0];
+      s1 += w[1];
+      s2 += w[2];
     }
+    s1 -= (unsigned long long)copies * kWyBias;
+    if (s0) atomicAdd(gs, s0);
+    if (s1) atomicAdd(gs + 1, s1);
+    if (s2) atomicAdd(gs + 2, s2);
   }
-  for (int g = tid; g < a.node_cnt; g += kHistThreads) {
-    int64_t nc = (int64_t)(a.node_base + g) * a.cols + col;
-    if (s_mn[g] != kEncPosInf) atomicMin(&a.min2_enc[nc], s_mn[g]);
-    if (s_mx[g] != kEncNegInf) atomicMax(&a.maxin_enc[nc], s_mx[g]);
+  for (int g = tid; g < cnt; g += kHistThreads) {
+    const int64_t nc = (int64_t)(a.node_base + g) * a.cols + col;
+    if (s_meta[g].emn != kEncPosInf) atomicMin(&a.min2_enc[nc], s_meta[g].emn);
+    if (s_meta[g].emx != kEncNegInf) atomicMax(&a.maxin_enc[nc], s_meta[g].emx);
   }
 }
 
@@ -284,7 +421,14 @@ cudaError_t launch_bin(const float* x, int64_t n, const h2ok_col_desc& d, int32_
 }
 
 size_t hist_smem_bytes(int node_cnt, int nb1, int copies) {
-  return (size_t)node_cnt * (2 * sizeof(double) + 3 * sizeof(int)) + (size_t)3 * node_cnt * nb1 * copies * sizeof(int);
+  // double2 desc + NodeMeta per node, then the histogram words
+  return (size_t)node_cnt * 32 + (size_t)3 * node_cnt * nb1 * copies * sizeof(int);
+}
+
+cudaError_t launch_pack_rows(const int32_t* nid, const int32_t* wq, const int32_t* wyq, const int32_t* wyyq, int64_t rows,
+                             int64_t padded, int n_nodes, uint2* rec, int32_t* err, cudaStream_t s) {
+  pack_rows_kernel<<<blocks_for(padded, 256), 256, 0, s>>>(nid, wq, wyq, wyyq, rows, padded, n_nodes, rec, err);
+  return cudaGetLastError();
 }
 
 // Chooses the node-group size and the number of privatised copies so that one CTA's histogram fits the
@@ -293,7 +437,7 @@ HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1) {
   HistPlan p;
   const size_t budget = 227 * 1024;
   const size_t slot = (size_t)nb1 * 3 * sizeof(int);
-  int slots = (int)((budget - 64 * 28) / slot);  // (node,copy) slots that fit
+  int slots = (int)((budget - 64 * 32) / slot);  // (node,copy) slots that fit
   int pow2 = 1;
   while (pow2 * 2 <= slots) pow2 *= 2;
   slots = pow2;  // 64 at 256 bins
@@ -321,9 +465,12 @@ HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1) {
 cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_nodes, bool weighted, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(hist_build_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(hist_build_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaSuccess;
+    const int kMax = 227 * 1024;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_build_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_build_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_build_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_build_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMax);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
@@ -335,10 +482,11 @@ cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_
     a.chunk_rows = plan.chunk_rows;
     size_t smem = hist_smem_bytes(a.node_cnt, a.nb1, a.copies);
     unsigned grid = (unsigned)(a.cols * plan.chunks);
-    if (weighted)
-      hist_build_kernel<true><<<grid, kHistThreads, smem, s>>>(a);
-    else
-      hist_build_kernel<false><<<grid, kHistThreads, smem, s>>>(a);
+    const bool one = n_nodes == 1;
+    if (weighted && one) hist_build_kernel<true, true><<<grid, kHistThreads, smem, s>>>(a);
+    else if (weighted) hist_build_kernel<true, false><<<grid, kHistThreads, smem, s>>>(a);
+    else if (one) hist_build_kernel<false, true><<<grid, kHistThreads, smem, s>>>(a);
+    else hist_build_kernel<false, false><<<grid, kHistThreads, smem, s>>>(a);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }

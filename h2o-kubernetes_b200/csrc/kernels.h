@@ -13,10 +13,8 @@ struct HistArgs {
   const float* X;
   int64_t ld, rows;
   int cols;
-  const int32_t* nid;
-  const int32_t* wq;  // NULL when unweighted
-  const int32_t* wyq;
-  const int32_t* wyyq;
+  const uint2* rec;    // packed row records (pack_rows_kernel): node + wyq + wyyq, 8 B per row
+  const int32_t* wq;   // NULL when unweighted
   const h2ok_col_desc* descs;  // [n_nodes][cols]
   int nb1;                     // max_bins + 1
   int node_base, node_cnt;     // node group handled by this launch
@@ -44,6 +42,8 @@ cudaError_t launch_target_absmax(const float* y, const float* w, int64_t rows, d
 cudaError_t launch_quantize_rows(const float* y, const float* w, int64_t rows, const h2ok_quant& q, int32_t* wq,
                                  int32_t* wyq, int32_t* wyyq, cudaStream_t s);
 cudaError_t launch_bin(const float* x, int64_t n, const h2ok_col_desc& d, int32_t* out, cudaStream_t s);
+cudaError_t launch_pack_rows(const int32_t* nid, const int32_t* wq, const int32_t* wyq, const int32_t* wyyq, int64_t rows,
+                             int64_t padded, int n_nodes, uint2* rec, int32_t* err, cudaStream_t s);
 cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_nodes, bool weighted, cudaStream_t s);
 cudaError_t launch_finalize(const int64_t* acc, const uint32_t* mn, const uint32_t* mx, int64_t n_node_cols, int nb1,
                             const h2ok_quant& q, double* hist, float* min2, float* maxin, cudaStream_t s);

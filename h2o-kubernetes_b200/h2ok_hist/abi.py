@@ -43,7 +43,7 @@ class Params(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("build_ms", C.c_float), ("launches", C.c_int32), ("passes", C.c_int32), ("copies", C.c_int32),
-                ("algo_bytes", C.c_double)]
+                ("range_errors", C.c_int32), ("pad", C.c_int32), ("algo_bytes", C.c_double)]
 
 
 def ptr(a):

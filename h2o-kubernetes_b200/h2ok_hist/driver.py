@@ -146,9 +146,9 @@ class CudaShard:
                       _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
         slots = 1
-        while slots * 2 <= (227 * 1024 - 64 * 28) // ((self.max_bins + 1) * 12):
+        while slots * 2 <= (227 * 1024 - 64 * 32) // ((self.max_bins + 1) * 12):
             slots *= 2  # same rule as plan_hist() in csrc/hist_kernels.cu
-        self.launches += 1 + (n_nodes + slots - 1) // slots  # init_enc + one hist_build per node group
+        self.launches += 2 + (n_nodes + slots - 1) // slots  # init_enc + pack_rows + one hist_build per node group
         return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
 
     def last_hist_ms(self):
@@ -216,7 +216,7 @@ class LevelDriver:
     """SharedTree.buildLayer loop over one shard per rank.  `shard` is a CudaShard (tests substitute a CPU double
     with the same methods to exercise the reduce logic under gloo)."""
 
-    def __init__(self, shard, params, is_int=None, qbits=26):
+    def __init__(self, shard, params, is_int=None, qbits=25):
         self.shard = shard
         self.params = params
         self.is_int = None if is_int is None else np.ascontiguousarray(is_int, np.int32)

@@ -44,7 +44,7 @@ extern "C" {
 #define H2OK_ERR_UNSUPPORTED 4 /* categorical columns, > H2OK_MAX_BINS bins, ... */
 
 #define H2OK_MAX_BINS 1024
-#define H2OK_MAX_LEVEL_NODES 4096
+#define H2OK_MAX_LEVEL_NODES 1023 /* node indices travel in 10 bits of the packed row records */
 /* limits of h2ok_hist_next_level_noalloc_dev: 2*n_nodes*cols and 2*n_nodes may not exceed these */
 #define H2OK_NOALLOC_MAX_SLOT_COLS 16384
 #define H2OK_NOALLOC_MAX_SLOTS 2048
@@ -88,7 +88,7 @@ typedef struct h2ok_split {
 typedef struct h2ok_quant {
   double scale_w, scale_wy, scale_wyy;
   int32_t weighted;
-  int32_t qbits; /* |quantised value| <= 2^qbits */
+  int32_t qbits; /* |quantised value| <= 2^qbits; at most 25 */
 } h2ok_quant;
 
 typedef struct h2ok_params {
@@ -105,6 +105,8 @@ typedef struct h2ok_stats {
   int32_t launches; /* kernels launched by the last build_level */
   int32_t passes;   /* node-group passes over X */
   int32_t copies;   /* privatised sub-histograms per (node,col) */
+  int32_t range_errors; /* != 0: some quantised target was outside the packed range (|wyq| < 2^26, wyyq, wq < 2^27) */
+  int32_t pad;
   double algo_bytes;
 } h2ok_stats;
 
@@ -145,7 +147,9 @@ int32_t h2ok_hist_bin_dev(h2ok_ctx* ctx, const float* d_x, int64_t n, const h2ok
 /* a3/a4 — ScoreBuildHistogram local phase: accumulate every active row into its (node,col) histogram.
  * d_acc: int64 [n_nodes][cols][max_bins+1][3] fixed-point sums, zeroed here when clear != 0.
  * d_min2_enc/d_maxin_enc: uint32 [n_nodes][cols] encoded observed min / max (DHistogram._min2/_maxIn), reset when clear != 0.
- * d_descs: device array [n_nodes][cols]. d_wq may be NULL (unweighted). */
+ * d_descs: device array [n_nodes][cols]. d_wq may be NULL (unweighted).  Targets must satisfy |wyq| < 2^26 and
+ * 0 <= wyyq, wq < 2^27 (true for h2ok_hist_choose_quant's scales); violations are counted in h2ok_stats.range_errors
+ * and the offending rows are left out. */
 int32_t h2ok_hist_build_level_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, int64_t rows, int32_t cols,
                                   const int32_t* d_nid, const int32_t* d_wq, const int32_t* d_wyq,
                                   const int32_t* d_wyyq, int32_t n_nodes, const h2ok_col_desc* d_descs,

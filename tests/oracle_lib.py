@@ -109,7 +109,7 @@ class Oracle:
         return out
 
     # ---- quantisation ----
-    def choose_quant(self, y, w, qbits=26):
+    def choose_quant(self, y, w, qbits=25):
         m = np.zeros(3, np.float64)
         self.lib.h2ok_oracle_target_absmax(abi.ptr(y), abi.ptr(w), y.size, abi.ptr(m))
         q = abi.Quant()

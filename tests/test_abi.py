@@ -81,10 +81,10 @@ def test_host_helpers_need_no_gpu(oracle):
     assert out.tobytes() == want.tobytes()  # product's host arithmetic == oracle's, byte for byte
     m = np.array([1.5, 0.7, 3.0])
     q = abi.Quant()
-    lib.call("h2ok_hist_choose_quant", abi.ptr(m), 1, 26, C.byref(q))
+    lib.call("h2ok_hist_choose_quant", abi.ptr(m), 1, 25, C.byref(q))
     qo = abi.Quant()
-    oracle.lib.h2ok_oracle_choose_quant(abi.ptr(m), 1, 26, C.byref(qo))
-    assert (q.scale_w, q.scale_wy, q.scale_wyy) == (qo.scale_w, qo.scale_wy, qo.scale_wyy) == (2.0**25, 2.0**26, 2.0**24)
+    oracle.lib.h2ok_oracle_choose_quant(abi.ptr(m), 1, 25, C.byref(qo))
+    assert (q.scale_w, q.scale_wy, q.scale_wyy) == (qo.scale_w, qo.scale_wy, qo.scale_wyy) == (2.0**24, 2.0**25, 2.0**23)
     ii[1] = 2
     with pytest.raises(capi.H2okError) as e:
         lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi), 4, C.byref(p), abi.ptr(ii), abi.ptr(out))

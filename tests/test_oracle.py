@@ -212,16 +212,16 @@ def test_accumulation_vs_sklearn(oracle):
 def test_quantisation_contract(oracle):
     rows = 3000
     _, y, w = oracle.synth(abi.SHAPE_HIGGS28, 5, 0, rows, 28, weight_mode=1)
-    q, m = oracle.choose_quant(y, w, 26)
+    q, m = oracle.choose_quant(y, w, 25)
     for s, mx in ((q.scale_w, m[0]), (q.scale_wy, m[1]), (q.scale_wyy, m[2])):
         assert math.frexp(s)[0] == 0.5  # power of two
-        assert 2.0**25 <= mx * s <= 2.0**26
+        assert 2.0**24 <= mx * s <= 2.0**25
     wq, wyq, wyyq = oracle.quantize_rows(y, w, q)
     wy = w.astype(np.float64) * y.astype(np.float64)
     assert np.array_equal(wyq, np.rint(wy * q.scale_wy).astype(np.int32))
     assert np.array_equal(wyyq, np.rint(wy * y.astype(np.float64) * q.scale_wyy).astype(np.int32))
     assert np.array_equal(wq == 0, w == 0)
-    q0, _ = oracle.choose_quant(y, None, 26)
+    q0, _ = oracle.choose_quant(y, None, 25)
     assert q0.scale_w == 1.0 and not q0.weighted
 
 
@@ -232,7 +232,7 @@ def test_quantised_level_matches_fp64_level(oracle, weight_mode):
     nid = (np.arange(rows) % 3).astype(np.int32)
     root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb))
     descs = np.stack([root] * 3)
-    q, m = oracle.choose_quant(y, w, 26)
+    q, m = oracle.choose_quant(y, w, 25)
     wq, wyq, wyyq = oracle.quantize_rows(y, w, q)
     acc, min2q, maxinq = oracle.build_level_q(X, rows, nid, wq, wyq, wyyq, descs, nb)
     hq = oracle.finalize(acc, q, nb)
@@ -255,7 +255,7 @@ def test_shard_then_sum_is_exact_in_fixed_point(oracle):
     nid = (np.arange(rows) % 2).astype(np.int32)
     root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb))
     descs = np.stack([root] * 2)
-    q, _ = oracle.choose_quant(y, None, 26)
+    q, _ = oracle.choose_quant(y, None, 25)
     _, wyq, wyyq = oracle.quantize_rows(y, None, q)
     whole, mn, mx = oracle.build_level_q(X, rows, nid, None, wyq, wyyq, descs, nb)
     parts, mns, mxs = [], [], []

@@ -45,7 +45,7 @@ def _worker(rank, world, init_file, split_rows, weight_mode, out_dir):
     # unsharded reference computed locally by the same oracle
     X, y, w = oracle.synth(abi.SHAPE_WIDE64, 55, 0, rows_total, cols, na_permille=10, weight_mode=weight_mode)
     assert root.tobytes() == oracle.root_descs(X, rows_total, params).tobytes()
-    q, _ = oracle.choose_quant(y, w, 26)
+    q, _ = oracle.choose_quant(y, w, 25)
     assert (q.scale_wy, q.scale_wyy, q.scale_w) == (drv.shard.quant.scale_wy, drv.shard.quant.scale_wyy, drv.shard.quant.scale_w)
     wq, wyq, wyyq = oracle.quantize_rows(y, w, q)
     descs, nid, leaf, gid = root.reshape(1, cols), np.zeros(rows_total, np.int32), np.full(rows_total, -1, np.int32), 0

@@ -78,7 +78,7 @@ def test_no_alloc_next_level_rejects_levels_beyond_its_fixed_scratch(lib):
     try:
         params = abi.Params.make(nbins=64)
         buf = torch.zeros(1 << 20, dtype=torch.uint8, device="cuda")
-        for n_nodes, cols in [(129, 64), (1025, 1), (64, 129)]:  # 2*n*cols > 16384 or 2*n > 2048
+        for n_nodes, cols in [(129, 64), (1023, 9), (64, 129)]:  # 2*n_nodes*cols > 16384
             with pytest.raises(capi.H2okError) as e:
                 lib.call("h2ok_hist_next_level_noalloc_dev", ctx, P(buf), P(buf), P(buf), P(buf), n_nodes, cols,
                          C.byref(params), 0, P(buf), P(buf), P(buf))
