@@ -142,7 +142,11 @@ __device__ __noinline__ void carry_to_global(int64_t* acc, int64_t cell_index, i
   atomicAdd(reinterpret_cast<unsigned long long*>(acc) + cell_index * 3 + ch, (unsigned long long)(long long)delta << 32);
 }
 
-struct NodeMeta {  // shared-memory record per node of the group (16 B, read with one LDS.128)
+// Descriptor tables are replicated 8x: entry (g, k) sits at g*8 + k and lane L reads k = L & 7, so the eight lanes
+// of every LDS.128 phase hit eight different 16-byte bank groups whatever their nodes are (conflict-free).
+constexpr int kRep = 8;
+
+struct NodeMeta {  // shared-memory record per (node, replica) (16 B, read with one LDS.128)
   int nbin;
   int cellofs;        // byte offset of the node's first histogram word
   unsigned emn, emx;  // encoded observed min / max so far; a row touches them only when it beats them
@@ -156,6 +160,7 @@ struct RowCtx {
   NodeMeta* s_meta;
   int cstride;  // bytes between consecutive bins of one node (copies * 12)
   int col;
+  int rep;  // this lane's replica of the descriptor tables
   // ONE_NODE: the single descriptor and the thread's running extremes live in registers
   double mn, step;
   int nbin;
@@ -183,18 +188,19 @@ __device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, ONE_NODE>& c, fl
   } else {
     g = ((lo & 31u) | ((hi & 31u) << 5)) - (unsigned)c.a.node_base;
     if (g >= (unsigned)c.a.node_cnt) return;
-    const int4 m = *reinterpret_cast<const int4*>(&c.s_meta[g]);
+    const int gk = g * kRep + c.rep;
+    const int4 m = *reinterpret_cast<const int4*>(&c.s_meta[gk]);
     nbin = m.x;
     if (nbin <= 0) return;
     cellofs = m.y;
-    const double2 d = c.s_desc[g];
+    const double2 d = c.s_desc[gk];
     b = bin_fast(x, d.x, d.y, nbin);
     const unsigned xb = __float_as_uint(x);
     const unsigned e = xb ^ ((unsigned)((int)xb >> 31) | 0x80000000u);  // == enc_f32_bits(xb)
     if ((e < (unsigned)m.z) | (e > (unsigned)m.w)) {  // a new record (rare), or NaN (whose encoding sorts above +inf)
       if (x == x) {
-        atomicMin(&c.s_meta[g].emn, e);
-        atomicMax(&c.s_meta[g].emx, e);
+        atomicMin(&c.s_meta[gk].emn, e);
+        atomicMax(&c.s_meta[gk].emx, e);
       }
     }
   }
@@ -228,8 +234,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int cnt = a.node_cnt;
   double2* s_desc = reinterpret_cast<double2*>(smem_raw);
-  NodeMeta* s_meta = reinterpret_cast<NodeMeta*>(s_desc + cnt);
-  unsigned* h = reinterpret_cast<unsigned*>(s_meta + cnt);
+  NodeMeta* s_meta = reinterpret_cast<NodeMeta*>(s_desc + cnt * kRep);
+  unsigned* h = reinterpret_cast<unsigned*>(s_meta + cnt * kRep);
   const int copies = a.copies, nb1 = a.nb1;
   const int cells = cnt * nb1;
   const int words = cells * copies * 3;
@@ -238,15 +244,16 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
   const int tid = threadIdx.x;
 
   for (int i = tid; i < words; i += kHistThreads) h[i] = (i % 3 == 1) ? kWyBias : 0u;
-  for (int g = tid; g < cnt; g += kHistThreads) {
+  for (int gk = tid; gk < cnt * kRep; gk += kHistThreads) {
+    const int g = gk / kRep;
     const h2ok_col_desc& d = a.descs[(int64_t)(a.node_base + g) * a.cols + col];
-    s_desc[g] = make_double2(d.min, d.step);
+    s_desc[gk] = make_double2(d.min, d.step);
     NodeMeta m;
     m.nbin = d.nbin;
     m.cellofs = g * nb1 * copies * 12;
     m.emn = kEncPosInf;
     m.emx = kEncNegInf;
-    s_meta[g] = m;
+    s_meta[gk] = m;
   }
   __syncthreads();
 
@@ -264,6 +271,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
   c.s_meta = s_meta;
   c.cstride = copies * 12;
   c.col = col;
+  c.rep = tid & (kRep - 1);
   c.mn = s_desc[0].x;
   c.step = s_desc[0].y;
   c.nbin = s_meta[0].nbin;
@@ -348,10 +356,10 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
     if (s1) atomicAdd(gs + 1, s1);
     if (s2) atomicAdd(gs + 2, s2);
   }
-  for (int g = tid; g < cnt; g += kHistThreads) {
-    const int64_t nc = (int64_t)(a.node_base + g) * a.cols + col;
-    if (s_meta[g].emn != kEncPosInf) atomicMin(&a.min2_enc[nc], s_meta[g].emn);
-    if (s_meta[g].emx != kEncNegInf) atomicMax(&a.maxin_enc[nc], s_meta[g].emx);
+  for (int gk = tid; gk < cnt * kRep; gk += kHistThreads) {
+    const int64_t nc = (int64_t)(a.node_base + gk / kRep) * a.cols + col;
+    if (s_meta[gk].emn != kEncPosInf) atomicMin(&a.min2_enc[nc], s_meta[gk].emn);
+    if (s_meta[gk].emx != kEncNegInf) atomicMax(&a.maxin_enc[nc], s_meta[gk].emx);
   }
 }
 
@@ -421,8 +429,8 @@ cudaError_t launch_bin(const float* x, int64_t n, const h2ok_col_desc& d, int32_
 }
 
 size_t hist_smem_bytes(int node_cnt, int nb1, int copies) {
-  // double2 desc + NodeMeta per node, then the histogram words
-  return (size_t)node_cnt * 32 + (size_t)3 * node_cnt * nb1 * copies * sizeof(int);
+  // 8 replicas of (double2 desc + NodeMeta) per node, then the histogram words
+  return (size_t)node_cnt * 32 * 8 + (size_t)3 * node_cnt * nb1 * copies * sizeof(int);
 }
 
 cudaError_t launch_pack_rows(const int32_t* nid, const int32_t* wq, const int32_t* wyq, const int32_t* wyyq, int64_t rows,
@@ -437,7 +445,7 @@ HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1) {
   HistPlan p;
   const size_t budget = 227 * 1024;
   const size_t slot = (size_t)nb1 * 3 * sizeof(int);
-  int slots = (int)((budget - 64 * 32) / slot);  // (node,copy) slots that fit
+  int slots = (int)((budget - 64 * 32 * 8) / slot);  // (node,copy) slots that fit beside the descriptor tables
   int pow2 = 1;
   while (pow2 * 2 <= slots) pow2 *= 2;
   slots = pow2;  // 64 at 256 bins
