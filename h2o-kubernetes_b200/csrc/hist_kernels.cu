@@ -142,26 +142,44 @@ __device__ __noinline__ void carry_to_global(int64_t* acc, int64_t cell_index, i
   atomicAdd(reinterpret_cast<unsigned long long*>(acc) + cell_index * 3 + ch, (unsigned long long)(long long)delta << 32);
 }
 
-// Descriptor tables are replicated 8x: entry (g, k) sits at g*8 + k and lane L reads k = L & 7, so the eight lanes
-// of every LDS.128 phase hit eight different 16-byte bank groups whatever their nodes are (conflict-free).
-constexpr int kRep = 8;
+// Shared-memory descriptor tables of the multi-node path.  A row's node is data dependent, so each lane reads its
+// node's record; the tables are replicated per lane group — T1 entry (g,k) at g*8+k with k = lane&7 (16-byte records:
+// the 8 lanes of an LDS.128 phase hit 8 different bank groups), T2 entry (g,k) at g*16+k with k = lane&15 (8-byte
+// records, 16 lanes per LDS.64 phase) — so the reads are conflict-free whatever the nodes are.
+constexpr int kRep1 = 8;
+constexpr int kRep2 = 16;
 
-struct NodeMeta {  // shared-memory record per (node, replica) (16 B, read with one LDS.128)
+// T1, fast form.  In this library a descriptor's min is always a value of the fp32 column (the observed minimum of
+// the parent's rows, or the float routing threshold `splat`), so it is stored as the float it is and the record
+// (step, min, nbin) fits one LDS.128.  A caller-made descriptor whose min is not exactly a float makes the CTA fall
+// back to the fp64 form below (block-uniform decision, same results).
+struct DescF32 {
+  double step;
+  float minf;
   int nbin;
-  int cellofs;        // byte offset of the node's first histogram word
-  unsigned emn, emx;  // encoded observed min / max so far; a row touches them only when it beats them
+};
+struct DescF64 {  // fallback form: two LDS.128 per row
+  double step;
+  double min;
+};
+struct Range {  // T2: encoded observed min / max so far; a row touches them only when it beats them
+  unsigned emn, emx;
 };
 
-template <bool WEIGHTED, bool ONE_NODE>
+enum { kOneNode = 0, kTableF64 = 1, kTableF32 = 2 };
+
+template <bool WEIGHTED, int MODE>
 struct RowCtx {
   const HistArgs& a;
   unsigned char* hsub;  // histogram base + this lane's copy offset
-  const double2* s_desc;
-  NodeMeta* s_meta;
-  int cstride;  // bytes between consecutive bins of one node (copies * 12)
+  const DescF32* t1;    // MODE kTableF32: + g*8 + (lane&7)
+  const DescF64* t1d;   // MODE kTableF64
+  const int* nbins;     // MODE kTableF64: per node
+  Range* t2;            // + g*16 + (lane&15)
+  int cstride;          // bytes between consecutive bins of one node (copies * 12)
+  int nstride;          // bytes between consecutive nodes (nb1 * copies * 12)
   int col;
-  int rep;  // this lane's replica of the descriptor tables
-  // ONE_NODE: the single descriptor and the thread's running extremes live in registers
+  // kOneNode: the single descriptor and the thread's running extremes live in registers
   double mn, step;
   int nbin;
   float fmn, fmx;
@@ -175,32 +193,36 @@ __device__ __forceinline__ int bin_fast(float x, double mn, double step, int nbi
   return x != x ? nbin : (int)idx;
 }
 
-template <bool WEIGHTED, bool ONE_NODE>
-__device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, ONE_NODE>& c, float x, unsigned lo, unsigned hi, int wq) {
+template <bool WEIGHTED, int MODE>
+__device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, MODE>& c, float x, unsigned lo, unsigned hi, int wq) {
   unsigned g = 0;
-  int nbin, cellofs = 0, b;
-  if (ONE_NODE) {
+  int b, cellofs = 0;
+  if (MODE == kOneNode) {
     if ((lo | hi) & 31u) return;  // only node 0 exists at this level
-    nbin = c.nbin;
-    b = bin_fast(x, c.mn, c.step, nbin);
+    b = bin_fast(x, c.mn, c.step, c.nbin);
     c.fmn = fminf(c.fmn, x);  // NaN-ignoring, exact: the thread's observed range stays in two registers
     c.fmx = fmaxf(c.fmx, x);
   } else {
     g = ((lo & 31u) | ((hi & 31u) << 5)) - (unsigned)c.a.node_base;
     if (g >= (unsigned)c.a.node_cnt) return;
-    const int gk = g * kRep + c.rep;
-    const int4 m = *reinterpret_cast<const int4*>(&c.s_meta[gk]);
-    nbin = m.x;
-    if (nbin <= 0) return;
-    cellofs = m.y;
-    const double2 d = c.s_desc[gk];
-    b = bin_fast(x, d.x, d.y, nbin);
+    // No branch on "column untracked in this node" (nbin == 0): such nodes carry a harmless 1-bin record, their
+    // shared words are simply never flushed, and the hot loop stays one LDS.128 + one LDS.64 per row.
+    if (MODE == kTableF32) {
+      const int4 q = *reinterpret_cast<const int4*>(c.t1 + g * kRep1);  // {step.lo, step.hi, minf, nbin}
+      b = bin_fast(x, (double)__int_as_float(q.z), __hiloint2double(q.y, q.x), q.w);
+    } else {
+      const double2 d = *reinterpret_cast<const double2*>(c.t1d + g * kRep1);
+      b = bin_fast(x, d.y, d.x, max(c.nbins[g], 1));
+    }
+    cellofs = g * c.nstride;
+    Range* rg = c.t2 + g * kRep2;
+    const uint2 r = *reinterpret_cast<const uint2*>(rg);
     const unsigned xb = __float_as_uint(x);
     const unsigned e = xb ^ ((unsigned)((int)xb >> 31) | 0x80000000u);  // == enc_f32_bits(xb)
-    if ((e < (unsigned)m.z) | (e > (unsigned)m.w)) {  // a new record (rare), or NaN (whose encoding sorts above +inf)
+    if ((e < r.x) | (e > r.y)) {  // a new record (rare), or NaN (whose encoding sorts above +inf)
       if (x == x) {
-        atomicMin(&c.s_meta[gk].emn, e);
-        atomicMax(&c.s_meta[gk].emx, e);
+        atomicMin(&rg->emn, e);
+        atomicMax(&rg->emx, e);
       }
     }
   }
@@ -219,7 +241,7 @@ __device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, ONE_NODE>& c, fl
   const bool e1 = (n1 < o1) != (v1 < 0);  // carry when adding a positive value, borrow when adding a negative one
   const unsigned o2 = atomicAdd(p + 2, v2);
   const bool e2 = o2 + v2 < o2;
-  if (ev | e1 | e2) {
+  if ((ev | e1 | e2) && (MODE == kOneNode || c.nbins[g] > 0)) {
     const int64_t cell = ((int64_t)(c.a.node_base + g) * c.a.cols + c.col) * c.a.nb1 + b;
     if (ev) carry_to_global(c.a.acc, cell, 0, 1);
     if (e1) carry_to_global(c.a.acc, cell, 1, v1 < 0 ? -1 : 1);
@@ -227,15 +249,72 @@ __device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, ONE_NODE>& c, fl
   }
 }
 
+// The row loop: two register tiles in ping-pong, so the next tile's loads are in flight while this tile's atomics
+// issue.  128-bit loads: 4 rows of x, 2 + 2 packed row records (and 4 weights).
+template <bool WEIGHTED, int MODE>
+__device__ __forceinline__ void row_loop(RowCtx<WEIGHTED, MODE>& c, const float* __restrict__ x,
+                                         const uint2* __restrict__ rec, const int32_t* __restrict__ wq, int n, int tid) {
+  constexpr int kStep = kHistThreads * 4;
+  const int nvec = n & ~3;
+  const float* xp = x + tid * 4;
+  const uint2* rp = rec + tid * 4;
+  const int32_t* wp = WEIGHTED ? wq + tid * 4 : nullptr;
+  int left = nvec - tid * 4;  // rows from this thread's position to the end of the vector part
+  float4 xa = make_float4(0, 0, 0, 0), xb = xa;
+  uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0, b0 = a0, b1 = a0;
+  int4 wa = make_int4(0, 0, 0, 0), wb = wa;
+#define H2OK_LOAD_TILE(XV, R0, R1, WV, OFF)                                        \
+  {                                                                                \
+    XV = __ldcs(reinterpret_cast<const float4*>(xp + (OFF))); /* streamed once */  \
+    R0 = __ldg(reinterpret_cast<const uint4*>(rp + (OFF)));                        \
+    R1 = __ldg(reinterpret_cast<const uint4*>(rp + (OFF) + 2));                    \
+    if (WEIGHTED) WV = __ldg(reinterpret_cast<const int4*>(wp + (OFF)));           \
+  }
+#define H2OK_DO_TILE(XV, R0, R1, WV)           \
+  {                                            \
+    accumulate_row(c, XV.x, R0.x, R0.y, WV.x); \
+    accumulate_row(c, XV.y, R0.z, R0.w, WV.y); \
+    accumulate_row(c, XV.z, R1.x, R1.y, WV.z); \
+    accumulate_row(c, XV.w, R1.z, R1.w, WV.w); \
+  }
+  if (left > 0) {
+    H2OK_LOAD_TILE(xa, a0, a1, wa, 0);
+    while (true) {
+      if (left > kStep) H2OK_LOAD_TILE(xb, b0, b1, wb, kStep);
+      H2OK_DO_TILE(xa, a0, a1, wa);
+      left -= kStep;
+      if (left <= 0) break;
+      xp += 2 * kStep;
+      rp += 2 * kStep;
+      if (WEIGHTED) wp += 2 * kStep;
+      if (left > kStep) H2OK_LOAD_TILE(xa, a0, a1, wa, 0);
+      H2OK_DO_TILE(xb, b0, b1, wb);
+      left -= kStep;
+      if (left <= 0) break;
+    }
+  }
+#undef H2OK_LOAD_TILE
+#undef H2OK_DO_TILE
+  if (tid < n - nvec) {  // at most 3 rows at the very end of the shard
+    const int r = nvec + tid;
+    const uint2 q = rec[r];
+    accumulate_row(c, x[r], q.x, q.y, WEIGHTED ? wq[r] : 1);
+  }
+}
+
 constexpr unsigned kWyBias = 0x80000000u;  // wY words start mid-range so that sums hovering around zero never wrap
+
+// shared-memory layout: [T1: cnt*8 x 16 B][T2: cnt*16 x 8 B][nbins: cnt x 4 B, padded to 16][histogram words]
+__host__ __device__ inline size_t hist_head_bytes(int cnt) { return (size_t)cnt * 256 + (((size_t)cnt * 4 + 15) & ~(size_t)15); }
 
 template <bool WEIGHTED, bool ONE_NODE>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int cnt = a.node_cnt;
-  double2* s_desc = reinterpret_cast<double2*>(smem_raw);
-  NodeMeta* s_meta = reinterpret_cast<NodeMeta*>(s_desc + cnt * kRep);
-  unsigned* h = reinterpret_cast<unsigned*>(s_meta + cnt * kRep);
+  DescF64* t1 = reinterpret_cast<DescF64*>(smem_raw);
+  Range* t2 = reinterpret_cast<Range*>(t1 + cnt * kRep1);
+  int* s_nbin = reinterpret_cast<int*>(t2 + cnt * kRep2);
+  unsigned* h = reinterpret_cast<unsigned*>(smem_raw + hist_head_bytes(cnt));
   const int copies = a.copies, nb1 = a.nb1;
   const int cells = cnt * nb1;
   const int words = cells * copies * 3;
@@ -244,95 +323,84 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
   const int tid = threadIdx.x;
 
   for (int i = tid; i < words; i += kHistThreads) h[i] = (i % 3 == 1) ? kWyBias : 0u;
-  for (int gk = tid; gk < cnt * kRep; gk += kHistThreads) {
-    const int g = gk / kRep;
+  // every tracked min exactly a float?  (block-uniform: decides which T1 form this CTA uses)
+  bool min_is_f32 = true;
+  for (int g = tid; g < cnt; g += kHistThreads) {
     const h2ok_col_desc& d = a.descs[(int64_t)(a.node_base + g) * a.cols + col];
-    s_desc[gk] = make_double2(d.min, d.step);
-    NodeMeta m;
-    m.nbin = d.nbin;
-    m.cellofs = g * nb1 * copies * 12;
-    m.emn = kEncPosInf;
-    m.emx = kEncNegInf;
-    s_meta[gk] = m;
+    s_nbin[g] = d.nbin;
+    if (d.nbin > 0 && (double)(float)d.min != d.min) min_is_f32 = false;
+  }
+  const bool f32 = __syncthreads_and(min_is_f32) != 0;
+  for (int gk = tid; gk < cnt * kRep1; gk += kHistThreads) {
+    const h2ok_col_desc& d = a.descs[(int64_t)(a.node_base + gk / kRep1) * a.cols + col];
+    const bool tracked = d.nbin > 0;
+    if (f32) {
+      DescF32 q;
+      q.step = tracked ? d.step : 0.0;
+      q.minf = tracked ? (float)d.min : 0.0f;
+      q.nbin = tracked ? d.nbin : 1;
+      reinterpret_cast<DescF32*>(t1)[gk] = q;
+    } else {
+      DescF64 q;
+      q.step = tracked ? d.step : 0.0;
+      q.min = tracked ? d.min : 0.0;
+      t1[gk] = q;
+    }
+  }
+  for (int gk = tid; gk < cnt * kRep2; gk += kHistThreads) {
+    Range r;
+    r.emn = kEncPosInf;
+    r.emx = kEncNegInf;
+    t2[gk] = r;
   }
   __syncthreads();
 
   const int64_t r0 = (int64_t)chunk * a.chunk_rows;
   const int64_t r1 = min(a.rows, r0 + a.chunk_rows);
   const int n = (int)(r1 - r0);
-  const int nvec = n & ~3;
   const float* __restrict__ x = a.X + (int64_t)col * a.ld + r0;
   const uint2* __restrict__ rec = a.rec + r0;
   const int32_t* __restrict__ wq = WEIGHTED ? a.wq + r0 : nullptr;
+  unsigned char* hsub = reinterpret_cast<unsigned char*>(h) + (tid & (copies - 1)) * 12;
 
-  RowCtx<WEIGHTED, ONE_NODE> c{a};
-  c.hsub = reinterpret_cast<unsigned char*>(h) + (tid & (copies - 1)) * 12;
-  c.s_desc = s_desc;
-  c.s_meta = s_meta;
-  c.cstride = copies * 12;
-  c.col = col;
-  c.rep = tid & (kRep - 1);
-  c.mn = s_desc[0].x;
-  c.step = s_desc[0].y;
-  c.nbin = s_meta[0].nbin;
-  c.fmn = __int_as_float(0x7f800000);
-  c.fmx = __int_as_float(0xff800000);
-
-  if (!ONE_NODE || c.nbin > 0) {
-    // two register tiles in ping-pong: the next tile's loads are in flight while this tile's atomics issue
-    constexpr int kStep = kHistThreads * 4;
-    const float* xp = x + tid * 4;
-    const uint2* rp = rec + tid * 4;
-    const int32_t* wp = WEIGHTED ? wq + tid * 4 : nullptr;
-    int left = nvec - tid * 4;  // rows from this thread's position to the end of the vector part
-    float4 xa = make_float4(0, 0, 0, 0), xb = xa;
-    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0, b0 = a0, b1 = a0;
-    int4 wa = make_int4(0, 0, 0, 0), wb = wa;
-#define H2OK_LOAD_TILE(XV, R0, R1, WV, OFF)                                        \
-  {                                                                                \
-    XV = __ldcs(reinterpret_cast<const float4*>(xp + (OFF))); /* streamed once */  \
-    R0 = __ldg(reinterpret_cast<const uint4*>(rp + (OFF)));                        \
-    R1 = __ldg(reinterpret_cast<const uint4*>(rp + (OFF) + 2));                    \
-    if (WEIGHTED) WV = __ldg(reinterpret_cast<const int4*>(wp + (OFF)));           \
-  }
-#define H2OK_DO_TILE(XV, R0, R1, WV)                 \
-  {                                                  \
-    accumulate_row(c, XV.x, R0.x, R0.y, WV.x);       \
-    accumulate_row(c, XV.y, R0.z, R0.w, WV.y);       \
-    accumulate_row(c, XV.z, R1.x, R1.y, WV.z);       \
-    accumulate_row(c, XV.w, R1.z, R1.w, WV.w);       \
-  }
-    if (left > 0) {
-      H2OK_LOAD_TILE(xa, a0, a1, wa, 0);
-      while (true) {
-        if (left > kStep) H2OK_LOAD_TILE(xb, b0, b1, wb, kStep);
-        H2OK_DO_TILE(xa, a0, a1, wa);
-        left -= kStep;
-        if (left <= 0) break;
-        xp += 2 * kStep;
-        rp += 2 * kStep;
-        if (WEIGHTED) wp += 2 * kStep;
-        if (left > kStep) H2OK_LOAD_TILE(xa, a0, a1, wa, 0);
-        H2OK_DO_TILE(xb, b0, b1, wb);
-        left -= kStep;
-        if (left <= 0) break;
-      }
-    }
-#undef H2OK_LOAD_TILE
-#undef H2OK_DO_TILE
-    if (tid < n - nvec) {  // at most 3 rows at the very end of the shard
-      const int r = nvec + tid;
-      const uint2 q = rec[r];
-      accumulate_row(c, x[r], q.x, q.y, WEIGHTED ? wq[r] : 1);
-    }
-  }
   if (ONE_NODE) {
+    RowCtx<WEIGHTED, kOneNode> c{a};
+    c.hsub = hsub;
+    c.cstride = copies * 12;
+    c.col = col;
+    const h2ok_col_desc& d = a.descs[(int64_t)a.node_base * a.cols + col];
+    c.mn = d.min;
+    c.step = d.step;
+    c.nbin = d.nbin;
+    c.fmn = __int_as_float(0x7f800000);
+    c.fmx = __int_as_float(0xff800000);
+    if (c.nbin > 0) row_loop(c, x, rec, wq, n, tid);
     unsigned emn = __reduce_min_sync(0xffffffffu, enc_f32_bits(__float_as_uint(c.fmn)));
     unsigned emx = __reduce_max_sync(0xffffffffu, enc_f32_bits(__float_as_uint(c.fmx)));
     if ((tid & 31) == 0) {
-      atomicMin(&s_meta[0].emn, emn);
-      atomicMax(&s_meta[0].emx, emx);
+      atomicMin(&t2[0].emn, emn);
+      atomicMax(&t2[0].emx, emx);
     }
+  } else if (f32) {
+    RowCtx<WEIGHTED, kTableF32> c{a};
+    c.hsub = hsub;
+    c.t1 = reinterpret_cast<const DescF32*>(t1) + (tid & (kRep1 - 1));
+    c.nbins = s_nbin;
+    c.t2 = t2 + (tid & (kRep2 - 1));
+    c.cstride = copies * 12;
+    c.nstride = nb1 * copies * 12;
+    c.col = col;
+    row_loop(c, x, rec, wq, n, tid);
+  } else {
+    RowCtx<WEIGHTED, kTableF64> c{a};
+    c.hsub = hsub;
+    c.t1d = t1 + (tid & (kRep1 - 1));
+    c.nbins = s_nbin;
+    c.t2 = t2 + (tid & (kRep2 - 1));
+    c.cstride = copies * 12;
+    c.nstride = nb1 * copies * 12;
+    c.col = col;
+    row_loop(c, x, rec, wq, n, tid);
   }
   __syncthreads();
 
@@ -341,6 +409,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
   const int lane = tid & 31;
   for (int i = tid; i < cells; i += kHistThreads) {
     const int g = i / nb1, b = i - g * nb1;
+    if (s_nbin[g] <= 0) continue;  // untracked (node, column): nothing was meant to be accumulated
     unsigned long long* gs =
         reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(a.node_base + g) * a.cols + col) * nb1 + b) * 3;
     const unsigned* hc = h + (size_t)i * copies * 3;
@@ -356,10 +425,11 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
     if (s1) atomicAdd(gs + 1, s1);
     if (s2) atomicAdd(gs + 2, s2);
   }
-  for (int gk = tid; gk < cnt * kRep; gk += kHistThreads) {
-    const int64_t nc = (int64_t)(a.node_base + gk / kRep) * a.cols + col;
-    if (s_meta[gk].emn != kEncPosInf) atomicMin(&a.min2_enc[nc], s_meta[gk].emn);
-    if (s_meta[gk].emx != kEncNegInf) atomicMax(&a.maxin_enc[nc], s_meta[gk].emx);
+  for (int gk = tid; gk < cnt * kRep2; gk += kHistThreads) {
+    if (s_nbin[gk / kRep2] <= 0) continue;
+    const int64_t nc = (int64_t)(a.node_base + gk / kRep2) * a.cols + col;
+    if (t2[gk].emn != kEncPosInf) atomicMin(&a.min2_enc[nc], t2[gk].emn);
+    if (t2[gk].emx != kEncNegInf) atomicMax(&a.maxin_enc[nc], t2[gk].emx);
   }
 }
 
@@ -429,8 +499,7 @@ cudaError_t launch_bin(const float* x, int64_t n, const h2ok_col_desc& d, int32_
 }
 
 size_t hist_smem_bytes(int node_cnt, int nb1, int copies) {
-  // 8 replicas of (double2 desc + NodeMeta) per node, then the histogram words
-  return (size_t)node_cnt * 32 * 8 + (size_t)3 * node_cnt * nb1 * copies * sizeof(int);
+  return hist_head_bytes(node_cnt) + (size_t)3 * node_cnt * nb1 * copies * sizeof(int);
 }
 
 cudaError_t launch_pack_rows(const int32_t* nid, const int32_t* wq, const int32_t* wyq, const int32_t* wyyq, int64_t rows,
@@ -445,7 +514,7 @@ HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1) {
   HistPlan p;
   const size_t budget = 227 * 1024;
   const size_t slot = (size_t)nb1 * 3 * sizeof(int);
-  int slots = (int)((budget - 64 * 32 * 8) / slot);  // (node,copy) slots that fit beside the descriptor tables
+  int slots = (int)((budget - hist_head_bytes(64)) / slot);  // (node,copy) slots that fit beside the descriptor tables
   int pow2 = 1;
   while (pow2 * 2 <= slots) pow2 *= 2;
   slots = pow2;  // 64 at 256 bins

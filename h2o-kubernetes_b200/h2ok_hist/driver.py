@@ -146,7 +146,7 @@ class CudaShard:
                       _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
         slots = 1
-        while slots * 2 <= (227 * 1024 - 64 * 32 * 8) // ((self.max_bins + 1) * 12):
+        while slots * 2 <= (227 * 1024 - 64 * 260) // ((self.max_bins + 1) * 12):
             slots *= 2  # same rule as plan_hist() in csrc/hist_kernels.cu
         self.launches += 2 + (n_nodes + slots - 1) // slots  # init_enc + pack_rows + one hist_build per node group
         return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
