@@ -175,7 +175,7 @@ def run_gpu(args, wl):
     import torch.distributed as dist
 
     from h2ok_hist import abi, capi
-    from h2ok_hist.driver import CudaShard, LevelDriver
+    from h2ok_hist.driver import CudaShard, EngineShard, LevelDriver
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -196,7 +196,7 @@ def run_gpu(args, wl):
     rows_total, cols, bins, depth = wl["rows"], wl["cols"], wl["bins"], wl["depth"]
     row0 = rows_total * rank // world
     rows = rows_total * (rank + 1) // world - row0
-    shard = CudaShard(local)
+    shard = EngineShard(local) if args.path == "engine" else CudaShard(local)
     shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
     params = abi.Params.make(nbins=bins, max_depth=depth)
     drv = LevelDriver(shard, params)
@@ -274,11 +274,12 @@ def run_gpu(args, wl):
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64 binning, i32/i64 fixed-point sums", "data": "synthetic",
             "config": {"workload": wl["name"], "rows": rows_total, "cols": cols, "bins": bins, "depth": depth,
-                       "rows_per_gpu": rows, "step": "one tree level (levels cycle 0..depth-1 of real trees)",
+                       "rows_per_gpu": rows, "path": args.path, "step": "one tree level (levels cycle 0..depth-1 of real trees)",
                        "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
                        "per_level": level_table},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "hist_build_kernel", "peak_source": peak_src,
+                         "traffic": None, "kernel": "eng_hist_kernel" if args.path == "engine" else "hist_build_kernel",
+                         "peak_source": peak_src,
                          "note": "algorithmic bytes of the timed levels / CUDA-event time of their hist_build launches"},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
@@ -460,6 +461,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the workload's row count (debug only)")
+    ap.add_argument("--path", default="engine", choices=["engine", "stateless"],
+                    help="engine: resident node-grouped tree engine (default); stateless: per-call kernels on rows in place")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     args = ap.parse_args()

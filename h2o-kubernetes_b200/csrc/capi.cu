@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "engine.h"
 #include "kernels.h"
 
 using namespace h2ok;
@@ -80,6 +81,8 @@ struct h2ok_ctx {
   int n_nodes = 0, max_bins = 0, gid_base = 0;
   bool level_built = false, splits_found = false, children_made = false;
   bool timed = false;  // ev0/ev1 bracket the last hist_build launches
+  Engine eng;          // resident tree engine (h2ok_hist_tree_*)
+  bool eng_ready = false;
   h2ok_stats stats{};
 };
 
@@ -153,6 +156,7 @@ int32_t h2ok_hist_destroy(h2ok_ctx* c) {
   if (!c) return H2OK_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  engine_free(c->eng);
   c->tmp_descs.release(); c->tmp_valid.release(); c->rec.release(); c->rec_err.release(); c->X.release(); c->y.release(); c->w.release();
   c->nid.release(); c->leaf.release(); c->wq.release(); c->wyq.release(); c->wyyq.release(); c->absmax.release();
   c->cmin.release(); c->cmax.release(); c->descs.release(); c->child_descs.release(); c->acc.release();
@@ -305,6 +309,85 @@ int32_t h2ok_hist_next_level_dev(h2ok_ctx* c, const h2ok_split* d_splits, const 
   CK(c->tmp_valid.ensure((size_t)2 * n_nodes));
   CK(launch_next_level(d_splits, d_descs, d_min2, d_maxin, n_nodes, cols, *params, c->tmp_descs.p, c->tmp_valid.p,
                        d_child_descs, d_child_ids, d_n_children, c->stream));
+  return H2OK_OK;
+}
+
+// ---------------------------------------------------------------------------------------- resident tree engine
+int32_t h2ok_hist_tree_create(h2ok_ctx* c, int64_t rows, int32_t cols, int32_t weighted, float** d_x_out, int64_t* ld_out) {
+  REQUIRE(c && d_x_out && ld_out, "null pointer");
+  REQUIRE(rows > 0 && cols > 0, "empty shard");
+  CK(cudaSetDevice(c->device));
+  c->eng_ready = false;
+  CK(engine_alloc(c->eng, rows, cols, weighted != 0));
+  CK(engine_reset_layout(c->eng, c->stream));
+  c->eng_ready = true;
+  *d_x_out = c->eng.X[0];
+  *ld_out = c->eng.cap;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_destroy(h2ok_ctx* c) {
+  REQUIRE(c != nullptr, "null context");
+  CK(cudaStreamSynchronize(c->stream));
+  engine_free(c->eng);
+  c->eng_ready = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* c, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq) {
+  REQUIRE(c && d_wyq && d_wyyq, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_begin_dev before tree_create");
+  REQUIRE(!c->eng.weighted || d_wq, "weighted engine needs d_wq");
+  CK(engine_begin_tree(c->eng, d_wq, d_wyq, d_wyyq, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_col_desc* d_descs, int32_t max_bins,
+                                       int32_t clear, int64_t* d_acc, uint32_t* d_min2_enc, uint32_t* d_maxin_enc) {
+  REQUIRE(c && d_descs && d_acc && d_min2_enc && d_maxin_enc, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_build_level_dev before tree_create");
+  int32_t rc = check_level_shape(n_nodes, c->eng.cols, max_bins);
+  if (rc) return rc;
+  if ((size_t)2 * (max_bins + 1) * 32 * 12 > 227 * 1024)
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: two children x 32 copies x (max_bins+1) bins must fit 227 KB (max_bins <= 301)");
+  const int nb1 = max_bins + 1;
+  const int64_t ncell = (int64_t)n_nodes * c->eng.cols;
+  if (clear) {
+    CK(cudaMemsetAsync(d_acc, 0, sizeof(int64_t) * (size_t)(ncell * nb1 * 3), c->stream));
+    CK(launch_init_enc(d_min2_enc, d_maxin_enc, ncell, c->stream));
+  }
+  c->stats.passes = 1;
+  c->stats.copies = 32;
+  c->stats.launches = 2 + (clear ? 1 : 0);  // items + hist (+ init_enc)
+  c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * (8.0 + (c->eng.weighted ? 4.0 : 0.0)) +
+                        (double)ncell * nb1 * 3 * 8.0;
+  CK(cudaEventRecord(c->ev0, c->stream));
+  CK(engine_build_level(c->eng, n_nodes, d_descs, nb1, d_acc, d_min2_enc, d_maxin_enc, c->stream));
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->timed = true;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* c, const h2ok_split* d_splits, const int32_t* d_child_ids,
+                                        int32_t gid_base, int32_t n_nodes, int32_t last_level) {
+  REQUIRE(c && d_splits && d_child_ids, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_apply_splits_dev before tree_create");
+  REQUIRE(n_nodes >= 1 && n_nodes <= H2OK_MAX_LEVEL_NODES, "n_nodes out of range");
+  CK(engine_apply_splits(c->eng, d_splits, d_child_ids, gid_base, n_nodes, last_level != 0, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_nid_dev(h2ok_ctx* c, int32_t* d_nid_out) {
+  REQUIRE(c && d_nid_out, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_nid_dev before tree_create");
+  CK(engine_nid(c->eng, d_nid_out, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_leaf_dev(h2ok_ctx* c, int32_t* d_leaf_out) {
+  REQUIRE(c && d_leaf_out, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_leaf_dev before tree_create");
+  CK(cudaMemcpyAsync(d_leaf_out, c->eng.leaf, sizeof(int32_t) * (size_t)c->eng.rows, cudaMemcpyDeviceToDevice, c->stream));
   return H2OK_OK;
 }
 

@@ -115,8 +115,6 @@ __global__ void bin_kernel(const float* __restrict__ x, int64_t n, h2ok_col_desc
 //   lo = wyq  << 5 | node[4:0]     (wyq  signed,   |wyq|  < 2^26)
 //   hi = wyyq << 5 | node[9:5]     (wyyq unsigned,  wyyq  < 2^27)
 // node 0x3FF marks a row that takes no part in this level (already in a leaf, or zero weight).
-constexpr unsigned kNoNode = 0x3FFu;
-
 __global__ void pack_rows_kernel(const int32_t* __restrict__ nid, const int32_t* __restrict__ wq,
                                  const int32_t* __restrict__ wyq, const int32_t* __restrict__ wyyq, int64_t rows,
                                  int64_t padded, int n_nodes, uint2* __restrict__ rec, int32_t* __restrict__ err) {
@@ -134,12 +132,7 @@ __global__ void pack_rows_kernel(const int32_t* __restrict__ nid, const int32_t*
       node = kNoNode;
     }
   }
-  rec[r] = make_uint2(((unsigned)y1 << 5) | (node & 31u), ((unsigned)y2 << 5) | (node >> 5));
-}
-
-// Cold path: a 32-bit shared word wrapped; the carry / borrow goes to the 64-bit global accumulator.
-__device__ __noinline__ void carry_to_global(int64_t* acc, int64_t cell_index, int ch, int delta) {
-  atomicAdd(reinterpret_cast<unsigned long long*>(acc) + cell_index * 3 + ch, (unsigned long long)(long long)delta << 32);
+  rec[r] = rec_pack(y1, y2, node);
 }
 
 // Shared-memory descriptor tables of the multi-node path.  A row's node is data dependent, so each lane reads its
@@ -184,14 +177,6 @@ struct RowCtx {
   int nbin;
   float fmn, fmx;
 };
-
-// a2 inside the hot loop: same value as bin_of() with fewer instructions — the saturating unsigned conversion sends
-// negative and NaN positions to 0 and huge ones to UINT_MAX, one unsigned min applies the round-off clamp.
-__device__ __forceinline__ int bin_fast(float x, double mn, double step, int nbin) {
-  const double pos = __dmul_rn(__dsub_rn((double)x, mn), step);
-  const unsigned idx = min(__double2uint_rz(pos), (unsigned)(nbin - 1));
-  return x != x ? nbin : (int)idx;
-}
 
 template <bool WEIGHTED, int MODE>
 __device__ __forceinline__ void accumulate_row(RowCtx<WEIGHTED, MODE>& c, float x, unsigned lo, unsigned hi, int wq) {
@@ -301,8 +286,6 @@ __device__ __forceinline__ void row_loop(RowCtx<WEIGHTED, MODE>& c, const float*
     accumulate_row(c, x[r], q.x, q.y, WEIGHTED ? wq[r] : 1);
   }
 }
-
-constexpr unsigned kWyBias = 0x80000000u;  // wY words start mid-range so that sums hovering around zero never wrap
 
 // shared-memory layout: [T1: cnt*8 x 16 B][T2: cnt*16 x 8 B][nbins: cnt x 4 B, padded to 16][histogram words]
 __host__ __device__ inline size_t hist_head_bytes(int cnt) { return (size_t)cnt * 256 + (((size_t)cnt * 4 + 15) & ~(size_t)15); }

@@ -31,6 +31,13 @@ SIGNATURES = {
     "h2ok_hist_next_level_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
     "h2ok_hist_next_level_noalloc_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
     "h2ok_hist_apply_splits_dev": [vp, vp, i64, i64, vp, vp, i32, i32, vp, vp],
+    "h2ok_hist_tree_create": [vp, i64, i32, i32, C.POINTER(vp), C.POINTER(i64)],
+    "h2ok_hist_tree_destroy": [vp],
+    "h2ok_hist_tree_begin_dev": [vp, vp, vp, vp],
+    "h2ok_hist_tree_build_level_dev": [vp, i32, vp, i32, i32, vp, vp, vp],
+    "h2ok_hist_tree_apply_splits_dev": [vp, vp, vp, i32, i32, i32],
+    "h2ok_hist_tree_nid_dev": [vp, vp],
+    "h2ok_hist_tree_leaf_dev": [vp, vp],
     "h2ok_hist_root_descs_from_ranges": [vp, vp, i32, pP, vp, vp],
     "h2ok_hist_choose_quant": [vp, i32, i32, pQ],
     "h2ok_hist_set_data_host": [vp, C.POINTER(vp), i64, i32],

@@ -176,7 +176,7 @@ class CudaShard:
     def no_children(self, n_nodes):
         self.child_ids[: 2 * n_nodes].fill_(-1)
 
-    def apply_splits(self, n_nodes, gid_base):
+    def apply_splits(self, n_nodes, gid_base, last=False):
         self.lib.call("h2ok_hist_apply_splits_dev", self.ctx, _ptr(self.X), self.ld, self.rows, _ptr(self.splits),
                       _ptr(self.child_ids), gid_base, n_nodes, _ptr(self.nid), _ptr(self.leaf))
         self.launches += 1
@@ -192,6 +192,65 @@ class CudaShard:
         s = abi.Stats()
         self.lib.call("h2ok_hist_last_level_stats", self.ctx, C.byref(s))
         return s
+
+
+class _DevMem:
+    """A raw device allocation owned by the library, exposed to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class EngineShard(CudaShard):
+    """One GPU's rows held in the library's resident tree engine (h2ok_hist_tree_*): the shard is kept physically
+    grouped by node, so every histogram CTA sees at most two nodes.  Same interface and bit-identical results as
+    CudaShard; costs a second copy of X in device memory."""
+
+    def _alloc_rows(self, rows, cols, weighted):
+        self.rows, self.cols = rows, cols
+        xp, ld = C.c_void_p(), C.c_int64()
+        self.lib.call("h2ok_hist_tree_create", self.ctx, rows, cols, 1 if weighted else 0, C.byref(xp), C.byref(ld))
+        self.ld = int(ld.value)
+        dev = self.device
+        self.X = torch.as_tensor(_DevMem(xp.value, (cols, self.ld), "<f4"), device=dev)  # valid until the first regroup
+        n = (rows + 63) // 64 * 64
+        self.y = torch.empty(n, dtype=torch.float32, device=dev)
+        self.w = torch.empty(n, dtype=torch.float32, device=dev) if weighted else None
+        self.weighted = weighted
+        self.wq = torch.empty(n, dtype=torch.int32, device=dev) if weighted else None
+        self.wyq = torch.empty(n, dtype=torch.int32, device=dev)
+        self.wyyq = torch.empty(n, dtype=torch.int32, device=dev)
+        self._nid = torch.empty(n, dtype=torch.int32, device=dev)
+        self._leaf = torch.empty(n, dtype=torch.int32, device=dev)
+
+    @property
+    def nid(self):
+        self.lib.call("h2ok_hist_tree_nid_dev", self.ctx, _ptr(self._nid))
+        return self._nid
+
+    @property
+    def leaf(self):
+        self.lib.call("h2ok_hist_tree_leaf_dev", self.ctx, _ptr(self._leaf))
+        return self._leaf
+
+    def quantize(self, quant):
+        super().quantize(quant)
+        self.lib.call("h2ok_hist_tree_begin_dev", self.ctx, _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq))
+        self.launches += 1
+
+    def reset_nodes(self):
+        pass  # tree_begin_dev put every row back at the root
+
+    def build_level(self, n_nodes):
+        self.lib.call("h2ok_hist_tree_build_level_dev", self.ctx, n_nodes, _ptr(self.descs), self.max_bins, 1,
+                      _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
+        self.launches += 3  # init_enc + work items + histogram pass
+        return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
+
+    def apply_splits(self, n_nodes, gid_base, last=False):
+        self.lib.call("h2ok_hist_tree_apply_splits_dev", self.ctx, _ptr(self.splits), _ptr(self.child_ids), gid_base,
+                      n_nodes, 1 if last else 0)
+        self.launches += 1 if last else 4  # route (+ tile scan, segment table, scatter)
 
 
 def _world():
@@ -281,7 +340,7 @@ class LevelDriver:
             nch = sh.next_level(n, p, self.depth)
         if inspect:
             inspect(self, n, nch)
-        sh.apply_splits(n, self.gid_base)
+        sh.apply_splits(n, self.gid_base, last=(nch == 0))
         self.gid_base += n
         self.depth += 1
         done_nodes = n

@@ -199,6 +199,29 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
                                    const int32_t* d_child_ids, int32_t gid_base, int32_t n_nodes, int32_t* d_nid,
                                    int32_t* d_leaf);
 
+/* ---- resident tree engine (device-resident; the fast path at depth) ---------------------------------------------
+ * Same results as build_level_dev / apply_splits_dev, bit for bit, but the shard lives inside the context and is kept
+ * physically grouped by node (what ScoreBuildHistogram2 does with row indices per chunk, done here to the data):
+ * every histogram CTA then sees at most two nodes, keeps their descriptors in registers and 32 private histogram
+ * copies per node, and the regrouping write for the next level is fused into the histogram pass.
+ * Call order: tree_create -> fill the X buffer it returns (column c at x + c*ld, rows in original order) ->
+ * per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce / finalize / find_splits / next_level as
+ * usual], tree_apply_splits_dev.  Costs two copies of X in device memory. */
+int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted, float** d_x_out,
+                              int64_t* ld_out);
+int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
+/* new tree: per-row fixed-point targets in ORIGINAL row order (d_wq NULL when unweighted); all rows back at the root */
+int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* ctx, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq);
+/* a3/a4 for the current level; outputs as h2ok_hist_build_level_dev */
+int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* ctx, int32_t n_nodes, const h2ok_col_desc* d_descs, int32_t max_bins,
+                                       int32_t clear, int64_t* d_acc, uint32_t* d_min2_enc, uint32_t* d_maxin_enc);
+/* a6 for the current level (+ preparation of the layout grouped by the children unless last_level != 0) */
+int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, const int32_t* d_child_ids,
+                                        int32_t gid_base, int32_t n_nodes, int32_t last_level);
+/* row -> node of the current level / leaf codes, in original row order */
+int32_t h2ok_hist_tree_nid_dev(h2ok_ctx* ctx, int32_t* d_nid_out);
+int32_t h2ok_hist_tree_leaf_dev(h2ok_ctx* ctx, int32_t* d_leaf_out);
+
 /* a1 — DHistogram.initialHist from column ranges that the caller has already combined across ranks (plain host
  * arithmetic, no device work): constant / all-NA / infinite-range columns get nbin 0. */
 int32_t h2ok_hist_root_descs_from_ranges(const float* col_min, const float* col_max, int32_t cols,

@@ -73,5 +73,5 @@ class CpuShard:
     def no_children(self, n):
         self.child_ids = np.full(2 * n, -1, np.int32)
 
-    def apply_splits(self, n, gid_base):
+    def apply_splits(self, n, gid_base, last=False):
         self.oracle.apply_splits(self.X, self.rows, self.splits, self.child_ids, gid_base, self.nid, self.leaf)

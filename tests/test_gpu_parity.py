@@ -28,6 +28,21 @@ def shard():
     s.close()
 
 
+@pytest.fixture(scope="module")
+def eshard():
+    from h2ok_hist.driver import EngineShard
+
+    s = EngineShard(0)
+    yield s
+    s.close()
+
+
+@pytest.fixture(params=["stateless", "engine"])
+def tree_shard(request, shard, eshard):
+    """Both histogram paths must give the same bits: the stateless kernels and the node-grouped resident engine."""
+    return shard if request.param == "stateless" else eshard
+
+
 def dev(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
@@ -311,14 +326,16 @@ def run_tree_both(shard, oracle, X, rows, y, w, params, is_int=None):
     return levels, state
 
 
-def test_tree_levels_match_oracle_config2_shape(shard, oracle):
+def test_tree_levels_match_oracle_config2_shape(tree_shard, oracle):
+    shard = tree_shard
     rows, cols = 120000, 28
     X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 20261106, 0, rows, cols)
     levels, st = run_tree_both(shard, oracle, X, rows, y, None, abi.Params.make(nbins=256, max_depth=6))
     assert levels == 6 and (st["leaf"] >= 0).all()
 
 
-def test_tree_levels_match_oracle_weighted_na_int(shard, oracle):
+def test_tree_levels_match_oracle_weighted_na_int(tree_shard, oracle):
+    shard = tree_shard
     rows, cols = 50001, 10
     X, y, w = oracle.synth(abi.SHAPE_WIDE64, 99, 0, rows, cols, na_permille=30, weight_mode=1)
     X[4, :rows] = np.floor(X[4, :rows] * 3)  # integer column, few values → step-1 bins
@@ -328,7 +345,8 @@ def test_tree_levels_match_oracle_weighted_na_int(shard, oracle):
     assert levels >= 4
 
 
-def test_tree_top_level_bins_shrink(shard, oracle):
+def test_tree_top_level_bins_shrink(tree_shard, oracle):
+    shard = tree_shard
     rows, cols = 30000, 8
     X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 4, 0, rows, cols)
     run_tree_both(shard, oracle, X, rows, y, None, abi.Params.make(nbins=20, nbins_top_level=160, max_depth=5))
@@ -424,7 +442,8 @@ def level_invariants(drv, n, nch):
     drv._checked = getattr(drv, "_checked", 0) + 1
 
 
-def test_full_size_config2_invariants(shard):
+def test_full_size_config2_invariants(tree_shard):
+    shard = tree_shard
     from h2ok_hist.driver import LevelDriver
 
     rows, cols = 1_000_000, 28  # BASELINE config 2 at full size
@@ -435,7 +454,8 @@ def test_full_size_config2_invariants(shard):
     assert int((shard.leaf[:rows] < 0).sum()) == 0
 
 
-def test_full_size_config3_slice_invariants_and_idempotence(shard):
+def test_full_size_config3_slice_invariants_and_idempotence(tree_shard):
+    shard = tree_shard
     from h2ok_hist.driver import LevelDriver
 
     free, _ = torch.cuda.mem_get_info()
