@@ -461,8 +461,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the workload's row count (debug only)")
-    ap.add_argument("--path", default="engine", choices=["engine", "stateless"],
-                    help="engine: resident node-grouped tree engine (default); stateless: per-call kernels on rows in place")
+    ap.add_argument("--path", default="stateless", choices=["engine", "stateless"],
+                    help="stateless (default): per-call kernels on rows in place; engine: resident node-grouped tree engine "
+                         "(flat cost per level whatever the depth, twice the device memory)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     args = ap.parse_args()
