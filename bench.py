@@ -44,6 +44,12 @@ def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False):
     return rows * cols * 4.0 + rows * (4.0 + 4.0 + (4.0 if weighted else 0.0)) + n_nodes * cols * (bins + 1) * 3 * 8.0
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per hist_build launch, from the committed `ncu --set full` capture
+# (profiles/r01_hist_build_ncu_full.csv: 26.5-27.6 GB read + 0.01-0.3 GB written per launch at 100M x 64); scaled
+# linearly to the rows/cols of the run.  None for shapes that were not profiled.
+NCU_TRAFFIC_BYTES_PER_CELL = 27.15e9 / (100_000_000 * 64)
+
+
 def measured_hbm_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -278,7 +284,8 @@ def run_gpu(args, wl):
                        "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
                        "per_level": level_table},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "eng_hist_kernel" if args.path == "engine" else "hist_build_kernel",
+                         "traffic": (NCU_TRAFFIC_BYTES_PER_CELL * rows * cols / 1e9 if args.path == "stateless" and args.workload == "c3" else None),
+                         "traffic_unit": "GB per launch (ncu dram read+write, profiles/r01_hist_build_ncu_full.csv)", "kernel": "eng_hist_kernel" if args.path == "engine" else "hist_build_kernel",
                          "peak_source": peak_src,
                          "note": "algorithmic bytes of the timed levels / CUDA-event time of their hist_build launches"},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,

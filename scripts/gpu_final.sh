@@ -1,0 +1,12 @@
+#!/bin/bash
+# GPU-box helper for the end-of-round evidence: full bench line, ncu launch list, ncu --set full capture of the
+# dominant kernel (each ncu run only after the same command exited 0 without ncu).
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/pytest_gpu.txt; cat gpurun_out/pytest_gpu.txt
+timeout 900 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; tail -3 gpurun_out/bench_full.err
+CMD="python bench.py --steps 8 --warmup 8 --no-cpu --no-e2e"
+$CMD > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+  --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+$CMD > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:hist_build -s 9 -c 9 \
+  -o gpurun_out/prof_final $CMD > gpurun_out/ncu_full.log 2>&1
+tail -1 gpurun_out/ncu_full.log | cut -c1-100
