@@ -35,6 +35,9 @@ WORKLOADS = {
                cols=64, bins=256, depth=8, shape=3),
     "c2": dict(name="GBM histogram build 1M rows x 28 cols (HIGGS-shaped), 256 bins, depth 6 (BASELINE config 2)",
                rows=1_000_000, cols=28, bins=256, depth=6, shape=2),
+    # config 4 as K separate class trees (the fused K-class pass is not built): one class tree, 80 GB of X
+    "c4": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, one of the 10 class trees "
+                    "(BASELINE config 4, unfused)", rows=10_000_000, cols=2000, bins=64, depth=6, shape=4),
 }
 CPU_SAMPLE_ROWS = 2_000_000
 

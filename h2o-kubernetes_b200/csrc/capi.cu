@@ -312,6 +312,34 @@ int32_t h2ok_hist_next_level_dev(h2ok_ctx* c, const h2ok_split* d_splits, const 
   return H2OK_OK;
 }
 
+// ---------------------------------------------------------------------------------------- a9: tree-level caller
+int32_t h2ok_hist_gbm_residual_dev(h2ok_ctx* c, int32_t dist, const float* d_label, const float* d_f, const float* d_w,
+                                   int64_t rows, double den_scale, float* d_res, int32_t* d_denq) {
+  REQUIRE(c && d_label && d_f && d_res, "null pointer");
+  REQUIRE(dist == H2OK_DIST_GAUSSIAN || dist == H2OK_DIST_BERNOULLI, "unknown distribution");
+  REQUIRE(rows >= 0 && den_scale > 0, "bad rows / den_scale");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_gbm_residual(dist, d_label, d_f, d_w, rows, den_scale, d_res, d_denq, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_gbm_gamma_pass_dev(h2ok_ctx* c, const int32_t* d_leaf, const int32_t* d_numq, const int32_t* d_denq,
+                                     int64_t rows, int32_t n_codes, int64_t* d_num_acc, int64_t* d_den_acc) {
+  REQUIRE(c && d_leaf && d_numq && d_num_acc && d_den_acc, "null pointer");
+  REQUIRE(rows >= 0 && n_codes > 0, "bad rows / n_codes");
+  CK(launch_gbm_gamma_pass(d_leaf, d_numq, d_denq, rows, n_codes, d_num_acc, d_den_acc, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_gbm_add_gamma_dev(h2ok_ctx* c, const int32_t* d_leaf, int64_t rows, const double* d_gamma,
+                                    int32_t n_codes, double learn_rate, float* d_f) {
+  REQUIRE(c && d_leaf && d_gamma && d_f, "null pointer");
+  REQUIRE(rows >= 0 && n_codes > 0, "bad rows / n_codes");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_gbm_add_gamma(d_leaf, rows, d_gamma, n_codes, learn_rate, d_f, c->stream));
+  return H2OK_OK;
+}
+
 // ---------------------------------------------------------------------------------------- resident tree engine
 int32_t h2ok_hist_tree_create(h2ok_ctx* c, int64_t rows, int32_t cols, int32_t weighted, float** d_x_out, int64_t* ld_out) {
   REQUIRE(c && d_x_out && ld_out, "null pointer");

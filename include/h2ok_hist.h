@@ -55,6 +55,10 @@ extern "C" {
 #define H2OK_NA_LEFT 2
 #define H2OK_NA_RIGHT 3
 
+/* Distributions of the tree-level caller (a9). */
+#define H2OK_DIST_GAUSSIAN 0
+#define H2OK_DIST_BERNOULLI 1
+
 /* Synthetic shapes of SURVEY.md §8(d). */
 #define H2OK_SHAPE_HIGGS28 2 /* config 2: 28 HIGGS-shaped columns */
 #define H2OK_SHAPE_WIDE64 3  /* config 3: the 28-column recipe tiled to any width with affine offsets */
@@ -221,6 +225,20 @@ int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* ctx, const h2ok_split* d_split
 /* row -> node of the current level / leaf codes, in original row order */
 int32_t h2ok_hist_tree_nid_dev(h2ok_ctx* ctx, int32_t* d_nid_out);
 int32_t h2ok_hist_tree_leaf_dev(h2ok_ctx* ctx, int32_t* d_leaf_out);
+
+/* ---- a9: the tree-level caller (GBM.buildNextKTrees) ---------------------------------------------------------
+ * ComputePredAndRes: d_res[r] = label - mu(f) (gaussian mu = f, bernoulli mu = 1/(1+exp(-f))), and, when d_denq is
+ * given, the fixed-point GammaPass denominator rint(w * mu * (1 - mu) * den_scale) (bernoulli) or rint(w * den_scale)
+ * / 1 (gaussian).  d_w may be NULL. */
+int32_t h2ok_hist_gbm_residual_dev(h2ok_ctx* ctx, int32_t dist, const float* d_label, const float* d_f, const float* d_w,
+                                   int64_t rows, double den_scale, float* d_res, int32_t* d_denq);
+/* GammaPass: integer sums of d_numq and d_denq (NULL: row count) per leaf code (d_leaf as written by apply_splits);
+ * d_num_acc / d_den_acc: int64 [n_codes], overwritten.  Combine across ranks with an integer sum. */
+int32_t h2ok_hist_gbm_gamma_pass_dev(h2ok_ctx* ctx, const int32_t* d_leaf, const int32_t* d_numq, const int32_t* d_denq,
+                                     int64_t rows, int32_t n_codes, int64_t* d_num_acc, int64_t* d_den_acc);
+/* AddTreeContributions: f[r] += (float)(learn_rate * d_gamma[d_leaf[r]]). */
+int32_t h2ok_hist_gbm_add_gamma_dev(h2ok_ctx* ctx, const int32_t* d_leaf, int64_t rows, const double* d_gamma,
+                                    int32_t n_codes, double learn_rate, float* d_f);
 
 /* a1 — DHistogram.initialHist from column ranges that the caller has already combined across ranks (plain host
  * arithmetic, no device work): constant / all-NA / infinite-range columns get nbin 0. */

@@ -621,6 +621,53 @@ void h2ok_oracle_apply_splits(const float* X, int64_t ld, int64_t rows, const h2
   }
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * a9 — the tree-level caller.  [H2O-3 GBM.ComputePredAndRes / GammaPass / AddTreeContributions, recalled]
+ * Residual r = y - mu(f); leaf value gamma = sum(w r) / sum(w mu (1 - mu)) (bernoulli) or sum(w r) / sum(w)
+ * (gaussian); f += learn_rate * gamma.  The leaf sums run over the same fixed-point integers the device uses.
+ * ---------------------------------------------------------------------------------------------- */
+void h2ok_oracle_gbm_residual(int32_t dist, const float* label, const float* f, const float* w, int64_t rows,
+                              double den_scale, float* res, int32_t* denq) {
+  for (int64_t r = 0; r < rows; r++) {
+    float fi = f[r];
+    if (dist == H2OK_DIST_BERNOULLI) {
+      float e = expf(-fi); /* libm: agrees with the device's expf to a few ulp, not bit for bit */
+      float den = 1.0f + e;
+      float mu = 1.0f / den;
+      res[r] = label[r] - mu;
+      double wd = w ? (double)w[r] : 1.0;
+      float om = 1.0f - mu;
+      double v = (wd * (double)mu) * (double)om;
+      if (denq) denq[r] = (int32_t)nearbyint(v * den_scale);
+    } else {
+      res[r] = label[r] - fi;
+      if (denq) denq[r] = w ? (int32_t)nearbyint((double)w[r] * den_scale) : 1;
+    }
+  }
+}
+
+void h2ok_oracle_gbm_gamma_pass(const int32_t* leaf, const int32_t* numq, const int32_t* denq, int64_t rows,
+                                int32_t n_codes, int64_t* num_acc, int64_t* den_acc) {
+  memset(num_acc, 0, sizeof(int64_t) * (size_t)n_codes);
+  memset(den_acc, 0, sizeof(int64_t) * (size_t)n_codes);
+  for (int64_t r = 0; r < rows; r++) {
+    int32_t c = leaf[r];
+    if (c < 0 || c >= n_codes) continue;
+    num_acc[c] += numq[r];
+    den_acc[c] += denq ? denq[r] : 1;
+  }
+}
+
+void h2ok_oracle_gbm_add_gamma(const int32_t* leaf, int64_t rows, const double* gamma, int32_t n_codes, double learn_rate,
+                               float* f) {
+  for (int64_t r = 0; r < rows; r++) {
+    int32_t c = leaf[r];
+    if (c < 0 || c >= n_codes) continue;
+    double step = learn_rate * gamma[c];
+    f[r] = f[r] + (float)step;
+  }
+}
+
 int32_t h2ok_oracle_max_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

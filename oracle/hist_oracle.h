@@ -68,6 +68,14 @@ void h2ok_oracle_next_level(const h2ok_split* splits, const h2ok_col_desc* descs
 void h2ok_oracle_apply_splits(const float* X, int64_t ld, int64_t rows, const h2ok_split* splits,
                               const int32_t* child_ids, int32_t gid_base, int32_t n_nodes, int32_t* nid, int32_t* leaf);
 
+/* a9 */
+void h2ok_oracle_gbm_residual(int32_t dist, const float* label, const float* f, const float* w, int64_t rows,
+                              double den_scale, float* res, int32_t* denq);
+void h2ok_oracle_gbm_gamma_pass(const int32_t* leaf, const int32_t* numq, const int32_t* denq, int64_t rows,
+                                int32_t n_codes, int64_t* num_acc, int64_t* den_acc);
+void h2ok_oracle_gbm_add_gamma(const int32_t* leaf, int64_t rows, const double* gamma, int32_t n_codes, double learn_rate,
+                               float* f);
+
 int32_t h2ok_oracle_max_threads(void);
 
 #ifdef __cplusplus

@@ -61,6 +61,12 @@ class Oracle:
         L.h2ok_oracle_next_level.argtypes = [vp, vp, vp, vp, i32, i32, C.POINTER(abi.Params), i32, vp, vp, vp]
         L.h2ok_oracle_apply_splits.restype = None
         L.h2ok_oracle_apply_splits.argtypes = [vp, i64, i64, vp, vp, i32, i32, vp, vp]
+        L.h2ok_oracle_gbm_residual.restype = None
+        L.h2ok_oracle_gbm_residual.argtypes = [i32, vp, vp, vp, i64, f64, vp, vp]
+        L.h2ok_oracle_gbm_gamma_pass.restype = None
+        L.h2ok_oracle_gbm_gamma_pass.argtypes = [vp, vp, vp, i64, i32, vp, vp]
+        L.h2ok_oracle_gbm_add_gamma.restype = None
+        L.h2ok_oracle_gbm_add_gamma.argtypes = [vp, i64, vp, i32, f64, vp]
         L.h2ok_oracle_max_threads.restype = i32
 
     # ---- generator ----
@@ -213,6 +219,79 @@ class Oracle:
             if nch == 0:
                 break
         return levels, nid, leaf
+
+
+def gbm_gamma(num, den, scale_num, scale_den):
+    """Leaf values from the integer GammaPass sums (same expression as h2ok_hist.gbm.leaf_gamma)."""
+    num = num.astype(np.float64) / scale_num
+    den = den.astype(np.float64) / scale_den
+    return np.where(den != 0, num / np.where(den != 0, den, 1.0), 0.0)
+
+
+class OracleGBM:
+    """The a9 loop on the CPU with the fixed-point level walk — the bit-exact checker for h2ok_hist.gbm.GBMTrainer."""
+
+    def __init__(self, oracle, X, rows, label, w, params, dist, learn_rate, qbits=25, is_int=None):
+        self.o, self.X, self.rows, self.label, self.w = oracle, X, rows, label, w
+        self.params, self.dist, self.lr, self.qbits, self.is_int = params, dist, learn_rate, qbits, is_int
+        self.cols = X.shape[0]
+        self.root = oracle.root_descs(X, rows, params, is_int)
+        self.f = np.zeros(rows, np.float32)
+        self.trees = []
+
+    def init_f(self, f0):
+        self.f[:] = np.float32(f0)
+
+    def tree_q(self, res):
+        """One tree on targets `res` with the quantised walk; returns leaf codes, quant, wyq, total nodes."""
+        o, X, rows, p = self.o, self.X, self.rows, self.params
+        q, _ = o.choose_quant(res, self.w, self.qbits)
+        wq, wyq, wyyq = o.quantize_rows(res, self.w, q)
+        descs = self.root.reshape(1, self.cols).copy()
+        nid = np.zeros(rows, np.int32)
+        leaf = np.full(rows, -1, np.int32)
+        gid, nb = 0, max(p.nbins, p.nbins_top_level)
+        levels = []
+        for depth in range(p.max_depth):
+            n = descs.shape[0]
+            acc, min2, maxin = o.build_level_q(X, rows, nid, wq, wyq, wyyq, descs, nb)
+            splits = o.find_splits(o.finalize(acc, q, nb), descs, p.min_rows, p.min_split_improvement)
+            if depth + 1 < p.max_depth:
+                child, ids, nch = o.next_level(splits, descs, min2, maxin, p, depth)
+            else:
+                child, ids, nch = None, np.full(2 * n, -1, np.int32), 0
+            o.apply_splits(X, rows, splits, ids, gid, nid, leaf)
+            levels.append((splits, ids))
+            gid += n
+            descs = child
+            if nch == 0:
+                break
+        return leaf, q, wq, wyq, gid, levels
+
+    def step(self):
+        o, rows = self.o, self.rows
+        den_scale = 2.0**28 if self.dist == abi.DIST_BERNOULLI else None
+        res = np.zeros(rows, np.float32)
+        # gaussian: the denominator is the weight (quantised with the histogram's own scale) or the row count
+        denq = None
+        if self.dist == abi.DIST_BERNOULLI:
+            denq = np.zeros(rows, np.int32)
+            o.lib.h2ok_oracle_gbm_residual(self.dist, abi.ptr(self.label), abi.ptr(self.f), abi.ptr(self.w), rows, den_scale,
+                                           abi.ptr(res), abi.ptr(denq))
+        else:
+            o.lib.h2ok_oracle_gbm_residual(self.dist, abi.ptr(self.label), abi.ptr(self.f), abi.ptr(self.w), rows, 1.0,
+                                           abi.ptr(res), None)
+        leaf, q, wq, wyq, n_tree_nodes, levels = self.tree_q(res)
+        if self.dist == abi.DIST_GAUSSIAN:
+            denq, den_scale = (wq, q.scale_w) if self.w is not None else (None, 1.0)
+        n_codes = 3 * n_tree_nodes
+        num = np.zeros(n_codes, np.int64)
+        den = np.zeros(n_codes, np.int64)
+        o.lib.h2ok_oracle_gbm_gamma_pass(abi.ptr(leaf), abi.ptr(wyq), abi.ptr(denq), rows, n_codes, abi.ptr(num), abi.ptr(den))
+        gamma = gbm_gamma(num, den, q.scale_wy, den_scale)
+        o.lib.h2ok_oracle_gbm_add_gamma(abi.ptr(leaf), rows, abi.ptr(gamma), n_codes, self.lr, abi.ptr(self.f))
+        self.trees.append(dict(levels=levels, gamma=gamma, leaf=leaf))
+        return gamma
 
 
 def load():

@@ -471,3 +471,70 @@ def test_full_size_config3_slice_invariants_and_idempotence(tree_shard):
     assert torch.equal(shard.leaf[:rows], leaf1) and torch.equal(shard.acc, acc1)
     shard.set_data_synth(abi.SHAPE_HIGGS28, 1, 0, 1024, 4)  # release the big buffers
     torch.cuda.empty_cache()
+
+
+# ------------------------------------------------------------------------------------------------ a9: GBM loop
+@pytest.mark.parametrize("path,weight_mode", [("stateless", 0), ("engine", 0), ("engine", 1)])
+def test_gbm_gaussian_trees_bit_exact(shard, eshard, oracle, path, weight_mode):
+    """Four boosting iterations: residual pass, tree, GammaPass, AddTreeContributions — leaf values and f after every
+    tree must equal the oracle's loop bit for bit (gaussian needs no transcendental, sums are integers)."""
+    import oracle_lib
+    from h2ok_hist.driver import LevelDriver
+    from h2ok_hist.gbm import GBMTrainer
+
+    sh = shard if path == "stateless" else eshard
+    rows, cols = 30011, 10
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 321, 0, rows, cols, na_permille=10, weight_mode=weight_mode)
+    label = (y * 3 + 1).astype(np.float32)
+    params = abi.Params.make(nbins=64, max_depth=4, min_rows=5)
+    sh.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(label),
+                        None if w is None else torch.from_numpy(w[:rows].copy()))
+    drv = LevelDriver(sh, params)
+    drv.prepare_data()
+    tr = GBMTrainer(drv, torch.from_numpy(label).cuda(), abi.DIST_GAUSSIAN, learn_rate=0.3)
+    f0 = tr.init_f()
+    ref = oracle_lib.OracleGBM(oracle, X, rows, label, None if w is None else w[:rows].copy(), params, abi.DIST_GAUSSIAN, 0.3)
+    ref.init_f(f0)
+    losses = [tr.loss()]
+    for t in range(4):
+        g = tr.step()
+        gr = ref.step()
+        torch.cuda.synchronize()
+        assert g.tobytes() == gr.tobytes(), f"tree {t}: leaf values differ"
+        assert np.array_equal(tr.f.cpu().numpy(), ref.f), f"tree {t}: f differs"
+        for (s_gpu, ids_gpu), (s_ref, ids_ref) in zip(tr.trees[t]["levels"], ref.trees[t]["levels"]):
+            assert s_gpu.tobytes() == s_ref.tobytes() and np.array_equal(ids_gpu, ids_ref)
+        losses.append(tr.loss())
+    assert all(b < a for a, b in zip(losses, losses[1:]))  # boosting reduces the training MSE every iteration
+
+
+def test_gbm_bernoulli_tracks_oracle(eshard, oracle):
+    """bernoulli needs exp(): device and libm agree to a few ulp only, so the check is the logloss trace (1e-6
+    relative) and that it falls — not bit equality."""
+    import oracle_lib
+    from h2ok_hist.driver import LevelDriver
+    from h2ok_hist.gbm import GBMTrainer
+
+    rows, cols = 40000, 8
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 77, 0, rows, cols)
+    label = (y > 0.2).astype(np.float32)
+    params = abi.Params.make(nbins=64, max_depth=4)
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(label))
+    drv = LevelDriver(eshard, params)
+    drv.prepare_data()
+    tr = GBMTrainer(drv, torch.from_numpy(label).cuda(), abi.DIST_BERNOULLI, learn_rate=0.2)
+    f0 = tr.init_f()
+    ref = oracle_lib.OracleGBM(oracle, X, rows, label, None, params, abi.DIST_BERNOULLI, 0.2)
+    ref.init_f(f0)
+
+    def logloss(f):
+        p = np.clip(1 / (1 + np.exp(-f.astype(np.float64))), 1e-15, 1 - 1e-15)
+        return float(-(label * np.log(p) + (1 - label) * np.log(1 - p)).mean())
+
+    trace = [tr.loss()]
+    for _ in range(5):
+        tr.step()
+        ref.step()
+        trace.append(tr.loss())
+        assert trace[-1] == pytest.approx(logloss(ref.f), rel=1e-6)
+    assert all(b < a for a, b in zip(trace, trace[1:]))

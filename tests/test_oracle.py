@@ -415,3 +415,32 @@ def test_train_tree_invariants(oracle):
                 assert s["n_left"] + s["n_right"] == cnt[g]
                 assert s["se_left"] + s["se_right"] < s["se_before"]
     assert (nid < 0).all() and (leaf >= 0).all()  # after the last level every row sits in a leaf
+
+
+# ---------------------------------------------------------------- a9
+def test_gbm_passes_paper_case(oracle):
+    label = np.array([1.0, 2.0, 4.0, 0.0], np.float32)
+    f = np.array([0.5, 0.5, 1.0, 0.0], np.float32)
+    res = np.zeros(4, np.float32)
+    oracle.lib.h2ok_oracle_gbm_residual(abi.DIST_GAUSSIAN, abi.ptr(label), abi.ptr(f), None, 4, 1.0, abi.ptr(res), None)
+    assert res.tolist() == [0.5, 1.5, 3.0, 0.0]
+    # bernoulli: mu(0) = 0.5 → residual label - 0.5, denominator w*mu*(1-mu) = 0.25 (x 2^28)
+    den = np.zeros(4, np.int32)
+    f0 = np.zeros(4, np.float32)
+    lab = np.array([1, 0, 1, 1], np.float32)
+    oracle.lib.h2ok_oracle_gbm_residual(abi.DIST_BERNOULLI, abi.ptr(lab), abi.ptr(f0), None, 4, 2.0**28, abi.ptr(res), abi.ptr(den))
+    assert res.tolist() == [0.5, -0.5, 0.5, 0.5] and den.tolist() == [2**26] * 4
+    # GammaPass: integer sums per leaf code; rows with a negative code are ignored
+    leaf = np.array([3, 3, 7, -1], np.int32)
+    numq = np.array([10, -4, 5, 99], np.int32)
+    num = np.zeros(9, np.int64)
+    dn = np.zeros(9, np.int64)
+    oracle.lib.h2ok_oracle_gbm_gamma_pass(abi.ptr(leaf), abi.ptr(numq), None, 4, 9, abi.ptr(num), abi.ptr(dn))
+    assert num.tolist() == [0, 0, 0, 6, 0, 0, 0, 5, 0] and dn.tolist() == [0, 0, 0, 2, 0, 0, 0, 1, 0]
+    import oracle_lib
+
+    gamma = oracle_lib.gbm_gamma(num, dn, 2.0, 1.0)
+    assert gamma.tolist() == [0, 0, 0, 1.5, 0, 0, 0, 2.5, 0]
+    ff = np.array([1.0, 1.0, 1.0, 1.0], np.float32)
+    oracle.lib.h2ok_oracle_gbm_add_gamma(abi.ptr(leaf), 4, abi.ptr(gamma), 9, 0.5, abi.ptr(ff))
+    assert ff.tolist() == [1.75, 1.75, 2.25, 1.0]
