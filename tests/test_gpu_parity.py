@@ -538,3 +538,42 @@ def test_gbm_bernoulli_tracks_oracle(eshard, oracle):
         trace.append(tr.loss())
         assert trace[-1] == pytest.approx(logloss(ref.f), rel=1e-6)
     assert all(b < a for a, b in zip(trace, trace[1:]))
+
+
+# ------------------------------------------------------------------------------------------------ engine edge cases
+@pytest.mark.parametrize("rows,cols,depth,min_rows", [(1, 3, 3, 1), (5, 3, 3, 1), (130, 4, 5, 1), (4097, 5, 6, 2),
+                                                      (60000, 6, 10, 1)])
+def test_engine_ragged_sizes_and_deep_trees(eshard, oracle, rows, cols, depth, min_rows):
+    """Tiny shards, sizes that are not multiples of the 128-position blocks / 4096-position tiles, and a depth-10
+    tree with min_rows 1 (hundreds of small segments, many rows retiring early) through the node-grouped engine."""
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 1000 + rows, 0, rows, cols, na_permille=20)
+    params = abi.Params.make(nbins=32, max_depth=depth, min_rows=min_rows, min_split_improvement=0.0)
+    levels, st = run_tree_both(eshard, oracle, X, rows, y, None, params)
+    assert levels >= 1
+    if rows == 60000:
+        assert levels == 10 and st["gid"] > 300  # hundreds of nodes over the ten levels
+
+
+def test_engine_second_tree_reuses_the_regrouped_layout(eshard, oracle):
+    """A new tree starts from whatever order the previous one left the rows in; results must not depend on it."""
+    from h2ok_hist.driver import LevelDriver
+
+    rows, cols = 50000, 6
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 9, 0, rows, cols, weight_mode=1)
+    params = abi.Params.make(nbins=64, max_depth=5)
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()),
+                            torch.from_numpy(w[:rows].copy()))
+    drv = LevelDriver(eshard, params)
+    drv.prepare_data()
+    drv.train_tree()
+    leaf1 = eshard.leaf[:rows].clone()
+    acc1 = eshard.acc.clone()
+    y2 = (-y[:rows] * 0.5 + 0.25).astype(np.float32)
+    eshard.set_targets(torch.from_numpy(y2), torch.from_numpy(w[:rows].copy()))
+    drv.train_tree()  # a different tree in between shuffles the layout further
+    eshard.set_targets(torch.from_numpy(y[:rows].copy()), torch.from_numpy(w[:rows].copy()))
+    drv.train_tree()
+    assert torch.equal(eshard.leaf[:rows], leaf1) and torch.equal(eshard.acc, acc1)
+    levels_ref, nid_ref, leaf_ref = oracle.train_tree(X, rows, y, w, params)
+    # the fp64 oracle agrees on the tree's shape: same leaves for every row
+    assert np.array_equal(leaf1.cpu().numpy(), leaf_ref)
