@@ -523,7 +523,10 @@ HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1) {
 }
 
 cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_nodes, bool weighted, cudaStream_t s) {
-  static bool attr_set = false;
+  static bool attr_done[64] = {};  // the opt-in to > 48 KB of dynamic shared memory is per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  bool& attr_set = attr_done[dev & 63];
   if (!attr_set) {
     cudaError_t e = cudaSuccess;
     const int kMax = 227 * 1024;

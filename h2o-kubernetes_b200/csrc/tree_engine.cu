@@ -568,7 +568,10 @@ cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* 
 
 template <bool W, bool TWO, bool WR>
 static cudaError_t launch_eng_hist(const EngHistArgs& a, unsigned grid, size_t smem, cudaStream_t s) {
-  static bool attr = false;
+  static bool attr_done[64] = {};  // per device, per instantiation
+  int dev = 0;
+  cudaGetDevice(&dev);
+  bool& attr = attr_done[dev & 63];
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<W, TWO, WR>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return e;

@@ -577,3 +577,49 @@ def test_engine_second_tree_reuses_the_regrouped_layout(eshard, oracle):
     levels_ref, nid_ref, leaf_ref = oracle.train_tree(X, rows, y, w, params)
     # the fp64 oracle agrees on the tree's shape: same leaves for every row
     assert np.array_equal(leaf1.cpu().numpy(), leaf_ref)
+
+
+# ------------------------------------------------------------------------------------------------ randomised parity
+def test_build_level_hypothesis(shard, oracle):
+    """Property test: for arbitrary shapes, descriptors (float and non-float mins, tiny and huge ranges, untracked
+    columns), specials (NaN, +-Inf, denormals, +-0) and weights, the kernel's integer histogram and observed ranges
+    equal the oracle's fixed-point walk bit for bit."""
+    hyp = pytest.importorskip("hypothesis")
+    from hypothesis import HealthCheck, given, settings
+    from hypothesis import strategies as st
+
+    specials = np.array([np.nan, np.inf, -np.inf, 0.0, -0.0, 1e-45, -1e-45, 3.4e38, -3.4e38, 1.0, -1.0], np.float32)
+
+    @settings(max_examples=40, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+    @given(st.integers(1, 5000), st.integers(1, 5), st.integers(1, 70), st.sampled_from([2, 7, 64, 256, 300]),
+           st.booleans(), st.booleans(), st.integers(0, 2**31 - 1))
+    def run(rows, cols, n_nodes, nb, weighted, float_min, seed):
+        rng = np.random.default_rng(seed)
+        ld = (rows + 3) // 4 * 4
+        X = np.zeros((cols, ld), np.float32)
+        scale = float(rng.choice([1e-3, 1.0, 50.0, 1e6]))
+        X[:, :rows] = (rng.standard_normal((cols, rows)) * scale).astype(np.float32)
+        k = max(1, rows // 20)
+        X[rng.integers(0, cols, k), rng.integers(0, rows, k)] = rng.choice(specials, k)
+        y = rng.standard_normal(rows).astype(np.float32)
+        w = None
+        if weighted:
+            w = rng.uniform(0.0, 3.0, rows).astype(np.float32)
+            w[rng.integers(0, rows, max(1, rows // 10))] = 0.0
+        nid = np.full(ld, -1, np.int32)
+        nid[:rows] = rng.integers(-1, n_nodes, rows)
+        descs = np.zeros((n_nodes, cols), abi.COL_DESC)
+        for g in range(n_nodes):
+            for c in range(cols):
+                lo = float(rng.uniform(-2, 1)) * scale
+                if float_min:
+                    lo = float(np.float32(lo))
+                hi = lo + float(rng.uniform(0.01, 4)) * scale
+                d, ok = oracle.make_desc(lo, hi, 0, int(rng.integers(1, nb + 1)))
+                descs[g, c] = d
+                if rng.random() < 0.1:
+                    descs[g, c]["nbin"] = 0
+        check_level(shard, oracle, X, rows, y, w, nid, descs, nb, qbits=25)
+
+    run()
+    del hyp
