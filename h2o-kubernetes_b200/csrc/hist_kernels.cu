@@ -1,17 +1,20 @@
 // hist_kernels.cu — sm_100a kernels for SURVEY.md §8 rows a2/a3/a4 (+ generator, ranges, quantisation).
 //
-// build_level (the hot kernel) — HBM-bound scatter-reduce, no tensor cores:
-//   * one CTA = one column x one contiguous chunk of rows; 128-bit coalesced loads of x / nid / targets;
-//   * the CTA's histogram lives in shared memory as int32 fixed-point words [channel][node][bin][copy]; the only
+// build_level (the hot kernel, stateless form: rows in their original order) — a scatter-reduce, no tensor cores:
+//   * one CTA = one column x one contiguous chunk of rows; 128-bit coalesced loads of x and of the 8-byte row
+//     records (node + fixed-point targets, packed once per level), two register tiles in ping-pong;
+//   * the CTA's histogram lives in shared memory as int32 fixed-point words [node][bin][copy][channel]; the only
 //     native shared-memory atomic on sm_100a is the 32-bit integer add (fp32/u64/f64 compile to CAS loops), so the
 //     sums are integers: exact, order-independent, and the cross-GPU reduce is an integer sum;
 //   * `copies` privatised sub-histograms per (node,bin), selected by lane, spread a warp's updates over banks:
-//     with few nodes every lane owns a bank (conflict-free even for 3-valued columns), with many nodes the node
-//     id itself spreads the addresses;
+//     up to 32 copies per node (bank == lane: conflict-free even for 3-valued columns); copies = 64 / nodes;
 //   * 32-bit words cannot hold a chunk's sum, so each add reads back the old word and the (rare) carry / borrow
 //     out of bit 31 goes straight to the 64-bit global accumulator; at the end the low words are flushed once;
+//   * one node: descriptor and observed range in registers; several nodes: two replicated, conflict-free
+//     shared-memory tables read with one LDS.128 + one LDS.64 per row;
 //   * grid = cols x chunks is a multiple of 148 SMs whenever cols % 4 == 0, column index fastest so the CTAs that
-//     share a row chunk run together and the row-indexed arrays are served from L2 after the first column.
+//     share a row chunk run together and the row records are served from L2 after the first column.
+// Measured bound (ncu): the SM's LSU / shared-memory data pipe (92-99 % busy beyond the root), see DESIGN.md §3.1.
 #include "common.cuh"
 #include "kernels.h"
 
