@@ -303,7 +303,7 @@ class LevelDriver:
         self.lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi), self.shard.cols,
                       C.byref(self.params), abi.ptr(self.is_int), abi.ptr(out))
         self.root = out
-        max_nodes = min(2 ** max(self.params.max_depth - 1, 0), 4096)
+        max_nodes = min(2 ** max(self.params.max_depth - 1, 0), 1023)  # H2OK_MAX_LEVEL_NODES
         self.shard.ensure_level_buffers(max_nodes, self.max_bins)
         return out
 

@@ -554,6 +554,26 @@ def test_engine_ragged_sizes_and_deep_trees(eshard, oracle, rows, cols, depth, m
         assert levels == 10 and st["gid"] > 300  # hundreds of nodes over the ten levels
 
 
+def test_engine_rejects_what_it_cannot_hold(lib):
+    h = C.c_void_p()
+    lib.call("h2ok_hist_create", 0, C.byref(h))
+    try:
+        buf = torch.zeros(1 << 16, dtype=torch.uint8, device="cuda")
+        with pytest.raises(capi.H2okError) as e:  # no engine yet
+            lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 256, 1, P(buf), P(buf), P(buf))
+        assert e.value.code == abi.ERR_STATE
+        xp, ld = C.c_void_p(), C.c_int64()
+        lib.call("h2ok_hist_tree_create", h, 1000, 2, 0, C.byref(xp), C.byref(ld))
+        assert xp.value and ld.value >= 1000
+        with pytest.raises(capi.H2okError) as e:  # two children x 32 copies x 513 bins do not fit 227 KB
+            lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 512, 1, P(buf), P(buf), P(buf))
+        assert e.value.code == abi.ERR_UNSUPPORTED and "max_bins" in str(e.value)
+        with pytest.raises(capi.H2okError):
+            lib.call("h2ok_hist_tree_create", h, 0, 2, 0, C.byref(xp), C.byref(ld))
+    finally:
+        lib.call("h2ok_hist_destroy", h)
+
+
 def test_engine_second_tree_reuses_the_regrouped_layout(eshard, oracle):
     """A new tree starts from whatever order the previous one left the rows in; results must not depend on it."""
     from h2ok_hist.driver import LevelDriver
