@@ -340,17 +340,25 @@ int32_t h2ok_hist_gbm_add_gamma_dev(h2ok_ctx* c, const int32_t* d_leaf, int64_t 
   return H2OK_OK;
 }
 
+int32_t h2ok_hist_synth_fill_cols_dev(h2ok_ctx* c, int32_t shape, uint64_t seed, int64_t row0, int64_t rows, int32_t col0,
+                                      int32_t ncols, int64_t ld, int32_t na_permille, float* d_X) {
+  REQUIRE(c && d_X, "null pointer");
+  REQUIRE(rows >= 0 && col0 >= 0 && ncols > 0 && ld >= rows, "bad shape");
+  REQUIRE(shape == H2OK_SHAPE_HIGGS28 || shape == H2OK_SHAPE_WIDE64 || shape == H2OK_SHAPE_SPARSE, "unknown shape id");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_synth_cols(shape, seed, row0, rows, col0, ncols, ld, na_permille, d_X, c->stream));
+  return H2OK_OK;
+}
+
 // ---------------------------------------------------------------------------------------- resident tree engine
-int32_t h2ok_hist_tree_create(h2ok_ctx* c, int64_t rows, int32_t cols, int32_t weighted, float** d_x_out, int64_t* ld_out) {
-  REQUIRE(c && d_x_out && ld_out, "null pointer");
+int32_t h2ok_hist_tree_create(h2ok_ctx* c, int64_t rows, int32_t cols, int32_t weighted) {
+  REQUIRE(c != nullptr, "null context");
   REQUIRE(rows > 0 && cols > 0, "empty shard");
   CK(cudaSetDevice(c->device));
   c->eng_ready = false;
+  CK(cudaStreamSynchronize(c->stream));
   CK(engine_alloc(c->eng, rows, cols, weighted != 0));
-  CK(engine_reset_layout(c->eng, c->stream));
   c->eng_ready = true;
-  *d_x_out = c->eng.X[0];
-  *ld_out = c->eng.cap;
   return H2OK_OK;
 }
 
@@ -359,6 +367,14 @@ int32_t h2ok_hist_tree_destroy(h2ok_ctx* c) {
   CK(cudaStreamSynchronize(c->stream));
   engine_free(c->eng);
   c->eng_ready = false;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* c, int32_t col0, int32_t ncols, const float* d_X, int64_t ld) {
+  REQUIRE(c && d_X, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_load_cols_dev before tree_create");
+  REQUIRE(col0 >= 0 && ncols > 0 && col0 + ncols <= c->eng.cols && ld >= c->eng.rows, "column block outside the shard");
+  CK(engine_load_cols(c->eng, col0, ncols, d_X, ld, c->stream));
   return H2OK_OK;
 }
 
@@ -376,8 +392,8 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_build_level_dev before tree_create");
   int32_t rc = check_level_shape(n_nodes, c->eng.cols, max_bins);
   if (rc) return rc;
-  if ((size_t)2 * (max_bins + 1) * 32 * 12 > 227 * 1024)
-    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: two children x 32 copies x (max_bins+1) bins must fit 227 KB (max_bins <= 301)");
+  if (max_bins + 1 > engine_max_nb1(c->eng.cols))
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: 32 columns x (max_bins+1) bins must fit 226 KB (max_bins <= 601)");
   const int nb1 = max_bins + 1;
   const int64_t ncell = (int64_t)n_nodes * c->eng.cols;
   if (clear) {
@@ -385,10 +401,9 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
     CK(launch_init_enc(d_min2_enc, d_maxin_enc, ncell, c->stream));
   }
   c->stats.passes = 1;
-  c->stats.copies = 32;
-  c->stats.launches = 2 + (clear ? 1 : 0);  // items + hist (+ init_enc)
-  c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * (8.0 + (c->eng.weighted ? 4.0 : 0.0)) +
-                        (double)ncell * nb1 * 3 * 8.0;
+  c->stats.copies = 1;
+  c->stats.launches = 1 + (clear ? 1 : 0);  // hist (+ init_enc)
+  c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * 16.0 + (double)ncell * nb1 * 3 * 8.0;
   CK(cudaEventRecord(c->ev0, c->stream));
   CK(engine_build_level(c->eng, n_nodes, d_descs, nb1, d_acc, d_min2_enc, d_maxin_enc, c->stream));
   CK(cudaEventRecord(c->ev1, c->stream));
@@ -398,10 +413,11 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
 
 int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* c, const h2ok_split* d_splits, const int32_t* d_child_ids,
                                         int32_t gid_base, int32_t n_nodes, int32_t last_level) {
+  (void)last_level;
   REQUIRE(c && d_splits && d_child_ids, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_apply_splits_dev before tree_create");
   REQUIRE(n_nodes >= 1 && n_nodes <= H2OK_MAX_LEVEL_NODES, "n_nodes out of range");
-  CK(engine_apply_splits(c->eng, d_splits, d_child_ids, gid_base, n_nodes, last_level != 0, c->stream));
+  CK(engine_apply_splits(c->eng, d_splits, d_child_ids, gid_base, n_nodes, c->stream));
   return H2OK_OK;
 }
 

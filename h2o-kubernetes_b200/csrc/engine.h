@@ -1,15 +1,21 @@
-// engine.h — resident, node-grouped tree engine (SURVEY.md §8 a3/a4/a6 at depth).
+// engine.h — resident row-wise tree engine (SURVEY.md §8 a3/a4/a6 at depth).
 //
-// The stateless histogram kernel (hist_kernels.cu) takes rows in their original order, so at depth d a CTA sees
-// rows of all 2^d nodes: the per-row descriptor comes from shared memory and 64 nodes x 257 bins leave room for a
-// single histogram copy, i.e. 3-4-way bank conflicts — its floor is ~23 shared-memory wavefronts per 32 cells.
-// The engine instead keeps the shard physically grouped by node.  H2O does the same per chunk (ScoreBuildHistogram2
-// buckets row indices by nid before calling updateHisto); here the data itself is regrouped, because a 4-byte gather
-// would waste 7/8 of every 32-byte sector.  The regrouping write is fused into the histogram pass: level d's pass
-// reads the layout grouped by level d-1 (each segment holds the two children of one parent), accumulates with both
-// descriptors in registers and 32 private histogram copies per child, and stores every x at its position in the
-// layout grouped by level d, which the next pass reads.  Integer accumulation makes the result independent of the
-// row order, so the engine's histograms are bit-identical to the stateless path's.
+// The stateless histogram kernel (hist_kernels.cu) walks one column of the rows in their original order, so at depth
+// d a CTA sees rows of all 2^d nodes: the per-row descriptor comes from shared memory and 64 nodes x 257 bins leave
+// room for a single histogram copy — its floor is ~23 shared-memory wavefronts per 32 cells.
+//
+// The engine turns the problem by 90 degrees.  X is kept ROW-major (one row = cols consecutive floats, 256 B at 64
+// columns) and never moves.  What is regrouped per level is a 16-byte row record {row, wyq, wyyq, wq}: the records
+// are kept grouped by node (H2O does the same per chunk: ScoreBuildHistogram2 buckets row indices by nid before
+// calling updateHisto).  A histogram CTA owns a contiguous run of records, i.e. the rows of ONE node at a time:
+//   * a warp takes one row at a time; lane L owns columns {2L, 2L+1} of a 64-column block, so the row is one
+//     coalesced 256-byte load whose every sector is used — the gather costs no extra HBM traffic;
+//   * the node's descriptors for the lane's columns sit in registers: no per-row table lookups at any depth;
+//   * the shared histogram is laid out [column slot][bin][channel][lane]: a lane only ever touches bank == lane,
+//     so every shared atomic is conflict-free at every depth and for every data distribution, with ONE copy;
+//   * the row record is the same for all lanes: one broadcast load per row, amortised over 64 cells.
+// Integer accumulation makes the result independent of the row order, so the engine's histograms are bit-identical
+// to the stateless path's.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -18,53 +24,42 @@
 
 namespace h2ok {
 
-constexpr int kEngTile = 4096;      // positions per partition tile
-constexpr int kEngSegAlign = 128;   // every segment starts at a multiple of 128 positions (one warp's block)
-constexpr int kEngMaxGroups = 2050; // children of one level + the dead group
+constexpr int kEngTile = 2048;      // records per routing / scatter tile
+constexpr int kEngMaxNodes = 1024;  // >= H2OK_MAX_LEVEL_NODES + 1
 
 struct Engine {
   int64_t rows = 0;  // rows of the shard
-  int64_t cap = 0;   // positions per layout buffer (rows + alignment padding)
+  int64_t ldt = 0;   // floats per row of XT (cols rounded up to a multiple of 8: rows start on 32-byte sectors)
   int cols = 0;
   bool weighted = false;
-  // layout buffers, double buffered: positions hold rows grouped by node; padding positions have rowid -1
-  float* X[2] = {nullptr, nullptr};       // [cols][cap]
-  uint2* rec[2] = {nullptr, nullptr};     // packed (node, wyq, wyyq) per position
-  int32_t* wq[2] = {nullptr, nullptr};    // weights per position (weighted only)
-  int32_t* rowid[2] = {nullptr, nullptr}; // original row of each position
-  int32_t* pnode[2] = {nullptr, nullptr}; // node of each position at the current level (-1: in a leaf / padding)
-  int32_t* seg[2] = {nullptr, nullptr};   // per layout: [0..kEngMaxGroups) lo, [kEngMaxGroups..2*) hi, then used extent
-  int32_t* seg_child = nullptr;           // [2*kEngMaxGroups] nodes (at the level being built) held by each segment
-  int cur = 0;                            // which buffer holds the current layout
-  int n_seg = 1;                          // segments of the current layout (the dead zone comes after them)
-  bool dest_valid = false;                // apply() has prepared the next layout; the next pass must write it
-  // per-position scratch
-  int32_t* newnode = nullptr;
-  int32_t* dest = nullptr;
-  int32_t* tile_counts = nullptr;  // [tiles][groups]
-  int64_t tile_cap = 0;
-  // per-row (original order) arrays
-  int32_t* leaf = nullptr;
-  // work items of the histogram pass
-  int4* items = nullptr;  // {segment, first position, end position, 0}
-  int32_t* n_items = nullptr;
-  int max_items = 0;
-  int64_t chunk_rows = 0;
+  float* XT = nullptr;                  // [rows][ldt] row-major copy of the shard
+  int4* grec[2] = {nullptr, nullptr};   // row records grouped by node: {row, wyq, wyyq, wq}; double buffered
+  int32_t* seg[2] = {nullptr, nullptr}; // [n_nodes + 1] first record of every node of the level; seg[n_nodes] = live rows
+  int cur = 0;
+  int n_nodes = 0;                      // nodes of the current level (0: no tree in progress)
+  uint8_t* codes = nullptr;             // [rows] way of every record: 0 / 1 = live child, 2 = into a leaf
+  int32_t* tile_base = nullptr;         // [kEngMaxNodes + 1] first tile of every node
+  int32_t* tile_cnt = nullptr;          // [max_tiles + 1][2] records of each tile going left / right (then scanned)
+  int32_t* slot_start = nullptr;        // [2 * kEngMaxNodes] first record of child slot 2 * node + way in the next order
+  int32_t* leaf = nullptr;              // [rows] leaf code of every row (original order), -1 while still in the tree
+  int64_t max_tiles = 0;
 };
 
 cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted);
 void engine_free(Engine& e);
-// the identity layout: position p = row p
-cudaError_t engine_reset_layout(Engine& e, cudaStream_t s);
-// new tree: gather the quantised targets into layout order, every row back at the root
+// copy columns [col0, col0 + ncols) of a column-major block (leading dimension ld) into the row-major copy
+cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s);
+// new tree: every row at the root, records in row order
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
                               cudaStream_t s);
-// one level's histogram pass (+ the fused regrouping write when apply() prepared one)
+// one level's histogram pass
 cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int64_t* acc,
                                uint32_t* min2_enc, uint32_t* maxin_enc, cudaStream_t s);
-// route rows with the level's splits, retire rows into leaves, prepare the layout grouped by the children
+// the largest max_bins + 1 one histogram CTA can hold for this shard's column count
+int engine_max_nb1(int cols);
+// route rows with the level's splits, retire rows into leaves, regroup the records by child
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,
-                                bool last_level, cudaStream_t s);
+                                cudaStream_t s);
 // row -> node map of the current level in original row order (tests / inspection)
 cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s);
 

@@ -21,11 +21,11 @@
 namespace h2ok {
 
 // ------------------------------------------------------------------------------------------------ generator
-__global__ void synth_x_kernel(int shape, uint64_t seed, int64_t row0, int64_t rows, int cols, int64_t ld,
+__global__ void synth_x_kernel(int shape, uint64_t seed, int64_t row0, int64_t rows, int col0, int64_t ld,
                                int na_permille, float* __restrict__ X) {
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int c = blockIdx.y;
-  if (r < ld) X[(int64_t)c * ld + r] = r < rows ? gen_x(shape, seed, row0 + r, c, na_permille) : 0.0f;
+  if (r < ld) X[(int64_t)c * ld + r] = r < rows ? gen_x(shape, seed, row0 + r, col0 + c, na_permille) : 0.0f;
 }
 
 __global__ void synth_yw_kernel(uint64_t seed, int64_t row0, int64_t rows, int cols, int weight_mode,
@@ -442,9 +442,16 @@ cudaError_t launch_synth(int shape, uint64_t seed, int64_t row0, int64_t rows, i
                          int weight_mode, float* X, float* y, float* w, cudaStream_t s) {
   if (X) {
     dim3 grid(blocks_for(ld, 256), (unsigned)cols);
-    synth_x_kernel<<<grid, 256, 0, s>>>(shape, seed, row0, rows, cols, ld, na_permille, X);
+    synth_x_kernel<<<grid, 256, 0, s>>>(shape, seed, row0, rows, 0, ld, na_permille, X);
   }
   if (y || w) synth_yw_kernel<<<blocks_for(rows, 256), 256, 0, s>>>(seed, row0, rows, cols, weight_mode, y, w);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_synth_cols(int shape, uint64_t seed, int64_t row0, int64_t rows, int col0, int ncols, int64_t ld,
+                              int na_permille, float* X, cudaStream_t s) {
+  dim3 grid(blocks_for(ld, 256), (unsigned)ncols);
+  synth_x_kernel<<<grid, 256, 0, s>>>(shape, seed, row0, rows, col0, ld, na_permille, X);
   return cudaGetLastError();
 }
 

@@ -36,6 +36,8 @@ size_t hist_smem_bytes(int node_cnt, int nb1, int copies);
 
 cudaError_t launch_synth(int shape, uint64_t seed, int64_t row0, int64_t rows, int cols, int64_t ld, int na_permille,
                          int weight_mode, float* X, float* y, float* w, cudaStream_t s);
+cudaError_t launch_synth_cols(int shape, uint64_t seed, int64_t row0, int64_t rows, int col0, int ncols, int64_t ld,
+                              int na_permille, float* X, cudaStream_t s);
 cudaError_t launch_init_enc(uint32_t* mn, uint32_t* mx, int64_t n, cudaStream_t s);
 cudaError_t launch_col_ranges(const float* X, int64_t ld, int64_t rows, int cols, uint32_t* mn, uint32_t* mx, cudaStream_t s);
 cudaError_t launch_target_absmax(const float* y, const float* w, int64_t rows, double* out, cudaStream_t s);

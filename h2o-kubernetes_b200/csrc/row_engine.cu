@@ -1,0 +1,651 @@
+// row_engine.cu — the resident row-wise tree engine (see engine.h for the design).
+//
+// Kernels:
+//   eng_load_kernel      column-major block -> row-major XT (tiled transpose), once per data set.
+//   eng_begin_kernel     new tree: records in row order, every row at the root.
+//   eng_hist_kernel      one level's histogram pass.  CTA = (contiguous run of records, block of 32*CPL columns); a
+//                        warp takes whole rows, lane L owns CPL adjacent columns; descriptors and observed ranges in
+//                        registers; shared histogram [slot][bin][channel][lane] -> bank == lane, no conflicts, one copy.
+//   eng_tiles_kernel     tiles (<= 2048 records of one node) of the level.
+//   eng_route_kernel     a6: record -> way (x >= splat, NA by direction), leaves recorded, per-tile left/right counts.
+//   eng_scan_kernel      exclusive scan of the tile counts, first record of every child, next level's node table.
+//   eng_scatter_kernel   stable move of the live records to their child's run in the other buffer.
+#include "common.cuh"
+#include "engine.h"
+#include "kernels.h"
+
+namespace h2ok {
+
+namespace {
+
+inline unsigned nblk(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
+
+constexpr int kHistSmemCap = 227 * 1024 - 1024;  // dynamic shared memory left beside the kernel's static arrays
+constexpr int kSegNodes = kEngMaxNodes + 1;       // seg[kSegNodes] = number of nodes the table describes
+constexpr int kSegInts = kEngMaxNodes + 2;
+
+// ------------------------------------------------------------------------------------------------ data / tree set-up
+__global__ void __launch_bounds__(256) eng_load_kernel(const float* __restrict__ X, int64_t ld, int64_t rows, int col0,
+                                                       int ncols, float* __restrict__ XT, int64_t ldt) {
+  __shared__ float t[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t r0 = (int64_t)blockIdx.x * 32;
+  const int c0 = blockIdx.y * 32;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int c = c0 + ty + i * 8;
+    const int64_t r = r0 + tx;
+    if (c < ncols && r < rows) t[ty + i * 8][tx] = X[(int64_t)c * ld + r];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int64_t r = r0 + ty + i * 8;
+    const int c = c0 + tx;
+    if (r < rows && c < ncols) XT[r * ldt + col0 + c] = t[tx][ty + i * 8];
+  }
+}
+
+__global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_rows, const int32_t* __restrict__ wyq_rows,
+                                 const int32_t* __restrict__ wyyq_rows, int4* __restrict__ grec, int32_t* __restrict__ leaf,
+                                 int32_t* __restrict__ seg) {
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p == 0) {
+    seg[0] = 0;
+    seg[1] = (int32_t)rows;
+    seg[kSegNodes] = 1;
+  }
+  if (p >= rows) return;
+  // zero-weight rows still travel down the tree (a6); the histogram pass skips them by weight
+  grec[p] = make_int4((int)p, wyq_rows[p], wyyq_rows[p], wq_rows ? wq_rows[p] : 1);
+  leaf[p] = -1;
+}
+
+// first g in [0, n) with table[g + 1] > v (table non-decreasing, table[n] > v)
+__device__ __forceinline__ int seg_of(const int32_t* __restrict__ table, int n, int64_t v) {
+  int lo = 0, hi = n - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (table[mid + 1] > v) hi = mid;
+    else lo = mid + 1;
+  }
+  return lo;
+}
+
+// ------------------------------------------------------------------------------------------------ histogram pass
+struct EngHistArgs {
+  const float* XT;
+  int64_t ldt;
+  int cols;
+  const int4* grec;
+  const int32_t* seg;
+  int n_nodes;
+  const h2ok_col_desc* descs;
+  int nb1;
+  int64_t* acc;
+  uint32_t* min2_enc;
+  uint32_t* maxin_enc;
+};
+
+// 32-bit shared-window addressing: keeps the per-cell address math to one IMAD (no generic->shared conversion)
+__device__ __forceinline__ void sh_inc(unsigned addr) { asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory"); }
+__device__ __forceinline__ unsigned sh_add(unsigned addr, unsigned v) {
+  unsigned o;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(o) : "r"(addr), "r"(v) : "memory");
+  return o;
+}
+
+// cold: a 32-bit shared word wrapped; the carry / borrow goes straight to the 64-bit global accumulator
+__device__ __noinline__ void eng_carry(int64_t* acc, const h2ok_col_desc* __restrict__ descs, int node, int cols, int col,
+                                       int nb1, int b, bool ev, bool e1, int v1, bool e2) {
+  if (col >= cols || descs[(int64_t)node * cols + col].nbin <= 0) return;  // untracked: its words are never flushed
+  const int64_t cell = ((int64_t)node * cols + col) * nb1 + b;
+  if (ev) carry_to_global(acc, cell, 0, 1);
+  if (e1) carry_to_global(acc, cell, 1, v1 < 0 ? -1 : 1);
+  if (e2) carry_to_global(acc, cell, 2, 1);
+}
+
+template <int CPL> struct XVec;
+template <> struct XVec<1> { using type = float; };
+template <> struct XVec<2> { using type = float2; };
+template <> struct XVec<4> { using type = float4; };
+
+__device__ __forceinline__ float xget(const float& v, int) { return v; }
+__device__ __forceinline__ float xget(const float2& v, int k) { return k ? v.y : v.x; }
+__device__ __forceinline__ float xget(const float4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
+
+// What a lane keeps in registers while it walks the rows of one node: the descriptors and running extremes of its CPL
+// columns.  A (node, column) that is not tracked gets a harmless 1-bin descriptor — its rows land in words that the
+// flush skips — so the hot loop has no per-column test.
+template <int CPL>
+struct EngLane {
+  double mn[CPL], st[CPL];
+  int nb[CPL];
+  float fmn[CPL], fmx[CPL];
+};
+
+template <int CPL, bool WEIGHTED>
+__device__ __forceinline__ void eng_row(EngLane<CPL>& c, const EngHistArgs& a, unsigned hb, int node, int col_lane,
+                                        const typename XVec<CPL>::type& xv, const int4& r) {
+  if (WEIGHTED && r.w == 0) return;  // updateHisto skips zero-weight rows before anything else
+#pragma unroll
+  for (int k = 0; k < CPL; k++) {
+    const float x = xget(xv, k);
+    const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
+    c.fmn[k] = fminf(c.fmn[k], x);  // NaN-ignoring and exact
+    c.fmx[k] = fmaxf(c.fmx[k], x);
+    const unsigned p = hb + (unsigned)(k * a.nb1 + b) * 384u;
+    bool ev = false;
+    if (WEIGHTED) {
+      const unsigned o0 = sh_add(p, (unsigned)r.w);
+      ev = o0 + (unsigned)r.w < o0;
+    } else {
+      sh_inc(p);
+    }
+    const int v1 = r.y;
+    const unsigned o1 = sh_add(p + 128u, (unsigned)v1);
+    const unsigned n1 = o1 + (unsigned)v1;
+    const bool e1 = (n1 < o1) != (v1 < 0);
+    const unsigned v2 = (unsigned)r.z;
+    const unsigned o2 = sh_add(p + 256u, v2);
+    const bool e2 = o2 + v2 < o2;
+    if (ev | e1 | e2) eng_carry(a.acc, a.descs, node, a.cols, col_lane + k, a.nb1, b, ev, e1, v1, e2);
+  }
+}
+
+template <int CPL>
+struct EngBatch {
+  static constexpr int value = CPL == 1 ? 6 : (CPL == 2 ? 4 : 2);  // rows a warp keeps in flight
+};
+
+template <int CPL, bool WEIGHTED>
+__global__ void __launch_bounds__(1024, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
+  using V = typename XVec<CPL>::type;
+  constexpr int U = EngBatch<CPL>::value;
+  extern __shared__ __align__(16) unsigned h[];
+  __shared__ unsigned s_mn[CPL * 32], s_mx[CPL * 32];
+  __shared__ unsigned char s_tracked[CPL * 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nb1 = a.nb1;
+  const int words = CPL * nb1 * 3 * 32;
+  const int col_lane = (int)blockIdx.y * 32 * CPL + lane * CPL;
+  const int n_nodes = min(a.n_nodes, a.seg[kSegNodes]);  // the table's own count bounds every read of it
+  if (n_nodes < 1) return;
+  const int64_t live = a.seg[n_nodes];
+  int p0 = (int)(live * (int64_t)blockIdx.x / gridDim.x);
+  const int p1 = (int)(live * (int64_t)(blockIdx.x + 1) / gridDim.x);
+  if (p0 >= p1) return;
+  int node = seg_of(a.seg, n_nodes, p0);
+
+  for (int i = tid; i < words; i += 1024) h[i] = ((i >> 5) % 3 == 1) ? kWyBias : 0u;
+
+  unsigned hb = (unsigned)__cvta_generic_to_shared(h) + lane * 4;  // (slot 0, bin 0, channel 0, this lane)
+  asm volatile("" : "+r"(hb));  // keep it in a register: recomputing it costs seven instructions per cell
+  // lanes past the last column read the row's last CPL floats instead (never accumulated: their columns are untracked)
+  const unsigned ldt = (unsigned)a.ldt;
+  const float* __restrict__ xrow = a.XT + min(col_lane, (int)ldt - CPL);
+  const int4* __restrict__ grec = a.grec;
+  EngLane<CPL> c;
+
+  while (p0 < p1) {
+    const int nend = a.seg[node + 1];
+    const int send = nend < p1 ? nend : p1;
+    if (send <= p0) {  // a node without rows on this shard
+      node++;
+      continue;
+    }
+    bool tracked[CPL];
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+      const int col = col_lane + k;
+      tracked[k] = false;
+      c.nb[k] = 1;
+      c.mn[k] = c.st[k] = 0.0;
+      if (col < a.cols) {
+        const h2ok_col_desc d = a.descs[(int64_t)node * a.cols + col];
+        if (d.nbin > 0) {
+          tracked[k] = true;
+          c.nb[k] = d.nbin;
+          c.mn[k] = d.min;
+          c.st[k] = d.step;
+        }
+      }
+      c.fmn[k] = __int_as_float(0x7f800000);
+      c.fmx[k] = __int_as_float(0xff800000);
+    }
+    if (warp == 0) {
+#pragma unroll
+      for (int k = 0; k < CPL; k++) {
+        s_mn[k * 32 + lane] = kEncPosInf;
+        s_mx[k * 32 + lane] = kEncNegInf;
+        s_tracked[k * 32 + lane] = tracked[k] ? 1 : 0;
+      }
+    }
+    __syncthreads();  // histogram words and range slots are initialised
+
+    // every warp takes U consecutive records at a time; the 32 warps of the CTA interleave
+    int p = p0 + warp * U;
+    for (; p + U <= send; p += 32 * U) {
+      int4 r[U];
+      V xv[U];
+#pragma unroll
+      for (int j = 0; j < U; j++) r[j] = __ldg(grec + p + j);
+#pragma unroll
+      for (int j = 0; j < U; j++) xv[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)r[j].x * ldt));
+#pragma unroll
+      for (int j = 0; j < U; j++) eng_row<CPL, WEIGHTED>(c, a, hb, node, col_lane, xv[j], r[j]);
+    }
+    for (; p < send; p++) {  // the run's last, partial batch
+      const int4 r = __ldg(grec + p);
+      const V xv = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)r.x * ldt));
+      eng_row<CPL, WEIGHTED>(c, a, hb, node, col_lane, xv, r);
+    }
+
+    // observed ranges: registers -> shared (integer min / max of the order-preserving encoding) -> global
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+      if (tracked[k]) {
+        atomicMin(&s_mn[k * 32 + lane], enc_f32_bits(__float_as_uint(c.fmn[k])));
+        atomicMax(&s_mx[k * 32 + lane], enc_f32_bits(__float_as_uint(c.fmx[k])));
+      }
+    }
+    __syncthreads();
+    if (tid < CPL * 32 && s_tracked[tid]) {
+      const int col = (int)blockIdx.y * 32 * CPL + (tid & 31) * CPL + (tid >> 5);
+      const unsigned e0 = s_mn[tid], e1 = s_mx[tid];
+      if (e0 != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)node * a.cols + col], e0);
+      if (e1 != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)node * a.cols + col], e1);
+    }
+    // flush the touched words to the 64-bit global accumulators and re-arm them for the next node
+    for (int i = tid; i < words; i += 1024) {
+      const unsigned v = h[i];
+      const int t = i >> 5;
+      const int ch = t % 3;
+      const unsigned init = ch == 1 ? kWyBias : 0u;
+      if (v != init) {
+        const int kb = t / 3;
+        const int k = kb / nb1, b = kb - k * nb1;
+        if (s_tracked[k * 32 + (i & 31)]) {
+          const int col = (int)blockIdx.y * 32 * CPL + (i & 31) * CPL + k;
+          atomicAdd(reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col) * nb1 + b) * 3 + ch,
+                    (unsigned long long)v - (unsigned long long)init);
+        }
+        h[i] = init;
+      }
+    }
+    __syncthreads();  // s_tracked and the range slots are rewritten at the top of the next run
+    p0 = send;
+    node++;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ a6 + regroup
+// 1024-thread exclusive scan; returns the exclusive prefix, *total gets the block sum (valid for every thread)
+__device__ __forceinline__ int block_exscan_1024(int v, int* s_warp, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+    int winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += t;
+    }
+    s_warp[lane] = winc - w;
+    if (lane == 31) s_warp[32] = winc;
+  }
+  __syncthreads();
+  const int ex = s_warp[warp] + inc - v;
+  *total = s_warp[32];
+  __syncthreads();  // s_warp may be reused
+  return ex;
+}
+
+__global__ void __launch_bounds__(1024) eng_tiles_kernel(const int32_t* __restrict__ seg, int n_nodes,
+                                                         int32_t* __restrict__ tile_base) {
+  __shared__ int s_warp[33];
+  const int g = threadIdx.x;
+  const int nt = g < n_nodes ? (seg[g + 1] - seg[g] + kEngTile - 1) / kEngTile : 0;
+  int total;
+  const int ex = block_exscan_1024(nt, s_warp, &total);
+  if (g <= n_nodes) tile_base[g] = ex;  // tile_base[n_nodes] = number of tiles
+}
+
+struct TileRange {
+  int g;
+  int64_t start, end;
+};
+__device__ __forceinline__ TileRange tile_range(const int32_t* __restrict__ seg, const int32_t* __restrict__ tile_base,
+                                                int n_nodes, int t) {
+  TileRange r;
+  r.g = seg_of(tile_base, n_nodes, t);
+  r.start = (int64_t)seg[r.g] + (int64_t)(t - tile_base[r.g]) * kEngTile;
+  const int64_t nend = seg[r.g + 1];
+  r.end = r.start + kEngTile < nend ? r.start + kEngTile : nend;
+  return r;
+}
+
+__global__ void __launch_bounds__(256) eng_route_kernel(const float* __restrict__ XT, int64_t ldt,
+                                                        const int4* __restrict__ grec, const int32_t* __restrict__ seg,
+                                                        const int32_t* __restrict__ tile_base, int n_nodes,
+                                                        const h2ok_split* __restrict__ splits,
+                                                        const int32_t* __restrict__ child_ids, int gid_base,
+                                                        uint8_t* __restrict__ codes, int32_t* __restrict__ leaf,
+                                                        int32_t* __restrict__ tile_cnt) {
+  __shared__ int s_cnt[2];
+  const int t = blockIdx.x;
+  if (t >= tile_base[n_nodes]) return;
+  const TileRange tr = tile_range(seg, tile_base, n_nodes, t);
+  const int g = tr.g;
+  if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int col = splits[g].col;
+  const int na = splits[g].na_dir;
+  const float splat = splits[g].splat;
+  const int c0 = child_ids[2 * g], c1 = child_ids[2 * g + 1];
+  const int leaf0 = (gid_base + g) * 3;
+  int n0 = 0, n1 = 0;
+#pragma unroll
+  for (int j = 0; j < kEngTile / 256; j++) {
+    const int64_t p = tr.start + j * 256 + threadIdx.x;
+    int code = 3;
+    if (p < tr.end) {
+      const int row = grec[p].x;
+      code = 2;
+      if (col < 0) {
+        leaf[row] = leaf0;
+      } else {
+        const float d = XT[(int64_t)row * ldt + col];
+        int way;
+        if (d != d) way = (na == H2OK_NA_LEFT) ? 0 : 1;
+        else if (na == H2OK_NA_VS_REST) way = 0;
+        else way = d >= splat ? 1 : 0;
+        if ((way ? c1 : c0) < 0) leaf[row] = leaf0 + 1 + way;
+        else code = way;
+      }
+      codes[p] = (uint8_t)code;
+    }
+    n0 += __popc(__ballot_sync(0xffffffffu, code == 0));
+    n1 += __popc(__ballot_sync(0xffffffffu, code == 1));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&s_cnt[0], n0);
+    atomicAdd(&s_cnt[1], n1);
+  }
+  __syncthreads();
+  if (threadIdx.x < 2) tile_cnt[2 * t + threadIdx.x] = s_cnt[threadIdx.x];
+}
+
+// One CTA: exclusive scan of the (left, right) tile counts in place (entry [tiles] = totals), the first record of every
+// child slot in the next order, and the next level's node table (children keep the order of their slots 2*node + way,
+// which is also the order of their ids).
+__global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ tile_cnt, const int32_t* __restrict__ tile_base,
+                                                        int n_nodes, const int32_t* __restrict__ child_ids,
+                                                        int32_t* __restrict__ slot_start, int32_t* __restrict__ seg_next) {
+  __shared__ int s_warp[33];
+  __shared__ int s_run[2];
+  const int T = tile_base[n_nodes];
+  if (threadIdx.x < 2) s_run[threadIdx.x] = 0;
+  __syncthreads();
+  for (int first = 0; first < T; first += 1024) {
+    const int t = first + threadIdx.x;
+    const int v0 = t < T ? tile_cnt[2 * t] : 0, v1 = t < T ? tile_cnt[2 * t + 1] : 0;
+    int tot0, tot1;
+    const int e0 = block_exscan_1024(v0, s_warp, &tot0);
+    const int e1 = block_exscan_1024(v1, s_warp, &tot1);
+    if (t < T) {
+      tile_cnt[2 * t] = s_run[0] + e0;
+      tile_cnt[2 * t + 1] = s_run[1] + e1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      s_run[0] += tot0;
+      s_run[1] += tot1;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < 2) tile_cnt[2 * T + threadIdx.x] = s_run[threadIdx.x];
+  __syncthreads();  // the scanned counts are visible to the whole block
+  const int g = threadIdx.x;
+  int tot0 = 0, tot1 = 0, cl = -1, cr = -1;
+  if (g < n_nodes) {
+    const int a = tile_base[g], b = tile_base[g + 1];
+    tot0 = tile_cnt[2 * b] - tile_cnt[2 * a];
+    tot1 = tile_cnt[2 * b + 1] - tile_cnt[2 * a + 1];
+    cl = child_ids[2 * g];
+    cr = child_ids[2 * g + 1];
+  }
+  int live, nc;
+  const int ex = block_exscan_1024(tot0 + tot1, s_warp, &live);
+  (void)block_exscan_1024((cl >= 0) + (cr >= 0), s_warp, &nc);
+  if (g < n_nodes) {
+    slot_start[2 * g] = ex;
+    slot_start[2 * g + 1] = ex + tot0;
+    if (cl >= 0) seg_next[cl] = ex;
+    if (cr >= 0) seg_next[cr] = ex + tot0;
+  }
+  if (g == 0) {
+    seg_next[nc] = live;
+    seg_next[kSegNodes] = nc;
+  }
+}
+
+__global__ void __launch_bounds__(256) eng_scatter_kernel(const int4* __restrict__ grec, int4* __restrict__ grec_n,
+                                                          const int32_t* __restrict__ seg,
+                                                          const int32_t* __restrict__ tile_base, int n_nodes,
+                                                          const uint8_t* __restrict__ codes,
+                                                          const int32_t* __restrict__ tile_cnt,
+                                                          const int32_t* __restrict__ slot_start) {
+  constexpr int J = kEngTile / 256;
+  __shared__ unsigned s_pre[J * 8];  // per (step, warp): records going left (low half) / right (high half)
+  const int t = blockIdx.x;
+  if (t >= tile_base[n_nodes]) return;
+  const TileRange tr = tile_range(seg, tile_base, n_nodes, t);
+  const int g = tr.g;
+  const int tb = tile_base[g];
+  const int64_t base0 = (int64_t)slot_start[2 * g] + tile_cnt[2 * t] - tile_cnt[2 * tb];
+  const int64_t base1 = (int64_t)slot_start[2 * g + 1] + tile_cnt[2 * t + 1] - tile_cnt[2 * tb + 1];
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  int code[J];
+#pragma unroll
+  for (int j = 0; j < J; j++) {
+    const int64_t p = tr.start + j * 256 + threadIdx.x;
+    code[j] = p < tr.end ? (int)codes[p] : 3;
+    const unsigned b0 = __ballot_sync(0xffffffffu, code[j] == 0), b1 = __ballot_sync(0xffffffffu, code[j] == 1);
+    if (lane == 0) s_pre[j * 8 + warp] = (unsigned)__popc(b0) | ((unsigned)__popc(b1) << 16);
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive scan of the J * 8 packed pairs in (step, warp) order = record order
+    unsigned v[J * 8 / 32], sum = 0;
+#pragma unroll
+    for (int i = 0; i < J * 8 / 32; i++) {
+      v[i] = s_pre[lane * (J * 8 / 32) + i];
+      sum += v[i];
+    }
+    unsigned inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += u;
+    }
+    unsigned run = inc - sum;
+#pragma unroll
+    for (int i = 0; i < J * 8 / 32; i++) {
+      s_pre[lane * (J * 8 / 32) + i] = run;
+      run += v[i];
+    }
+  }
+  __syncthreads();
+  const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int j = 0; j < J; j++) {
+    const int64_t p = tr.start + j * 256 + threadIdx.x;
+    const unsigned b0 = __ballot_sync(0xffffffffu, code[j] == 0), b1 = __ballot_sync(0xffffffffu, code[j] == 1);
+    const unsigned pre = s_pre[j * 8 + warp];
+    if (code[j] == 0) grec_n[base0 + (pre & 0xFFFFu) + __popc(b0 & lt)] = grec[p];
+    else if (code[j] == 1) grec_n[base1 + (pre >> 16) + __popc(b1 & lt)] = grec[p];
+  }
+}
+
+__global__ void eng_nid_kernel(const int4* __restrict__ grec, const int32_t* __restrict__ seg,
+                               int32_t* __restrict__ nid_rows) {
+  const int n_nodes = seg[kSegNodes];
+  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n_nodes < 1 || p >= seg[n_nodes]) return;
+  nid_rows[grec[p].x] = seg_of(seg, n_nodes, p);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ host side
+cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
+  engine_free(e);
+  if (rows >= (1ll << 31) - kEngTile) return cudaErrorInvalidValue;
+  e.rows = rows;
+  e.cols = cols;
+  e.weighted = weighted;
+  e.ldt = ((int64_t)cols + 7) / 8 * 8;
+  e.max_tiles = rows / kEngTile + kEngMaxNodes + 1;
+  cudaError_t err = cudaSuccess;
+  auto A = [&](void** p, size_t bytes) {
+    if (err == cudaSuccess) err = cudaMalloc(p, bytes);
+  };
+  A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  for (int k = 0; k < 2; k++) {
+    A((void**)&e.grec[k], sizeof(int4) * (size_t)rows);
+    A((void**)&e.seg[k], sizeof(int32_t) * kSegInts);
+  }
+  A((void**)&e.codes, (size_t)rows);
+  A((void**)&e.tile_base, sizeof(int32_t) * (kEngMaxNodes + 1));
+  A((void**)&e.tile_cnt, sizeof(int32_t) * 2 * (size_t)(e.max_tiles + 1));
+  A((void**)&e.slot_start, sizeof(int32_t) * 2 * kEngMaxNodes);
+  A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
+  if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  if (err != cudaSuccess) engine_free(e);
+  return err;
+}
+
+void engine_free(Engine& e) {
+  cudaFree(e.XT);
+  for (int k = 0; k < 2; k++) {
+    cudaFree(e.grec[k]);
+    cudaFree(e.seg[k]);
+    e.grec[k] = nullptr;
+    e.seg[k] = nullptr;
+  }
+  cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.slot_start); cudaFree(e.leaf);
+  e.XT = nullptr;
+  e.codes = nullptr;
+  e.tile_base = e.tile_cnt = e.slot_start = e.leaf = nullptr;
+  e.rows = e.ldt = 0;
+  e.n_nodes = 0;
+}
+
+cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s) {
+  dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
+  eng_load_kernel<<<grid, 256, 0, s>>>(X, ld, e.rows, col0, ncols, e.XT, e.ldt);
+  return cudaGetLastError();
+}
+
+cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
+                              cudaStream_t s) {
+  e.cur = 0;
+  e.n_nodes = 1;
+  eng_begin_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.rows, e.weighted ? wq_rows : nullptr, wyq_rows, wyyq_rows,
+                                                     e.grec[0], e.leaf, e.seg[0]);
+  return cudaGetLastError();
+}
+
+static int eng_cpl(int cols, int nb1) {
+  if (cols > 64 && (size_t)128 * nb1 * 12 <= (size_t)kHistSmemCap) return 4;
+  if (cols > 32 && (size_t)64 * nb1 * 12 <= (size_t)kHistSmemCap) return 2;
+  if ((size_t)32 * nb1 * 12 <= (size_t)kHistSmemCap) return 1;
+  return 0;
+}
+
+int engine_max_nb1(int cols) {
+  (void)cols;
+  return kHistSmemCap / (32 * 12);
+}
+
+template <int CPL, bool W>
+static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
+  static bool attr_done[64] = {};  // per device, per instantiation
+  int dev = 0;
+  cudaGetDevice(&dev);
+  bool& attr = attr_done[dev & 63];
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+    if (e != cudaSuccess) return e;
+    attr = true;
+  }
+  eng_hist_kernel<CPL, W><<<grid, 1024, smem, s>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int64_t* acc,
+                               uint32_t* min2_enc, uint32_t* maxin_enc, cudaStream_t s) {
+  if (n_nodes < 1 || n_nodes >= kEngMaxNodes) return cudaErrorInvalidValue;
+  const int cpl = eng_cpl(e.cols, nb1);
+  if (!cpl) return cudaErrorInvalidValue;
+  e.n_nodes = n_nodes;
+  EngHistArgs a{};
+  a.XT = e.XT;
+  a.ldt = e.ldt;
+  a.cols = e.cols;
+  a.grec = e.grec[e.cur];
+  a.seg = e.seg[e.cur];
+  a.n_nodes = n_nodes;
+  a.descs = descs;
+  a.nb1 = nb1;
+  a.acc = acc;
+  a.min2_enc = min2_enc;
+  a.maxin_enc = maxin_enc;
+  const int colblk = 32 * cpl;
+  // one CTA per SM and column block; every CTA owns the same share of the level's records
+  const dim3 grid((unsigned)kSMs, (unsigned)((e.cols + colblk - 1) / colblk));
+  const size_t smem = (size_t)colblk * nb1 * 12;
+  if (e.weighted) {
+    if (cpl == 4) return launch_eng_hist<4, true>(a, grid, smem, s);
+    if (cpl == 2) return launch_eng_hist<2, true>(a, grid, smem, s);
+    return launch_eng_hist<1, true>(a, grid, smem, s);
+  }
+  if (cpl == 4) return launch_eng_hist<4, false>(a, grid, smem, s);
+  if (cpl == 2) return launch_eng_hist<2, false>(a, grid, smem, s);
+  return launch_eng_hist<1, false>(a, grid, smem, s);
+}
+
+cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,
+                                cudaStream_t s) {
+  if (n_nodes < 1 || n_nodes >= kEngMaxNodes) return cudaErrorInvalidValue;
+  const int nx = 1 - e.cur;
+  const unsigned tiles = (unsigned)(e.rows / kEngTile + n_nodes + 1);  // bound: the live count stays on the device
+  eng_tiles_kernel<<<1, 1024, 0, s>>>(e.seg[e.cur], n_nodes, e.tile_base);
+  eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.grec[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
+                                         gid_base, e.codes, e.leaf, e.tile_cnt);
+  eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx]);
+  eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.grec[e.cur], e.grec[nx], e.seg[e.cur], e.tile_base, n_nodes, e.codes,
+                                           e.tile_cnt, e.slot_start);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return err;
+  e.cur = nx;
+  e.n_nodes = 0;  // the caller says how many children there are (build_level / nid)
+  return cudaSuccess;
+}
+
+cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s) {
+  cudaError_t err = cudaMemsetAsync(nid_rows, 0xFF, sizeof(int32_t) * (size_t)e.rows, s);
+  if (err != cudaSuccess) return err;
+  eng_nid_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.grec[e.cur], e.seg[e.cur], nid_rows);
+  return cudaGetLastError();
+}
+
+}  // namespace h2ok

@@ -21,6 +21,7 @@ SIGNATURES = {
     "h2ok_hist_set_stream": [vp, vp, i32],
     "h2ok_hist_sync": [vp],
     "h2ok_hist_synth_fill_dev": [vp, i32, u64, i64, i64, i32, i64, i32, i32, vp, vp, vp],
+    "h2ok_hist_synth_fill_cols_dev": [vp, i32, u64, i64, i64, i32, i32, i64, i32, vp],
     "h2ok_hist_col_ranges_dev": [vp, vp, i64, i64, i32, vp, vp],
     "h2ok_hist_target_absmax_dev": [vp, vp, vp, i64, vp],
     "h2ok_hist_quantize_rows_dev": [vp, vp, vp, i64, pQ, vp, vp, vp],
@@ -31,7 +32,8 @@ SIGNATURES = {
     "h2ok_hist_next_level_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
     "h2ok_hist_next_level_noalloc_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
     "h2ok_hist_apply_splits_dev": [vp, vp, i64, i64, vp, vp, i32, i32, vp, vp],
-    "h2ok_hist_tree_create": [vp, i64, i32, i32, C.POINTER(vp), C.POINTER(i64)],
+    "h2ok_hist_tree_create": [vp, i64, i32, i32],
+    "h2ok_hist_tree_load_cols_dev": [vp, i32, i32, vp, i64],
     "h2ok_hist_tree_destroy": [vp],
     "h2ok_hist_tree_begin_dev": [vp, vp, vp, vp],
     "h2ok_hist_tree_build_level_dev": [vp, i32, vp, i32, i32, vp, vp, vp],

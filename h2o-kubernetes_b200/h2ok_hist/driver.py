@@ -194,26 +194,21 @@ class CudaShard:
         return s
 
 
-class _DevMem:
-    """A raw device allocation owned by the library, exposed to torch through __cuda_array_interface__."""
-
-    def __init__(self, ptr, shape, typestr):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
-
-
 class EngineShard(CudaShard):
-    """One GPU's rows held in the library's resident tree engine (h2ok_hist_tree_*): the shard is kept physically
-    grouped by node, so every histogram CTA sees at most two nodes.  Same interface and bit-identical results as
-    CudaShard; costs a second copy of X in device memory."""
+    """One GPU's rows held in the library's resident tree engine (h2ok_hist_tree_*): a row-major copy of X plus row
+    records kept grouped by node, so every histogram CTA works on one node at a time with its descriptors in
+    registers.  Same interface and bit-identical results as CudaShard.  The column-major X only passes through a
+    staging buffer of at most `stage_bytes`; it is not kept."""
+
+    stage_bytes = 2 << 30
 
     def _alloc_rows(self, rows, cols, weighted):
         self.rows, self.cols = rows, cols
-        xp, ld = C.c_void_p(), C.c_int64()
-        self.lib.call("h2ok_hist_tree_create", self.ctx, rows, cols, 1 if weighted else 0, C.byref(xp), C.byref(ld))
-        self.ld = int(ld.value)
-        dev = self.device
-        self.X = torch.as_tensor(_DevMem(xp.value, (cols, self.ld), "<f4"), device=dev)  # valid until the first regroup
+        self.lib.call("h2ok_hist_tree_create", self.ctx, rows, cols, 1 if weighted else 0)
         n = (rows + 63) // 64 * 64
+        self.ld = n
+        dev = self.device
+        self.X = None
         self.y = torch.empty(n, dtype=torch.float32, device=dev)
         self.w = torch.empty(n, dtype=torch.float32, device=dev) if weighted else None
         self.weighted = weighted
@@ -222,6 +217,45 @@ class EngineShard(CudaShard):
         self.wyyq = torch.empty(n, dtype=torch.int32, device=dev)
         self._nid = torch.empty(n, dtype=torch.int32, device=dev)
         self._leaf = torch.empty(n, dtype=torch.int32, device=dev)
+        self._cmn = torch.empty(cols, dtype=torch.int32, device=dev)
+        self._cmx = torch.empty(cols, dtype=torch.int32, device=dev)
+
+    def _blocks(self):
+        """Column blocks whose column-major staging copy stays under stage_bytes."""
+        per = max(1, min(self.cols, self.stage_bytes // (4 * self.ld)))
+        return [(c0, min(per, self.cols - c0)) for c0 in range(0, self.cols, per)]
+
+    def _load_block(self, stage, c0, nc):
+        """Column-major staging block -> the engine's row-major copy; the block's column ranges are kept for a1."""
+        self.lib.call("h2ok_hist_tree_load_cols_dev", self.ctx, c0, nc, _ptr(stage), self.ld)
+        self.lib.call("h2ok_hist_col_ranges_dev", self.ctx, _ptr(stage), self.ld, self.rows, nc,
+                      C.c_void_p(self._cmn.data_ptr() + 4 * c0), C.c_void_p(self._cmx.data_ptr() + 4 * c0))
+
+    def set_data_synth(self, shape, seed, row0, rows, cols, na_permille=0, weight_mode=0):
+        self._alloc_rows(rows, cols, weight_mode != 0)
+        blocks = self._blocks()
+        stage = torch.empty((blocks[0][1], self.ld), dtype=torch.float32, device=self.device)
+        for c0, nc in blocks:
+            self.lib.call("h2ok_hist_synth_fill_cols_dev", self.ctx, shape, seed, row0, rows, c0, nc, self.ld,
+                          na_permille, _ptr(stage))
+            self._load_block(stage, c0, nc)
+        self.lib.call("h2ok_hist_synth_fill_dev", self.ctx, shape, seed, row0, rows, cols, self.ld, na_permille,
+                      weight_mode, None, _ptr(self.y), _ptr(self.w))
+        torch.cuda.current_stream(self.device).synchronize()  # the staging buffer is released here
+
+    def set_data_tensors(self, X, y, w=None):
+        cols, rows = X.shape
+        self._alloc_rows(rows, cols, w is not None)
+        blocks = self._blocks()
+        stage = torch.zeros((blocks[0][1], self.ld), dtype=torch.float32, device=self.device)
+        for c0, nc in blocks:
+            stage[:nc, :rows].copy_(X[c0:c0 + nc], non_blocking=False)
+            self._load_block(stage, c0, nc)
+        self.set_targets(y, w)
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def col_ranges(self):
+        return self._cmn.clone(), self._cmx.clone()
 
     @property
     def nid(self):
@@ -244,13 +278,13 @@ class EngineShard(CudaShard):
     def build_level(self, n_nodes):
         self.lib.call("h2ok_hist_tree_build_level_dev", self.ctx, n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
-        self.launches += 3  # init_enc + work items + histogram pass
+        self.launches += 2  # init_enc + histogram pass
         return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
 
     def apply_splits(self, n_nodes, gid_base, last=False):
         self.lib.call("h2ok_hist_tree_apply_splits_dev", self.ctx, _ptr(self.splits), _ptr(self.child_ids), gid_base,
                       n_nodes, 1 if last else 0)
-        self.launches += 1 if last else 4  # route (+ tile scan, segment table, scatter)
+        self.launches += 4  # tiles, route, scan, scatter
 
 
 def _world():

@@ -131,6 +131,10 @@ int32_t h2ok_hist_sync(h2ok_ctx* ctx);
 int32_t h2ok_hist_synth_fill_dev(h2ok_ctx* ctx, int32_t shape, uint64_t seed, int64_t row0, int64_t rows,
                                  int32_t cols, int64_t ld, int32_t na_permille, int32_t weight_mode,
                                  float* d_X, float* d_y, float* d_w);
+/* The same generator for columns [col0, col0 + ncols) only (column c at d_X + (c - col0) * ld): lets a caller stage a
+ * wide matrix block by block (h2ok_hist_tree_load_cols_dev). */
+int32_t h2ok_hist_synth_fill_cols_dev(h2ok_ctx* ctx, int32_t shape, uint64_t seed, int64_t row0, int64_t rows,
+                                      int32_t col0, int32_t ncols, int64_t ld, int32_t na_permille, float* d_X);
 
 /* Root ranges (DHistogram.initialHist reads Vec.min()/max()): finite-or-inf min and max per column, NaN skipped.
  * Output is the order-preserving uint32 encoding (see h2ok_hist_decode_f32) so ranks can be combined with integer min/max. */
@@ -204,22 +208,30 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
                                    int32_t* d_leaf);
 
 /* ---- resident tree engine (device-resident; the fast path at depth) ---------------------------------------------
- * Same results as build_level_dev / apply_splits_dev, bit for bit, but the shard lives inside the context and is kept
- * physically grouped by node (what ScoreBuildHistogram2 does with row indices per chunk, done here to the data):
- * every histogram CTA then sees at most two nodes, keeps their descriptors in registers and 32 private histogram
- * copies per node, and the regrouping write for the next level is fused into the histogram pass.
- * Call order: tree_create -> fill the X buffer it returns (column c at x + c*ld, rows in original order) ->
- * per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce / finalize / find_splits / next_level as
- * usual], tree_apply_splits_dev.  Costs two copies of X in device memory. */
-int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted, float** d_x_out,
-                              int64_t* ld_out);
+ * Same results as build_level_dev / apply_splits_dev, bit for bit.  The shard lives inside the context as a ROW-major
+ * copy of X that never moves; per level only a 16-byte row record {row, wyq, wyyq, wq} is kept grouped by node (what
+ * ScoreBuildHistogram2 does with row indices per chunk, hex/tree/ScoreBuildHistogram2.java).  A histogram CTA then
+ * works on one node at a time: a warp takes whole rows (one coalesced load, every sector used), each lane owns its
+ * columns' descriptors in registers and its own shared-memory bank, so there are no descriptor lookups and no
+ * bank conflicts at any depth.
+ * Call order: tree_create -> tree_load_cols_dev for every block of columns (in any order; the caller's column-major
+ * block can be freed or reused afterwards) -> per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce /
+ * finalize / find_splits / next_level as usual], tree_apply_splits_dev.  Device memory: rows * (4 * cols rounded up
+ * to 8 + 41) bytes.  Limits: rows < 2^31 - 2048; (max_bins + 1) <= 602 (one 32-column block must fit 226 KB). */
+int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
+/* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in
+ * original order */
+int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* ctx, int32_t col0, int32_t ncols, const float* d_X, int64_t ld);
 /* new tree: per-row fixed-point targets in ORIGINAL row order (d_wq NULL when unweighted); all rows back at the root */
 int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* ctx, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq);
-/* a3/a4 for the current level; outputs as h2ok_hist_build_level_dev */
+/* a3/a4 for the current level; outputs as h2ok_hist_build_level_dev.  n_nodes must be the number of children the
+ * previous tree_apply_splits_dev produced (1 after tree_begin_dev). */
 int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* ctx, int32_t n_nodes, const h2ok_col_desc* d_descs, int32_t max_bins,
                                        int32_t clear, int64_t* d_acc, uint32_t* d_min2_enc, uint32_t* d_maxin_enc);
-/* a6 for the current level (+ preparation of the layout grouped by the children unless last_level != 0) */
+/* a6 for the current level + regrouping of the records by child.  Child ids must be numbered in slot order
+ * (2 * node + way), which is what next_level_dev produces; last_level is accepted for symmetry and not needed
+ * (with every child id -1 all rows retire). */
 int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, const int32_t* d_child_ids,
                                         int32_t gid_base, int32_t n_nodes, int32_t last_level);
 /* row -> node of the current level / leaf codes, in original row order */

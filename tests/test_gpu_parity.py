@@ -544,8 +544,8 @@ def test_gbm_bernoulli_tracks_oracle(eshard, oracle):
 @pytest.mark.parametrize("rows,cols,depth,min_rows", [(1, 3, 3, 1), (5, 3, 3, 1), (130, 4, 5, 1), (4097, 5, 6, 2),
                                                       (60000, 6, 10, 1)])
 def test_engine_ragged_sizes_and_deep_trees(eshard, oracle, rows, cols, depth, min_rows):
-    """Tiny shards, sizes that are not multiples of the 128-position blocks / 4096-position tiles, and a depth-10
-    tree with min_rows 1 (hundreds of small segments, many rows retiring early) through the node-grouped engine."""
+    """Tiny shards, sizes that are not multiples of the 2048-record tiles, and a depth-10 tree with min_rows 1
+    (hundreds of small nodes, many rows retiring early) through the node-grouped engine."""
     X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 1000 + rows, 0, rows, cols, na_permille=20)
     params = abi.Params.make(nbins=32, max_depth=depth, min_rows=min_rows, min_split_improvement=0.0)
     levels, st = run_tree_both(eshard, oracle, X, rows, y, None, params)
@@ -562,20 +562,21 @@ def test_engine_rejects_what_it_cannot_hold(lib):
         with pytest.raises(capi.H2okError) as e:  # no engine yet
             lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 256, 1, P(buf), P(buf), P(buf))
         assert e.value.code == abi.ERR_STATE
-        xp, ld = C.c_void_p(), C.c_int64()
-        lib.call("h2ok_hist_tree_create", h, 1000, 2, 0, C.byref(xp), C.byref(ld))
-        assert xp.value and ld.value >= 1000
-        with pytest.raises(capi.H2okError) as e:  # two children x 32 copies x 513 bins do not fit 227 KB
-            lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 512, 1, P(buf), P(buf), P(buf))
+        lib.call("h2ok_hist_tree_create", h, 1000, 2, 0)
+        with pytest.raises(capi.H2okError) as e:  # 32 columns x 1025 bins x 12 B do not fit 226 KB
+            lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 1024, 1, P(buf), P(buf), P(buf))
         assert e.value.code == abi.ERR_UNSUPPORTED and "max_bins" in str(e.value)
+        with pytest.raises(capi.H2okError) as e:  # a column block outside the shard
+            lib.call("h2ok_hist_tree_load_cols_dev", h, 1, 2, P(buf), 1000)
+        assert e.value.code == abi.ERR_ARG
         with pytest.raises(capi.H2okError):
-            lib.call("h2ok_hist_tree_create", h, 0, 2, 0, C.byref(xp), C.byref(ld))
+            lib.call("h2ok_hist_tree_create", h, 0, 2, 0)
     finally:
         lib.call("h2ok_hist_destroy", h)
 
 
-def test_engine_second_tree_reuses_the_regrouped_layout(eshard, oracle):
-    """A new tree starts from whatever order the previous one left the rows in; results must not depend on it."""
+def test_engine_trees_back_to_back(eshard, oracle):
+    """Trees built one after the other on the same resident shard do not see each other's record order."""
     from h2ok_hist.driver import LevelDriver
 
     rows, cols = 50000, 6
@@ -590,7 +591,7 @@ def test_engine_second_tree_reuses_the_regrouped_layout(eshard, oracle):
     acc1 = eshard.acc.clone()
     y2 = (-y[:rows] * 0.5 + 0.25).astype(np.float32)
     eshard.set_targets(torch.from_numpy(y2), torch.from_numpy(w[:rows].copy()))
-    drv.train_tree()  # a different tree in between shuffles the layout further
+    drv.train_tree()  # a different tree in between
     eshard.set_targets(torch.from_numpy(y[:rows].copy()), torch.from_numpy(w[:rows].copy()))
     drv.train_tree()
     assert torch.equal(eshard.leaf[:rows], leaf1) and torch.equal(eshard.acc, acc1)
