@@ -33,7 +33,10 @@ struct Engine {
   int cols = 0;
   bool weighted = false;
   float* XT = nullptr;                  // [rows][ldt] row-major copy of the shard
-  int4* grec[2] = {nullptr, nullptr};   // row records grouped by node: {row, wyq, wyyq, wq}; double buffered
+  // row records grouped by node, double buffered: the row, its fixed-point targets {wyq, wyyq}, its weight
+  int32_t* gidx[2] = {nullptr, nullptr};
+  uint2* gval[2] = {nullptr, nullptr};
+  int32_t* gw[2] = {nullptr, nullptr};  // weighted shards only
   int32_t* seg[2] = {nullptr, nullptr}; // [n_nodes + 1] first record of every node of the level; seg[n_nodes] = live rows
   int cur = 0;
   int n_nodes = 0;                      // nodes of the current level (0: no tree in progress)

@@ -47,7 +47,8 @@ __global__ void __launch_bounds__(256) eng_load_kernel(const float* __restrict__
 }
 
 __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_rows, const int32_t* __restrict__ wyq_rows,
-                                 const int32_t* __restrict__ wyyq_rows, int4* __restrict__ grec, int32_t* __restrict__ leaf,
+                                 const int32_t* __restrict__ wyyq_rows, int32_t* __restrict__ gidx,
+                                 uint2* __restrict__ gval, int32_t* __restrict__ gw, int32_t* __restrict__ leaf,
                                  int32_t* __restrict__ seg) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0) {
@@ -57,7 +58,9 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
   }
   if (p >= rows) return;
   // zero-weight rows still travel down the tree (a6); the histogram pass skips them by weight
-  grec[p] = make_int4((int)p, wyq_rows[p], wyyq_rows[p], wq_rows ? wq_rows[p] : 1);
+  gidx[p] = (int32_t)p;
+  gval[p] = make_uint2((unsigned)wyq_rows[p], (unsigned)wyyq_rows[p]);
+  if (gw) gw[p] = wq_rows[p];
   leaf[p] = -1;
 }
 
@@ -77,7 +80,9 @@ struct EngHistArgs {
   const float* XT;
   int64_t ldt;
   int cols;
-  const int4* grec;
+  const int32_t* gidx;  // row of every record
+  const uint2* gval;    // {wyq, wyyq}
+  const int32_t* gw;    // wq (weighted only)
   const int32_t* seg;
   int n_nodes;
   const h2ok_col_desc* descs;
@@ -97,12 +102,12 @@ __device__ __forceinline__ unsigned sh_add(unsigned addr, unsigned v) {
 
 // cold: a 32-bit shared word wrapped; the carry / borrow goes straight to the 64-bit global accumulator
 __device__ __noinline__ void eng_carry(int64_t* acc, const h2ok_col_desc* __restrict__ descs, int node, int cols, int col,
-                                       int nb1, int b, bool ev, bool e1, int v1, bool e2) {
+                                       int nb1, int b, int d0, int d1, int d2) {
   if (col >= cols || descs[(int64_t)node * cols + col].nbin <= 0) return;  // untracked: its words are never flushed
   const int64_t cell = ((int64_t)node * cols + col) * nb1 + b;
-  if (ev) carry_to_global(acc, cell, 0, 1);
-  if (e1) carry_to_global(acc, cell, 1, v1 < 0 ? -1 : 1);
-  if (e2) carry_to_global(acc, cell, 2, 1);
+  if (d0) carry_to_global(acc, cell, 0, d0);
+  if (d1) carry_to_global(acc, cell, 1, d1);
+  if (d2) carry_to_global(acc, cell, 2, d2);
 }
 
 template <int CPL> struct XVec;
@@ -124,50 +129,90 @@ struct EngLane {
   float fmn[CPL], fmx[CPL];
 };
 
-template <int CPL, bool WEIGHTED>
-__device__ __forceinline__ void eng_row(EngLane<CPL>& c, const EngHistArgs& a, unsigned hb, int node, int col_lane,
-                                        const typename XVec<CPL>::type& xv, const int4& r) {
-  if (WEIGHTED && r.w == 0) return;  // updateHisto skips zero-weight rows before anything else
+// a signed value v was added to a word that held `old`: did the 32-bit word wrap, and which way?
+__device__ __forceinline__ bool wrapped(unsigned old, int v) { return (old > ~(unsigned)v) != (v < 0); }
+
+// U rows x CPL cells in three phases, so that the independent cells overlap their latencies instead of running one
+// behind the other: (1) every cell's bin and shared address, (2) every cell's atomics, (3) ONE test for "some 32-bit
+// word wrapped".  The cold path looks at the saved old values again to find which.  wq == 0 rows (weighted only) are
+// turned into NaNs that add zeros: the NA bin gets +0 and the running extremes ignore NaN — which is what skipping
+// the row means.  v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
+template <int CPL, bool WEIGHTED, int U>
+__device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a, unsigned hb, int node, int col_lane,
+                                          const typename XVec<CPL>::type (&xv)[U], const int (&v1)[U], const int (&v2)[U],
+                                          const int (&w)[U]) {
+  unsigned pa[U * CPL], o1[U * CPL], o2[U * CPL], o0[WEIGHTED ? U * CPL : 1];
 #pragma unroll
-  for (int k = 0; k < CPL; k++) {
-    const float x = xget(xv, k);
-    const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
-    c.fmn[k] = fminf(c.fmn[k], x);  // NaN-ignoring and exact
-    c.fmx[k] = fmaxf(c.fmx[k], x);
-    const unsigned p = hb + (unsigned)(k * a.nb1 + b) * 384u;
-    bool ev = false;
-    if (WEIGHTED) {
-      const unsigned o0 = sh_add(p, (unsigned)r.w);
-      ev = o0 + (unsigned)r.w < o0;
-    } else {
-      sh_inc(p);
+  for (int j = 0; j < U; j++) {
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+      float x = xget(xv[j], k);
+      if (WEIGHTED) x = w[j] != 0 ? x : __int_as_float(0x7FC00000);
+      const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
+      c.fmn[k] = fminf(c.fmn[k], x);  // NaN-ignoring and exact
+      c.fmx[k] = fmaxf(c.fmx[k], x);
+      pa[j * CPL + k] = hb + (unsigned)(k * a.nb1 + b) * 384u;
     }
-    const int v1 = r.y;
-    const unsigned o1 = sh_add(p + 128u, (unsigned)v1);
-    const unsigned n1 = o1 + (unsigned)v1;
-    const bool e1 = (n1 < o1) != (v1 < 0);
-    const unsigned v2 = (unsigned)r.z;
-    const unsigned o2 = sh_add(p + 256u, v2);
-    const bool e2 = o2 + v2 < o2;
-    if (ev | e1 | e2) eng_carry(a.acc, a.descs, node, a.cols, col_lane + k, a.nb1, b, ev, e1, v1, e2);
+  }
+#pragma unroll
+  for (int j = 0; j < U; j++) {
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+      const unsigned p = pa[j * CPL + k];
+      if (WEIGHTED) o0[j * CPL + k] = sh_add(p, (unsigned)w[j]);
+      else sh_inc(p);
+      o1[j * CPL + k] = sh_add(p + 128u, (unsigned)v1[j]);
+      o2[j * CPL + k] = sh_add(p + 256u, (unsigned)v2[j]);
+    }
+  }
+  bool any = false;
+#pragma unroll
+  for (int j = 0; j < U; j++) {
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+      any |= wrapped(o1[j * CPL + k], v1[j]);
+      any |= wrapped(o2[j * CPL + k], v2[j]);
+      if (WEIGHTED) any |= o0[j * CPL + k] > ~(unsigned)w[j];
+    }
+  }
+  if (any) {  // fully unrolled: dynamic indexing would push the saved values into local memory on the hot path too
+#pragma unroll
+    for (int i = 0; i < U * CPL; i++) {
+      const int j = i / CPL, k = i - j * CPL;
+      const bool e1 = wrapped(o1[i], v1[j]), e2 = wrapped(o2[i], v2[j]);
+      const bool ev = WEIGHTED ? o0[WEIGHTED ? i : 0] > ~(unsigned)w[j] : false;
+      if (ev | e1 | e2) {
+        const int b = (int)((pa[i] - hb) / 384u) - k * a.nb1;
+        eng_carry(a.acc, a.descs, node, a.cols, col_lane + k, a.nb1, b, ev ? 1 : 0, e1 ? (v1[j] < 0 ? -1 : 1) : 0,
+                  e2 ? (v2[j] < 0 ? -1 : 1) : 0);
+      }
+    }
   }
 }
 
 template <int CPL>
-struct EngBatch {
-  static constexpr int value = CPL == 1 ? 6 : (CPL == 2 ? 4 : 2);  // rows a warp keeps in flight
+struct EngCfg {
+  static constexpr int threads = 1024;
+  static constexpr int U = 8 / CPL;  // rows per batch: eight cells per lane in flight
 };
 
+// The wY and wYY words hold the sum of (target - M) for an offset M close to the run's mean target, so that they
+// wander around their 2^31 starting point instead of marching through the 32-bit range (a wrap costs a trip to the
+// global accumulator).  Any M gives exact results: the flush adds count * M back.  Weighted shards keep M = 0 — their
+// count word holds the weight sum, not the number of rows.
+constexpr int kEngMeanSample = 1024;
+
 template <int CPL, bool WEIGHTED>
-__global__ void __launch_bounds__(1024, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
+__global__ void __launch_bounds__(EngCfg<CPL>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
   using V = typename XVec<CPL>::type;
-  constexpr int U = EngBatch<CPL>::value;
+  constexpr int THREADS = EngCfg<CPL>::threads, U = EngCfg<CPL>::U, NW = THREADS / 32;
   extern __shared__ __align__(16) unsigned h[];
   __shared__ unsigned s_mn[CPL * 32], s_mx[CPL * 32];
   __shared__ unsigned char s_tracked[CPL * 32];
+  __shared__ int s_m[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nb1 = a.nb1;
-  const int words = CPL * nb1 * 3 * 32;
+  const int triples = CPL * nb1 * 32;
   const int col_lane = (int)blockIdx.y * 32 * CPL + lane * CPL;
   const int n_nodes = min(a.n_nodes, a.seg[kSegNodes]);  // the table's own count bounds every read of it
   if (n_nodes < 1) return;
@@ -177,14 +222,16 @@ __global__ void __launch_bounds__(1024, 1) eng_hist_kernel(const __grid_constant
   if (p0 >= p1) return;
   int node = seg_of(a.seg, n_nodes, p0);
 
-  for (int i = tid; i < words; i += 1024) h[i] = ((i >> 5) % 3 == 1) ? kWyBias : 0u;
+  for (int i = tid; i < triples * 3; i += THREADS) h[i] = ((i >> 5) % 3 == 0) ? 0u : kWyBias;
 
   unsigned hb = (unsigned)__cvta_generic_to_shared(h) + lane * 4;  // (slot 0, bin 0, channel 0, this lane)
   asm volatile("" : "+r"(hb));  // keep it in a register: recomputing it costs seven instructions per cell
   // lanes past the last column read the row's last CPL floats instead (never accumulated: their columns are untracked)
   const unsigned ldt = (unsigned)a.ldt;
   const float* __restrict__ xrow = a.XT + min(col_lane, (int)ldt - CPL);
-  const int4* __restrict__ grec = a.grec;
+  const int32_t* __restrict__ gidx = a.gidx;
+  const uint2* __restrict__ gval = a.gval;
+  const int32_t* __restrict__ gw = a.gw;
   EngLane<CPL> c;
 
   while (p0 < p1) {
@@ -220,25 +267,59 @@ __global__ void __launch_bounds__(1024, 1) eng_hist_kernel(const __grid_constant
         s_mx[k * 32 + lane] = kEncNegInf;
         s_tracked[k * 32 + lane] = tracked[k] ? 1 : 0;
       }
+      int m1 = 0, m2 = 0;
+      if (!WEIGHTED) {  // centring offsets: the mean targets of the run's first records (>> 10 keeps the sums in 32 bits)
+        const int cnt = min(send - p0, kEngMeanSample);
+        int t1 = 0, t2 = 0;
+        for (int i = lane; i < cnt; i += 32) {
+          const uint2 v = __ldg(gval + p0 + i);
+          t1 += (int)v.x >> 10;
+          t2 += (int)v.y >> 10;
+        }
+        t1 = __reduce_add_sync(0xffffffffu, t1);
+        t2 = __reduce_add_sync(0xffffffffu, t2);
+        m1 = (int)((long long)t1 * 1024 / cnt);
+        m2 = (int)((long long)t2 * 1024 / cnt);
+      }
+      if (lane == 0) {
+        s_m[0] = m1;
+        s_m[1] = m2;
+      }
     }
-    __syncthreads();  // histogram words and range slots are initialised
+    __syncthreads();  // histogram words, range slots and offsets are ready
+    const int m1 = s_m[0], m2 = s_m[1];
 
-    // every warp takes U consecutive records at a time; the 32 warps of the CTA interleave
-    int p = p0 + warp * U;
-    for (; p + U <= send; p += 32 * U) {
-      int4 r[U];
-      V xv[U];
+    // Every warp takes U consecutive records at a time; the warps of the CTA interleave.
+    {
+      constexpr int stride = NW * U;
+      int p = p0 + warp * U;
+      for (; p + U <= send; p += stride) {
+        int idx[U], v1[U], v2[U], w[U];
+        V x[U];
 #pragma unroll
-      for (int j = 0; j < U; j++) r[j] = __ldg(grec + p + j);
+        for (int j = 0; j < U; j++) idx[j] = __ldg(gidx + p + j);
 #pragma unroll
-      for (int j = 0; j < U; j++) xv[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)r[j].x * ldt));
+        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[j] * ldt));
 #pragma unroll
-      for (int j = 0; j < U; j++) eng_row<CPL, WEIGHTED>(c, a, hb, node, col_lane, xv[j], r[j]);
-    }
-    for (; p < send; p++) {  // the run's last, partial batch
-      const int4 r = __ldg(grec + p);
-      const V xv = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)r.x * ldt));
-      eng_row<CPL, WEIGHTED>(c, a, hb, node, col_lane, xv, r);
+        for (int j = 0; j < U; j++) {
+          const uint2 r = __ldg(gval + p + j);
+          v1[j] = (int)r.x - m1;
+          v2[j] = (int)r.y - m2;
+          w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
+        }
+        eng_batch<CPL, WEIGHTED, U>(c, a, hb, node, col_lane, x, v1, v2, w);
+      }
+      for (; p < send; p++) {  // the run's last, partial batch: one row at a time
+        int idx[1], v1[1], v2[1], w[1];
+        V x[1];
+        idx[0] = __ldg(gidx + p);
+        x[0] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[0] * ldt));
+        const uint2 r = __ldg(gval + p);
+        v1[0] = (int)r.x - m1;
+        v2[0] = (int)r.y - m2;
+        w[0] = WEIGHTED ? __ldg(gw + p) : 1;
+        eng_batch<CPL, WEIGHTED, 1>(c, a, hb, node, col_lane, x, v1, v2, w);
+      }
     }
 
     // observed ranges: registers -> shared (integer min / max of the order-preserving encoding) -> global
@@ -256,24 +337,29 @@ __global__ void __launch_bounds__(1024, 1) eng_hist_kernel(const __grid_constant
       if (e0 != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)node * a.cols + col], e0);
       if (e1 != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)node * a.cols + col], e1);
     }
-    // flush the touched words to the 64-bit global accumulators and re-arm them for the next node
-    for (int i = tid; i < words; i += 1024) {
-      const unsigned v = h[i];
-      const int t = i >> 5;
-      const int ch = t % 3;
-      const unsigned init = ch == 1 ? kWyBias : 0u;
-      if (v != init) {
-        const int kb = t / 3;
+    // flush the touched (slot, bin, lane) triples to the 64-bit global accumulators, undo the centring with the
+    // triple's own count, and re-arm the words for the next node
+    for (int t = tid; t < triples; t += THREADS) {
+      const int kb = t >> 5, ln = t & 31;
+      unsigned* w0 = h + (kb * 3) * 32 + ln;
+      const unsigned c0 = w0[0], u1 = w0[32], u2 = w0[64];
+      if (c0 | (u1 ^ kWyBias) | (u2 ^ kWyBias)) {
+        w0[0] = 0u;
+        w0[32] = kWyBias;
+        w0[64] = kWyBias;
         const int k = kb / nb1, b = kb - k * nb1;
-        if (s_tracked[k * 32 + (i & 31)]) {
-          const int col = (int)blockIdx.y * 32 * CPL + (i & 31) * CPL + k;
-          atomicAdd(reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col) * nb1 + b) * 3 + ch,
-                    (unsigned long long)v - (unsigned long long)init);
+        if (s_tracked[k * 32 + ln]) {
+          const int col = (int)blockIdx.y * 32 * CPL + ln * CPL + k;
+          unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col) * nb1 + b) * 3;
+          const long long s1 = (long long)u1 - (long long)kWyBias + (long long)c0 * m1;
+          const long long s2 = (long long)u2 - (long long)kWyBias + (long long)c0 * m2;
+          if (c0) atomicAdd(g, (unsigned long long)c0);
+          if (s1) atomicAdd(g + 1, (unsigned long long)s1);
+          if (s2) atomicAdd(g + 2, (unsigned long long)s2);
         }
-        h[i] = init;
       }
     }
-    __syncthreads();  // s_tracked and the range slots are rewritten at the top of the next run
+    __syncthreads();  // s_tracked, the offsets and the range slots are rewritten at the top of the next run
     p0 = send;
     node++;
   }
@@ -334,7 +420,7 @@ __device__ __forceinline__ TileRange tile_range(const int32_t* __restrict__ seg,
 }
 
 __global__ void __launch_bounds__(256) eng_route_kernel(const float* __restrict__ XT, int64_t ldt,
-                                                        const int4* __restrict__ grec, const int32_t* __restrict__ seg,
+                                                        const int32_t* __restrict__ gidx, const int32_t* __restrict__ seg,
                                                         const int32_t* __restrict__ tile_base, int n_nodes,
                                                         const h2ok_split* __restrict__ splits,
                                                         const int32_t* __restrict__ child_ids, int gid_base,
@@ -358,7 +444,7 @@ __global__ void __launch_bounds__(256) eng_route_kernel(const float* __restrict_
     const int64_t p = tr.start + j * 256 + threadIdx.x;
     int code = 3;
     if (p < tr.end) {
-      const int row = grec[p].x;
+      const int row = gidx[p];
       code = 2;
       if (col < 0) {
         leaf[row] = leaf0;
@@ -438,7 +524,9 @@ __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ ti
   }
 }
 
-__global__ void __launch_bounds__(256) eng_scatter_kernel(const int4* __restrict__ grec, int4* __restrict__ grec_n,
+__global__ void __launch_bounds__(256) eng_scatter_kernel(const int32_t* __restrict__ gidx, const uint2* __restrict__ gval,
+                                                          const int32_t* __restrict__ gw, int32_t* __restrict__ gidx_n,
+                                                          uint2* __restrict__ gval_n, int32_t* __restrict__ gw_n,
                                                           const int32_t* __restrict__ seg,
                                                           const int32_t* __restrict__ tile_base, int n_nodes,
                                                           const uint8_t* __restrict__ codes,
@@ -490,17 +578,21 @@ __global__ void __launch_bounds__(256) eng_scatter_kernel(const int4* __restrict
     const int64_t p = tr.start + j * 256 + threadIdx.x;
     const unsigned b0 = __ballot_sync(0xffffffffu, code[j] == 0), b1 = __ballot_sync(0xffffffffu, code[j] == 1);
     const unsigned pre = s_pre[j * 8 + warp];
-    if (code[j] == 0) grec_n[base0 + (pre & 0xFFFFu) + __popc(b0 & lt)] = grec[p];
-    else if (code[j] == 1) grec_n[base1 + (pre >> 16) + __popc(b1 & lt)] = grec[p];
+    if (code[j] < 2) {
+      const int64_t d = code[j] == 0 ? base0 + (pre & 0xFFFFu) + __popc(b0 & lt) : base1 + (pre >> 16) + __popc(b1 & lt);
+      gidx_n[d] = gidx[p];
+      gval_n[d] = gval[p];
+      if (gw) gw_n[d] = gw[p];
+    }
   }
 }
 
-__global__ void eng_nid_kernel(const int4* __restrict__ grec, const int32_t* __restrict__ seg,
+__global__ void eng_nid_kernel(const int32_t* __restrict__ gidx, const int32_t* __restrict__ seg,
                                int32_t* __restrict__ nid_rows) {
   const int n_nodes = seg[kSegNodes];
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n_nodes < 1 || p >= seg[n_nodes]) return;
-  nid_rows[grec[p].x] = seg_of(seg, n_nodes, p);
+  nid_rows[gidx[p]] = seg_of(seg, n_nodes, p);
 }
 
 }  // namespace
@@ -520,7 +612,9 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   };
   A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   for (int k = 0; k < 2; k++) {
-    A((void**)&e.grec[k], sizeof(int4) * (size_t)rows);
+    A((void**)&e.gidx[k], sizeof(int32_t) * (size_t)rows);
+    A((void**)&e.gval[k], sizeof(uint2) * (size_t)rows);
+    if (weighted) A((void**)&e.gw[k], sizeof(int32_t) * (size_t)rows);
     A((void**)&e.seg[k], sizeof(int32_t) * kSegInts);
   }
   A((void**)&e.codes, (size_t)rows);
@@ -536,10 +630,8 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
 void engine_free(Engine& e) {
   cudaFree(e.XT);
   for (int k = 0; k < 2; k++) {
-    cudaFree(e.grec[k]);
-    cudaFree(e.seg[k]);
-    e.grec[k] = nullptr;
-    e.seg[k] = nullptr;
+    cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]);
+    e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr;
   }
   cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.slot_start); cudaFree(e.leaf);
   e.XT = nullptr;
@@ -560,7 +652,7 @@ cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* 
   e.cur = 0;
   e.n_nodes = 1;
   eng_begin_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.rows, e.weighted ? wq_rows : nullptr, wyq_rows, wyyq_rows,
-                                                     e.grec[0], e.leaf, e.seg[0]);
+                                                     e.gidx[0], e.gval[0], e.gw[0], e.leaf, e.seg[0]);
   return cudaGetLastError();
 }
 
@@ -587,7 +679,7 @@ static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem,
     if (e != cudaSuccess) return e;
     attr = true;
   }
-  eng_hist_kernel<CPL, W><<<grid, 1024, smem, s>>>(a);
+  eng_hist_kernel<CPL, W><<<grid, EngCfg<CPL>::threads, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -601,7 +693,9 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   a.XT = e.XT;
   a.ldt = e.ldt;
   a.cols = e.cols;
-  a.grec = e.grec[e.cur];
+  a.gidx = e.gidx[e.cur];
+  a.gval = e.gval[e.cur];
+  a.gw = e.gw[e.cur];
   a.seg = e.seg[e.cur];
   a.n_nodes = n_nodes;
   a.descs = descs;
@@ -629,11 +723,11 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   const int nx = 1 - e.cur;
   const unsigned tiles = (unsigned)(e.rows / kEngTile + n_nodes + 1);  // bound: the live count stays on the device
   eng_tiles_kernel<<<1, 1024, 0, s>>>(e.seg[e.cur], n_nodes, e.tile_base);
-  eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.grec[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
+  eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.gidx[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
                                          gid_base, e.codes, e.leaf, e.tile_cnt);
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx]);
-  eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.grec[e.cur], e.grec[nx], e.seg[e.cur], e.tile_base, n_nodes, e.codes,
-                                           e.tile_cnt, e.slot_start);
+  eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.gidx[e.cur], e.gval[e.cur], e.gw[e.cur], e.gidx[nx], e.gval[nx], e.gw[nx],
+                                           e.seg[e.cur], e.tile_base, n_nodes, e.codes, e.tile_cnt, e.slot_start);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return err;
   e.cur = nx;
@@ -644,7 +738,7 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
 cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s) {
   cudaError_t err = cudaMemsetAsync(nid_rows, 0xFF, sizeof(int32_t) * (size_t)e.rows, s);
   if (err != cudaSuccess) return err;
-  eng_nid_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.grec[e.cur], e.seg[e.cur], nid_rows);
+  eng_nid_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.gidx[e.cur], e.seg[e.cur], nid_rows);
   return cudaGetLastError();
 }
 
