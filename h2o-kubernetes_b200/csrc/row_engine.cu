@@ -138,7 +138,7 @@ __device__ __forceinline__ bool wrapped(unsigned old, int v) { return (old > ~(u
 // turned into NaNs that add zeros: the NA bin gets +0 and the running extremes ignore NaN — which is what skipping
 // the row means.  v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
 template <int CPL, bool WEIGHTED, int U>
-__device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a, unsigned hb, int node, int col_lane,
+__device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a, const unsigned (&hb)[CPL], int node, int col_lane,
                                           const typename XVec<CPL>::type (&xv)[U], const int (&v1)[U], const int (&v2)[U],
                                           const int (&w)[U]) {
   unsigned pa[U * CPL], o1[U * CPL], o2[U * CPL], o0[WEIGHTED ? U * CPL : 1];
@@ -151,7 +151,7 @@ __device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a,
       const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
       c.fmn[k] = fminf(c.fmn[k], x);  // NaN-ignoring and exact
       c.fmx[k] = fmaxf(c.fmx[k], x);
-      pa[j * CPL + k] = hb + (unsigned)(k * a.nb1 + b) * 384u;
+      pa[j * CPL + k] = hb[k] + (unsigned)b * 384u;
     }
   }
 #pragma unroll
@@ -182,7 +182,7 @@ __device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a,
       const bool e1 = wrapped(o1[i], v1[j]), e2 = wrapped(o2[i], v2[j]);
       const bool ev = WEIGHTED ? o0[WEIGHTED ? i : 0] > ~(unsigned)w[j] : false;
       if (ev | e1 | e2) {
-        const int b = (int)((pa[i] - hb) / 384u) - k * a.nb1;
+        const int b = (int)((pa[i] - hb[k]) / 384u);
         eng_carry(a.acc, a.descs, node, a.cols, col_lane + k, a.nb1, b, ev ? 1 : 0, e1 ? (v1[j] < 0 ? -1 : 1) : 0,
                   e2 ? (v2[j] < 0 ? -1 : 1) : 0);
       }
@@ -190,10 +190,13 @@ __device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a,
   }
 }
 
-template <int CPL>
+// 1024 threads leave 64 registers per thread, and a single spilled register in the row loop costs ~30% (with 227 KB
+// of shared memory carved out, local memory has almost no L1 behind it): rows per batch are chosen so that every
+// instantiation compiles without spills — eight cells per lane in flight, four where the weights need registers too.
+template <int CPL, bool WEIGHTED>
 struct EngCfg {
   static constexpr int threads = 1024;
-  static constexpr int U = 8 / CPL;  // rows per batch: eight cells per lane in flight
+  static constexpr int U = (WEIGHTED || CPL == 4) ? (CPL == 4 ? 1 : 4 / CPL) : 8 / CPL;
 };
 
 // The wY and wYY words hold the sum of (target - M) for an offset M close to the run's mean target, so that they
@@ -203,9 +206,9 @@ struct EngCfg {
 constexpr int kEngMeanSample = 1024;
 
 template <int CPL, bool WEIGHTED>
-__global__ void __launch_bounds__(EngCfg<CPL>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
+__global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
   using V = typename XVec<CPL>::type;
-  constexpr int THREADS = EngCfg<CPL>::threads, U = EngCfg<CPL>::U, NW = THREADS / 32;
+  constexpr int THREADS = EngCfg<CPL, WEIGHTED>::threads, U = EngCfg<CPL, WEIGHTED>::U, NW = THREADS / 32;
   extern __shared__ __align__(16) unsigned h[];
   __shared__ unsigned s_mn[CPL * 32], s_mx[CPL * 32];
   __shared__ unsigned char s_tracked[CPL * 32];
@@ -224,11 +227,15 @@ __global__ void __launch_bounds__(EngCfg<CPL>::threads, 1) eng_hist_kernel(const
 
   for (int i = tid; i < triples * 3; i += THREADS) h[i] = ((i >> 5) % 3 == 0) ? 0u : kWyBias;
 
-  unsigned hb = (unsigned)__cvta_generic_to_shared(h) + lane * 4;  // (slot 0, bin 0, channel 0, this lane)
-  asm volatile("" : "+r"(hb));  // keep it in a register: recomputing it costs seven instructions per cell
+  unsigned hb[CPL];  // shared address of (slot k, bin 0, channel 0, this lane)
+#pragma unroll
+  for (int k = 0; k < CPL; k++) {
+    hb[k] = (unsigned)__cvta_generic_to_shared(h) + lane * 4 + (unsigned)(k * nb1) * 384u;
+    asm volatile("" : "+r"(hb[k]));  // keep it in a register: recomputing it costs seven instructions per cell
+  }
   // lanes past the last column read the row's last CPL floats instead (never accumulated: their columns are untracked)
-  const unsigned ldt = (unsigned)a.ldt;
-  const float* __restrict__ xrow = a.XT + min(col_lane, (int)ldt - CPL);
+  const unsigned ldt4 = (unsigned)a.ldt * 4u;  // row pitch in bytes: one IMAD.WIDE per row address
+  const char* __restrict__ xrow = reinterpret_cast<const char*>(a.XT + min(col_lane, (int)a.ldt - CPL));
   const int32_t* __restrict__ gidx = a.gidx;
   const uint2* __restrict__ gval = a.gval;
   const int32_t* __restrict__ gw = a.gw;
@@ -299,7 +306,7 @@ __global__ void __launch_bounds__(EngCfg<CPL>::threads, 1) eng_hist_kernel(const
 #pragma unroll
         for (int j = 0; j < U; j++) idx[j] = __ldg(gidx + p + j);
 #pragma unroll
-        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[j] * ldt));
+        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[j] * ldt4));
 #pragma unroll
         for (int j = 0; j < U; j++) {
           const uint2 r = __ldg(gval + p + j);
@@ -313,7 +320,7 @@ __global__ void __launch_bounds__(EngCfg<CPL>::threads, 1) eng_hist_kernel(const
         int idx[1], v1[1], v2[1], w[1];
         V x[1];
         idx[0] = __ldg(gidx + p);
-        x[0] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[0] * ldt));
+        x[0] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[0] * ldt4));
         const uint2 r = __ldg(gval + p);
         v1[0] = (int)r.x - m1;
         v2[0] = (int)r.y - m2;
@@ -679,7 +686,7 @@ static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem,
     if (e != cudaSuccess) return e;
     attr = true;
   }
-  eng_hist_kernel<CPL, W><<<grid, EngCfg<CPL>::threads, smem, s>>>(a);
+  eng_hist_kernel<CPL, W><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
   return cudaGetLastError();
 }
 
