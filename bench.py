@@ -47,10 +47,10 @@ def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False):
     return rows * cols * 4.0 + rows * (4.0 + 4.0 + (4.0 if weighted else 0.0)) + n_nodes * cols * (bins + 1) * 3 * 8.0
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per hist_build launch, from the committed `ncu --set full` capture
-# (profiles/r01_hist_build_ncu_full.csv: 26.5-27.6 GB read + 0.01-0.3 GB written per launch at 100M x 64); scaled
-# linearly to the rows/cols of the run.  None for shapes that were not profiled.
-NCU_TRAFFIC_BYTES_PER_CELL = 27.15e9 / (100_000_000 * 64)
+# dram__bytes_read.sum + dram__bytes_write.sum per histogram launch, from the committed `ncu --set full` captures at
+# 100M x 64 (profiles/r01_eng_hist_ncu_full.csv: 27.1 GB read + 0.13 GB written; profiles/r01_hist_build_ncu_full.csv:
+# 26.5-27.6 GB read + 0.01-0.3 GB written); scaled linearly to the rows of the run.  None for shapes not profiled.
+NCU_TRAFFIC_BYTES_PER_CELL = {"engine": 27.24e9 / (100_000_000 * 64), "stateless": 27.15e9 / (100_000_000 * 64)}
 
 
 def measured_hbm_peak():
@@ -287,8 +287,8 @@ def run_gpu(args, wl):
                        "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
                        "per_level": level_table},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": (NCU_TRAFFIC_BYTES_PER_CELL * rows * cols / 1e9 if args.path == "stateless" and args.workload == "c3" else None),
-                         "traffic_unit": "GB per launch (ncu dram read+write, profiles/r01_hist_build_ncu_full.csv)", "kernel": "eng_hist_kernel" if args.path == "engine" else "hist_build_kernel",
+                         "traffic": (NCU_TRAFFIC_BYTES_PER_CELL[args.path] * rows * cols / 1e9 if args.workload == "c3" else None),
+                         "traffic_unit": "GB per launch (ncu dram read+write, profiles/r01_%s_ncu_full.csv)" % ("eng_hist" if args.path == "engine" else "hist_build"), "kernel": "eng_hist_kernel" if args.path == "engine" else "hist_build_kernel",
                          "peak_source": peak_src,
                          "note": "algorithmic bytes of the timed levels / CUDA-event time of their hist_build launches"},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
@@ -314,18 +314,16 @@ def run_e2e(args, wl, shard, drv, world, rank, rows_total, rows, barrier):
     max_nodes = shard.acc.shape[0]
     y_host = shard.y[:rows].cpu().pin_memory()
     # one-time upload of X through the host path (measured on a slice, scaled is NOT reported: we report the slice)
-    t0 = time.perf_counter()
     slice_cols = min(cols, 4)
-    xs = shard.X[:slice_cols, :rows].cpu()
-    d2h_s = time.perf_counter() - t0
-    xs = xs.pin_memory()
+    xs = torch.empty((slice_cols, rows), dtype=torch.float32).pin_memory()
+    xd = torch.empty((slice_cols, rows), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    shard.X[:slice_cols, :rows].copy_(xs, non_blocking=True)
+    xd.copy_(xs, non_blocking=True)
     torch.cuda.synchronize()
     h2d_s = time.perf_counter() - t0
     upload_gbs = slice_cols * rows * 4 / h2d_s / 1e9
-    del xs
+    del xs, xd
     host = dict(hist=torch.empty((max_nodes, cols, nb1, 3), dtype=torch.float64).pin_memory(),
                 min2=torch.empty((max_nodes, cols), dtype=torch.float32).pin_memory(),
                 maxin=torch.empty((max_nodes, cols), dtype=torch.float32).pin_memory(),
@@ -379,7 +377,7 @@ def run_e2e(args, wl, shard, drv, world, rank, rows_total, rows, barrier):
             "path": "LevelDriver: y from pinned host memory per tree; hist/ranges/splits/child ids to pinned host buffers per level",
             "x_upload": {"note": "one-time, outside the timed region (X is resident across levels like H2O's DKV chunks)",
                          "measured_h2d_gbs": upload_gbs, "full_x_bytes_per_gpu": rows * cols * 4,
-                         "est_ms": rows * cols * 4 / upload_gbs / 1e6, "slice_d2h_s": d2h_s}}
+                         "est_ms": rows * cols * 4 / upload_gbs / 1e6}}
 
 
 def run_e2e_cabi(args, wl, shard, params):
@@ -396,14 +394,28 @@ def run_e2e_cabi(args, wl, shard, params):
     nb1 = bins + 1
     max_nodes = 2 ** (depth - 1)
     t0 = time.perf_counter()
-    Xh = torch.empty((cols, rows), dtype=torch.float32)
-    for c in range(cols):
-        Xh[c].copy_(shard.X[c, :rows])
     yh = shard.y[:rows].cpu().pin_memory()
-    prep_s = time.perf_counter() - t0
-    # free the resident shard's big buffers: the library owns its own copy from here on
-    shard.X = shard.nid = shard.leaf = shard.wyq = shard.wyyq = None
+    # free the resident shard: the host-buffer context owns its own copy of the data from here on
+    if args.path == "engine":
+        shard.lib.call("h2ok_hist_tree_destroy", shard.ctx)
+        shard._nid = shard._leaf = None
+    else:
+        shard.X = shard.nid = shard.leaf = None
+    shard.wyq = shard.wyyq = None
     torch.cuda.empty_cache()
+    # the caller's data: column vectors in pageable host memory (generated block-wise on the device, copied out)
+    Xh = torch.empty((cols, rows), dtype=torch.float32)
+    ld = (rows + 63) // 64 * 64
+    blk = max(1, min(cols, (1 << 30) // (4 * ld)))
+    stage = torch.empty((blk, ld), dtype=torch.float32, device="cuda")
+    for c0 in range(0, cols, blk):
+        nc = min(blk, cols - c0)
+        shard.lib.call("h2ok_hist_synth_fill_cols_dev", shard.ctx, wl["shape"], SEED, 0, rows, c0, nc, ld, 0,
+                       C.c_void_p(stage.data_ptr()))
+        Xh[c0:c0 + nc].copy_(stage[:nc, :rows])
+    del stage
+    torch.cuda.empty_cache()
+    prep_s = time.perf_counter() - t0
     h = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(h))
     colptrs = (C.c_void_p * cols)(*[Xh[c].data_ptr() for c in range(cols)])
@@ -471,9 +483,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the workload's row count (debug only)")
-    ap.add_argument("--path", default="stateless", choices=["engine", "stateless"],
-                    help="stateless (default): per-call kernels on rows in place; engine: resident node-grouped tree engine "
-                         "(flat cost per level whatever the depth, twice the device memory)")
+    ap.add_argument("--path", default="engine", choices=["engine", "stateless"],
+                    help="engine (default): resident row-wise tree engine, flat cost per level whatever the depth; "
+                         "stateless: per-call kernels on column-major rows in place")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")
     args = ap.parse_args()

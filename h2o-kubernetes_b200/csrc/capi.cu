@@ -468,23 +468,36 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* c, const float* d_X, int64_t ld, in
 }
 
 // ---------------------------------------------------------------------------------------- host-buffer API
+// The host-buffer entry points run on the resident tree engine (row_engine.cu): the columns pass through a small
+// staging buffer into the engine's row-major copy, so the context holds the data once.
 int32_t h2ok_hist_set_data_host(h2ok_ctx* c, const float* const* cols_host, int64_t rows, int32_t cols) {
   REQUIRE(c && cols_host, "null pointer");
   REQUIRE(rows > 0 && cols > 0, "empty data");
+  for (int32_t j = 0; j < cols; j++) REQUIRE(cols_host[j] != nullptr, "null column");
   CK(cudaSetDevice(c->device));
-  int64_t ld = (rows + 63) / 64 * 64;
-  CK(c->X.ensure((size_t)ld * cols));
-  for (int32_t j = 0; j < cols; j++) {
-    REQUIRE(cols_host[j] != nullptr, "null column");
-    CK(cudaMemcpyAsync(c->X.p + (int64_t)j * ld, cols_host[j], sizeof(float) * (size_t)rows, cudaMemcpyHostToDevice, c->stream));
-    if (ld > rows) CK(cudaMemsetAsync(c->X.p + (int64_t)j * ld + rows, 0, sizeof(float) * (size_t)(ld - rows), c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->have_data = c->have_targets = c->eng_ready = false;
+  CK(engine_alloc(c->eng, rows, cols, false));
+  c->eng_ready = true;
+  const int64_t ld = (rows + 63) / 64 * 64;
+  int64_t per = ((int64_t)256 << 20) / (4 * ld);  // columns per staging block (<= 256 MB)
+  per = per < 1 ? 1 : (per > cols ? cols : per);
+  CK(c->X.ensure((size_t)ld * per));
+  CK(c->cmin.ensure(cols)); CK(c->cmax.ensure(cols));
+  for (int32_t c0 = 0; c0 < cols; c0 += (int32_t)per) {
+    const int32_t nc = cols - c0 < per ? cols - c0 : (int32_t)per;
+    for (int32_t j = 0; j < nc; j++)
+      CK(cudaMemcpyAsync(c->X.p + (int64_t)j * ld, cols_host[c0 + j], sizeof(float) * (size_t)rows, cudaMemcpyHostToDevice,
+                         c->stream));
+    CK(launch_col_ranges(c->X.p, ld, rows, nc, c->cmin.p + c0, c->cmax.p + c0, c->stream));
+    CK(engine_load_cols(c->eng, c0, nc, c->X.p, ld, c->stream));
   }
   CK(cudaStreamSynchronize(c->stream));
+  c->X.release();
   c->rows = rows;
   c->ld = ld;
   c->cols = cols;
   c->have_data = true;
-  c->have_targets = false;
   c->level_built = c->splits_found = c->children_made = false;
   return H2OK_OK;
 }
@@ -495,10 +508,11 @@ int32_t h2ok_hist_set_targets_host(h2ok_ctx* c, const float* y_host, const float
   CK(cudaSetDevice(c->device));
   const int64_t n = c->rows;
   const size_t pad = (size_t)(n + 3) / 4 * 4;
-  CK(c->y.ensure(pad)); CK(c->nid.ensure(pad)); CK(c->leaf.ensure(pad)); CK(c->wyq.ensure(pad)); CK(c->wyyq.ensure(pad));
+  CK(c->y.ensure(pad)); CK(c->wyq.ensure(pad)); CK(c->wyyq.ensure(pad));
   CK(c->absmax.ensure(3));
   c->weighted = w_host != nullptr;
   if (c->weighted) { CK(c->w.ensure(pad)); CK(c->wq.ensure(pad)); }
+  CK(engine_set_weighted(c->eng, c->weighted));
   CK(cudaMemcpyAsync(c->y.p, y_host, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
   if (c->weighted) CK(cudaMemcpyAsync(c->w.p, w_host, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
   CK(launch_target_absmax(c->y.p, c->weighted ? c->w.p : nullptr, n, c->absmax.p, c->stream));
@@ -508,8 +522,7 @@ int32_t h2ok_hist_set_targets_host(h2ok_ctx* c, const float* y_host, const float
   h2ok_hist_choose_quant(m, c->weighted ? 1 : 0, 25, &c->q);
   CK(launch_quantize_rows(c->y.p, c->weighted ? c->w.p : nullptr, n, c->q, c->weighted ? c->wq.p : nullptr, c->wyq.p,
                           c->wyyq.p, c->stream));
-  CK(cudaMemsetAsync(c->nid.p, 0, sizeof(int32_t) * (size_t)n, c->stream));
-  CK(cudaMemsetAsync(c->leaf.p, 0xFF, sizeof(int32_t) * (size_t)n, c->stream));
+  CK(engine_begin_tree(c->eng, c->weighted ? c->wq.p : nullptr, c->wyq.p, c->wyyq.p, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   c->gid_base = 0;
   c->have_targets = true;
@@ -548,9 +561,7 @@ int32_t h2ok_hist_root_descs(h2ok_ctx* c, const h2ok_params* params, const int32
   REQUIRE(c && params && descs_out, "null pointer");
   if (!c->have_data) return fail(H2OK_ERR_STATE, "%s", "root_descs before set_data_host");
   CK(cudaSetDevice(c->device));
-  CK(c->cmin.ensure(c->cols)); CK(c->cmax.ensure(c->cols));
-  CK(launch_col_ranges(c->X.p, c->ld, c->rows, c->cols, c->cmin.p, c->cmax.p, c->stream));
-  std::vector<uint32_t> mn(c->cols), mx(c->cols);
+  std::vector<uint32_t> mn(c->cols), mx(c->cols);  // the column ranges were taken while the data went through staging
   CK(cudaMemcpyAsync(mn.data(), c->cmin.p, sizeof(uint32_t) * c->cols, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(mx.data(), c->cmax.p, sizeof(uint32_t) * c->cols, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
@@ -575,8 +586,7 @@ int32_t h2ok_hist_build_level(h2ok_ctx* c, int32_t n_nodes, const h2ok_col_desc*
   CK(c->descs.ensure(ncell)); CK(c->acc.ensure(ncell * nb1 * 3)); CK(c->hist.ensure(ncell * nb1 * 3));
   CK(c->mn.ensure(ncell)); CK(c->mx.ensure(ncell)); CK(c->min2.ensure(ncell)); CK(c->maxin.ensure(ncell));
   CK(cudaMemcpyAsync(c->descs.p, descs, sizeof(h2ok_col_desc) * ncell, cudaMemcpyHostToDevice, c->stream));
-  rc = h2ok_hist_build_level_dev(c, c->X.p, c->ld, c->rows, c->cols, c->nid.p, c->weighted ? c->wq.p : nullptr, c->wyq.p,
-                                 c->wyyq.p, n_nodes, c->descs.p, max_bins, 1, c->acc.p, c->mn.p, c->mx.p);
+  rc = h2ok_hist_tree_build_level_dev(c, n_nodes, c->descs.p, max_bins, 1, c->acc.p, c->mn.p, c->mx.p);
   if (rc) return rc;
   rc = h2ok_hist_finalize_level_dev(c, c->acc.p, c->mn.p, c->mx.p, n_nodes, c->cols, max_bins, &c->q, c->hist.p,
                                     c->min2.p, c->maxin.p);
@@ -637,8 +647,7 @@ int32_t h2ok_hist_apply_splits(h2ok_ctx* c) {
     CK(c->child_ids.ensure((size_t)2 * c->n_nodes));
     CK(cudaMemsetAsync(c->child_ids.p, 0xFF, sizeof(int32_t) * 2 * (size_t)c->n_nodes, c->stream));
   }
-  int32_t rc = h2ok_hist_apply_splits_dev(c, c->X.p, c->ld, c->rows, c->splits.p, c->child_ids.p, c->gid_base, c->n_nodes,
-                                          c->nid.p, c->leaf.p);
+  int32_t rc = h2ok_hist_tree_apply_splits_dev(c, c->splits.p, c->child_ids.p, c->gid_base, c->n_nodes, 0);
   if (rc) return rc;
   CK(cudaStreamSynchronize(c->stream));
   c->gid_base += c->n_nodes;
@@ -650,8 +659,12 @@ int32_t h2ok_hist_get_nid_host(h2ok_ctx* c, int32_t* nid_out, int32_t* leaf_out)
   REQUIRE(c != nullptr, "null context");
   if (!c->have_targets) return fail(H2OK_ERR_STATE, "%s", "get_nid_host before set_targets_host");
   CK(cudaSetDevice(c->device));
-  if (nid_out) CK(cudaMemcpyAsync(nid_out, c->nid.p, sizeof(int32_t) * (size_t)c->rows, cudaMemcpyDeviceToHost, c->stream));
-  if (leaf_out) CK(cudaMemcpyAsync(leaf_out, c->leaf.p, sizeof(int32_t) * (size_t)c->rows, cudaMemcpyDeviceToHost, c->stream));
+  if (nid_out) {
+    CK(c->nid.ensure((size_t)c->rows));
+    CK(engine_nid(c->eng, c->nid.p, c->stream));
+    CK(cudaMemcpyAsync(nid_out, c->nid.p, sizeof(int32_t) * (size_t)c->rows, cudaMemcpyDeviceToHost, c->stream));
+  }
+  if (leaf_out) CK(cudaMemcpyAsync(leaf_out, c->eng.leaf, sizeof(int32_t) * (size_t)c->rows, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   return H2OK_OK;
 }

@@ -50,6 +50,8 @@ struct Engine {
 
 cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted);
 void engine_free(Engine& e);
+// switch the shard between unweighted and weighted trees (allocates the weight arrays the first time)
+cudaError_t engine_set_weighted(Engine& e, bool weighted);
 // copy columns [col0, col0 + ncols) of a column-major block (leading dimension ld) into the row-major copy
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s);
 // new tree: every row at the root, records in row order

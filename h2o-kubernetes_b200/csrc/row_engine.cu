@@ -648,6 +648,19 @@ void engine_free(Engine& e) {
   e.n_nodes = 0;
 }
 
+cudaError_t engine_set_weighted(Engine& e, bool weighted) {
+  if (weighted) {
+    for (int k = 0; k < 2; k++) {
+      if (!e.gw[k]) {
+        cudaError_t err = cudaMalloc((void**)&e.gw[k], sizeof(int32_t) * (size_t)e.rows);
+        if (err != cudaSuccess) return err;
+      }
+    }
+  }
+  e.weighted = weighted;
+  return cudaSuccess;
+}
+
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s) {
   dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
   eng_load_kernel<<<grid, 256, 0, s>>>(X, ld, e.rows, col0, ncols, e.XT, e.ldt);
@@ -659,7 +672,7 @@ cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* 
   e.cur = 0;
   e.n_nodes = 1;
   eng_begin_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.rows, e.weighted ? wq_rows : nullptr, wyq_rows, wyyq_rows,
-                                                     e.gidx[0], e.gval[0], e.gw[0], e.leaf, e.seg[0]);
+                                                     e.gidx[0], e.gval[0], e.weighted ? e.gw[0] : nullptr, e.leaf, e.seg[0]);
   return cudaGetLastError();
 }
 
@@ -702,7 +715,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   a.cols = e.cols;
   a.gidx = e.gidx[e.cur];
   a.gval = e.gval[e.cur];
-  a.gw = e.gw[e.cur];
+  a.gw = e.weighted ? e.gw[e.cur] : nullptr;
   a.seg = e.seg[e.cur];
   a.n_nodes = n_nodes;
   a.descs = descs;
@@ -733,7 +746,8 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.gidx[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
                                          gid_base, e.codes, e.leaf, e.tile_cnt);
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx]);
-  eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.gidx[e.cur], e.gval[e.cur], e.gw[e.cur], e.gidx[nx], e.gval[nx], e.gw[nx],
+  eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.gidx[e.cur], e.gval[e.cur], e.weighted ? e.gw[e.cur] : nullptr, e.gidx[nx],
+                                           e.gval[nx], e.weighted ? e.gw[nx] : nullptr,
                                            e.seg[e.cur], e.tile_base, n_nodes, e.codes, e.tile_cnt, e.slot_start);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return err;
