@@ -393,7 +393,7 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
   int32_t rc = check_level_shape(n_nodes, c->eng.cols, max_bins);
   if (rc) return rc;
   if (max_bins + 1 > engine_max_nb1(c->eng.cols))
-    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: 32 columns x (max_bins+1) bins must fit 226 KB (max_bins <= 601)");
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: 32 columns x (max_bins+1) bins must fit 225 KB (max_bins <= 599)");
   const int nb1 = max_bins + 1;
   const int64_t ncell = (int64_t)n_nodes * c->eng.cols;
   if (clear) {

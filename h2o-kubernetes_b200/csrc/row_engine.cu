@@ -20,7 +20,7 @@ namespace {
 
 inline unsigned nblk(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
 
-constexpr int kHistSmemCap = 227 * 1024 - 1024;  // dynamic shared memory left beside the kernel's static arrays
+constexpr int kHistSmemCap = 227 * 1024 - 2048;  // dynamic shared memory left beside the kernel's static arrays (<= 1.2 KB)
 constexpr int kSegNodes = kEngMaxNodes + 1;       // seg[kSegNodes] = number of nodes the table describes
 constexpr int kSegInts = kEngMaxNodes + 2;
 

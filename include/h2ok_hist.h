@@ -217,7 +217,8 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
  * Call order: tree_create -> tree_load_cols_dev for every block of columns (in any order; the caller's column-major
  * block can be freed or reused afterwards) -> per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce /
  * finalize / find_splits / next_level as usual], tree_apply_splits_dev.  Device memory: rows * (4 * cols rounded up
- * to 8 + 41) bytes.  Limits: rows < 2^31 - 2048; (max_bins + 1) <= 602 (one 32-column block must fit 226 KB). */
+ * to 8 + 29) bytes, + 8 per row for weighted shards.  Limits: rows < 2^31 - 2048; (max_bins + 1) <= 600 (one
+ * 32-column block of the shared histogram must fit 225 KB). */
 int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
 /* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in

@@ -23,7 +23,7 @@ ap.add_argument("--cols", type=int, default=100)
 ap.add_argument("--trees", type=int, default=100)
 ap.add_argument("--depth", type=int, default=5)  # H2O's GBM default
 ap.add_argument("--bins", type=int, default=256)
-ap.add_argument("--path", default="stateless", choices=["stateless", "engine"])
+ap.add_argument("--path", default="engine", choices=["stateless", "engine"])
 a = ap.parse_args()
 world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -34,8 +34,18 @@ rows = a.rows * (rank + 1) // world - row0
 shard = (EngineShard if a.path == "engine" else CudaShard)(local)
 shard.set_data_synth(abi.SHAPE_WIDE64, 20261106, row0, rows, a.cols)
 # label = 1 if x0 + x2*x5 - x9 > tau; tau = the expression's median on a sample, so classes balance
-X = shard.X
-expr = X[0, :rows] + X[2, :rows] * X[5, :rows] - X[9, :rows]
+import ctypes as C  # noqa: E402
+
+
+def column(c):
+    """Column c of this rank's rows, from the same counter-based generator that filled the shard."""
+    t = torch.empty(shard.ld, dtype=torch.float32, device="cuda")
+    shard.lib.call("h2ok_hist_synth_fill_cols_dev", shard.ctx, abi.SHAPE_WIDE64, 20261106, row0, rows, c, 1, shard.ld, 0,
+                   C.c_void_p(t.data_ptr()))
+    return t[:rows]
+
+
+expr = column(0) + column(2) * column(5) - column(9)
 tau = expr[: min(rows, 1_000_000)].median()
 label = (expr > tau).float()
 del expr

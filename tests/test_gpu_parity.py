@@ -554,6 +554,17 @@ def test_engine_ragged_sizes_and_deep_trees(eshard, oracle, rows, cols, depth, m
         assert levels == 10 and st["gid"] > 300  # hundreds of nodes over the ten levels
 
 
+@pytest.mark.parametrize("cols,nbins,weight_mode", [(130, 32, 0), (130, 32, 1), (70, 256, 0), (33, 300, 1), (3, 500, 0)])
+def test_engine_column_blocks(eshard, oracle, cols, nbins, weight_mode):
+    """Every lane / column-block layout of the engine's histogram kernel: four, two and one column per lane, a last
+    block that is only partly filled, and column counts that are not a multiple of the row pitch."""
+    rows = 20011
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 77 + cols, 0, rows, cols, na_permille=15, weight_mode=weight_mode)
+    params = abi.Params.make(nbins=nbins, max_depth=4, min_rows=3)
+    levels, _ = run_tree_both(eshard, oracle, X, rows, y, w, params)
+    assert levels == 4
+
+
 def test_engine_rejects_what_it_cannot_hold(lib):
     h = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(h))
@@ -563,7 +574,7 @@ def test_engine_rejects_what_it_cannot_hold(lib):
             lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 256, 1, P(buf), P(buf), P(buf))
         assert e.value.code == abi.ERR_STATE
         lib.call("h2ok_hist_tree_create", h, 1000, 2, 0)
-        with pytest.raises(capi.H2okError) as e:  # 32 columns x 1025 bins x 12 B do not fit 226 KB
+        with pytest.raises(capi.H2okError) as e:  # 32 columns x 1025 bins x 12 B do not fit 225 KB
             lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 1024, 1, P(buf), P(buf), P(buf))
         assert e.value.code == abi.ERR_UNSUPPORTED and "max_bins" in str(e.value)
         with pytest.raises(capi.H2okError) as e:  # a column block outside the shard
