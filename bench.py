@@ -113,6 +113,15 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU arms
+def host_threads():
+    """Host cores this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1, so the OpenMP default is not
+    the answer under torchrun; the oracle takes the thread count as an argument (num_threads clause)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_levels(oracle, wl, sample_rows, threads, max_seconds, levels=None):
     """The oracle's own level loop (fp64, column-parallel like H2O's LocalMR) on the first `sample_rows` rows of the
     workload.  Returns per-level seconds of build_level + find_splits + next_level + apply_splits."""
@@ -153,7 +162,7 @@ def run_reference(args, wl):
     import oracle_lib
 
     oracle = oracle_lib.load()
-    threads = oracle.max_threads()
+    threads = host_threads()
     rows = min(CPU_SAMPLE_ROWS, wl["rows"])
     # every "step" is one level of a depth-`depth` tree over the sample; warm-up levels come first
     need = args.steps + args.warmup
@@ -271,7 +280,7 @@ def run_gpu(args, wl):
         import oracle_lib
 
         oracle = oracle_lib.load()
-        threads = oracle.max_threads()
+        threads = host_threads()
         srows = min(CPU_SAMPLE_ROWS, rows_total)
         t, nodes = cpu_levels(oracle, wl, srows, threads, max_seconds=40)
         cpu = {"value": srows * cols * len(t) / float(np.sum(t)), "unit": UNIT, "cores": threads, "kind": "port",
