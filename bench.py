@@ -113,6 +113,9 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU arms
+_REAL_STDOUT = 1
+
+
 def host_threads():
     """Host cores this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1, so the OpenMP default is not
     the answer under torchrun; the oracle takes the thread count as an argument (num_threads clause)."""
@@ -194,6 +197,12 @@ def run_gpu(args, wl):
 
     from h2ok_hist import abi, capi
     from h2ok_hist.driver import CudaShard, EngineShard, LevelDriver
+
+    # libraries (NCCL's version banner, for one) may write to stdout: everything but the final line goes to stderr
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -287,6 +296,8 @@ def run_gpu(args, wl):
                "sample": f"{len(t)} levels of a depth-{depth} tree on the first {srows} rows x {cols} cols (slice, not extrapolated)"}
 
     if rank == 0:
+        sys.stdout.flush()
+        os.dup2(_REAL_STDOUT, 1)  # the JSON line is the only thing this process writes to its real stdout
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

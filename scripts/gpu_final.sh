@@ -7,6 +7,6 @@ timeout 900 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_ful
 CMD="python bench.py --steps 8 --warmup 8 --no-cpu --no-e2e"
 $CMD > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
   --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
-$CMD > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:hist_build -s 9 -c 9 \
+$CMD > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:eng_hist -s 8 -c 8 \
   -o gpurun_out/prof_final $CMD > gpurun_out/ncu_full.log 2>&1
 tail -1 gpurun_out/ncu_full.log | cut -c1-100
