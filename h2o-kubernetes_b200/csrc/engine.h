@@ -42,6 +42,7 @@ struct Engine {
   int n_nodes = 0;                      // nodes of the current level (0: no tree in progress)
   uint8_t* codes = nullptr;             // [rows] way of every record: 0 / 1 = live child, 2 = into a leaf
   int32_t* tile_base = nullptr;         // [kEngMaxNodes + 1] first tile of every node
+  int32_t* tile_order = nullptr;        // [max_tiles + 1] tiles in the order routing visits them
   int32_t* tile_cnt = nullptr;          // [max_tiles + 1][2] records of each tile going left / right (then scanned)
   int32_t* slot_start = nullptr;        // [2 * kEngMaxNodes] first record of child slot 2 * node + way in the next order
   int32_t* leaf = nullptr;              // [rows] leaf code of every row (original order), -1 while still in the tree

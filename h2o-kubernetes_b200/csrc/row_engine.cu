@@ -7,6 +7,7 @@
 //                        warp takes whole rows, lane L owns CPL adjacent columns; descriptors and observed ranges in
 //                        registers; shared histogram [slot][bin][channel][lane] -> bank == lane, no conflicts, one copy.
 //   eng_tiles_kernel     tiles (<= 2048 records of one node) of the level.
+//   eng_order_kernel     the order routing visits the tiles in (k-th tile of every node together).
 //   eng_route_kernel     a6: record -> way (x >= splat, NA by direction), leaves recorded, per-tile left/right counts.
 //   eng_scan_kernel      exclusive scan of the tile counts, first record of every child, next level's node table.
 //   eng_scatter_kernel   stable move of the live records to their child's run in the other buffer.
@@ -412,6 +413,24 @@ __global__ void __launch_bounds__(1024) eng_tiles_kernel(const int32_t* __restri
   if (g <= n_nodes) tile_base[g] = ex;  // tile_base[n_nodes] = number of tiles
 }
 
+// Routing visits the tiles in "k-th tile of every node" order instead of node by node.  Inside a node the records are
+// ascending in row number, so the k-th tiles of all nodes cover the same stretch of rows: the CTAs in flight together
+// then gather from the same DRAM pages of XT and write the same sectors of leaf[] within a short time of each other
+// (L2 merges the partial sector writes) instead of coming back to every page once per node.
+__global__ void __launch_bounds__(256) eng_order_kernel(const int32_t* __restrict__ tile_base, int n_nodes,
+                                                        int32_t* __restrict__ tile_order) {
+  __shared__ int s_nt[kEngMaxNodes];
+  for (int g = threadIdx.x; g < n_nodes; g += 256) s_nt[g] = tile_base[g + 1] - tile_base[g];
+  __syncthreads();
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= tile_base[n_nodes]) return;
+  const int g = seg_of(tile_base, n_nodes, t);
+  const int k = t - tile_base[g];
+  int rank = 0;
+  for (int j = 0; j < n_nodes; j++) rank += min(s_nt[j], k) + (j < g && s_nt[j] > k ? 1 : 0);
+  tile_order[rank] = t;
+}
+
 struct TileRange {
   int g;
   int64_t start, end;
@@ -432,10 +451,11 @@ __global__ void __launch_bounds__(256) eng_route_kernel(const float* __restrict_
                                                         const h2ok_split* __restrict__ splits,
                                                         const int32_t* __restrict__ child_ids, int gid_base,
                                                         uint8_t* __restrict__ codes, int32_t* __restrict__ leaf,
-                                                        int32_t* __restrict__ tile_cnt) {
+                                                        int32_t* __restrict__ tile_cnt,
+                                                        const int32_t* __restrict__ tile_order) {
   __shared__ int s_cnt[2];
-  const int t = blockIdx.x;
-  if (t >= tile_base[n_nodes]) return;
+  if ((int)blockIdx.x >= tile_base[n_nodes]) return;
+  const int t = tile_order[blockIdx.x];
   const TileRange tr = tile_range(seg, tile_base, n_nodes, t);
   const int g = tr.g;
   if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
@@ -627,6 +647,7 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   A((void**)&e.codes, (size_t)rows);
   A((void**)&e.tile_base, sizeof(int32_t) * (kEngMaxNodes + 1));
   A((void**)&e.tile_cnt, sizeof(int32_t) * 2 * (size_t)(e.max_tiles + 1));
+  A((void**)&e.tile_order, sizeof(int32_t) * (size_t)(e.max_tiles + 1));
   A((void**)&e.slot_start, sizeof(int32_t) * 2 * kEngMaxNodes);
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
   if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
@@ -640,10 +661,11 @@ void engine_free(Engine& e) {
     cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]);
     e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr;
   }
-  cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.slot_start); cudaFree(e.leaf);
+  cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.tile_order); cudaFree(e.slot_start);
+  cudaFree(e.leaf);
   e.XT = nullptr;
   e.codes = nullptr;
-  e.tile_base = e.tile_cnt = e.slot_start = e.leaf = nullptr;
+  e.tile_base = e.tile_cnt = e.tile_order = e.slot_start = e.leaf = nullptr;
   e.rows = e.ldt = 0;
   e.n_nodes = 0;
 }
@@ -743,8 +765,9 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   const int nx = 1 - e.cur;
   const unsigned tiles = (unsigned)(e.rows / kEngTile + n_nodes + 1);  // bound: the live count stays on the device
   eng_tiles_kernel<<<1, 1024, 0, s>>>(e.seg[e.cur], n_nodes, e.tile_base);
+  eng_order_kernel<<<nblk(tiles, 256), 256, 0, s>>>(e.tile_base, n_nodes, e.tile_order);
   eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.gidx[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
-                                         gid_base, e.codes, e.leaf, e.tile_cnt);
+                                         gid_base, e.codes, e.leaf, e.tile_cnt, e.tile_order);
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx]);
   eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.gidx[e.cur], e.gval[e.cur], e.weighted ? e.gw[e.cur] : nullptr, e.gidx[nx],
                                            e.gval[nx], e.weighted ? e.gw[nx] : nullptr,

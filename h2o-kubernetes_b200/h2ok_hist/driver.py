@@ -284,7 +284,7 @@ class EngineShard(CudaShard):
     def apply_splits(self, n_nodes, gid_base, last=False):
         self.lib.call("h2ok_hist_tree_apply_splits_dev", self.ctx, _ptr(self.splits), _ptr(self.child_ids), gid_base,
                       n_nodes, 1 if last else 0)
-        self.launches += 4  # tiles, route, scan, scatter
+        self.launches += 5  # tiles, order, route, scan, scatter
 
 
 def _world():
