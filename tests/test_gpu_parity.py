@@ -473,6 +473,41 @@ def test_full_size_config3_slice_invariants_and_idempotence(tree_shard):
     torch.cuda.empty_cache()
 
 
+def test_full_size_config3_paths_agree(shard, eshard):
+    """Config 3 at full size: the stateless kernels and the resident engine build the same tree — every level's
+    integer accumulators, observed ranges, splits and the final leaf of every row, bit for bit."""
+    from h2ok_hist.driver import LevelDriver
+
+    free, _ = torch.cuda.mem_get_info()
+    rows = 100_000_000 if free > 100e9 else 5_000_000
+    cols = 64
+    params = abi.Params.make(nbins=256, max_depth=8)
+    trace = {}
+    for name, sh in (("engine", eshard), ("stateless", shard)):
+        sh.set_data_synth(abi.SHAPE_WIDE64, 20261106, 0, rows, cols)
+        drv = LevelDriver(sh, params)
+        drv.prepare_data()
+        levels = []
+
+        def inspect(d, n, nch):
+            s_ = d.shard
+            levels.append((n, nch, s_.acc[:n].clone(), s_.mn[:n].clone(), s_.mx[:n].clone(), s_.splits[:n].clone(),
+                           s_.child_ids[: 2 * n].clone()))
+
+        assert drv.train_tree(inspect=inspect) == 8
+        trace[name] = (levels, sh.leaf[:rows].clone())
+    (la, leaf_a), (lb, leaf_b) = trace["engine"], trace["stateless"]
+    assert len(la) == len(lb) == 8
+    for a, b in zip(la, lb):
+        assert a[0] == b[0] and a[1] == b[1]
+        for ta, tb in zip(a[2:], b[2:]):
+            assert torch.equal(ta, tb)
+    assert torch.equal(leaf_a, leaf_b)
+    for sh in (shard, eshard):
+        sh.set_data_synth(abi.SHAPE_HIGGS28, 1, 0, 1024, 4)  # release the big buffers
+    torch.cuda.empty_cache()
+
+
 # ------------------------------------------------------------------------------------------------ a9: GBM loop
 @pytest.mark.parametrize("path,weight_mode", [("stateless", 0), ("engine", 0), ("engine", 1)])
 def test_gbm_gaussian_trees_bit_exact(shard, eshard, oracle, path, weight_mode):
