@@ -134,15 +134,14 @@ struct EngLane {
 __device__ __forceinline__ bool wrapped(unsigned old, int v) { return (old > ~(unsigned)v) != (v < 0); }
 
 // U rows x CPL cells in three phases, so that the independent cells overlap their latencies instead of running one
-// behind the other: (1) every cell's bin and shared address, (2) every cell's atomics, (3) ONE test for "some 32-bit
-// word wrapped".  The cold path looks at the saved old values again to find which.  wq == 0 rows (weighted only) are
-// turned into NaNs that add zeros: the NA bin gets +0 and the running extremes ignore NaN — which is what skipping
-// the row means.  v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
+// behind the other: (1) eng_bins: every cell's bin and shared address — after it the row values are dead and their
+// registers take the next batch's rows; (2) every cell's atomics; (3) ONE test for "some 32-bit word wrapped".  The
+// cold path looks at the saved old values again to find which.  wq == 0 rows (weighted only) are turned into NaNs
+// that add zeros: the NA bin gets +0 and the running extremes ignore NaN — which is what skipping the row means.
+// v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
 template <int CPL, bool WEIGHTED, int U>
-__device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a, const unsigned (&hb)[CPL], int node, int col_lane,
-                                          const typename XVec<CPL>::type (&xv)[U], const int (&v1)[U], const int (&v2)[U],
-                                          const int (&w)[U]) {
-  unsigned pa[U * CPL], o1[U * CPL], o2[U * CPL], o0[WEIGHTED ? U * CPL : 1];
+__device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[CPL], const typename XVec<CPL>::type (&xv)[U],
+                                         const int (&w)[U], unsigned (&pa)[U * CPL]) {
 #pragma unroll
   for (int j = 0; j < U; j++) {
 #pragma unroll
@@ -155,6 +154,13 @@ __device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a,
       pa[j * CPL + k] = hb[k] + (unsigned)b * 384u;
     }
   }
+}
+
+template <int CPL, bool WEIGHTED, int U>
+__device__ __forceinline__ void eng_accum(const EngHistArgs& a, const unsigned (&hb)[CPL], int node, int col_lane,
+                                          const unsigned (&pa)[U * CPL], const int (&v1)[U], const int (&v2)[U],
+                                          const int (&w)[U]) {
+  unsigned o1[U * CPL], o2[U * CPL], o0[WEIGHTED ? U * CPL : 1];
 #pragma unroll
   for (int j = 0; j < U; j++) {
 #pragma unroll
@@ -190,6 +196,8 @@ __device__ __forceinline__ void eng_batch(EngLane<CPL>& c, const EngHistArgs& a,
     }
   }
 }
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // 1024 threads leave 64 registers per thread, and a single spilled register in the row loop costs ~30% (with 227 KB
 // of shared memory carved out, local memory has almost no L1 behind it): rows per batch are chosen so that every
@@ -297,17 +305,28 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     __syncthreads();  // histogram words, range slots and offsets are ready
     const int m1 = s_m[0], m2 = s_m[1];
 
-    // Every warp takes U consecutive records at a time; the warps of the CTA interleave.
+    // Every warp takes U consecutive records at a time; the warps of the CTA interleave.  The row numbers of a batch
+    // are fetched one batch ahead, and as soon as they are there (after the bin phase) the rows themselves are pulled
+    // into L2 with one prefetch per row (each lane names its own sector), so that the next batch's row loads are L2
+    // hits instead of DRAM round trips — without holding a single register for data in flight.
     {
       constexpr int stride = NW * U;
       int p = p0 + warp * U;
+      int nx[U];
+      if (p + U <= send) {
+#pragma unroll
+        for (int j = 0; j < U; j++) nx[j] = __ldg(gidx + p + j);
+      }
       for (; p + U <= send; p += stride) {
-        int idx[U], v1[U], v2[U], w[U];
+        int v1[U], v2[U], w[U];
         V x[U];
 #pragma unroll
-        for (int j = 0; j < U; j++) idx[j] = __ldg(gidx + p + j);
+        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)nx[j] * ldt4));
+        const bool more = p + stride + U <= send;
+        if (more) {
 #pragma unroll
-        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[j] * ldt4));
+          for (int j = 0; j < U; j++) nx[j] = __ldg(gidx + p + stride + j);
+        }
 #pragma unroll
         for (int j = 0; j < U; j++) {
           const uint2 r = __ldg(gval + p + j);
@@ -315,7 +334,13 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
           v2[j] = (int)r.y - m2;
           w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
         }
-        eng_batch<CPL, WEIGHTED, U>(c, a, hb, node, col_lane, x, v1, v2, w);
+        unsigned pa[U * CPL];
+        eng_bins<CPL, WEIGHTED, U>(c, hb, x, w, pa);
+        if (more) {
+#pragma unroll
+          for (int j = 0; j < U; j++) prefetch_l2(xrow + (uint64_t)(unsigned)nx[j] * ldt4);
+        }
+        eng_accum<CPL, WEIGHTED, U>(a, hb, node, col_lane, pa, v1, v2, w);
       }
       for (; p < send; p++) {  // the run's last, partial batch: one row at a time
         int idx[1], v1[1], v2[1], w[1];
@@ -326,7 +351,9 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         v1[0] = (int)r.x - m1;
         v2[0] = (int)r.y - m2;
         w[0] = WEIGHTED ? __ldg(gw + p) : 1;
-        eng_batch<CPL, WEIGHTED, 1>(c, a, hb, node, col_lane, x, v1, v2, w);
+        unsigned pa[CPL];
+        eng_bins<CPL, WEIGHTED, 1>(c, hb, x, w, pa);
+        eng_accum<CPL, WEIGHTED, 1>(a, hb, node, col_lane, pa, v1, v2, w);
       }
     }
 
