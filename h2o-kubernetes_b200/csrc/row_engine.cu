@@ -142,16 +142,29 @@ __device__ __forceinline__ bool wrapped(unsigned old, int v) { return (old > ~(u
 template <int CPL, bool WEIGHTED, int U>
 __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[CPL], const typename XVec<CPL>::type (&xv)[U],
                                          const int (&w)[U], unsigned (&pa)[U * CPL]) {
+  float xs[U][CPL];
 #pragma unroll
   for (int j = 0; j < U; j++) {
 #pragma unroll
     for (int k = 0; k < CPL; k++) {
       float x = xget(xv[j], k);
       if (WEIGHTED) x = w[j] != 0 ? x : __int_as_float(0x7FC00000);
+      xs[j][k] = x;
       const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
-      c.fmn[k] = fminf(c.fmn[k], x);  // NaN-ignoring and exact
-      c.fmx[k] = fmaxf(c.fmx[k], x);
       pa[j * CPL + k] = hb[k] + (unsigned)b * 384u;
+    }
+  }
+  // running extremes (NaN-ignoring and exact), two rows at a time: min(min(m, a), b) is one three-input FMNMX3
+#pragma unroll
+  for (int k = 0; k < CPL; k++) {
+#pragma unroll
+    for (int j = 0; j + 1 < U; j += 2) {
+      c.fmn[k] = fminf(fminf(c.fmn[k], xs[j][k]), xs[j + 1][k]);
+      c.fmx[k] = fmaxf(fmaxf(c.fmx[k], xs[j][k]), xs[j + 1][k]);
+    }
+    if (U & 1) {
+      c.fmn[k] = fminf(c.fmn[k], xs[U - 1][k]);
+      c.fmx[k] = fmaxf(c.fmx[k], xs[U - 1][k]);
     }
   }
 }
