@@ -4,7 +4,7 @@
 //   eng_load_kernel      column-major block -> row-major XT (tiled transpose), once per data set.
 //   eng_begin_kernel     new tree: records in row order, every row at the root.
 //   eng_hist_kernel      one level's histogram pass.  CTA = (contiguous run of records, block of 32*CPL columns); a
-//                        warp takes whole rows, lane L owns CPL adjacent columns; descriptors and observed ranges in
+//                        warp takes whole rows, lane L owns CPL (1 or 2) adjacent columns; descriptors and observed ranges in
 //                        registers; shared histogram [slot][bin][channel][lane] -> bank == lane, no conflicts, one copy.
 //   eng_tiles_kernel     tiles (<= 2048 records of one node) of the level.
 //   eng_order_kernel     the order routing visits the tiles in (k-th tile of every node together).
@@ -114,11 +114,9 @@ __device__ __noinline__ void eng_carry(int64_t* acc, const h2ok_col_desc* __rest
 template <int CPL> struct XVec;
 template <> struct XVec<1> { using type = float; };
 template <> struct XVec<2> { using type = float2; };
-template <> struct XVec<4> { using type = float4; };
 
 __device__ __forceinline__ float xget(const float& v, int) { return v; }
 __device__ __forceinline__ float xget(const float2& v, int k) { return k ? v.y : v.x; }
-__device__ __forceinline__ float xget(const float4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); }
 
 // What a lane keeps in registers while it walks the rows of one node: the descriptors and running extremes of its CPL
 // columns.  A (node, column) that is not tracked gets a harmless 1-bin descriptor — its rows land in words that the
@@ -218,7 +216,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 template <int CPL, bool WEIGHTED>
 struct EngCfg {
   static constexpr int threads = 1024;
-  static constexpr int U = (WEIGHTED || CPL == 4) ? (CPL == 4 ? 1 : 4 / CPL) : 8 / CPL;
+  static constexpr int U = WEIGHTED ? 4 / CPL : 8 / CPL;
 };
 
 // The wY and wYY words hold the sum of (target - M) for an offset M close to the run's mean target, so that they
@@ -739,7 +737,6 @@ cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* 
 }
 
 static int eng_cpl(int cols, int nb1) {
-  if (cols > 64 && (size_t)128 * nb1 * 12 <= (size_t)kHistSmemCap) return 4;
   if (cols > 32 && (size_t)64 * nb1 * 12 <= (size_t)kHistSmemCap) return 2;
   if ((size_t)32 * nb1 * 12 <= (size_t)kHistSmemCap) return 1;
   return 0;
@@ -790,11 +787,9 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   const dim3 grid((unsigned)kSMs, (unsigned)((e.cols + colblk - 1) / colblk));
   const size_t smem = (size_t)colblk * nb1 * 12;
   if (e.weighted) {
-    if (cpl == 4) return launch_eng_hist<4, true>(a, grid, smem, s);
     if (cpl == 2) return launch_eng_hist<2, true>(a, grid, smem, s);
     return launch_eng_hist<1, true>(a, grid, smem, s);
   }
-  if (cpl == 4) return launch_eng_hist<4, false>(a, grid, smem, s);
   if (cpl == 2) return launch_eng_hist<2, false>(a, grid, smem, s);
   return launch_eng_hist<1, false>(a, grid, smem, s);
 }

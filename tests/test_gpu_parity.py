@@ -591,8 +591,8 @@ def test_engine_ragged_sizes_and_deep_trees(eshard, oracle, rows, cols, depth, m
 
 @pytest.mark.parametrize("cols,nbins,weight_mode", [(130, 32, 0), (130, 32, 1), (70, 256, 0), (33, 300, 1), (3, 500, 0)])
 def test_engine_column_blocks(eshard, oracle, cols, nbins, weight_mode):
-    """Every lane / column-block layout of the engine's histogram kernel: four, two and one column per lane, a last
-    block that is only partly filled, and column counts that are not a multiple of the row pitch."""
+    """Every lane / column-block layout of the engine's histogram kernel: two and one column per lane, several column
+    blocks, a last block that is only partly filled, and column counts that are not a multiple of the row pitch."""
     rows = 20011
     X, y, w = oracle.synth(abi.SHAPE_WIDE64, 77 + cols, 0, rows, cols, na_permille=15, weight_mode=weight_mode)
     params = abi.Params.make(nbins=nbins, max_depth=4, min_rows=3)
