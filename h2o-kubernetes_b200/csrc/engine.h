@@ -5,15 +5,17 @@
 // room for a single histogram copy — its floor is ~23 shared-memory wavefronts per 32 cells.
 //
 // The engine turns the problem by 90 degrees.  X is kept ROW-major (one row = cols consecutive floats, 256 B at 64
-// columns) and never moves.  What is regrouped per level is a 16-byte row record {row, wyq, wyyq, wq}: the records
-// are kept grouped by node (H2O does the same per chunk: ScoreBuildHistogram2 buckets row indices by nid before
+// columns) and never moves.  What is regrouped per level is a 12-byte row record {row, wyq, wyyq} (+ wq on weighted
+// shards): the records are kept grouped by node (H2O does the same per chunk: ScoreBuildHistogram2 buckets row indices by nid before
 // calling updateHisto).  A histogram CTA owns a contiguous run of records, i.e. the rows of ONE node at a time:
 //   * a warp takes one row at a time; lane L owns columns {2L, 2L+1} of a 64-column block, so the row is one
 //     coalesced 256-byte load whose every sector is used — the gather costs no extra HBM traffic;
 //   * the node's descriptors for the lane's columns sit in registers: no per-row table lookups at any depth;
 //   * the shared histogram is laid out [column slot][bin][channel][lane]: a lane only ever touches bank == lane,
 //     so every shared atomic is conflict-free at every depth and for every data distribution, with ONE copy;
-//   * the row record is the same for all lanes: one broadcast load per row, amortised over 64 cells.
+//   * the row record is the same for all lanes: broadcast loads, amortised over 64 cells;
+//   * the rows of a warp's next batch are pulled into L2 while the current batch is accumulated (one prefetch per
+//     row in which every lane names its own sector), so row loads are L2 hits and no register holds data in flight.
 // Integer accumulation makes the result independent of the row order, so the engine's histograms are bit-identical
 // to the stateless path's.
 #pragma once

@@ -4,8 +4,9 @@
 //   eng_load_kernel      column-major block -> row-major XT (tiled transpose), once per data set.
 //   eng_begin_kernel     new tree: records in row order, every row at the root.
 //   eng_hist_kernel      one level's histogram pass.  CTA = (contiguous run of records, block of 32*CPL columns); a
-//                        warp takes whole rows, lane L owns CPL (1 or 2) adjacent columns; descriptors and observed ranges in
-//                        registers; shared histogram [slot][bin][channel][lane] -> bank == lane, no conflicts, one copy.
+//                        warp takes whole rows, lane L owns CPL (1 or 2) adjacent columns; descriptors and observed
+//                        ranges in registers; shared histogram [slot][bin][channel][lane] -> bank == lane, no
+//                        conflicts, one copy; the next batch's rows are prefetched into L2.
 //   eng_tiles_kernel     tiles (<= 2048 records of one node) of the level.
 //   eng_order_kernel     the order routing visits the tiles in (k-th tile of every node together).
 //   eng_route_kernel     a6: record -> way (x >= splat, NA by direction), leaves recorded, per-tile left/right counts.

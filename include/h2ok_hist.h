@@ -209,7 +209,7 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
 
 /* ---- resident tree engine (device-resident; the fast path at depth) ---------------------------------------------
  * Same results as build_level_dev / apply_splits_dev, bit for bit.  The shard lives inside the context as a ROW-major
- * copy of X that never moves; per level only a 16-byte row record {row, wyq, wyyq, wq} is kept grouped by node (what
+ * copy of X that never moves; per level only a 12-byte row record {row, wyq, wyyq} (+ wq) is kept grouped by node (what
  * ScoreBuildHistogram2 does with row indices per chunk, hex/tree/ScoreBuildHistogram2.java).  A histogram CTA then
  * works on one node at a time: a warp takes whole rows (one coalesced load, every sector used), each lane owns its
  * columns' descriptors in registers and its own shared-memory bank, so there are no descriptor lookups and no
