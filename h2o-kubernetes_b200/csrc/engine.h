@@ -6,8 +6,9 @@
 //
 // The engine turns the problem by 90 degrees.  X is kept ROW-major (one row = cols consecutive floats, 256 B at 64
 // columns) and never moves.  What is regrouped per level is a 12-byte row record {row, wyq, wyyq} (+ wq on weighted
-// shards): the records are kept grouped by node (H2O does the same per chunk: ScoreBuildHistogram2 buckets row indices by nid before
-// calling updateHisto).  A histogram CTA owns a contiguous run of records, i.e. the rows of ONE node at a time:
+// shards): the records are kept grouped by node (H2O does the same per chunk: ScoreBuildHistogram2 buckets row
+// indices by nid before calling updateHisto).  A histogram CTA owns a contiguous run of records, i.e. the rows of
+// ONE node at a time:
 //   * a warp takes one row at a time; lane L owns columns {2L, 2L+1} of a 64-column block, so the row is one
 //     coalesced 256-byte load whose every sector is used — the gather costs no extra HBM traffic;
 //   * the node's descriptors for the lane's columns sit in registers: no per-row table lookups at any depth;
