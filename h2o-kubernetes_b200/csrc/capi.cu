@@ -323,6 +323,16 @@ int32_t h2ok_hist_gbm_residual_dev(h2ok_ctx* c, int32_t dist, const float* d_lab
   return H2OK_OK;
 }
 
+int32_t h2ok_hist_gbm_residual_multi_dev(h2ok_ctx* c, int32_t n_classes, const float* d_label, const float* d_f, int64_t ld,
+                                         const float* d_w, int64_t rows, double den_scale, float* d_res, int32_t* d_denq) {
+  REQUIRE(c && d_label && d_f && d_res && d_denq, "null pointer");
+  REQUIRE(n_classes >= 2 && n_classes <= 1024, "n_classes outside [2, 1024]");
+  REQUIRE(rows >= 0 && ld >= rows && den_scale > 0, "bad rows / ld / den_scale");
+  if (rows == 0) return H2OK_OK;
+  CK(launch_gbm_residual_multi(n_classes, d_label, d_f, ld, d_w, rows, den_scale, d_res, d_denq, c->stream));
+  return H2OK_OK;
+}
+
 int32_t h2ok_hist_gbm_gamma_pass_dev(h2ok_ctx* c, const int32_t* d_leaf, const int32_t* d_numq, const int32_t* d_denq,
                                      int64_t rows, int32_t n_codes, int64_t* d_num_acc, int64_t* d_den_acc) {
   REQUIRE(c && d_leaf && d_numq && d_num_acc && d_den_acc, "null pointer");

@@ -1,5 +1,6 @@
 // gbm_kernels.cu — SURVEY.md §8 row a9, the caller of the histogram path: GBM.buildNextKTrees' residual pass
-// (ComputePredAndRes), GammaPass and AddTreeContributions for one-class trees (gaussian, bernoulli).
+// (ComputePredAndRes), GammaPass and AddTreeContributions for one-class trees (gaussian, bernoulli) and the K-class
+// residual pass (multinomial: K one-class trees per iteration on softmax residuals).
 // [H2O-3 hex/tree/gbm/GBM.java, recalled; not under /root/reference]
 //
 // Leaf values are ratios of sums over a leaf's rows.  The sums are taken over the same fixed-point integers the
@@ -28,6 +29,28 @@ __global__ void gbm_residual_kernel(int dist, const float* __restrict__ label, c
   } else {
     res[r] = __fsub_rn(label[r], fi);  // gaussian: exact on host and device alike
     if (denq) denq[r] = w ? __double2int_rn(__dmul_rn((double)w[r], den_scale)) : 1;
+  }
+}
+
+// K-class residuals: one thread per row walks the K scores three times (max, exp + sum, residual); K is small.
+__global__ void gbm_residual_multi_kernel(int K, const float* __restrict__ label, const float* __restrict__ f, int64_t ld,
+                                          const float* __restrict__ w, int64_t rows, double den_scale,
+                                          float* __restrict__ res, int32_t* __restrict__ denq) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  float m = f[r];
+  for (int k = 1; k < K; k++) m = fmaxf(m, f[(int64_t)k * ld + r]);
+  float s = 0.0f;
+  for (int k = 0; k < K; k++) s = __fadd_rn(s, expf(__fsub_rn(f[(int64_t)k * ld + r], m)));
+  const int cls = (int)label[r];
+  const double wd = w ? (double)w[r] : 1.0;
+  for (int k = 0; k < K; k++) {
+    const float p = __fdiv_rn(expf(__fsub_rn(f[(int64_t)k * ld + r], m)), s);
+    const float rk = __fsub_rn(k == cls ? 1.0f : 0.0f, p);
+    res[(int64_t)k * ld + r] = rk;
+    const float a = fabsf(rk);
+    const double v = __dmul_rn(__dmul_rn(wd, (double)a), (double)__fsub_rn(1.0f, a));
+    denq[(int64_t)k * ld + r] = __double2int_rn(__dmul_rn(v, den_scale));
   }
 }
 
@@ -78,6 +101,12 @@ __global__ void gbm_add_gamma_kernel(const int32_t* __restrict__ leaf, int64_t r
 cudaError_t launch_gbm_residual(int dist, const float* label, const float* f, const float* w, int64_t rows,
                                 double den_scale, float* res, int32_t* denq, cudaStream_t s) {
   gbm_residual_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(dist, label, f, w, rows, den_scale, res, denq);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gbm_residual_multi(int K, const float* label, const float* f, int64_t ld, const float* w, int64_t rows,
+                                      double den_scale, float* res, int32_t* denq, cudaStream_t s) {
+  gbm_residual_multi_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(K, label, f, ld, w, rows, den_scale, res, denq);
   return cudaGetLastError();
 }
 

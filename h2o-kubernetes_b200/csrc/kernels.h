@@ -66,6 +66,8 @@ cudaError_t launch_apply_splits(const float* X, int64_t ld, int64_t rows, const 
 
 cudaError_t launch_gbm_residual(int dist, const float* label, const float* f, const float* w, int64_t rows,
                                 double den_scale, float* res, int32_t* denq, cudaStream_t s);
+cudaError_t launch_gbm_residual_multi(int K, const float* label, const float* f, int64_t ld, const float* w, int64_t rows,
+                                      double den_scale, float* res, int32_t* denq, cudaStream_t s);
 cudaError_t launch_gbm_gamma_pass(const int32_t* leaf, const int32_t* numq, const int32_t* denq, int64_t rows, int n_codes,
                                   int64_t* num_acc, int64_t* den_acc, cudaStream_t s);
 cudaError_t launch_gbm_add_gamma(const int32_t* leaf, int64_t rows, const double* gamma, int n_codes, double learn_rate,

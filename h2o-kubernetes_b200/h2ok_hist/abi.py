@@ -11,7 +11,7 @@ OK, ERR_ARG, ERR_CUDA, ERR_STATE, ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 MAX_BINS = 1024
 NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT = 0, 1, 2, 3
 SHAPE_HIGGS28, SHAPE_WIDE64, SHAPE_SPARSE = 2, 3, 4
-DIST_GAUSSIAN, DIST_BERNOULLI = 0, 1
+DIST_GAUSSIAN, DIST_BERNOULLI, DIST_MULTINOMIAL = 0, 1, 2
 
 COL_DESC = np.dtype(
     [("min", "<f8"), ("maxex", "<f8"), ("step", "<f8"), ("nbin", "<i4"), ("is_int", "<i4")], align=True

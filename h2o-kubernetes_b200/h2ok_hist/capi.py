@@ -41,6 +41,7 @@ SIGNATURES = {
     "h2ok_hist_tree_nid_dev": [vp, vp],
     "h2ok_hist_tree_leaf_dev": [vp, vp],
     "h2ok_hist_gbm_residual_dev": [vp, i32, vp, vp, vp, i64, f64, vp, vp],
+    "h2ok_hist_gbm_residual_multi_dev": [vp, i32, vp, vp, i64, vp, i64, f64, vp, vp],
     "h2ok_hist_gbm_gamma_pass_dev": [vp, vp, vp, vp, i64, i32, vp, vp],
     "h2ok_hist_gbm_add_gamma_dev": [vp, vp, i64, vp, i32, f64, vp],
     "h2ok_hist_root_descs_from_ranges": [vp, vp, i32, pP, vp, vp],

@@ -1,6 +1,7 @@
-"""a9 — the tree-level caller of the histogram path: GBM.buildNextKTrees for one-class
-trees (gaussian, bernoulli) as H2O-3 runs it [hex/tree/gbm/GBM.java, recalled]: residual pass → one tree through
-LevelDriver → GammaPass → AddTreeContributions.  All arithmetic is in libh2ok_hist.so; this file only sequences it and
+"""a9 — the tree-level caller of the histogram path: GBM.buildNextKTrees as H2O-3 runs it
+[hex/tree/gbm/GBM.java, recalled] for one-class trees (gaussian, bernoulli) and for K-class multinomial (K trees per
+iteration on softmax residuals, the workload of BASELINE config 4): residual pass → tree(s) through LevelDriver →
+GammaPass → AddTreeContributions.  All arithmetic is in libh2ok_hist.so; this file only sequences it and
 does the one cross-rank reduce of the leaf sums (integers, so every rank derives the same leaf values).
 """
 import ctypes as C
@@ -22,19 +23,34 @@ def leaf_gamma(num, den, scale_num, scale_den):
 
 
 class GBMTrainer:
-    def __init__(self, driver, label, dist=abi.DIST_GAUSSIAN, learn_rate=0.1):
-        """driver: a LevelDriver whose shard already holds X (prepare_data() done); label: device tensor [rows]."""
+    def __init__(self, driver, label, dist=abi.DIST_GAUSSIAN, learn_rate=0.1, n_classes=None):
+        """driver: a LevelDriver whose shard already holds X (prepare_data() done); label: device tensor [rows]
+        (multinomial: class ids 0..n_classes-1 as floats)."""
         self.drv, self.shard = driver, driver.shard
         self.lib = driver.lib
         self.dist, self.lr = dist, float(learn_rate)
         self.rows = self.shard.rows
         self.label = label
-        self.f = torch.zeros(self.rows, dtype=torch.float32, device=self.shard.device)
-        self.denq = torch.zeros(self.rows, dtype=torch.int32, device=self.shard.device) if dist == abi.DIST_BERNOULLI else None
+        dev = self.shard.device
         self.trees = []
+        if dist == abi.DIST_MULTINOMIAL:
+            if n_classes is None or n_classes < 2:
+                raise ValueError("multinomial needs n_classes >= 2")
+            self.K = int(n_classes)
+            self.ld = (self.rows + 63) // 64 * 64
+            self.f = torch.zeros((self.K, self.ld), dtype=torch.float32, device=dev)
+            self.res = torch.zeros((self.K, self.ld), dtype=torch.float32, device=dev)
+            self.denq = torch.zeros((self.K, self.ld), dtype=torch.int32, device=dev)
+            return
+        self.K = 1
+        self.f = torch.zeros(self.rows, dtype=torch.float32, device=dev)
+        self.denq = torch.zeros(self.rows, dtype=torch.int32, device=dev) if dist == abi.DIST_BERNOULLI else None
 
     def init_f(self):
-        """H2O's _initial_f: the (weighted) mean response, on the link scale."""
+        """H2O's _initial_f: the (weighted) mean response, on the link scale; multinomial starts from zero scores."""
+        if self.dist == abi.DIST_MULTINOMIAL:
+            self.f.zero_()
+            return 0.0
         w = self.shard.w[: self.rows].double() if self.shard.weighted else None
         y = self.label.double()
         s = torch.stack([(y * w).sum() if w is not None else y.sum(), w.sum() if w is not None else torch.tensor(float(self.rows), device=y.device, dtype=torch.float64)])
@@ -45,12 +61,9 @@ class GBMTrainer:
         self.f.fill_(np.float32(f0))
         return float(np.float32(f0))
 
-    def step(self):
-        """One boosting iteration; returns the tree's leaf values indexed by leaf code."""
+    def _tree_and_gamma(self, denq, den_scale, f_out, factor=1.0):
+        """One tree on the targets in shard.y, its GammaPass and AddTreeContributions into f_out."""
         sh, rows = self.shard, self.rows
-        den_scale = 2.0**28 if self.dist == abi.DIST_BERNOULLI else 1.0
-        self.lib.call("h2ok_hist_gbm_residual_dev", sh.ctx, self.dist, _ptr(self.label), _ptr(self.f), _ptr(sh.w), rows,
-                      den_scale, _ptr(sh.y), _ptr(self.denq))
         levels = []
 
         def keep(d, n, nch):
@@ -59,10 +72,8 @@ class GBMTrainer:
         self.drv.train_tree(inspect=keep)
         n_codes = 3 * self.drv.gid_base
         q = sh.quant
-        if self.dist == abi.DIST_GAUSSIAN:
+        if den_scale is None:  # gaussian
             denq, den_scale = (sh.wq, q.scale_w) if sh.weighted else (None, 1.0)
-        else:
-            denq = self.denq
         num = torch.zeros(n_codes, dtype=torch.int64, device=sh.device)
         den = torch.zeros(n_codes, dtype=torch.int64, device=sh.device)
         leaf = sh.leaf
@@ -71,12 +82,45 @@ class GBMTrainer:
         if _world() > 1:
             dist_.all_reduce(num)
             dist_.all_reduce(den)
-        gamma = leaf_gamma(num.cpu().numpy(), den.cpu().numpy(), q.scale_wy, den_scale)
+        gamma = factor * leaf_gamma(num.cpu().numpy(), den.cpu().numpy(), q.scale_wy, den_scale)
         dg = torch.from_numpy(gamma).to(sh.device)
-        self.lib.call("h2ok_hist_gbm_add_gamma_dev", sh.ctx, _ptr(leaf), rows, _ptr(dg), n_codes, self.lr, _ptr(self.f))
-        sh.launches += 3
-        self.trees.append(dict(levels=levels, gamma=gamma))
-        return gamma
+        self.lib.call("h2ok_hist_gbm_add_gamma_dev", sh.ctx, _ptr(leaf), rows, _ptr(dg), n_codes, self.lr, _ptr(f_out))
+        sh.launches += 2
+        return dict(levels=levels, gamma=gamma)
+
+    def _step_multinomial(self):
+        """K trees on the softmax residuals of the current scores (all residuals are taken before the first tree)."""
+        sh, rows, K = self.shard, self.rows, self.K
+        den_scale = 2.0**28
+        self.lib.call("h2ok_hist_gbm_residual_multi_dev", sh.ctx, K, _ptr(self.label), _ptr(self.f), self.ld, _ptr(sh.w),
+                      rows, den_scale, _ptr(self.res), _ptr(self.denq))
+        sh.launches += 1
+        out = []
+        for k in range(K):
+            sh.y[:rows].copy_(self.res[k, :rows])
+            t = self._tree_and_gamma(self.denq[k], den_scale, self.f[k], factor=(K - 1.0) / K)
+            t["cls"] = k
+            self.trees.append(t)
+            out.append(t["gamma"])
+        return out
+
+    def step(self):
+        """One boosting iteration; returns the tree's leaf values indexed by leaf code (multinomial: one per class)."""
+        if self.dist == abi.DIST_MULTINOMIAL:
+            return self._step_multinomial()
+        sh, rows = self.shard, self.rows
+        den_scale = 2.0**28 if self.dist == abi.DIST_BERNOULLI else 1.0
+        self.lib.call("h2ok_hist_gbm_residual_dev", sh.ctx, self.dist, _ptr(self.label), _ptr(self.f), _ptr(sh.w), rows,
+                      den_scale, _ptr(sh.y), _ptr(self.denq))
+        sh.launches += 1
+        if self.dist == abi.DIST_GAUSSIAN:
+            # the denominator is the weight (quantised with the histogram's own scale, known after the tree's
+            # prepare_tree) or the row count: resolved lazily below
+            t = self._tree_and_gamma(None, None, self.f)
+        else:
+            t = self._tree_and_gamma(self.denq, den_scale, self.f)
+        self.trees.append(t)
+        return t["gamma"]
 
     def train(self, n_trees):
         for _ in range(n_trees):
@@ -85,8 +129,13 @@ class GBMTrainer:
 
     def loss(self):
         """Training loss (MSE or logloss) of the current f — reporting only."""
-        y, f = self.label.double(), self.f.double()
-        if self.dist == abi.DIST_GAUSSIAN:
+        y = self.label.double()
+        f = self.f.double() if self.dist != abi.DIST_MULTINOMIAL else None
+        if self.dist == abi.DIST_MULTINOMIAL:
+            logp = torch.log_softmax(self.f[:, : self.rows].double(), dim=0)
+            picked = logp.gather(0, self.label.long()[None, :])[0]
+            s = torch.stack([-picked.sum(), torch.tensor(float(self.rows), device=y.device, dtype=torch.float64)])
+        elif self.dist == abi.DIST_GAUSSIAN:
             s = torch.stack([((y - f) ** 2).sum(), torch.tensor(float(self.rows), device=y.device, dtype=torch.float64)])
         else:
             p = torch.sigmoid(f).clamp(1e-15, 1 - 1e-15)

@@ -58,6 +58,7 @@ extern "C" {
 /* Distributions of the tree-level caller (a9). */
 #define H2OK_DIST_GAUSSIAN 0
 #define H2OK_DIST_BERNOULLI 1
+#define H2OK_DIST_MULTINOMIAL 2
 
 /* Synthetic shapes of SURVEY.md §8(d). */
 #define H2OK_SHAPE_HIGGS28 2 /* config 2: 28 HIGGS-shaped columns */
@@ -247,6 +248,14 @@ int32_t h2ok_hist_gbm_residual_dev(h2ok_ctx* ctx, int32_t dist, const float* d_l
                                    int64_t rows, double den_scale, float* d_res, int32_t* d_denq);
 /* GammaPass: integer sums of d_numq and d_denq (NULL: row count) per leaf code (d_leaf as written by apply_splits);
  * d_num_acc / d_den_acc: int64 [n_codes], overwritten.  Combine across ranks with an integer sum. */
+/* ComputePredAndRes for K-class (multinomial) GBM, all classes in one pass over f: p = softmax(f[0..K)[r]) in fp32
+ * (max-subtracted, expf, summed in class order), d_res[k*ld + r] = (label[r] == k) - p_k, and
+ * d_denq[k*ld + r] = rint(w * |res| * (1 - |res|) * den_scale), the GammaPass denominator.  d_label holds class
+ * ids 0..K-1 as floats; d_f, d_res, d_denq are [K][ld].  The class-k tree is then built on d_res + k*ld and its
+ * leaf values are (K-1)/K * sum(res) / sum(|res|(1-|res|)) (GBM.java GammaPass, m1class). */
+int32_t h2ok_hist_gbm_residual_multi_dev(h2ok_ctx* ctx, int32_t n_classes, const float* d_label, const float* d_f,
+                                         int64_t ld, const float* d_w, int64_t rows, double den_scale, float* d_res,
+                                         int32_t* d_denq);
 int32_t h2ok_hist_gbm_gamma_pass_dev(h2ok_ctx* ctx, const int32_t* d_leaf, const int32_t* d_numq, const int32_t* d_denq,
                                      int64_t rows, int32_t n_codes, int64_t* d_num_acc, int64_t* d_den_acc);
 /* AddTreeContributions: f[r] += (float)(learn_rate * d_gamma[d_leaf[r]]). */

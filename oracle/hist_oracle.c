@@ -646,6 +646,33 @@ void h2ok_oracle_gbm_residual(int32_t dist, const float* label, const float* f, 
   }
 }
 
+/* a9, K classes: GBM.java ComputePredAndRes for multinomial — softmax of the K scores (fp32, max-subtracted, summed in
+ * class order), residual (label == k) - p_k, GammaPass denominator w * |res| * (1 - |res|) quantised. */
+void h2ok_oracle_gbm_residual_multi(int32_t K, const float* label, const float* f, int64_t ld, const float* w, int64_t rows,
+                                    double den_scale, float* res, int32_t* denq) {
+  for (int64_t r = 0; r < rows; r++) {
+    float m = f[r];
+    for (int k = 1; k < K; k++) m = fmaxf(m, f[(int64_t)k * ld + r]);
+    float s = 0.0f;
+    for (int k = 0; k < K; k++) {
+      float e = expf(f[(int64_t)k * ld + r] - m); /* libm: a few ulp from the device's expf */
+      s = s + e;
+    }
+    int cls = (int)label[r];
+    double wd = w ? (double)w[r] : 1.0;
+    for (int k = 0; k < K; k++) {
+      float e = expf(f[(int64_t)k * ld + r] - m);
+      float p = e / s;
+      float rk = (k == cls ? 1.0f : 0.0f) - p;
+      res[(int64_t)k * ld + r] = rk;
+      float a = fabsf(rk);
+      float om = 1.0f - a;
+      double v = (wd * (double)a) * (double)om;
+      denq[(int64_t)k * ld + r] = (int32_t)nearbyint(v * den_scale);
+    }
+  }
+}
+
 void h2ok_oracle_gbm_gamma_pass(const int32_t* leaf, const int32_t* numq, const int32_t* denq, int64_t rows,
                                 int32_t n_codes, int64_t* num_acc, int64_t* den_acc) {
   memset(num_acc, 0, sizeof(int64_t) * (size_t)n_codes);

@@ -71,6 +71,8 @@ void h2ok_oracle_apply_splits(const float* X, int64_t ld, int64_t rows, const h2
 /* a9 */
 void h2ok_oracle_gbm_residual(int32_t dist, const float* label, const float* f, const float* w, int64_t rows,
                               double den_scale, float* res, int32_t* denq);
+void h2ok_oracle_gbm_residual_multi(int32_t K, const float* label, const float* f, int64_t ld, const float* w, int64_t rows,
+                                    double den_scale, float* res, int32_t* denq);
 void h2ok_oracle_gbm_gamma_pass(const int32_t* leaf, const int32_t* numq, const int32_t* denq, int64_t rows,
                                 int32_t n_codes, int64_t* num_acc, int64_t* den_acc);
 void h2ok_oracle_gbm_add_gamma(const int32_t* leaf, int64_t rows, const double* gamma, int32_t n_codes, double learn_rate,

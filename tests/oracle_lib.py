@@ -63,6 +63,8 @@ class Oracle:
         L.h2ok_oracle_apply_splits.argtypes = [vp, i64, i64, vp, vp, i32, i32, vp, vp]
         L.h2ok_oracle_gbm_residual.restype = None
         L.h2ok_oracle_gbm_residual.argtypes = [i32, vp, vp, vp, i64, f64, vp, vp]
+        L.h2ok_oracle_gbm_residual_multi.restype = None
+        L.h2ok_oracle_gbm_residual_multi.argtypes = [i32, vp, vp, i64, vp, i64, f64, vp, vp]
         L.h2ok_oracle_gbm_gamma_pass.restype = None
         L.h2ok_oracle_gbm_gamma_pass.argtypes = [vp, vp, vp, i64, i32, vp, vp]
         L.h2ok_oracle_gbm_add_gamma.restype = None
@@ -231,12 +233,13 @@ def gbm_gamma(num, den, scale_num, scale_den):
 class OracleGBM:
     """The a9 loop on the CPU with the fixed-point level walk — the bit-exact checker for h2ok_hist.gbm.GBMTrainer."""
 
-    def __init__(self, oracle, X, rows, label, w, params, dist, learn_rate, qbits=25, is_int=None):
+    def __init__(self, oracle, X, rows, label, w, params, dist, learn_rate, qbits=25, is_int=None, n_classes=1):
         self.o, self.X, self.rows, self.label, self.w = oracle, X, rows, label, w
         self.params, self.dist, self.lr, self.qbits, self.is_int = params, dist, learn_rate, qbits, is_int
         self.cols = X.shape[0]
         self.root = oracle.root_descs(X, rows, params, is_int)
-        self.f = np.zeros(rows, np.float32)
+        self.K = n_classes
+        self.f = np.zeros(rows, np.float32) if dist != abi.DIST_MULTINOMIAL else np.zeros((n_classes, rows), np.float32)
         self.trees = []
 
     def init_f(self, f0):
@@ -268,7 +271,33 @@ class OracleGBM:
                 break
         return leaf, q, wq, wyq, gid, levels
 
+    def step_multinomial(self):
+        """K trees per iteration on the softmax residuals (GBM.java buildNextKTrees, multinomial)."""
+        o, rows, K = self.o, self.rows, self.K
+        den_scale = 2.0**28
+        res = np.zeros((K, rows), np.float32)
+        denq = np.zeros((K, rows), np.int32)
+        o.lib.h2ok_oracle_gbm_residual_multi(K, abi.ptr(self.label), abi.ptr(self.f), rows, abi.ptr(self.w), rows, den_scale,
+                                             abi.ptr(res), abi.ptr(denq))
+        out = []
+        for k in range(K):
+            leaf, q, wq, wyq, n_tree_nodes, levels = self.tree_q(np.ascontiguousarray(res[k]))
+            n_codes = 3 * n_tree_nodes
+            num = np.zeros(n_codes, np.int64)
+            den = np.zeros(n_codes, np.int64)
+            dk = np.ascontiguousarray(denq[k])
+            o.lib.h2ok_oracle_gbm_gamma_pass(abi.ptr(leaf), abi.ptr(wyq), abi.ptr(dk), rows, n_codes, abi.ptr(num), abi.ptr(den))
+            gamma = (K - 1.0) / K * gbm_gamma(num, den, q.scale_wy, den_scale)
+            fk = np.ascontiguousarray(self.f[k])
+            o.lib.h2ok_oracle_gbm_add_gamma(abi.ptr(leaf), rows, abi.ptr(gamma), n_codes, self.lr, abi.ptr(fk))
+            self.f[k] = fk
+            self.trees.append(dict(levels=levels, gamma=gamma, leaf=leaf, cls=k))
+            out.append(gamma)
+        return out
+
     def step(self):
+        if self.dist == abi.DIST_MULTINOMIAL:
+            return self.step_multinomial()
         o, rows = self.o, self.rows
         den_scale = 2.0**28 if self.dist == abi.DIST_BERNOULLI else None
         res = np.zeros(rows, np.float32)

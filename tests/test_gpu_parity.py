@@ -575,6 +575,49 @@ def test_gbm_bernoulli_tracks_oracle(eshard, oracle):
     assert all(b < a for a, b in zip(trace, trace[1:]))
 
 
+def test_gbm_multinomial_tracks_oracle(eshard, oracle):
+    """K-class GBM (K trees per iteration on softmax residuals, BASELINE config 4's workload).  The first iteration
+    starts from zero scores, where exp() is exact on both sides: its K trees and leaf values must equal the oracle's
+    bit for bit.  Later iterations go through expf (device vs libm: a few ulp), so the check is the logloss trace."""
+    import oracle_lib
+    from h2ok_hist.driver import LevelDriver
+    from h2ok_hist.gbm import GBMTrainer
+
+    rows, cols, K = 30000, 12, 3
+    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 5, 0, rows, cols, na_permille=5)
+    label = np.digitize(y[:rows], np.quantile(y[:rows], [1 / 3, 2 / 3])).astype(np.float32)  # three balanced classes
+    params = abi.Params.make(nbins=32, max_depth=4, min_rows=5)
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(label))
+    drv = LevelDriver(eshard, params)
+    drv.prepare_data()
+    tr = GBMTrainer(drv, torch.from_numpy(label).cuda(), abi.DIST_MULTINOMIAL, learn_rate=0.3, n_classes=K)
+    assert tr.init_f() == 0.0
+    ref = oracle_lib.OracleGBM(oracle, X, rows, label, None, params, abi.DIST_MULTINOMIAL, 0.3, n_classes=K)
+
+    def logloss(f):
+        z = f.astype(np.float64)
+        z = z - z.max(axis=0, keepdims=True)
+        logp = z - np.log(np.exp(z).sum(axis=0, keepdims=True))
+        return float(-logp[label.astype(np.int64), np.arange(rows)].mean())
+
+    trace = [tr.loss()]
+    assert trace[0] == pytest.approx(np.log(K), rel=1e-12)
+    for it in range(3):
+        gs = tr.step()
+        grs = ref.step()
+        torch.cuda.synchronize()
+        if it == 0:
+            for k in range(K):
+                assert gs[k].tobytes() == grs[k].tobytes(), f"class {k}: leaf values differ"
+                for (s_gpu, ids_gpu), (s_ref, ids_ref) in zip(tr.trees[k]["levels"], ref.trees[k]["levels"]):
+                    assert s_gpu.tobytes() == s_ref.tobytes() and np.array_equal(ids_gpu, ids_ref)
+            assert np.array_equal(tr.f[:, :rows].cpu().numpy(), ref.f)
+        trace.append(tr.loss())
+        assert trace[-1] == pytest.approx(logloss(ref.f), rel=1e-6)
+    assert all(b < a for a, b in zip(trace, trace[1:]))
+    assert len(tr.trees) == 3 * K
+
+
 # ------------------------------------------------------------------------------------------------ engine edge cases
 @pytest.mark.parametrize("rows,cols,depth,min_rows", [(1, 3, 3, 1), (5, 3, 3, 1), (130, 4, 5, 1), (4097, 5, 6, 2),
                                                       (60000, 6, 10, 1)])

@@ -444,3 +444,25 @@ def test_gbm_passes_paper_case(oracle):
     ff = np.array([1.0, 1.0, 1.0, 1.0], np.float32)
     oracle.lib.h2ok_oracle_gbm_add_gamma(abi.ptr(leaf), 4, abi.ptr(gamma), 9, 0.5, abi.ptr(ff))
     assert ff.tolist() == [1.75, 1.75, 2.25, 1.0]
+
+
+def test_gbm_multinomial_residuals_paper_case(oracle):
+    """K-class residual pass: zero scores give p = 1/K exactly; a score of ln 2 against zeros gives (1/2, 1/4, 1/4);
+    residuals of a row sum to zero and the GammaPass denominator is |res| (1 - |res|)."""
+    K, rows = 3, 4
+    label = np.array([0, 1, 2, 1], np.float32)
+    f = np.zeros((K, rows), np.float32)
+    f[0, 3] = np.float32(np.log(2.0))
+    res = np.zeros((K, rows), np.float32)
+    den = np.zeros((K, rows), np.int32)
+    oracle.lib.h2ok_oracle_gbm_residual_multi(K, abi.ptr(label), abi.ptr(f), rows, None, rows, 2.0**28, abi.ptr(res), abi.ptr(den))
+    third = np.float32(1.0) / np.float32(3.0)
+    for r in range(3):
+        for k in range(K):
+            want = (np.float32(1.0) if label[r] == k else np.float32(0.0)) - third
+            assert res[k, r] == want
+            a = abs(float(want))
+            assert den[k, r] == int(np.rint(np.float64(np.float32(abs(want))) * np.float64(np.float32(1.0) - np.float32(abs(want))) * 2.0**28))
+    assert res[:, 3] == pytest.approx([-0.5, 0.75, -0.25], abs=1e-6)
+    assert abs(float(res[:, 3].astype(np.float64).sum())) < 1e-6
+    assert den[:, 3] == pytest.approx([0.25 * 2**28, 0.1875 * 2**28, 0.1875 * 2**28], rel=1e-5)
