@@ -217,7 +217,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 template <int CPL, bool WEIGHTED>
 struct EngCfg {
   static constexpr int threads = 1024;
-  static constexpr int U = WEIGHTED ? 4 / CPL : 8 / CPL;
+  static constexpr int U = WEIGHTED ? 4 / CPL : 8 / CPL;  // 8, 4 (unweighted) or 4, 2 (weighted): even
 };
 
 // The wY and wYY words hold the sum of (target - M) for an offset M close to the run's mean target, so that they
@@ -321,31 +321,61 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     // are fetched one batch ahead, and as soon as they are there (after the bin phase) the rows themselves are pulled
     // into L2 with one prefetch per row (each lane names its own sector), so that the next batch's row loads are L2
     // hits instead of DRAM round trips — without holding a single register for data in flight.
+    // Batches start on multiples of U records, so the (warp-uniform) record loads are 128-bit: one load brings four
+    // row numbers or two {wyq, wyyq} pairs.  The records before the first aligned batch and after the last whole one
+    // go one row at a time.
     {
       constexpr int stride = NW * U;
-      int p = p0 + warp * U;
-      int nx[U];
-      if (p + U <= send) {
+      auto one_row = [&](int q) {
+        int v1[1], v2[1], w[1];
+        V x[1];
+        x[0] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)__ldg(gidx + q) * ldt4));
+        const uint2 r = __ldg(gval + q);
+        v1[0] = (int)r.x - m1;
+        v2[0] = (int)r.y - m2;
+        w[0] = WEIGHTED ? __ldg(gw + q) : 1;
+        unsigned pa[CPL];
+        eng_bins<CPL, WEIGHTED, 1>(c, hb, x, w, pa);
+        eng_accum<CPL, WEIGHTED, 1>(a, hb, node, col_lane, pa, v1, v2, w);
+      };
+      auto load_idx = [&](int q, int (&idx)[U]) {
+        if (U % 4 == 0) {
 #pragma unroll
-        for (int j = 0; j < U; j++) nx[j] = __ldg(gidx + p + j);
-      }
+          for (int j = 0; j < U; j += 4) {
+            const int4 t = __ldg(reinterpret_cast<const int4*>(gidx + q + j));
+            idx[j] = t.x; idx[j + 1 < U ? j + 1 : j] = t.y; idx[j + 2 < U ? j + 2 : j] = t.z; idx[j + 3 < U ? j + 3 : j] = t.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < U; j += 2) {
+            const int2 t = __ldg(reinterpret_cast<const int2*>(gidx + q + j));
+            idx[j] = t.x; idx[j + 1 < U ? j + 1 : j] = t.y;
+          }
+        }
+      };
+      const int pal = (p0 + U - 1) / U * U;  // first aligned record of the run
+      if (warp == NW - 1)
+        for (int q = p0; q < pal && q < send; q++) one_row(q);
+      int p = pal + warp * U;
+      int nx[U];
+      if (p + U <= send) load_idx(p, nx);
       for (; p + U <= send; p += stride) {
         int v1[U], v2[U], w[U];
         V x[U];
 #pragma unroll
         for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)nx[j] * ldt4));
         const bool more = p + stride + U <= send;
-        if (more) {
+        if (more) load_idx(p + stride, nx);
 #pragma unroll
-          for (int j = 0; j < U; j++) nx[j] = __ldg(gidx + p + stride + j);
-        }
-#pragma unroll
-        for (int j = 0; j < U; j++) {
-          const uint2 r = __ldg(gval + p + j);
+        for (int j = 0; j < U; j += 2) {
+          const uint4 r = __ldg(reinterpret_cast<const uint4*>(gval + p + j));
           v1[j] = (int)r.x - m1;
           v2[j] = (int)r.y - m2;
-          w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
+          v1[j + 1 < U ? j + 1 : j] = (int)r.z - m1;
+          v2[j + 1 < U ? j + 1 : j] = (int)r.w - m2;
         }
+#pragma unroll
+        for (int j = 0; j < U; j++) w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
         unsigned pa[U * CPL];
         eng_bins<CPL, WEIGHTED, U>(c, hb, x, w, pa);
         if (more) {
@@ -354,19 +384,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         }
         eng_accum<CPL, WEIGHTED, U>(a, hb, node, col_lane, pa, v1, v2, w);
       }
-      for (; p < send; p++) {  // the run's last, partial batch: one row at a time
-        int idx[1], v1[1], v2[1], w[1];
-        V x[1];
-        idx[0] = __ldg(gidx + p);
-        x[0] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)idx[0] * ldt4));
-        const uint2 r = __ldg(gval + p);
-        v1[0] = (int)r.x - m1;
-        v2[0] = (int)r.y - m2;
-        w[0] = WEIGHTED ? __ldg(gw + p) : 1;
-        unsigned pa[CPL];
-        eng_bins<CPL, WEIGHTED, 1>(c, hb, x, w, pa);
-        eng_accum<CPL, WEIGHTED, 1>(a, hb, node, col_lane, pa, v1, v2, w);
-      }
+      for (; p < send; p++) one_row(p);  // the run's last, partial batch
     }
 
     // observed ranges: registers -> shared (integer min / max of the order-preserving encoding) -> global
