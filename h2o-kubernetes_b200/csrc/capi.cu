@@ -82,6 +82,7 @@ struct h2ok_ctx {
   bool level_built = false, splits_found = false, children_made = false;
   bool timed = false;  // ev0/ev1 bracket the last hist_build launches
   Engine eng;          // resident tree engine (h2ok_hist_tree_*)
+  int eng_level_bins = 0;  // h2ok_hist_tree_level_bins hint for the next tree_build_level_dev (0: none)
   bool eng_ready = false;
   h2ok_stats stats{};
 };
@@ -402,9 +403,11 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_build_level_dev before tree_create");
   int32_t rc = check_level_shape(n_nodes, c->eng.cols, max_bins);
   if (rc) return rc;
-  if (max_bins + 1 > engine_max_nb1(c->eng.cols))
-    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: 32 columns x (max_bins+1) bins must fit 225 KB (max_bins <= 599)");
   const int nb1 = max_bins + 1;
+  const int level_nb1 = c->eng_level_bins > 0 && c->eng_level_bins < max_bins ? c->eng_level_bins + 1 : nb1;
+  c->eng_level_bins = 0;  // the hint covers one level
+  if (level_nb1 > engine_max_nb1(c->eng.cols))
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "tree engine: 16 columns x (bins+1) of the level must fit 225 KB (bins <= 1199)");
   const int64_t ncell = (int64_t)n_nodes * c->eng.cols;
   if (clear) {
     CK(cudaMemsetAsync(d_acc, 0, sizeof(int64_t) * (size_t)(ncell * nb1 * 3), c->stream));
@@ -415,9 +418,16 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
   c->stats.launches = 1 + (clear ? 1 : 0);  // hist (+ init_enc)
   c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * 16.0 + (double)ncell * nb1 * 3 * 8.0;
   CK(cudaEventRecord(c->ev0, c->stream));
-  CK(engine_build_level(c->eng, n_nodes, d_descs, nb1, d_acc, d_min2_enc, d_maxin_enc, c->stream));
+  CK(engine_build_level(c->eng, n_nodes, d_descs, nb1, level_nb1, d_acc, d_min2_enc, d_maxin_enc, c->stream));
   CK(cudaEventRecord(c->ev1, c->stream));
   c->timed = true;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_level_bins(h2ok_ctx* c, int32_t level_bins) {
+  REQUIRE(c != nullptr, "null context");
+  REQUIRE(level_bins >= 0 && level_bins <= H2OK_MAX_BINS, "level_bins outside [0, H2OK_MAX_BINS]");
+  c->eng_level_bins = level_bins;
   return H2OK_OK;
 }
 
@@ -697,6 +707,12 @@ int32_t h2ok_hist_last_level_stats(h2ok_ctx* c, h2ok_stats* out) {
       CK(cudaMemcpyAsync(&e, c->rec_err.p, sizeof(e), cudaMemcpyDeviceToHost, c->stream));
       CK(cudaStreamSynchronize(c->stream));
       c->stats.range_errors = e;
+    }
+    if (c->eng_ready && c->eng.err) {  // (node, column) pairs wider than a tree_level_bins hint allowed
+      int32_t e = 0;
+      CK(cudaMemcpyAsync(&e, c->eng.err, sizeof(e), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      c->stats.range_errors += e;
     }
   }
   *out = c->stats;

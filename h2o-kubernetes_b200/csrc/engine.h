@@ -49,6 +49,7 @@ struct Engine {
   int32_t* tile_cnt = nullptr;          // [max_tiles + 1][2] records of each tile going left / right (then scanned)
   int32_t* slot_start = nullptr;        // [2 * kEngMaxNodes] first record of child slot 2 * node + way in the next order
   int32_t* leaf = nullptr;              // [rows] leaf code of every row (original order), -1 while still in the tree
+  int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
   int64_t max_tiles = 0;
 };
 
@@ -61,10 +62,11 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
 // new tree: every row at the root, records in row order
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
                               cudaStream_t s);
-// one level's histogram pass
-cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int64_t* acc,
+// one level's histogram pass.  nb1 = bins + 1 of the accumulators' layout; level_nb1 (0: same as nb1) = bins + 1 of
+// the widest histogram of THIS level, which sizes the shared histogram (H2O halves nbins_top_level per level)
+cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int level_nb1, int64_t* acc,
                                uint32_t* min2_enc, uint32_t* maxin_enc, cudaStream_t s);
-// the largest max_bins + 1 one histogram CTA can hold for this shard's column count
+// the largest bins + 1 a level may use (16 columns per block must fit the shared memory)
 int engine_max_nb1(int cols);
 // route rows with the level's splits, retire rows into leaves, regroup the records by child
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,

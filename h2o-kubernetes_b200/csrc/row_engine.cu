@@ -88,10 +88,12 @@ struct EngHistArgs {
   const int32_t* seg;
   int n_nodes;
   const h2ok_col_desc* descs;
-  int nb1;
+  int nb1;  // bins + 1 of the global accumulators (row stride of acc / hist)
+  int nbs;  // bins + 1 of the shared histogram: the most any node of THIS level uses (<= nb1)
   int64_t* acc;
   uint32_t* min2_enc;
   uint32_t* maxin_enc;
+  int32_t* err;  // counts (node, column) pairs with more bins than the level's shared histogram holds
 };
 
 // 32-bit shared-window addressing: keeps the per-cell address math to one IMAD (no generic->shared conversion)
@@ -138,7 +140,9 @@ __device__ __forceinline__ bool wrapped(unsigned old, int v) { return (old > ~(u
 // cold path looks at the saved old values again to find which.  wq == 0 rows (weighted only) are turned into NaNs
 // that add zeros: the NA bin gets +0 and the running extremes ignore NaN — which is what skipping the row means.
 // v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
-template <int CPL, bool WEIGHTED, int U>
+// LPR = lanes per row (32, or 16 for levels whose histograms are too wide for 32 columns per block): a bin of one
+// column slot is 3 channels x LPR lanes x 4 bytes.
+template <int CPL, bool WEIGHTED, int U, int LPR>
 __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[CPL], const typename XVec<CPL>::type (&xv)[U],
                                          const int (&w)[U], unsigned (&pa)[U * CPL]) {
   float xs[U][CPL];
@@ -150,7 +154,7 @@ __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[C
       if (WEIGHTED) x = w[j] != 0 ? x : __int_as_float(0x7FC00000);
       xs[j][k] = x;
       const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
-      pa[j * CPL + k] = hb[k] + (unsigned)b * 384u;
+      pa[j * CPL + k] = hb[k] + (unsigned)b * (12u * LPR);
     }
   }
   // running extremes (NaN-ignoring and exact), two rows at a time: min(min(m, a), b) is one three-input FMNMX3
@@ -168,7 +172,7 @@ __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[C
   }
 }
 
-template <int CPL, bool WEIGHTED, int U>
+template <int CPL, bool WEIGHTED, int U, int LPR>
 __device__ __forceinline__ void eng_accum(const EngHistArgs& a, const unsigned (&hb)[CPL], int node, int col_lane,
                                           const unsigned (&pa)[U * CPL], const int (&v1)[U], const int (&v2)[U],
                                           const int (&w)[U]) {
@@ -180,8 +184,8 @@ __device__ __forceinline__ void eng_accum(const EngHistArgs& a, const unsigned (
       const unsigned p = pa[j * CPL + k];
       if (WEIGHTED) o0[j * CPL + k] = sh_add(p, (unsigned)w[j]);
       else sh_inc(p);
-      o1[j * CPL + k] = sh_add(p + 128u, (unsigned)v1[j]);
-      o2[j * CPL + k] = sh_add(p + 256u, (unsigned)v2[j]);
+      o1[j * CPL + k] = sh_add(p + 4u * LPR, (unsigned)v1[j]);
+      o2[j * CPL + k] = sh_add(p + 8u * LPR, (unsigned)v2[j]);
     }
   }
   bool any = false;
@@ -201,7 +205,7 @@ __device__ __forceinline__ void eng_accum(const EngHistArgs& a, const unsigned (
       const bool e1 = wrapped(o1[i], v1[j]), e2 = wrapped(o2[i], v2[j]);
       const bool ev = WEIGHTED ? o0[WEIGHTED ? i : 0] > ~(unsigned)w[j] : false;
       if (ev | e1 | e2) {
-        const int b = (int)((pa[i] - hb[k]) / 384u);
+        const int b = (int)((pa[i] - hb[k]) / (12u * LPR));
         eng_carry(a.acc, a.descs, node, a.cols, col_lane + k, a.nb1, b, ev ? 1 : 0, e1 ? (v1[j] < 0 ? -1 : 1) : 0,
                   e2 ? (v2[j] < 0 ? -1 : 1) : 0);
       }
@@ -226,18 +230,20 @@ struct EngCfg {
 // count word holds the weight sum, not the number of rows.
 constexpr int kEngMeanSample = 1024;
 
-template <int CPL, bool WEIGHTED>
+template <int CPL, bool WEIGHTED, int LPR>
 __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
   using V = typename XVec<CPL>::type;
-  constexpr int THREADS = EngCfg<CPL, WEIGHTED>::threads, U = EngCfg<CPL, WEIGHTED>::U, NW = THREADS / 32;
+  constexpr int THREADS = EngCfg<CPL, WEIGHTED>::threads, NW = THREADS / 32;
+  constexpr int U = LPR == 16 && !WEIGHTED ? 4 : EngCfg<CPL, WEIGHTED>::U;  // (the 16-lane layout spills at eight rows)
   extern __shared__ __align__(16) unsigned h[];
   __shared__ unsigned s_mn[CPL * 32], s_mx[CPL * 32];
   __shared__ unsigned char s_tracked[CPL * 32];
   __shared__ int s_m[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nb1 = a.nb1;
-  const int triples = CPL * nb1 * 32;
-  const int col_lane = (int)blockIdx.y * 32 * CPL + lane * CPL;
+  const int nb1 = a.nb1, nbs = a.nbs;
+  const int triples = CPL * nbs * LPR;
+  const bool on = LPR == 32 || lane < LPR;  // with 16 lanes per row the upper half of every warp only loads and prefetches
+  const int col_lane = (int)blockIdx.y * LPR * CPL + (lane & (LPR - 1)) * CPL;
   const int n_nodes = min(a.n_nodes, a.seg[kSegNodes]);  // the table's own count bounds every read of it
   if (n_nodes < 1) return;
   const int64_t live = a.seg[n_nodes];
@@ -246,12 +252,12 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
   if (p0 >= p1) return;
   int node = seg_of(a.seg, n_nodes, p0);
 
-  for (int i = tid; i < triples * 3; i += THREADS) h[i] = ((i >> 5) % 3 == 0) ? 0u : kWyBias;
+  for (int i = tid; i < triples * 3; i += THREADS) h[i] = ((i / LPR) % 3 == 0) ? 0u : kWyBias;
 
   unsigned hb[CPL];  // shared address of (slot k, bin 0, channel 0, this lane)
 #pragma unroll
   for (int k = 0; k < CPL; k++) {
-    hb[k] = (unsigned)__cvta_generic_to_shared(h) + lane * 4 + (unsigned)(k * nb1) * 384u;
+    hb[k] = (unsigned)__cvta_generic_to_shared(h) + (lane & (LPR - 1)) * 4 + (unsigned)(k * nbs) * (12u * LPR);
     asm volatile("" : "+r"(hb[k]));  // keep it in a register: recomputing it costs seven instructions per cell
   }
   // lanes past the last column read the row's last CPL floats instead (never accumulated: their columns are untracked)
@@ -276,9 +282,10 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
       tracked[k] = false;
       c.nb[k] = 1;
       c.mn[k] = c.st[k] = 0.0;
-      if (col < a.cols) {
+      if (on && col < a.cols) {
         const h2ok_col_desc d = a.descs[(int64_t)node * a.cols + col];
-        if (d.nbin > 0) {
+        if (d.nbin >= nbs) atomicAdd(a.err, 1);  // the caller's level_bins hint was too small: counted, not accumulated
+        else if (d.nbin > 0) {
           tracked[k] = true;
           c.nb[k] = d.nbin;
           c.mn[k] = d.min;
@@ -335,8 +342,10 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         v2[0] = (int)r.y - m2;
         w[0] = WEIGHTED ? __ldg(gw + q) : 1;
         unsigned pa[CPL];
-        eng_bins<CPL, WEIGHTED, 1>(c, hb, x, w, pa);
-        eng_accum<CPL, WEIGHTED, 1>(a, hb, node, col_lane, pa, v1, v2, w);
+        if (on) {
+          eng_bins<CPL, WEIGHTED, 1, LPR>(c, hb, x, w, pa);
+          eng_accum<CPL, WEIGHTED, 1, LPR>(a, hb, node, col_lane, pa, v1, v2, w);
+        }
       };
       auto load_idx = [&](int q, int (&idx)[U]) {
         if (U % 4 == 0) {
@@ -377,12 +386,12 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
 #pragma unroll
         for (int j = 0; j < U; j++) w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
         unsigned pa[U * CPL];
-        eng_bins<CPL, WEIGHTED, U>(c, hb, x, w, pa);
+        if (on) eng_bins<CPL, WEIGHTED, U, LPR>(c, hb, x, w, pa);
         if (more) {
 #pragma unroll
           for (int j = 0; j < U; j++) prefetch_l2(xrow + (uint64_t)(unsigned)nx[j] * ldt4);
         }
-        eng_accum<CPL, WEIGHTED, U>(a, hb, node, col_lane, pa, v1, v2, w);
+        if (on) eng_accum<CPL, WEIGHTED, U, LPR>(a, hb, node, col_lane, pa, v1, v2, w);
       }
       for (; p < send; p++) one_row(p);  // the run's last, partial batch
     }
@@ -397,7 +406,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     }
     __syncthreads();
     if (tid < CPL * 32 && s_tracked[tid]) {
-      const int col = (int)blockIdx.y * 32 * CPL + (tid & 31) * CPL + (tid >> 5);
+      const int col = (int)blockIdx.y * LPR * CPL + (tid & 31) * CPL + (tid >> 5);
       const unsigned e0 = s_mn[tid], e1 = s_mx[tid];
       if (e0 != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)node * a.cols + col], e0);
       if (e1 != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)node * a.cols + col], e1);
@@ -405,16 +414,16 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     // flush the touched (slot, bin, lane) triples to the 64-bit global accumulators, undo the centring with the
     // triple's own count, and re-arm the words for the next node
     for (int t = tid; t < triples; t += THREADS) {
-      const int kb = t >> 5, ln = t & 31;
-      unsigned* w0 = h + (kb * 3) * 32 + ln;
-      const unsigned c0 = w0[0], u1 = w0[32], u2 = w0[64];
+      const int kb = t / LPR, ln = t % LPR;
+      unsigned* w0 = h + (kb * 3) * LPR + ln;
+      const unsigned c0 = w0[0], u1 = w0[LPR], u2 = w0[2 * LPR];
       if (c0 | (u1 ^ kWyBias) | (u2 ^ kWyBias)) {
         w0[0] = 0u;
-        w0[32] = kWyBias;
-        w0[64] = kWyBias;
-        const int k = kb / nb1, b = kb - k * nb1;
+        w0[LPR] = kWyBias;
+        w0[2 * LPR] = kWyBias;
+        const int k = kb / nbs, b = kb - k * nbs;
         if (s_tracked[k * 32 + ln]) {
-          const int col = (int)blockIdx.y * 32 * CPL + ln * CPL + k;
+          const int col = (int)blockIdx.y * LPR * CPL + ln * CPL + k;
           unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col) * nb1 + b) * 3;
           const long long s1 = (long long)u1 - (long long)kWyBias + (long long)c0 * m1;
           const long long s2 = (long long)u2 - (long long)kWyBias + (long long)c0 * m2;
@@ -707,6 +716,8 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   A((void**)&e.tile_order, sizeof(int32_t) * (size_t)(e.max_tiles + 1));
   A((void**)&e.slot_start, sizeof(int32_t) * 2 * kEngMaxNodes);
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
+  A((void**)&e.err, sizeof(int32_t));
+  if (err == cudaSuccess) err = cudaMemset(e.err, 0, sizeof(int32_t));
   if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   if (err != cudaSuccess) engine_free(e);
   return err;
@@ -719,7 +730,8 @@ void engine_free(Engine& e) {
     e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr;
   }
   cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.tile_order); cudaFree(e.slot_start);
-  cudaFree(e.leaf);
+  cudaFree(e.leaf); cudaFree(e.err);
+  e.err = nullptr;
   e.XT = nullptr;
   e.codes = nullptr;
   e.tile_base = e.tile_cnt = e.tile_order = e.slot_start = e.leaf = nullptr;
@@ -755,37 +767,43 @@ cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* 
   return cudaGetLastError();
 }
 
-static int eng_cpl(int cols, int nb1) {
-  if (cols > 32 && (size_t)64 * nb1 * 12 <= (size_t)kHistSmemCap) return 2;
-  if ((size_t)32 * nb1 * 12 <= (size_t)kHistSmemCap) return 1;
-  return 0;
+// columns per block = lanes per row x columns per lane: the widest layout whose shared histogram fits
+struct EngLayout {
+  int cpl, lpr;
+};
+static EngLayout eng_layout(int cols, int nbs) {
+  if (cols > 32 && (size_t)64 * nbs * 12 <= (size_t)kHistSmemCap) return {2, 32};
+  if ((size_t)32 * nbs * 12 <= (size_t)kHistSmemCap) return {1, 32};
+  if ((size_t)16 * nbs * 12 <= (size_t)kHistSmemCap) return {1, 16};
+  return {0, 0};
 }
 
 int engine_max_nb1(int cols) {
   (void)cols;
-  return kHistSmemCap / (32 * 12);
+  return kHistSmemCap / (16 * 12);
 }
 
-template <int CPL, bool W>
+template <int CPL, bool W, int LPR>
 static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
   static bool attr_done[64] = {};  // per device, per instantiation
   int dev = 0;
   cudaGetDevice(&dev);
   bool& attr = attr_done[dev & 63];
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
     if (e != cudaSuccess) return e;
     attr = true;
   }
-  eng_hist_kernel<CPL, W><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
+  eng_hist_kernel<CPL, W, LPR><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
   return cudaGetLastError();
 }
 
-cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int64_t* acc,
+cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int level_nb1, int64_t* acc,
                                uint32_t* min2_enc, uint32_t* maxin_enc, cudaStream_t s) {
   if (n_nodes < 1 || n_nodes >= kEngMaxNodes) return cudaErrorInvalidValue;
-  const int cpl = eng_cpl(e.cols, nb1);
-  if (!cpl) return cudaErrorInvalidValue;
+  const int nbs = level_nb1 > 0 && level_nb1 < nb1 ? level_nb1 : nb1;
+  const EngLayout lay = eng_layout(e.cols, nbs);
+  if (!lay.cpl) return cudaErrorInvalidValue;
   e.n_nodes = n_nodes;
   EngHistArgs a{};
   a.XT = e.XT;
@@ -798,19 +816,23 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   a.n_nodes = n_nodes;
   a.descs = descs;
   a.nb1 = nb1;
+  a.nbs = nbs;
   a.acc = acc;
   a.min2_enc = min2_enc;
   a.maxin_enc = maxin_enc;
-  const int colblk = 32 * cpl;
+  a.err = e.err;
+  const int colblk = lay.lpr * lay.cpl;
   // one CTA per SM and column block; every CTA owns the same share of the level's records
   const dim3 grid((unsigned)kSMs, (unsigned)((e.cols + colblk - 1) / colblk));
-  const size_t smem = (size_t)colblk * nb1 * 12;
+  const size_t smem = (size_t)colblk * nbs * 12;
   if (e.weighted) {
-    if (cpl == 2) return launch_eng_hist<2, true>(a, grid, smem, s);
-    return launch_eng_hist<1, true>(a, grid, smem, s);
+    if (lay.cpl == 2) return launch_eng_hist<2, true, 32>(a, grid, smem, s);
+    if (lay.lpr == 32) return launch_eng_hist<1, true, 32>(a, grid, smem, s);
+    return launch_eng_hist<1, true, 16>(a, grid, smem, s);
   }
-  if (cpl == 2) return launch_eng_hist<2, false>(a, grid, smem, s);
-  return launch_eng_hist<1, false>(a, grid, smem, s);
+  if (lay.cpl == 2) return launch_eng_hist<2, false, 32>(a, grid, smem, s);
+  if (lay.lpr == 32) return launch_eng_hist<1, false, 32>(a, grid, smem, s);
+  return launch_eng_hist<1, false, 16>(a, grid, smem, s);
 }
 
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,

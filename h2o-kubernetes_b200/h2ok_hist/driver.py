@@ -141,7 +141,7 @@ class CudaShard:
         self.descs[:n].copy_(self.child_descs[:n])
 
     # ---- a3/a4: local histogram --------------------------------------------------------------------------
-    def build_level(self, n_nodes):
+    def build_level(self, n_nodes, level_bins=0):
         self.lib.call("h2ok_hist_build_level_dev", self.ctx, _ptr(self.X), self.ld, self.rows, self.cols, _ptr(self.nid),
                       _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
@@ -275,7 +275,9 @@ class EngineShard(CudaShard):
     def reset_nodes(self):
         pass  # tree_begin_dev put every row back at the root
 
-    def build_level(self, n_nodes):
+    def build_level(self, n_nodes, level_bins=0):
+        if level_bins:
+            self.lib.call("h2ok_hist_tree_level_bins", self.ctx, int(level_bins))
         self.lib.call("h2ok_hist_tree_build_level_dev", self.ctx, n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
         self.launches += 2  # init_enc + histogram pass
@@ -362,7 +364,8 @@ class LevelDriver:
         children are known and before the row map and descriptors are overwritten (tests read the level there)."""
         sh, p = self.shard, self.params
         n = self.n_nodes
-        acc, mn, mx = sh.build_level(n)
+        # H2O halves nbins_top_level per level (Split.nextLevelHistos: max(parent bins >> 1, nbins))
+        acc, mn, mx = sh.build_level(n, level_bins=max(p.nbins, p.nbins_top_level >> self.depth))
         reduce_level(acc, mn, mx)
         sh.finalize_level(n)
         sh.find_splits(n, p.min_rows, p.min_split_improvement)

@@ -218,8 +218,8 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
  * Call order: tree_create -> tree_load_cols_dev for every block of columns (in any order; the caller's column-major
  * block can be freed or reused afterwards) -> per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce /
  * finalize / find_splits / next_level as usual], tree_apply_splits_dev.  Device memory: rows * (4 * cols rounded up
- * to 8 + 29) bytes, + 8 per row for weighted shards.  Limits: rows < 2^31 - 2048; (max_bins + 1) <= 600 (one
- * 32-column block of the shared histogram must fit 225 KB). */
+ * to 8 + 29) bytes, + 8 per row for weighted shards.  Limits: rows < 2^31 - 2048; every bin count up to
+ * H2OK_MAX_BINS runs (64 columns per block up to 299 bins + NA, 32 up to 599, 16 beyond). */
 int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
 /* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in
@@ -231,6 +231,12 @@ int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* ctx, const int32_t* d_wq, const int32
  * previous tree_apply_splits_dev produced (1 after tree_begin_dev). */
 int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* ctx, int32_t n_nodes, const h2ok_col_desc* d_descs, int32_t max_bins,
                                        int32_t clear, int64_t* d_acc, uint32_t* d_min2_enc, uint32_t* d_maxin_enc);
+/* Optional hint for the NEXT tree_build_level_dev only: no node of that level has more than level_bins bins (H2O
+ * halves nbins_top_level per level: level d uses max(nbins, nbins_top_level >> d)).  The shared histogram is then
+ * sized for the level instead of for max_bins, which keeps 64 columns per block at 256 bins and lets a 1024-bin root
+ * level run (16 columns per block).  A descriptor with more bins than the hint is not accumulated and counted in
+ * h2ok_stats.range_errors. */
+int32_t h2ok_hist_tree_level_bins(h2ok_ctx* ctx, int32_t level_bins);
 /* a6 for the current level + regrouping of the records by child.  Child ids must be numbered in slot order
  * (2 * node + way), which is what next_level_dev produces; last_level is accepted for symmetry and not needed
  * (with every child id -1 all rows retire). */

@@ -50,7 +50,7 @@ class CpuShard:
     def adopt_children(self, n):
         self.descs = self.child[:n].copy()
 
-    def build_level(self, n):
+    def build_level(self, n, level_bins=0):
         acc, min2, maxin = self.oracle.build_level_q(self.X, self.rows, self.nid, self.wq, self.wyq, self.wyyq,
                                                      self.descs[:n], self.max_bins)
         self.acc = torch.from_numpy(acc)

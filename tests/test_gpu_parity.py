@@ -643,6 +643,35 @@ def test_engine_column_blocks(eshard, oracle, cols, nbins, weight_mode):
     assert levels == 4
 
 
+@pytest.mark.parametrize("cols,weight_mode", [(40, 0), (9, 1)])
+def test_engine_h2o_default_bins(eshard, oracle, cols, weight_mode):
+    """H2O's GBM defaults: nbins 20, nbins_top_level 1024 (halved per level).  The root level's 1025-slot histograms only
+    fit 16 columns per block; deeper levels are sized by the level-bins hint LevelDriver passes."""
+    rows = 50021
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 31, 0, rows, cols, na_permille=10, weight_mode=weight_mode)
+    params = abi.Params.make(nbins=20, nbins_top_level=1024, max_depth=5, min_rows=10)
+    levels, _ = run_tree_both(eshard, oracle, X, rows, y, w, params)
+    assert levels == 5
+    assert eshard.stats().range_errors == 0
+
+
+def test_engine_level_bins_hint_too_small_is_counted(eshard, oracle):
+    """A level-bins hint below a node's real bin count must not corrupt memory: the pair is skipped and counted."""
+    from h2ok_hist.driver import LevelDriver
+
+    rows, cols = 5000, 4
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 3, 0, rows, cols)
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()))
+    drv = LevelDriver(eshard, abi.Params.make(nbins=64, max_depth=3))
+    drv.prepare_data()
+    drv.prepare_tree()
+    acc, _, _ = eshard.build_level(1, level_bins=8)  # the root descriptors have 64 bins
+    torch.cuda.synchronize()
+    assert eshard.stats().range_errors > 0
+    tracked = eshard.descs_np(1)["nbin"][0] > 0
+    assert int(acc[0][torch.from_numpy(tracked).cuda()].abs().sum()) == 0
+
+
 def test_engine_rejects_what_it_cannot_hold(lib):
     h = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(h))
@@ -652,9 +681,11 @@ def test_engine_rejects_what_it_cannot_hold(lib):
             lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 256, 1, P(buf), P(buf), P(buf))
         assert e.value.code == abi.ERR_STATE
         lib.call("h2ok_hist_tree_create", h, 1000, 2, 0)
-        with pytest.raises(capi.H2okError) as e:  # 32 columns x 1025 bins x 12 B do not fit 225 KB
-            lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 1024, 1, P(buf), P(buf), P(buf))
+        with pytest.raises(capi.H2okError) as e:  # more bins than the ABI allows
+            lib.call("h2ok_hist_tree_build_level_dev", h, 1, P(buf), 1025, 1, P(buf), P(buf), P(buf))
         assert e.value.code == abi.ERR_UNSUPPORTED and "max_bins" in str(e.value)
+        with pytest.raises(capi.H2okError):
+            lib.call("h2ok_hist_tree_level_bins", h, -1)
         with pytest.raises(capi.H2okError) as e:  # a column block outside the shard
             lib.call("h2ok_hist_tree_load_cols_dev", h, 1, 2, P(buf), 1000)
         assert e.value.code == abi.ERR_ARG
