@@ -606,6 +606,9 @@ int32_t h2ok_hist_build_level(h2ok_ctx* c, int32_t n_nodes, const h2ok_col_desc*
   CK(c->descs.ensure(ncell)); CK(c->acc.ensure(ncell * nb1 * 3)); CK(c->hist.ensure(ncell * nb1 * 3));
   CK(c->mn.ensure(ncell)); CK(c->mx.ensure(ncell)); CK(c->min2.ensure(ncell)); CK(c->maxin.ensure(ncell));
   CK(cudaMemcpyAsync(c->descs.p, descs, sizeof(h2ok_col_desc) * ncell, cudaMemcpyHostToDevice, c->stream));
+  int32_t level_bins = 1;  // the descriptors are on the host: size the shared histogram for this level's widest one
+  for (size_t i = 0; i < ncell; i++) level_bins = descs[i].nbin > level_bins ? descs[i].nbin : level_bins;
+  c->eng_level_bins = level_bins < max_bins ? level_bins : 0;
   rc = h2ok_hist_tree_build_level_dev(c, n_nodes, c->descs.p, max_bins, 1, c->acc.p, c->mn.p, c->mx.p);
   if (rc) return rc;
   rc = h2ok_hist_finalize_level_dev(c, c->acc.p, c->mn.p, c->mx.p, n_nodes, c->cols, max_bins, &c->q, c->hist.p,

@@ -353,10 +353,11 @@ def test_tree_top_level_bins_shrink(tree_shard, oracle):
 
 
 # ------------------------------------------------------------------------------------------------ host-buffer ABI
-def test_host_buffer_entry_points(oracle, lib):
-    rows, cols, nb = 40003, 7, 64
+@pytest.mark.parametrize("nbins,top", [(64, None), (20, 1024)])
+def test_host_buffer_entry_points(oracle, lib, nbins, top):
+    rows, cols, nb = 40003, 7, max(nbins, top or nbins)
     X, y, w = oracle.synth(abi.SHAPE_WIDE64, 12, 0, rows, cols, na_permille=10, weight_mode=1)
-    p = abi.Params.make(nbins=nb, max_depth=3)
+    p = abi.Params.make(nbins=nbins, nbins_top_level=top, max_depth=3)
     h = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(h))
     try:
