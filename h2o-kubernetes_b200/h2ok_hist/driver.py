@@ -295,16 +295,16 @@ def _world():
 
 def reduce_level(acc, mn, mx):
     """a5 — MRTask.reduce / DHistogram.add across ranks: integer sum of the fixed-point histogram, integer min / max
-    of the encoded observed ranges.  The encodings are unsigned; flipping the top bit makes signed min/max agree."""
+    of the encoded observed ranges.  The encodings are unsigned; flipping the top bit makes signed compares agree,
+    and min(a) = ~max(~a) folds the two range reductions into ONE max all-reduce."""
     if _world() == 1:
         return
     dist.all_reduce(acc, op=dist.ReduceOp.SUM)
-    mn ^= _I32_SIGN
-    mx ^= _I32_SIGN
-    dist.all_reduce(mn, op=dist.ReduceOp.MIN)
-    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    mn ^= _I32_SIGN
-    mx ^= _I32_SIGN
+    n = mn.numel()
+    buf = torch.cat([~(mn.reshape(-1) ^ _I32_SIGN), mx.reshape(-1) ^ _I32_SIGN])
+    dist.all_reduce(buf, op=dist.ReduceOp.MAX)
+    mn.copy_(((~buf[:n]) ^ _I32_SIGN).view_as(mn))
+    mx.copy_((buf[n:] ^ _I32_SIGN).view_as(mx))
 
 
 class LevelDriver:
