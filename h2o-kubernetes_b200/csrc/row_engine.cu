@@ -131,8 +131,15 @@ struct EngLane {
   float fmn[CPL], fmx[CPL];
 };
 
-// a signed value v was added to a word that held `old`: did the 32-bit word wrap, and which way?
-__device__ __forceinline__ bool wrapped(unsigned old, int v) { return (old > ~(unsigned)v) != (v < 0); }
+// A signed value v (|v| < 2^31) was added to a word that held `old`; did the 32-bit word wrap?  Bit 31 of the result
+// is set when it did: the word crossed between its halves (old and new differ in bit 31) in the direction that cannot
+// be reached without leaving the range (old's bit 31 differs from v's sign).
+__device__ __forceinline__ unsigned wrap_bit(unsigned old, int v) {
+  const unsigned n = old + (unsigned)v;
+  return (old ^ n) & (old ^ (unsigned)v);
+}
+// __byte_perm selectors that put byte 3 of the second operand into byte 0 / 1 / 2 / 3 of the first
+__device__ constexpr unsigned kPark[4] = {0x3217u, 0x3270u, 0x3710u, 0x7210u};
 
 // U rows x CPL cells in three phases, so that the independent cells overlap their latencies instead of running one
 // behind the other: (1) eng_bins: every cell's bin and shared address — after it the row values are dead and their
@@ -188,22 +195,31 @@ __device__ __forceinline__ void eng_accum(const EngHistArgs& a, const unsigned (
       o2[j * CPL + k] = sh_add(p + 8u * LPR, (unsigned)v2[j]);
     }
   }
-  bool any = false;
+  // Wrap flags without predicates: bit 31 of (old ^ new) & (old ^ v) says that the add wrapped the word (see
+  // wrap_bit).  The top byte of every flag word is parked in a byte of a mask register with one PRMT, four flags per
+  // register; one test of the masks decides whether the cold path runs, and the cold path reads the parked bytes.
+  constexpr int PER = WEIGHTED ? 3 : 2, NF = PER * U * CPL, NM = (NF + 3) / 4;
+  unsigned m[NM];
 #pragma unroll
-  for (int j = 0; j < U; j++) {
+  for (int i = 0; i < NM; i++) m[i] = 0;
 #pragma unroll
-    for (int k = 0; k < CPL; k++) {
-      any |= wrapped(o1[j * CPL + k], v1[j]);
-      any |= wrapped(o2[j * CPL + k], v2[j]);
-      if (WEIGHTED) any |= o0[j * CPL + k] > ~(unsigned)w[j];
-    }
+  for (int i = 0; i < U * CPL; i++) {
+    const int j = i / CPL;
+    const int f0 = PER * i, f1 = PER * i + 1, f2 = PER * i + 2;
+    m[f0 >> 2] = __byte_perm(m[f0 >> 2], wrap_bit(o1[i], v1[j]), kPark[f0 & 3]);
+    m[f1 >> 2] = __byte_perm(m[f1 >> 2], wrap_bit(o2[i], v2[j]), kPark[f1 & 3]);
+    if (WEIGHTED) m[f2 >> 2] = __byte_perm(m[f2 >> 2], wrap_bit(o0[WEIGHTED ? i : 0], w[j]), kPark[f2 & 3]);
   }
-  if (any) {  // fully unrolled: dynamic indexing would push the saved values into local memory on the hot path too
+  unsigned any = 0;
+#pragma unroll
+  for (int i = 0; i < NM; i++) any |= m[i];
+  if (any & 0x80808080u) {
 #pragma unroll
     for (int i = 0; i < U * CPL; i++) {
       const int j = i / CPL, k = i - j * CPL;
-      const bool e1 = wrapped(o1[i], v1[j]), e2 = wrapped(o2[i], v2[j]);
-      const bool ev = WEIGHTED ? o0[WEIGHTED ? i : 0] > ~(unsigned)w[j] : false;
+      const int f0 = PER * i, f1 = PER * i + 1, f2 = PER * i + 2;
+      const bool e1 = (m[f0 >> 2] >> (8 * (f0 & 3) + 7)) & 1u, e2 = (m[f1 >> 2] >> (8 * (f1 & 3) + 7)) & 1u;
+      const bool ev = WEIGHTED ? (m[(WEIGHTED ? f2 : 0) >> 2] >> (8 * (f2 & 3) + 7)) & 1u : false;
       if (ev | e1 | e2) {
         const int b = (int)((pa[i] - hb[k]) / (12u * LPR));
         eng_carry(a.acc, a.descs, node, a.cols, col_lane + k, a.nb1, b, ev ? 1 : 0, e1 ? (v1[j] < 0 ? -1 : 1) : 0,
