@@ -142,9 +142,8 @@ __device__ __forceinline__ unsigned wrap_bit(unsigned old, int v) {
 __device__ constexpr unsigned kPark[4] = {0x3217u, 0x3270u, 0x3710u, 0x7210u};
 
 // U rows x CPL cells in three phases, so that the independent cells overlap their latencies instead of running one
-// behind the other: (1) eng_bins: every cell's bin and shared address — after it the row values are dead and their
-// registers take the next batch's rows; (2) every cell's atomics; (3) ONE test for "some 32-bit word wrapped".  The
-// cold path looks at the saved old values again to find which.  wq == 0 rows (weighted only) are turned into NaNs
+// behind the other: (1) eng_bins: every cell's bin and shared address; (2) every cell's atomics; (3) ONE test for
+// "some 32-bit word wrapped" over flag bytes parked in mask registers, which the cold path reads.  wq == 0 rows (weighted only) are turned into NaNs
 // that add zeros: the NA bin gets +0 and the running extremes ignore NaN — which is what skipping the row means.
 // v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
 // LPR = lanes per row (32, or 16 for levels whose histograms are too wide for 32 columns per block): a bin of one
