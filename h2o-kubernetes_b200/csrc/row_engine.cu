@@ -104,6 +104,20 @@ __device__ __forceinline__ unsigned sh_add(unsigned addr, unsigned v) {
   return o;
 }
 
+// base + idx * pitch in ONE instruction (IMAD.WIDE.U32 with the 64-bit base as addend); written as C the compiler adds
+// the zero high half of the pitch separately
+__device__ __forceinline__ const char* row_addr(const char* base, unsigned idx, unsigned pitch) {
+  unsigned long long r;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(idx), "r"(pitch), "l"((unsigned long long)base));
+  return reinterpret_cast<const char*>(r);
+}
+// hb + b * pitch in one IMAD (the compiler splits it when b comes out of a select)
+__device__ __forceinline__ unsigned cell_addr(unsigned hb, unsigned b, unsigned pitch) {
+  unsigned r;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(b), "r"(pitch), "r"(hb));
+  return r;
+}
+
 // cold: a 32-bit shared word wrapped; the carry / borrow goes straight to the 64-bit global accumulator
 __device__ __noinline__ void eng_carry(int64_t* acc, const h2ok_col_desc* __restrict__ descs, int node, int cols, int col,
                                        int nb1, int b, int d0, int d1, int d2) {
@@ -160,7 +174,7 @@ __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[C
       if (WEIGHTED) x = w[j] != 0 ? x : __int_as_float(0x7FC00000);
       xs[j][k] = x;
       const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
-      pa[j * CPL + k] = hb[k] + (unsigned)b * (12u * LPR);
+      pa[j * CPL + k] = cell_addr(hb[k], (unsigned)b, 12u * LPR);
     }
   }
   // running extremes (NaN-ignoring and exact), two rows at a time: min(min(m, a), b) is one three-input FMNMX3
@@ -236,7 +250,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 template <int CPL, bool WEIGHTED>
 struct EngCfg {
   static constexpr int threads = 1024;
-  static constexpr int U = WEIGHTED ? 4 / CPL : 8 / CPL;  // 8, 4 (unweighted) or 4, 2 (weighted): even
+  static constexpr int U = WEIGHTED ? 4 / CPL : (CPL == 1 ? 6 : 4);  // 6, 4 (unweighted) or 4, 2 (weighted): even
 };
 
 // The wY and wYY words hold the sum of (target - M) for an offset M close to the run's mean target, so that they
@@ -351,7 +365,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
       auto one_row = [&](int q) {
         int v1[1], v2[1], w[1];
         V x[1];
-        x[0] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)__ldg(gidx + q) * ldt4));
+        x[0] = __ldg(reinterpret_cast<const V*>(row_addr(xrow, (unsigned)__ldg(gidx + q), ldt4)));
         const uint2 r = __ldg(gval + q);
         v1[0] = (int)r.x - m1;
         v2[0] = (int)r.y - m2;
@@ -387,7 +401,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         int v1[U], v2[U], w[U];
         V x[U];
 #pragma unroll
-        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(xrow + (uint64_t)(unsigned)nx[j] * ldt4));
+        for (int j = 0; j < U; j++) x[j] = __ldg(reinterpret_cast<const V*>(row_addr(xrow, (unsigned)nx[j], ldt4)));
         const bool more = p + stride + U <= send;
         if (more) load_idx(p + stride, nx);
 #pragma unroll
@@ -404,7 +418,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         if (on) eng_bins<CPL, WEIGHTED, U, LPR>(c, hb, x, w, pa);
         if (more) {
 #pragma unroll
-          for (int j = 0; j < U; j++) prefetch_l2(xrow + (uint64_t)(unsigned)nx[j] * ldt4);
+          for (int j = 0; j < U; j++) prefetch_l2(row_addr(xrow, (unsigned)nx[j], ldt4));
         }
         if (on) eng_accum<CPL, WEIGHTED, U, LPR>(a, hb, node, col_lane, pa, v1, v2, w);
       }
