@@ -389,11 +389,12 @@ int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* c, int32_t col0, int32_t ncols, c
   return H2OK_OK;
 }
 
-int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* c, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq) {
+int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* c, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq,
+                                 const h2ok_quant* q) {
   REQUIRE(c && d_wyq && d_wyyq, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_begin_dev before tree_create");
   REQUIRE(!c->eng.weighted || d_wq, "weighted engine needs d_wq");
-  CK(engine_begin_tree(c->eng, d_wq, d_wyq, d_wyyq, c->stream));
+  CK(engine_begin_tree(c->eng, d_wq, d_wyq, d_wyyq, q, c->stream));
   return H2OK_OK;
 }
 
@@ -542,7 +543,7 @@ int32_t h2ok_hist_set_targets_host(h2ok_ctx* c, const float* y_host, const float
   h2ok_hist_choose_quant(m, c->weighted ? 1 : 0, 25, &c->q);
   CK(launch_quantize_rows(c->y.p, c->weighted ? c->w.p : nullptr, n, c->q, c->weighted ? c->wq.p : nullptr, c->wyq.p,
                           c->wyyq.p, c->stream));
-  CK(engine_begin_tree(c->eng, c->weighted ? c->wq.p : nullptr, c->wyq.p, c->wyyq.p, c->stream));
+  CK(engine_begin_tree(c->eng, c->weighted ? c->wq.p : nullptr, c->wyq.p, c->wyyq.p, &c->q, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   c->gid_base = 0;
   c->have_targets = true;

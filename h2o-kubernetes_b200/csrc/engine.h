@@ -49,6 +49,9 @@ struct Engine {
   int32_t* tile_cnt = nullptr;          // [max_tiles + 1][2] records of each tile going left / right (then scanned)
   int32_t* slot_start = nullptr;        // [2 * kEngMaxNodes] first record of child slot 2 * node + way in the next order
   int32_t* leaf = nullptr;              // [rows] leaf code of every row (original order), -1 while still in the tree
+  int32_t* mnode[2] = {nullptr, nullptr};  // [kEngMaxNodes][2] centring offsets {M1, M2} of every node (row_engine.cu)
+  int32_t* slot_delta = nullptr;        // [2 * kEngMaxNodes][2] parent offset - child offset per child slot
+  double scale_wy = 0, scale_wyy = 0;   // fixed-point scales of the tree's targets (0: no centring)
   int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
   int64_t max_tiles = 0;
 };
@@ -59,9 +62,10 @@ void engine_free(Engine& e);
 cudaError_t engine_set_weighted(Engine& e, bool weighted);
 // copy columns [col0, col0 + ncols) of a column-major block (leading dimension ld) into the row-major copy
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s);
-// new tree: every row at the root, records in row order
+// new tree: every row at the root, records in row order.  q (may be NULL) gives the targets' fixed-point scales, from
+// which the children's centring offsets are derived; without it every node keeps the root's offsets.
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
-                              cudaStream_t s);
+                              const h2ok_quant* q, cudaStream_t s);
 // one level's histogram pass.  nb1 = bins + 1 of the accumulators' layout; level_nb1 (0: same as nb1) = bins + 1 of
 // the widest histogram of THIS level, which sizes the shared histogram (H2O halves nbins_top_level per level)
 cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int level_nb1, int64_t* acc,

@@ -48,10 +48,43 @@ __global__ void __launch_bounds__(256) eng_load_kernel(const float* __restrict__
   }
 }
 
+// Centring offsets.  The record arrays hold (target - M[node]) for an offset M near the node's mean target, so that the
+// 32-bit histogram words wander around their starting point instead of marching through the range (a wrap costs a
+// trip to the global accumulator).  Any M gives exact results: the flush adds count * M back.  The root's M is the
+// mean over the shard's first rows; a child's M comes from its parent's split record (mean y and mean y^2 of the
+// side, scaled like the targets).  Weighted shards keep M = 0 — their count word holds the weight sum, not the rows.
+__global__ void __launch_bounds__(1024) eng_root_mean_kernel(int64_t rows, const int32_t* __restrict__ wyq_rows,
+                                                             const int32_t* __restrict__ wyyq_rows, bool weighted,
+                                                             int32_t* __restrict__ mnode) {
+  __shared__ int s1[32], s2[32];
+  const int64_t cnt = rows < 65536 ? rows : 65536;
+  int t1 = 0, t2 = 0;
+  if (!weighted)
+    for (int64_t i = threadIdx.x; i < cnt; i += 1024) {  // >> 16 keeps the sums in 32 bits
+      t1 += wyq_rows[i] >> 16;
+      t2 += wyyq_rows[i] >> 16;
+    }
+  t1 = __reduce_add_sync(0xffffffffu, t1);
+  t2 = __reduce_add_sync(0xffffffffu, t2);
+  if ((threadIdx.x & 31) == 0) {
+    s1[threadIdx.x >> 5] = t1;
+    s2[threadIdx.x >> 5] = t2;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    t1 = __reduce_add_sync(0xffffffffu, s1[threadIdx.x]);
+    t2 = __reduce_add_sync(0xffffffffu, s2[threadIdx.x]);
+    if (threadIdx.x == 0) {
+      mnode[0] = (int32_t)((long long)t1 * 65536 / cnt);
+      mnode[1] = (int32_t)((long long)t2 * 65536 / cnt);
+    }
+  }
+}
+
 __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_rows, const int32_t* __restrict__ wyq_rows,
-                                 const int32_t* __restrict__ wyyq_rows, int32_t* __restrict__ gidx,
-                                 uint2* __restrict__ gval, int32_t* __restrict__ gw, int32_t* __restrict__ leaf,
-                                 int32_t* __restrict__ seg) {
+                                 const int32_t* __restrict__ wyyq_rows, const int32_t* __restrict__ mnode,
+                                 int32_t* __restrict__ gidx, uint2* __restrict__ gval, int32_t* __restrict__ gw,
+                                 int32_t* __restrict__ leaf, int32_t* __restrict__ seg) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0) {
     seg[0] = 0;
@@ -61,7 +94,7 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
   if (p >= rows) return;
   // zero-weight rows still travel down the tree (a6); the histogram pass skips them by weight
   gidx[p] = (int32_t)p;
-  gval[p] = make_uint2((unsigned)wyq_rows[p], (unsigned)wyyq_rows[p]);
+  gval[p] = make_uint2((unsigned)(wyq_rows[p] - mnode[0]), (unsigned)(wyyq_rows[p] - mnode[1]));
   if (gw) gw[p] = wq_rows[p];
   leaf[p] = -1;
 }
@@ -83,8 +116,9 @@ struct EngHistArgs {
   int64_t ldt;
   int cols;
   const int32_t* gidx;  // row of every record
-  const uint2* gval;    // {wyq, wyyq}
+  const uint2* gval;    // {wyq - M1[node], wyyq - M2[node]}
   const int32_t* gw;    // wq (weighted only)
+  const int32_t* mnode; // centring offsets {M1, M2} of every node of the level
   const int32_t* seg;
   int n_nodes;
   const h2ok_col_desc* descs;
@@ -253,12 +287,6 @@ struct EngCfg {
   static constexpr int U = WEIGHTED ? 4 / CPL : (CPL == 1 ? 6 : 4);  // 6, 4 (unweighted) or 4, 2 (weighted): even
 };
 
-// The wY and wYY words hold the sum of (target - M) for an offset M close to the run's mean target, so that they
-// wander around their 2^31 starting point instead of marching through the 32-bit range (a wrap costs a trip to the
-// global accumulator).  Any M gives exact results: the flush adds count * M back.  Weighted shards keep M = 0 — their
-// count word holds the weight sum, not the number of rows.
-constexpr int kEngMeanSample = 1024;
-
 template <int CPL, bool WEIGHTED, int LPR>
 __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
   using V = typename XVec<CPL>::type;
@@ -267,7 +295,6 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
   extern __shared__ __align__(16) unsigned h[];
   __shared__ unsigned s_mn[CPL * 32], s_mx[CPL * 32];
   __shared__ unsigned char s_tracked[CPL * 32];
-  __shared__ int s_m[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nb1 = a.nb1, nbs = a.nbs;
   const int triples = CPL * nbs * LPR;
@@ -331,27 +358,8 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         s_mx[k * 32 + lane] = kEncNegInf;
         s_tracked[k * 32 + lane] = tracked[k] ? 1 : 0;
       }
-      int m1 = 0, m2 = 0;
-      if (!WEIGHTED) {  // centring offsets: the mean targets of the run's first records (>> 10 keeps the sums in 32 bits)
-        const int cnt = min(send - p0, kEngMeanSample);
-        int t1 = 0, t2 = 0;
-        for (int i = lane; i < cnt; i += 32) {
-          const uint2 v = __ldg(gval + p0 + i);
-          t1 += (int)v.x >> 10;
-          t2 += (int)v.y >> 10;
-        }
-        t1 = __reduce_add_sync(0xffffffffu, t1);
-        t2 = __reduce_add_sync(0xffffffffu, t2);
-        m1 = (int)((long long)t1 * 1024 / cnt);
-        m2 = (int)((long long)t2 * 1024 / cnt);
-      }
-      if (lane == 0) {
-        s_m[0] = m1;
-        s_m[1] = m2;
-      }
     }
-    __syncthreads();  // histogram words, range slots and offsets are ready
-    const int m1 = s_m[0], m2 = s_m[1];
+    __syncthreads();  // histogram words and range slots are ready
 
     // Every warp takes U consecutive records at a time; the warps of the CTA interleave.  The row numbers of a batch
     // are fetched one batch ahead, and as soon as they are there (after the bin phase) the rows themselves are pulled
@@ -367,8 +375,8 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         V x[1];
         x[0] = __ldg(reinterpret_cast<const V*>(row_addr(xrow, (unsigned)__ldg(gidx + q), ldt4)));
         const uint2 r = __ldg(gval + q);
-        v1[0] = (int)r.x - m1;
-        v2[0] = (int)r.y - m2;
+        v1[0] = (int)r.x;
+        v2[0] = (int)r.y;
         w[0] = WEIGHTED ? __ldg(gw + q) : 1;
         unsigned pa[CPL];
         if (on) {
@@ -407,10 +415,10 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
 #pragma unroll
         for (int j = 0; j < U; j += 2) {
           const uint4 r = __ldg(reinterpret_cast<const uint4*>(gval + p + j));
-          v1[j] = (int)r.x - m1;
-          v2[j] = (int)r.y - m2;
-          v1[j + 1 < U ? j + 1 : j] = (int)r.z - m1;
-          v2[j + 1 < U ? j + 1 : j] = (int)r.w - m2;
+          v1[j] = (int)r.x;
+          v2[j] = (int)r.y;
+          v1[j + 1 < U ? j + 1 : j] = (int)r.z;
+          v2[j + 1 < U ? j + 1 : j] = (int)r.w;
         }
 #pragma unroll
         for (int j = 0; j < U; j++) w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
@@ -442,6 +450,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     }
     // flush the touched (slot, bin, lane) triples to the 64-bit global accumulators, undo the centring with the
     // triple's own count, and re-arm the words for the next node
+    const int m1 = a.mnode[2 * node], m2 = a.mnode[2 * node + 1];
     for (int t = tid; t < triples; t += THREADS) {
       const int kb = t / LPR, ln = t % LPR;
       unsigned* w0 = h + (kb * 3) * LPR + ln;
@@ -597,7 +606,10 @@ __global__ void __launch_bounds__(256) eng_route_kernel(const float* __restrict_
 // which is also the order of their ids).
 __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ tile_cnt, const int32_t* __restrict__ tile_base,
                                                         int n_nodes, const int32_t* __restrict__ child_ids,
-                                                        int32_t* __restrict__ slot_start, int32_t* __restrict__ seg_next) {
+                                                        int32_t* __restrict__ slot_start, int32_t* __restrict__ seg_next,
+                                                        const h2ok_split* __restrict__ splits, double scale_wy,
+                                                        double scale_wyy, const int32_t* __restrict__ mnode,
+                                                        int32_t* __restrict__ mnode_next, int32_t* __restrict__ slot_delta) {
   __shared__ int s_warp[33];
   __shared__ int s_run[2];
   const int T = tile_base[n_nodes];
@@ -639,6 +651,31 @@ __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ ti
     slot_start[2 * g + 1] = ex + tot0;
     if (cl >= 0) seg_next[cl] = ex;
     if (cr >= 0) seg_next[cr] = ex + tot0;
+    // centring offsets of the children (see eng_root_mean_kernel): mean y and mean y^2 of the side from the split
+    // record, scaled like the targets; scale 0 (weighted shards) keeps every offset at 0.  slot_delta is what the
+    // scatter adds to a record's stored targets when it moves it from this node to the child.
+    const h2ok_split sp = splits[g];
+    const int pm1 = mnode[2 * g], pm2 = mnode[2 * g + 1];
+#pragma unroll
+    for (int way = 0; way < 2; way++) {
+      const int ch = way ? cr : cl;
+      const double pred = way ? sp.pred_right : sp.pred_left, se = way ? sp.se_right : sp.se_left;
+      const double n = way ? sp.n_right : sp.n_left;
+      int c1 = pm1, c2 = pm2;
+      if (scale_wy > 0.0 && n > 0.0 && pred == pred && se == se) {
+        const double a1 = pred * scale_wy, a2 = (se / n + pred * pred) * scale_wyy;
+        if (fabs(a1) < 134217728.0 && fabs(a2) < 134217728.0) {  // 2^27: the centred targets stay far inside 32 bits
+          c1 = __double2int_rn(a1);
+          c2 = __double2int_rn(a2);
+        }
+      }
+      slot_delta[2 * (2 * g + way)] = pm1 - c1;
+      slot_delta[2 * (2 * g + way) + 1] = pm2 - c2;
+      if (ch >= 0) {
+        mnode_next[2 * ch] = c1;
+        mnode_next[2 * ch + 1] = c2;
+      }
+    }
   }
   if (g == 0) {
     seg_next[nc] = live;
@@ -653,7 +690,8 @@ __global__ void __launch_bounds__(256) eng_scatter_kernel(const int32_t* __restr
                                                           const int32_t* __restrict__ tile_base, int n_nodes,
                                                           const uint8_t* __restrict__ codes,
                                                           const int32_t* __restrict__ tile_cnt,
-                                                          const int32_t* __restrict__ slot_start) {
+                                                          const int32_t* __restrict__ slot_start,
+                                                          const int32_t* __restrict__ slot_delta) {
   constexpr int J = kEngTile / 256;
   __shared__ unsigned s_pre[J * 8];  // per (step, warp): records going left (low half) / right (high half)
   const int t = blockIdx.x;
@@ -663,6 +701,7 @@ __global__ void __launch_bounds__(256) eng_scatter_kernel(const int32_t* __restr
   const int tb = tile_base[g];
   const int64_t base0 = (int64_t)slot_start[2 * g] + tile_cnt[2 * t] - tile_cnt[2 * tb];
   const int64_t base1 = (int64_t)slot_start[2 * g + 1] + tile_cnt[2 * t + 1] - tile_cnt[2 * tb + 1];
+  const int d1l = slot_delta[4 * g], d2l = slot_delta[4 * g + 1], d1r = slot_delta[4 * g + 2], d2r = slot_delta[4 * g + 3];
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   int code[J];
 #pragma unroll
@@ -703,7 +742,10 @@ __global__ void __launch_bounds__(256) eng_scatter_kernel(const int32_t* __restr
     if (code[j] < 2) {
       const int64_t d = code[j] == 0 ? base0 + (pre & 0xFFFFu) + __popc(b0 & lt) : base1 + (pre >> 16) + __popc(b1 & lt);
       gidx_n[d] = gidx[p];
-      gval_n[d] = gval[p];
+      uint2 v = gval[p];  // stored relative to this node's offsets; the child's run stores it relative to the child's
+      v.x += (unsigned)(code[j] ? d1r : d1l);
+      v.y += (unsigned)(code[j] ? d2r : d2l);
+      gval_n[d] = v;
       if (gw) gw_n[d] = gw[p];
     }
   }
@@ -738,6 +780,7 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
     A((void**)&e.gval[k], sizeof(uint2) * (size_t)rows);
     if (weighted) A((void**)&e.gw[k], sizeof(int32_t) * (size_t)rows);
     A((void**)&e.seg[k], sizeof(int32_t) * kSegInts);
+    A((void**)&e.mnode[k], sizeof(int32_t) * 2 * kEngMaxNodes);
   }
   A((void**)&e.codes, (size_t)rows);
   A((void**)&e.tile_base, sizeof(int32_t) * (kEngMaxNodes + 1));
@@ -745,6 +788,7 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   A((void**)&e.tile_order, sizeof(int32_t) * (size_t)(e.max_tiles + 1));
   A((void**)&e.slot_start, sizeof(int32_t) * 2 * kEngMaxNodes);
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
+  A((void**)&e.slot_delta, sizeof(int32_t) * 4 * kEngMaxNodes);
   A((void**)&e.err, sizeof(int32_t));
   if (err == cudaSuccess) err = cudaMemset(e.err, 0, sizeof(int32_t));
   if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
@@ -755,12 +799,13 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
 void engine_free(Engine& e) {
   cudaFree(e.XT);
   for (int k = 0; k < 2; k++) {
-    cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]);
-    e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr;
+    cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]); cudaFree(e.mnode[k]);
+    e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr; e.mnode[k] = nullptr;
   }
   cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.tile_order); cudaFree(e.slot_start);
-  cudaFree(e.leaf); cudaFree(e.err);
+  cudaFree(e.leaf); cudaFree(e.err); cudaFree(e.slot_delta);
   e.err = nullptr;
+  e.slot_delta = nullptr;
   e.XT = nullptr;
   e.codes = nullptr;
   e.tile_base = e.tile_cnt = e.tile_order = e.slot_start = e.leaf = nullptr;
@@ -788,11 +833,15 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
 }
 
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
-                              cudaStream_t s) {
+                              const h2ok_quant* q, cudaStream_t s) {
   e.cur = 0;
   e.n_nodes = 1;
+  e.scale_wy = (q && !e.weighted) ? q->scale_wy : 0.0;
+  e.scale_wyy = (q && !e.weighted) ? q->scale_wyy : 0.0;
+  eng_root_mean_kernel<<<1, 1024, 0, s>>>(e.rows, wyq_rows, wyyq_rows, e.weighted, e.mnode[0]);
   eng_begin_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.rows, e.weighted ? wq_rows : nullptr, wyq_rows, wyyq_rows,
-                                                     e.gidx[0], e.gval[0], e.weighted ? e.gw[0] : nullptr, e.leaf, e.seg[0]);
+                                                     e.mnode[0], e.gidx[0], e.gval[0], e.weighted ? e.gw[0] : nullptr,
+                                                     e.leaf, e.seg[0]);
   return cudaGetLastError();
 }
 
@@ -841,6 +890,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   a.gidx = e.gidx[e.cur];
   a.gval = e.gval[e.cur];
   a.gw = e.weighted ? e.gw[e.cur] : nullptr;
+  a.mnode = e.mnode[e.cur];
   a.seg = e.seg[e.cur];
   a.n_nodes = n_nodes;
   a.descs = descs;
@@ -873,10 +923,12 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   eng_order_kernel<<<nblk(tiles, 256), 256, 0, s>>>(e.tile_base, n_nodes, e.tile_order);
   eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.gidx[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
                                          gid_base, e.codes, e.leaf, e.tile_cnt, e.tile_order);
-  eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx]);
+  eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx], splits, e.scale_wy,
+                                     e.scale_wyy, e.mnode[e.cur], e.mnode[nx], e.slot_delta);
   eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.gidx[e.cur], e.gval[e.cur], e.weighted ? e.gw[e.cur] : nullptr, e.gidx[nx],
                                            e.gval[nx], e.weighted ? e.gw[nx] : nullptr,
-                                           e.seg[e.cur], e.tile_base, n_nodes, e.codes, e.tile_cnt, e.slot_start);
+                                           e.seg[e.cur], e.tile_base, n_nodes, e.codes, e.tile_cnt, e.slot_start,
+                                           e.slot_delta);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return err;
   e.cur = nx;

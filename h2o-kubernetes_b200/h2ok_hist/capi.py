@@ -35,7 +35,7 @@ SIGNATURES = {
     "h2ok_hist_tree_create": [vp, i64, i32, i32],
     "h2ok_hist_tree_load_cols_dev": [vp, i32, i32, vp, i64],
     "h2ok_hist_tree_destroy": [vp],
-    "h2ok_hist_tree_begin_dev": [vp, vp, vp, vp],
+    "h2ok_hist_tree_begin_dev": [vp, vp, vp, vp, vp],
     "h2ok_hist_tree_build_level_dev": [vp, i32, vp, i32, i32, vp, vp, vp],
     "h2ok_hist_tree_level_bins": [vp, i32],
     "h2ok_hist_tree_apply_splits_dev": [vp, vp, vp, i32, i32, i32],

@@ -269,7 +269,7 @@ class EngineShard(CudaShard):
 
     def quantize(self, quant):
         super().quantize(quant)
-        self.lib.call("h2ok_hist_tree_begin_dev", self.ctx, _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq))
+        self.lib.call("h2ok_hist_tree_begin_dev", self.ctx, _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), C.byref(quant))
         self.launches += 1
 
     def reset_nodes(self):

@@ -225,8 +225,12 @@ int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
 /* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in
  * original order */
 int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* ctx, int32_t col0, int32_t ncols, const float* d_X, int64_t ld);
-/* new tree: per-row fixed-point targets in ORIGINAL row order (d_wq NULL when unweighted); all rows back at the root */
-int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* ctx, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq);
+/* new tree: per-row fixed-point targets in ORIGINAL row order (d_wq NULL when unweighted); all rows back at the root.
+ * q = the h2ok_quant the targets were quantised with (host pointer; may be NULL): the engine stores every node's
+ * targets relative to an offset near the node's mean, which it derives from the parent's split record and these
+ * scales, so that its 32-bit histogram words rarely wrap.  Results do not depend on it. */
+int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* ctx, const int32_t* d_wq, const int32_t* d_wyq, const int32_t* d_wyyq,
+                                 const h2ok_quant* q);
 /* a3/a4 for the current level; outputs as h2ok_hist_build_level_dev.  n_nodes must be the number of children the
  * previous tree_apply_splits_dev produced (1 after tree_begin_dev). */
 int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* ctx, int32_t n_nodes, const h2ok_col_desc* d_descs, int32_t max_bins,
