@@ -114,6 +114,7 @@ __device__ __forceinline__ int seg_of(const int32_t* __restrict__ table, int n, 
 struct EngHistArgs {
   const float* XT;
   int64_t ldt;
+  unsigned ldt4;  // row pitch in bytes
   int cols;
   const int32_t* gidx;  // row of every record
   const uint2* gval;    // {wyq - M1[node], wyyq - M2[node]}
@@ -138,12 +139,10 @@ __device__ __forceinline__ unsigned sh_add(unsigned addr, unsigned v) {
   return o;
 }
 
-// base + idx * pitch in ONE instruction (IMAD.WIDE.U32 with the 64-bit base as addend); written as C the compiler adds
-// the zero high half of the pitch separately
+// base + idx * pitch: with both factors 32-bit this is one IMAD.WIDE.U32 with the base as its 64-bit addend (ptxas
+// splits an explicit mad.wide.u32 into three instructions)
 __device__ __forceinline__ const char* row_addr(const char* base, unsigned idx, unsigned pitch) {
-  unsigned long long r;
-  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(idx), "r"(pitch), "l"((unsigned long long)base));
-  return reinterpret_cast<const char*>(r);
+  return base + (unsigned long long)idx * pitch;
 }
 // hb + b * pitch in one IMAD (the compiler splits it when b comes out of a select)
 __device__ __forceinline__ unsigned cell_addr(unsigned hb, unsigned b, unsigned pitch) {
@@ -317,8 +316,9 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     asm volatile("" : "+r"(hb[k]));  // keep it in a register: recomputing it costs seven instructions per cell
   }
   // lanes past the last column read the row's last CPL floats instead (never accumulated: their columns are untracked)
-  const unsigned ldt4 = (unsigned)a.ldt * 4u;  // row pitch in bytes: one IMAD.WIDE per row address
-  const char* __restrict__ xrow = reinterpret_cast<const char*>(a.XT + min(col_lane, (int)a.ldt - CPL));
+  const unsigned ldt4 = a.ldt4;  // row pitch in bytes: one IMAD.WIDE per row address
+  const char* xrow = reinterpret_cast<const char*>(a.XT + min(col_lane, (int)a.ldt - CPL));
+  asm volatile("" : "+l"(xrow));  // kept in a register pair: rebuilt per batch it turns every row address into three instructions
   const int32_t* __restrict__ gidx = a.gidx;
   const uint2* __restrict__ gval = a.gval;
   const int32_t* __restrict__ gw = a.gw;
@@ -886,6 +886,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   EngHistArgs a{};
   a.XT = e.XT;
   a.ldt = e.ldt;
+  a.ldt4 = (unsigned)(e.ldt * 4);
   a.cols = e.cols;
   a.gidx = e.gidx[e.cur];
   a.gval = e.gval[e.cur];
