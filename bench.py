@@ -48,9 +48,9 @@ def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per histogram launch, from the committed `ncu --set full` captures at
-# 100M x 64 (profiles/r01_eng_hist_ncu_full.csv: 27.6-28.0 GB read + 0.01-0.06 GB written; profiles/r01_hist_build_ncu_full.csv:
+# 100M x 64 (profiles/r01_eng_hist_ncu_full.csv: 26.8-27.5 GB read + 0.01-0.05 GB written; profiles/r01_hist_build_ncu_full.csv:
 # 26.5-27.6 GB read + 0.01-0.3 GB written); scaled linearly to the rows of the run.  None for shapes not profiled.
-NCU_TRAFFIC_BYTES_PER_CELL = {"engine": 27.77e9 / (100_000_000 * 64), "stateless": 27.15e9 / (100_000_000 * 64)}
+NCU_TRAFFIC_BYTES_PER_CELL = {"engine": 27.13e9 / (100_000_000 * 64), "stateless": 27.15e9 / (100_000_000 * 64)}
 
 
 def measured_hbm_peak():
