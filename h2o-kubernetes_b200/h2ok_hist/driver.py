@@ -155,10 +155,13 @@ class CudaShard:
         """Device time of the last build_level's hist_build launches (CUDA events inside the library)."""
         return float(self.stats().build_ms)
 
-    def finalize_level(self, n_nodes):
-        self.lib.call("h2ok_hist_finalize_level_dev", self.ctx, _ptr(self.acc), _ptr(self.mn), _ptr(self.mx), n_nodes,
-                      self.cols, self.max_bins, C.byref(self.quant), _ptr(self.hist), _ptr(self.min2), _ptr(self.maxin))
-        self.launches += 2
+    def finalize_level(self, n_nodes, hist=True, ranges=True):
+        """Integer accumulators -> fp64 histogram (hist) and encoded -> float observed ranges (ranges)."""
+        self.lib.call("h2ok_hist_finalize_level_dev", self.ctx, _ptr(self.acc) if hist else None,
+                      _ptr(self.mn) if ranges else None, _ptr(self.mx) if ranges else None, n_nodes, self.cols,
+                      self.max_bins, C.byref(self.quant), _ptr(self.hist) if hist else None,
+                      _ptr(self.min2) if ranges else None, _ptr(self.maxin) if ranges else None)
+        self.launches += int(hist) + int(ranges)
 
     # ---- a7 / a8 / a6 ------------------------------------------------------------------------------------
     def find_splits(self, n_nodes, min_rows, msi):
@@ -293,18 +296,28 @@ def _world():
     return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
 
 
-def reduce_level(acc, mn, mx):
+def reduce_level(acc, mn, mx, wait=True):
     """a5 — MRTask.reduce / DHistogram.add across ranks: integer sum of the fixed-point histogram, integer min / max
     of the encoded observed ranges.  The encodings are unsigned; flipping the top bit makes signed compares agree,
-    and min(a) = ~max(~a) folds the two range reductions into ONE max all-reduce."""
+    and min(a) = ~max(~a) folds the two range reductions into ONE max all-reduce.  With wait=False the range
+    reduction is left in flight (only next_level needs it, the split search does not) and the returned function
+    completes it."""
     if _world() == 1:
-        return
+        return lambda: None
     dist.all_reduce(acc, op=dist.ReduceOp.SUM)
     n = mn.numel()
     buf = torch.cat([~(mn.reshape(-1) ^ _I32_SIGN), mx.reshape(-1) ^ _I32_SIGN])
-    dist.all_reduce(buf, op=dist.ReduceOp.MAX)
-    mn.copy_(((~buf[:n]) ^ _I32_SIGN).view_as(mn))
-    mx.copy_((buf[n:] ^ _I32_SIGN).view_as(mx))
+    work = dist.all_reduce(buf, op=dist.ReduceOp.MAX, async_op=True)
+
+    def finish():
+        work.wait()
+        mn.copy_(((~buf[:n]) ^ _I32_SIGN).view_as(mn))
+        mx.copy_((buf[n:] ^ _I32_SIGN).view_as(mx))
+
+    if wait:
+        finish()
+        return lambda: None
+    return finish
 
 
 class LevelDriver:
@@ -366,9 +379,11 @@ class LevelDriver:
         n = self.n_nodes
         # H2O halves nbins_top_level per level (Split.nextLevelHistos: max(parent bins >> 1, nbins))
         acc, mn, mx = sh.build_level(n, level_bins=max(p.nbins, p.nbins_top_level >> self.depth))
-        reduce_level(acc, mn, mx)
-        sh.finalize_level(n)
+        finish_ranges = reduce_level(acc, mn, mx, wait=False)
+        sh.finalize_level(n, ranges=False)  # the split search starts while the range reduction is still in flight
         sh.find_splits(n, p.min_rows, p.min_split_improvement)
+        finish_ranges()
+        sh.finalize_level(n, hist=False)
         last = (self.depth + 1 >= p.max_depth) if last is None else last
         if last:
             sh.no_children(n)

@@ -58,10 +58,12 @@ class CpuShard:
         self.mx = torch.from_numpy(abi.encode_f32(maxin).view(np.int32).copy())
         return self.acc, self.mn, self.mx
 
-    def finalize_level(self, n):
-        self.hist = self.oracle.finalize(self.acc.numpy(), self.quant, self.max_bins)
-        self.min2 = abi.decode_f32(self.mn.numpy().view(np.uint32)) + np.float32(0)
-        self.maxin = abi.decode_f32(self.mx.numpy().view(np.uint32)) + np.float32(0)
+    def finalize_level(self, n, hist=True, ranges=True):
+        if hist:
+            self.hist = self.oracle.finalize(self.acc.numpy(), self.quant, self.max_bins)
+        if ranges:
+            self.min2 = abi.decode_f32(self.mn.numpy().view(np.uint32)) + np.float32(0)
+            self.maxin = abi.decode_f32(self.mx.numpy().view(np.uint32)) + np.float32(0)
 
     def find_splits(self, n, min_rows, msi):
         self.splits = self.oracle.find_splits(self.hist, self.descs[:n], min_rows, msi)
