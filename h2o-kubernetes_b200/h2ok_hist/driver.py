@@ -17,6 +17,7 @@ import torch.distributed as dist
 from . import abi, capi
 
 _I32_SIGN = -(2**31)
+_I32_MAX = 2**31 - 1
 
 
 def _ptr(t):
@@ -306,13 +307,16 @@ def reduce_level(acc, mn, mx, wait=True):
         return lambda: None
     dist.all_reduce(acc, op=dist.ReduceOp.SUM)
     n = mn.numel()
-    buf = torch.cat([~(mn.reshape(-1) ^ _I32_SIGN), mx.reshape(-1) ^ _I32_SIGN])
+    buf = torch.empty(2 * n, dtype=mn.dtype, device=mn.device)
+    # ~(x ^ SIGN) == x ^ 0x7fffffff: one xor per half on the way in, one on the way out
+    torch.bitwise_xor(mn.reshape(-1), _I32_MAX, out=buf[:n])
+    torch.bitwise_xor(mx.reshape(-1), _I32_SIGN, out=buf[n:])
     work = dist.all_reduce(buf, op=dist.ReduceOp.MAX, async_op=True)
 
     def finish():
         work.wait()
-        mn.copy_(((~buf[:n]) ^ _I32_SIGN).view_as(mn))
-        mx.copy_((buf[n:] ^ _I32_SIGN).view_as(mx))
+        torch.bitwise_xor(buf[:n], _I32_MAX, out=mn.view(-1))
+        torch.bitwise_xor(buf[n:], _I32_SIGN, out=mx.view(-1))
 
     if wait:
         finish()
