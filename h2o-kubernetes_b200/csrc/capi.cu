@@ -8,84 +8,12 @@
 #include <vector>
 
 #include "common.cuh"
-#include "engine.h"
-#include "kernels.h"
+#include "ctx.h"
 
 using namespace h2ok;
 
-static thread_local char g_err[512] = "";
-
-static int32_t fail(int32_t code, const char* fmt, const char* a = "", const char* b = "") {
-  snprintf(g_err, sizeof(g_err), fmt, a, b);
-  return code;
-}
-
-#define CK(call)                                                                         \
-  do {                                                                                   \
-    cudaError_t _e = (call);                                                             \
-    if (_e != cudaSuccess) return fail(H2OK_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_e)); \
-  } while (0)
-
-#define REQUIRE(cond, msg) \
-  do {                     \
-    if (!(cond)) return fail(H2OK_ERR_ARG, "%s (%s)", msg, #cond); \
-  } while (0)
-
-template <typename T>
-struct DevBuf {  // grow-only device buffer
-  T* p = nullptr;
-  size_t cap = 0;
-  cudaError_t ensure(size_t n) {
-    if (n <= cap) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-    cudaError_t e = cudaMalloc(&p, n * sizeof(T));
-    if (e == cudaSuccess) cap = n;
-    return e;
-  }
-  void release() {
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-  }
-};
-
-struct h2ok_ctx {
-  int device = 0;
-  cudaStream_t own_stream = nullptr, stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  // scratch of next_level (a8)
-  DevBuf<h2ok_col_desc> tmp_descs;
-  DevBuf<int32_t> tmp_valid;
-  // scratch of build_level: packed row records + range-error flag
-  DevBuf<uint2> rec;
-  DevBuf<int32_t> rec_err;
-  // resident data of the host-buffer API
-  DevBuf<float> X, y, w;
-  DevBuf<int32_t> nid, leaf, wq, wyq, wyyq;
-  DevBuf<double> absmax;
-  DevBuf<uint32_t> cmin, cmax;
-  int64_t rows = 0, ld = 0;
-  int cols = 0;
-  bool have_data = false, have_targets = false, weighted = false;
-  h2ok_quant q{};
-  // level state
-  DevBuf<h2ok_col_desc> descs, child_descs;
-  DevBuf<int64_t> acc;
-  DevBuf<uint32_t> mn, mx;
-  DevBuf<double> hist;
-  DevBuf<float> min2, maxin;
-  DevBuf<h2ok_split> splits;
-  DevBuf<int32_t> child_ids, n_children;
-  int n_nodes = 0, max_bins = 0, gid_base = 0;
-  bool level_built = false, splits_found = false, children_made = false;
-  bool timed = false;  // ev0/ev1 bracket the last hist_build launches
-  Engine eng;          // resident tree engine (h2ok_hist_tree_*)
-  int eng_level_bins = 0;  // h2ok_hist_tree_level_bins hint for the next tree_build_level_dev (0: none)
-  bool eng_ready = false;
-  h2ok_stats stats{};
-};
+static thread_local char g_err[h2ok::kErrBufLen] = "";
+char* h2ok::err_buf() { return g_err; }
 
 // ---- host copies of the a1 rules (DHistogram.<init> / find_maxEx) for root descriptors -------------------
 static double h_ulp(double x) {
@@ -145,10 +73,17 @@ int32_t h2ok_hist_create(int32_t device, h2ok_ctx** out) {
   if (prop.major < 10) return fail(H2OK_ERR_UNSUPPORTED, "%s", "this library is built for sm_100a (B200) only");
   h2ok_ctx* c = new h2ok_ctx();
   c->device = device;
-  CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  cudaError_t e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&c->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&c->ev1);
+  if (e != cudaSuccess) {  // nothing half-made is left behind
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+    return fail(H2OK_ERR_CUDA, "h2ok_hist_create: %s", cudaGetErrorString(e));
+  }
   c->stream = c->own_stream;
-  CK(cudaEventCreate(&c->ev0));
-  CK(cudaEventCreate(&c->ev1));
   *out = c;
   return H2OK_OK;
 }
@@ -157,8 +92,10 @@ int32_t h2ok_hist_destroy(h2ok_ctx* c) {
   if (!c) return H2OK_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  loop_free(c);
+  comm_free(c);
   engine_free(c->eng);
-  c->tmp_descs.release(); c->tmp_valid.release(); c->rec.release(); c->rec_err.release(); c->X.release(); c->y.release(); c->w.release();
+  c->tmp_descs.release(); c->tmp_valid.release(); c->cand.release(); c->rec.release(); c->rec_err.release(); c->X.release(); c->y.release(); c->w.release();
   c->nid.release(); c->leaf.release(); c->wq.release(); c->wyq.release(); c->wyyq.release(); c->absmax.release();
   c->cmin.release(); c->cmax.release(); c->descs.release(); c->child_descs.release(); c->acc.release();
   c->mn.release(); c->mx.release(); c->hist.release(); c->min2.release(); c->maxin.release(); c->splits.release();
@@ -179,6 +116,15 @@ int32_t h2ok_hist_set_stream(h2ok_ctx* c, void* stream, int32_t use_own) {
 
 int32_t h2ok_hist_sync(h2ok_ctx* c) {
   REQUIRE(c != nullptr, "null context");
+  CK(cudaStreamSynchronize(c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_copy_to_host(h2ok_ctx* c, const void* d_src, void* host_dst, size_t bytes) {
+  REQUIRE(c && (bytes == 0 || (d_src && host_dst)), "null pointer");
+  if (bytes == 0) return H2OK_OK;
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemcpyAsync(host_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   return H2OK_OK;
 }
@@ -293,7 +239,9 @@ int32_t h2ok_hist_find_splits_dev(h2ok_ctx* c, const double* d_hist, const h2ok_
   REQUIRE(c && d_hist && d_descs && d_splits, "null pointer");
   int32_t rc = check_level_shape(n_nodes, cols, max_bins);
   if (rc) return rc;
-  CK(launch_find_splits(d_hist, d_descs, n_nodes, cols, max_bins + 1, min_rows, min_split_improvement, d_splits, c->stream));
+  CK(c->cand.ensure((size_t)n_nodes * cols));
+  CK(launch_find_splits(d_hist, d_descs, n_nodes, cols, max_bins + 1, min_rows, min_split_improvement, c->cand.p, d_splits,
+                        c->stream));
   return H2OK_OK;
 }
 
@@ -375,7 +323,9 @@ int32_t h2ok_hist_tree_create(h2ok_ctx* c, int64_t rows, int32_t cols, int32_t w
 
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* c) {
   REQUIRE(c != nullptr, "null context");
+  CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->stream));
+  loop_free(c);
   engine_free(c->eng);
   c->eng_ready = false;
   return H2OK_OK;
@@ -434,11 +384,10 @@ int32_t h2ok_hist_tree_level_bins(h2ok_ctx* c, int32_t level_bins) {
 
 int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* c, const h2ok_split* d_splits, const int32_t* d_child_ids,
                                         int32_t gid_base, int32_t n_nodes, int32_t last_level) {
-  (void)last_level;
   REQUIRE(c && d_splits && d_child_ids, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_apply_splits_dev before tree_create");
   REQUIRE(n_nodes >= 1 && n_nodes <= H2OK_MAX_LEVEL_NODES, "n_nodes out of range");
-  CK(engine_apply_splits(c->eng, d_splits, d_child_ids, gid_base, n_nodes, c->stream));
+  CK(engine_apply_splits(c->eng, d_splits, d_child_ids, gid_base, n_nodes, last_level == 0, c->stream));
   return H2OK_OK;
 }
 
@@ -671,7 +620,8 @@ int32_t h2ok_hist_apply_splits(h2ok_ctx* c) {
     CK(c->child_ids.ensure((size_t)2 * c->n_nodes));
     CK(cudaMemsetAsync(c->child_ids.p, 0xFF, sizeof(int32_t) * 2 * (size_t)c->n_nodes, c->stream));
   }
-  int32_t rc = h2ok_hist_tree_apply_splits_dev(c, c->splits.p, c->child_ids.p, c->gid_base, c->n_nodes, 0);
+  int32_t rc = h2ok_hist_tree_apply_splits_dev(c, c->splits.p, c->child_ids.p, c->gid_base, c->n_nodes,
+                                               c->children_made ? 0 : 1);
   if (rc) return rc;
   CK(cudaStreamSynchronize(c->stream));
   c->gid_base += c->n_nodes;

@@ -27,15 +27,21 @@
 
 namespace h2ok {
 
-constexpr int kEngTile = 2048;      // records per routing / scatter tile
 constexpr int kEngMaxNodes = 1024;  // >= H2OK_MAX_LEVEL_NODES + 1
 
 struct Engine {
   int64_t rows = 0;  // rows of the shard
   int64_t ldt = 0;   // floats per row of XT (cols rounded up to a multiple of 8: rows start on 32-byte sectors)
+  int64_t ld8 = 0;   // bytes per column of code8 (rows rounded up to 128)
   int cols = 0;
+  int sms = 0;         // SMs of the device: the histogram pass runs one CTA per SM and column block
+  int route_ctas = 0;  // CTAs of the routing / regrouping kernels (each owns one contiguous range of rows)
   bool weighted = false;
-  float* XT = nullptr;                  // [rows][ldt] row-major copy of the shard
+  float* XT = nullptr;       // [rows][ldt] row-major copy of the shard
+  uint8_t* code8 = nullptr;  // [cols][ld8] order-preserving 8-bit code of every cell (255 = NaN), for routing
+  uint32_t* thr = nullptr;   // [cols][256] the codes' thresholds (encoded floats, ascending; unused = 0xFFFFFFFF)
+  uint32_t* cmin = nullptr;  // [cols] encoded column minimum / maximum of the shard (NaN skipped), taken while loading
+  uint32_t* cmax = nullptr;
   // row records grouped by node, double buffered: the row, its fixed-point targets {wyq, wyyq}, its weight
   int32_t* gidx[2] = {nullptr, nullptr};
   uint2* gval[2] = {nullptr, nullptr};
@@ -43,17 +49,16 @@ struct Engine {
   int32_t* seg[2] = {nullptr, nullptr}; // [n_nodes + 1] first record of every node of the level; seg[n_nodes] = live rows
   int cur = 0;
   int n_nodes = 0;                      // nodes of the current level (0: no tree in progress)
-  uint8_t* codes = nullptr;             // [rows] way of every record: 0 / 1 = live child, 2 = into a leaf
-  int32_t* tile_base = nullptr;         // [kEngMaxNodes + 1] first tile of every node
-  int32_t* tile_order = nullptr;        // [max_tiles + 1] tiles in the order routing visits them
-  int32_t* tile_cnt = nullptr;          // [max_tiles + 1][2] records of each tile going left / right (then scanned)
-  int32_t* slot_start = nullptr;        // [2 * kEngMaxNodes] first record of child slot 2 * node + way in the next order
+  uint16_t* nid16 = nullptr;            // [rows] node of every row in the current level, 0xFFFF = in a leaf
+  int32_t* cta_cnt = nullptr;           // [kEngMaxNodes][route_ctas] rows per (child, routing CTA), then scanned
   int32_t* leaf = nullptr;              // [rows] leaf code of every row (original order), -1 while still in the tree
   int32_t* mnode[2] = {nullptr, nullptr};  // [kEngMaxNodes][2] centring offsets {M1, M2} of every node (row_engine.cu)
-  int32_t* slot_delta = nullptr;        // [2 * kEngMaxNodes][2] parent offset - child offset per child slot
+  // the current tree's targets in original row order (the caller's arrays: they must stay valid until the tree is done)
+  const int32_t* wq_rows = nullptr;
+  const int32_t* wyq_rows = nullptr;
+  const int32_t* wyyq_rows = nullptr;
   double scale_wy = 0, scale_wyy = 0;   // fixed-point scales of the tree's targets (0: no centring)
   int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
-  int64_t max_tiles = 0;
 };
 
 cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted);
@@ -63,7 +68,8 @@ cudaError_t engine_set_weighted(Engine& e, bool weighted);
 // copy columns [col0, col0 + ncols) of a column-major block (leading dimension ld) into the row-major copy
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s);
 // new tree: every row at the root, records in row order.  q (may be NULL) gives the targets' fixed-point scales, from
-// which the children's centring offsets are derived; without it every node keeps the root's offsets.
+// which the children's centring offsets are derived; without it every node keeps the root's offsets.  The target
+// arrays are read again by every level's regrouping: they must stay valid and unchanged until the tree is finished.
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
                               const h2ok_quant* q, cudaStream_t s);
 // one level's histogram pass.  nb1 = bins + 1 of the accumulators' layout; level_nb1 (0: same as nb1) = bins + 1 of
@@ -73,8 +79,9 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
 // the largest bins + 1 a level may use (16 columns per block must fit the shared memory)
 int engine_max_nb1(int cols);
 // route rows with the level's splits, retire rows into leaves, regroup the records by child
+// (regroup == false: the tree's last level — rows only get their leaves, no records are laid out)
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,
-                                cudaStream_t s);
+                                bool regroup, cudaStream_t s);
 // row -> node map of the current level in original row order (tests / inspection)
 cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s);
 

@@ -50,12 +50,31 @@ cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_
 cudaError_t launch_finalize(const int64_t* acc, const uint32_t* mn, const uint32_t* mx, int64_t n_node_cols, int nb1,
                             const h2ok_quant& q, double* hist, float* min2, float* maxin, cudaStream_t s);
 
+// a7: the best split point of one (node, column) pair (DTree.findBestSplitPoint + Split.splat), before bestCol
+struct PairCand {
+  double key;  // se_left + se_right
+  double seL, seR, nL, nR, pL, pR, se_before;
+  int32_t bin, na, found;
+  float splat;
+};
+// pairs [pair0, pair1) of the flat [n_nodes * cols] list, from the fp64 histogram (hist != NULL) or straight from the
+// int64 accumulators with q's scales (hist == NULL); cand is indexed by pair
+cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_col_desc* descs,
+                                int64_t pair0, int64_t pair1, int nb1, double min_rows, double msi, PairCand* cand,
+                                cudaStream_t s);
+cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_split* splits, cudaStream_t s);
+// both steps over every pair; cand: [n_nodes * cols] scratch
 cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
-                               double min_rows, double msi, h2ok_split* splits, cudaStream_t s);
+                               double min_rows, double msi, PairCand* cand, h2ok_split* splits, cudaStream_t s);
 // tmp_descs: [2*n_nodes][cols] scratch; tmp_valid: [2*n_nodes] scratch
 cudaError_t launch_next_level(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2, const float* maxin,
                               int n_nodes, int cols, const h2ok_params& p, h2ok_col_desc* tmp_descs, int32_t* tmp_valid,
                               h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children, cudaStream_t s);
+// the same from the encoded observed ranges (what the histogram pass and the cross-rank reduce produce)
+cudaError_t launch_next_level_enc(const h2ok_split* splits, const h2ok_col_desc* descs, const uint32_t* min2_enc,
+                                  const uint32_t* maxin_enc, int n_nodes, int cols, const h2ok_params& p,
+                                  h2ok_col_desc* tmp_descs, int32_t* tmp_valid, h2ok_col_desc* child_descs,
+                                  int32_t* child_ids, int32_t* n_children, cudaStream_t s);
 cudaError_t launch_next_level_noalloc(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2,
                                       const float* maxin, int n_nodes, int cols, const h2ok_params& p,
                                       h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children,

@@ -7,11 +7,13 @@
 //                        warp takes whole rows, lane L owns CPL (1 or 2) adjacent columns; descriptors and observed
 //                        ranges in registers; shared histogram [slot][bin][channel][lane] -> bank == lane, no
 //                        conflicts, one copy; the next batch's rows are prefetched into L2.
-//   eng_tiles_kernel     tiles (<= 2048 records of one node) of the level.
-//   eng_order_kernel     the order routing visits the tiles in (k-th tile of every node together).
-//   eng_route_kernel     a6: record -> way (x >= splat, NA by direction), leaves recorded, per-tile left/right counts.
-//   eng_scan_kernel      exclusive scan of the tile counts, first record of every child, next level's node table.
-//   eng_scatter_kernel   stable move of the live records to their child's run in the other buffer.
+//   eng_thresholds_kernel / eng_code_kernel   once per data set: 8-bit order-preserving code of every cell, column-major.
+//   eng_route_kernel     a6 in original row order: row -> child (code compare, exact float compare on code ties),
+//                        leaves recorded, rows per (child, CTA) counted.
+//   eng_scan_kernel      first record of every (child, CTA), next level's node table and centring offsets.
+//   eng_scatter_kernel   next level's records {row, targets - child offset} written to their child's run.
+#include <atomic>
+
 #include "common.cuh"
 #include "engine.h"
 #include "kernels.h"
@@ -84,7 +86,7 @@ __global__ void __launch_bounds__(1024) eng_root_mean_kernel(int64_t rows, const
 __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_rows, const int32_t* __restrict__ wyq_rows,
                                  const int32_t* __restrict__ wyyq_rows, const int32_t* __restrict__ mnode,
                                  int32_t* __restrict__ gidx, uint2* __restrict__ gval, int32_t* __restrict__ gw,
-                                 int32_t* __restrict__ leaf, int32_t* __restrict__ seg) {
+                                 int32_t* __restrict__ leaf, uint16_t* __restrict__ nid16, int32_t* __restrict__ seg) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0) {
     seg[0] = 0;
@@ -97,6 +99,7 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
   gval[p] = make_uint2((unsigned)(wyq_rows[p] - mnode[0]), (unsigned)(wyyq_rows[p] - mnode[1]));
   if (gw) gw[p] = wq_rows[p];
   leaf[p] = -1;
+  nid16[p] = 0;
 }
 
 // first g in [0, n) with table[g + 1] > v (table non-decreasing, table[n] > v)
@@ -478,6 +481,19 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
 }
 
 // ------------------------------------------------------------------------------------------------ a6 + regroup
+// Routing walks the rows in their ORIGINAL order (row -> node map nid16), not the node-grouped records: every access
+// is then a stream.  The value the split needs is not gathered from the row-major copy — a gather of one float per
+// row costs a 128-byte DRAM access each (ncu: 13.2 GB per level at 100M rows, profiles/r02_route_scatter_r01code_*) —
+// but decided from an 8-bit order-preserving code of the cell, kept column-major (code8, one byte per cell, written
+// once per data set): code(x) < code(splat) => x < splat, code(x) > code(splat) => x > splat, and only a row whose
+// code EQUALS the threshold's (~1/255 of a column's rows) reads its float and compares exactly as H2O does
+// (DecidedNode: x >= splat).  A warp of 32 consecutive rows reads one sector per distinct split column among its
+// rows, so a level streams (distinct split columns) x rows bytes at most.
+//
+// Regrouping is a stable-by-range multi-way partition in the same row order: every CTA owns one contiguous range of
+// rows in both kernels; eng_route_kernel counts its rows per child, eng_scan_kernel turns the [child][CTA] counts
+// into first positions, eng_scatter_kernel writes the next level's records {row, targets - child's offset} there.
+// Rows of a node stay ascending up to the order inside a 512-row tile — integer sums do not depend on it.
 // 1024-thread exclusive scan; returns the exclusive prefix, *total gets the block sum (valid for every thread)
 __device__ __forceinline__ int block_exscan_1024(int v, int* s_warp, int* total) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -507,158 +523,210 @@ __device__ __forceinline__ int block_exscan_1024(int v, int* s_warp, int* total)
   return ex;
 }
 
-__global__ void __launch_bounds__(1024) eng_tiles_kernel(const int32_t* __restrict__ seg, int n_nodes,
-                                                         int32_t* __restrict__ tile_base) {
-  __shared__ int s_warp[33];
-  const int g = threadIdx.x;
-  const int nt = g < n_nodes ? (seg[g + 1] - seg[g] + kEngTile - 1) / kEngTile : 0;
-  int total;
-  const int ex = block_exscan_1024(nt, s_warp, &total);
-  if (g <= n_nodes) tile_base[g] = ex;  // tile_base[n_nodes] = number of tiles
-}
+constexpr int kRouteThreads = 512;
+constexpr unsigned kNoNid = 0xFFFFu;
 
-// Routing visits the tiles in "k-th tile of every node" order instead of node by node.  Inside a node the records are
-// ascending in row number, so the k-th tiles of all nodes cover the same stretch of rows: the CTAs in flight together
-// then gather from the same DRAM pages of XT and write the same sectors of leaf[] within a short time of each other
-// (L2 merges the partial sector writes) instead of coming back to every page once per node.
-__global__ void __launch_bounds__(256) eng_order_kernel(const int32_t* __restrict__ tile_base, int n_nodes,
-                                                        int32_t* __restrict__ tile_order) {
-  __shared__ int s_nt[kEngMaxNodes];
-  for (int g = threadIdx.x; g < n_nodes; g += 256) s_nt[g] = tile_base[g + 1] - tile_base[g];
-  __syncthreads();
-  const int t = blockIdx.x * 256 + threadIdx.x;
-  if (t >= tile_base[n_nodes]) return;
-  const int g = seg_of(tile_base, n_nodes, t);
-  const int k = t - tile_base[g];
-  int rank = 0;
-  for (int j = 0; j < n_nodes; j++) rank += min(s_nt[j], k) + (j < g && s_nt[j] > k ? 1 : 0);
-  tile_order[rank] = t;
-}
-
-struct TileRange {
-  int g;
-  int64_t start, end;
-};
-__device__ __forceinline__ TileRange tile_range(const int32_t* __restrict__ seg, const int32_t* __restrict__ tile_base,
-                                                int n_nodes, int t) {
-  TileRange r;
-  r.g = seg_of(tile_base, n_nodes, t);
-  r.start = (int64_t)seg[r.g] + (int64_t)(t - tile_base[r.g]) * kEngTile;
-  const int64_t nend = seg[r.g + 1];
-  r.end = r.start + kEngTile < nend ? r.start + kEngTile : nend;
-  return r;
-}
-
-__global__ void __launch_bounds__(256) eng_route_kernel(const float* __restrict__ XT, int64_t ldt,
-                                                        const int32_t* __restrict__ gidx, const int32_t* __restrict__ seg,
-                                                        const int32_t* __restrict__ tile_base, int n_nodes,
-                                                        const h2ok_split* __restrict__ splits,
-                                                        const int32_t* __restrict__ child_ids, int gid_base,
-                                                        uint8_t* __restrict__ codes, int32_t* __restrict__ leaf,
-                                                        int32_t* __restrict__ tile_cnt,
-                                                        const int32_t* __restrict__ tile_order) {
-  __shared__ int s_cnt[2];
-  if ((int)blockIdx.x >= tile_base[n_nodes]) return;
-  const int t = tile_order[blockIdx.x];
-  const TileRange tr = tile_range(seg, tile_base, n_nodes, t);
-  const int g = tr.g;
-  if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
-  __syncthreads();
-  const int col = splits[g].col;
-  const int na = splits[g].na_dir;
-  const float splat = splits[g].splat;
-  const int c0 = child_ids[2 * g], c1 = child_ids[2 * g + 1];
-  const int leaf0 = (gid_base + g) * 3;
-  int n0 = 0, n1 = 0;
+// order-preserving code of a non-NaN float: -0 counts as +0 so that the codes agree with float comparison
+__device__ __forceinline__ unsigned enc_key(float x) { return enc_f32_bits(__float_as_uint(__fadd_rn(x, 0.0f))); }
+// number of thresholds <= e (thr ascending, 256 entries, unused ones 0xFFFFFFFF)
+__device__ __forceinline__ unsigned code_of(const unsigned* __restrict__ thr, unsigned e) {
+  int lo = 0, hi = 255;  // answer in [0, 255): at most 254 real thresholds
 #pragma unroll
-  for (int j = 0; j < kEngTile / 256; j++) {
-    const int64_t p = tr.start + j * 256 + threadIdx.x;
-    int code = 3;
-    if (p < tr.end) {
-      const int row = gidx[p];
-      code = 2;
-      if (col < 0) {
-        leaf[row] = leaf0;
-      } else {
-        const float d = XT[(int64_t)row * ldt + col];
-        int way;
-        if (d != d) way = (na == H2OK_NA_LEFT) ? 0 : 1;
-        else if (na == H2OK_NA_VS_REST) way = 0;
-        else way = d >= splat ? 1 : 0;
-        if ((way ? c1 : c0) < 0) leaf[row] = leaf0 + 1 + way;
-        else code = way;
-      }
-      codes[p] = (uint8_t)code;
-    }
-    n0 += __popc(__ballot_sync(0xffffffffu, code == 0));
-    n1 += __popc(__ballot_sync(0xffffffffu, code == 1));
+  for (int i = 0; i < 8; i++) {
+    const int mid = (lo + hi) >> 1;
+    if (thr[mid] <= e) lo = mid + 1;
+    else hi = mid;
   }
-  if ((threadIdx.x & 31) == 0) {
-    atomicAdd(&s_cnt[0], n0);
-    atomicAdd(&s_cnt[1], n1);
-  }
-  __syncthreads();
-  if (threadIdx.x < 2) tile_cnt[2 * t + threadIdx.x] = s_cnt[threadIdx.x];
+  return (unsigned)lo;
 }
 
-// One CTA: exclusive scan of the (left, right) tile counts in place (entry [tiles] = totals), the first record of every
-// child slot in the next order, and the next level's node table (children keep the order of their slots 2*node + way,
-// which is also the order of their ids).
-__global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ tile_cnt, const int32_t* __restrict__ tile_base,
-                                                        int n_nodes, const int32_t* __restrict__ child_ids,
-                                                        int32_t* __restrict__ slot_start, int32_t* __restrict__ seg_next,
+// One CTA per column: 4096 evenly spaced sample values, sorted; thresholds = the sample's 1/255 .. 254/255 quantiles.
+__global__ void __launch_bounds__(1024) eng_thresholds_kernel(const float* __restrict__ X, int64_t ld, int64_t rows,
+                                                              unsigned* __restrict__ thr) {
+  constexpr int S = 4096;
+  __shared__ unsigned s[S];
+  const float* x = X + (int64_t)blockIdx.x * ld;
+  for (int i = threadIdx.x; i < S; i += 1024) {
+    const float v = x[(int64_t)i * rows / S];
+    s[i] = v != v ? 0xFFFFFFFFu : enc_key(v);
+  }
+  __syncthreads();
+  for (int k = 2; k <= S; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < S; i += 1024) {
+        const int l = i ^ j;
+        if (l > i) {
+          const unsigned a = s[i], b = s[l];
+          if (((i & k) == 0) == (a > b)) {
+            s[i] = b;
+            s[l] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  unsigned* t = thr + (int64_t)blockIdx.x * 256;
+  for (int i = threadIdx.x; i < 256; i += 1024) t[i] = i < 254 ? s[(i + 1) * S / 255] : 0xFFFFFFFFu;
+}
+
+__global__ void __launch_bounds__(256) eng_code_kernel(const float* __restrict__ X, int64_t ld, int64_t rows,
+                                                       const unsigned* __restrict__ thr, uint8_t* __restrict__ code8,
+                                                       int64_t ld8) {
+  __shared__ unsigned t[256];
+  t[threadIdx.x] = thr[(int64_t)blockIdx.y * 256 + threadIdx.x];
+  __syncthreads();
+  const float* x = X + (int64_t)blockIdx.y * ld;
+  uint8_t* o = code8 + (int64_t)blockIdx.y * ld8;
+  const int64_t r0 = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 4;  // four rows per thread: 128-bit in, 32-bit out
+  if (r0 + 3 < rows && ((ld & 3) == 0)) {
+    const float4 v = *reinterpret_cast<const float4*>(x + r0);
+    const float f[4] = {v.x, v.y, v.z, v.w};
+    unsigned w = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) w |= (f[k] != f[k] ? 255u : code_of(t, enc_key(f[k]))) << (8 * k);
+    *reinterpret_cast<unsigned*>(o + r0) = w;
+  } else {
+    for (int k = 0; k < 4 && r0 + k < rows; k++) {
+      const float f = x[r0 + k];
+      o[r0 + k] = (uint8_t)(f != f ? 255u : code_of(t, enc_key(f)));
+    }
+  }
+}
+
+struct RouteNode {  // what routing needs of one node's split, 16 bytes
+  float splat;
+  short col;          // < 0: the node does not split
+  unsigned char na;   // H2OK_NA_*
+  unsigned char cs;   // code of splat
+  short c0, c1;       // child ids (< 0: that side is a leaf)
+  int leaf0;          // leaf code of "did not split"
+};
+
+// rows of route / scatter CTA b: [b * per, min(rows, (b + 1) * per)), per a multiple of the tile
+__device__ __forceinline__ int64_t route_per(int64_t rows, int G) {
+  const int64_t per = (rows + G - 1) / G;
+  return (per + kRouteThreads - 1) / kRouteThreads * kRouteThreads;
+}
+
+__global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
+    const float* __restrict__ XT, int64_t ldt, const uint8_t* __restrict__ code8, int64_t ld8,
+    const unsigned* __restrict__ thr, int64_t rows, int n_nodes, const h2ok_split* __restrict__ splits,
+    const int32_t* __restrict__ child_ids, int gid_base, uint16_t* __restrict__ nid16, int32_t* __restrict__ leaf,
+    int32_t* __restrict__ cta_cnt, int n_slots) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  RouteNode* tab = reinterpret_cast<RouteNode*>(smem_raw);
+  int* s_cnt = reinterpret_cast<int*>(tab + n_nodes);
+  for (int g = threadIdx.x; g < n_nodes; g += kRouteThreads) {
+    const h2ok_split sp = splits[g];
+    RouteNode t;
+    t.splat = sp.splat;
+    t.col = (short)sp.col;
+    t.na = (unsigned char)sp.na_dir;
+    t.cs = 0;
+    if (sp.col >= 0 && sp.na_dir != H2OK_NA_VS_REST && sp.splat == sp.splat)
+      t.cs = (unsigned char)code_of(thr + (int64_t)sp.col * 256, enc_key(sp.splat));
+    t.c0 = (short)child_ids[2 * g];
+    t.c1 = (short)child_ids[2 * g + 1];
+    t.leaf0 = (gid_base + g) * 3;
+    tab[g] = t;
+  }
+  for (int i = threadIdx.x; i < n_slots; i += kRouteThreads) s_cnt[i] = 0;
+  __syncthreads();
+  const int64_t per = route_per(rows, gridDim.x);
+  const int64_t r0 = (int64_t)blockIdx.x * per;
+  const int64_t r1 = r0 + per < rows ? r0 + per : rows;
+  const unsigned lane = threadIdx.x & 31u;
+  for (int64_t base = r0; base < r1; base += kRouteThreads) {
+    const int64_t r = base + threadIdx.x;
+    unsigned next = kNoNid;
+    if (r < r1) {
+      const unsigned n = nid16[r];
+      if (n != kNoNid && (int)n < n_nodes) {
+        const RouteNode t = tab[n];
+        if (t.col < 0) {
+          leaf[r] = t.leaf0;
+        } else {
+          const unsigned c = code8[(int64_t)t.col * ld8 + r];
+          int way;
+          if (c == 255u) way = (t.na == H2OK_NA_LEFT) ? 0 : 1;
+          else if (t.na == H2OK_NA_VS_REST) way = 0;
+          else if (c != t.cs) way = c > t.cs ? 1 : 0;
+          else way = XT[r * ldt + t.col] >= t.splat ? 1 : 0;  // same code as the threshold: the float decides
+          const int ch = way ? t.c1 : t.c0;
+          if (ch < 0) leaf[r] = t.leaf0 + 1 + way;
+          else next = (unsigned)ch;
+        }
+        nid16[r] = (uint16_t)next;
+      }
+    }
+    // rows per child: one shared-memory add per distinct child of the warp
+    const unsigned grp = __match_any_sync(0xffffffffu, next);
+    if (next != kNoNid && lane == (unsigned)(__ffs(grp) - 1)) atomicAdd(&s_cnt[next], __popc(grp));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_slots; i += kRouteThreads) cta_cnt[(int64_t)i * gridDim.x + blockIdx.x] = s_cnt[i];
+}
+
+// One CTA, one warp per child at a time: exclusive scan of the child's per-CTA counts in place; then the first record
+// of every child (children are numbered in slot order, so their runs follow each other in id order), the next
+// level's node table and the children's centring offsets.
+__global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ cta_cnt, int G, int n_nodes,
+                                                        const int32_t* __restrict__ child_ids, int32_t* __restrict__ seg_next,
                                                         const h2ok_split* __restrict__ splits, double scale_wy,
                                                         double scale_wyy, const int32_t* __restrict__ mnode,
-                                                        int32_t* __restrict__ mnode_next, int32_t* __restrict__ slot_delta) {
+                                                        int32_t* __restrict__ mnode_next) {
   __shared__ int s_warp[33];
-  __shared__ int s_run[2];
-  const int T = tile_base[n_nodes];
-  if (threadIdx.x < 2) s_run[threadIdx.x] = 0;
+  __shared__ int s_tot[kEngMaxNodes];
+  __shared__ int s_nc;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // number of children = 1 + the largest child id
+  int mx = -1;
+  for (int i = threadIdx.x; i < 2 * n_nodes; i += 1024) mx = max(mx, child_ids[i]);
+  mx = __reduce_max_sync(0xffffffffu, mx);
+  if (lane == 0) s_warp[warp] = mx;
   __syncthreads();
-  for (int first = 0; first < T; first += 1024) {
-    const int t = first + threadIdx.x;
-    const int v0 = t < T ? tile_cnt[2 * t] : 0, v1 = t < T ? tile_cnt[2 * t + 1] : 0;
-    int tot0, tot1;
-    const int e0 = block_exscan_1024(v0, s_warp, &tot0);
-    const int e1 = block_exscan_1024(v1, s_warp, &tot1);
-    if (t < T) {
-      tile_cnt[2 * t] = s_run[0] + e0;
-      tile_cnt[2 * t + 1] = s_run[1] + e1;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      s_run[0] += tot0;
-      s_run[1] += tot1;
-    }
-    __syncthreads();
+  if (threadIdx.x == 0) {
+    int m = -1;
+    for (int w = 0; w < 32; w++) m = max(m, s_warp[w]);
+    s_nc = m + 1;
   }
-  if (threadIdx.x < 2) tile_cnt[2 * T + threadIdx.x] = s_run[threadIdx.x];
-  __syncthreads();  // the scanned counts are visible to the whole block
+  __syncthreads();
+  const int nc = s_nc;
+  for (int c = warp; c < nc; c += 32) {
+    int32_t* row = cta_cnt + (int64_t)c * G;
+    int run = 0;
+    for (int b0 = 0; b0 < G; b0 += 32) {
+      const int b = b0 + lane;
+      const int v = b < G ? row[b] : 0;
+      int inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+      }
+      if (b < G) row[b] = run + inc - v;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) s_tot[c] = run;
+  }
+  __syncthreads();
   const int g = threadIdx.x;
-  int tot0 = 0, tot1 = 0, cl = -1, cr = -1;
-  if (g < n_nodes) {
-    const int a = tile_base[g], b = tile_base[g + 1];
-    tot0 = tile_cnt[2 * b] - tile_cnt[2 * a];
-    tot1 = tile_cnt[2 * b + 1] - tile_cnt[2 * a + 1];
-    cl = child_ids[2 * g];
-    cr = child_ids[2 * g + 1];
+  int live;
+  const int ex = block_exscan_1024(g < nc ? s_tot[g] : 0, s_warp, &live);
+  if (g < nc) seg_next[g] = ex;
+  if (g == 0) {
+    seg_next[nc] = live;
+    seg_next[kSegNodes] = nc;
   }
-  int live, nc;
-  const int ex = block_exscan_1024(tot0 + tot1, s_warp, &live);
-  (void)block_exscan_1024((cl >= 0) + (cr >= 0), s_warp, &nc);
   if (g < n_nodes) {
-    slot_start[2 * g] = ex;
-    slot_start[2 * g + 1] = ex + tot0;
-    if (cl >= 0) seg_next[cl] = ex;
-    if (cr >= 0) seg_next[cr] = ex + tot0;
     // centring offsets of the children (see eng_root_mean_kernel): mean y and mean y^2 of the side from the split
-    // record, scaled like the targets; scale 0 (weighted shards) keeps every offset at 0.  slot_delta is what the
-    // scatter adds to a record's stored targets when it moves it from this node to the child.
+    // record, scaled like the targets; scale 0 (weighted shards) keeps every offset at 0
     const h2ok_split sp = splits[g];
     const int pm1 = mnode[2 * g], pm2 = mnode[2 * g + 1];
 #pragma unroll
     for (int way = 0; way < 2; way++) {
-      const int ch = way ? cr : cl;
+      const int ch = child_ids[2 * g + way];
+      if (ch < 0) continue;
       const double pred = way ? sp.pred_right : sp.pred_left, se = way ? sp.se_right : sp.se_left;
       const double n = way ? sp.n_right : sp.n_left;
       int c1 = pm1, c2 = pm2;
@@ -669,94 +737,110 @@ __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ ti
           c2 = __double2int_rn(a2);
         }
       }
-      slot_delta[2 * (2 * g + way)] = pm1 - c1;
-      slot_delta[2 * (2 * g + way) + 1] = pm2 - c2;
-      if (ch >= 0) {
-        mnode_next[2 * ch] = c1;
-        mnode_next[2 * ch + 1] = c2;
+      mnode_next[2 * ch] = c1;
+      mnode_next[2 * ch + 1] = c2;
+    }
+  }
+}
+
+// Tiles of kScatTile consecutive rows are grouped by child in shared memory first (a counting sort inside the tile), so
+// that what goes out to a child's run is one contiguous stretch of records per tile and child instead of one record
+// per store: at depth, 32 consecutive rows belong to ~32 different children, and writing them where they fall was
+// one 32-byte L2 transaction per 4-byte store (4 ms per level at 100M rows and 128 children against 0.5 ms at the root).
+constexpr int kScatThreads = 1024, kScatPer = 4, kScatTile = kScatThreads * kScatPer;
+
+template <bool WEIGHTED>
+__global__ void __launch_bounds__(kScatThreads, 2) eng_scatter_kernel(
+    int64_t rows, const uint16_t* __restrict__ nid16, const int32_t* __restrict__ wq_rows,
+    const int32_t* __restrict__ wyq_rows, const int32_t* __restrict__ wyyq_rows, const int32_t* __restrict__ seg_next,
+    const int32_t* __restrict__ mnode_next, const int32_t* __restrict__ cta_cnt, int G, int32_t* __restrict__ gidx_n,
+    uint2* __restrict__ gval_n, int32_t* __restrict__ gw_n) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_warp[33];
+  const int nc = seg_next[kSegNodes];
+  const int ncp = (nc + 1) & ~1;
+  // per child: running first free record of this CTA's share, the tile's count, its first position in the tile,
+  // (global first record - tile position), centring offsets
+  int* s_off = reinterpret_cast<int*>(smem_raw);
+  int* s_cnt = s_off + ncp;
+  int* s_lb = s_cnt + ncp;
+  int* s_gb = s_lb + ncp;
+  int2* s_m = reinterpret_cast<int2*>(s_gb + ncp);
+  uint2* s_val = reinterpret_cast<uint2*>(s_m + ncp);
+  int* s_row = reinterpret_cast<int*>(s_val + kScatTile);
+  int* s_w = s_row + kScatTile;
+  uint16_t* s_child = reinterpret_cast<uint16_t*>(s_w + (WEIGHTED ? kScatTile : 0));
+  // every scatter CTA covers the rows of G / gridDim.x routing CTAs
+  const int per_cta = G / gridDim.x;
+  for (int c = threadIdx.x; c < nc; c += kScatThreads) {
+    s_off[c] = seg_next[c] + cta_cnt[(int64_t)c * G + blockIdx.x * per_cta];
+    s_m[c] = make_int2(mnode_next[2 * c], mnode_next[2 * c + 1]);
+  }
+  const int64_t per = route_per(rows, G) * per_cta;
+  const int64_t r0 = (int64_t)blockIdx.x * per;
+  const int64_t r1 = r0 + per < rows ? r0 + per : rows;
+  const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  for (int64_t base = r0; base < r1; base += kScatTile) {
+    for (int c = threadIdx.x; c < nc; c += kScatThreads) s_cnt[c] = 0;
+    __syncthreads();
+    unsigned ch[kScatPer];
+    int rank[kScatPer];
+#pragma unroll
+    for (int k = 0; k < kScatPer; k++) {
+      const int64_t r = base + k * kScatThreads + threadIdx.x;
+      ch[k] = r < r1 ? nid16[r] : kNoNid;
+    }
+#pragma unroll
+    for (int k = 0; k < kScatPer; k++) {  // position of the row among the tile's rows of its child
+      const unsigned grp = __match_any_sync(0xffffffffu, ch[k]);
+      const int leader = __ffs(grp) - 1;
+      int first = 0;
+      if (ch[k] != kNoNid && (int)lane == leader) first = atomicAdd(&s_cnt[ch[k]], __popc(grp));
+      rank[k] = __shfl_sync(0xffffffffu, first, leader) + __popc(grp & lt);
+    }
+    __syncthreads();
+    int total = 0;
+    for (int c0 = 0; c0 < nc; c0 += kScatThreads) {  // tile positions of the children (exclusive scan of the counts)
+      const int c = c0 + threadIdx.x;
+      const int v = c < nc ? s_cnt[c] : 0;
+      int tot;
+      const int ex = block_exscan_1024(v, s_warp, &tot);
+      if (c < nc) {
+        s_lb[c] = total + ex;
+        s_gb[c] = s_off[c] - (total + ex);
+        s_off[c] += v;
+      }
+      total += tot;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kScatPer; k++) {
+      if (ch[k] != kNoNid) {
+        const int64_t r = base + k * kScatThreads + threadIdx.x;
+        const int pos = s_lb[ch[k]] + rank[k];
+        const int2 m = s_m[ch[k]];
+        s_row[pos] = (int)r;
+        s_val[pos] = make_uint2((unsigned)(wyq_rows[r] - m.x), (unsigned)(wyyq_rows[r] - m.y));
+        if (WEIGHTED) s_w[pos] = wq_rows[r];
+        s_child[pos] = (uint16_t)ch[k];
       }
     }
-  }
-  if (g == 0) {
-    seg_next[nc] = live;
-    seg_next[kSegNodes] = nc;
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += kScatThreads) {
+      const int d = s_gb[s_child[i]] + i;
+      gidx_n[d] = s_row[i];
+      gval_n[d] = s_val[i];
+      if (WEIGHTED) gw_n[d] = s_w[i];
+    }
+    __syncthreads();
   }
 }
 
-__global__ void __launch_bounds__(256) eng_scatter_kernel(const int32_t* __restrict__ gidx, const uint2* __restrict__ gval,
-                                                          const int32_t* __restrict__ gw, int32_t* __restrict__ gidx_n,
-                                                          uint2* __restrict__ gval_n, int32_t* __restrict__ gw_n,
-                                                          const int32_t* __restrict__ seg,
-                                                          const int32_t* __restrict__ tile_base, int n_nodes,
-                                                          const uint8_t* __restrict__ codes,
-                                                          const int32_t* __restrict__ tile_cnt,
-                                                          const int32_t* __restrict__ slot_start,
-                                                          const int32_t* __restrict__ slot_delta) {
-  constexpr int J = kEngTile / 256;
-  __shared__ unsigned s_pre[J * 8];  // per (step, warp): records going left (low half) / right (high half)
-  const int t = blockIdx.x;
-  if (t >= tile_base[n_nodes]) return;
-  const TileRange tr = tile_range(seg, tile_base, n_nodes, t);
-  const int g = tr.g;
-  const int tb = tile_base[g];
-  const int64_t base0 = (int64_t)slot_start[2 * g] + tile_cnt[2 * t] - tile_cnt[2 * tb];
-  const int64_t base1 = (int64_t)slot_start[2 * g + 1] + tile_cnt[2 * t + 1] - tile_cnt[2 * tb + 1];
-  const int d1l = slot_delta[4 * g], d2l = slot_delta[4 * g + 1], d1r = slot_delta[4 * g + 2], d2r = slot_delta[4 * g + 3];
-  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  int code[J];
-#pragma unroll
-  for (int j = 0; j < J; j++) {
-    const int64_t p = tr.start + j * 256 + threadIdx.x;
-    code[j] = p < tr.end ? (int)codes[p] : 3;
-    const unsigned b0 = __ballot_sync(0xffffffffu, code[j] == 0), b1 = __ballot_sync(0xffffffffu, code[j] == 1);
-    if (lane == 0) s_pre[j * 8 + warp] = (unsigned)__popc(b0) | ((unsigned)__popc(b1) << 16);
-  }
-  __syncthreads();
-  if (warp == 0) {  // exclusive scan of the J * 8 packed pairs in (step, warp) order = record order
-    unsigned v[J * 8 / 32], sum = 0;
-#pragma unroll
-    for (int i = 0; i < J * 8 / 32; i++) {
-      v[i] = s_pre[lane * (J * 8 / 32) + i];
-      sum += v[i];
-    }
-    unsigned inc = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const unsigned u = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += u;
-    }
-    unsigned run = inc - sum;
-#pragma unroll
-    for (int i = 0; i < J * 8 / 32; i++) {
-      s_pre[lane * (J * 8 / 32) + i] = run;
-      run += v[i];
-    }
-  }
-  __syncthreads();
-  const unsigned lt = (1u << lane) - 1u;
-#pragma unroll
-  for (int j = 0; j < J; j++) {
-    const int64_t p = tr.start + j * 256 + threadIdx.x;
-    const unsigned b0 = __ballot_sync(0xffffffffu, code[j] == 0), b1 = __ballot_sync(0xffffffffu, code[j] == 1);
-    const unsigned pre = s_pre[j * 8 + warp];
-    if (code[j] < 2) {
-      const int64_t d = code[j] == 0 ? base0 + (pre & 0xFFFFu) + __popc(b0 & lt) : base1 + (pre >> 16) + __popc(b1 & lt);
-      gidx_n[d] = gidx[p];
-      uint2 v = gval[p];  // stored relative to this node's offsets; the child's run stores it relative to the child's
-      v.x += (unsigned)(code[j] ? d1r : d1l);
-      v.y += (unsigned)(code[j] ? d2r : d2l);
-      gval_n[d] = v;
-      if (gw) gw_n[d] = gw[p];
-    }
-  }
-}
-
-__global__ void eng_nid_kernel(const int32_t* __restrict__ gidx, const int32_t* __restrict__ seg,
-                               int32_t* __restrict__ nid_rows) {
-  const int n_nodes = seg[kSegNodes];
-  const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n_nodes < 1 || p >= seg[n_nodes]) return;
-  nid_rows[gidx[p]] = seg_of(seg, n_nodes, p);
+__global__ void eng_nid_kernel(const uint16_t* __restrict__ nid16, int64_t rows, int32_t* __restrict__ nid_rows) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  const unsigned n = nid16[r];
+  nid_rows[r] = n == kNoNid ? -1 : (int32_t)n;
 }
 
 }  // namespace
@@ -764,17 +848,27 @@ __global__ void eng_nid_kernel(const int32_t* __restrict__ gidx, const int32_t* 
 // ------------------------------------------------------------------------------------------------ host side
 cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   engine_free(e);
-  if (rows >= (1ll << 31) - kEngTile) return cudaErrorInvalidValue;
+  if (rows >= (1ll << 31) - 4096) return cudaErrorInvalidValue;
+  if (cols > 32767) return cudaErrorInvalidValue;  // the routing table keeps the split column in 16 bits
   e.rows = rows;
   e.cols = cols;
   e.weighted = weighted;
   e.ldt = ((int64_t)cols + 7) / 8 * 8;
-  e.max_tiles = rows / kEngTile + kEngMaxNodes + 1;
-  cudaError_t err = cudaSuccess;
+  e.ld8 = (rows + 127) / 128 * 128;
+  int dev = 0, sms = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (err != cudaSuccess) return err;
+  e.sms = sms;
+  e.route_ctas = 4 * sms;  // four 512-thread CTAs per SM, each with one contiguous range of rows
   auto A = [&](void** p, size_t bytes) {
     if (err == cudaSuccess) err = cudaMalloc(p, bytes);
   };
   A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  A((void**)&e.code8, (size_t)cols * (size_t)e.ld8);
+  A((void**)&e.thr, sizeof(uint32_t) * 256 * (size_t)cols);
+  A((void**)&e.cmin, sizeof(uint32_t) * (size_t)cols);
+  A((void**)&e.cmax, sizeof(uint32_t) * (size_t)cols);
   for (int k = 0; k < 2; k++) {
     A((void**)&e.gidx[k], sizeof(int32_t) * (size_t)rows);
     A((void**)&e.gval[k], sizeof(uint2) * (size_t)rows);
@@ -782,13 +876,9 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
     A((void**)&e.seg[k], sizeof(int32_t) * kSegInts);
     A((void**)&e.mnode[k], sizeof(int32_t) * 2 * kEngMaxNodes);
   }
-  A((void**)&e.codes, (size_t)rows);
-  A((void**)&e.tile_base, sizeof(int32_t) * (kEngMaxNodes + 1));
-  A((void**)&e.tile_cnt, sizeof(int32_t) * 2 * (size_t)(e.max_tiles + 1));
-  A((void**)&e.tile_order, sizeof(int32_t) * (size_t)(e.max_tiles + 1));
-  A((void**)&e.slot_start, sizeof(int32_t) * 2 * kEngMaxNodes);
+  A((void**)&e.nid16, sizeof(uint16_t) * (size_t)rows);
+  A((void**)&e.cta_cnt, sizeof(int32_t) * (size_t)kEngMaxNodes * (size_t)e.route_ctas);
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
-  A((void**)&e.slot_delta, sizeof(int32_t) * 4 * kEngMaxNodes);
   A((void**)&e.err, sizeof(int32_t));
   if (err == cudaSuccess) err = cudaMemset(e.err, 0, sizeof(int32_t));
   if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
@@ -797,19 +887,20 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
 }
 
 void engine_free(Engine& e) {
-  cudaFree(e.XT);
+  cudaFree(e.XT); cudaFree(e.code8); cudaFree(e.thr); cudaFree(e.cmin); cudaFree(e.cmax);
+  e.cmin = e.cmax = nullptr;
   for (int k = 0; k < 2; k++) {
     cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]); cudaFree(e.mnode[k]);
     e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr; e.mnode[k] = nullptr;
   }
-  cudaFree(e.codes); cudaFree(e.tile_base); cudaFree(e.tile_cnt); cudaFree(e.tile_order); cudaFree(e.slot_start);
-  cudaFree(e.leaf); cudaFree(e.err); cudaFree(e.slot_delta);
-  e.err = nullptr;
-  e.slot_delta = nullptr;
+  cudaFree(e.nid16); cudaFree(e.cta_cnt); cudaFree(e.leaf); cudaFree(e.err);
   e.XT = nullptr;
-  e.codes = nullptr;
-  e.tile_base = e.tile_cnt = e.tile_order = e.slot_start = e.leaf = nullptr;
-  e.rows = e.ldt = 0;
+  e.code8 = nullptr;
+  e.thr = nullptr;
+  e.nid16 = nullptr;
+  e.cta_cnt = e.leaf = e.err = nullptr;
+  e.wq_rows = e.wyq_rows = e.wyyq_rows = nullptr;
+  e.rows = e.ldt = e.ld8 = 0;
   e.n_nodes = 0;
 }
 
@@ -829,7 +920,13 @@ cudaError_t engine_set_weighted(Engine& e, bool weighted) {
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s) {
   dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
   eng_load_kernel<<<grid, 256, 0, s>>>(X, ld, e.rows, col0, ncols, e.XT, e.ldt);
-  return cudaGetLastError();
+  // the routing codes of the same columns: thresholds from a sorted sample, then one byte per cell
+  eng_thresholds_kernel<<<ncols, 1024, 0, s>>>(X, ld, e.rows, e.thr + (int64_t)col0 * 256);
+  dim3 cgrid(nblk(e.rows, 1024), (unsigned)ncols);
+  eng_code_kernel<<<cgrid, 256, 0, s>>>(X, ld, e.rows, e.thr + (int64_t)col0 * 256, e.code8 + (int64_t)col0 * e.ld8, e.ld8);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return err;
+  return launch_col_ranges(X, ld, e.rows, ncols, e.cmin + col0, e.cmax + col0, s);  // DHistogram.initialHist reads them
 }
 
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
@@ -838,10 +935,13 @@ cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* 
   e.n_nodes = 1;
   e.scale_wy = (q && !e.weighted) ? q->scale_wy : 0.0;
   e.scale_wyy = (q && !e.weighted) ? q->scale_wyy : 0.0;
+  e.wq_rows = e.weighted ? wq_rows : nullptr;  // read again by every level's regrouping
+  e.wyq_rows = wyq_rows;
+  e.wyyq_rows = wyyq_rows;
   eng_root_mean_kernel<<<1, 1024, 0, s>>>(e.rows, wyq_rows, wyyq_rows, e.weighted, e.mnode[0]);
   eng_begin_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.rows, e.weighted ? wq_rows : nullptr, wyq_rows, wyyq_rows,
                                                      e.mnode[0], e.gidx[0], e.gval[0], e.weighted ? e.gw[0] : nullptr,
-                                                     e.leaf, e.seg[0]);
+                                                     e.leaf, e.nid16, e.seg[0]);
   return cudaGetLastError();
 }
 
@@ -863,14 +963,14 @@ int engine_max_nb1(int cols) {
 
 template <int CPL, bool W, int LPR>
 static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
-  static bool attr_done[64] = {};  // per device, per instantiation
+  static std::atomic<bool> attr_done[64];  // per device, per instantiation (setting it twice is harmless)
   int dev = 0;
   cudaGetDevice(&dev);
-  bool& attr = attr_done[dev & 63];
-  if (!attr) {
+  std::atomic<bool>& attr = attr_done[dev & 63];
+  if (!attr.load(std::memory_order_acquire)) {
     cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
     if (e != cudaSuccess) return e;
-    attr = true;
+    attr.store(true, std::memory_order_release);
   }
   eng_hist_kernel<CPL, W, LPR><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
   return cudaGetLastError();
@@ -903,7 +1003,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   a.err = e.err;
   const int colblk = lay.lpr * lay.cpl;
   // one CTA per SM and column block; every CTA owns the same share of the level's records
-  const dim3 grid((unsigned)kSMs, (unsigned)((e.cols + colblk - 1) / colblk));
+  const dim3 grid((unsigned)e.sms, (unsigned)((e.cols + colblk - 1) / colblk));
   const size_t smem = (size_t)colblk * nbs * 12;
   if (e.weighted) {
     if (lay.cpl == 2) return launch_eng_hist<2, true, 32>(a, grid, smem, s);
@@ -916,20 +1016,40 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
 }
 
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,
-                                cudaStream_t s) {
+                                bool regroup, cudaStream_t s) {
   if (n_nodes < 1 || n_nodes >= kEngMaxNodes) return cudaErrorInvalidValue;
+  if (!e.wyq_rows) return cudaErrorInvalidValue;
   const int nx = 1 - e.cur;
-  const unsigned tiles = (unsigned)(e.rows / kEngTile + n_nodes + 1);  // bound: the live count stays on the device
-  eng_tiles_kernel<<<1, 1024, 0, s>>>(e.seg[e.cur], n_nodes, e.tile_base);
-  eng_order_kernel<<<nblk(tiles, 256), 256, 0, s>>>(e.tile_base, n_nodes, e.tile_order);
-  eng_route_kernel<<<tiles, 256, 0, s>>>(e.XT, e.ldt, e.gidx[e.cur], e.seg[e.cur], e.tile_base, n_nodes, splits, child_ids,
-                                         gid_base, e.codes, e.leaf, e.tile_cnt, e.tile_order);
-  eng_scan_kernel<<<1, 1024, 0, s>>>(e.tile_cnt, e.tile_base, n_nodes, child_ids, e.slot_start, e.seg[nx], splits, e.scale_wy,
-                                     e.scale_wyy, e.mnode[e.cur], e.mnode[nx], e.slot_delta);
-  eng_scatter_kernel<<<tiles, 256, 0, s>>>(e.gidx[e.cur], e.gval[e.cur], e.weighted ? e.gw[e.cur] : nullptr, e.gidx[nx],
-                                           e.gval[nx], e.weighted ? e.gw[nx] : nullptr,
-                                           e.seg[e.cur], e.tile_base, n_nodes, e.codes, e.tile_cnt, e.slot_start,
-                                           e.slot_delta);
+  const int G = e.route_ctas;
+  const int n_slots = 2 * n_nodes < kEngMaxNodes ? 2 * n_nodes : kEngMaxNodes;  // child ids are < this
+  const size_t rsmem = (size_t)n_nodes * sizeof(RouteNode) + (size_t)n_slots * sizeof(int);
+  eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, e.code8, e.ld8, e.thr, e.rows, n_nodes, splits, child_ids,
+                                                   gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots);
+  // every level but a tree's last: lay the children's records out for the next histogram pass
+  eng_scan_kernel<<<1, 1024, 0, s>>>(e.cta_cnt, G, n_nodes, child_ids, e.seg[nx], splits, e.scale_wy, e.scale_wyy,
+                                     e.mnode[e.cur], e.mnode[nx]);
+  if (regroup) {
+    const size_t ncp = (size_t)(n_slots + 1) & ~(size_t)1;
+    const size_t ssmem = ncp * (4 * sizeof(int) + sizeof(int2)) +
+                         (size_t)kScatTile * (sizeof(uint2) + sizeof(int) + sizeof(uint16_t) + (e.weighted ? sizeof(int) : 0));
+    const int SG = G / 2;  // two 1024-thread CTAs per SM; each covers the rows of two routing CTAs
+    static std::atomic<bool> attr_done[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
+      cudaError_t ea = cudaFuncSetAttribute(eng_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+      if (ea == cudaSuccess)
+        ea = cudaFuncSetAttribute(eng_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+      if (ea != cudaSuccess) return ea;
+      attr_done[dev & 63].store(true, std::memory_order_release);
+    }
+    if (e.weighted)
+      eng_scatter_kernel<true><<<SG, kScatThreads, ssmem, s>>>(e.rows, e.nid16, e.wq_rows, e.wyq_rows, e.wyyq_rows, e.seg[nx],
+                                                               e.mnode[nx], e.cta_cnt, G, e.gidx[nx], e.gval[nx], e.gw[nx]);
+    else
+      eng_scatter_kernel<false><<<SG, kScatThreads, ssmem, s>>>(e.rows, e.nid16, e.wq_rows, e.wyq_rows, e.wyyq_rows, e.seg[nx],
+                                                                e.mnode[nx], e.cta_cnt, G, e.gidx[nx], e.gval[nx], nullptr);
+  }
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return err;
   e.cur = nx;
@@ -938,9 +1058,7 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
 }
 
 cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s) {
-  cudaError_t err = cudaMemsetAsync(nid_rows, 0xFF, sizeof(int32_t) * (size_t)e.rows, s);
-  if (err != cudaSuccess) return err;
-  eng_nid_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.gidx[e.cur], e.seg[e.cur], nid_rows);
+  eng_nid_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.nid16, e.rows, nid_rows);
   return cudaGetLastError();
 }
 

@@ -55,20 +55,33 @@ __device__ __forceinline__ double warp_incl_scan(double v, int lane) {
   return v;
 }
 
+// Where a (node, column)'s bins come from: the fp64 histogram, or the int64 fixed-point accumulators converted on the
+// fly with finalize's rule (one exact multiplication by a power of two), which skips materialising the histogram.
+struct ValsF64 {
+  const double* __restrict__ p;
+  __device__ __forceinline__ double operator()(int b, int ch) const { return p[3 * b + ch]; }
+};
+struct ValsAcc {
+  const int64_t* __restrict__ p;
+  double inv[3];
+  __device__ __forceinline__ double operator()(int b, int ch) const { return __dmul_rn((double)p[3 * b + ch], inv[ch]); }
+};
+
 // One warp evaluates one (node, column).  Returns found != 0 in every lane and the winning candidate in `out`.
-__device__ int warp_best_split_point(const double* __restrict__ vals, int nbins, double min_rows, double msi, int lane,
+template <class V>
+__device__ int warp_best_split_point(const V& vals, int nbins, double min_rows, double msi, int lane,
                                      Cand& out, double& se_before_out) {
   if (nbins <= 1) return 0;
   double W = 0, WY = 0, WYY = 0;
   for (int b = lane; b < nbins; b += 32) {
-    W = __dadd_rn(W, vals[3 * b]);
-    WY = __dadd_rn(WY, vals[3 * b + 1]);
-    WYY = __dadd_rn(WYY, vals[3 * b + 2]);
+    W = __dadd_rn(W, vals(b, 0));
+    WY = __dadd_rn(WY, vals(b, 1));
+    WYY = __dadd_rn(WYY, vals(b, 2));
   }
   W = warp_sum(W);
   WY = warp_sum(WY);
   WYY = warp_sum(WYY);
-  const double wNA = vals[3 * nbins], wYNA = vals[3 * nbins + 1], wYYNA = vals[3 * nbins + 2];
+  const double wNA = vals(nbins, 0), wYNA = vals(nbins, 1), wYYNA = vals(nbins, 2);
   const double tot = __dadd_rn(W, wNA);
   if (tot < __dmul_rn(2.0, min_rows)) return 0;
   const double sy = __dadd_rn(WY, wYNA);
@@ -109,9 +122,9 @@ __device__ int warp_best_split_point(const double* __restrict__ vals, int nbins,
     const int b = 32 * k + lane;
     double v0 = 0, v1 = 0, v2 = 0;
     if (b < nbins) {
-      v0 = vals[3 * b];
-      v1 = vals[3 * b + 1];
-      v2 = vals[3 * b + 2];
+      v0 = vals(b, 0);
+      v1 = vals(b, 1);
+      v2 = vals(b, 2);
     }
     double i0 = warp_incl_scan(v0, lane), i1 = warp_incl_scan(v1, lane), i2 = warp_incl_scan(v2, lane);
     const double wlo = __dadd_rn(cw, __dsub_rn(i0, v0));  // exclusive prefix: bins [0,b)
@@ -194,11 +207,12 @@ __device__ int warp_best_split_point(const double* __restrict__ vals, int nbins,
 }
 
 // DTree.Split.splat for the chosen (node, col, bin): warp-parallel search of the neighbouring non-empty bins.
-__device__ float warp_splat(const double* __restrict__ vals, const h2ok_col_desc& d, int bin, int na, int lane) {
+template <class V>
+__device__ float warp_splat(const V& vals, const h2ok_col_desc& d, int bin, int na, int lane) {
   if (na == H2OK_NA_VS_REST) return -1.0f;
   int x = -1, n = d.nbin;
   for (int b = lane; b < d.nbin; b += 32) {
-    if (vals[3 * b] != 0) {
+    if (vals(b, 0) != 0) {
       if (b < bin) x = max(x, b);
       else n = min(n, b);
     }
@@ -212,74 +226,88 @@ __device__ float warp_splat(const double* __restrict__ vals, const h2ok_col_desc
   return (float)__ddiv_rn(__dadd_rn(lo, hi), 2.0);
 }
 
-__global__ void __launch_bounds__(kSplitWarps * 32) find_splits_kernel(const double* __restrict__ hist,
-                                                                      const h2ok_col_desc* __restrict__ descs, int cols,
-                                                                      int nb1, double min_rows, double msi,
-                                                                      h2ok_split* __restrict__ splits) {
-  __shared__ Cand s_best[kSplitWarps];
-  __shared__ double s_se_before[kSplitWarps];
-  __shared__ int s_col[kSplitWarps];
-  __shared__ int s_win;
-  const int g = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  Cand wbest;
-  double wbefore = 0;
-  int wcol = -1;
-  for (int c = warp; c < cols; c += kSplitWarps) {
-    const h2ok_col_desc& d = descs[(int64_t)g * cols + c];
-    if (d.nbin <= 1) continue;
-    const double* vals = hist + ((int64_t)g * cols + c) * nb1 * 3;
+// a7 in two steps, so that the (node, column) pairs can be spread over all SMs — and over ranks (SURVEY.md §8(e)
+// "preferred form": every rank searches the pairs whose histograms the reduce-scatter left with it):
+//   split_points_kernel  one warp per pair of [pair0, pair1): DTree.findBestSplitPoint + Split.splat -> PairCand
+//   best_col_kernel      one warp per node: UndecidedNode.bestCol over the node's PairCands -> h2ok_split
+// n_nodes may live on the device (n_dev != NULL): grids are then sized by an upper bound and surplus warps leave.
+template <class V>
+__global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, const h2ok_col_desc* __restrict__ descs,
+                                                                        int64_t pair0, int64_t pair1, int nb1,
+                                                                        double min_rows, double msi,
+                                                                        PairCand* __restrict__ out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t pair = pair0 + (int64_t)blockIdx.x * kSplitWarps + warp;
+  if (pair >= pair1) return;
+  const h2ok_col_desc d = descs[pair];
+  PairCand pc;
+  pc.found = 0;
+  pc.bin = pc.na = 0;
+  pc.splat = 0.0f;
+  pc.key = pc.seL = pc.seR = pc.nL = pc.nR = pc.pL = pc.pR = pc.se_before = 0;
+  if (d.nbin > 1) {
+    V vals = base;
+    vals.p += pair * nb1 * 3;
     Cand cand;
     double before;
-    if (!warp_best_split_point(vals, d.nbin, min_rows, msi, lane, cand, before)) continue;
-    if (wcol < 0 || cand.key < wbest.key) {  // bestCol: strictly smaller se wins, lowest column on ties
-      wbest = cand;
-      wbefore = before;
-      wcol = c;
+    if (warp_best_split_point(vals, d.nbin, min_rows, msi, lane, cand, before)) {
+      pc.found = 1;
+      pc.key = cand.key;
+      pc.seL = cand.seL; pc.seR = cand.seR; pc.nL = cand.nL; pc.nR = cand.nR; pc.pL = cand.pL; pc.pR = cand.pR;
+      pc.se_before = before;
+      pc.bin = cand.bin;
+      pc.na = cand.na;
+      pc.splat = warp_splat(vals, d, cand.bin, cand.na, lane);
     }
   }
-  if (lane == 0) {
-    s_col[warp] = wcol;
-    if (wcol >= 0) {
-      s_best[warp] = wbest;
-      s_se_before[warp] = wbefore;
+  if (lane == 0) out[pair] = pc;
+}
+
+__global__ void __launch_bounds__(kSplitWarps * 32) best_col_kernel(const PairCand* __restrict__ cand, int n_nodes, int cols,
+                                                                   h2ok_split* __restrict__ splits) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x * kSplitWarps + warp;
+  if (g >= n_nodes) return;
+  // bestCol: strictly smaller se wins, lowest column on ties
+  double bk = 0;
+  int bc = 0x7fffffff;
+  for (int c = lane; c < cols; c += 32) {
+    const PairCand& p = cand[(int64_t)g * cols + c];
+    if (p.found && (bc == 0x7fffffff || p.key < bk)) {
+      bk = p.key;
+      bc = c;
     }
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int win = -1;
-    for (int w = 0; w < kSplitWarps; w++) {
-      if (s_col[w] < 0) continue;
-      if (win < 0 || s_best[w].key < s_best[win].key || (s_best[w].key == s_best[win].key && s_col[w] < s_col[win])) win = w;
+  for (int off = 16; off; off >>= 1) {
+    const double k2 = __shfl_xor_sync(kFull, bk, off);
+    const int c2 = __shfl_xor_sync(kFull, bc, off);
+    if (c2 != 0x7fffffff && (bc == 0x7fffffff || k2 < bk || (k2 == bk && c2 < bc))) {
+      bk = k2;
+      bc = c2;
     }
-    s_win = win;
   }
-  __syncthreads();
-  if (warp != 0) return;
-  const int win = s_win;
+  if (lane != 0) return;
   h2ok_split out;
   out.col = -1;
   out.bin = 0;
   out.na_dir = 0;
   out.splat = 0.0f;
   out.se_before = out.se_left = out.se_right = out.n_left = out.n_right = out.pred_left = out.pred_right = 0;
-  if (win >= 0) {
-    const Cand b = s_best[win];
-    const int c = s_col[win];
-    const h2ok_col_desc d = descs[(int64_t)g * cols + c];
-    const double* vals = hist + ((int64_t)g * cols + c) * nb1 * 3;
-    out.col = c;
-    out.bin = b.bin;
-    out.na_dir = b.na;
-    out.splat = warp_splat(vals, d, b.bin, b.na, lane);
-    out.se_before = s_se_before[win];
-    out.se_left = b.seL;
-    out.se_right = b.seR;
-    out.n_left = b.nL;
-    out.n_right = b.nR;
-    out.pred_left = b.pL;
-    out.pred_right = b.pR;
+  if (bc != 0x7fffffff) {
+    const PairCand p = cand[(int64_t)g * cols + bc];
+    out.col = bc;
+    out.bin = p.bin;
+    out.na_dir = p.na;
+    out.splat = p.splat;
+    out.se_before = p.se_before;
+    out.se_left = p.seL;
+    out.se_right = p.seR;
+    out.n_left = p.nL;
+    out.n_right = p.nR;
+    out.pred_left = p.pL;
+    out.pred_right = p.pR;
   }
-  if (lane == 0) splits[g] = out;
+  splits[g] = out;
 }
 
 // ---- a8 ---------------------------------------------------------------------------------------------------
@@ -326,8 +354,11 @@ __device__ inline bool equals_within_one_small_ulp(double a, double b) {
   return fabs(__dsub_rn(a, b)) <= su;
 }
 
+// ENC: min2 / maxin are the order-preserving uint32 encodings the histogram pass (and the cross-rank reduce) work on,
+// decoded here with finalize's rule instead of in a kernel of their own
+template <bool ENC>
 __global__ void next_level_descs_kernel(const h2ok_split* __restrict__ splits, const h2ok_col_desc* __restrict__ descs,
-                                        const float* __restrict__ min2, const float* __restrict__ maxin, int n_nodes,
+                                        const void* __restrict__ min2_v, const void* __restrict__ maxin_v, int n_nodes,
                                         int cols, h2ok_params p, h2ok_col_desc* __restrict__ tmp,
                                         int32_t* __restrict__ valid) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -349,8 +380,14 @@ __global__ void next_level_descs_kernel(const h2ok_split* __restrict__ splits, c
   }
   if (ok) {
     int adj_nbins = (h.nbin >> 1) > p.nbins ? (h.nbin >> 1) : p.nbins;
-    double mn = (double)min2[(int64_t)g * cols + j];
-    double mxin = (double)maxin[(int64_t)g * cols + j];
+    double mn, mxin;
+    if (ENC) {
+      mn = (double)__fadd_rn(__uint_as_float(dec_f32_bits(static_cast<const uint32_t*>(min2_v)[(int64_t)g * cols + j])), 0.0f);
+      mxin = (double)__fadd_rn(__uint_as_float(dec_f32_bits(static_cast<const uint32_t*>(maxin_v)[(int64_t)g * cols + j])), 0.0f);
+    } else {
+      mn = (double)static_cast<const float*>(min2_v)[(int64_t)g * cols + j];
+      mxin = (double)static_cast<const float*>(maxin_v)[(int64_t)g * cols + j];
+    }
     ok = !(mxin == mn) && (mn <= mxin);
     if (ok) {
       double maxex = find_maxex(mxin, h.is_int);
@@ -446,24 +483,64 @@ __global__ void apply_splits_kernel(const float* __restrict__ X, int64_t ld, int
 
 }  // namespace
 
+cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_col_desc* descs,
+                                int64_t pair0, int64_t pair1, int nb1, double min_rows, double msi, PairCand* cand,
+                                cudaStream_t s) {
+  if (pair1 <= pair0) return cudaSuccess;
+  const unsigned grid = (unsigned)((pair1 - pair0 + kSplitWarps - 1) / kSplitWarps);
+  if (hist) {
+    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, 0, s>>>(ValsF64{hist}, descs, pair0, pair1, nb1, min_rows, msi, cand);
+  } else {
+    ValsAcc v{acc, {1.0 / q->scale_w, 1.0 / q->scale_wy, 1.0 / q->scale_wyy}};
+    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, 0, s>>>(v, descs, pair0, pair1, nb1, min_rows, msi, cand);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_split* splits, cudaStream_t s) {
+  best_col_kernel<<<(unsigned)((n_nodes + kSplitWarps - 1) / kSplitWarps), kSplitWarps * 32, 0, s>>>(cand, n_nodes, cols, splits);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
-                               double min_rows, double msi, h2ok_split* splits, cudaStream_t s) {
-  find_splits_kernel<<<n_nodes, kSplitWarps * 32, 0, s>>>(hist, descs, cols, nb1, min_rows, msi, splits);
+                               double min_rows, double msi, PairCand* cand, h2ok_split* splits, cudaStream_t s) {
+  cudaError_t e = launch_split_points(hist, nullptr, nullptr, descs, 0, (int64_t)n_nodes * cols, nb1, min_rows, msi, cand, s);
+  if (e != cudaSuccess) return e;
+  return launch_best_col(cand, n_nodes, cols, splits, s);
+}
+
+static cudaError_t next_level_any(bool enc, const h2ok_split* splits, const h2ok_col_desc* descs, const void* min2,
+                                  const void* maxin, int n_nodes, int cols, const h2ok_params& p, h2ok_col_desc* tmp_descs,
+                                  int32_t* tmp_valid, h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children,
+                                  cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(tmp_valid, 0, sizeof(int32_t) * 2 * (size_t)n_nodes, s);
+  if (e != cudaSuccess) return e;
+  int64_t n = (int64_t)2 * n_nodes * cols;
+  if (enc)
+    next_level_descs_kernel<true><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(splits, descs, min2, maxin, n_nodes, cols, p,
+                                                                              tmp_descs, tmp_valid);
+  else
+    next_level_descs_kernel<false><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(splits, descs, min2, maxin, n_nodes, cols, p,
+                                                                               tmp_descs, tmp_valid);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  next_level_compact_kernel<<<1, 1024, 0, s>>>(tmp_descs, tmp_valid, n_nodes, cols, child_descs, child_ids, n_children);
   return cudaGetLastError();
 }
 
 cudaError_t launch_next_level(const h2ok_split* splits, const h2ok_col_desc* descs, const float* min2, const float* maxin,
                               int n_nodes, int cols, const h2ok_params& p, h2ok_col_desc* tmp_descs, int32_t* tmp_valid,
                               h2ok_col_desc* child_descs, int32_t* child_ids, int32_t* n_children, cudaStream_t s) {
-  cudaError_t e = cudaMemsetAsync(tmp_valid, 0, sizeof(int32_t) * 2 * (size_t)n_nodes, s);
-  if (e != cudaSuccess) return e;
-  int64_t n = (int64_t)2 * n_nodes * cols;
-  next_level_descs_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(splits, descs, min2, maxin, n_nodes, cols, p,
-                                                                      tmp_descs, tmp_valid);
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  next_level_compact_kernel<<<1, 1024, 0, s>>>(tmp_descs, tmp_valid, n_nodes, cols, child_descs, child_ids, n_children);
-  return cudaGetLastError();
+  return next_level_any(false, splits, descs, min2, maxin, n_nodes, cols, p, tmp_descs, tmp_valid, child_descs, child_ids,
+                        n_children, s);
+}
+
+cudaError_t launch_next_level_enc(const h2ok_split* splits, const h2ok_col_desc* descs, const uint32_t* min2_enc,
+                                  const uint32_t* maxin_enc, int n_nodes, int cols, const h2ok_params& p,
+                                  h2ok_col_desc* tmp_descs, int32_t* tmp_valid, h2ok_col_desc* child_descs,
+                                  int32_t* child_ids, int32_t* n_children, cudaStream_t s) {
+  return next_level_any(true, splits, descs, min2_enc, maxin_enc, n_nodes, cols, p, tmp_descs, tmp_valid, child_descs,
+                        child_ids, n_children, s);
 }
 
 // ---- allocation-free variant of a8 ---------------------------------------------------------------------------

@@ -1,0 +1,685 @@
+// tree_driver.cu — SharedTree.buildLayer inside the library (h2ok_hist_loop_*, h2ok_hist_comm_*, h2ok_hist_group_*).
+//
+// One call per tree level enqueues, without a host round trip in between:
+//   clear -> histogram pass (row_engine.cu) -> [reduce over ranks] -> split points per (node, column) -> [all-gather of
+//   the candidates] -> bestCol -> children's descriptors -> routing + regrouping of the row records
+// and returns once the level's (small) results are on the host; the routing kernels are still running then and the
+// next level's pass queues up behind them.
+//
+// Across ranks (rows are sharded) the exchange is the "preferred form": the int64 accumulators are
+// reduce-scattered over the flat (node, column) list, every rank searches the split points of the pairs it received,
+// the 80-byte candidates are all-gathered and every rank picks the same bestCol from identical bytes.  The histogram
+// crosses the wire once (half an all-reduce) and the split search is spread over the ranks.  Integer sums make the
+// result independent of the number of ranks, bit for bit.  H2OK_REDUCE_ALL keeps the plain all-reduce (every rank then
+// holds the whole reduced histogram).
+//
+// NCCL is looked up at run time (dlopen of libnccl.so.2, the copy already loaded into the process if there is one), so
+// single-GPU callers need no NCCL at all.
+#include <dlfcn.h>
+#include <math.h>
+#include <nccl.h>
+#include <string.h>
+
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "ctx.h"
+
+namespace h2ok {
+
+// ------------------------------------------------------------------------------------------------ NCCL, late bound
+namespace {
+
+struct NcclApi {
+  decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+  decltype(&ncclCommInitRank) CommInitRank = nullptr;
+  decltype(&ncclCommInitAll) CommInitAll = nullptr;
+  decltype(&ncclCommDestroy) CommDestroy = nullptr;
+  decltype(&ncclAllReduce) AllReduce = nullptr;
+  decltype(&ncclReduceScatter) ReduceScatter = nullptr;
+  decltype(&ncclAllGather) AllGather = nullptr;
+  decltype(&ncclGroupStart) GroupStart = nullptr;
+  decltype(&ncclGroupEnd) GroupEnd = nullptr;
+  decltype(&ncclGetErrorString) GetErrorString = nullptr;
+  bool ok = false;
+};
+
+NcclApi* nccl_api() {
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);  // the process's own copy first (e.g. torch's)
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h) return;
+#define H2OK_SYM(name) api.name = reinterpret_cast<decltype(api.name)>(dlsym(h, "nccl" #name))
+    H2OK_SYM(GetUniqueId); H2OK_SYM(CommInitRank); H2OK_SYM(CommInitAll); H2OK_SYM(CommDestroy); H2OK_SYM(AllReduce);
+    H2OK_SYM(ReduceScatter); H2OK_SYM(AllGather); H2OK_SYM(GroupStart); H2OK_SYM(GroupEnd); H2OK_SYM(GetErrorString);
+#undef H2OK_SYM
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommInitAll && api.CommDestroy && api.AllReduce &&
+             api.ReduceScatter && api.AllGather && api.GroupStart && api.GroupEnd && api.GetErrorString;
+  });
+  return api.ok ? &api : nullptr;
+}
+
+#define NK(call)                                                                                              \
+  do {                                                                                                        \
+    ncclResult_t _r = (call);                                                                                 \
+    if (_r != ncclSuccess) return fail(H2OK_ERR_CUDA, "%s: %s", #call, nccl_api()->GetErrorString(_r));       \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------- result checksum
+// Order-independent 64-bit sums: every element is multiplied by a hash of its GLOBAL index and added up mod 2^64, so
+// ranks can hash their own part and the parts add up to the same value whatever the sharding.
+__device__ __forceinline__ unsigned long long warp_add_u64(unsigned long long v) {
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__global__ void hash_i64_kernel(const int64_t* __restrict__ p, int64_t n, uint64_t idx0, uint64_t salt,
+                                unsigned long long* __restrict__ out) {
+  unsigned long long s = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    s += splitmix64((idx0 + (uint64_t)i) ^ salt) * (unsigned long long)p[i];
+  s = warp_add_u64(s);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+__global__ void hash_i32_kernel(const int32_t* __restrict__ p, int64_t n, uint64_t idx0, uint64_t salt,
+                                unsigned long long* __restrict__ out) {
+  unsigned long long s = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    s += splitmix64((idx0 + (uint64_t)i) ^ salt) * (unsigned long long)(long long)p[i];
+  s = warp_add_u64(s);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+// the tree's shape: {col, bin, na_dir, bits of splat} of every node, indexed by the tree-wide node id
+__global__ void hash_splits_kernel(const h2ok_split* __restrict__ sp, int n, int gid_base, uint64_t salt,
+                                   unsigned long long* __restrict__ out) {
+  unsigned long long s = 0;
+  for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < n; g += gridDim.x * blockDim.x) {
+    const h2ok_split t = sp[g];
+    const uint64_t b = (uint64_t)(gid_base + g) * 4;
+    s += splitmix64((b + 0) ^ salt) * (unsigned long long)(long long)t.col;
+    s += splitmix64((b + 1) ^ salt) * (unsigned long long)(long long)t.bin;
+    s += splitmix64((b + 2) ^ salt) * (unsigned long long)(long long)t.na_dir;
+    s += splitmix64((b + 3) ^ salt) * (unsigned long long)__float_as_uint(t.splat);
+  }
+  s = warp_add_u64(s);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+constexpr uint64_t kSaltAcc = 0xACC0ull, kSaltSplit = 0x5911ull, kSaltLeaf = 0x1EAFull;
+
+inline unsigned grid_for(int64_t n, int t, int cap) {
+  int64_t g = (n + t - 1) / t;
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ loop state
+struct TreeLoop {
+  h2ok_params params{};
+  std::vector<int32_t> is_int;
+  std::vector<h2ok_col_desc> root;
+  int cols = 0, max_nodes = 0, max_bins = 0, nb1 = 0;
+  int reduce_mode = H2OK_REDUCE_SCATTER;
+  // level buffers (device)
+  h2ok_col_desc* descs[2] = {nullptr, nullptr};  // [max_nodes][cols], this level / the next
+  int64_t* acc = nullptr;                        // [pairs padded to a multiple of the ranks][nb1][3]
+  uint32_t* rng = nullptr;                       // [2][max_nodes * cols] encoded observed min | max
+  PairCand* cand = nullptr;                      // [padded pairs]
+  h2ok_split* splits = nullptr;                  // [max_nodes]
+  int32_t* child_ids = nullptr;                  // [2 * max_nodes]
+  int32_t* n_children = nullptr;                 // [1]
+  h2ok_col_desc* tmp_descs = nullptr;            // [2 * max_nodes][cols] scratch of next_level
+  int32_t* tmp_valid = nullptr;                  // [2 * max_nodes]
+  double* hist = nullptr;                        // fp64 copy of acc, made only when a caller asks for it
+  float* rngf = nullptr;                         // [2][max_nodes * cols] decoded ranges, likewise
+  unsigned long long* sums = nullptr;            // [3] checksums {acc, splits, leaf}
+  size_t pairs_cap = 0, acc_pairs = 0;
+  int32_t* h_nch = nullptr;                      // pinned
+  cudaStream_t out_stream = nullptr;             // device -> host copies of a level's results
+  cudaEvent_t ev_ready = nullptr, ev_out = nullptr, ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_e = nullptr;
+  // targets of the current tree (device, owned)
+  DevBuf<float> y, w;
+  DevBuf<int32_t> wq, wyq, wyyq;
+  DevBuf<double> absmax;
+  h2ok_quant q{};
+  bool have_tree = false, checksum = false;
+  // tree state
+  int cur = 0, n_nodes = 0, depth = 0, gid_base = 0;
+  // the level just finished (what h2ok_hist_loop_view shows)
+  int done_nodes = 0, done_children = 0, done_depth = -1, done_gid_base = 0, done_cur = 0;
+  bool phases_timed = false;
+  // pending level (between the phases of one h2ok_hist_loop_level)
+  int64_t pairs = 0, chunk = 0, p0 = 0, p1 = 0;
+  bool last = false;
+  const h2ok_level_out* out = nullptr;
+};
+
+void comm_free(h2ok_ctx* c) {
+  if (c->comm) {
+    NcclApi* n = nccl_api();
+    if (n) n->CommDestroy((ncclComm_t)c->comm);
+    c->comm = nullptr;
+  }
+  c->comm_rank = 0;
+  c->comm_ranks = 1;
+}
+
+void loop_free(h2ok_ctx* c) {
+  TreeLoop* L = c->loop;
+  if (!L) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  if (L->out_stream) cudaStreamSynchronize(L->out_stream);
+  for (int k = 0; k < 2; k++) cudaFree(L->descs[k]);
+  cudaFree(L->acc); cudaFree(L->rng); cudaFree(L->cand); cudaFree(L->splits); cudaFree(L->child_ids);
+  cudaFree(L->n_children); cudaFree(L->tmp_descs); cudaFree(L->tmp_valid); cudaFree(L->hist); cudaFree(L->rngf);
+  cudaFree(L->sums);
+  if (L->h_nch) cudaFreeHost(L->h_nch);
+  if (L->out_stream) cudaStreamDestroy(L->out_stream);
+  for (cudaEvent_t e : {L->ev_ready, L->ev_out, L->ev_a, L->ev_b, L->ev_c, L->ev_d, L->ev_e})
+    if (e) cudaEventDestroy(e);
+  L->y.release(); L->w.release(); L->wq.release(); L->wyq.release(); L->wyyq.release(); L->absmax.release();
+  delete L;
+  c->loop = nullptr;
+}
+
+namespace {
+
+int32_t need_loop(h2ok_ctx* c, const char* who) {
+  if (!c) return fail(H2OK_ERR_ARG, "%s: null context", who);
+  if (!c->loop) return fail(H2OK_ERR_STATE, "%s before h2ok_hist_loop_create", who);
+  return H2OK_OK;
+}
+
+// ---- the phases of one level; a group of contexts (one host thread, several devices) runs each phase for every
+//      member before the next, with the NCCL calls of a phase inside one ncclGroupStart / ncclGroupEnd ---------------
+int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
+  TreeLoop& L = *c->loop;
+  if (!L.have_tree) return fail(H2OK_ERR_STATE, "%s", "loop_level before loop_begin_tree");
+  if (L.n_nodes < 1 || L.depth >= L.params.max_depth) return fail(H2OK_ERR_STATE, "%s", "loop_level: the tree is finished");
+  CK(cudaSetDevice(c->device));
+  const int n = L.n_nodes, R = c->comm_ranks;
+  L.out = out;
+  L.pairs = (int64_t)n * L.cols;
+  L.chunk = (L.pairs + R - 1) / R;
+  const bool scatter = R > 1 && L.reduce_mode == H2OK_REDUCE_SCATTER;
+  L.p0 = scatter ? L.chunk * c->comm_rank : 0;
+  L.p1 = scatter ? (L.p0 + L.chunk < L.pairs ? L.p0 + L.chunk : L.pairs) : L.pairs;
+  if (L.p0 > L.pairs) L.p0 = L.pairs;
+  L.last = L.depth + 1 >= L.params.max_depth;
+  const size_t cell = (size_t)L.nb1 * 3;
+  if (L.phases_timed) CK(cudaEventRecord(L.ev_a, c->stream));
+  CK(cudaMemsetAsync(L.acc, 0, sizeof(int64_t) * cell * (size_t)(L.chunk * R), c->stream));
+  CK(launch_init_enc(L.rng, L.rng + L.pairs_cap, L.pairs, c->stream));
+  // H2O halves nbins_top_level per level (Split.nextLevelHistos: max(parent bins >> 1, nbins)): the shared histogram
+  // is sized for the level's widest one
+  int level_bins = L.params.nbins_top_level >> (L.depth < 30 ? L.depth : 30);
+  if (level_bins < L.params.nbins) level_bins = L.params.nbins;
+  const int level_nb1 = level_bins < L.max_bins ? level_bins + 1 : L.nb1;
+  c->stats.passes = 1;
+  c->stats.copies = 1;
+  c->stats.launches = 3;
+  c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * (c->eng.weighted ? 12.0 : 8.0) +
+                        (double)L.pairs * cell * 8.0;
+  CK(cudaEventRecord(c->ev0, c->stream));
+  CK(engine_build_level(c->eng, n, L.descs[L.cur], L.nb1, level_nb1, L.acc, L.rng, L.rng + L.pairs_cap, c->stream));
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->timed = true;
+  if (L.phases_timed) CK(cudaEventRecord(L.ev_b, c->stream));
+  return H2OK_OK;
+}
+
+// MRTask.reduce / DHistogram.add across ranks
+int32_t level_reduce(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  if (c->comm_ranks <= 1) return H2OK_OK;
+  NcclApi* n = nccl_api();
+  ncclComm_t comm = (ncclComm_t)c->comm;
+  const size_t cell = (size_t)L.nb1 * 3;
+  if (L.reduce_mode == H2OK_REDUCE_SCATTER)
+    NK(n->ReduceScatter(L.acc, L.acc + (size_t)L.chunk * c->comm_rank * cell, (size_t)L.chunk * cell, ncclInt64, ncclSum, comm,
+                        c->stream));
+  else
+    NK(n->AllReduce(L.acc, L.acc, (size_t)L.pairs * cell, ncclInt64, ncclSum, comm, c->stream));
+  NK(n->AllReduce(L.rng, L.rng, (size_t)L.pairs, ncclUint32, ncclMin, comm, c->stream));
+  NK(n->AllReduce(L.rng + L.pairs_cap, L.rng + L.pairs_cap, (size_t)L.pairs, ncclUint32, ncclMax, comm, c->stream));
+  return H2OK_OK;
+}
+
+// DTree.findBestSplitPoint on this rank's pairs, straight from the integer accumulators
+int32_t level_search(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  if (L.phases_timed) CK(cudaEventRecord(L.ev_c, c->stream));
+  CK(launch_split_points(nullptr, L.acc, &L.q, L.descs[L.cur], L.p0, L.p1, L.nb1, L.params.min_rows,
+                         L.params.min_split_improvement, L.cand, c->stream));
+  if (L.checksum && L.p1 > L.p0) {
+    const int64_t cell = (int64_t)L.nb1 * 3, cnt = (L.p1 - L.p0) * cell;
+    hash_i64_kernel<<<grid_for(cnt, 256, 1184), 256, 0, c->stream>>>(L.acc + L.p0 * cell, cnt, (uint64_t)(L.p0 * cell),
+                                                                    splitmix64(kSaltAcc + (uint64_t)L.depth), L.sums);
+    CK(cudaGetLastError());
+  }
+  return H2OK_OK;
+}
+
+int32_t level_gather(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  if (c->comm_ranks <= 1 || L.reduce_mode != H2OK_REDUCE_SCATTER) return H2OK_OK;
+  NcclApi* n = nccl_api();
+  const size_t bytes = (size_t)L.chunk * sizeof(PairCand);
+  NK(n->AllGather(reinterpret_cast<char*>(L.cand) + bytes * c->comm_rank, L.cand, bytes, ncclInt8, (ncclComm_t)c->comm,
+                  c->stream));
+  return H2OK_OK;
+}
+
+// bestCol, the children's descriptors, the results' way to the host, then routing + regrouping
+int32_t level_finish(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  const int n = L.n_nodes, nx = 1 - L.cur;
+  const h2ok_level_out* out = L.out;
+  CK(launch_best_col(L.cand, n, L.cols, L.splits, c->stream));
+  if (L.last) {
+    CK(cudaMemsetAsync(L.child_ids, 0xFF, sizeof(int32_t) * 2 * (size_t)n, c->stream));
+    CK(cudaMemsetAsync(L.n_children, 0, sizeof(int32_t), c->stream));
+  } else {
+    CK(launch_next_level_enc(L.splits, L.descs[L.cur], L.rng, L.rng + L.pairs_cap, n, L.cols, L.params, L.tmp_descs,
+                             L.tmp_valid, L.descs[nx], L.child_ids, L.n_children, c->stream));
+  }
+  if (L.checksum) {
+    hash_splits_kernel<<<grid_for(n, 128, 8), 128, 0, c->stream>>>(L.splits, n, L.gid_base, kSaltSplit, L.sums + 1);
+    CK(cudaGetLastError());
+  }
+  if (out && out->hist && !L.hist) CK(cudaMalloc((void**)&L.hist, sizeof(double) * (size_t)L.nb1 * 3 * L.acc_pairs));
+  if (out && (out->min2 || out->maxin) && !L.rngf) CK(cudaMalloc((void**)&L.rngf, sizeof(float) * 2 * L.pairs_cap));
+  if (out && out->hist && L.p1 > L.p0) {
+    const int64_t cell = (int64_t)L.nb1 * 3;
+    CK(launch_finalize(L.acc + L.p0 * cell, nullptr, nullptr, L.p1 - L.p0, L.nb1, L.q, L.hist + L.p0 * cell, nullptr, nullptr,
+                       c->stream));
+  }
+  if (out && (out->min2 || out->maxin))
+    CK(launch_finalize(nullptr, L.rng, L.rng + L.pairs_cap, L.pairs, L.nb1, L.q, nullptr, L.rngf, L.rngf + L.pairs_cap, c->stream));
+  if (L.phases_timed) CK(cudaEventRecord(L.ev_d, c->stream));
+  // results to the host on their own stream, so that routing does not wait for the copies
+  CK(cudaEventRecord(L.ev_ready, c->stream));
+  CK(cudaStreamWaitEvent(L.out_stream, L.ev_ready, 0));
+  CK(cudaMemcpyAsync(L.h_nch, L.n_children, sizeof(int32_t), cudaMemcpyDeviceToHost, L.out_stream));
+  if (out) {
+    const size_t cell = (size_t)L.nb1 * 3;
+    if (out->hist && L.p1 > L.p0)
+      CK(cudaMemcpyAsync(out->hist + L.p0 * cell, L.hist + L.p0 * cell, sizeof(double) * cell * (size_t)(L.p1 - L.p0),
+                         cudaMemcpyDeviceToHost, L.out_stream));
+    if (out->min2) CK(cudaMemcpyAsync(out->min2, L.rngf, sizeof(float) * (size_t)L.pairs, cudaMemcpyDeviceToHost, L.out_stream));
+    if (out->maxin)
+      CK(cudaMemcpyAsync(out->maxin, L.rngf + L.pairs_cap, sizeof(float) * (size_t)L.pairs, cudaMemcpyDeviceToHost, L.out_stream));
+    if (out->splits) CK(cudaMemcpyAsync(out->splits, L.splits, sizeof(h2ok_split) * (size_t)n, cudaMemcpyDeviceToHost, L.out_stream));
+    if (out->child_ids)
+      CK(cudaMemcpyAsync(out->child_ids, L.child_ids, sizeof(int32_t) * 2 * (size_t)n, cudaMemcpyDeviceToHost, L.out_stream));
+  }
+  CK(cudaEventRecord(L.ev_out, L.out_stream));
+  CK(engine_apply_splits(c->eng, L.splits, L.child_ids, L.gid_base, n, !L.last, c->stream));
+  if (L.phases_timed) CK(cudaEventRecord(L.ev_e, c->stream));
+  c->stats.launches += L.last ? 6 : 9;
+  return H2OK_OK;
+}
+
+int32_t level_wait(h2ok_ctx* c, int32_t* n_done, int32_t* n_children) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  CK(cudaEventSynchronize(L.ev_out));
+  const int nch = L.last ? 0 : *L.h_nch;
+  if (nch < 0 || nch > L.max_nodes) {
+    L.have_tree = false;
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "loop_level: the next level has more nodes than max_depth allows for");
+  }
+  if (L.out && L.out->child_descs && nch > 0) {
+    CK(cudaMemcpyAsync(L.out->child_descs, L.descs[1 - L.cur], sizeof(h2ok_col_desc) * (size_t)nch * L.cols,
+                       cudaMemcpyDeviceToHost, L.out_stream));
+    CK(cudaStreamSynchronize(L.out_stream));
+  }
+  L.done_nodes = L.n_nodes;
+  L.done_children = nch;
+  L.done_depth = L.depth;
+  L.done_gid_base = L.gid_base;
+  L.done_cur = L.cur;
+  L.gid_base += L.n_nodes;
+  L.depth += 1;
+  L.cur = 1 - L.cur;
+  L.n_nodes = nch;
+  L.out = nullptr;
+  if (n_done) *n_done = L.done_nodes;
+  if (n_children) *n_children = nch;
+  return H2OK_OK;
+}
+
+int32_t begin_tree_common(h2ok_ctx* c, const float* d_y, const float* d_w) {
+  TreeLoop& L = *c->loop;
+  const int64_t n = c->eng.rows;
+  const size_t pad = (size_t)(n + 3) / 4 * 4;
+  const bool weighted = d_w != nullptr;
+  if (weighted != c->eng.weighted) CK(engine_set_weighted(c->eng, weighted));
+  CK(L.wyq.ensure(pad)); CK(L.wyyq.ensure(pad)); CK(L.absmax.ensure(3));
+  if (weighted) CK(L.wq.ensure(pad));
+  CK(launch_target_absmax(d_y, d_w, n, L.absmax.p, c->stream));
+  if (c->comm_ranks > 1)
+    NK(nccl_api()->AllReduce(L.absmax.p, L.absmax.p, 3, ncclFloat64, ncclMax, (ncclComm_t)c->comm, c->stream));
+  double m[3];
+  CK(cudaMemcpyAsync(m, L.absmax.p, sizeof(m), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  h2ok_hist_choose_quant(m, weighted ? 1 : 0, 25, &L.q);
+  CK(launch_quantize_rows(d_y, d_w, n, L.q, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, c->stream));
+  CK(engine_begin_tree(c->eng, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, &L.q, c->stream));
+  CK(cudaMemcpyAsync(L.descs[0], L.root.data(), sizeof(h2ok_col_desc) * L.cols, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(L.sums, 0, 3 * sizeof(unsigned long long), c->stream));
+  L.cur = 0;
+  L.n_nodes = 1;
+  L.depth = 0;
+  L.gid_base = 0;
+  L.done_depth = -1;
+  L.have_tree = true;
+  return H2OK_OK;
+}
+
+}  // namespace
+}  // namespace h2ok
+
+using namespace h2ok;
+
+extern "C" {
+
+// ------------------------------------------------------------------------------------------------ communicator
+int32_t h2ok_hist_comm_unique_id(void* id_out) {
+  REQUIRE(id_out != nullptr, "null pointer");
+  NcclApi* n = nccl_api();
+  if (!n) return fail(H2OK_ERR_UNSUPPORTED, "%s", "libnccl.so.2 could not be loaded");
+  static_assert(sizeof(ncclUniqueId) == H2OK_COMM_ID_BYTES, "H2OK_COMM_ID_BYTES must be NCCL's unique id size");
+  ncclUniqueId id;
+  NK(n->GetUniqueId(&id));
+  memcpy(id_out, &id, sizeof(id));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_comm_init(h2ok_ctx* c, const void* id_bytes, int32_t rank, int32_t n_ranks) {
+  REQUIRE(c && id_bytes, "null pointer");
+  REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, "rank outside [0, n_ranks)");
+  if (c->loop) return fail(H2OK_ERR_STATE, "%s", "comm_init after loop_create: join the communicator first");
+  comm_free(c);
+  if (n_ranks == 1) return H2OK_OK;
+  NcclApi* n = nccl_api();
+  if (!n) return fail(H2OK_ERR_UNSUPPORTED, "%s", "libnccl.so.2 could not be loaded");
+  CK(cudaSetDevice(c->device));
+  ncclUniqueId id;
+  memcpy(&id, id_bytes, sizeof(id));
+  ncclComm_t comm = nullptr;
+  NK(n->CommInitRank(&comm, n_ranks, id, rank));
+  c->comm = comm;
+  c->comm_rank = rank;
+  c->comm_ranks = n_ranks;
+  return H2OK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ data without a host
+int32_t h2ok_hist_tree_load_synth(h2ok_ctx* c, int32_t shape, uint64_t seed, int64_t row0, int32_t na_permille) {
+  REQUIRE(c != nullptr, "null context");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_load_synth before tree_create");
+  REQUIRE(shape == H2OK_SHAPE_HIGGS28 || shape == H2OK_SHAPE_WIDE64 || shape == H2OK_SHAPE_SPARSE, "unknown shape id");
+  CK(cudaSetDevice(c->device));
+  const int64_t rows = c->eng.rows, ld = (rows + 63) / 64 * 64;
+  const int cols = c->eng.cols;
+  int64_t per = ((int64_t)512 << 20) / (4 * ld);  // columns per staging block (<= 512 MB)
+  per = per < 1 ? 1 : (per > cols ? cols : per);
+  CK(c->X.ensure((size_t)ld * per));
+  for (int c0 = 0; c0 < cols; c0 += (int)per) {
+    const int nc = cols - c0 < per ? cols - c0 : (int)per;
+    CK(launch_synth_cols(shape, seed, row0, rows, c0, nc, ld, na_permille, c->X.p, c->stream));
+    CK(engine_load_cols(c->eng, c0, nc, c->X.p, ld, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  c->X.release();
+  return H2OK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ the loop
+int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int) {
+  REQUIRE(c && params, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "loop_create before tree_create / the data is loaded");
+  REQUIRE(params->max_depth >= 1 && params->nbins >= 1 && params->nbins_top_level >= 1, "bad params");
+  const int max_bins = params->nbins > params->nbins_top_level ? params->nbins : params->nbins_top_level;
+  if (max_bins > H2OK_MAX_BINS) return fail(H2OK_ERR_UNSUPPORTED, "%s", "bins outside [1, H2OK_MAX_BINS]");
+  const int cols = c->eng.cols;
+  for (int j = 0; is_int && j < cols; j++)
+    if (is_int[j] > 1) return fail(H2OK_ERR_UNSUPPORTED, "%s", "categorical columns (is_int == 2) are not supported");
+  CK(cudaSetDevice(c->device));
+  loop_free(c);
+  TreeLoop* L = new TreeLoop();
+  c->loop = L;
+  L->params = *params;
+  L->cols = cols;
+  L->max_bins = max_bins;
+  L->nb1 = max_bins + 1;
+  if (is_int) L->is_int.assign(is_int, is_int + cols);
+  int64_t mn = (int64_t)1 << (params->max_depth - 1 < 10 ? params->max_depth - 1 : 10);
+  L->max_nodes = (int)(mn < H2OK_MAX_LEVEL_NODES ? mn : H2OK_MAX_LEVEL_NODES);
+  const int R = c->comm_ranks;
+  L->pairs_cap = (size_t)L->max_nodes * cols;
+  L->acc_pairs = (L->pairs_cap + R - 1) / R * R;
+  const size_t cell = (size_t)L->nb1 * 3;
+  cudaError_t e = cudaSuccess;
+  auto A = [&](void** p, size_t bytes) {
+    if (e == cudaSuccess) e = cudaMalloc(p, bytes);
+  };
+  for (int k = 0; k < 2; k++) A((void**)&L->descs[k], sizeof(h2ok_col_desc) * L->pairs_cap);
+  A((void**)&L->acc, sizeof(int64_t) * cell * L->acc_pairs);
+  A((void**)&L->rng, sizeof(uint32_t) * 2 * L->pairs_cap);
+  A((void**)&L->cand, sizeof(PairCand) * L->acc_pairs);
+  A((void**)&L->splits, sizeof(h2ok_split) * (size_t)L->max_nodes);
+  A((void**)&L->child_ids, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
+  A((void**)&L->n_children, sizeof(int32_t));
+  A((void**)&L->tmp_descs, sizeof(h2ok_col_desc) * 2 * L->pairs_cap);
+  A((void**)&L->tmp_valid, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
+  A((void**)&L->sums, 3 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_nch, sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->out_stream, cudaStreamNonBlocking);
+  for (cudaEvent_t* ev : {&L->ev_ready, &L->ev_out})
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+  for (cudaEvent_t* ev : {&L->ev_a, &L->ev_b, &L->ev_c, &L->ev_d, &L->ev_e})
+    if (e == cudaSuccess) e = cudaEventCreate(ev);
+  if (e != cudaSuccess) {
+    loop_free(c);
+    return fail(H2OK_ERR_CUDA, "loop_create: %s", cudaGetErrorString(e));
+  }
+  // DHistogram.initialHist: root descriptors from the column ranges of ALL ranks (taken while the data was loaded)
+  if (R > 1) {
+    NcclApi* n = nccl_api();
+    NK(n->AllReduce(c->eng.cmin, c->eng.cmin, (size_t)cols, ncclUint32, ncclMin, (ncclComm_t)c->comm, c->stream));
+    NK(n->AllReduce(c->eng.cmax, c->eng.cmax, (size_t)cols, ncclUint32, ncclMax, (ncclComm_t)c->comm, c->stream));
+  }
+  std::vector<uint32_t> emn(cols), emx(cols);
+  CK(cudaMemcpyAsync(emn.data(), c->eng.cmin, sizeof(uint32_t) * cols, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(emx.data(), c->eng.cmax, sizeof(uint32_t) * cols, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  std::vector<float> lo(cols), hi(cols);
+  for (int j = 0; j < cols; j++) {
+    const uint32_t a = dec_f32_bits(emn[j]), b = dec_f32_bits(emx[j]);
+    memcpy(&lo[j], &a, 4);
+    memcpy(&hi[j], &b, 4);
+  }
+  L->root.resize(cols);
+  return h2ok_hist_root_descs_from_ranges(lo.data(), hi.data(), cols, params, is_int, L->root.data());
+}
+
+int32_t h2ok_hist_loop_destroy(h2ok_ctx* c) {
+  REQUIRE(c != nullptr, "null context");
+  loop_free(c);
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_loop_root_descs(h2ok_ctx* c, h2ok_col_desc* descs_out) {
+  int32_t rc = need_loop(c, "loop_root_descs");
+  if (rc) return rc;
+  REQUIRE(descs_out != nullptr, "null pointer");
+  memcpy(descs_out, c->loop->root.data(), sizeof(h2ok_col_desc) * c->loop->cols);
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_loop_set_reduce(h2ok_ctx* c, int32_t mode) {
+  int32_t rc = need_loop(c, "loop_set_reduce");
+  if (rc) return rc;
+  REQUIRE(mode == H2OK_REDUCE_SCATTER || mode == H2OK_REDUCE_ALL, "unknown reduce mode");
+  c->loop->reduce_mode = mode;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_loop_set_options(h2ok_ctx* c, int32_t checksum, int32_t time_phases) {
+  int32_t rc = need_loop(c, "loop_set_options");
+  if (rc) return rc;
+  c->loop->checksum = checksum != 0;
+  c->loop->phases_timed = time_phases != 0;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_loop_begin_tree_dev(h2ok_ctx* c, const float* d_y, const float* d_w) {
+  int32_t rc = need_loop(c, "loop_begin_tree_dev");
+  if (rc) return rc;
+  REQUIRE(d_y != nullptr, "null pointer");
+  CK(cudaSetDevice(c->device));
+  return begin_tree_common(c, d_y, d_w);
+}
+
+int32_t h2ok_hist_loop_begin_tree_host(h2ok_ctx* c, const float* y_host, const float* w_host) {
+  int32_t rc = need_loop(c, "loop_begin_tree_host");
+  if (rc) return rc;
+  REQUIRE(y_host != nullptr, "null pointer");
+  CK(cudaSetDevice(c->device));
+  TreeLoop& L = *c->loop;
+  const size_t n = (size_t)c->eng.rows, pad = (n + 3) / 4 * 4;
+  CK(L.y.ensure(pad));
+  CK(cudaMemcpyAsync(L.y.p, y_host, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+  if (w_host) {
+    CK(L.w.ensure(pad));
+    CK(cudaMemcpyAsync(L.w.p, w_host, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+  }
+  return begin_tree_common(c, L.y.p, w_host ? L.w.p : nullptr);
+}
+
+int32_t h2ok_hist_loop_begin_tree_synth(h2ok_ctx* c, uint64_t seed, int64_t row0, int32_t weight_mode) {
+  int32_t rc = need_loop(c, "loop_begin_tree_synth");
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device));
+  TreeLoop& L = *c->loop;
+  const size_t n = (size_t)c->eng.rows, pad = (n + 3) / 4 * 4;
+  CK(L.y.ensure(pad));
+  if (weight_mode) CK(L.w.ensure(pad));
+  CK(launch_synth(H2OK_SHAPE_HIGGS28, seed, row0, (int64_t)n, c->eng.cols, (int64_t)pad, 0, weight_mode, nullptr, L.y.p,
+                  weight_mode ? L.w.p : nullptr, c->stream));
+  return begin_tree_common(c, L.y.p, weight_mode ? L.w.p : nullptr);
+}
+
+int32_t h2ok_hist_loop_level(h2ok_ctx* c, const h2ok_level_out* out, int32_t* n_nodes_done, int32_t* n_children) {
+  int32_t rc = need_loop(c, "loop_level");
+  if (rc) return rc;
+  if ((rc = level_local(c, out))) return rc;
+  if ((rc = level_reduce(c))) return rc;
+  if ((rc = level_search(c))) return rc;
+  if ((rc = level_gather(c))) return rc;
+  if ((rc = level_finish(c))) return rc;
+  return level_wait(c, n_nodes_done, n_children);
+}
+
+int32_t h2ok_hist_loop_view(h2ok_ctx* c, h2ok_loop_view* v) {
+  int32_t rc = need_loop(c, "loop_view");
+  if (rc) return rc;
+  REQUIRE(v != nullptr, "null pointer");
+  TreeLoop& L = *c->loop;
+  memset(v, 0, sizeof(*v));
+  v->depth = L.depth;
+  v->n_nodes = L.n_nodes;
+  v->gid_base = L.gid_base;
+  v->max_nodes = L.max_nodes;
+  v->max_bins = L.max_bins;
+  v->cols = L.cols;
+  v->rank = c->comm_rank;
+  v->n_ranks = c->comm_ranks;
+  v->reduce_mode = L.reduce_mode;
+  v->quant = L.q;
+  v->d_descs = L.descs[L.cur];
+  v->d_wq = L.wq.p;
+  v->d_wyq = L.wyq.p;
+  v->d_wyyq = L.wyyq.p;
+  v->d_leaf = c->eng.leaf;
+  if (L.done_depth >= 0) {
+    const int R = c->comm_ranks;
+    const int64_t pairs = (int64_t)L.done_nodes * L.cols, chunk = (pairs + R - 1) / R;
+    const bool scatter = R > 1 && L.reduce_mode == H2OK_REDUCE_SCATTER;
+    v->done_depth = L.done_depth;
+    v->done_nodes = L.done_nodes;
+    v->done_children = L.done_children;
+    v->done_gid_base = L.done_gid_base;
+    v->done_pair0 = scatter ? (chunk * c->comm_rank < pairs ? chunk * c->comm_rank : pairs) : 0;
+    v->done_pair1 = scatter ? (v->done_pair0 + chunk < pairs ? v->done_pair0 + chunk : pairs) : pairs;
+    v->d_done_descs = L.descs[L.done_cur];
+    v->d_done_acc = L.acc;
+    v->d_done_min2_enc = L.rng;
+    v->d_done_maxin_enc = L.rng + L.pairs_cap;
+    v->d_done_splits = L.splits;
+    v->d_done_child_ids = L.child_ids;
+  } else {
+    v->done_depth = -1;
+  }
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_loop_phase_ms(h2ok_ctx* c, float* ms4) {
+  int32_t rc = need_loop(c, "loop_phase_ms");
+  if (rc) return rc;
+  REQUIRE(ms4 != nullptr, "null pointer");
+  TreeLoop& L = *c->loop;
+  if (!L.phases_timed || L.done_depth < 0) return fail(H2OK_ERR_STATE, "%s", "loop_phase_ms: no timed level (loop_set_options)");
+  CK(cudaSetDevice(c->device));
+  CK(cudaEventSynchronize(L.ev_e));
+  CK(cudaEventElapsedTime(&ms4[0], L.ev_a, L.ev_b));  // clear + histogram pass
+  CK(cudaEventElapsedTime(&ms4[1], L.ev_b, L.ev_c));  // reduce over ranks
+  CK(cudaEventElapsedTime(&ms4[2], L.ev_c, L.ev_d));  // split search + gather + children
+  CK(cudaEventElapsedTime(&ms4[3], L.ev_d, L.ev_e));  // routing + regrouping
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_loop_checksum(h2ok_ctx* c, int64_t row0, uint64_t* out3) {
+  int32_t rc = need_loop(c, "loop_checksum");
+  if (rc) return rc;
+  REQUIRE(out3 != nullptr && row0 >= 0, "bad arguments");
+  TreeLoop& L = *c->loop;
+  if (!L.checksum) return fail(H2OK_ERR_STATE, "%s", "loop_checksum: switch the checksum on with loop_set_options first");
+  CK(cudaSetDevice(c->device));
+  // {acc, splits} were accumulated level by level; every rank hashed the same splits, so only rank 0's count
+  CK(cudaMemsetAsync(L.sums + 2, 0, sizeof(unsigned long long), c->stream));
+  hash_i32_kernel<<<grid_for(c->eng.rows, 256, 1184), 256, 0, c->stream>>>(c->eng.leaf, c->eng.rows, (uint64_t)row0, kSaltLeaf,
+                                                                          L.sums + 2);
+  CK(cudaGetLastError());
+  unsigned long long h[3];
+  if (c->comm_ranks > 1) {
+    // the accumulator sum of a rank covers its own pairs in either reduce mode only under H2OK_REDUCE_SCATTER; under
+    // H2OK_REDUCE_ALL every rank hashed everything, like the splits
+    CK(c->absmax.ensure(3));
+    unsigned long long* tmp = reinterpret_cast<unsigned long long*>(c->absmax.p);
+    CK(cudaMemcpyAsync(tmp, L.sums, sizeof(h), cudaMemcpyDeviceToDevice, c->stream));
+    const bool own_part = L.reduce_mode == H2OK_REDUCE_SCATTER;
+    if (c->comm_rank != 0) {
+      CK(cudaMemsetAsync(tmp + 1, 0, sizeof(unsigned long long), c->stream));
+      if (!own_part) CK(cudaMemsetAsync(tmp, 0, sizeof(unsigned long long), c->stream));
+    }
+    NK(nccl_api()->AllReduce(tmp, tmp, 3, ncclUint64, ncclSum, (ncclComm_t)c->comm, c->stream));
+    CK(cudaMemcpyAsync(h, tmp, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  } else {
+    CK(cudaMemcpyAsync(h, L.sums, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < 3; k++) out3[k] = h[k];
+  return H2OK_OK;
+}
+
+}  // extern "C"

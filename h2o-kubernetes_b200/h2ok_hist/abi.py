@@ -12,6 +12,8 @@ MAX_BINS = 1024
 NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT = 0, 1, 2, 3
 SHAPE_HIGGS28, SHAPE_WIDE64, SHAPE_SPARSE = 2, 3, 4
 DIST_GAUSSIAN, DIST_BERNOULLI, DIST_MULTINOMIAL = 0, 1, 2
+REDUCE_SCATTER, REDUCE_ALL = 0, 1
+COMM_ID_BYTES = 128
 
 COL_DESC = np.dtype(
     [("min", "<f8"), ("maxex", "<f8"), ("step", "<f8"), ("nbin", "<i4"), ("is_int", "<i4")], align=True
@@ -45,6 +47,26 @@ class Params(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("build_ms", C.c_float), ("launches", C.c_int32), ("passes", C.c_int32), ("copies", C.c_int32),
                 ("range_errors", C.c_int32), ("pad", C.c_int32), ("algo_bytes", C.c_double)]
+
+
+class LevelOut(C.Structure):
+    """h2ok_level_out: host buffers h2ok_hist_loop_level fills (NULL = not wanted)."""
+    _fields_ = [("hist", C.c_void_p), ("min2", C.c_void_p), ("maxin", C.c_void_p), ("splits", C.c_void_p),
+                ("child_descs", C.c_void_p), ("child_ids", C.c_void_p)]
+
+
+class LoopView(C.Structure):
+    """h2ok_loop_view: where the loop stands + device pointers to the level that ran last."""
+    _fields_ = [("depth", C.c_int32), ("n_nodes", C.c_int32), ("gid_base", C.c_int32),
+                ("max_nodes", C.c_int32), ("max_bins", C.c_int32), ("cols", C.c_int32), ("rank", C.c_int32),
+                ("n_ranks", C.c_int32), ("reduce_mode", C.c_int32),
+                ("done_depth", C.c_int32), ("done_nodes", C.c_int32), ("done_children", C.c_int32),
+                ("done_gid_base", C.c_int32), ("pad", C.c_int32),
+                ("done_pair0", C.c_int64), ("done_pair1", C.c_int64), ("quant", Quant),
+                ("d_descs", C.c_void_p), ("d_wq", C.c_void_p), ("d_wyq", C.c_void_p), ("d_wyyq", C.c_void_p),
+                ("d_leaf", C.c_void_p), ("d_done_descs", C.c_void_p), ("d_done_acc", C.c_void_p),
+                ("d_done_min2_enc", C.c_void_p), ("d_done_maxin_enc", C.c_void_p), ("d_done_splits", C.c_void_p),
+                ("d_done_child_ids", C.c_void_p)]
 
 
 def ptr(a):

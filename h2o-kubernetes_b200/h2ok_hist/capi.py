@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libh2ok_hist.so")
 
 i32, i64, u64, f64, vp = C.c_int32, C.c_int64, C.c_uint64, C.c_double, C.c_void_p
 pQ, pP, pS = C.POINTER(abi.Quant), C.POINTER(abi.Params), C.POINTER(abi.Stats)
+pLO, pLV = C.POINTER(abi.LevelOut), C.POINTER(abi.LoopView)
 
 # name -> argtypes; every function returns int32 status except h2ok_last_error
 SIGNATURES = {
@@ -20,6 +21,7 @@ SIGNATURES = {
     "h2ok_hist_abi_version": [],
     "h2ok_hist_set_stream": [vp, vp, i32],
     "h2ok_hist_sync": [vp],
+    "h2ok_hist_copy_to_host": [vp, vp, vp, C.c_size_t],
     "h2ok_hist_synth_fill_dev": [vp, i32, u64, i64, i64, i32, i64, i32, i32, vp, vp, vp],
     "h2ok_hist_synth_fill_cols_dev": [vp, i32, u64, i64, i64, i32, i32, i64, i32, vp],
     "h2ok_hist_col_ranges_dev": [vp, vp, i64, i64, i32, vp, vp],
@@ -41,6 +43,21 @@ SIGNATURES = {
     "h2ok_hist_tree_apply_splits_dev": [vp, vp, vp, i32, i32, i32],
     "h2ok_hist_tree_nid_dev": [vp, vp],
     "h2ok_hist_tree_leaf_dev": [vp, vp],
+    "h2ok_hist_tree_load_synth": [vp, i32, u64, i64, i32],
+    "h2ok_hist_comm_unique_id": [vp],
+    "h2ok_hist_comm_init": [vp, vp, i32, i32],
+    "h2ok_hist_loop_create": [vp, pP, vp],
+    "h2ok_hist_loop_destroy": [vp],
+    "h2ok_hist_loop_root_descs": [vp, vp],
+    "h2ok_hist_loop_set_reduce": [vp, i32],
+    "h2ok_hist_loop_set_options": [vp, i32, i32],
+    "h2ok_hist_loop_begin_tree_dev": [vp, vp, vp],
+    "h2ok_hist_loop_begin_tree_host": [vp, vp, vp],
+    "h2ok_hist_loop_begin_tree_synth": [vp, u64, i64, i32],
+    "h2ok_hist_loop_level": [vp, pLO, C.POINTER(i32), C.POINTER(i32)],
+    "h2ok_hist_loop_view": [vp, pLV],
+    "h2ok_hist_loop_phase_ms": [vp, vp],
+    "h2ok_hist_loop_checksum": [vp, i64, vp],
     "h2ok_hist_gbm_residual_dev": [vp, i32, vp, vp, vp, i64, f64, vp, vp],
     "h2ok_hist_gbm_residual_multi_dev": [vp, i32, vp, vp, i64, vp, i64, f64, vp, vp],
     "h2ok_hist_gbm_gamma_pass_dev": [vp, vp, vp, vp, i64, i32, vp, vp],

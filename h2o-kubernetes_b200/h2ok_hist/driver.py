@@ -290,7 +290,127 @@ class EngineShard(CudaShard):
     def apply_splits(self, n_nodes, gid_base, last=False):
         self.lib.call("h2ok_hist_tree_apply_splits_dev", self.ctx, _ptr(self.splits), _ptr(self.child_ids), gid_base,
                       n_nodes, 1 if last else 0)
-        self.launches += 5  # tiles, order, route, scan, scatter
+        self.launches += 2 if last else 3  # route, scan (+ scatter unless the tree ends here)
+
+
+class TreeLoop:
+    """The level loop that runs INSIDE libh2ok_hist.so (h2ok_hist_loop_*): one C call per tree level, the cross-rank
+    reduce done by the library over NCCL.  Python only hands over pointers; torch.distributed is used for one thing,
+    carrying the 128-byte rendezvous id from rank 0 to the other ranks when the process group exists.
+
+    shard: an EngineShard whose data is loaded.  Same results as LevelDriver, bit for bit."""
+
+    def __init__(self, shard, params, is_int=None, reduce_mode=abi.REDUCE_SCATTER, checksum=False, time_phases=False):
+        self.shard, self.params, self.lib = shard, params, shard.lib
+        self.is_int = None if is_int is None else np.ascontiguousarray(is_int, np.int32)
+        self.max_bins = max(params.nbins, params.nbins_top_level)
+        self.lib.call("h2ok_hist_loop_create", shard.ctx, C.byref(params), abi.ptr(self.is_int))
+        self.lib.call("h2ok_hist_loop_set_reduce", shard.ctx, reduce_mode)
+        self.lib.call("h2ok_hist_loop_set_options", shard.ctx, 1 if checksum else 0, 1 if time_phases else 0)
+        self.n_nodes = 0
+        self.depth = 0
+
+    @staticmethod
+    def join_ranks(shard):
+        """Every rank's context joins one NCCL communicator (call before the data is loaded / TreeLoop is made)."""
+        world = _world()
+        if world == 1:
+            return
+        ident = torch.zeros(abi.COMM_ID_BYTES, dtype=torch.uint8)
+        if dist.get_rank() == 0:
+            shard.lib.call("h2ok_hist_comm_unique_id", C.c_void_p(ident.data_ptr()))
+        if dist.get_backend() == "nccl":
+            dev = ident.to(shard.device)
+            dist.broadcast(dev, 0)
+            ident = dev.cpu()
+        else:
+            dist.broadcast(ident, 0)
+        shard.lib.call("h2ok_hist_comm_init", shard.ctx, C.c_void_p(ident.data_ptr()), dist.get_rank(), world)
+
+    def root_descs(self):
+        out = np.zeros(self.shard.cols, abi.COL_DESC)
+        self.lib.call("h2ok_hist_loop_root_descs", self.shard.ctx, abi.ptr(out))
+        return out
+
+    def begin_tree(self, y=None, w=None):
+        """y / w: device tensors in original row order (default: the shard's own targets)."""
+        y = self.shard.y if y is None else y
+        w = (self.shard.w if self.shard.weighted else None) if y is self.shard.y and w is None else w
+        self.lib.call("h2ok_hist_loop_begin_tree_dev", self.shard.ctx, _ptr(y), _ptr(w))
+        self.shard.launches += 5  # absmax, quantise, root mean, begin, + the library's own memsets do not count
+        self.n_nodes, self.depth = 1, 0
+
+    def begin_tree_host(self, y_host, w_host=None):
+        """y_host / w_host: host tensors or numpy arrays (fp32); the library copies them in."""
+        p = lambda a: None if a is None else C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        self.lib.call("h2ok_hist_loop_begin_tree_host", self.shard.ctx, p(y_host), p(w_host))
+        self.shard.launches += 5
+        self.n_nodes, self.depth = 1, 0
+
+    def level(self, out=None):
+        done, nch = C.c_int32(), C.c_int32()
+        self.lib.call("h2ok_hist_loop_level", self.shard.ctx, None if out is None else C.byref(out), C.byref(done),
+                      C.byref(nch))
+        last = self.depth + 1 >= self.params.max_depth
+        # init_enc, histogram pass, split points, bestCol, [children: descs + compact], route, scan, [scatter]
+        self.shard.launches += 6 if last else 9
+        self.depth += 1
+        self.n_nodes = nch.value
+        return done.value, nch.value
+
+    def n_nodes_left(self):
+        return self.n_nodes if self.depth < self.params.max_depth else 0
+
+    def train_tree(self, y=None, w=None, after_level=None):
+        self.begin_tree(y, w)
+        levels = 0
+        while self.n_nodes_left() > 0:
+            self.level()
+            levels += 1
+            if after_level:
+                after_level(self)
+        return levels
+
+    def view(self):
+        v = abi.LoopView()
+        self.lib.call("h2ok_hist_loop_view", self.shard.ctx, C.byref(v))
+        return v
+
+    def phase_ms(self):
+        out = (C.c_float * 4)()
+        self.lib.call("h2ok_hist_loop_phase_ms", self.shard.ctx, out)
+        return [float(x) for x in out]
+
+    def checksum(self, row0=0):
+        out = (C.c_uint64 * 3)()
+        self.lib.call("h2ok_hist_loop_checksum", self.shard.ctx, int(row0), out)
+        return [int(x) for x in out]
+
+    # ---- host copies of the level that ran last (tests) ------------------------------------------------------
+    def _dev_array(self, ptr, nbytes):
+        out = np.empty(nbytes, np.uint8)
+        torch.cuda.current_stream(self.shard.device).synchronize()
+        self.lib.call("h2ok_hist_copy_to_host", self.shard.ctx, C.c_void_p(ptr), abi.ptr(out), nbytes)
+        return out
+
+    def done_level(self):
+        """dict of numpy copies: descs, acc, min2, maxin (decoded), splits, child_ids, n, nch, pair0, pair1."""
+        v = self.view()
+        n, cols, nb1 = v.done_nodes, v.cols, v.max_bins + 1
+        out = dict(n=n, nch=v.done_children, pair0=v.done_pair0, pair1=v.done_pair1, depth=v.done_depth,
+                   gid_base=v.done_gid_base, quant=v.quant)
+        out["descs"] = self._dev_array(v.d_done_descs, n * cols * abi.COL_DESC.itemsize).view(abi.COL_DESC).reshape(n, cols)
+        out["acc"] = self._dev_array(v.d_done_acc, n * cols * nb1 * 3 * 8).view(np.int64).reshape(n, cols, nb1, 3)
+        mn = self._dev_array(v.d_done_min2_enc, n * cols * 4).view(np.uint32).reshape(n, cols)
+        mx = self._dev_array(v.d_done_maxin_enc, n * cols * 4).view(np.uint32).reshape(n, cols)
+        out["min2"] = abi.decode_f32(mn) + np.float32(0)
+        out["maxin"] = abi.decode_f32(mx) + np.float32(0)
+        out["splits"] = self._dev_array(v.d_done_splits, n * abi.SPLIT.itemsize).view(abi.SPLIT).reshape(n)
+        out["child_ids"] = self._dev_array(v.d_done_child_ids, 2 * n * 4).view(np.int32)
+        if v.done_children:
+            out["child_descs"] = self._dev_array(v.d_descs, v.done_children * cols * abi.COL_DESC.itemsize).view(
+                abi.COL_DESC).reshape(v.done_children, cols)
+        return out
 
 
 def _world():

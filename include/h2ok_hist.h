@@ -60,6 +60,11 @@ extern "C" {
 #define H2OK_DIST_BERNOULLI 1
 #define H2OK_DIST_MULTINOMIAL 2
 
+/* How h2ok_hist_loop_level combines the ranks' histograms (a5, MRTask.reduce). */
+#define H2OK_REDUCE_SCATTER 0 /* reduce-scatter over (node, column) pairs + sharded split search + all-gather of candidates */
+#define H2OK_REDUCE_ALL 1     /* plain all-reduce: every rank holds the whole reduced histogram */
+#define H2OK_COMM_ID_BYTES 128 /* size of the rendezvous id of h2ok_hist_comm_unique_id (an ncclUniqueId) */
+
 /* Synthetic shapes of SURVEY.md §8(d). */
 #define H2OK_SHAPE_HIGGS28 2 /* config 2: 28 HIGGS-shaped columns */
 #define H2OK_SHAPE_WIDE64 3  /* config 3: the 28-column recipe tiled to any width with affine offsets */
@@ -115,6 +120,39 @@ typedef struct h2ok_stats {
   double algo_bytes;
 } h2ok_stats;
 
+/* Host buffers that h2ok_hist_loop_level fills for the level it ran; any pointer may be NULL (not wanted), and the
+ * whole struct may be NULL.  Shapes as in the per-step entry points.  With several ranks under H2OK_REDUCE_SCATTER a
+ * rank's `hist` receives only the (node, column) pairs it reduced — pairs [done_pair0, done_pair1) of h2ok_loop_view,
+ * the rest of the buffer is left untouched — so that the reduced histogram reaches host memory once, in parallel over
+ * the ranks' links; everything else is complete on every rank. */
+typedef struct h2ok_level_out {
+  double* hist;               /* [n_nodes][cols][max_bins+1][3] */
+  float* min2;                /* [n_nodes][cols] */
+  float* maxin;               /* [n_nodes][cols] */
+  h2ok_split* splits;         /* [n_nodes] */
+  h2ok_col_desc* child_descs; /* [n_children][cols] */
+  int32_t* child_ids;         /* [2*n_nodes] */
+} h2ok_level_out;
+
+/* Where the loop stands, and device pointers to the level that h2ok_hist_loop_level finished last (valid until the
+ * next loop_level / loop_begin_tree call; tests and callers that keep everything on the device read them). */
+typedef struct h2ok_loop_view {
+  int32_t depth, n_nodes, gid_base; /* the level the NEXT loop_level call will run; n_nodes == 0: tree finished */
+  int32_t max_nodes, max_bins, cols, rank, n_ranks, reduce_mode;
+  int32_t done_depth;               /* -1: no level has run since loop_begin_tree */
+  int32_t done_nodes, done_children, done_gid_base, pad;
+  int64_t done_pair0, done_pair1;   /* (node, column) pairs whose reduced sums this rank holds in d_done_acc */
+  h2ok_quant quant;                 /* fixed-point scales of the current tree's targets */
+  const h2ok_col_desc* d_descs;     /* [n_nodes][cols] descriptors of the next level */
+  const int32_t *d_wq, *d_wyq, *d_wyyq; /* the tree's quantised targets, original row order (d_wq NULL-able) */
+  const int32_t* d_leaf;            /* [rows] leaf codes, -1 while a row is still in the tree */
+  const h2ok_col_desc* d_done_descs;
+  const int64_t* d_done_acc;        /* [done_nodes][cols][max_bins+1][3] int64 fixed-point sums */
+  const uint32_t *d_done_min2_enc, *d_done_maxin_enc;
+  const h2ok_split* d_done_splits;
+  const int32_t* d_done_child_ids;
+} h2ok_loop_view;
+
 /* ---- lifecycle ------------------------------------------------------------------------------ */
 int32_t h2ok_hist_create(int32_t device, h2ok_ctx** out);
 int32_t h2ok_hist_destroy(h2ok_ctx* ctx);
@@ -124,6 +162,9 @@ int32_t h2ok_hist_abi_version(void);
  * use_own != 0: go back to the context's own non-blocking stream (the state after create). */
 int32_t h2ok_hist_set_stream(h2ok_ctx* ctx, void* stream, int32_t use_own);
 int32_t h2ok_hist_sync(h2ok_ctx* ctx);
+/* Blocking device -> host copy ordered after everything enqueued on the context's stream (how a caller without its own
+ * CUDA runtime reads the device pointers of h2ok_loop_view). */
+int32_t h2ok_hist_copy_to_host(h2ok_ctx* ctx, const void* d_src, void* host_dst, size_t bytes);
 
 /* ---- device-resident entry points (pointers are device pointers; asynchronous) -------------- */
 
@@ -183,6 +224,7 @@ int32_t h2ok_hist_next_level_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, cons
                                  const float* d_min2, const float* d_maxin, int32_t n_nodes, int32_t cols,
                                  const h2ok_params* params, int32_t depth, h2ok_col_desc* d_child_descs,
                                  int32_t* d_child_ids, int32_t* d_n_children);
+/* (depth is reserved: the children's bin count follows from the parent's descriptor, max(parent nbin >> 1, nbins).) */
 
 /* a8 without any allocation — same inputs, outputs and results as h2ok_hist_next_level_dev.  No counterpart in the
  * reference (nor in H2O-3): it exists for hosts that cannot allocate device memory while they run — a process whose
@@ -218,7 +260,7 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
  * Call order: tree_create -> tree_load_cols_dev for every block of columns (in any order; the caller's column-major
  * block can be freed or reused afterwards) -> per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce /
  * finalize / find_splits / next_level as usual], tree_apply_splits_dev.  Device memory: rows * (4 * cols rounded up
- * to 8 + 29) bytes, + 8 per row for weighted shards.  Limits: rows < 2^31 - 2048; every bin count up to
+ * to 8 + cols + 30) bytes, + 8 per row for weighted shards.  Limits: rows < 2^31 - 4096, cols < 32768; every bin count up to
  * H2OK_MAX_BINS runs (64 columns per block up to 299 bins + NA, 32 up to 599, 16 beyond). */
 int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
@@ -226,6 +268,8 @@ int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
  * original order */
 int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* ctx, int32_t col0, int32_t ncols, const float* d_X, int64_t ld);
 /* new tree: per-row fixed-point targets in ORIGINAL row order (d_wq NULL when unweighted); all rows back at the root.
+ * The target arrays are read again by every tree_apply_splits_dev of the tree: keep them valid and unchanged until
+ * the tree is finished.
  * q = the h2ok_quant the targets were quantised with (host pointer; may be NULL): the engine stores every node's
  * targets relative to an offset near the node's mean, which it derives from the parent's split record and these
  * scales, so that its 32-bit histogram words rarely wrap.  Results do not depend on it. */
@@ -242,13 +286,61 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* ctx, int32_t n_nodes, const h2o
  * h2ok_stats.range_errors. */
 int32_t h2ok_hist_tree_level_bins(h2ok_ctx* ctx, int32_t level_bins);
 /* a6 for the current level + regrouping of the records by child.  Child ids must be numbered in slot order
- * (2 * node + way), which is what next_level_dev produces; last_level is accepted for symmetry and not needed
- * (with every child id -1 all rows retire). */
+ * (2 * node + way), which is what next_level_dev produces.  last_level != 0: the tree ends here — rows get their leaf
+ * codes and no records are laid out for a next level (pass 0 whenever another tree_build_level_dev follows). */
 int32_t h2ok_hist_tree_apply_splits_dev(h2ok_ctx* ctx, const h2ok_split* d_splits, const int32_t* d_child_ids,
                                         int32_t gid_base, int32_t n_nodes, int32_t last_level);
 /* row -> node of the current level / leaf codes, in original row order */
 int32_t h2ok_hist_tree_nid_dev(h2ok_ctx* ctx, int32_t* d_nid_out);
 int32_t h2ok_hist_tree_leaf_dev(h2ok_ctx* ctx, int32_t* d_leaf_out);
+
+/* The same generator straight into the engine: fills every column of the shard created by tree_create with rows
+ * [row0, row0 + rows) of the global synthetic matrix (no caller-side staging; synchronous). */
+int32_t h2ok_hist_tree_load_synth(h2ok_ctx* ctx, int32_t shape, uint64_t seed, int64_t row0, int32_t na_permille);
+
+/* ---- the level loop inside the library (SharedTree.buildLayer, hex/tree/SharedTree.java) ------------------------
+ * One call per tree level: ScoreBuildHistogram2's local phase on the resident engine, MRTask.reduce over the ranks
+ * (NCCL, called from inside the library), DTree.findBestSplitPoint + bestCol, Split.nextLevelHistos, score_decide and
+ * the regrouping of the row records — enqueued back to back without a host round trip; the call returns when the
+ * level's small results (and the host buffers asked for) have arrived, while routing is still running.
+ * Call order: create -> [comm_init] -> tree_create + data (tree_load_cols_dev / tree_load_synth) -> loop_create ->
+ * per tree: loop_begin_tree_* -> loop_level until *n_children == 0 or max_depth levels have run.
+ * Results are bit-identical to the per-step entry points and to any number of ranks (integer sums).
+ *
+ * Ranks.  One context per process and GPU: rank 0 calls h2ok_hist_comm_unique_id, hands the H2OK_COMM_ID_BYTES bytes
+ * to the other processes by any means, and every rank calls h2ok_hist_comm_init (collective, blocking) BEFORE
+ * loop_create.  Rows are sharded (each rank loads its own rows); descriptors, splits and child ids are replicated.
+ * The reference's counterpart is the H2O cloud the StatefulSet forms (src/k8s/templates.rs:18-32, port 54321): pods
+ * there, GPUs of one node here.  A single-threaded caller that owns several GPUs uses h2ok_hist_group_* below. */
+int32_t h2ok_hist_comm_unique_id(void* id_out /*[H2OK_COMM_ID_BYTES]*/);
+int32_t h2ok_hist_comm_init(h2ok_ctx* ctx, const void* id /*[H2OK_COMM_ID_BYTES]*/, int32_t rank, int32_t n_ranks);
+/* Root descriptors from the column ranges of all ranks (DHistogram.initialHist), level buffers for
+ * min(2^(max_depth-1), H2OK_MAX_LEVEL_NODES) nodes.  Collective when n_ranks > 1.  is_int: [cols] or NULL. */
+int32_t h2ok_hist_loop_create(h2ok_ctx* ctx, const h2ok_params* params, const int32_t* is_int);
+int32_t h2ok_hist_loop_destroy(h2ok_ctx* ctx);
+int32_t h2ok_hist_loop_root_descs(h2ok_ctx* ctx, h2ok_col_desc* descs_out /*[cols], host*/);
+int32_t h2ok_hist_loop_set_reduce(h2ok_ctx* ctx, int32_t mode /*H2OK_REDUCE_**/);
+/* checksum != 0: keep the running result checksums of h2ok_hist_loop_checksum (one extra read of every level's
+ * accumulators); time_phases != 0: bracket the phases of every level with CUDA events (h2ok_hist_loop_phase_ms). */
+int32_t h2ok_hist_loop_set_options(h2ok_ctx* ctx, int32_t checksum, int32_t time_phases);
+/* New tree on targets y (and weights w, NULL: unweighted) in original row order: common fixed-point scales over all
+ * ranks (one blocking read of three doubles), quantised targets, every row back at the root.  _dev: device pointers,
+ * read during this call only; _host: the library copies them in; _synth: the generator's y / w for rows from row0. */
+int32_t h2ok_hist_loop_begin_tree_dev(h2ok_ctx* ctx, const float* d_y, const float* d_w);
+int32_t h2ok_hist_loop_begin_tree_host(h2ok_ctx* ctx, const float* y_host, const float* w_host);
+int32_t h2ok_hist_loop_begin_tree_synth(h2ok_ctx* ctx, uint64_t seed, int64_t row0, int32_t weight_mode);
+/* One level.  out may be NULL.  *n_nodes_done: nodes of the level that ran; *n_children: nodes of the next level
+ * (0: the tree is finished; every row then has its leaf code). */
+int32_t h2ok_hist_loop_level(h2ok_ctx* ctx, const h2ok_level_out* out, int32_t* n_nodes_done, int32_t* n_children);
+int32_t h2ok_hist_loop_view(h2ok_ctx* ctx, h2ok_loop_view* view_out);
+/* Device milliseconds of the last level's phases: {clear + histogram pass, reduce over ranks, split search + candidate
+ * gather + children, routing + regrouping}. */
+int32_t h2ok_hist_loop_phase_ms(h2ok_ctx* ctx, float* ms_out /*[4]*/);
+/* 64-bit checksums of the current tree so far, the same for any number of ranks: out[0] every level's reduced integer
+ * accumulators, out[1] the splits {col, bin, na_dir, splat} of every node, out[2] the leaf code of every row.  Each is
+ * sum(splitmix64(global index ^ salt) * value) mod 2^64 (tests/oracle_lib.py has the host restatement).  row0 = global
+ * index of this rank's first row.  Collective when n_ranks > 1. */
+int32_t h2ok_hist_loop_checksum(h2ok_ctx* ctx, int64_t row0, uint64_t* out /*[3]*/);
 
 /* ---- a9: the tree-level caller (GBM.buildNextKTrees) ---------------------------------------------------------
  * ComputePredAndRes: d_res[r] = label - mu(f) (gaussian mu = f, bernoulli mu = 1/(1+exp(-f))), and, when d_denq is

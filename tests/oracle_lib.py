@@ -223,6 +223,77 @@ class Oracle:
         return levels, nid, leaf
 
 
+def train_tree_q(oracle, X, rows, y, w, params, is_int=None, qbits=25, on_level=None):
+    """The level loop over the FIXED-POINT targets (every channel an exact integer): what the CUDA path must equal
+    bit for bit.  Returns (levels, nid, leaf, quant); a level holds descs, acc, hist, min2, maxin, splits, child_ids,
+    child_descs, nid (before routing), gid_base."""
+    cols = X.shape[0]
+    descs = oracle.root_descs(X, rows, params, is_int).reshape(1, cols)
+    q, _ = oracle.choose_quant(y[:rows], None if w is None else w[:rows], qbits)
+    wq, wyq, wyyq = oracle.quantize_rows(y[:rows], None if w is None else w[:rows], q)
+    nid = np.zeros(rows, np.int32)
+    leaf = np.full(rows, -1, np.int32)
+    gid_base, levels = 0, []
+    max_bins = max(params.nbins, params.nbins_top_level)
+    for depth in range(params.max_depth):
+        n = descs.shape[0]
+        acc, min2, maxin = oracle.build_level_q(X, rows, nid, wq, wyq, wyyq, descs, max_bins)
+        hist = oracle.finalize(acc, q, max_bins)
+        splits = oracle.find_splits(hist, descs, params.min_rows, params.min_split_improvement)
+        if depth + 1 < params.max_depth:
+            child, ids, nch = oracle.next_level(splits, descs, min2, maxin, params, depth)
+        else:
+            child, ids, nch = np.zeros((0, cols), abi.COL_DESC), np.full(2 * n, -1, np.int32), 0
+        levels.append(dict(descs=descs, acc=acc, hist=hist, min2=min2, maxin=maxin, splits=splits, child_ids=ids,
+                           child_descs=child, nid=nid.copy(), gid_base=gid_base, depth=depth))
+        if on_level:
+            on_level(depth, levels[-1])
+        oracle.apply_splits(X, rows, splits, ids, gid_base, nid, leaf)
+        gid_base += n
+        descs = child
+        if nch == 0:
+            break
+    return levels, nid, leaf, q
+
+
+# ---- host restatement of h2ok_hist_loop_checksum (csrc/tree_driver.cu) --------------------------------------------
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+SALT_ACC, SALT_SPLIT, SALT_LEAF = 0xACC0, 0x5911, 0x1EAF
+
+
+def splitmix64_np(z):
+    z = np.asarray(z, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        z = z + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return z ^ (z >> np.uint64(31))
+
+
+def _hash_sum(values_i64, idx0, salt):
+    v = np.ascontiguousarray(values_i64, dtype=np.int64).reshape(-1).view(np.uint64)
+    total = np.uint64(0)
+    step = 1 << 22
+    with np.errstate(over="ignore"):
+        for a in range(0, v.size, step):
+            i = np.arange(a, min(a + step, v.size), dtype=np.uint64) + np.uint64(idx0)
+            total = total + np.sum(splitmix64_np(i ^ np.uint64(salt)) * v[a:a + step], dtype=np.uint64)
+    return int(total)
+
+
+def tree_checksum(levels, leaf, row0=0):
+    """[acc, splits, leaf] sums of a tree given its levels (each with acc, splits, gid_base, depth) and leaf codes."""
+    acc_sum = split_sum = 0
+    for lv in levels:
+        salt = int(splitmix64_np(np.uint64(SALT_ACC + lv["depth"])))
+        acc_sum = (acc_sum + _hash_sum(lv["acc"], 0, salt)) & 0xFFFFFFFFFFFFFFFF
+        sp = lv["splits"]
+        f = np.stack([sp["col"].astype(np.int64), sp["bin"].astype(np.int64), sp["na_dir"].astype(np.int64),
+                      sp["splat"].view(np.uint32).astype(np.int64)], axis=1)
+        split_sum = (split_sum + _hash_sum(f, 4 * lv["gid_base"], SALT_SPLIT)) & 0xFFFFFFFFFFFFFFFF
+    return [acc_sum, split_sum, _hash_sum(np.asarray(leaf, np.int32).astype(np.int64), row0, SALT_LEAF)]
+
+
 def gbm_gamma(num, den, scale_num, scale_den):
     """Leaf values from the integer GammaPass sums (same expression as h2ok_hist.gbm.leaf_gamma)."""
     num = num.astype(np.float64) / scale_num

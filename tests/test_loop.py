@@ -1,0 +1,176 @@
+"""GPU parity tests of the level loop that runs inside the library (h2ok_hist_loop_*): every level's descriptors,
+integer accumulators, observed ranges, splits, child ids / descriptors, the row -> node map and the leaf of every row
+must equal the oracle's fixed-point level loop bit for bit — on small ragged cases and at the shapes BASELINE.json
+names (config 2 at full size, a 10M-row slice of config 3, config 4's sparse 2000-column shape)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+import oracle_lib  # noqa: E402
+from h2ok_hist import abi  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eshard():
+    from h2ok_hist.driver import EngineShard
+
+    s = EngineShard(0)
+    yield s
+    s.close()
+
+
+def check_tree(eshard, oracle, X, rows, y, w, params, is_int=None, host_out=False):
+    from h2ok_hist.driver import TreeLoop
+
+    cols = X.shape[0]
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()),
+                            None if w is None else torch.from_numpy(w[:rows].copy()))
+    loop = TreeLoop(eshard, params, is_int=is_int, checksum=True)
+    assert loop.root_descs().tobytes() == oracle.root_descs(X, rows, params, is_int).tobytes()
+    ref_levels, ref_nid, ref_leaf, q = oracle_lib.train_tree_q(oracle, X, rows, y, w, params, is_int)
+    nb1 = loop.max_bins + 1
+    loop.begin_tree()
+    for lv in ref_levels:
+        n = lv["descs"].shape[0]
+        assert loop.n_nodes == n
+        assert np.array_equal(eshard.nid[:rows].cpu().numpy(), lv["nid"])
+        out = None
+        if host_out:
+            nch_max = 2 * n
+            bufs = dict(hist=np.full((n, cols, nb1, 3), -1.0), min2=np.zeros((n, cols), np.float32),
+                        maxin=np.zeros((n, cols), np.float32), splits=np.zeros(n, abi.SPLIT),
+                        child_descs=np.zeros((nch_max, cols), abi.COL_DESC), child_ids=np.zeros(2 * n, np.int32))
+            out = abi.LevelOut(*[C.c_void_p(bufs[k].ctypes.data) for k in ("hist", "min2", "maxin", "splits", "child_descs", "child_ids")])
+        done, nch = loop.level(out)
+        got = loop.done_level()
+        assert done == n and got["n"] == n and got["depth"] == lv["depth"] and got["gid_base"] == lv["gid_base"]
+        assert (got["pair0"], got["pair1"]) == (0, n * cols)
+        assert got["descs"].tobytes() == lv["descs"].tobytes()
+        assert np.array_equal(got["acc"], lv["acc"])
+        assert np.array_equal(got["min2"], lv["min2"]) and np.array_equal(got["maxin"], lv["maxin"])
+        assert got["splits"].tobytes() == lv["splits"].tobytes()
+        assert np.array_equal(got["child_ids"], lv["child_ids"])
+        assert nch == lv["child_descs"].shape[0]
+        if nch:
+            assert got["child_descs"].tobytes() == lv["child_descs"].tobytes()
+        if host_out:
+            assert np.array_equal(bufs["hist"], lv["hist"])
+            assert np.array_equal(bufs["min2"], lv["min2"]) and np.array_equal(bufs["maxin"], lv["maxin"])
+            assert bufs["splits"].tobytes() == lv["splits"].tobytes()
+            assert np.array_equal(bufs["child_ids"], lv["child_ids"])
+            assert bufs["child_descs"][:nch].tobytes() == lv["child_descs"].tobytes()
+    assert loop.n_nodes_left() == 0
+    assert np.array_equal(eshard.nid[:rows].cpu().numpy(), ref_nid)
+    assert np.array_equal(eshard.leaf[:rows].cpu().numpy(), ref_leaf)
+    assert loop.checksum(0) == oracle_lib.tree_checksum(ref_levels, ref_leaf)
+    return ref_levels
+
+
+@pytest.mark.parametrize("rows,cols,nbins,depth,weight_mode,na,host_out",
+                         [(1, 3, 16, 3, 0, 0, False), (130, 4, 32, 5, 0, 20, True), (4097, 5, 32, 6, 1, 10, False),
+                          (60001, 9, 64, 7, 0, 10, True), (50021, 40, 20, 5, 1, 10, False), (20011, 130, 32, 4, 0, 15, False),
+                          (30011, 70, 256, 5, 0, 0, True)])
+def test_loop_levels_match_oracle(eshard, oracle, rows, cols, nbins, depth, weight_mode, na, host_out):
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 500 + rows, 0, rows, cols, na_permille=na, weight_mode=weight_mode)
+    top = 1024 if nbins == 20 else None  # H2O's defaults: nbins 20, nbins_top_level 1024 halved per level
+    params = abi.Params.make(nbins=nbins, nbins_top_level=top, max_depth=depth, min_rows=1 if rows < 1000 else 5)
+    check_tree(eshard, oracle, X, rows, y, w, params, host_out=host_out)
+
+
+def test_loop_integer_columns_and_early_leaves(eshard, oracle):
+    rows, cols = 50001, 10
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 99, 0, rows, cols, na_permille=30, weight_mode=1)
+    X[4, :rows] = np.floor(X[4, :rows] * 3)
+    X[7, :rows] = np.floor(X[7, :rows] * 1000)
+    is_int = [0, 0, 0, 0, 1, 0, 0, 1, 0, 0]
+    levels = check_tree(eshard, oracle, X, rows, y, w, abi.Params.make(nbins=64, max_depth=9, min_rows=50), is_int)
+    assert len(levels) >= 5
+
+
+def test_loop_config2_full_size_matches_oracle(eshard, oracle):
+    """BASELINE config 2 as specified: 1M x 28 HIGGS-shaped, 256 bins, depth 6 — every level against the oracle."""
+    rows, cols = 1_000_000, 28
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 20261106, 0, rows, cols)
+    levels = check_tree(eshard, oracle, X, rows, y, None, abi.Params.make(nbins=256, max_depth=6))
+    assert [lv["descs"].shape[0] for lv in levels] == [1, 2, 4, 8, 16, 32]
+
+
+def test_loop_config3_slice_matches_oracle(eshard, oracle):
+    """A 10M-row slice of BASELINE config 3 (64 columns, 256 bins, depth 8: 128 nodes at the last level)."""
+    rows, cols = 10_000_000, 64
+    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 20261106, 0, rows, cols)
+    levels = check_tree(eshard, oracle, X, rows, y, None, abi.Params.make(nbins=256, max_depth=8))
+    assert levels[-1]["descs"].shape[0] == 128
+
+
+def test_loop_config4_shape_matches_oracle(eshard, oracle):
+    """BASELINE config 4's shape: 2000 sparse-ish columns (90 % exact zeros), 64 bins — 63 column blocks."""
+    rows, cols = 120_000, 2000
+    X, y, _ = oracle.synth(abi.SHAPE_SPARSE, 20261106, 0, rows, cols)
+    levels = check_tree(eshard, oracle, X, rows, y, None, abi.Params.make(nbins=64, max_depth=5))
+    assert len(levels) == 5
+
+
+def test_loop_rejects_wrong_call_order(lib):
+    h = C.c_void_p()
+    lib.call("h2ok_hist_create", 0, C.byref(h))
+    from h2ok_hist import capi
+
+    try:
+        p = abi.Params.make(nbins=64, max_depth=3)
+        with pytest.raises(capi.H2okError) as e:
+            lib.call("h2ok_hist_loop_create", h, C.byref(p), None)
+        assert e.value.code == abi.ERR_STATE
+        with pytest.raises(capi.H2okError) as e:
+            lib.call("h2ok_hist_loop_level", h, None, None, None)
+        assert e.value.code == abi.ERR_STATE
+        lib.call("h2ok_hist_tree_create", h, 1000, 3, 0)
+        lib.call("h2ok_hist_tree_load_synth", h, abi.SHAPE_HIGGS28, 7, 0, 0)
+        lib.call("h2ok_hist_loop_create", h, C.byref(p), None)
+        with pytest.raises(capi.H2okError) as e:  # no tree begun
+            lib.call("h2ok_hist_loop_level", h, None, None, None)
+        assert e.value.code == abi.ERR_STATE
+        lib.call("h2ok_hist_loop_begin_tree_synth", h, 7, 0, 0)
+        done, nch = C.c_int32(), C.c_int32()
+        for _ in range(3):
+            lib.call("h2ok_hist_loop_level", h, None, C.byref(done), C.byref(nch))
+            if nch.value == 0:
+                break
+        with pytest.raises(capi.H2okError) as e:  # the tree is finished
+            lib.call("h2ok_hist_loop_level", h, None, None, None)
+        assert e.value.code == abi.ERR_STATE
+        bad = abi.Params.make(nbins=5000, max_depth=3)
+        with pytest.raises(capi.H2okError) as e:
+            lib.call("h2ok_hist_loop_create", h, C.byref(bad), None)
+        assert e.value.code == abi.ERR_UNSUPPORTED
+    finally:
+        lib.call("h2ok_hist_destroy", h)
+
+
+def test_loop_synth_entry_points_need_no_torch_memory(lib, oracle):
+    """tree_load_synth + loop_begin_tree_synth (what a torch-free caller such as h2ok-bench uses) give the same tree as
+    the oracle on the generator's own data."""
+    rows, cols = 70001, 28
+    h = C.c_void_p()
+    lib.call("h2ok_hist_create", 0, C.byref(h))
+    try:
+        p = abi.Params.make(nbins=64, max_depth=5)
+        lib.call("h2ok_hist_tree_create", h, rows, cols, 0)
+        lib.call("h2ok_hist_tree_load_synth", h, abi.SHAPE_HIGGS28, 20261106, 0, 0)
+        lib.call("h2ok_hist_loop_create", h, C.byref(p), None)
+        lib.call("h2ok_hist_loop_set_options", h, 1, 0)
+        lib.call("h2ok_hist_loop_begin_tree_synth", h, 20261106, 0, 0)
+        nch = C.c_int32(1)
+        while nch.value:
+            lib.call("h2ok_hist_loop_level", h, None, None, C.byref(nch))
+        got = (C.c_uint64 * 3)()
+        lib.call("h2ok_hist_loop_checksum", h, 0, got)
+        X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 20261106, 0, rows, cols)
+        levels, _, leaf, _ = oracle_lib.train_tree_q(oracle, X, rows, y, None, p)
+        assert [int(x) for x in got] == oracle_lib.tree_checksum(levels, leaf)
+    finally:
+        lib.call("h2ok_hist_destroy", h)
