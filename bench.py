@@ -50,7 +50,8 @@ def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False):
 # dram__bytes_read.sum + dram__bytes_write.sum per histogram launch, from the committed `ncu --set full` captures at
 # 100M x 64 (profiles/r01_eng_hist_ncu_full.csv: 26.8-27.5 GB read + 0.01-0.05 GB written; profiles/r01_hist_build_ncu_full.csv:
 # 26.5-27.6 GB read + 0.01-0.3 GB written); scaled linearly to the rows of the run.  None for shapes not profiled.
-NCU_TRAFFIC_BYTES_PER_CELL = {"engine": 27.13e9 / (100_000_000 * 64), "stateless": 27.15e9 / (100_000_000 * 64)}
+NCU_TRAFFIC_BYTES_PER_CELL = {"engine": 27.13e9 / (100_000_000 * 64), "engine-py": 27.13e9 / (100_000_000 * 64),
+                              "stateless": 27.15e9 / (100_000_000 * 64)}
 
 
 def measured_hbm_peak():
@@ -191,12 +192,67 @@ def run_reference(args, wl):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
+class PyLoop:
+    """The Python per-step loop (LevelDriver) behind the interface bench uses, for --path stateless / engine-py."""
+
+    def __init__(self, drv, shard):
+        self.drv, self.shard = drv, shard
+
+    def begin_tree(self):
+        self.drv.prepare_tree()
+
+    def level(self, out=None):
+        return self.drv.level()
+
+    def n_nodes_left(self):
+        return self.drv.n_nodes_left()
+
+    depth = property(lambda self: self.drv.depth)
+    n_nodes = property(lambda self: self.drv.n_nodes)
+
+
+def cpu_leg(wl, rows_total, gpu_slice_checksum):
+    """cpu_baseline: the oracle's level loop on the first CPU_SAMPLE_ROWS rows (a slice, not extrapolated), timed
+    single-threaded (north_star's oracle) and with OpenMP over columns on every host core, best of N after one warm-up;
+    plus the checksum of the oracle's fixed-point tree on the slice, which must equal the GPU's on the same rows."""
+    import oracle_lib
+    from h2ok_hist import abi
+
+    oracle = oracle_lib.load()
+    threads = host_threads()
+    srows = min(CPU_SAMPLE_ROWS, rows_total)
+    cols, depth = wl["cols"], wl["depth"]
+
+    def best(th, reps, budget):
+        vals, t_all = [], time.perf_counter()
+        for i in range(reps + 1):
+            t, nodes = cpu_levels(oracle, wl, srows, th, max_seconds=budget)
+            if i > 0 or reps == 0:
+                vals.append(srows * cols * len(t) / float(np.sum(t)))
+            if time.perf_counter() - t_all > budget:
+                break
+        return (max(vals) if vals else srows * cols * len(t) / float(np.sum(t))), len(t)
+
+    v_omp, nlev = best(threads, 5, 12.0)
+    v_one, _ = best(1, 1, 15.0)
+    X, y, _ = oracle.synth(wl["shape"], SEED, 0, srows, cols)
+    levels, _, leaf, _ = oracle_lib.train_tree_q(oracle, X, srows, y, None, abi.Params.make(nbins=wl["bins"], max_depth=depth))
+    cks = oracle_lib.tree_checksum(levels, leaf)
+    return {"value": v_omp, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{nlev} levels of a depth-{depth} tree on the first {srows} rows x {cols} cols (slice, not "
+                      f"extrapolated); OpenMP over columns, best of 5 after one warm-up",
+            "single_thread_value": v_one, "single_thread_note": "the same loops on one thread (north_star's oracle), best of 2",
+            "checksum_slice_oracle": ["%016x" % c for c in cks],
+            "checksum_slice_gpu": None if gpu_slice_checksum is None else ["%016x" % c for c in gpu_slice_checksum],
+            "checksum_slice_match": None if gpu_slice_checksum is None else (list(cks) == list(gpu_slice_checksum))}
+
+
 def run_gpu(args, wl):
     import torch
     import torch.distributed as dist
 
     from h2ok_hist import abi, capi
-    from h2ok_hist.driver import CudaShard, EngineShard, LevelDriver
+    from h2ok_hist.driver import CudaShard, EngineShard, LevelDriver, TreeLoop
 
     # libraries (NCCL's version banner, for one) may write to stdout: everything but the final line goes to stderr
     global _REAL_STDOUT
@@ -223,28 +279,35 @@ def run_gpu(args, wl):
     rows_total, cols, bins, depth = wl["rows"], wl["cols"], wl["bins"], wl["depth"]
     row0 = rows_total * rank // world
     rows = rows_total * (rank + 1) // world - row0
-    shard = EngineShard(local) if args.path == "engine" else CudaShard(local)
-    shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
     params = abi.Params.make(nbins=bins, max_depth=depth)
-    drv = LevelDriver(shard, params)
-    drv.prepare_data()
+    in_library = args.path == "engine"
+    shard = CudaShard(local) if args.path == "stateless" else EngineShard(local)
+    if in_library:
+        TreeLoop.join_ranks(shard)  # the library's own NCCL communicator (h2ok_hist_comm_init)
+    shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
+    if in_library:
+        loop = TreeLoop(shard, params, checksum=True, time_phases=True)
+    else:
+        drv = LevelDriver(shard, params)
+        drv.prepare_data()
+        loop = PyLoop(drv, shard)
     barrier()
 
     # ---- resident path: inputs in HBM when the timed region starts ------------------------------------
-    rec = []  # per timed step: (level, n_nodes, hist_ms)
+    rec = []  # per timed step: (level, n_nodes, hist_ms, phase_ms)
 
     def run_steps(n_steps, record):
         done = 0
         while done < n_steps:
-            if drv.n_nodes_left() == 0:
-                drv.prepare_tree()
-            lvl, n = drv.depth, drv.n_nodes
-            drv.level()
+            if loop.n_nodes_left() == 0:
+                loop.begin_tree()
+            lvl, n = loop.depth, loop.n_nodes
+            loop.level()
             if record:
-                rec.append((lvl, n, shard.last_hist_ms()))
+                rec.append((lvl, n, shard.last_hist_ms(), loop.phase_ms() if in_library else None))
             done += 1
 
-    drv.prepare_tree()
+    loop.begin_tree()
     run_steps(args.warmup, False)
     sampler = ClockSampler(local)
     barrier()
@@ -264,54 +327,83 @@ def run_gpu(args, wl):
     launches = shard.launches - launches0
     value = rows_total * cols * args.steps / (total_ms * 1e-3)
 
-    # roofline of the dominant kernel (hist_build_kernel): algorithmic bytes of THIS rank's launches / their device time
+    # result checksum: a full tree on the timed inputs, built right after the timed region.  Integer sums make every
+    # tree on these inputs the same bits, whatever the number of ranks: the lines of a scaling run must agree.
+    checksum = None
+    if in_library:
+        loop.begin_tree()
+        while loop.n_nodes_left() > 0:
+            loop.level()
+        checksum = ["%016x" % c for c in loop.checksum(row0)]
+
+    # roofline of the dominant kernel: algorithmic bytes of THIS rank's launches / their device time
     hist_ms = float(sum(r[2] for r in rec))
     abytes = float(sum(algo_bytes_level(rows, cols, r[1], bins) for r in rec))
     peak, peak_src = measured_hbm_peak()
     achieved = abytes / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
     per_level = {}
-    for lvl, n, t in rec:
-        per_level.setdefault(lvl, []).append((n, t))
-    level_table = {str(k): {"nodes": v[0][0], "hist_ms": round(float(np.mean([x[1] for x in v])), 4),
-                            "frac": round(algo_bytes_level(rows, cols, v[0][0], bins) / (np.mean([x[1] for x in v]) * 1e-3) / 1e9 / peak, 4)}
-                   for k, v in sorted(per_level.items())}
+    for lvl, n, t, ph in rec:
+        per_level.setdefault(lvl, []).append((n, t, ph))
+    level_table = {}
+    for k, v in sorted(per_level.items()):
+        t = float(np.mean([x[1] for x in v]))
+        row = {"nodes": v[0][0], "hist_ms": round(t, 4),
+               "frac": round(algo_bytes_level(rows, cols, v[0][0], bins) / (t * 1e-3) / 1e9 / peak, 4)}
+        if v[0][2] is not None:
+            ph = np.mean([x[2] for x in v], axis=0)
+            row.update(reduce_ms=round(float(ph[1]), 4), search_ms=round(float(ph[2]), 4), route_ms=round(float(ph[3]), 4))
+        level_table[str(k)] = row
+    phases = None
+    if in_library and rec:
+        ph = np.mean([r[3] for r in rec], axis=0)
+        step_ms = total_ms / args.steps
+        phases = {"hist_ms": round(float(ph[0]), 4), "reduce_ms": round(float(ph[1]), 4), "search_children_ms": round(float(ph[2]), 4),
+                  "route_regroup_ms": round(float(ph[3]), 4), "other_ms": round(float(step_ms - ph.sum()), 4),
+                  "note": "CUDA events inside the library around the phases of every timed level (this rank); other = "
+                          "per-tree set-up (absmax, quantise, root records) and gaps"}
+    whole_level_frac = abytes / (total_ms * 1e-3) / 1e9 / peak
 
     # ---- e2e: host buffers in, host buffers out, copies inside the timed region ---------------------------
-    if args.no_e2e:
-        e2e = None
-    elif world == 1:
-        e2e = run_e2e_cabi(args, wl, shard, params)
-    else:
-        e2e = run_e2e(args, wl, shard, drv, world, rank, rows_total, rows, barrier)
+    e2e = None
+    if not args.no_e2e and in_library:
+        e2e = run_e2e_loop(args, wl, shard, loop, world, rank, rows_total, rows, barrier)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        import oracle_lib
-
-        oracle = oracle_lib.load()
-        threads = host_threads()
-        srows = min(CPU_SAMPLE_ROWS, rows_total)
-        t, nodes = cpu_levels(oracle, wl, srows, threads, max_seconds=40)
-        cpu = {"value": srows * cols * len(t) / float(np.sum(t)), "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"{len(t)} levels of a depth-{depth} tree on the first {srows} rows x {cols} cols (slice, not extrapolated)"}
+        gpu_slice = None
+        if in_library:
+            srows = min(CPU_SAMPLE_ROWS, rows_total)
+            s2 = EngineShard(local)
+            s2.set_data_synth(wl["shape"], SEED, 0, srows, cols)
+            l2 = TreeLoop(s2, params, checksum=True)
+            l2.train_tree()
+            gpu_slice = l2.checksum(0)
+            s2.close()
+        cpu = cpu_leg(wl, rows_total, gpu_slice)
 
     if rank == 0:
         sys.stdout.flush()
         os.dup2(_REAL_STDOUT, 1)  # the JSON line is the only thing this process writes to its real stdout
+        kern = "hist_build_kernel" if args.path == "stateless" else "eng_hist_kernel"
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64 binning, i32/i64 fixed-point sums", "data": "synthetic",
             "config": {"workload": wl["name"], "rows": rows_total, "cols": cols, "bins": bins, "depth": depth,
-                       "rows_per_gpu": rows, "path": args.path, "step": "one tree level (levels cycle 0..depth-1 of real trees)",
+                       "rows_per_gpu": rows, "path": args.path,
+                       "step": "one tree level (levels cycle 0..depth-1 of real trees); " +
+                               ("one h2ok_hist_loop_level call per step, reduce over ranks by the library's NCCL calls"
+                                if in_library else "Python per-step loop"),
                        "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
-                       "per_level": level_table},
+                       "per_level": level_table, "phases_ms": phases, "whole_level_frac": round(whole_level_frac, 4)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": (NCU_TRAFFIC_BYTES_PER_CELL[args.path] * rows * cols / 1e9 if args.workload == "c3" else None),
-                         "traffic_unit": "GB per launch (ncu dram read+write, profiles/r01_%s_ncu_full.csv)" % ("eng_hist" if args.path == "engine" else "hist_build"), "kernel": "eng_hist_kernel" if args.path == "engine" else "hist_build_kernel",
-                         "peak_source": peak_src,
-                         "note": "algorithmic bytes of the timed levels / CUDA-event time of their hist_build launches"},
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+                         "traffic": (NCU_TRAFFIC_BYTES_PER_CELL[args.path] * rows * cols / 1e9
+                                     if args.workload == "c3" and args.path in NCU_TRAFFIC_BYTES_PER_CELL else None),
+                         "traffic_unit": "GB per launch: ncu dram read+write of the N=1 capture at 100M rows "
+                                         "(profiles/, see README), scaled linearly to this rank's rows",
+                         "kernel": kern, "peak_source": peak_src,
+                         "note": "algorithmic bytes of the timed levels / CUDA-event time of their histogram launches"},
+            "checksum": checksum, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     shard.close()
@@ -319,180 +411,93 @@ def run_gpu(args, wl):
         dist.destroy_process_group()
 
 
-def run_e2e(args, wl, shard, drv, world, rank, rows_total, rows, barrier):
-    """Same metric through the public API with HOST buffers.  Per tree the targets y come from pinned host memory
-    (H2D inside the timed region); per level the histogram, observed ranges, splits and child ids are copied to
-    pinned host buffers (D2H inside the timed region).  X stays resident between levels, as it does in a training job;
-    its one-time upload is reported separately (set_data_ms) and not hidden."""
-    import torch
-    import torch.distributed as dist
-
-    from h2ok_hist import abi
-
-    cols, bins, depth = wl["cols"], wl["bins"], wl["depth"]
-    nb1 = bins + 1
-    max_nodes = shard.acc.shape[0]
-    y_host = shard.y[:rows].cpu().pin_memory()
-    # one-time upload of X through the host path (measured on a slice, scaled is NOT reported: we report the slice)
-    slice_cols = min(cols, 4)
-    xs = torch.empty((slice_cols, rows), dtype=torch.float32).pin_memory()
-    xd = torch.empty((slice_cols, rows), dtype=torch.float32, device="cuda")
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    xd.copy_(xs, non_blocking=True)
-    torch.cuda.synchronize()
-    h2d_s = time.perf_counter() - t0
-    upload_gbs = slice_cols * rows * 4 / h2d_s / 1e9
-    del xs, xd
-    host = dict(hist=torch.empty((max_nodes, cols, nb1, 3), dtype=torch.float64).pin_memory(),
-                min2=torch.empty((max_nodes, cols), dtype=torch.float32).pin_memory(),
-                maxin=torch.empty((max_nodes, cols), dtype=torch.float32).pin_memory(),
-                splits=torch.empty((max_nodes, abi.SPLIT.itemsize), dtype=torch.uint8).pin_memory(),
-                child_ids=torch.empty(2 * max_nodes, dtype=torch.int32).pin_memory())
-    h2d = d2h = 0
-
-    def tree_start():
-        nonlocal h2d
-        shard.set_targets(y_host)  # H2D from pinned memory
-        drv.prepare_tree()
-        h2d += rows * 4 + cols * abi.COL_DESC.itemsize
-
-    def level_out(d, n, nch):
-        nonlocal d2h
-        sh = d.shard
-        host["hist"][:n].copy_(sh.hist[:n], non_blocking=True)
-        host["min2"][:n].copy_(sh.min2[:n], non_blocking=True)
-        host["maxin"][:n].copy_(sh.maxin[:n], non_blocking=True)
-        host["splits"][:n].copy_(sh.splits[:n], non_blocking=True)
-        host["child_ids"][: 2 * n].copy_(sh.child_ids[: 2 * n], non_blocking=True)
-        d2h += n * cols * nb1 * 24 + n * cols * 8 + n * abi.SPLIT.itemsize + 2 * n * 4
-
-    def steps(k):
-        done = 0
-        while done < k:
-            if drv.n_nodes_left() == 0:
-                tree_start()
-            drv.level(inspect=level_out)
-            torch.cuda.current_stream().synchronize()  # the caller owns the host buffers only after the copies land
-            done += 1
-
-    drv.n_nodes = 0
-    steps(min(args.warmup, depth))
-    drv.n_nodes = 0  # timed region starts at a tree boundary so the y upload is counted
-    h2d = d2h = 0
-    barrier()
-    t0 = time.perf_counter()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    steps(args.steps)
-    ev1.record()
-    barrier()
-    wall = time.perf_counter() - t0
-    ms = torch.tensor([max(ev0.elapsed_time(ev1), 0.0)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms.item())
-    return {"value": rows_total * cols * args.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d / args.steps,
-            "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": ms / args.steps, "wall_ms_per_step": wall * 1e3 / args.steps,
-            "path": "LevelDriver: y from pinned host memory per tree; hist/ranges/splits/child ids to pinned host buffers per level",
-            "x_upload": {"note": "one-time, outside the timed region (X is resident across levels like H2O's DKV chunks)",
-                         "measured_h2d_gbs": upload_gbs, "full_x_bytes_per_gpu": rows * cols * 4,
-                         "est_ms": rows * cols * 4 / upload_gbs / 1e6}}
-
-
-def run_e2e_cabi(args, wl, shard, params):
-    """N=1: the same metric through the host-buffer C-ABI entry points (what an H2O-side binding calls): every level
-    the descriptors go host→device and the histogram, observed ranges, splits, child descriptors and child ids come
-    device→host; every tree the targets y go host→device (h2ok_hist_set_targets_host).  X is uploaded once with
-    h2ok_hist_set_data_host before the timed region (reported as x_upload), exactly as a training job would."""
+def run_e2e_loop(args, wl, shard, loop, world, rank, rows_total, rows, barrier):
+    """The same metric through the host-buffer side of the C ABI (what an H2O-side binding calls): per tree the targets
+    y come from host memory (h2ok_hist_loop_begin_tree_host: H2D inside the timed region), per level
+    h2ok_hist_loop_level fills host buffers with the histogram, observed ranges, splits, child descriptors and child
+    ids (D2H inside the timed region; with several ranks every rank receives the (node, column) pairs it reduced, so
+    the reduced histogram reaches host memory exactly once).  X stays resident between levels and trees, as it does in a
+    training job; its one-time upload through h2ok_hist_set_data_host is measured beside it on a bounded sample."""
     import torch
 
     from h2ok_hist import abi, capi
 
-    lib = capi.load()
-    rows, cols, bins, depth = shard.rows, wl["cols"], wl["bins"], wl["depth"]
+    cols, bins, depth = wl["cols"], wl["bins"], wl["depth"]
     nb1 = bins + 1
     max_nodes = 2 ** (depth - 1)
-    t0 = time.perf_counter()
     yh = shard.y[:rows].cpu().pin_memory()
-    # free the resident shard: the host-buffer context owns its own copy of the data from here on
-    if args.path == "engine":
-        shard.lib.call("h2ok_hist_tree_destroy", shard.ctx)
-        shard._nid = shard._leaf = None
-    else:
-        shard.X = shard.nid = shard.leaf = None
-    shard.wyq = shard.wyyq = None
-    torch.cuda.empty_cache()
-    # the caller's data: column vectors in pageable host memory (generated block-wise on the device, copied out)
-    Xh = torch.empty((cols, rows), dtype=torch.float32)
-    ld = (rows + 63) // 64 * 64
-    blk = max(1, min(cols, (1 << 30) // (4 * ld)))
-    stage = torch.empty((blk, ld), dtype=torch.float32, device="cuda")
-    for c0 in range(0, cols, blk):
-        nc = min(blk, cols - c0)
-        shard.lib.call("h2ok_hist_synth_fill_cols_dev", shard.ctx, wl["shape"], SEED, 0, rows, c0, nc, ld, 0,
-                       C.c_void_p(stage.data_ptr()))
-        Xh[c0:c0 + nc].copy_(stage[:nc, :rows])
-    del stage
-    torch.cuda.empty_cache()
-    prep_s = time.perf_counter() - t0
+
+    def pinned(shape, dtype):
+        return torch.empty(shape, dtype=dtype).pin_memory()
+
+    bufs = dict(hist=pinned((max_nodes, cols, nb1, 3), torch.float64), min2=pinned((max_nodes, cols), torch.float32),
+                maxin=pinned((max_nodes, cols), torch.float32), splits=pinned((max_nodes, abi.SPLIT.itemsize), torch.uint8),
+                child_descs=pinned((max_nodes, cols, abi.COL_DESC.itemsize), torch.uint8),
+                child_ids=pinned((2 * max_nodes,), torch.int32))
+    out = abi.LevelOut(*[C.c_void_p(bufs[k].data_ptr()) for k in ("hist", "min2", "maxin", "splits", "child_descs", "child_ids")])
+    st = dict(h2d=0, d2h=0)
+
+    def steps(k):
+        done = 0
+        while done < k:
+            if loop.n_nodes_left() == 0:
+                loop.begin_tree_host(yh)
+                st["h2d"] += rows * 4
+            n = loop.n_nodes
+            _, nch = loop.level(out)
+            pairs = n * cols
+            share = -(-pairs // world)  # the pairs this rank reduced
+            st["d2h"] += min(share, pairs) * nb1 * 24 + pairs * 8 + n * abi.SPLIT.itemsize + 2 * n * 4 + 4 + \
+                nch * cols * abi.COL_DESC.itemsize
+            done += 1
+
+    steps(min(args.warmup, depth))
+    while loop.n_nodes_left() > 0:  # the timed region starts at a tree boundary so that the y upload is counted
+        loop.level(out)
+    st.update(h2d=0, d2h=0)
+    barrier()
+    t0 = time.perf_counter()
+    steps(args.steps)
+    torch.cuda.synchronize()
+    sec = time.perf_counter() - t0  # loop_level is complete on return as far as its host buffers go
+    barrier()
+    t = torch.tensor([sec], dtype=torch.float64, device="cuda")
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    sec = float(t.item())
+    up = None
+    if rank == 0 and world == 1:
+        up = measure_upload(wl, min(rows, 10_000_000))
+    return {"value": rows_total * cols * args.steps / sec, "unit": UNIT, "h2d_bytes_per_step": st["h2d"] / args.steps,
+            "d2h_bytes_per_step": st["d2h"] / args.steps, "ms_per_step": sec * 1e3 / args.steps,
+            "path": "C ABI host-buffer calls: h2ok_hist_loop_begin_tree_host per tree (y from host memory), "
+                    "h2ok_hist_loop_level per level with host buffers for histogram, ranges, splits, child descriptors, child ids; "
+                    "host wall clock, max over ranks",
+            "x_upload": up}
+
+
+def measure_upload(wl, srows):
+    """One-time h2ok_hist_set_data_host of a bounded sample of the workload from pageable host memory."""
+    import torch
+
+    from h2ok_hist import capi
+
+    lib = capi.load()
+    cols = wl["cols"]
+    Xh = torch.empty((cols, srows), dtype=torch.float32)
+    Xh.uniform_(0, 1)
     h = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(h))
     colptrs = (C.c_void_p * cols)(*[Xh[c].data_ptr() for c in range(cols)])
     t0 = time.perf_counter()
-    lib.call("h2ok_hist_set_data_host", h, colptrs, rows, cols)
-    upload_s = time.perf_counter() - t0
-
-    def pinned(shape, dtype):
-        return torch.empty(shape, dtype=dtype).pin_memory().numpy()
-
-    hist = pinned((max_nodes, cols, nb1, 3), torch.float64)
-    min2 = pinned((max_nodes, cols), torch.float32)
-    maxin = pinned((max_nodes, cols), torch.float32)
-    splits = pinned((max_nodes, abi.SPLIT.itemsize), torch.uint8)
-    child = pinned((2 * max_nodes, cols, abi.COL_DESC.itemsize), torch.uint8)
-    ids = pinned((2 * max_nodes,), torch.int32)
-    root = np.zeros((1, cols), abi.COL_DESC)
-    lib.call("h2ok_hist_root_descs", h, C.byref(params), None, abi.ptr(root))
-    state = dict(n=0, depth=0, descs=None, h2d=0, d2h=0)
-    yp = C.c_void_p(yh.data_ptr())
-
-    def step():
-        if state["n"] == 0 or state["depth"] >= depth:
-            lib.call("h2ok_hist_set_targets_host", h, yp, None)
-            state.update(n=1, depth=0, descs=root)
-            state["h2d"] += rows * 4
-        n, d = state["n"], state["depth"]
-        lib.call("h2ok_hist_build_level", h, n, abi.ptr(state["descs"]), bins, abi.ptr(hist), abi.ptr(min2), abi.ptr(maxin))
-        lib.call("h2ok_hist_find_splits", h, params.min_rows, params.min_split_improvement, abi.ptr(splits))
-        state["h2d"] += n * cols * abi.COL_DESC.itemsize
-        state["d2h"] += n * cols * nb1 * 24 + n * cols * 8 + n * abi.SPLIT.itemsize
-        nch = 0
-        if d + 1 < depth:
-            nc = C.c_int32()
-            lib.call("h2ok_hist_next_level", h, C.byref(params), d, abi.ptr(child), abi.ptr(ids), C.byref(nc))
-            nch = nc.value
-            state["d2h"] += nch * cols * abi.COL_DESC.itemsize + 2 * n * 4 + 4
-        lib.call("h2ok_hist_apply_splits", h)
-        state.update(n=nch, depth=d + 1, descs=child.view(abi.COL_DESC).reshape(2 * max_nodes, cols)[:nch] if nch else None)
-
-    for _ in range(depth):  # warm-up: one whole tree
-        step()
-    state.update(n=0, h2d=0, d2h=0)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    torch.cuda.synchronize()
-    sec = time.perf_counter() - t0  # every entry point is synchronous on return, so host time == end-to-end time
+    lib.call("h2ok_hist_set_data_host", h, colptrs, srows, cols)
+    sec = time.perf_counter() - t0
     lib.call("h2ok_hist_destroy", h)
-    return {"value": rows * cols * args.steps / sec, "unit": UNIT, "h2d_bytes_per_step": state["h2d"] / args.steps,
-            "d2h_bytes_per_step": state["d2h"] / args.steps, "ms_per_step": sec * 1e3 / args.steps,
-            "path": "C ABI host-buffer entry points: set_targets_host per tree; build_level / find_splits / next_level / "
-                    "apply_splits per level with host descriptors in and host histogram, ranges, splits, children out",
-            "x_upload": {"note": "one-time h2ok_hist_set_data_host from pageable host memory, outside the timed region "
-                                 "(X stays resident across levels and trees, like H2O's in-memory chunks)",
-                         "ms": upload_s * 1e3, "bytes": rows * cols * 4, "host_copy_prep_s": prep_s}}
+    return {"note": "one-time h2ok_hist_set_data_host (pageable host columns -> row-major resident copy + routing codes), "
+                    "outside the timed region; measured on a sample",
+            "sample_rows": srows, "bytes": srows * cols * 4, "ms": sec * 1e3, "gbs": srows * cols * 4 / sec / 1e9}
 
 
 def main():
@@ -503,8 +508,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the workload's row count (debug only)")
-    ap.add_argument("--path", default="engine", choices=["engine", "stateless"],
-                    help="engine (default): resident row-wise tree engine, flat cost per level whatever the depth; "
+    ap.add_argument("--path", default="engine", choices=["engine", "engine-py", "stateless"],
+                    help="engine (default): resident row-wise tree engine driven by the level loop inside the library "
+                         "(h2ok_hist_loop_level); engine-py: the same kernels stepped from Python (LevelDriver); "
                          "stateless: per-call kernels on column-major rows in place")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs only)")

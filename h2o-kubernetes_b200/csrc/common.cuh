@@ -105,6 +105,12 @@ __device__ __forceinline__ int bin_fast(float x, double mn, double step, int nbi
   return x != x ? nbin : (int)idx;
 }
 
+// the same for a value known not to be NaN
+__device__ __forceinline__ int bin_fast_no_na(float x, double mn, double step, int nbin) {
+  const double pos = __dmul_rn(__dsub_rn((double)x, mn), step);
+  return (int)min(__double2uint_rz(pos), (unsigned)(nbin - 1));
+}
+
 // Packed row record (8 B): lo = wyq << 5 | node[4:0], hi = wyyq << 5 | node[9:5]; node 0x3FF = takes no part.
 constexpr unsigned kNoNode = 0x3FFu;
 __device__ __forceinline__ unsigned rec_node(unsigned lo, unsigned hi) { return (lo & 31u) | ((hi & 31u) << 5); }

@@ -58,6 +58,8 @@ struct Engine {
   const int32_t* wyq_rows = nullptr;
   const int32_t* wyyq_rows = nullptr;
   double scale_wy = 0, scale_wyy = 0;   // fixed-point scales of the tree's targets (0: no centring)
+  int32_t* na_flag = nullptr;           // != 0 once a NaN cell has been seen while loading (device)
+  bool na_known = false, has_na = true; // host copy of it, read once per data set: NaN-free shards skip the NA test
   int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
 };
 

@@ -198,7 +198,7 @@ __device__ constexpr unsigned kPark[4] = {0x3217u, 0x3270u, 0x3710u, 0x7210u};
 // v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
 // LPR = lanes per row (32, or 16 for levels whose histograms are too wide for 32 columns per block): a bin of one
 // column slot is 3 channels x LPR lanes x 4 bytes.
-template <int CPL, bool WEIGHTED, int U, int LPR>
+template <int CPL, bool WEIGHTED, int U, int LPR, bool NA>
 __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[CPL], const typename XVec<CPL>::type (&xv)[U],
                                          const int (&w)[U], unsigned (&pa)[U * CPL]) {
   float xs[U][CPL];
@@ -209,7 +209,8 @@ __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[C
       float x = xget(xv[j], k);
       if (WEIGHTED) x = w[j] != 0 ? x : __int_as_float(0x7FC00000);
       xs[j][k] = x;
-      const int b = bin_fast(x, c.mn[k], c.st[k], c.nb[k]);
+      // NA == false: the shard holds no NaN at all (census taken while the data was loaded), the NA test is dropped
+      const int b = NA ? bin_fast(x, c.mn[k], c.st[k], c.nb[k]) : bin_fast_no_na(x, c.mn[k], c.st[k], c.nb[k]);
       pa[j * CPL + k] = cell_addr(hb[k], (unsigned)b, 12u * LPR);
     }
   }
@@ -289,8 +290,9 @@ struct EngCfg {
   static constexpr int U = WEIGHTED ? 4 / CPL : (CPL == 1 ? 6 : 4);  // 6, 4 (unweighted) or 4, 2 (weighted): even
 };
 
-template <int CPL, bool WEIGHTED, int LPR>
+template <int CPL, bool WEIGHTED, int LPR, bool NA>
 __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
+  static_assert(NA || !WEIGHTED, "zero-weight rows are turned into NaNs: weighted shards need the NA test");
   using V = typename XVec<CPL>::type;
   constexpr int THREADS = EngCfg<CPL, WEIGHTED>::threads, NW = THREADS / 32;
   constexpr int U = LPR == 16 && !WEIGHTED ? 4 : EngCfg<CPL, WEIGHTED>::U;  // (the 16-lane layout spills at eight rows)
@@ -383,7 +385,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         w[0] = WEIGHTED ? __ldg(gw + q) : 1;
         unsigned pa[CPL];
         if (on) {
-          eng_bins<CPL, WEIGHTED, 1, LPR>(c, hb, x, w, pa);
+          eng_bins<CPL, WEIGHTED, 1, LPR, NA>(c, hb, x, w, pa);
           eng_accum<CPL, WEIGHTED, 1, LPR>(a, hb, node, col_lane, pa, v1, v2, w);
         }
       };
@@ -426,7 +428,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
 #pragma unroll
         for (int j = 0; j < U; j++) w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
         unsigned pa[U * CPL];
-        if (on) eng_bins<CPL, WEIGHTED, U, LPR>(c, hb, x, w, pa);
+        if (on) eng_bins<CPL, WEIGHTED, U, LPR, NA>(c, hb, x, w, pa);
         if (more) {
 #pragma unroll
           for (int j = 0; j < U; j++) prefetch_l2(row_addr(xrow, (unsigned)nx[j], ldt4));
@@ -571,7 +573,7 @@ __global__ void __launch_bounds__(1024) eng_thresholds_kernel(const float* __res
 
 __global__ void __launch_bounds__(256) eng_code_kernel(const float* __restrict__ X, int64_t ld, int64_t rows,
                                                        const unsigned* __restrict__ thr, uint8_t* __restrict__ code8,
-                                                       int64_t ld8) {
+                                                       int64_t ld8, int* __restrict__ na_flag) {
   __shared__ unsigned t[256];
   t[threadIdx.x] = thr[(int64_t)blockIdx.y * 256 + threadIdx.x];
   __syncthreads();
@@ -585,10 +587,12 @@ __global__ void __launch_bounds__(256) eng_code_kernel(const float* __restrict__
 #pragma unroll
     for (int k = 0; k < 4; k++) w |= (f[k] != f[k] ? 255u : code_of(t, enc_key(f[k]))) << (8 * k);
     *reinterpret_cast<unsigned*>(o + r0) = w;
+    if ((v.x != v.x) | (v.y != v.y) | (v.z != v.z) | (v.w != v.w)) *na_flag = 1;
   } else {
     for (int k = 0; k < 4 && r0 + k < rows; k++) {
       const float f = x[r0 + k];
       o[r0 + k] = (uint8_t)(f != f ? 255u : code_of(t, enc_key(f)));
+      if (f != f) *na_flag = 1;
     }
   }
 }
@@ -880,7 +884,11 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   A((void**)&e.cta_cnt, sizeof(int32_t) * (size_t)kEngMaxNodes * (size_t)e.route_ctas);
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
   A((void**)&e.err, sizeof(int32_t));
+  A((void**)&e.na_flag, sizeof(int32_t));
   if (err == cudaSuccess) err = cudaMemset(e.err, 0, sizeof(int32_t));
+  if (err == cudaSuccess) err = cudaMemset(e.na_flag, 0, sizeof(int32_t));
+  e.na_known = false;
+  e.has_na = true;
   if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   if (err != cudaSuccess) engine_free(e);
   return err;
@@ -893,7 +901,8 @@ void engine_free(Engine& e) {
     cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]); cudaFree(e.mnode[k]);
     e.gidx[k] = nullptr; e.gval[k] = nullptr; e.gw[k] = nullptr; e.seg[k] = nullptr; e.mnode[k] = nullptr;
   }
-  cudaFree(e.nid16); cudaFree(e.cta_cnt); cudaFree(e.leaf); cudaFree(e.err);
+  cudaFree(e.nid16); cudaFree(e.cta_cnt); cudaFree(e.leaf); cudaFree(e.err); cudaFree(e.na_flag);
+  e.na_flag = nullptr;
   e.XT = nullptr;
   e.code8 = nullptr;
   e.thr = nullptr;
@@ -923,7 +932,9 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
   // the routing codes of the same columns: thresholds from a sorted sample, then one byte per cell
   eng_thresholds_kernel<<<ncols, 1024, 0, s>>>(X, ld, e.rows, e.thr + (int64_t)col0 * 256);
   dim3 cgrid(nblk(e.rows, 1024), (unsigned)ncols);
-  eng_code_kernel<<<cgrid, 256, 0, s>>>(X, ld, e.rows, e.thr + (int64_t)col0 * 256, e.code8 + (int64_t)col0 * e.ld8, e.ld8);
+  eng_code_kernel<<<cgrid, 256, 0, s>>>(X, ld, e.rows, e.thr + (int64_t)col0 * 256, e.code8 + (int64_t)col0 * e.ld8, e.ld8,
+                                        e.na_flag);
+  e.na_known = false;
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return err;
   return launch_col_ranges(X, ld, e.rows, ncols, e.cmin + col0, e.cmax + col0, s);  // DHistogram.initialHist reads them
@@ -961,18 +972,18 @@ int engine_max_nb1(int cols) {
   return kHistSmemCap / (16 * 12);
 }
 
-template <int CPL, bool W, int LPR>
+template <int CPL, bool W, int LPR, bool NA>
 static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
   static std::atomic<bool> attr_done[64];  // per device, per instantiation (setting it twice is harmless)
   int dev = 0;
   cudaGetDevice(&dev);
   std::atomic<bool>& attr = attr_done[dev & 63];
   if (!attr.load(std::memory_order_acquire)) {
-    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W, LPR, NA>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
     if (e != cudaSuccess) return e;
     attr.store(true, std::memory_order_release);
   }
-  eng_hist_kernel<CPL, W, LPR><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
+  eng_hist_kernel<CPL, W, LPR, NA><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -1006,13 +1017,26 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   const dim3 grid((unsigned)e.sms, (unsigned)((e.cols + colblk - 1) / colblk));
   const size_t smem = (size_t)colblk * nbs * 12;
   if (e.weighted) {
-    if (lay.cpl == 2) return launch_eng_hist<2, true, 32>(a, grid, smem, s);
-    if (lay.lpr == 32) return launch_eng_hist<1, true, 32>(a, grid, smem, s);
-    return launch_eng_hist<1, true, 16>(a, grid, smem, s);
+    if (lay.cpl == 2) return launch_eng_hist<2, true, 32, true>(a, grid, smem, s);
+    if (lay.lpr == 32) return launch_eng_hist<1, true, 32, true>(a, grid, smem, s);
+    return launch_eng_hist<1, true, 16, true>(a, grid, smem, s);
   }
-  if (lay.cpl == 2) return launch_eng_hist<2, false, 32>(a, grid, smem, s);
-  if (lay.lpr == 32) return launch_eng_hist<1, false, 32>(a, grid, smem, s);
-  return launch_eng_hist<1, false, 16>(a, grid, smem, s);
+  if (!e.na_known) {  // once per data set: did any cell of the shard turn out to be NaN while the codes were made?
+    int flag = 1;
+    cudaError_t err = cudaMemcpyAsync(&flag, e.na_flag, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+    if (err != cudaSuccess) return err;
+    e.has_na = flag != 0;
+    e.na_known = true;
+  }
+  if (e.has_na) {
+    if (lay.cpl == 2) return launch_eng_hist<2, false, 32, true>(a, grid, smem, s);
+    if (lay.lpr == 32) return launch_eng_hist<1, false, 32, true>(a, grid, smem, s);
+    return launch_eng_hist<1, false, 16, true>(a, grid, smem, s);
+  }
+  if (lay.cpl == 2) return launch_eng_hist<2, false, 32, false>(a, grid, smem, s);
+  if (lay.lpr == 32) return launch_eng_hist<1, false, 32, false>(a, grid, smem, s);
+  return launch_eng_hist<1, false, 16, false>(a, grid, smem, s);
 }
 
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,
