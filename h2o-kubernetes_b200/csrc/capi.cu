@@ -218,6 +218,11 @@ int32_t h2ok_hist_build_level_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int
   return H2OK_OK;
 }
 
+int32_t h2ok_hist_build_level_passes(int32_t n_nodes, int32_t cols, int64_t rows, int32_t max_bins) {
+  if (n_nodes < 1 || cols < 1 || max_bins < 1 || max_bins > H2OK_MAX_BINS) return 0;
+  return plan_hist(n_nodes, cols, rows, max_bins + 1).passes;
+}
+
 int32_t h2ok_hist_finalize_level_dev(h2ok_ctx* c, const int64_t* d_acc, const uint32_t* d_min2_enc,
                                      const uint32_t* d_maxin_enc, int32_t n_nodes, int32_t cols, int32_t max_bins,
                                      const h2ok_quant* q, double* d_hist, float* d_min2, float* d_maxin) {
@@ -286,6 +291,11 @@ int32_t h2ok_hist_gbm_gamma_pass_dev(h2ok_ctx* c, const int32_t* d_leaf, const i
                                      int64_t rows, int32_t n_codes, int64_t* d_num_acc, int64_t* d_den_acc) {
   REQUIRE(c && d_leaf && d_numq && d_num_acc && d_den_acc, "null pointer");
   REQUIRE(rows >= 0 && n_codes > 0, "bad rows / n_codes");
+  if (rows == 0) {  // a rank with an empty shard still has to produce zero sums
+    CK(cudaMemsetAsync(d_num_acc, 0, sizeof(int64_t) * (size_t)n_codes, c->stream));
+    CK(cudaMemsetAsync(d_den_acc, 0, sizeof(int64_t) * (size_t)n_codes, c->stream));
+    return H2OK_OK;
+  }
   CK(launch_gbm_gamma_pass(d_leaf, d_numq, d_denq, rows, n_codes, d_num_acc, d_den_acc, c->stream));
   return H2OK_OK;
 }
@@ -344,6 +354,7 @@ int32_t h2ok_hist_tree_begin_dev(h2ok_ctx* c, const int32_t* d_wq, const int32_t
   REQUIRE(c && d_wyq && d_wyyq, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_begin_dev before tree_create");
   REQUIRE(!c->eng.weighted || d_wq, "weighted engine needs d_wq");
+  CK(cudaMemsetAsync(c->eng.err, 0, sizeof(int32_t), c->stream));  // range_errors count per tree
   CK(engine_begin_tree(c->eng, d_wq, d_wyq, d_wyyq, q, c->stream));
   return H2OK_OK;
 }

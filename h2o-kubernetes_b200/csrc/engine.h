@@ -58,6 +58,7 @@ struct Engine {
   const int32_t* wyq_rows = nullptr;
   const int32_t* wyyq_rows = nullptr;
   double scale_wy = 0, scale_wyy = 0;   // fixed-point scales of the tree's targets (0: no centring)
+  const h2ok_quant* q_dev = nullptr;    // the same scales in device memory, when the tree was started without a host copy
   int32_t* na_flag = nullptr;           // != 0 once a NaN cell has been seen while loading (device)
   bool na_known = false, has_na = true; // host copy of it, read once per data set: NaN-free shards skip the NA test
   int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
@@ -72,8 +73,9 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
 // new tree: every row at the root, records in row order.  q (may be NULL) gives the targets' fixed-point scales, from
 // which the children's centring offsets are derived; without it every node keeps the root's offsets.  The target
 // arrays are read again by every level's regrouping: they must stay valid and unchanged until the tree is finished.
+// (q_dev: q in device memory instead — a tree then starts without a host round trip; q may be NULL with it)
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
-                              const h2ok_quant* q, cudaStream_t s);
+                              const h2ok_quant* q, cudaStream_t s, const h2ok_quant* q_dev = nullptr);
 // one level's histogram pass.  nb1 = bins + 1 of the accumulators' layout; level_nb1 (0: same as nb1) = bins + 1 of
 // the widest histogram of THIS level, which sizes the shared histogram (H2O halves nbins_top_level per level)
 cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* descs, int nb1, int level_nb1, int64_t* acc,

@@ -93,11 +93,29 @@ __global__ void target_absmax_kernel(const float* __restrict__ y, const float* _
   }
 }
 
+// Power-of-two fixed-point scales from max|w|, max|w*y|, max|w*y*y| on the device (the host rule of
+// h2ok_hist_choose_quant, bit for bit): lets a tree start without a host round trip.
+__device__ inline double pow2_scale_dev(double absmax, int qbits) {
+  if (!(absmax > 0.0) || isinf(absmax)) return 1.0;
+  int ex;
+  frexp(absmax, &ex);
+  return ldexp(1.0, qbits - ex);
+}
+__global__ void choose_quant_kernel(const double* __restrict__ m, int weighted, int qbits, h2ok_quant* __restrict__ q) {
+  q->weighted = weighted ? 1 : 0;
+  q->qbits = qbits;
+  q->scale_w = weighted ? pow2_scale_dev(m[0], qbits) : 1.0;
+  q->scale_wy = pow2_scale_dev(m[1], qbits);
+  q->scale_wyy = pow2_scale_dev(m[2], qbits);
+}
+
+// qd != NULL: the scales come from device memory (choose_quant_kernel) instead of the by-value copy
 __global__ void quantize_rows_kernel(const float* __restrict__ y, const float* __restrict__ w, int64_t rows,
-                                     h2ok_quant q, int32_t* __restrict__ wq, int32_t* __restrict__ wyq,
-                                     int32_t* __restrict__ wyyq) {
+                                     h2ok_quant q, const h2ok_quant* __restrict__ qd, int32_t* __restrict__ wq,
+                                     int32_t* __restrict__ wyq, int32_t* __restrict__ wyyq) {
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= rows) return;
+  if (qd) q = *qd;
   double wd = (q.weighted && w) ? (double)w[r] : 1.0, yd = (double)y[r];
   double wy = __dmul_rn(wd, yd);
   double wyy = __dmul_rn(wy, yd);
@@ -420,9 +438,14 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_build_kernel(HistArgs a)
 }
 
 __global__ void finalize_kernel(const int64_t* __restrict__ acc, int64_t n, double inv_w, double inv_wy, double inv_wyy,
-                                double* __restrict__ hist) {
+                                const h2ok_quant* __restrict__ qd, double* __restrict__ hist) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  if (qd) {  // powers of two: the reciprocals are exact
+    inv_w = 1.0 / qd->scale_w;
+    inv_wy = 1.0 / qd->scale_wy;
+    inv_wyy = 1.0 / qd->scale_wyy;
+  }
   int ch = (int)(i % 3);
   hist[i] = __dmul_rn((double)acc[i], ch == 0 ? inv_w : (ch == 1 ? inv_wy : inv_wyy));
 }
@@ -482,7 +505,20 @@ cudaError_t launch_target_absmax(const float* y, const float* w, int64_t rows, d
 
 cudaError_t launch_quantize_rows(const float* y, const float* w, int64_t rows, const h2ok_quant& q, int32_t* wq,
                                  int32_t* wyq, int32_t* wyyq, cudaStream_t s) {
-  quantize_rows_kernel<<<blocks_for(rows, 256), 256, 0, s>>>(y, w, rows, q, wq, wyq, wyyq);
+  quantize_rows_kernel<<<blocks_for(rows, 256), 256, 0, s>>>(y, w, rows, q, nullptr, wq, wyq, wyyq);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_choose_quant_dev(const double* absmax3, int weighted, int qbits, h2ok_quant* q_dev, cudaStream_t s) {
+  choose_quant_kernel<<<1, 1, 0, s>>>(absmax3, weighted, qbits, q_dev);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_quantize_rows_dev(const float* y, const float* w, int64_t rows, bool weighted, const h2ok_quant* q_dev,
+                                     int32_t* wq, int32_t* wyq, int32_t* wyyq, cudaStream_t s) {
+  h2ok_quant q{};
+  q.weighted = weighted ? 1 : 0;  // overwritten from q_dev inside the kernel
+  quantize_rows_kernel<<<blocks_for(rows, 256), 256, 0, s>>>(y, w, rows, q, q_dev, wq, wyq, wyyq);
   return cudaGetLastError();
 }
 
@@ -507,14 +543,18 @@ HistPlan plan_hist(int n_nodes, int cols, int64_t rows, int nb1) {
   HistPlan p;
   const size_t budget = 227 * 1024;
   const size_t slot = (size_t)nb1 * 3 * sizeof(int);
-  int slots = (int)((budget - hist_head_bytes(64)) / slot);  // (node,copy) slots that fit beside the descriptor tables
+  // (node, copy) slots that fit beside the descriptor tables of 64 nodes: a first guess (64 at 256 bins) ...
+  int slots = (int)((budget - hist_head_bytes(64)) / slot);
   int pow2 = 1;
   while (pow2 * 2 <= slots) pow2 *= 2;
-  slots = pow2;  // 64 at 256 bins
+  slots = pow2;
   p.group = n_nodes < slots ? n_nodes : slots;
+  // ... which is too generous once a group has more than 64 nodes (fewer than 256 bins): the tables grow with the
+  // group, so the group shrinks until tables + one histogram copy per node really fit (more passes over X instead)
+  while (p.group > 1 && hist_smem_bytes(p.group, nb1, 1) > budget) p.group--;
   p.passes = (n_nodes + p.group - 1) / p.group;
   int copies = 1;
-  while (copies * 2 <= 32 && copies * 2 * p.group <= slots) copies *= 2;
+  while (copies * 2 <= 32 && hist_smem_bytes(p.group, nb1, copies * 2) <= budget) copies *= 2;
   p.copies = copies;
   // chunks: cols*chunks CTAs, a multiple of 148 when cols % 4 == 0, about 4-16 waves; never below one tile
   int64_t tile = (int64_t)kHistThreads * 4;
@@ -554,6 +594,7 @@ cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_
     a.copies = plan.copies;
     a.chunk_rows = plan.chunk_rows;
     size_t smem = hist_smem_bytes(a.node_cnt, a.nb1, a.copies);
+    if (smem > (size_t)227 * 1024) return cudaErrorInvalidValue;  // a plan that does not fit must not reach the launch
     unsigned grid = (unsigned)(a.cols * plan.chunks);
     const bool one = n_nodes == 1;
     if (weighted && one) hist_build_kernel<true, true><<<grid, kHistThreads, smem, s>>>(a);
@@ -569,8 +610,16 @@ cudaError_t launch_hist_build(const HistArgs& base, const HistPlan& plan, int n_
 cudaError_t launch_finalize(const int64_t* acc, const uint32_t* mn, const uint32_t* mx, int64_t n_node_cols, int nb1,
                             const h2ok_quant& q, double* hist, float* min2, float* maxin, cudaStream_t s) {
   int64_t n = n_node_cols * nb1 * 3;
-  if (hist) finalize_kernel<<<blocks_for(n, 256), 256, 0, s>>>(acc, n, 1.0 / q.scale_w, 1.0 / q.scale_wy, 1.0 / q.scale_wyy, hist);
+  if (hist)
+    finalize_kernel<<<blocks_for(n, 256), 256, 0, s>>>(acc, n, 1.0 / q.scale_w, 1.0 / q.scale_wy, 1.0 / q.scale_wyy, nullptr, hist);
   if (min2) decode_ranges_kernel<<<blocks_for(n_node_cols, 256), 256, 0, s>>>(mn, mx, n_node_cols, min2, maxin);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_finalize_dev(const int64_t* acc, int64_t n_node_cols, int nb1, const h2ok_quant* q_dev, double* hist,
+                                cudaStream_t s) {
+  int64_t n = n_node_cols * nb1 * 3;
+  finalize_kernel<<<blocks_for(n, 256), 256, 0, s>>>(acc, n, 1.0, 1.0, 1.0, q_dev, hist);
   return cudaGetLastError();
 }
 

@@ -43,6 +43,12 @@ cudaError_t launch_col_ranges(const float* X, int64_t ld, int64_t rows, int cols
 cudaError_t launch_target_absmax(const float* y, const float* w, int64_t rows, double* out, cudaStream_t s);
 cudaError_t launch_quantize_rows(const float* y, const float* w, int64_t rows, const h2ok_quant& q, int32_t* wq,
                                  int32_t* wyq, int32_t* wyyq, cudaStream_t s);
+// the same with the scales in device memory (no host round trip between absmax and the quantised targets)
+cudaError_t launch_choose_quant_dev(const double* absmax3, int weighted, int qbits, h2ok_quant* q_dev, cudaStream_t s);
+cudaError_t launch_quantize_rows_dev(const float* y, const float* w, int64_t rows, bool weighted, const h2ok_quant* q_dev,
+                                     int32_t* wq, int32_t* wyq, int32_t* wyyq, cudaStream_t s);
+cudaError_t launch_finalize_dev(const int64_t* acc, int64_t n_node_cols, int nb1, const h2ok_quant* q_dev, double* hist,
+                                cudaStream_t s);
 cudaError_t launch_bin(const float* x, int64_t n, const h2ok_col_desc& d, int32_t* out, cudaStream_t s);
 cudaError_t launch_pack_rows(const int32_t* nid, const int32_t* wq, const int32_t* wyq, const int32_t* wyyq, int64_t rows,
                              int64_t padded, int n_nodes, uint2* rec, int32_t* err, cudaStream_t s);
@@ -59,7 +65,9 @@ struct PairCand {
 };
 // pairs [pair0, pair1) of the flat [n_nodes * cols] list, from the fp64 histogram (hist != NULL) or straight from the
 // int64 accumulators with q's scales (hist == NULL); cand is indexed by pair
-cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_col_desc* descs,
+// (q_dev != NULL: q's scales are read from device memory instead)
+cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
+                                const h2ok_col_desc* descs,
                                 int64_t pair0, int64_t pair1, int nb1, double min_rows, double msi, PairCand* cand,
                                 cudaStream_t s);
 cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_split* splits, cudaStream_t s);

@@ -96,7 +96,10 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
   if (p >= rows) return;
   // zero-weight rows still travel down the tree (a6); the histogram pass skips them by weight
   gidx[p] = (int32_t)p;
-  gval[p] = make_uint2((unsigned)(wyq_rows[p] - mnode[0]), (unsigned)(wyyq_rows[p] - mnode[1]));
+  // a row whose quantised weight is 0 takes no part, whatever its (independently scaled) targets round to — the
+  // histogram pass sends it to the NA bin with weight 0, so its targets must be 0 too (weighted shards keep M == 0)
+  const bool dead = gw && wq_rows[p] == 0;
+  gval[p] = dead ? make_uint2(0u, 0u) : make_uint2((unsigned)(wyq_rows[p] - mnode[0]), (unsigned)(wyyq_rows[p] - mnode[1]));
   if (gw) gw[p] = wq_rows[p];
   leaf[p] = -1;
   nid16[p] = 0;
@@ -677,8 +680,13 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
 __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ cta_cnt, int G, int n_nodes,
                                                         const int32_t* __restrict__ child_ids, int32_t* __restrict__ seg_next,
                                                         const h2ok_split* __restrict__ splits, double scale_wy,
-                                                        double scale_wyy, const int32_t* __restrict__ mnode,
+                                                        double scale_wyy, const h2ok_quant* __restrict__ q_dev,
+                                                        const int32_t* __restrict__ mnode,
                                                         int32_t* __restrict__ mnode_next) {
+  if (q_dev) {  // the tree's scales live on the device (no host round trip at tree start)
+    scale_wy = q_dev->scale_wy;
+    scale_wyy = q_dev->scale_wyy;
+  }
   __shared__ int s_warp[33];
   __shared__ int s_tot[kEngMaxNodes];
   __shared__ int s_nc;
@@ -825,7 +833,11 @@ __global__ void __launch_bounds__(kScatThreads, 2) eng_scatter_kernel(
         const int2 m = s_m[ch[k]];
         s_row[pos] = (int)r;
         s_val[pos] = make_uint2((unsigned)(wyq_rows[r] - m.x), (unsigned)(wyyq_rows[r] - m.y));
-        if (WEIGHTED) s_w[pos] = wq_rows[r];
+        if (WEIGHTED) {
+          const int wq = wq_rows[r];
+          s_w[pos] = wq;
+          if (wq == 0) s_val[pos] = make_uint2(0u, 0u);  // zero weight: no part in any sum (see eng_begin_kernel)
+        }
         s_child[pos] = (uint16_t)ch[k];
       }
     }
@@ -941,7 +953,8 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
 }
 
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
-                              const h2ok_quant* q, cudaStream_t s) {
+                              const h2ok_quant* q, cudaStream_t s, const h2ok_quant* q_dev) {
+  e.q_dev = q_dev;
   e.cur = 0;
   e.n_nodes = 1;
   e.scale_wy = (q && !e.weighted) ? q->scale_wy : 0.0;
@@ -1051,6 +1064,7 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
                                                    gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots);
   // every level but a tree's last: lay the children's records out for the next histogram pass
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.cta_cnt, G, n_nodes, child_ids, e.seg[nx], splits, e.scale_wy, e.scale_wyy,
+                                     e.weighted ? nullptr : e.q_dev,
                                      e.mnode[e.cur], e.mnode[nx]);
   if (regroup) {
     const size_t ncp = (size_t)(n_slots + 1) & ~(size_t)1;

@@ -60,11 +60,17 @@ __device__ __forceinline__ double warp_incl_scan(double v, int lane) {
 struct ValsF64 {
   const double* __restrict__ p;
   __device__ __forceinline__ double operator()(int b, int ch) const { return p[3 * b + ch]; }
+  __device__ __forceinline__ void scales_from(const h2ok_quant*) {}
 };
 struct ValsAcc {
   const int64_t* __restrict__ p;
   double inv[3];
   __device__ __forceinline__ double operator()(int b, int ch) const { return __dmul_rn((double)p[3 * b + ch], inv[ch]); }
+  __device__ __forceinline__ void scales_from(const h2ok_quant* q) {  // powers of two: exact reciprocals
+    inv[0] = 1.0 / q->scale_w;
+    inv[1] = 1.0 / q->scale_wy;
+    inv[2] = 1.0 / q->scale_wyy;
+  }
 };
 
 // One warp evaluates one (node, column).  Returns found != 0 in every lane and the winning candidate in `out`.
@@ -232,7 +238,8 @@ __device__ float warp_splat(const V& vals, const h2ok_col_desc& d, int bin, int 
 //   best_col_kernel      one warp per node: UndecidedNode.bestCol over the node's PairCands -> h2ok_split
 // n_nodes may live on the device (n_dev != NULL): grids are then sized by an upper bound and surplus warps leave.
 template <class V>
-__global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, const h2ok_col_desc* __restrict__ descs,
+__global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, const h2ok_quant* __restrict__ q_dev,
+                                                                        const h2ok_col_desc* __restrict__ descs,
                                                                         int64_t pair0, int64_t pair1, int nb1,
                                                                         double min_rows, double msi,
                                                                         PairCand* __restrict__ out) {
@@ -247,6 +254,7 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, 
   pc.key = pc.seL = pc.seR = pc.nL = pc.nR = pc.pL = pc.pR = pc.se_before = 0;
   if (d.nbin > 1) {
     V vals = base;
+    if (q_dev) vals.scales_from(q_dev);
     vals.p += pair * nb1 * 3;
     Cand cand;
     double before;
@@ -483,16 +491,22 @@ __global__ void apply_splits_kernel(const float* __restrict__ X, int64_t ld, int
 
 }  // namespace
 
-cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_col_desc* descs,
-                                int64_t pair0, int64_t pair1, int nb1, double min_rows, double msi, PairCand* cand,
-                                cudaStream_t s) {
+cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
+                                const h2ok_col_desc* descs, int64_t pair0, int64_t pair1, int nb1, double min_rows,
+                                double msi, PairCand* cand, cudaStream_t s) {
   if (pair1 <= pair0) return cudaSuccess;
   const unsigned grid = (unsigned)((pair1 - pair0 + kSplitWarps - 1) / kSplitWarps);
   if (hist) {
-    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, 0, s>>>(ValsF64{hist}, descs, pair0, pair1, nb1, min_rows, msi, cand);
+    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, 0, s>>>(ValsF64{hist}, nullptr, descs, pair0, pair1, nb1, min_rows,
+                                                                   msi, cand);
   } else {
-    ValsAcc v{acc, {1.0 / q->scale_w, 1.0 / q->scale_wy, 1.0 / q->scale_wyy}};
-    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, 0, s>>>(v, descs, pair0, pair1, nb1, min_rows, msi, cand);
+    ValsAcc v{acc, {1.0, 1.0, 1.0}};
+    if (!q_dev) {
+      v.inv[0] = 1.0 / q->scale_w;
+      v.inv[1] = 1.0 / q->scale_wy;
+      v.inv[2] = 1.0 / q->scale_wyy;
+    }
+    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, 0, s>>>(v, q_dev, descs, pair0, pair1, nb1, min_rows, msi, cand);
   }
   return cudaGetLastError();
 }
@@ -504,7 +518,8 @@ cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_sp
 
 cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
                                double min_rows, double msi, PairCand* cand, h2ok_split* splits, cudaStream_t s) {
-  cudaError_t e = launch_split_points(hist, nullptr, nullptr, descs, 0, (int64_t)n_nodes * cols, nb1, min_rows, msi, cand, s);
+  cudaError_t e = launch_split_points(hist, nullptr, nullptr, nullptr, descs, 0, (int64_t)n_nodes * cols, nb1, min_rows, msi,
+                                      cand, s);
   if (e != cudaSuccess) return e;
   return launch_best_col(cand, n_nodes, cols, splits, s);
 }

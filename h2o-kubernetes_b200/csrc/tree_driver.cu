@@ -145,7 +145,8 @@ struct TreeLoop {
   DevBuf<float> y, w;
   DevBuf<int32_t> wq, wyq, wyyq;
   DevBuf<double> absmax;
-  h2ok_quant q{};
+  h2ok_quant* q_dev = nullptr;  // the tree's fixed-point scales, chosen on the device
+  h2ok_quant* h_q = nullptr;    // pinned host copy (arrives with the first level's results)
   bool have_tree = false, checksum = false;
   // tree state
   int cur = 0, n_nodes = 0, depth = 0, gid_base = 0;
@@ -177,8 +178,9 @@ void loop_free(h2ok_ctx* c) {
   for (int k = 0; k < 2; k++) cudaFree(L->descs[k]);
   cudaFree(L->acc); cudaFree(L->rng); cudaFree(L->cand); cudaFree(L->splits); cudaFree(L->child_ids);
   cudaFree(L->n_children); cudaFree(L->tmp_descs); cudaFree(L->tmp_valid); cudaFree(L->hist); cudaFree(L->rngf);
-  cudaFree(L->sums);
+  cudaFree(L->sums); cudaFree(L->q_dev);
   if (L->h_nch) cudaFreeHost(L->h_nch);
+  if (L->h_q) cudaFreeHost(L->h_q);
   if (L->out_stream) cudaStreamDestroy(L->out_stream);
   for (cudaEvent_t e : {L->ev_ready, L->ev_out, L->ev_a, L->ev_b, L->ev_c, L->ev_d, L->ev_e})
     if (e) cudaEventDestroy(e);
@@ -240,6 +242,7 @@ int32_t level_reduce(h2ok_ctx* c) {
   NcclApi* n = nccl_api();
   ncclComm_t comm = (ncclComm_t)c->comm;
   const size_t cell = (size_t)L.nb1 * 3;
+  NK(n->GroupStart());  // one launch for the three collectives
   if (L.reduce_mode == H2OK_REDUCE_SCATTER)
     NK(n->ReduceScatter(L.acc, L.acc + (size_t)L.chunk * c->comm_rank * cell, (size_t)L.chunk * cell, ncclInt64, ncclSum, comm,
                         c->stream));
@@ -247,6 +250,7 @@ int32_t level_reduce(h2ok_ctx* c) {
     NK(n->AllReduce(L.acc, L.acc, (size_t)L.pairs * cell, ncclInt64, ncclSum, comm, c->stream));
   NK(n->AllReduce(L.rng, L.rng, (size_t)L.pairs, ncclUint32, ncclMin, comm, c->stream));
   NK(n->AllReduce(L.rng + L.pairs_cap, L.rng + L.pairs_cap, (size_t)L.pairs, ncclUint32, ncclMax, comm, c->stream));
+  NK(n->GroupEnd());
   return H2OK_OK;
 }
 
@@ -255,7 +259,7 @@ int32_t level_search(h2ok_ctx* c) {
   TreeLoop& L = *c->loop;
   CK(cudaSetDevice(c->device));
   if (L.phases_timed) CK(cudaEventRecord(L.ev_c, c->stream));
-  CK(launch_split_points(nullptr, L.acc, &L.q, L.descs[L.cur], L.p0, L.p1, L.nb1, L.params.min_rows,
+  CK(launch_split_points(nullptr, L.acc, nullptr, L.q_dev, L.descs[L.cur], L.p0, L.p1, L.nb1, L.params.min_rows,
                          L.params.min_split_improvement, L.cand, c->stream));
   if (L.checksum && L.p1 > L.p0) {
     const int64_t cell = (int64_t)L.nb1 * 3, cnt = (L.p1 - L.p0) * cell;
@@ -298,11 +302,11 @@ int32_t level_finish(h2ok_ctx* c) {
   if (out && (out->min2 || out->maxin) && !L.rngf) CK(cudaMalloc((void**)&L.rngf, sizeof(float) * 2 * L.pairs_cap));
   if (out && out->hist && L.p1 > L.p0) {
     const int64_t cell = (int64_t)L.nb1 * 3;
-    CK(launch_finalize(L.acc + L.p0 * cell, nullptr, nullptr, L.p1 - L.p0, L.nb1, L.q, L.hist + L.p0 * cell, nullptr, nullptr,
-                       c->stream));
+    CK(launch_finalize_dev(L.acc + L.p0 * cell, L.p1 - L.p0, L.nb1, L.q_dev, L.hist + L.p0 * cell, c->stream));
   }
   if (out && (out->min2 || out->maxin))
-    CK(launch_finalize(nullptr, L.rng, L.rng + L.pairs_cap, L.pairs, L.nb1, L.q, nullptr, L.rngf, L.rngf + L.pairs_cap, c->stream));
+    CK(launch_finalize(nullptr, L.rng, L.rng + L.pairs_cap, L.pairs, L.nb1, h2ok_quant{}, nullptr, L.rngf, L.rngf + L.pairs_cap,
+                       c->stream));
   if (L.phases_timed) CK(cudaEventRecord(L.ev_d, c->stream));
   // results to the host on their own stream, so that routing does not wait for the copies
   CK(cudaEventRecord(L.ev_ready, c->stream));
@@ -364,15 +368,14 @@ int32_t begin_tree_common(h2ok_ctx* c, const float* d_y, const float* d_w) {
   if (weighted != c->eng.weighted) CK(engine_set_weighted(c->eng, weighted));
   CK(L.wyq.ensure(pad)); CK(L.wyyq.ensure(pad)); CK(L.absmax.ensure(3));
   if (weighted) CK(L.wq.ensure(pad));
+  // no host round trip: the scales are chosen and used on the device; the host copy travels with the first level's results
   CK(launch_target_absmax(d_y, d_w, n, L.absmax.p, c->stream));
   if (c->comm_ranks > 1)
     NK(nccl_api()->AllReduce(L.absmax.p, L.absmax.p, 3, ncclFloat64, ncclMax, (ncclComm_t)c->comm, c->stream));
-  double m[3];
-  CK(cudaMemcpyAsync(m, L.absmax.p, sizeof(m), cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  h2ok_hist_choose_quant(m, weighted ? 1 : 0, 25, &L.q);
-  CK(launch_quantize_rows(d_y, d_w, n, L.q, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, c->stream));
-  CK(engine_begin_tree(c->eng, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, &L.q, c->stream));
+  CK(launch_choose_quant_dev(L.absmax.p, weighted ? 1 : 0, 25, L.q_dev, c->stream));
+  CK(cudaMemcpyAsync(L.h_q, L.q_dev, sizeof(h2ok_quant), cudaMemcpyDeviceToHost, c->stream));
+  CK(launch_quantize_rows_dev(d_y, d_w, n, weighted, L.q_dev, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, c->stream));
+  CK(engine_begin_tree(c->eng, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, nullptr, c->stream, L.q_dev));
   CK(cudaMemcpyAsync(L.descs[0], L.root.data(), sizeof(h2ok_col_desc) * L.cols, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(L.sums, 0, 3 * sizeof(unsigned long long), c->stream));
   L.cur = 0;
@@ -482,7 +485,9 @@ int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int3
   A((void**)&L->tmp_descs, sizeof(h2ok_col_desc) * 2 * L->pairs_cap);
   A((void**)&L->tmp_valid, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
   A((void**)&L->sums, 3 * sizeof(unsigned long long));
+  A((void**)&L->q_dev, sizeof(h2ok_quant));
   if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_nch, sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_q, sizeof(h2ok_quant));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->out_stream, cudaStreamNonBlocking);
   for (cudaEvent_t* ev : {&L->ev_ready, &L->ev_out})
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
@@ -605,7 +610,8 @@ int32_t h2ok_hist_loop_view(h2ok_ctx* c, h2ok_loop_view* v) {
   v->rank = c->comm_rank;
   v->n_ranks = c->comm_ranks;
   v->reduce_mode = L.reduce_mode;
-  v->quant = L.q;
+  CK(cudaStreamSynchronize(c->stream));  // the host copy of the scales is in flight until the tree's first level is done
+  v->quant = *L.h_q;
   v->d_descs = L.descs[L.cur];
   v->d_wq = L.wq.p;
   v->d_wyq = L.wyq.p;

@@ -29,6 +29,7 @@ SIGNATURES = {
     "h2ok_hist_quantize_rows_dev": [vp, vp, vp, i64, pQ, vp, vp, vp],
     "h2ok_hist_bin_dev": [vp, vp, i64, vp, vp],
     "h2ok_hist_build_level_dev": [vp, vp, i64, i64, i32, vp, vp, vp, vp, i32, vp, i32, i32, vp, vp, vp],
+    "h2ok_hist_build_level_passes": [i32, i32, i64, i32],
     "h2ok_hist_finalize_level_dev": [vp, vp, vp, vp, i32, i32, i32, pQ, vp, vp, vp],
     "h2ok_hist_find_splits_dev": [vp, vp, vp, i32, i32, i32, f64, f64, vp],
     "h2ok_hist_next_level_dev": [vp, vp, vp, vp, vp, i32, i32, pP, i32, vp, vp, vp],
@@ -92,6 +93,10 @@ class Lib:
             fn = getattr(cdll, name)  # AttributeError if the library does not export a declared symbol
             fn.restype = i32
             fn.argtypes = args
+
+    def value(self, name, *args):
+        """For the few entry points that return a number instead of a status."""
+        return getattr(self.cdll, name)(*args)
 
     def call(self, name, *args):
         rc = getattr(self.cdll, name)(*args)

@@ -146,10 +146,8 @@ class CudaShard:
         self.lib.call("h2ok_hist_build_level_dev", self.ctx, _ptr(self.X), self.ld, self.rows, self.cols, _ptr(self.nid),
                       _ptr(self.wq), _ptr(self.wyq), _ptr(self.wyyq), n_nodes, _ptr(self.descs), self.max_bins, 1,
                       _ptr(self.acc), _ptr(self.mn), _ptr(self.mx))
-        slots = 1
-        while slots * 2 <= (227 * 1024 - 64 * 260) // ((self.max_bins + 1) * 12):
-            slots *= 2  # same rule as plan_hist() in csrc/hist_kernels.cu
-        self.launches += 2 + (n_nodes + slots - 1) // slots  # init_enc + pack_rows + one hist_build per node group
+        # init_enc + pack_rows + one hist_build per node group (the library's own plan)
+        self.launches += 2 + self.lib.value("h2ok_hist_build_level_passes", n_nodes, self.cols, self.rows, self.max_bins)
         return self.acc[:n_nodes], self.mn[:n_nodes], self.mx[:n_nodes]
 
     def last_hist_ms(self):

@@ -206,6 +206,11 @@ int32_t h2ok_hist_build_level_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, i
                                   int32_t max_bins, int32_t clear, int64_t* d_acc, uint32_t* d_min2_enc,
                                   uint32_t* d_maxin_enc);
 
+/* Passes over X (= histogram kernel launches) h2ok_hist_build_level_dev makes for a level of this shape: the nodes are
+ * taken in groups whose histograms and descriptor tables fit one CTA's 227 KB of shared memory.  Host arithmetic only;
+ * returns 0 for shapes build_level_dev rejects.  (Not a status code.) */
+int32_t h2ok_hist_build_level_passes(int32_t n_nodes, int32_t cols, int64_t rows, int32_t max_bins);
+
 /* a5 tail — after the cross-rank reduce (MRTask.reduce / DHistogram.add, done by the caller on d_acc with an
  * integer sum and on the encoded ranges with integer min/max): fixed-point → double, encoded → float. */
 int32_t h2ok_hist_finalize_level_dev(h2ok_ctx* ctx, const int64_t* d_acc, const uint32_t* d_min2_enc,
@@ -324,8 +329,9 @@ int32_t h2ok_hist_loop_set_reduce(h2ok_ctx* ctx, int32_t mode /*H2OK_REDUCE_**/)
  * accumulators); time_phases != 0: bracket the phases of every level with CUDA events (h2ok_hist_loop_phase_ms). */
 int32_t h2ok_hist_loop_set_options(h2ok_ctx* ctx, int32_t checksum, int32_t time_phases);
 /* New tree on targets y (and weights w, NULL: unweighted) in original row order: common fixed-point scales over all
- * ranks (one blocking read of three doubles), quantised targets, every row back at the root.  _dev: device pointers,
- * read during this call only; _host: the library copies them in; _synth: the generator's y / w for rows from row0. */
+ * ranks (chosen on the device: no host round trip), quantised targets, every row back at the root.  Asynchronous.
+ * _dev: device pointers, read by work enqueued on the context's stream (order later writes to them after it);
+ * _host: the library copies them in; _synth: the generator's y / w for rows from row0. */
 int32_t h2ok_hist_loop_begin_tree_dev(h2ok_ctx* ctx, const float* d_y, const float* d_w);
 int32_t h2ok_hist_loop_begin_tree_host(h2ok_ctx* ctx, const float* y_host, const float* w_host);
 int32_t h2ok_hist_loop_begin_tree_synth(h2ok_ctx* ctx, uint64_t seed, int64_t row0, int32_t weight_mode);
@@ -368,7 +374,11 @@ int32_t h2ok_hist_gbm_add_gamma_dev(h2ok_ctx* ctx, const int32_t* d_leaf, int64_
  * arithmetic, no device work): constant / all-NA / infinite-range columns get nbin 0. */
 int32_t h2ok_hist_root_descs_from_ranges(const float* col_min, const float* col_max, int32_t cols,
                                          const h2ok_params* params, const int32_t* is_int, h2ok_col_desc* descs_out);
-/* Power-of-two fixed-point scales from max|w|, max|w*y|, max|w*y*y| (host arithmetic). */
+/* Power-of-two fixed-point scales from max|w|, max|w*y|, max|w*y*y| (host arithmetic).
+ * Limit: the split search and finalize turn the integer sums into doubles, which is exact (and therefore equal to the
+ * oracle's sequential sums, bit for bit) while |sum| < 2^53 quanta, i.e. while (rows over ALL ranks) * 2^qbits < 2^53:
+ * 2^28 = 268M rows at the default qbits = 25.  Beyond that ranks still agree with each other (the sums are integers)
+ * but equality with a sequential fp64 walk is no longer guaranteed; lower qbits for larger jobs. */
 int32_t h2ok_hist_choose_quant(const double* absmax3, int32_t weighted, int32_t qbits, h2ok_quant* out);
 
 /* ---- host-buffer entry points (what an H2O-side caller binds; synchronous) ------------------ */

@@ -1,0 +1,10 @@
+#!/bin/bash
+# multi-GPU: bit-identity tests, then the bench at N = all visible GPUs
+mkdir -p gpurun_out
+N=$(python -c "import torch; print(torch.cuda.device_count())")
+timeout 1500 python -m pytest tests/test_multi_gpu.py -m gpu -x -q 2>&1 | tail -15 > gpurun_out/pytest_mgpu.txt; cat gpurun_out/pytest_mgpu.txt
+for n in $N; do
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29555 bench.py --gpus $n --steps 16 --warmup 8 > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err; tail -3 gpurun_out/bench_n$n.err
+python -c "
+import json; d=json.load(open('gpurun_out/bench_n$n.json')); print('N=$n value %.1f Gcells/s  ms/step %.3f  frac %.3f whole %.3f' % (d['value']/1e9, d['ms_per_step'], d['roofline']['frac'], d['config']['whole_level_frac'])); print(d['config']['phases_ms']); print(d['checksum']); print({k:v for k,v in d['e2e'].items() if k in ('value','ms_per_step','d2h_bytes_per_step')})"
+done

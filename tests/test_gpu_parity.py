@@ -1,10 +1,13 @@
 """GPU parity tests: every call goes through the C ABI (ctypes → libh2ok_hist.so) and is checked against the
 oracle on the same seeded inputs.  Integer / index work must be bit-exact; fp sums are checked two ways:
  (1) against the oracle's fixed-point walk — every channel an exact integer, so equality is bit-for-bit;
- (2) against the oracle's fp64 walk of the unquantised fp32 inputs with north_star's tolerance:
-     |got - ref| <= 1e-5 * sum|w*y| over the bin + rows_in_bin * half a quantum (0.5/scale <= 2^-26 * max|w*y|,
-     the documented fixed-point allowance: >300x below the 1e-5 term for any bin whose mean |w*y| is within
-     1/1000 of the max).
+ (2) against the oracle's fp64 walk of the unquantised fp32 inputs with north_star's tolerance, plain:
+     |got - ref| <= 1e-5 * sum|w*y| over the bin (sum w*y*y, sum w for the other channels).
+     The only bins excused from the plain bound are those where it is smaller than the fixed-point quantum itself
+     (1e-5 * sum|w*y| < rows_in_bin * 0.5 / scale: a handful of rows whose targets are ~1000x below the largest one —
+     they occur in the randomised small cases, never at the BASELINE shapes); for them the error must stay within
+     half a quantum per row.  test_fp_sums_plain_tolerance_at_baseline_shapes asserts the plain bound with no excused
+     bin at all on config-2 / config-3 data and records the largest relative error seen.
 """
 import ctypes as C
 
@@ -142,10 +145,64 @@ def check_level(shard, oracle, X, rows, y, w, nid, descs, nb, qbits=25):
     if w is None:
         assert np.array_equal(got[..., 0], hist[..., 0])  # counts exact
     else:
-        assert (np.abs(got[..., 0] - hist[..., 0]) <= REL_TOL * hist[..., 0] + nrows * 0.5 / q.scale_w).all()
-    assert (np.abs(got[..., 1] - hist[..., 1]) <= REL_TOL * absy + nrows * 0.5 / q.scale_wy).all()  # (2)
-    assert (np.abs(got[..., 2] - hist[..., 2]) <= REL_TOL * hist[..., 2] + nrows * 0.5 / q.scale_wyy).all()
+        assert_fp_close(got[..., 0], hist[..., 0], hist[..., 0], nrows, q.scale_w)
+    assert_fp_close(got[..., 1], hist[..., 1], absy, nrows, q.scale_wy)  # (2)
+    assert_fp_close(got[..., 2], hist[..., 2], hist[..., 2], nrows, q.scale_wyy)
     return acc
+
+
+def assert_fp_close(got, ref, denom, nrows, scale, allow_quantum_bins=True):
+    """|got - ref| <= 1e-5 * denom, plain.  Bins whose plain bound is below the quantisation step itself may fall back
+    to half a quantum per row (allow_quantum_bins); returns (largest error / denom over the plainly checked bins,
+    number of excused bins)."""
+    err = np.abs(got - ref)
+    plain = REL_TOL * denom
+    quantum = nrows * 0.5 / scale
+    excused = plain < quantum
+    if not allow_quantum_bins:
+        assert not excused.any(), f"{int(excused.sum())} bins need the fixed-point allowance"
+    assert (err[~excused] <= plain[~excused]).all()
+    assert (err[excused] <= quantum[excused]).all()
+    checked = (~excused) & (denom > 0)
+    worst = float((err[checked] / denom[checked]).max()) if checked.any() else 0.0
+    return worst, int(excused.sum())
+
+
+@pytest.mark.parametrize("shape,rows,cols,depth", [(abi.SHAPE_HIGGS28, 1_000_000, 28, 6), (abi.SHAPE_WIDE64, 2_000_000, 64, 8)])
+def test_fp_sums_plain_tolerance_at_baseline_shapes(eshard, oracle, shape, rows, cols, depth):
+    """north_star's tolerance as written — 1e-5 relative, no additive term — on config-2 data at full size and on a
+    2M-row slice of config 3, at every level of a real tree; the largest relative error observed is recorded."""
+    import json
+    import os
+
+    import oracle_lib
+    from h2ok_hist.driver import TreeLoop
+
+    nb = 256
+    X, y, _ = oracle.synth(shape, 20261106, 0, rows, cols)
+    params = abi.Params.make(nbins=nb, max_depth=depth)
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()))
+    loop = TreeLoop(eshard, params)
+    ref_levels, _, _, q = oracle_lib.train_tree_q(oracle, X, rows, y, None, params)
+    ones = np.ones(rows, np.float32)
+    loop.begin_tree()
+    worst = [0.0, 0.0]
+    for lv in ref_levels:
+        loop.level()
+        acc = loop.done_level()["acc"]
+        got = oracle.finalize(acc, q, nb)
+        hist, absy, _, _ = oracle.build_level(X, rows, y, None, lv["nid"], lv["descs"], nb, threads=oracle.max_threads())
+        nrows = oracle.build_level(X, rows, ones, None, lv["nid"], lv["descs"], nb, threads=oracle.max_threads(),
+                                   want_abs=False)[0][..., 0]
+        assert np.array_equal(got[..., 0], hist[..., 0])
+        w1, e1 = assert_fp_close(got[..., 1], hist[..., 1], absy, nrows, q.scale_wy, allow_quantum_bins=False)
+        w2, e2 = assert_fp_close(got[..., 2], hist[..., 2], hist[..., 2], nrows, q.scale_wyy, allow_quantum_bins=False)
+        worst = [max(worst[0], w1), max(worst[1], w2)]
+    assert worst[0] <= REL_TOL and worst[1] <= REL_TOL
+    os.makedirs(os.path.join(os.path.dirname(__file__), "..", "gpurun_out"), exist_ok=True)
+    with open(os.path.join(os.path.dirname(__file__), "..", "gpurun_out", f"fp_tolerance_{cols}cols.json"), "w") as f:
+        json.dump({"shape": f"{rows} x {cols}, 256 bins, depth {depth}", "bound": REL_TOL, "excused_bins": 0,
+                   "max_rel_err_wY": worst[0], "max_rel_err_wYY": worst[1]}, f)
 
 
 @pytest.mark.parametrize("rows", [1, 3, 4, 5, 4095, 4097, 150001])
@@ -175,6 +232,23 @@ def test_build_level_many_nodes(shard, oracle, n_nodes, weight_mode, na):
     descs[n_nodes // 2, 1]["nbin"] = 0
     descs[0, 3]["nbin"] = 17
     check_level(shard, oracle, X, rows, y, w, nid, descs, nb)
+
+
+@pytest.mark.parametrize("n_nodes,nb", [(128, 64), (224, 64), (127, 32), (512, 20), (1023, 7)])
+def test_build_level_node_groups_beyond_64(shard, oracle, n_nodes, nb):
+    """Fewer than 256 bins let more than 64 nodes into one group; the descriptor tables then grow with the group and the
+    plan has to count them (64 bins x 128 nodes used to ask for 512 bytes more than a CTA can have)."""
+    rows, cols = 40001, 3
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 900 + n_nodes, 0, rows, cols, na_permille=5, weight_mode=n_nodes % 2)
+    rng = np.random.default_rng(n_nodes)
+    nid = np.full(X.shape[1], -1, np.int32)
+    nid[:rows] = rng.integers(-1, n_nodes, rows)
+    root = oracle.root_descs(X, rows, abi.Params.make(nbins=nb))
+    descs = np.stack([root] * n_nodes)
+    for g in range(n_nodes):
+        descs[g]["min"] += (g % 7) * 0.01
+    check_level(shard, oracle, X, rows, y, w, nid, descs, nb)
+    assert shard.lib.value("h2ok_hist_build_level_passes", n_nodes, cols, rows, nb) >= 1
 
 
 def test_build_level_skewed_and_small_bins(shard, oracle):

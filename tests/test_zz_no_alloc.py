@@ -58,6 +58,8 @@ def test_no_alloc_next_level_matches_allocating_entry_point(oracle, lib):
     params, cols, levels = oracle_levels(oracle)
     ctx = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(ctx))
+    # the library's kernels go on the stream torch fills the output buffers on, so the fills cannot land late
+    lib.call("h2ok_hist_set_stream", ctx, C.c_void_p(torch.cuda.current_stream().cuda_stream), 0)
     try:
         for lv in levels:  # two calls in a row through the shared scratch array
             want = run(lib, ctx, "h2ok_hist_next_level_dev", params, cols, lv)
