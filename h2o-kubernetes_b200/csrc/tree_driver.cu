@@ -137,6 +137,7 @@ struct TreeLoop {
   double* hist = nullptr;                        // fp64 copy of acc, made only when a caller asks for it
   float* rngf = nullptr;                         // [2][max_nodes * cols] decoded ranges, likewise
   unsigned long long* sums = nullptr;            // [3] checksums {acc, splits, leaf}
+  unsigned long long* sums_tmp = nullptr;        // [3] this rank's share on its way through the all-reduce
   size_t pairs_cap = 0, acc_pairs = 0;
   int32_t* h_nch = nullptr;                      // pinned
   cudaStream_t out_stream = nullptr;             // device -> host copies of a level's results
@@ -147,6 +148,8 @@ struct TreeLoop {
   DevBuf<double> absmax;
   h2ok_quant* q_dev = nullptr;  // the tree's fixed-point scales, chosen on the device
   h2ok_quant* h_q = nullptr;    // pinned host copy (arrives with the first level's results)
+  const float* tree_y = nullptr;  // the current tree's targets between the phases of loop_begin_tree
+  const float* tree_w = nullptr;
   bool have_tree = false, checksum = false;
   // tree state
   int cur = 0, n_nodes = 0, depth = 0, gid_base = 0;
@@ -178,7 +181,7 @@ void loop_free(h2ok_ctx* c) {
   for (int k = 0; k < 2; k++) cudaFree(L->descs[k]);
   cudaFree(L->acc); cudaFree(L->rng); cudaFree(L->cand); cudaFree(L->splits); cudaFree(L->child_ids);
   cudaFree(L->n_children); cudaFree(L->tmp_descs); cudaFree(L->tmp_valid); cudaFree(L->hist); cudaFree(L->rngf);
-  cudaFree(L->sums); cudaFree(L->q_dev);
+  cudaFree(L->sums); cudaFree(L->sums_tmp); cudaFree(L->q_dev);
   if (L->h_nch) cudaFreeHost(L->h_nch);
   if (L->h_q) cudaFreeHost(L->h_q);
   if (L->out_stream) cudaStreamDestroy(L->out_stream);
@@ -360,21 +363,37 @@ int32_t level_wait(h2ok_ctx* c, int32_t* n_done, int32_t* n_children) {
   return H2OK_OK;
 }
 
-int32_t begin_tree_common(h2ok_ctx* c, const float* d_y, const float* d_w) {
+// a tree's start in three phases (a group runs each phase for all its members, the NCCL one inside a group call)
+int32_t begin_tree_local(h2ok_ctx* c, const float* d_y, const float* d_w) {
   TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
   const int64_t n = c->eng.rows;
   const size_t pad = (size_t)(n + 3) / 4 * 4;
   const bool weighted = d_w != nullptr;
   if (weighted != c->eng.weighted) CK(engine_set_weighted(c->eng, weighted));
   CK(L.wyq.ensure(pad)); CK(L.wyyq.ensure(pad)); CK(L.absmax.ensure(3));
   if (weighted) CK(L.wq.ensure(pad));
-  // no host round trip: the scales are chosen and used on the device; the host copy travels with the first level's results
+  L.tree_y = d_y;
+  L.tree_w = d_w;
   CK(launch_target_absmax(d_y, d_w, n, L.absmax.p, c->stream));
+  return H2OK_OK;
+}
+int32_t begin_tree_reduce(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
   if (c->comm_ranks > 1)
     NK(nccl_api()->AllReduce(L.absmax.p, L.absmax.p, 3, ncclFloat64, ncclMax, (ncclComm_t)c->comm, c->stream));
+  return H2OK_OK;
+}
+int32_t begin_tree_finish(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  const int64_t n = c->eng.rows;
+  const bool weighted = L.tree_w != nullptr;
+  // no host round trip: the scales are chosen and used on the device; the host copy travels with the first level's results
   CK(launch_choose_quant_dev(L.absmax.p, weighted ? 1 : 0, 25, L.q_dev, c->stream));
   CK(cudaMemcpyAsync(L.h_q, L.q_dev, sizeof(h2ok_quant), cudaMemcpyDeviceToHost, c->stream));
-  CK(launch_quantize_rows_dev(d_y, d_w, n, weighted, L.q_dev, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, c->stream));
+  CK(launch_quantize_rows_dev(L.tree_y, L.tree_w, n, weighted, L.q_dev, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, c->stream));
+  CK(cudaMemsetAsync(c->eng.err, 0, sizeof(int32_t), c->stream));
   CK(engine_begin_tree(c->eng, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, nullptr, c->stream, L.q_dev));
   CK(cudaMemcpyAsync(L.descs[0], L.root.data(), sizeof(h2ok_col_desc) * L.cols, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(L.sums, 0, 3 * sizeof(unsigned long long), c->stream));
@@ -384,6 +403,46 @@ int32_t begin_tree_common(h2ok_ctx* c, const float* d_y, const float* d_w) {
   L.gid_base = 0;
   L.done_depth = -1;
   L.have_tree = true;
+  return H2OK_OK;
+}
+int32_t begin_tree_common(h2ok_ctx* c, const float* d_y, const float* d_w) {
+  int32_t rc = begin_tree_local(c, d_y, d_w);
+  if (rc) return rc;
+  if ((rc = begin_tree_reduce(c))) return rc;
+  return begin_tree_finish(c);
+}
+
+// the checksum query in three phases
+int32_t checksum_local(h2ok_ctx* c, int64_t row0) {
+  TreeLoop& L = *c->loop;
+  if (!L.checksum) return fail(H2OK_ERR_STATE, "%s", "loop_checksum: switch the checksum on with loop_set_options first");
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemsetAsync(L.sums + 2, 0, sizeof(unsigned long long), c->stream));
+  hash_i32_kernel<<<grid_for(c->eng.rows, 256, 1184), 256, 0, c->stream>>>(c->eng.leaf, c->eng.rows, (uint64_t)row0, kSaltLeaf,
+                                                                          L.sums + 2);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(L.sums_tmp, L.sums, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
+  if (c->comm_ranks > 1 && c->comm_rank != 0) {
+    // every rank hashed the same splits: rank 0's count.  Under H2OK_REDUCE_ALL the same holds for the accumulators;
+    // under H2OK_REDUCE_SCATTER a rank hashed only the pairs it reduced
+    CK(cudaMemsetAsync(L.sums_tmp + 1, 0, sizeof(unsigned long long), c->stream));
+    if (L.reduce_mode != H2OK_REDUCE_SCATTER) CK(cudaMemsetAsync(L.sums_tmp, 0, sizeof(unsigned long long), c->stream));
+  }
+  return H2OK_OK;
+}
+int32_t checksum_reduce(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  if (c->comm_ranks > 1)
+    NK(nccl_api()->AllReduce(L.sums_tmp, L.sums_tmp, 3, ncclUint64, ncclSum, (ncclComm_t)c->comm, c->stream));
+  return H2OK_OK;
+}
+int32_t checksum_fetch(h2ok_ctx* c, uint64_t* out3) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  unsigned long long h[3];
+  CK(cudaMemcpyAsync(h, L.sums_tmp, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < 3; k++) out3[k] = h[k];
   return H2OK_OK;
 }
 
@@ -447,7 +506,7 @@ int32_t h2ok_hist_tree_load_synth(h2ok_ctx* c, int32_t shape, uint64_t seed, int
 }
 
 // ------------------------------------------------------------------------------------------------ the loop
-int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int) {
+static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int) {
   REQUIRE(c && params, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "loop_create before tree_create / the data is loaded");
   REQUIRE(params->max_depth >= 1 && params->nbins >= 1 && params->nbins_top_level >= 1, "bad params");
@@ -485,6 +544,7 @@ int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int3
   A((void**)&L->tmp_descs, sizeof(h2ok_col_desc) * 2 * L->pairs_cap);
   A((void**)&L->tmp_valid, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
   A((void**)&L->sums, 3 * sizeof(unsigned long long));
+  A((void**)&L->sums_tmp, 3 * sizeof(unsigned long long));
   A((void**)&L->q_dev, sizeof(h2ok_quant));
   if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_nch, sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_q, sizeof(h2ok_quant));
@@ -497,12 +557,23 @@ int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int3
     loop_free(c);
     return fail(H2OK_ERR_CUDA, "loop_create: %s", cudaGetErrorString(e));
   }
-  // DHistogram.initialHist: root descriptors from the column ranges of ALL ranks (taken while the data was loaded)
-  if (R > 1) {
-    NcclApi* n = nccl_api();
-    NK(n->AllReduce(c->eng.cmin, c->eng.cmin, (size_t)cols, ncclUint32, ncclMin, (ncclComm_t)c->comm, c->stream));
-    NK(n->AllReduce(c->eng.cmax, c->eng.cmax, (size_t)cols, ncclUint32, ncclMax, (ncclComm_t)c->comm, c->stream));
-  }
+  return H2OK_OK;
+}
+
+// DHistogram.initialHist reads the column ranges of ALL ranks (each took its own while the data was loaded)
+static int32_t loop_reduce_ranges(h2ok_ctx* c) {
+  if (c->comm_ranks <= 1) return H2OK_OK;
+  NcclApi* n = nccl_api();
+  const size_t cols = (size_t)c->eng.cols;
+  NK(n->AllReduce(c->eng.cmin, c->eng.cmin, cols, ncclUint32, ncclMin, (ncclComm_t)c->comm, c->stream));
+  NK(n->AllReduce(c->eng.cmax, c->eng.cmax, cols, ncclUint32, ncclMax, (ncclComm_t)c->comm, c->stream));
+  return H2OK_OK;
+}
+
+static int32_t loop_make_root(h2ok_ctx* c) {
+  TreeLoop* L = c->loop;
+  const int cols = L->cols;
+  CK(cudaSetDevice(c->device));
   std::vector<uint32_t> emn(cols), emx(cols);
   CK(cudaMemcpyAsync(emn.data(), c->eng.cmin, sizeof(uint32_t) * cols, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(emx.data(), c->eng.cmax, sizeof(uint32_t) * cols, cudaMemcpyDeviceToHost, c->stream));
@@ -514,7 +585,15 @@ int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int3
     memcpy(&hi[j], &b, 4);
   }
   L->root.resize(cols);
-  return h2ok_hist_root_descs_from_ranges(lo.data(), hi.data(), cols, params, is_int, L->root.data());
+  return h2ok_hist_root_descs_from_ranges(lo.data(), hi.data(), cols, &L->params, L->is_int.empty() ? nullptr : L->is_int.data(),
+                                          L->root.data());
+}
+
+int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int) {
+  int32_t rc = loop_alloc(c, params, is_int);
+  if (rc) return rc;
+  if ((rc = loop_reduce_ranges(c))) return rc;
+  return loop_make_root(c);
 }
 
 int32_t h2ok_hist_loop_destroy(h2ok_ctx* c) {
@@ -658,33 +737,257 @@ int32_t h2ok_hist_loop_checksum(h2ok_ctx* c, int64_t row0, uint64_t* out3) {
   int32_t rc = need_loop(c, "loop_checksum");
   if (rc) return rc;
   REQUIRE(out3 != nullptr && row0 >= 0, "bad arguments");
-  TreeLoop& L = *c->loop;
-  if (!L.checksum) return fail(H2OK_ERR_STATE, "%s", "loop_checksum: switch the checksum on with loop_set_options first");
-  CK(cudaSetDevice(c->device));
-  // {acc, splits} were accumulated level by level; every rank hashed the same splits, so only rank 0's count
-  CK(cudaMemsetAsync(L.sums + 2, 0, sizeof(unsigned long long), c->stream));
-  hash_i32_kernel<<<grid_for(c->eng.rows, 256, 1184), 256, 0, c->stream>>>(c->eng.leaf, c->eng.rows, (uint64_t)row0, kSaltLeaf,
-                                                                          L.sums + 2);
-  CK(cudaGetLastError());
-  unsigned long long h[3];
-  if (c->comm_ranks > 1) {
-    // the accumulator sum of a rank covers its own pairs in either reduce mode only under H2OK_REDUCE_SCATTER; under
-    // H2OK_REDUCE_ALL every rank hashed everything, like the splits
-    CK(c->absmax.ensure(3));
-    unsigned long long* tmp = reinterpret_cast<unsigned long long*>(c->absmax.p);
-    CK(cudaMemcpyAsync(tmp, L.sums, sizeof(h), cudaMemcpyDeviceToDevice, c->stream));
-    const bool own_part = L.reduce_mode == H2OK_REDUCE_SCATTER;
-    if (c->comm_rank != 0) {
-      CK(cudaMemsetAsync(tmp + 1, 0, sizeof(unsigned long long), c->stream));
-      if (!own_part) CK(cudaMemsetAsync(tmp, 0, sizeof(unsigned long long), c->stream));
-    }
-    NK(nccl_api()->AllReduce(tmp, tmp, 3, ncclUint64, ncclSum, (ncclComm_t)c->comm, c->stream));
-    CK(cudaMemcpyAsync(h, tmp, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
-  } else {
-    CK(cudaMemcpyAsync(h, L.sums, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  if ((rc = checksum_local(c, row0))) return rc;
+  if ((rc = checksum_reduce(c))) return rc;
+  return checksum_fetch(c, out3);
+}
+
+// ------------------------------------------------------------------------------------------------ a group of devices
+// One host thread, several GPUs (what a caller shaped like the reference's main() needs: src/main.rs:18-37 is single
+// threaded and blocking).  A group owns one context per device and one NCCL communicator over them; every group call
+// runs the phases of the per-context call for all members, with the phases that talk to NCCL inside one
+// ncclGroupStart / ncclGroupEnd (several devices driven from one thread must be grouped).
+struct h2ok_group {
+  std::vector<h2ok_ctx*> m;
+  std::vector<int64_t> row0;  // global index of every member's first row
+  int64_t rows_total = 0;
+};
+
+#define EACH(g, expr)                          \
+  do {                                         \
+    for (h2ok_ctx * c : (g)->m) {              \
+      int32_t _rc = (expr);                    \
+      if (_rc) return _rc;                     \
+    }                                          \
+  } while (0)
+#define EACH_NCCL(g, expr)                                  \
+  do {                                                      \
+    if ((g)->m.size() > 1) NK(nccl_api()->GroupStart());    \
+    int32_t _first = H2OK_OK;                               \
+    for (h2ok_ctx * c : (g)->m) {                           \
+      int32_t _rc = (expr);                                 \
+      if (_rc && !_first) _first = _rc;                     \
+    }                                                       \
+    if ((g)->m.size() > 1) NK(nccl_api()->GroupEnd());      \
+    if (_first) return _first;                              \
+  } while (0)
+
+int32_t h2ok_hist_group_create(const int32_t* device_ids, int32_t n_dev, h2ok_group** out) {
+  REQUIRE(device_ids && out, "null pointer");
+  REQUIRE(n_dev >= 1 && n_dev <= 64, "n_dev outside [1, 64]");
+  for (int i = 0; i < n_dev; i++)
+    for (int j = 0; j < i; j++) REQUIRE(device_ids[i] != device_ids[j], "a device appears twice");
+  h2ok_group* g = new h2ok_group();
+  int32_t rc = H2OK_OK;
+  for (int i = 0; i < n_dev && !rc; i++) {
+    h2ok_ctx* c = nullptr;
+    rc = h2ok_hist_create(device_ids[i], &c);
+    if (!rc) g->m.push_back(c);
   }
-  CK(cudaStreamSynchronize(c->stream));
-  for (int k = 0; k < 3; k++) out3[k] = h[k];
+  if (!rc && n_dev > 1) {
+    NcclApi* n = nccl_api();
+    if (!n) rc = fail(H2OK_ERR_UNSUPPORTED, "%s", "libnccl.so.2 could not be loaded");
+    else {
+      std::vector<ncclComm_t> comms(n_dev);
+      std::vector<int> devs(device_ids, device_ids + n_dev);
+      ncclResult_t r = n->CommInitAll(comms.data(), n_dev, devs.data());
+      if (r != ncclSuccess) rc = fail(H2OK_ERR_CUDA, "ncclCommInitAll: %s", n->GetErrorString(r));
+      else
+        for (int i = 0; i < n_dev; i++) {
+          g->m[i]->comm = comms[i];
+          g->m[i]->comm_rank = i;
+          g->m[i]->comm_ranks = n_dev;
+        }
+    }
+  }
+  if (rc) {
+    for (h2ok_ctx* c : g->m) h2ok_hist_destroy(c);
+    delete g;
+    return rc;
+  }
+  g->row0.assign(n_dev, 0);
+  *out = g;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_destroy(h2ok_group* g) {
+  if (!g) return H2OK_OK;
+  for (h2ok_ctx* c : g->m) h2ok_hist_destroy(c);
+  delete g;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_size(h2ok_group* g) { return g ? (int32_t)g->m.size() : 0; }
+
+int32_t h2ok_hist_group_member(h2ok_group* g, int32_t i, h2ok_ctx** out, int64_t* row0, int64_t* rows) {
+  REQUIRE(g && out, "null pointer");
+  REQUIRE(i >= 0 && i < (int32_t)g->m.size(), "member index out of range");
+  *out = g->m[i];
+  if (row0) *row0 = g->row0[i];
+  if (rows) *rows = g->m[i]->eng_ready ? g->m[i]->eng.rows : 0;
+  return H2OK_OK;
+}
+
+// contiguous row blocks: member i holds rows [i * R / n, (i + 1) * R / n) of every column
+int32_t h2ok_hist_group_load_synth(h2ok_group* g, int32_t shape, uint64_t seed, int64_t rows_total, int32_t cols,
+                                   int32_t na_permille) {
+  REQUIRE(g != nullptr, "null group");
+  const int64_t n = (int64_t)g->m.size();
+  REQUIRE(rows_total >= n && cols > 0, "fewer rows than devices");
+  g->rows_total = rows_total;
+  for (int64_t i = 0; i < n; i++) {
+    g->row0[i] = rows_total * i / n;
+    const int64_t rows = rows_total * (i + 1) / n - g->row0[i];
+    int32_t rc = h2ok_hist_tree_create(g->m[i], rows, cols, 0);
+    if (rc) return rc;
+  }
+  // every device generates its own rows; the members work at the same time (the calls below only enqueue)
+  for (int64_t i = 0; i < n; i++) {
+    int32_t rc = h2ok_hist_tree_load_synth(g->m[i], shape, seed, g->row0[i], na_permille);
+    if (rc) return rc;
+  }
+  return H2OK_OK;
+}
+
+// The caller's columns (host memory, all rows): every member copies its own row block.
+int32_t h2ok_hist_group_set_data_host(h2ok_group* g, const float* const* cols_host, int64_t rows_total, int32_t cols) {
+  REQUIRE(g && cols_host, "null pointer");
+  const int64_t n = (int64_t)g->m.size();
+  REQUIRE(rows_total >= n && cols > 0, "fewer rows than devices");
+  g->rows_total = rows_total;
+  std::vector<const float*> ptrs(cols);
+  for (int64_t i = 0; i < n; i++) {
+    g->row0[i] = rows_total * i / n;
+    const int64_t rows = rows_total * (i + 1) / n - g->row0[i];
+    for (int j = 0; j < cols; j++) ptrs[j] = cols_host[j] + g->row0[i];
+    int32_t rc = h2ok_hist_set_data_host(g->m[i], ptrs.data(), rows, cols);
+    if (rc) return rc;
+  }
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_loop_create(h2ok_group* g, const h2ok_params* params, const int32_t* is_int) {
+  REQUIRE(g && params, "null pointer");
+  EACH(g, loop_alloc(c, params, is_int));
+  EACH_NCCL(g, loop_reduce_ranges(c));
+  EACH(g, loop_make_root(c));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_set_options(h2ok_group* g, int32_t reduce_mode, int32_t checksum, int32_t time_phases) {
+  REQUIRE(g != nullptr, "null group");
+  EACH(g, h2ok_hist_loop_set_reduce(c, reduce_mode));
+  EACH(g, h2ok_hist_loop_set_options(c, checksum, time_phases));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_begin_tree_synth(h2ok_group* g, uint64_t seed, int32_t weight_mode) {
+  REQUIRE(g != nullptr, "null group");
+  for (size_t i = 0; i < g->m.size(); i++) {
+    h2ok_ctx* c = g->m[i];
+    int32_t rc = need_loop(c, "group_begin_tree_synth");
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    TreeLoop& L = *c->loop;
+    const size_t n = (size_t)c->eng.rows, pad = (n + 3) / 4 * 4;
+    CK(L.y.ensure(pad));
+    if (weight_mode) CK(L.w.ensure(pad));
+    CK(launch_synth(H2OK_SHAPE_HIGGS28, seed, g->row0[i], (int64_t)n, c->eng.cols, (int64_t)pad, 0, weight_mode, nullptr, L.y.p,
+                    weight_mode ? L.w.p : nullptr, c->stream));
+    if ((rc = begin_tree_local(c, L.y.p, weight_mode ? L.w.p : nullptr))) return rc;
+  }
+  EACH_NCCL(g, begin_tree_reduce(c));
+  EACH(g, begin_tree_finish(c));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_begin_tree_host(h2ok_group* g, const float* y_host, const float* w_host) {
+  REQUIRE(g && y_host, "null pointer");
+  for (size_t i = 0; i < g->m.size(); i++) {
+    h2ok_ctx* c = g->m[i];
+    int32_t rc = need_loop(c, "group_begin_tree_host");
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    TreeLoop& L = *c->loop;
+    const size_t n = (size_t)c->eng.rows, pad = (n + 3) / 4 * 4;
+    CK(L.y.ensure(pad));
+    CK(cudaMemcpyAsync(L.y.p, y_host + g->row0[i], sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+    if (w_host) {
+      CK(L.w.ensure(pad));
+      CK(cudaMemcpyAsync(L.w.p, w_host + g->row0[i], sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+    }
+    if ((rc = begin_tree_local(c, L.y.p, w_host ? L.w.p : nullptr))) return rc;
+  }
+  EACH_NCCL(g, begin_tree_reduce(c));
+  EACH(g, begin_tree_finish(c));
+  return H2OK_OK;
+}
+
+// One level on every member.  `out` is ONE set of host buffers: under H2OK_REDUCE_SCATTER every member writes the
+// (node, column) pairs it reduced into the same `hist`, so the buffer is complete on return and arrives over all the
+// devices' links at once; the replicated results (ranges, splits, children) are written by member 0.
+int32_t h2ok_hist_group_level(h2ok_group* g, const h2ok_level_out* out, int32_t* n_nodes_done, int32_t* n_children) {
+  REQUIRE(g != nullptr, "null group");
+  for (h2ok_ctx* c : g->m) {
+    int32_t rc = need_loop(c, "group_level");
+    if (rc) return rc;
+  }
+  h2ok_level_out rest{};  // members other than the first deliver their share of the histogram only
+  if (out) rest.hist = out->hist;
+  const bool all = g->m[0]->loop->reduce_mode == H2OK_REDUCE_ALL;
+  for (size_t i = 0; i < g->m.size(); i++) {
+    int32_t rc = level_local(g->m[i], i == 0 ? out : (out && !all ? &rest : nullptr));
+    if (rc) return rc;
+  }
+  EACH_NCCL(g, level_reduce(c));
+  EACH(g, level_search(c));
+  EACH_NCCL(g, level_gather(c));
+  EACH(g, level_finish(c));
+  int32_t done = 0, nch = 0;
+  for (size_t i = 0; i < g->m.size(); i++) {
+    int32_t d = 0, n = 0;
+    int32_t rc = level_wait(g->m[i], &d, &n);
+    if (rc) return rc;
+    if (i == 0) {
+      done = d;
+      nch = n;
+    } else if (d != done || n != nch) {
+      return fail(H2OK_ERR_STATE, "%s", "group_level: the members disagree on the level (not the same data set-up on every device?)");
+    }
+  }
+  if (n_nodes_done) *n_nodes_done = done;
+  if (n_children) *n_children = nch;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_checksum(h2ok_group* g, uint64_t* out3) {
+  REQUIRE(g && out3, "null pointer");
+  for (size_t i = 0; i < g->m.size(); i++) {
+    int32_t rc = need_loop(g->m[i], "group_checksum");
+    if (rc) return rc;
+    if ((rc = checksum_local(g->m[i], g->row0[i]))) return rc;
+  }
+  EACH_NCCL(g, checksum_reduce(c));
+  return checksum_fetch(g->m[0], out3);
+}
+
+// device milliseconds of the last level's histogram pass, the slowest member's
+int32_t h2ok_hist_group_hist_ms(h2ok_group* g, float* ms_out) {
+  REQUIRE(g && ms_out, "null pointer");
+  float worst = 0;
+  for (h2ok_ctx* c : g->m) {
+    h2ok_stats st;
+    int32_t rc = h2ok_hist_last_level_stats(c, &st);
+    if (rc) return rc;
+    worst = st.build_ms > worst ? st.build_ms : worst;
+  }
+  *ms_out = worst;
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_group_sync(h2ok_group* g) {
+  REQUIRE(g != nullptr, "null group");
+  EACH(g, h2ok_hist_sync(c));
   return H2OK_OK;
 }
 

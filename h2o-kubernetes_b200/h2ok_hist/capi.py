@@ -59,6 +59,20 @@ SIGNATURES = {
     "h2ok_hist_loop_view": [vp, pLV],
     "h2ok_hist_loop_phase_ms": [vp, vp],
     "h2ok_hist_loop_checksum": [vp, i64, vp],
+    "h2ok_hist_group_create": [vp, i32, C.POINTER(vp)],
+    "h2ok_hist_group_destroy": [vp],
+    "h2ok_hist_group_size": [vp],
+    "h2ok_hist_group_member": [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(i64)],
+    "h2ok_hist_group_load_synth": [vp, i32, u64, i64, i32, i32],
+    "h2ok_hist_group_set_data_host": [vp, C.POINTER(vp), i64, i32],
+    "h2ok_hist_group_loop_create": [vp, pP, vp],
+    "h2ok_hist_group_set_options": [vp, i32, i32, i32],
+    "h2ok_hist_group_begin_tree_synth": [vp, u64, i32],
+    "h2ok_hist_group_begin_tree_host": [vp, vp, vp],
+    "h2ok_hist_group_level": [vp, pLO, C.POINTER(i32), C.POINTER(i32)],
+    "h2ok_hist_group_checksum": [vp, vp],
+    "h2ok_hist_group_hist_ms": [vp, vp],
+    "h2ok_hist_group_sync": [vp],
     "h2ok_hist_gbm_residual_dev": [vp, i32, vp, vp, vp, i64, f64, vp, vp],
     "h2ok_hist_gbm_residual_multi_dev": [vp, i32, vp, vp, i64, vp, i64, f64, vp, vp],
     "h2ok_hist_gbm_gamma_pass_dev": [vp, vp, vp, vp, i64, i32, vp, vp],

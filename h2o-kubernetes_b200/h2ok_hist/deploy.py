@@ -4,11 +4,14 @@ reference renders (src/k8s/templates.rs:9-57 StatefulSet, :74-89 Service, placeh
 (ii) `--gpus G` adds `nvidia.com/gpu` limits/requests and a node selector so the pods land on a B200 node.
 
 No Kubernetes client, no cluster: this module only renders.  The reference's toolchain (cargo) is absent, so the
-corresponding Rust edit (a `gpus: Option<u32>` field with #[serde(default)] on both specification structs,
-src/cli/mod.rs:88-109 and src/k8s/mod.rs:58-80, and a `--gpus` clap arg next to `--cpus`, src/cli/mod.rs:207-212) is
-described in INTEGRATION.md rather than compiled.
+corresponding Rust edit (a `gpus` field with #[serde(default)] on both specification structs, src/cli/mod.rs:88-109 and
+src/k8s/mod.rs:58-80, a `--gpus` clap arg next to `--cpus`, src/cli/mod.rs:207-212, and two conditional blocks in
+src/k8s/templates.rs) is delivered as unverified source under reference_patch/; this module is the checked restatement
+of what that patch renders.  `h2ok bench` is the C++ binary tools/h2ok-bench (same flags); the `bench` sub-command
+here hands its arguments to it.
 """
 import argparse
+import os
 import re
 
 IMAGE, TAG = "h2oai/h2o-open-source-k8s", "latest"  # src/k8s/mod.rs:115-116
@@ -75,6 +78,13 @@ def _positive_int(s):  # cli/mod.rs:245-252
     return v
 
 
+def _not_negative_int(s):
+    v = int(s)
+    if v < 0:
+        raise argparse.ArgumentTypeError("must not be negative")
+    return v
+
+
 def _percentage(s):  # cli/mod.rs:259-266
     v = int(s)
     if not 1 <= v <= 100:
@@ -101,15 +111,44 @@ def build_parser():
     d.add_argument("--memory", "-m", type=_memory, default="1Gi")
     d.add_argument("--cpus", type=_positive_int, default=1)
     d.add_argument("--gpus", type=_positive_int, default=None, help="nvidia.com/gpu per pod (new)")
-    b = sub.add_parser("bench")
-    b.add_argument("--gpus", type=_positive_int, default=1)
-    b.add_argument("--workload", default="c3")
-    b.add_argument("--steps", type=_positive_int, default=16)
-    b.add_argument("--warmup", type=_positive_int, default=8)
+    b = sub.add_parser("bench")  # the flags of tools/h2ok_bench.cpp (and of reference_patch/src/cli/bench.rs)
+    b.add_argument("--shape", choices=["c2", "c3", "c4"], default="c3")
+    b.add_argument("--rows", "-r", type=_not_negative_int, default=0)
+    b.add_argument("--cols", type=_not_negative_int, default=0)
+    b.add_argument("--bins", "-b", type=_not_negative_int, default=0)
+    b.add_argument("--depth", "-d", type=_not_negative_int, default=0)
+    b.add_argument("--gpus", "-g", type=_positive_int, default=1)
+    b.add_argument("--trees", "-t", type=_positive_int, default=3)
+    b.add_argument("--seed", type=_not_negative_int, default=20261106)
     return ap
+
+
+BENCH_BINARY = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "h2ok-bench")
+
+
+def bench_argv(args):
+    """The command line `h2ok bench ...` stands for: the stand-alone binary with the same flags."""
+    return [BENCH_BINARY, "--shape", args.shape, "--rows", str(args.rows), "--cols", str(args.cols), "--bins", str(args.bins),
+            "--depth", str(args.depth), "--gpus", str(args.gpus), "--trees", str(args.trees), "--seed", str(args.seed)]
 
 
 def render(args):
     return [service(args.cluster_name, args.namespace),
             stateful_set(args.cluster_name, args.namespace, args.cluster_size, args.memory_percentage, args.memory,
                          args.cpus, args.gpus)]
+
+
+def main(argv=None):
+    """`deploy` prints the manifests it would send (YAML documents); `bench` runs tools/h2ok-bench."""
+    args = build_parser().parse_args(argv)
+    if args.command == "bench":
+        if not os.path.exists(BENCH_BINARY):
+            raise SystemExit(f"{BENCH_BINARY} is missing: build it with `make -C h2o-kubernetes_b200/csrc`")
+        os.execv(BENCH_BINARY, bench_argv(args))
+    import yaml
+
+    print(yaml.safe_dump_all(render(args), sort_keys=False), end="")
+
+
+if __name__ == "__main__":
+    main()

@@ -71,6 +71,7 @@ extern "C" {
 #define H2OK_SHAPE_SPARSE 4  /* config 4: 90 % exact zeros, else u */
 
 typedef struct h2ok_ctx h2ok_ctx;
+typedef struct h2ok_group h2ok_group; /* several devices driven by one host thread (h2ok_hist_group_*) */
 
 /* a1 — one DHistogram's constructor fields for one (node, column).  nbin == 0 means the column is
  * not tracked for this node (constant / all-NA there) and contributes nothing. */
@@ -347,6 +348,35 @@ int32_t h2ok_hist_loop_phase_ms(h2ok_ctx* ctx, float* ms_out /*[4]*/);
  * sum(splitmix64(global index ^ salt) * value) mod 2^64 (tests/oracle_lib.py has the host restatement).  row0 = global
  * index of this rank's first row.  Collective when n_ranks > 1. */
 int32_t h2ok_hist_loop_checksum(h2ok_ctx* ctx, int64_t row0, uint64_t* out /*[3]*/);
+
+/* ---- a group of devices behind one host thread -------------------------------------------------------------------
+ * What a caller shaped like the reference needs to use all GPUs of a node: `h2ok` is single-threaded and blocking
+ * (src/main.rs:18-37; one Runtime + block_on per operation, src/k8s/mod.rs:85-93), so the library drives the devices.
+ * A group owns one context per device and one NCCL communicator over them (ncclCommInitAll); rows are sharded in
+ * contiguous blocks, member i holding rows [i*R/n, (i+1)*R/n).  Every call is the per-context call of the same name run
+ * on all members, the NCCL phases grouped.  Results are the single-device results, bit for bit. */
+int32_t h2ok_hist_group_create(const int32_t* device_ids, int32_t n_dev, h2ok_group** out);
+int32_t h2ok_hist_group_destroy(h2ok_group* group);
+int32_t h2ok_hist_group_size(h2ok_group* group); /* number of members (not a status code) */
+/* Member i's context (for the per-context calls: tree_create + tree_load_cols_dev with caller-made device blocks,
+ * loop_view, copy_to_host, last_level_stats ...), the global index of its first row and its row count. */
+int32_t h2ok_hist_group_member(h2ok_group* group, int32_t i, h2ok_ctx** ctx_out, int64_t* row0_out, int64_t* rows_out);
+/* Data: the generator's rows_total x cols matrix, every member its own block / the caller's host columns (all rows). */
+int32_t h2ok_hist_group_load_synth(h2ok_group* group, int32_t shape, uint64_t seed, int64_t rows_total, int32_t cols,
+                                   int32_t na_permille);
+int32_t h2ok_hist_group_set_data_host(h2ok_group* group, const float* const* cols_host, int64_t rows_total, int32_t cols);
+int32_t h2ok_hist_group_loop_create(h2ok_group* group, const h2ok_params* params, const int32_t* is_int);
+int32_t h2ok_hist_group_set_options(h2ok_group* group, int32_t reduce_mode, int32_t checksum, int32_t time_phases);
+int32_t h2ok_hist_group_begin_tree_synth(h2ok_group* group, uint64_t seed, int32_t weight_mode);
+/* y_host / w_host: all rows_total targets in original row order (w_host NULL: unweighted) */
+int32_t h2ok_hist_group_begin_tree_host(h2ok_group* group, const float* y_host, const float* w_host);
+/* One level on every member.  `out` is ONE set of host buffers: under H2OK_REDUCE_SCATTER each member writes the
+ * (node, column) pairs it reduced into the same `hist`, which is therefore complete on return and travels over all the
+ * devices' links at once; ranges, splits and children are written by member 0. */
+int32_t h2ok_hist_group_level(h2ok_group* group, const h2ok_level_out* out, int32_t* n_nodes_done, int32_t* n_children);
+int32_t h2ok_hist_group_checksum(h2ok_group* group, uint64_t* out /*[3]*/);
+int32_t h2ok_hist_group_hist_ms(h2ok_group* group, float* ms_out); /* last level's histogram pass, slowest member */
+int32_t h2ok_hist_group_sync(h2ok_group* group);
 
 /* ---- a9: the tree-level caller (GBM.buildNextKTrees) ---------------------------------------------------------
  * ComputePredAndRes: d_res[r] = label - mu(f) (gaussian mu = f, bernoulli mu = 1/(1+exp(-f))), and, when d_denq is
