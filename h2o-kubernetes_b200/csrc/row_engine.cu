@@ -485,6 +485,312 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
   }
 }
 
+// ------------------------------------------------------------------------------------------------ sparse storage
+// For matrices that are mostly exact zeros (BASELINE config 4: 90 % zeros; H2O itself keeps such columns in sparse
+// chunks, CXIChunk / CX0Chunk) the shard can be stored as one 64-byte slot per (row, block of 64 columns) holding the
+// block's NONZERO cells only: byte 0 = their number, bytes 1..12 = their columns inside the block, words 4..15 = their
+// values (a NaN is a nonzero).  A (row, block) with more than 12 nonzeros (1.3 % at 10 % density) says 0xFF and points
+// (word 4) at a dense 64-float row in an overflow store.  256 B of dense floats become 64 B.
+//
+// The histogram pass then touches only the nonzeros: a warp flattens the nonzero cells of four rows into a work list
+// and every lane takes one (column, value) pair, so a warp instruction updates ~26 cells instead of the ~3 nonzero
+// lanes of the one-column-per-lane layout.  A lane no longer owns its columns, so descriptors come from a shared
+// table, the histogram is [copy][column][bin][channel] with the copy chosen by lane, and observed ranges go through a
+// shared table (compare first, atomic only on improvement).  The zeros are accounted for exactly at the flush: the
+// node's totals over the CTA's rows minus what its nonzeros added is what the zero cells contribute, and it goes to
+// the bin 0.0 falls into; a column with a zero row has 0.0 inside its observed range.  Integer sums make this exact.
+constexpr int kSpCols = 64, kSpInline = 12, kSpRows = 4;
+struct SpSlot {
+  unsigned w[16];
+};
+
+__global__ void __launch_bounds__(256) eng_load_sparse_kernel(const float* __restrict__ X, int64_t ld, int64_t rows, int ncols,
+                                                              SpSlot* __restrict__ slots, int nblk, int blk,
+                                                              float* __restrict__ ovf, unsigned* __restrict__ ovf_count,
+                                                              unsigned ovf_cap, int32_t* __restrict__ err) {
+  __shared__ unsigned s[256][17];
+  const int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (r >= rows) return;
+  unsigned* w = s[threadIdx.x];
+#pragma unroll
+  for (int i = 0; i < 16; i++) w[i] = 0u;
+  int cnt = 0;
+  for (int c = 0; c < ncols; c++) {
+    const float x = X[(int64_t)c * ld + r];
+    if (!(x == 0.0f)) {  // NaN counts as a nonzero; -0.0 as a zero
+      if (cnt < kSpInline) {
+        w[(1 + cnt) >> 2] |= (unsigned)c << (8 * ((1 + cnt) & 3));
+        w[4 + cnt] = __float_as_uint(x);
+      }
+      cnt++;
+    }
+  }
+  if (cnt <= kSpInline) {
+    w[0] |= (unsigned)cnt;
+  } else {
+    const unsigned idx = atomicAdd(ovf_count, 1u);
+    if (idx < ovf_cap) {
+      for (int c = 0; c < kSpCols; c++) ovf[(int64_t)idx * kSpCols + c] = c < ncols ? X[(int64_t)c * ld + r] : 0.0f;
+      w[0] = 0xFFu;
+      w[4] = idx;
+    } else {
+      *err = 1;  // denser than the overflow store was sized for: the caller must use dense storage
+      w[0] = 0u;
+    }
+  }
+  unsigned* out = slots[r * nblk + blk].w;
+#pragma unroll
+  for (int i = 0; i < 16; i += 4) *reinterpret_cast<uint4*>(out + i) = make_uint4(w[i], w[i + 1], w[i + 2], w[i + 3]);
+}
+
+// one cell of the sparse shard (routing's exact comparison on a code tie)
+__device__ __forceinline__ float sp_get(const SpSlot* __restrict__ slots, int nblk, const float* __restrict__ ovf, int64_t r,
+                                        int col) {
+  const unsigned* w = slots[r * nblk + (col >> 6)].w;
+  const int c = col & 63;
+  const unsigned w0 = w[0], cnt = w0 & 0xFFu;
+  if (cnt == 0xFFu) return ovf[(int64_t)w[4] * kSpCols + c];
+  for (unsigned p = 0; p < cnt; p++) {
+    const unsigned byte = (w[(1 + p) >> 2] >> (8 * ((1 + p) & 3))) & 0xFFu;
+    if ((int)byte == c) return __uint_as_float(w[4 + p]);
+  }
+  return 0.0f;
+}
+
+struct SpHistArgs {
+  const SpSlot* slots;
+  int nblk;
+  const float* ovf;
+  int cols;
+  const int32_t* gidx;
+  const uint2* gval;
+  const int32_t* mnode;
+  const int32_t* seg;
+  int n_nodes;
+  const h2ok_col_desc* descs;
+  int nb1, nbs, copies;
+  int64_t* acc;
+  uint32_t* min2_enc;
+  uint32_t* maxin_enc;
+  int32_t* err;
+};
+
+__global__ void __launch_bounds__(1024, 1) eng_hist_sparse_kernel(const __grid_constant__ SpHistArgs a) {
+  constexpr int THREADS = 1024, NW = THREADS / 32;
+  extern __shared__ __align__(16) unsigned h[];  // [copy][column][bin][channel]
+  __shared__ double s_mn[kSpCols], s_st[kSpCols];
+  __shared__ int s_nb[kSpCols];
+  __shared__ unsigned s_rmin[kSpCols], s_rmax[kSpCols];
+  __shared__ unsigned char s_tracked[kSpCols];
+  __shared__ unsigned long long s_tot[3];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nb1 = a.nb1, nbs = a.nbs, copies = a.copies;
+  const int col0 = (int)blockIdx.y * kSpCols;
+  const int n_nodes = min(a.n_nodes, a.seg[kSegNodes]);
+  if (n_nodes < 1) return;
+  const int64_t live = a.seg[n_nodes];
+  int p0 = (int)(live * (int64_t)blockIdx.x / gridDim.x);
+  const int p1 = (int)(live * (int64_t)(blockIdx.x + 1) / gridDim.x);
+  if (p0 >= p1) return;
+  int node = seg_of(a.seg, n_nodes, p0);
+  const int words = copies * kSpCols * nbs * 3;
+  for (int i = tid; i < words; i += THREADS) h[i] = (i % 3 == 0) ? 0u : kWyBias;
+  const unsigned hbase = (unsigned)__cvta_generic_to_shared(h) + (unsigned)((lane & (copies - 1)) * kSpCols * nbs) * 12u;
+  const int32_t* __restrict__ gidx = a.gidx;
+  const uint2* __restrict__ gval = a.gval;
+  const char* sbase = reinterpret_cast<const char*>(a.slots) + (size_t)blockIdx.y * sizeof(SpSlot);
+  const unsigned pitch = (unsigned)a.nblk * (unsigned)sizeof(SpSlot);
+
+  while (p0 < p1) {
+    const int nend = a.seg[node + 1];
+    const int send = nend < p1 ? nend : p1;
+    if (send <= p0) {
+      node++;
+      continue;
+    }
+    if (tid < kSpCols) {
+      const int col = col0 + tid;
+      bool tracked = false;
+      double mn = 0.0, st = 0.0;
+      int nb = 1;
+      if (col < a.cols) {
+        const h2ok_col_desc d = a.descs[(int64_t)node * a.cols + col];
+        if (d.nbin >= nbs) atomicAdd(a.err, 1);
+        else if (d.nbin > 0) {
+          tracked = true;
+          mn = d.min;
+          st = d.step;
+          nb = d.nbin;
+        }
+      }
+      s_mn[tid] = mn;
+      s_st[tid] = st;
+      s_nb[tid] = nb;
+      s_rmin[tid] = kEncPosInf;
+      s_rmax[tid] = kEncNegInf;
+      s_tracked[tid] = tracked ? 1 : 0;
+    }
+    if (tid < 3) s_tot[tid] = 0ull;
+    __syncthreads();
+
+    // one (column, value) pair of row slot j: bin from the shared descriptor table, three shared atomics, range
+    auto item = [&](bool active, int col, float x, int v1, int v2) {
+      if (!active) return;
+      const int b = bin_fast(x, s_mn[col], s_st[col], s_nb[col]);
+      const unsigned addr = hbase + (unsigned)((col * nbs + b) * 12);
+      sh_inc(addr);
+      const unsigned o1 = sh_add(addr + 4u, (unsigned)v1), o2 = sh_add(addr + 8u, (unsigned)v2);
+      const unsigned f1 = wrap_bit(o1, v1), f2 = wrap_bit(o2, v2);
+      if ((f1 | f2) >> 31)
+        eng_carry(a.acc, a.descs, node, a.cols, col0 + col, nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
+                  (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
+      if (x == x) {
+        const unsigned e = enc_f32_bits(__float_as_uint(x));
+        if (e < s_rmin[col]) atomicMin(&s_rmin[col], e);
+        if (e > s_rmax[col]) atomicMax(&s_rmax[col], e);
+      }
+    };
+
+    unsigned tc = 0;            // this warp's rows of the run and their (centred) target sums: what the zeros are
+    long long t1 = 0, t2 = 0;   // worked out from at the flush
+    for (int p = p0 + warp * kSpRows; p < send; p += NW * kSpRows) {
+      const int nr = send - p < kSpRows ? send - p : kSpRows;
+      int v1[kSpRows], v2[kSpRows];
+      unsigned ridx[kSpRows];
+#pragma unroll
+      for (int j = 0; j < kSpRows; j++) {
+        const int q = j < nr ? p + j : p;
+        ridx[j] = (unsigned)__ldg(gidx + q);
+        const uint2 r = __ldg(gval + q);
+        v1[j] = (int)r.x;
+        v2[j] = (int)r.y;
+        if (j < nr) {
+          tc += 1u;
+          t1 += (int)r.x;
+          t2 += (int)r.y;
+        }
+      }
+      // rows 0/1 in the two halves of regA, rows 2/3 in regB: one 64-byte slot per half warp
+      const int half = lane >> 4, word = lane & 15;
+      const unsigned regA = __ldg(reinterpret_cast<const unsigned*>(row_addr(sbase, half ? ridx[1] : ridx[0], pitch)) + word);
+      const unsigned regB = __ldg(reinterpret_cast<const unsigned*>(row_addr(sbase, half ? ridx[3] : ridx[2], pitch)) + word);
+      unsigned cnt[kSpRows];
+      cnt[0] = __shfl_sync(0xffffffffu, regA, 0) & 0xFFu;
+      cnt[1] = __shfl_sync(0xffffffffu, regA, 16) & 0xFFu;
+      cnt[2] = __shfl_sync(0xffffffffu, regB, 0) & 0xFFu;
+      cnt[3] = __shfl_sync(0xffffffffu, regB, 16) & 0xFFu;
+      unsigned dense_mask = 0;
+#pragma unroll
+      for (int j = 0; j < kSpRows; j++) {
+        if (j >= nr) cnt[j] = 0;
+        if (cnt[j] == 0xFFu) {
+          dense_mask |= 1u << j;
+          cnt[j] = 0;
+        }
+      }
+      const int P1 = (int)cnt[0], P2 = P1 + (int)cnt[1], P3 = P2 + (int)cnt[2], T = P3 + (int)cnt[3];
+      for (int base = 0; base < T; base += 32) {
+        const int i = base + lane;
+        const int j = (i >= P1) + (i >= P2) + (i >= P3);
+        const int pp = i - (j == 0 ? 0 : (j == 1 ? P1 : (j == 2 ? P2 : P3)));
+        const int src = (j & 1) << 4;
+        const int hw = (1 + pp) >> 2;
+        const unsigned cwA = __shfl_sync(0xffffffffu, regA, (src + hw) & 31), cwB = __shfl_sync(0xffffffffu, regB, (src + hw) & 31);
+        const unsigned vA = __shfl_sync(0xffffffffu, regA, (src + 4 + pp) & 31), vB = __shfl_sync(0xffffffffu, regB, (src + 4 + pp) & 31);
+        const unsigned cw = (j >> 1) ? cwB : cwA;
+        const int col = (int)((cw >> (8 * ((1 + pp) & 3))) & 0xFFu) & 63;
+        const float x = __uint_as_float((j >> 1) ? vB : vA);
+        const int a1 = j == 0 ? v1[0] : (j == 1 ? v1[1] : (j == 2 ? v1[2] : v1[3]));
+        const int a2 = j == 0 ? v2[0] : (j == 1 ? v2[1] : (j == 2 ? v2[2] : v2[3]));
+        item(i < T, col, x, a1, a2);
+      }
+      if (dense_mask) {  // rows with more nonzeros than a slot holds: their dense 64-float row, two columns per lane
+#pragma unroll
+        for (int j = 0; j < kSpRows; j++) {
+          if (!((dense_mask >> j) & 1u)) continue;
+          const unsigned idx = __shfl_sync(0xffffffffu, (j >> 1) ? regB : regA, ((j & 1) << 4) + 4);
+          const float* row = a.ovf + (int64_t)idx * kSpCols;
+          const float x0 = __ldg(row + lane), x1 = __ldg(row + 32 + lane);
+          item(!(x0 == 0.0f), lane, x0, v1[j], v2[j]);
+          item(!(x1 == 0.0f), 32 + lane, x1, v1[j], v2[j]);
+        }
+      }
+    }
+    if (lane == 0 && tc) {
+      atomicAdd(&s_tot[0], (unsigned long long)tc);
+      atomicAdd(&s_tot[1], (unsigned long long)t1);
+      atomicAdd(&s_tot[2], (unsigned long long)t2);
+    }
+    __syncthreads();
+
+    // flush.  First per column (one warp each): what the nonzeros added, hence what the zero cells contribute.
+    const int m1 = a.mnode[2 * node], m2 = a.mnode[2 * node + 1];
+    for (int c = warp; c < kSpCols; c += NW) {
+      if (!s_tracked[c]) continue;  // warp-uniform
+      unsigned long long nc = 0;
+      long long n1 = 0, n2 = 0;
+      for (int i = lane; i < nbs * copies; i += 32) {
+        const int cp = i / nbs, b = i - cp * nbs;
+        const unsigned* w = h + ((cp * kSpCols + c) * nbs + b) * 3;
+        nc += w[0];
+        n1 += (long long)w[1] - (long long)kWyBias;
+        n2 += (long long)w[2] - (long long)kWyBias;
+      }
+      for (int o = 16; o; o >>= 1) {
+        nc += __shfl_xor_sync(0xffffffffu, nc, o);
+        n1 += __shfl_xor_sync(0xffffffffu, n1, o);
+        n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+      }
+      if (lane == 0) {
+        const int col = col0 + c;
+        const long long zc = (long long)s_tot[0] - (long long)nc;
+        const long long z1 = (long long)s_tot[1] - n1 + zc * m1, z2 = (long long)s_tot[2] - n2 + zc * m2;
+        if (zc > 0) {
+          const int bz = bin_of(0.0f, s_mn[c], s_st[c], s_nb[c]);
+          unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col) * nb1 + bz) * 3;
+          atomicAdd(g, (unsigned long long)zc);
+          if (z1) atomicAdd(g + 1, (unsigned long long)z1);
+          if (z2) atomicAdd(g + 2, (unsigned long long)z2);
+          const unsigned ez = enc_f32_bits(__float_as_uint(0.0f));
+          if (ez < s_rmin[c]) s_rmin[c] = ez;  // only this lane touches the column's slots now
+          if (ez > s_rmax[c]) s_rmax[c] = ez;
+        }
+        if (s_rmin[c] != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)node * a.cols + col], s_rmin[c]);
+        if (s_rmax[c] != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)node * a.cols + col], s_rmax[c]);
+      }
+    }
+    __syncthreads();
+    // then every (column, bin): copies added up, centring undone with the bin's own count, words re-armed
+    for (int t = tid; t < kSpCols * nbs; t += THREADS) {
+      const int c = t / nbs, b = t - c * nbs;
+      unsigned long long nc = 0;
+      long long n1 = 0, n2 = 0;
+      for (int cp = 0; cp < copies; cp++) {
+        unsigned* w = h + ((cp * kSpCols + c) * nbs + b) * 3;
+        const unsigned c0 = w[0], u1 = w[1], u2 = w[2];
+        if (c0 | (u1 ^ kWyBias) | (u2 ^ kWyBias)) {
+          nc += c0;
+          n1 += (long long)u1 - (long long)kWyBias;
+          n2 += (long long)u2 - (long long)kWyBias;
+          w[0] = 0u;
+          w[1] = kWyBias;
+          w[2] = kWyBias;
+        }
+      }
+      if (s_tracked[c] && (nc | (unsigned long long)n1 | (unsigned long long)n2)) {
+        unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col0 + c) * nb1 + b) * 3;
+        const long long s1 = n1 + (long long)nc * m1, s2 = n2 + (long long)nc * m2;
+        if (nc) atomicAdd(g, nc);
+        if (s1) atomicAdd(g + 1, (unsigned long long)s1);
+        if (s2) atomicAdd(g + 2, (unsigned long long)s2);
+      }
+    }
+    __syncthreads();
+    p0 = send;
+    node++;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ a6 + regroup
 // Routing walks the rows in their ORIGINAL order (row -> node map nid16), not the node-grouped records: every access
 // is then a stream.  The value the split needs is not gathered from the row-major copy — a gather of one float per
@@ -616,7 +922,8 @@ __device__ __forceinline__ int64_t route_per(int64_t rows, int G) {
 }
 
 __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
-    const float* __restrict__ XT, int64_t ldt, const uint8_t* __restrict__ code8, int64_t ld8,
+    const float* __restrict__ XT, int64_t ldt, const SpSlot* __restrict__ slots, int nblk, const float* __restrict__ ovf,
+    const uint8_t* __restrict__ code8, int64_t ld8,
     const unsigned* __restrict__ thr, int64_t rows, int n_nodes, const h2ok_split* __restrict__ splits,
     const int32_t* __restrict__ child_ids, int gid_base, uint16_t* __restrict__ nid16, int32_t* __restrict__ leaf,
     int32_t* __restrict__ cta_cnt, int n_slots) {
@@ -658,7 +965,7 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
           if (c == 255u) way = (t.na == H2OK_NA_LEFT) ? 0 : 1;
           else if (t.na == H2OK_NA_VS_REST) way = 0;
           else if (c != t.cs) way = c > t.cs ? 1 : 0;
-          else way = XT[r * ldt + t.col] >= t.splat ? 1 : 0;  // same code as the threshold: the float decides
+          else way = (XT ? XT[r * ldt + t.col] : sp_get(slots, nblk, ovf, r, t.col)) >= t.splat ? 1 : 0;  // code tie: the float decides
           const int ch = way ? t.c1 : t.c0;
           if (ch < 0) leaf[r] = t.leaf0 + 1 + way;
           else next = (unsigned)ch;
@@ -862,8 +1169,10 @@ __global__ void eng_nid_kernel(const uint16_t* __restrict__ nid16, int64_t rows,
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ host side
-cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
+cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool sparse) {
   engine_free(e);
+  if (sparse && weighted) return cudaErrorInvalidValue;
+  e.sparse = sparse;
   if (rows >= (1ll << 31) - 4096) return cudaErrorInvalidValue;
   if (cols > 32767) return cudaErrorInvalidValue;  // the routing table keeps the split column in 16 bits
   e.rows = rows;
@@ -880,7 +1189,18 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   auto A = [&](void** p, size_t bytes) {
     if (err == cudaSuccess) err = cudaMalloc(p, bytes);
   };
-  A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  if (sparse) {
+    e.nblk = (cols + kSpCols - 1) / kSpCols;
+    // dense rows for the (row, block) pairs with more nonzeros than a slot holds: room for one pair in sixteen
+    const size_t cap = (size_t)rows * (size_t)e.nblk / 16 + 4096;
+    e.ovf_cap = cap > 0xFFFFFF00ull ? 0xFFFFFF00u : (unsigned)cap;
+    A(&e.slots, sizeof(SpSlot) * (size_t)rows * (size_t)e.nblk);
+    A((void**)&e.ovf, sizeof(float) * kSpCols * (size_t)e.ovf_cap);
+    A((void**)&e.ovf_count, sizeof(unsigned));
+    if (err == cudaSuccess) err = cudaMemset(e.ovf_count, 0, sizeof(unsigned));
+  } else {
+    A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  }
   A((void**)&e.code8, (size_t)cols * (size_t)e.ld8);
   A((void**)&e.thr, sizeof(uint32_t) * 256 * (size_t)cols);
   A((void**)&e.cmin, sizeof(uint32_t) * (size_t)cols);
@@ -897,17 +1217,26 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted) {
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
   A((void**)&e.err, sizeof(int32_t));
   A((void**)&e.na_flag, sizeof(int32_t));
+  A((void**)&e.load_err, sizeof(int32_t));
+  if (err == cudaSuccess) err = cudaMemset(e.load_err, 0, sizeof(int32_t));
+  e.load_checked = false;
   if (err == cudaSuccess) err = cudaMemset(e.err, 0, sizeof(int32_t));
   if (err == cudaSuccess) err = cudaMemset(e.na_flag, 0, sizeof(int32_t));
   e.na_known = false;
   e.has_na = true;
-  if (err == cudaSuccess && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  if (err == cudaSuccess && !sparse && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   if (err != cudaSuccess) engine_free(e);
   return err;
 }
 
 void engine_free(Engine& e) {
   cudaFree(e.XT); cudaFree(e.code8); cudaFree(e.thr); cudaFree(e.cmin); cudaFree(e.cmax);
+  cudaFree(e.slots); cudaFree(e.ovf); cudaFree(e.ovf_count);
+  e.slots = nullptr;
+  e.ovf = nullptr;
+  e.ovf_count = nullptr;
+  e.sparse = false;
+  e.nblk = 0;
   e.cmin = e.cmax = nullptr;
   for (int k = 0; k < 2; k++) {
     cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]); cudaFree(e.mnode[k]);
@@ -915,6 +1244,8 @@ void engine_free(Engine& e) {
   }
   cudaFree(e.nid16); cudaFree(e.cta_cnt); cudaFree(e.leaf); cudaFree(e.err); cudaFree(e.na_flag);
   e.na_flag = nullptr;
+  cudaFree(e.load_err);
+  e.load_err = nullptr;
   e.XT = nullptr;
   e.code8 = nullptr;
   e.thr = nullptr;
@@ -939,8 +1270,19 @@ cudaError_t engine_set_weighted(Engine& e, bool weighted) {
 }
 
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s) {
-  dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
-  eng_load_kernel<<<grid, 256, 0, s>>>(X, ld, e.rows, col0, ncols, e.XT, e.ldt);
+  if (e.sparse) {
+    if (col0 % kSpCols) return cudaErrorInvalidValue;  // column blocks arrive whole (the last one may be short)
+    for (int c = 0; c < ncols; c += kSpCols) {
+      const int nc = ncols - c < kSpCols ? ncols - c : kSpCols;
+      eng_load_sparse_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(X + (int64_t)c * ld, ld, e.rows, nc, static_cast<SpSlot*>(e.slots),
+                                                               e.nblk, (col0 + c) / kSpCols, e.ovf, e.ovf_count, e.ovf_cap,
+                                                               e.load_err);
+    }
+    e.load_checked = false;
+  } else {
+    dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
+    eng_load_kernel<<<grid, 256, 0, s>>>(X, ld, e.rows, col0, ncols, e.XT, e.ldt);
+  }
   // the routing codes of the same columns: thresholds from a sorted sample, then one byte per cell
   eng_thresholds_kernel<<<ncols, 1024, 0, s>>>(X, ld, e.rows, e.thr + (int64_t)col0 * 256);
   dim3 cgrid(nblk(e.rows, 1024), (unsigned)ncols);
@@ -1004,6 +1346,40 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
                                uint32_t* min2_enc, uint32_t* maxin_enc, cudaStream_t s) {
   if (n_nodes < 1 || n_nodes >= kEngMaxNodes) return cudaErrorInvalidValue;
   const int nbs = level_nb1 > 0 && level_nb1 < nb1 ? level_nb1 : nb1;
+  if (e.sparse) {
+    if ((size_t)kSpCols * nbs * 12 > (size_t)kHistSmemCap) return cudaErrorInvalidValue;
+    e.n_nodes = n_nodes;
+    SpHistArgs a{};
+    a.slots = static_cast<const SpSlot*>(e.slots);
+    a.nblk = e.nblk;
+    a.ovf = e.ovf;
+    a.cols = e.cols;
+    a.gidx = e.gidx[e.cur];
+    a.gval = e.gval[e.cur];
+    a.mnode = e.mnode[e.cur];
+    a.seg = e.seg[e.cur];
+    a.n_nodes = n_nodes;
+    a.descs = descs;
+    a.nb1 = nb1;
+    a.nbs = nbs;
+    a.copies = 1;
+    while (a.copies < 4 && (size_t)kSpCols * nbs * 12 * (a.copies * 2) <= (size_t)kHistSmemCap) a.copies *= 2;
+    a.acc = acc;
+    a.min2_enc = min2_enc;
+    a.maxin_enc = maxin_enc;
+    a.err = e.err;
+    static std::atomic<bool> attr_done[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
+      cudaError_t ea = cudaFuncSetAttribute(eng_hist_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+      if (ea != cudaSuccess) return ea;
+      attr_done[dev & 63].store(true, std::memory_order_release);
+    }
+    const dim3 grid((unsigned)e.sms, (unsigned)e.nblk);
+    eng_hist_sparse_kernel<<<grid, 1024, (size_t)a.copies * kSpCols * nbs * 12, s>>>(a);
+    return cudaGetLastError();
+  }
   const EngLayout lay = eng_layout(e.cols, nbs);
   if (!lay.cpl) return cudaErrorInvalidValue;
   e.n_nodes = n_nodes;
@@ -1060,7 +1436,8 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   const int G = e.route_ctas;
   const int n_slots = 2 * n_nodes < kEngMaxNodes ? 2 * n_nodes : kEngMaxNodes;  // child ids are < this
   const size_t rsmem = (size_t)n_nodes * sizeof(RouteNode) + (size_t)n_slots * sizeof(int);
-  eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, e.code8, e.ld8, e.thr, e.rows, n_nodes, splits, child_ids,
+  eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, static_cast<const SpSlot*>(e.slots), e.nblk, e.ovf, e.code8, e.ld8,
+                                                   e.thr, e.rows, n_nodes, splits, child_ids,
                                                    gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots);
   // every level but a tree's last: lay the children's records out for the next histogram pass
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.cta_cnt, G, n_nodes, child_ids, e.seg[nx], splits, e.scale_wy, e.scale_wyy,
@@ -1092,6 +1469,21 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   if (err != cudaSuccess) return err;
   e.cur = nx;
   e.n_nodes = 0;  // the caller says how many children there are (build_level / nid)
+  return cudaSuccess;
+}
+
+cudaError_t engine_check_load(Engine& e, cudaStream_t s, bool* too_dense) {
+  *too_dense = false;
+  if (!e.sparse) return cudaSuccess;
+  if (!e.load_checked) {
+    int flag = 0;
+    cudaError_t err = cudaMemcpyAsync(&flag, e.load_err, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+    if (err != cudaSuccess) return err;
+    e.load_failed = flag != 0;
+    e.load_checked = true;
+  }
+  *too_dense = e.load_failed;
   return cudaSuccess;
 }
 

@@ -204,9 +204,15 @@ class EngineShard(CudaShard):
 
     stage_bytes = 2 << 30
 
+    def __init__(self, device=0, max_level_nodes=128, sparse=False):
+        """sparse: keep only the nonzero cells (H2OK_TREE_SPARSE) — for matrices that are mostly exact zeros."""
+        super().__init__(device, max_level_nodes)
+        self.sparse = sparse
+
     def _alloc_rows(self, rows, cols, weighted):
         self.rows, self.cols = rows, cols
-        self.lib.call("h2ok_hist_tree_create", self.ctx, rows, cols, 1 if weighted else 0)
+        flags = (abi.TREE_WEIGHTED if weighted else 0) | (abi.TREE_SPARSE if self.sparse else 0)
+        self.lib.call("h2ok_hist_tree_create", self.ctx, rows, cols, flags)
         n = (rows + 63) // 64 * 64
         self.ld = n
         dev = self.device
@@ -225,6 +231,8 @@ class EngineShard(CudaShard):
     def _blocks(self):
         """Column blocks whose column-major staging copy stays under stage_bytes."""
         per = max(1, min(self.cols, self.stage_bytes // (4 * self.ld)))
+        if self.sparse:
+            per = max(64, per // 64 * 64)  # sparse storage takes whole blocks of 64 columns
         return [(c0, min(per, self.cols - c0)) for c0 in range(0, self.cols, per)]
 
     def _load_block(self, stage, c0, nc):

@@ -65,6 +65,10 @@ extern "C" {
 #define H2OK_REDUCE_ALL 1     /* plain all-reduce: every rank holds the whole reduced histogram */
 #define H2OK_COMM_ID_BYTES 128 /* size of the rendezvous id of h2ok_hist_comm_unique_id (an ncclUniqueId) */
 
+/* Flags of h2ok_hist_tree_create. */
+#define H2OK_TREE_WEIGHTED 1 /* trees with per-row weights (8 more bytes per row) */
+#define H2OK_TREE_SPARSE 2   /* store only the nonzero cells: for matrices that are mostly exact zeros (see below) */
+
 /* Synthetic shapes of SURVEY.md §8(d). */
 #define H2OK_SHAPE_HIGGS28 2 /* config 2: 28 HIGGS-shaped columns */
 #define H2OK_SHAPE_WIDE64 3  /* config 3: the 28-column recipe tiled to any width with affine offsets */
@@ -267,8 +271,16 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
  * block can be freed or reused afterwards) -> per tree: tree_begin_dev -> per level: tree_build_level_dev, [reduce /
  * finalize / find_splits / next_level as usual], tree_apply_splits_dev.  Device memory: rows * (4 * cols rounded up
  * to 8 + cols + 30) bytes, + 8 per row for weighted shards.  Limits: rows < 2^31 - 4096, cols < 32768; every bin count up to
- * H2OK_MAX_BINS runs (64 columns per block up to 299 bins + NA, 32 up to 599, 16 beyond). */
-int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t weighted);
+ * H2OK_MAX_BINS runs (64 columns per block up to 299 bins + NA, 32 up to 599, 16 beyond).
+ *
+ * H2OK_TREE_SPARSE (an input format beyond dense fp32; H2O keeps mostly-zero columns in sparse
+ * chunks too): the shard is stored as one 64-byte slot per (row, block of 64 columns) with the block's nonzero cells —
+ * up to 12 inline, denser (row, block) pairs in an overflow store sized for one pair in sixteen — instead of 256 bytes
+ * of floats, and the histogram pass touches the nonzeros only; what the zero cells contribute follows exactly from the
+ * node totals at the flush.  Same results bit for bit.  Unweighted trees, at most 299 bins + NA, column blocks loaded
+ * in multiples of 64 columns; a matrix too dense for the overflow store makes the first level fail (H2OK_ERR_UNSUPPORTED).
+ * Algorithmic bytes per level: nnz * 5 + rows * blocks * 4 (values, column bytes, counts) + rows * 8 + histogram. */
+int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t flags /*H2OK_TREE_**/);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
 /* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in
  * original order */
