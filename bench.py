@@ -35,15 +35,24 @@ WORKLOADS = {
                cols=64, bins=256, depth=8, shape=3),
     "c2": dict(name="GBM histogram build 1M rows x 28 cols (HIGGS-shaped), 256 bins, depth 6 (BASELINE config 2)",
                rows=1_000_000, cols=28, bins=256, depth=6, shape=2),
-    # config 4 as K separate class trees (the fused K-class pass is not built): one class tree, 80 GB of X
-    "c4": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, one of the 10 class trees "
-                    "(BASELINE config 4, unfused)", rows=10_000_000, cols=2000, bins=64, depth=6, shape=4),
+    # config 4: the K = 10 class trees of one multinomial iteration, one after the other on the sparse storage (a level
+    # of all ten = one "fused level" of SURVEY.md §8(d)); a step is one class-tree level, ten steps one fused level
+    "c4": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, multinomial 10-class targets "
+                    "(BASELINE config 4)", rows=10_000_000, cols=2000, bins=64, depth=6, shape=4, k=10, sparse=True),
+    "c4-dense": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, 10-class targets, DENSE "
+                          "fp32 storage (BASELINE config 4 as round 1 ran it)", rows=10_000_000, cols=2000, bins=64, depth=6,
+                     shape=4, k=10),
 }
 CPU_SAMPLE_ROWS = 2_000_000
+CPU_SAMPLE_CELLS = 128_000_000  # and at most this many cells per level (2M rows x 64 columns; 64K rows x 2000)
 
 
-def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False):
-    """every fp32 cell once, nid + y (+ w) once per row, the fp64 histogram written once."""
+def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False, sparse_nnz=None):
+    """every fp32 cell once, nid + y (+ w) once per row, the fp64 histogram written once.
+    Sparse storage (its own formula, include/h2ok_hist.h): 8 bytes per nonzero cell {row, value} instead of 4 bytes per
+    cell, and 10 bytes per row (2-byte node + two 4-byte targets)."""
+    if sparse_nnz is not None:
+        return sparse_nnz * 8.0 + rows * 10.0 + n_nodes * cols * (bins + 1) * 3 * 8.0
     return rows * cols * 4.0 + rows * (4.0 + 4.0 + (4.0 if weighted else 0.0)) + n_nodes * cols * (bins + 1) * 3 * 8.0
 
 
@@ -126,6 +135,10 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
+def cpu_sample_rows(wl):
+    return int(min(CPU_SAMPLE_ROWS, wl["rows"], max(1000, CPU_SAMPLE_CELLS // wl["cols"])))
+
+
 def cpu_levels(oracle, wl, sample_rows, threads, max_seconds, levels=None):
     """The oracle's own level loop (fp64, column-parallel like H2O's LocalMR) on the first `sample_rows` rows of the
     workload.  Returns per-level seconds of build_level + find_splits + next_level + apply_splits."""
@@ -167,7 +180,7 @@ def run_reference(args, wl):
 
     oracle = oracle_lib.load()
     threads = host_threads()
-    rows = min(CPU_SAMPLE_ROWS, wl["rows"])
+    rows = cpu_sample_rows(wl)
     # every "step" is one level of a depth-`depth` tree over the sample; warm-up levels come first
     need = args.steps + args.warmup
     times = []
@@ -220,7 +233,7 @@ def cpu_leg(wl, rows_total, gpu_slice_checksum):
 
     oracle = oracle_lib.load()
     threads = host_threads()
-    srows = min(CPU_SAMPLE_ROWS, rows_total)
+    srows = cpu_sample_rows(wl)
     cols, depth = wl["cols"], wl["depth"]
 
     def best(th, reps, budget):
@@ -281,10 +294,26 @@ def run_gpu(args, wl):
     rows = rows_total * (rank + 1) // world - row0
     params = abi.Params.make(nbins=bins, max_depth=depth)
     in_library = args.path == "engine"
-    shard = CudaShard(local) if args.path == "stateless" else EngineShard(local)
+    K = int(wl.get("k", 1))
+    sparse = bool(wl.get("sparse")) and args.path != "stateless"
+    nnz = rows * cols * (1.0 - 58982.0 / 65536.0) if sparse else None  # the generator zeroes a cell when hash16 < 58982
+    shard = CudaShard(local) if args.path == "stateless" else EngineShard(local, sparse=sparse)
     if in_library:
         TreeLoop.join_ranks(shard)  # the library's own NCCL communicator (h2ok_hist_comm_init)
     shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
+    # K class trees per boosting iteration: K target vectors (y_k = 2 u_k - 1 from their own hashes)
+    ys = [shard.y]
+    for k in range(1, K):
+        yk = torch.empty_like(shard.y)
+        shard.lib.call("h2ok_hist_synth_fill_dev", shard.ctx, abi.SHAPE_HIGGS28, SEED + 7919 * k, row0, rows, cols, shard.ld, 0, 0,
+                       None, C.c_void_p(yk.data_ptr()), None)
+        ys.append(yk)
+    tree_no = [0]
+
+    def next_targets():
+        y = ys[tree_no[0] % K]
+        tree_no[0] += 1
+        return y
     if in_library:
         loop = TreeLoop(shard, params, checksum=True, time_phases=True)
     else:
@@ -300,14 +329,20 @@ def run_gpu(args, wl):
         done = 0
         while done < n_steps:
             if loop.n_nodes_left() == 0:
-                loop.begin_tree()
+                begin()
             lvl, n = loop.depth, loop.n_nodes
             loop.level()
             if record:
                 rec.append((lvl, n, shard.last_hist_ms(), loop.phase_ms() if in_library else None))
             done += 1
 
-    loop.begin_tree()
+    def begin():
+        if in_library:
+            loop.begin_tree(y=next_targets())
+        else:
+            loop.begin_tree()
+
+    begin()
     run_steps(args.warmup, False)
     sampler = ClockSampler(local)
     barrier()
@@ -331,14 +366,15 @@ def run_gpu(args, wl):
     # tree on these inputs the same bits, whatever the number of ranks: the lines of a scaling run must agree.
     checksum = None
     if in_library:
-        loop.begin_tree()
+        tree_no[0] = 0
+        begin()
         while loop.n_nodes_left() > 0:
             loop.level()
         checksum = ["%016x" % c for c in loop.checksum(row0)]
 
     # roofline of the dominant kernel: algorithmic bytes of THIS rank's launches / their device time
     hist_ms = float(sum(r[2] for r in rec))
-    abytes = float(sum(algo_bytes_level(rows, cols, r[1], bins) for r in rec))
+    abytes = float(sum(algo_bytes_level(rows, cols, r[1], bins, sparse_nnz=nnz) for r in rec))
     peak, peak_src = measured_hbm_peak()
     achieved = abytes / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
     per_level = {}
@@ -348,7 +384,7 @@ def run_gpu(args, wl):
     for k, v in sorted(per_level.items()):
         t = float(np.mean([x[1] for x in v]))
         row = {"nodes": v[0][0], "hist_ms": round(t, 4),
-               "frac": round(algo_bytes_level(rows, cols, v[0][0], bins) / (t * 1e-3) / 1e9 / peak, 4)}
+               "frac": round(algo_bytes_level(rows, cols, v[0][0], bins, sparse_nnz=nnz) / (t * 1e-3) / 1e9 / peak, 4)}
         if v[0][2] is not None:
             ph = np.mean([x[2] for x in v], axis=0)
             row.update(reduce_ms=round(float(ph[1]), 4), search_ms=round(float(ph[2]), 4), route_ms=round(float(ph[3]), 4))
@@ -372,8 +408,8 @@ def run_gpu(args, wl):
     if rank == 0 and world == 1 and not args.no_cpu:
         gpu_slice = None
         if in_library:
-            srows = min(CPU_SAMPLE_ROWS, rows_total)
-            s2 = EngineShard(local)
+            srows = cpu_sample_rows(wl)
+            s2 = EngineShard(local, sparse=sparse)
             s2.set_data_synth(wl["shape"], SEED, 0, srows, cols)
             l2 = TreeLoop(s2, params, checksum=True)
             l2.train_tree()
@@ -395,7 +431,13 @@ def run_gpu(args, wl):
                                ("one h2ok_hist_loop_level call per step, reduce over ranks by the library's NCCL calls"
                                 if in_library else "Python per-step loop"),
                        "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
-                       "per_level": level_table, "phases_ms": phases, "whole_level_frac": round(whole_level_frac, 4)},
+                       "per_level": level_table, "phases_ms": phases, "whole_level_frac": round(whole_level_frac, 4),
+                       **({"k_classes": K, "storage": "sparse (H2OK_TREE_SPARSE)" if sparse else "dense fp32",
+                           "fused_level_ms": round(K * total_ms / args.steps, 3),
+                           "fused_level_note": "one level of all K class trees = K steps; SURVEY.md §8(d)'s floor for it is one "
+                                               "read of the DENSE matrix (80.8 GB): frac_of_dense_fused_floor compares with that",
+                           "frac_of_dense_fused_floor": round((rows * cols * 4.0 + K * rows * 8.0) / (K * total_ms / args.steps * 1e-3) / 1e9 / peak, 4)}
+                          if K > 1 else {})},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (NCU_TRAFFIC_BYTES_PER_CELL[args.path] * rows * cols / 1e9
                                      if args.workload == "c3" and args.path in NCU_TRAFFIC_BYTES_PER_CELL else None),
@@ -425,7 +467,7 @@ def run_e2e_loop(args, wl, shard, loop, world, rank, rows_total, rows, barrier):
     cols, bins, depth = wl["cols"], wl["bins"], wl["depth"]
     nb1 = bins + 1
     max_nodes = 2 ** (depth - 1)
-    yh = shard.y[:rows].cpu().pin_memory()
+    yh = shard.y[:rows].cpu().pin_memory()  # (K > 1: every class tree re-uploads a target vector of the same size)
 
     def pinned(shape, dtype):
         return torch.empty(shape, dtype=dtype).pin_memory()
@@ -469,7 +511,7 @@ def run_e2e_loop(args, wl, shard, loop, world, rank, rows_total, rows, barrier):
     sec = float(t.item())
     up = None
     if rank == 0 and world == 1:
-        up = measure_upload(wl, min(rows, 10_000_000))
+        up = measure_upload(wl, int(min(rows, max(1000, 640_000_000 // cols))))
     return {"value": rows_total * cols * args.steps / sec, "unit": UNIT, "h2d_bytes_per_step": st["h2d"] / args.steps,
             "d2h_bytes_per_step": st["d2h"] / args.steps, "ms_per_step": sec * 1e3 / args.steps,
             "path": "C ABI host-buffer calls: h2ok_hist_loop_begin_tree_host per tree (y from host memory), "

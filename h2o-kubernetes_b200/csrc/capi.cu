@@ -57,10 +57,6 @@ static double pow2_scale(double absmax, int qbits) {
   return ldexp(1.0, qbits - ex);
 }
 
-static const char* kTooDense =
-    "sparse storage: more (row, block) pairs with over 12 nonzeros than the overflow store holds (one pair in sixteen); "
-    "create the shard without H2OK_TREE_SPARSE";
-
 extern "C" {
 
 const char* h2ok_last_error(void) { return g_err; }
@@ -353,7 +349,6 @@ int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* c, int32_t col0, int32_t ncols, c
   REQUIRE(c && d_X, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_load_cols_dev before tree_create");
   REQUIRE(col0 >= 0 && ncols > 0 && col0 + ncols <= c->eng.cols && ld >= c->eng.rows, "column block outside the shard");
-  REQUIRE(!c->eng.sparse || col0 % 64 == 0, "sparse storage: column blocks must start on a multiple of 64");
   CK(engine_load_cols(c->eng, col0, ncols, d_X, ld, c->stream));
   return H2OK_OK;
 }
@@ -374,9 +369,6 @@ int32_t h2ok_hist_tree_build_level_dev(h2ok_ctx* c, int32_t n_nodes, const h2ok_
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_build_level_dev before tree_create");
   int32_t rc = check_level_shape(n_nodes, c->eng.cols, max_bins);
   if (rc) return rc;
-  bool too_dense = false;
-  CK(engine_check_load(c->eng, c->stream, &too_dense));
-  if (too_dense) return fail(H2OK_ERR_UNSUPPORTED, "%s", kTooDense);
   const int nb1 = max_bins + 1;
   const int level_nb1 = c->eng_level_bins > 0 && c->eng_level_bins < max_bins ? c->eng_level_bins + 1 : nb1;
   c->eng_level_bins = 0;  // the hint covers one level

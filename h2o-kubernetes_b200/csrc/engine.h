@@ -23,6 +23,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <vector>
+
 #include "../../include/h2ok_hist.h"
 
 namespace h2ok {
@@ -38,13 +40,14 @@ struct Engine {
   int route_ctas = 0;  // CTAs of the routing / regrouping kernels (each owns one contiguous range of rows)
   bool weighted = false;
   float* XT = nullptr;       // [rows][ldt] row-major copy of the shard (dense storage)
-  // sparse storage instead (row_engine.cu "sparse storage"): one 64-byte slot of nonzeros per (row, block of 64 columns)
+  // sparse storage instead (row_engine.cu "sparse storage"): per column the list of its nonzero cells {row, value}
   bool sparse = false;
-  int nblk = 0;
-  void* slots = nullptr;           // [rows][nblk] SpSlot
-  float* ovf = nullptr;            // [ovf_cap][64] dense rows of the (row, block) pairs with more than 12 nonzeros
-  unsigned* ovf_count = nullptr;   // entries of ovf in use (device)
-  unsigned ovf_cap = 0;
+  const uint2** csc_ptr = nullptr;   // [cols] device table of the columns' lists
+  int64_t* csc_len = nullptr;        // [cols] their lengths
+  std::vector<void*> csc_blocks;     // the allocations behind them (one per loaded block of columns)
+  int64_t nnz = 0;                   // nonzero cells of the shard
+  unsigned long long* node_tot = nullptr;  // [kEngMaxNodes][3] rows / sum wyq / sum wyyq of every node of the level
+  uint2* rec = nullptr;              // [rows] {node, wyq, wyyq} of every row packed in 8 bytes, rebuilt per level
   uint8_t* code8 = nullptr;  // [cols][ld8] order-preserving 8-bit code of every cell (255 = NaN), for routing
   uint32_t* thr = nullptr;   // [cols][256] the codes' thresholds (encoded floats, ascending; unused = 0xFFFFFFFF)
   uint32_t* cmin = nullptr;  // [cols] encoded column minimum / maximum of the shard (NaN skipped), taken while loading
@@ -66,8 +69,6 @@ struct Engine {
   const int32_t* wyyq_rows = nullptr;
   double scale_wy = 0, scale_wyy = 0;   // fixed-point scales of the tree's targets (0: no centring)
   const h2ok_quant* q_dev = nullptr;    // the same scales in device memory, when the tree was started without a host copy
-  int32_t* load_err = nullptr;          // != 0: the sparse overflow store was too small for the data (device)
-  bool load_checked = false, load_failed = false;  // host copy of it, read once per data set
   int32_t* na_flag = nullptr;           // != 0 once a NaN cell has been seen while loading (device)
   bool na_known = false, has_na = true; // host copy of it, read once per data set: NaN-free shards skip the NA test
   int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
@@ -95,8 +96,6 @@ int engine_max_nb1(int cols);
 // (regroup == false: the tree's last level — rows only get their leaves, no records are laid out)
 cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32_t* child_ids, int gid_base, int n_nodes,
                                 bool regroup, cudaStream_t s);
-// sparse storage: did every dense (row, block) pair find room in the overflow store?  (one blocking read per data set)
-cudaError_t engine_check_load(Engine& e, cudaStream_t s, bool* too_dense);
 // row -> node map of the current level in original row order (tests / inspection)
 cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s);
 

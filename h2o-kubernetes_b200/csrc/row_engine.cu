@@ -13,6 +13,7 @@
 //   eng_scan_kernel      first record of every (child, CTA), next level's node table and centring offsets.
 //   eng_scatter_kernel   next level's records {row, targets - child offset} written to their child's run.
 #include <atomic>
+#include <vector>
 
 #include "common.cuh"
 #include "engine.h"
@@ -24,6 +25,7 @@ namespace {
 
 inline unsigned nblk(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
 
+constexpr unsigned kNoNidConst = 0xFFFFu;  // row -> node map: the row sits in a leaf
 constexpr int kHistSmemCap = 227 * 1024 - 2048;  // dynamic shared memory left beside the kernel's static arrays (<= 1.2 KB)
 constexpr int kSegNodes = kEngMaxNodes + 1;       // seg[kSegNodes] = number of nodes the table describes
 constexpr int kSegInts = kEngMaxNodes + 2;
@@ -94,6 +96,9 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
     seg[kSegNodes] = 1;
   }
   if (p >= rows) return;
+  leaf[p] = -1;
+  nid16[p] = 0;
+  if (!gidx) return;  // sparse storage keeps no row records: the row -> node map is all it needs
   // zero-weight rows still travel down the tree (a6); the histogram pass skips them by weight
   gidx[p] = (int32_t)p;
   // a row whose quantised weight is 0 takes no part, whatever its (independently scaled) targets round to — the
@@ -101,8 +106,6 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
   const bool dead = gw && wq_rows[p] == 0;
   gval[p] = dead ? make_uint2(0u, 0u) : make_uint2((unsigned)(wyq_rows[p] - mnode[0]), (unsigned)(wyyq_rows[p] - mnode[1]));
   if (gw) gw[p] = wq_rows[p];
-  leaf[p] = -1;
-  nid16[p] = 0;
 }
 
 // first g in [0, n) with table[g + 1] > v (table non-decreasing, table[n] > v)
@@ -485,326 +488,6 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
   }
 }
 
-// ------------------------------------------------------------------------------------------------ sparse storage
-// For matrices that are mostly exact zeros (BASELINE config 4: 90 % zeros; H2O itself keeps such columns in sparse
-// chunks, CXIChunk / CX0Chunk) the shard can be stored as one 64-byte slot per (row, block of 64 columns) holding the
-// block's NONZERO cells only: byte 0 = their number, bytes 1..12 = their columns inside the block, words 4..15 = their
-// values (a NaN is a nonzero).  A (row, block) with more than 12 nonzeros (1.3 % at 10 % density) says 0xFF and points
-// (word 4) at a dense 64-float row in an overflow store.  256 B of dense floats become 64 B.
-//
-// The histogram pass then touches only the nonzeros: a warp flattens the nonzero cells of four rows into a work list
-// and every lane takes one (column, value) pair, so a warp instruction updates ~26 cells instead of the ~3 nonzero
-// lanes of the one-column-per-lane layout.  A lane no longer owns its columns, so descriptors come from a shared
-// table, the histogram is [copy][column][bin][channel] with the copy chosen by lane, and observed ranges go through a
-// shared table (compare first, atomic only on improvement).  The zeros are accounted for exactly at the flush: the
-// node's totals over the CTA's rows minus what its nonzeros added is what the zero cells contribute, and it goes to
-// the bin 0.0 falls into; a column with a zero row has 0.0 inside its observed range.  Integer sums make this exact.
-constexpr int kSpCols = 64, kSpInline = 12, kSpRows = 4;
-struct SpSlot {
-  unsigned w[16];
-};
-
-__global__ void __launch_bounds__(256) eng_load_sparse_kernel(const float* __restrict__ X, int64_t ld, int64_t rows, int ncols,
-                                                              SpSlot* __restrict__ slots, int nblk, int blk,
-                                                              float* __restrict__ ovf, unsigned* __restrict__ ovf_count,
-                                                              unsigned ovf_cap, int32_t* __restrict__ err) {
-  __shared__ unsigned s[256][17];
-  const int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (r >= rows) return;
-  unsigned* w = s[threadIdx.x];
-#pragma unroll
-  for (int i = 0; i < 16; i++) w[i] = 0u;
-  int cnt = 0;
-  for (int c = 0; c < ncols; c++) {
-    const float x = X[(int64_t)c * ld + r];
-    if (!(x == 0.0f)) {  // NaN counts as a nonzero; -0.0 as a zero
-      if (cnt < kSpInline) {
-        w[(1 + cnt) >> 2] |= (unsigned)c << (8 * ((1 + cnt) & 3));
-        w[4 + cnt] = __float_as_uint(x);
-      }
-      cnt++;
-    }
-  }
-  if (cnt <= kSpInline) {
-    w[0] |= (unsigned)cnt;
-  } else {
-    const unsigned idx = atomicAdd(ovf_count, 1u);
-    if (idx < ovf_cap) {
-      for (int c = 0; c < kSpCols; c++) ovf[(int64_t)idx * kSpCols + c] = c < ncols ? X[(int64_t)c * ld + r] : 0.0f;
-      w[0] = 0xFFu;
-      w[4] = idx;
-    } else {
-      *err = 1;  // denser than the overflow store was sized for: the caller must use dense storage
-      w[0] = 0u;
-    }
-  }
-  unsigned* out = slots[r * nblk + blk].w;
-#pragma unroll
-  for (int i = 0; i < 16; i += 4) *reinterpret_cast<uint4*>(out + i) = make_uint4(w[i], w[i + 1], w[i + 2], w[i + 3]);
-}
-
-// one cell of the sparse shard (routing's exact comparison on a code tie)
-__device__ __forceinline__ float sp_get(const SpSlot* __restrict__ slots, int nblk, const float* __restrict__ ovf, int64_t r,
-                                        int col) {
-  const unsigned* w = slots[r * nblk + (col >> 6)].w;
-  const int c = col & 63;
-  const unsigned w0 = w[0], cnt = w0 & 0xFFu;
-  if (cnt == 0xFFu) return ovf[(int64_t)w[4] * kSpCols + c];
-  for (unsigned p = 0; p < cnt; p++) {
-    const unsigned byte = (w[(1 + p) >> 2] >> (8 * ((1 + p) & 3))) & 0xFFu;
-    if ((int)byte == c) return __uint_as_float(w[4 + p]);
-  }
-  return 0.0f;
-}
-
-struct SpHistArgs {
-  const SpSlot* slots;
-  int nblk;
-  const float* ovf;
-  int cols;
-  const int32_t* gidx;
-  const uint2* gval;
-  const int32_t* mnode;
-  const int32_t* seg;
-  int n_nodes;
-  const h2ok_col_desc* descs;
-  int nb1, nbs, copies;
-  int64_t* acc;
-  uint32_t* min2_enc;
-  uint32_t* maxin_enc;
-  int32_t* err;
-};
-
-__global__ void __launch_bounds__(1024, 1) eng_hist_sparse_kernel(const __grid_constant__ SpHistArgs a) {
-  constexpr int THREADS = 1024, NW = THREADS / 32;
-  extern __shared__ __align__(16) unsigned h[];  // [copy][column][bin][channel]
-  __shared__ double s_mn[kSpCols], s_st[kSpCols];
-  __shared__ int s_nb[kSpCols];
-  __shared__ unsigned s_rmin[kSpCols], s_rmax[kSpCols];
-  __shared__ unsigned char s_tracked[kSpCols];
-  __shared__ unsigned long long s_tot[3];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nb1 = a.nb1, nbs = a.nbs, copies = a.copies;
-  const int col0 = (int)blockIdx.y * kSpCols;
-  const int n_nodes = min(a.n_nodes, a.seg[kSegNodes]);
-  if (n_nodes < 1) return;
-  const int64_t live = a.seg[n_nodes];
-  int p0 = (int)(live * (int64_t)blockIdx.x / gridDim.x);
-  const int p1 = (int)(live * (int64_t)(blockIdx.x + 1) / gridDim.x);
-  if (p0 >= p1) return;
-  int node = seg_of(a.seg, n_nodes, p0);
-  const int words = copies * kSpCols * nbs * 3;
-  for (int i = tid; i < words; i += THREADS) h[i] = (i % 3 == 0) ? 0u : kWyBias;
-  const unsigned hbase = (unsigned)__cvta_generic_to_shared(h) + (unsigned)((lane & (copies - 1)) * kSpCols * nbs) * 12u;
-  const int32_t* __restrict__ gidx = a.gidx;
-  const uint2* __restrict__ gval = a.gval;
-  const char* sbase = reinterpret_cast<const char*>(a.slots) + (size_t)blockIdx.y * sizeof(SpSlot);
-  const unsigned pitch = (unsigned)a.nblk * (unsigned)sizeof(SpSlot);
-
-  while (p0 < p1) {
-    const int nend = a.seg[node + 1];
-    const int send = nend < p1 ? nend : p1;
-    if (send <= p0) {
-      node++;
-      continue;
-    }
-    if (tid < kSpCols) {
-      const int col = col0 + tid;
-      bool tracked = false;
-      double mn = 0.0, st = 0.0;
-      int nb = 1;
-      if (col < a.cols) {
-        const h2ok_col_desc d = a.descs[(int64_t)node * a.cols + col];
-        if (d.nbin >= nbs) atomicAdd(a.err, 1);
-        else if (d.nbin > 0) {
-          tracked = true;
-          mn = d.min;
-          st = d.step;
-          nb = d.nbin;
-        }
-      }
-      s_mn[tid] = mn;
-      s_st[tid] = st;
-      s_nb[tid] = nb;
-      s_rmin[tid] = kEncPosInf;
-      s_rmax[tid] = kEncNegInf;
-      s_tracked[tid] = tracked ? 1 : 0;
-    }
-    if (tid < 3) s_tot[tid] = 0ull;
-    __syncthreads();
-
-    // one (column, value) pair of row slot j: bin from the shared descriptor table, three shared atomics, range
-    auto item = [&](bool active, int col, float x, int v1, int v2) {
-      if (!active) return;
-      const int b = bin_fast(x, s_mn[col], s_st[col], s_nb[col]);
-      const unsigned addr = hbase + (unsigned)((col * nbs + b) * 12);
-      sh_inc(addr);
-      const unsigned o1 = sh_add(addr + 4u, (unsigned)v1), o2 = sh_add(addr + 8u, (unsigned)v2);
-      const unsigned f1 = wrap_bit(o1, v1), f2 = wrap_bit(o2, v2);
-      if ((f1 | f2) >> 31)
-        eng_carry(a.acc, a.descs, node, a.cols, col0 + col, nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
-                  (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
-      if (x == x) {
-        const unsigned e = enc_f32_bits(__float_as_uint(x));
-        if (e < s_rmin[col]) atomicMin(&s_rmin[col], e);
-        if (e > s_rmax[col]) atomicMax(&s_rmax[col], e);
-      }
-    };
-
-    unsigned tc = 0;            // this warp's rows of the run and their (centred) target sums: what the zeros are
-    long long t1 = 0, t2 = 0;   // worked out from at the flush
-    for (int p = p0 + warp * kSpRows; p < send; p += NW * kSpRows) {
-      const int nr = send - p < kSpRows ? send - p : kSpRows;
-      int v1[kSpRows], v2[kSpRows];
-      unsigned ridx[kSpRows];
-#pragma unroll
-      for (int j = 0; j < kSpRows; j++) {
-        const int q = j < nr ? p + j : p;
-        ridx[j] = (unsigned)__ldg(gidx + q);
-        const uint2 r = __ldg(gval + q);
-        v1[j] = (int)r.x;
-        v2[j] = (int)r.y;
-        if (j < nr) {
-          tc += 1u;
-          t1 += (int)r.x;
-          t2 += (int)r.y;
-        }
-      }
-      // rows 0/1 in the two halves of regA, rows 2/3 in regB: one 64-byte slot per half warp
-      const int half = lane >> 4, word = lane & 15;
-      const unsigned regA = __ldg(reinterpret_cast<const unsigned*>(row_addr(sbase, half ? ridx[1] : ridx[0], pitch)) + word);
-      const unsigned regB = __ldg(reinterpret_cast<const unsigned*>(row_addr(sbase, half ? ridx[3] : ridx[2], pitch)) + word);
-      unsigned cnt[kSpRows];
-      cnt[0] = __shfl_sync(0xffffffffu, regA, 0) & 0xFFu;
-      cnt[1] = __shfl_sync(0xffffffffu, regA, 16) & 0xFFu;
-      cnt[2] = __shfl_sync(0xffffffffu, regB, 0) & 0xFFu;
-      cnt[3] = __shfl_sync(0xffffffffu, regB, 16) & 0xFFu;
-      unsigned dense_mask = 0;
-#pragma unroll
-      for (int j = 0; j < kSpRows; j++) {
-        if (j >= nr) cnt[j] = 0;
-        if (cnt[j] == 0xFFu) {
-          dense_mask |= 1u << j;
-          cnt[j] = 0;
-        }
-      }
-      const int P1 = (int)cnt[0], P2 = P1 + (int)cnt[1], P3 = P2 + (int)cnt[2], T = P3 + (int)cnt[3];
-      for (int base = 0; base < T; base += 32) {
-        const int i = base + lane;
-        const int j = (i >= P1) + (i >= P2) + (i >= P3);
-        const int pp = i - (j == 0 ? 0 : (j == 1 ? P1 : (j == 2 ? P2 : P3)));
-        const int src = (j & 1) << 4;
-        const int hw = (1 + pp) >> 2;
-        const unsigned cwA = __shfl_sync(0xffffffffu, regA, (src + hw) & 31), cwB = __shfl_sync(0xffffffffu, regB, (src + hw) & 31);
-        const unsigned vA = __shfl_sync(0xffffffffu, regA, (src + 4 + pp) & 31), vB = __shfl_sync(0xffffffffu, regB, (src + 4 + pp) & 31);
-        const unsigned cw = (j >> 1) ? cwB : cwA;
-        const int col = (int)((cw >> (8 * ((1 + pp) & 3))) & 0xFFu) & 63;
-        const float x = __uint_as_float((j >> 1) ? vB : vA);
-        const int a1 = j == 0 ? v1[0] : (j == 1 ? v1[1] : (j == 2 ? v1[2] : v1[3]));
-        const int a2 = j == 0 ? v2[0] : (j == 1 ? v2[1] : (j == 2 ? v2[2] : v2[3]));
-        item(i < T, col, x, a1, a2);
-      }
-      if (dense_mask) {  // rows with more nonzeros than a slot holds: their dense 64-float row, two columns per lane
-#pragma unroll
-        for (int j = 0; j < kSpRows; j++) {
-          if (!((dense_mask >> j) & 1u)) continue;
-          const unsigned idx = __shfl_sync(0xffffffffu, (j >> 1) ? regB : regA, ((j & 1) << 4) + 4);
-          const float* row = a.ovf + (int64_t)idx * kSpCols;
-          const float x0 = __ldg(row + lane), x1 = __ldg(row + 32 + lane);
-          item(!(x0 == 0.0f), lane, x0, v1[j], v2[j]);
-          item(!(x1 == 0.0f), 32 + lane, x1, v1[j], v2[j]);
-        }
-      }
-    }
-    if (lane == 0 && tc) {
-      atomicAdd(&s_tot[0], (unsigned long long)tc);
-      atomicAdd(&s_tot[1], (unsigned long long)t1);
-      atomicAdd(&s_tot[2], (unsigned long long)t2);
-    }
-    __syncthreads();
-
-    // flush.  First per column (one warp each): what the nonzeros added, hence what the zero cells contribute.
-    const int m1 = a.mnode[2 * node], m2 = a.mnode[2 * node + 1];
-    for (int c = warp; c < kSpCols; c += NW) {
-      if (!s_tracked[c]) continue;  // warp-uniform
-      unsigned long long nc = 0;
-      long long n1 = 0, n2 = 0;
-      for (int i = lane; i < nbs * copies; i += 32) {
-        const int cp = i / nbs, b = i - cp * nbs;
-        const unsigned* w = h + ((cp * kSpCols + c) * nbs + b) * 3;
-        nc += w[0];
-        n1 += (long long)w[1] - (long long)kWyBias;
-        n2 += (long long)w[2] - (long long)kWyBias;
-      }
-      for (int o = 16; o; o >>= 1) {
-        nc += __shfl_xor_sync(0xffffffffu, nc, o);
-        n1 += __shfl_xor_sync(0xffffffffu, n1, o);
-        n2 += __shfl_xor_sync(0xffffffffu, n2, o);
-      }
-      if (lane == 0) {
-        const int col = col0 + c;
-        const long long zc = (long long)s_tot[0] - (long long)nc;
-        const long long z1 = (long long)s_tot[1] - n1 + zc * m1, z2 = (long long)s_tot[2] - n2 + zc * m2;
-        if (zc > 0) {
-          const int bz = bin_of(0.0f, s_mn[c], s_st[c], s_nb[c]);
-          unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col) * nb1 + bz) * 3;
-          atomicAdd(g, (unsigned long long)zc);
-          if (z1) atomicAdd(g + 1, (unsigned long long)z1);
-          if (z2) atomicAdd(g + 2, (unsigned long long)z2);
-          const unsigned ez = enc_f32_bits(__float_as_uint(0.0f));
-          if (ez < s_rmin[c]) s_rmin[c] = ez;  // only this lane touches the column's slots now
-          if (ez > s_rmax[c]) s_rmax[c] = ez;
-        }
-        if (s_rmin[c] != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)node * a.cols + col], s_rmin[c]);
-        if (s_rmax[c] != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)node * a.cols + col], s_rmax[c]);
-      }
-    }
-    __syncthreads();
-    // then every (column, bin): copies added up, centring undone with the bin's own count, words re-armed
-    for (int t = tid; t < kSpCols * nbs; t += THREADS) {
-      const int c = t / nbs, b = t - c * nbs;
-      unsigned long long nc = 0;
-      long long n1 = 0, n2 = 0;
-      for (int cp = 0; cp < copies; cp++) {
-        unsigned* w = h + ((cp * kSpCols + c) * nbs + b) * 3;
-        const unsigned c0 = w[0], u1 = w[1], u2 = w[2];
-        if (c0 | (u1 ^ kWyBias) | (u2 ^ kWyBias)) {
-          nc += c0;
-          n1 += (long long)u1 - (long long)kWyBias;
-          n2 += (long long)u2 - (long long)kWyBias;
-          w[0] = 0u;
-          w[1] = kWyBias;
-          w[2] = kWyBias;
-        }
-      }
-      if (s_tracked[c] && (nc | (unsigned long long)n1 | (unsigned long long)n2)) {
-        unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)node * a.cols + col0 + c) * nb1 + b) * 3;
-        const long long s1 = n1 + (long long)nc * m1, s2 = n2 + (long long)nc * m2;
-        if (nc) atomicAdd(g, nc);
-        if (s1) atomicAdd(g + 1, (unsigned long long)s1);
-        if (s2) atomicAdd(g + 2, (unsigned long long)s2);
-      }
-    }
-    __syncthreads();
-    p0 = send;
-    node++;
-  }
-}
-
-// ------------------------------------------------------------------------------------------------ a6 + regroup
-// Routing walks the rows in their ORIGINAL order (row -> node map nid16), not the node-grouped records: every access
-// is then a stream.  The value the split needs is not gathered from the row-major copy — a gather of one float per
-// row costs a 128-byte DRAM access each (ncu: 13.2 GB per level at 100M rows, profiles/r02_route_scatter_r01code_*) —
-// but decided from an 8-bit order-preserving code of the cell, kept column-major (code8, one byte per cell, written
-// once per data set): code(x) < code(splat) => x < splat, code(x) > code(splat) => x > splat, and only a row whose
-// code EQUALS the threshold's (~1/255 of a column's rows) reads its float and compares exactly as H2O does
-// (DecidedNode: x >= splat).  A warp of 32 consecutive rows reads one sector per distinct split column among its
-// rows, so a level streams (distinct split columns) x rows bytes at most.
-//
-// Regrouping is a stable-by-range multi-way partition in the same row order: every CTA owns one contiguous range of
-// rows in both kernels; eng_route_kernel counts its rows per child, eng_scan_kernel turns the [child][CTA] counts
-// into first positions, eng_scatter_kernel writes the next level's records {row, targets - child's offset} there.
-// Rows of a node stay ascending up to the order inside a 512-row tile — integer sums do not depend on it.
 // 1024-thread exclusive scan; returns the exclusive prefix, *total gets the block sum (valid for every thread)
 __device__ __forceinline__ int block_exscan_1024(int v, int* s_warp, int* total) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -834,8 +517,313 @@ __device__ __forceinline__ int block_exscan_1024(int v, int* s_warp, int* total)
   return ex;
 }
 
+// ------------------------------------------------------------------------------------------------ sparse storage
+// For matrices that are mostly exact zeros (BASELINE config 4: 90 % zeros; H2O itself keeps such columns in sparse
+// chunks, CXIChunk / CX0Chunk) the shard is stored column by column as the list of its NONZERO cells {row, value},
+// rows ascending (a NaN is a nonzero, -0.0 a zero): 8 bytes per nonzero instead of 4 bytes per cell.
+//
+// The histogram pass then works like H2O's own (one column at a time, every node of the level at once) but on the
+// nonzeros only: a CTA streams a stretch of one column's list, looks the row's node up in the row -> node map (2 bytes,
+// L2-resident) and its targets in the row-order target arrays, bins against the node's descriptor for this column
+// (a shared table indexed by node) and adds into a shared histogram [copy][node][bin][channel].  Every lane works on
+// a nonzero cell: a warp instruction updates 32 cells where the row-wise layouts keep 3 of 32 lanes busy at 10 %
+// density.  No row records are regrouped for such a shard — routing alone keeps the row -> node map current.
+// The zeros are accounted for exactly afterwards (eng_csc_zero_kernel): a node's totals over all its rows minus what
+// the column's nonzeros added is what its zero cells contribute; it goes to the bin 0.0 falls into, and a (node,
+// column) with a zero cell has 0.0 inside its observed range.  Integer sums make this exact.
+constexpr int kCscChunk = 65536;  // rows per compaction CTA
+
+// nonzeros of every (column, chunk of kCscChunk rows)
+__global__ void __launch_bounds__(1024) eng_csc_count_kernel(const float* __restrict__ X, int64_t ld, int64_t rows, int n_chunks,
+                                                             unsigned* __restrict__ cnt) {
+  __shared__ int s_warp[32];
+  const float* x = X + (int64_t)blockIdx.y * ld;
+  const int64_t r0 = (int64_t)blockIdx.x * kCscChunk;
+  const int64_t r1 = r0 + kCscChunk < rows ? r0 + kCscChunk : rows;
+  int n = 0;
+  for (int64_t r = r0 + threadIdx.x; r < r1; r += 1024) n += !(x[r] == 0.0f);
+  n = __reduce_add_sync(0xffffffffu, n);
+  if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = n;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    n = __reduce_add_sync(0xffffffffu, s_warp[threadIdx.x]);
+    if (threadIdx.x == 0) cnt[(int64_t)blockIdx.y * n_chunks + blockIdx.x] = (unsigned)n;
+  }
+}
+
+// stable compaction of one (column, chunk): {row, value bits} pairs, rows ascending
+__global__ void __launch_bounds__(1024) eng_csc_fill_kernel(const float* __restrict__ X, int64_t ld, int64_t rows, int n_chunks,
+                                                            const int64_t* __restrict__ start, uint2* __restrict__ out) {
+  __shared__ int s_warp[33];
+  const float* x = X + (int64_t)blockIdx.y * ld;
+  const int64_t r0 = (int64_t)blockIdx.x * kCscChunk;
+  const int64_t r1 = r0 + kCscChunk < rows ? r0 + kCscChunk : rows;
+  int64_t base = start[(int64_t)blockIdx.y * n_chunks + blockIdx.x];
+  const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  for (int64_t rb = r0; rb < r1; rb += 1024) {
+    const int64_t r = rb + threadIdx.x;
+    const float v = r < r1 ? x[r] : 0.0f;
+    const bool nz = !(v == 0.0f);
+    const unsigned bal = __ballot_sync(0xffffffffu, nz);
+    int tot;
+    const int ex = block_exscan_1024(lane == 0 ? __popc(bal) : 0, s_warp, &tot);
+    const int wbase = __shfl_sync(0xffffffffu, ex, 0);
+    if (nz) out[base + wbase + __popc(bal & lt)] = make_uint2((unsigned)r, __float_as_uint(v));
+    base += tot;
+  }
+}
+
+// one cell of the sparse shard (routing's exact comparison on a code tie): binary search of the row in its column
+__device__ __forceinline__ float csc_get(const uint2* const* __restrict__ cptr, const int64_t* __restrict__ clen, int64_t r,
+                                         int col) {
+  const uint2* p = cptr[col];
+  int64_t lo = 0, hi = clen[col];
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if ((int64_t)p[mid].x < r) lo = mid + 1;
+    else hi = mid;
+  }
+  if (lo < clen[col] && (int64_t)p[lo].x == r) return __uint_as_float(p[lo].y);
+  return 0.0f;
+}
+
+// per node: rows, sum of wyq, sum of wyyq over ALL its rows (what the zero cells are worked out from).  Rows of one warp
+// that share a node are added up with shuffles first; the CTA's partial sums live in shared memory as 32-bit words
+// (the only native shared atomic): a group sum s (|s| < 2^31) goes in as s >> 16 and s & 0xFFFF, and the words are
+// flushed to the 64-bit global totals every 32768 rows, before either half can overflow.  (64-bit shared atomics are
+// CAS loops: with 32 nodes they made this pass cost 8 ms per level.)
+// The same pass packs {node, wyq, wyyq} of every row into ONE 8-byte record (common.cuh rec_pack): the histogram pass
+// then fetches a row's node and targets with a single gather instead of three — its gathers are sector-granular L2
+// traffic, 168 GB per level on config 4 with three arrays against 64 GB with one.
+__global__ void __launch_bounds__(512) eng_node_totals_kernel(int64_t rows, const uint16_t* __restrict__ nid16,
+                                                              const int32_t* __restrict__ wyq, const int32_t* __restrict__ wyyq,
+                                                              int n_nodes, unsigned long long* __restrict__ tot,
+                                                              uint2* __restrict__ rec) {
+  extern __shared__ int s_t[];  // [n_nodes][5]: rows, hi/lo of sum wyq, hi/lo of sum wyyq
+  const unsigned lane = threadIdx.x & 31u;
+  const int64_t per = ((rows + gridDim.x - 1) / gridDim.x + 511) / 512 * 512;
+  const int64_t r0 = (int64_t)blockIdx.x * per, r1 = r0 + per < rows ? r0 + per : rows;
+  for (int64_t rs = r0; rs < r1; rs += 32768) {
+    for (int i = threadIdx.x; i < 5 * n_nodes; i += 512) s_t[i] = 0;
+    __syncthreads();
+    const int64_t re = rs + 32768 < r1 ? rs + 32768 : r1;
+    for (int64_t rb = rs; rb < re; rb += 512) {
+      const int64_t r = rb + threadIdx.x;
+      const unsigned nd = r < re ? nid16[r] : kNoNidConst;
+      const int a = nd != kNoNidConst ? wyq[r] : 0, b = nd != kNoNidConst ? wyyq[r] : 0;
+      if (r < re) rec[r] = rec_pack(a, b, nd != kNoNidConst && (int)nd < n_nodes ? nd : kNoNode);
+      unsigned todo = __ballot_sync(0xffffffffu, nd != kNoNidConst);
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        const unsigned key = __shfl_sync(0xffffffffu, nd, src);
+        const unsigned grp = __ballot_sync(0xffffffffu, nd == key);
+        const int sa = __reduce_add_sync(0xffffffffu, nd == key ? a : 0), sb = __reduce_add_sync(0xffffffffu, nd == key ? b : 0);
+        if ((int)lane == src && (int)key < n_nodes) {
+          int* t = s_t + 5 * key;
+          atomicAdd(t, __popc(grp));
+          atomicAdd(t + 1, sa >> 16);
+          atomicAdd(t + 2, sa & 0xFFFF);
+          atomicAdd(t + 3, sb >> 16);
+          atomicAdd(t + 4, sb & 0xFFFF);
+        }
+        todo &= ~grp;
+      }
+    }
+    __syncthreads();
+    for (int g = threadIdx.x; g < n_nodes; g += 512) {
+      const int* t = s_t + 5 * g;
+      if (t[0]) {
+        atomicAdd(&tot[3 * g], (unsigned long long)t[0]);
+        atomicAdd(&tot[3 * g + 1], (unsigned long long)((long long)t[1] * 65536 + (long long)t[2]));
+        atomicAdd(&tot[3 * g + 2], (unsigned long long)((long long)t[3] * 65536 + (long long)t[4]));
+      }
+    }
+    __syncthreads();
+  }
+}
+
+struct CscNode {  // what the pass needs of one node for one column, 32 bytes
+  double mn, st;
+  int nb;      // 0: (node, column) not tracked
+  int m1, m2;  // centring offsets of the node
+  int pad;
+};
+
+struct CscHistArgs {
+  const uint2* const* cptr;  // [cols] nonzeros of every column
+  const int64_t* clen;       // [cols]
+  int cols, chunks;
+  int node_base;  // this launch covers nodes [node_base, node_base + n_nodes)
+  const uint2* rec;  // [rows] {node, wyq, wyyq} packed (rec_pack)
+  const int32_t* mnode;
+  int n_nodes;
+  const h2ok_col_desc* descs;
+  int nb1, nbs, copies;
+  int64_t* acc;
+  uint32_t* min2_enc;
+  uint32_t* maxin_enc;
+  int32_t* err;
+};
+
+// 512 threads, four nonzeros per thread in flight: the pass is a chain of dependent loads per cell (list entry, then the
+// row's node, then its targets), so throughput comes from independent chains — one cell per thread at a time ran at
+// 18.6 ms per level on config 4, latency-bound.  Two CTAs share an SM whenever their histograms fit.
+constexpr int kCscThreads = 512;
+
+template <int U>
+__global__ void __launch_bounds__(kCscThreads, U <= 4 ? 2 : 1) eng_hist_csc_kernel(const __grid_constant__ CscHistArgs a) {
+  constexpr int THREADS = kCscThreads;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int n = a.n_nodes, nbs = a.nbs, copies = a.copies, nb1 = a.nb1;
+  CscNode* tab = reinterpret_cast<CscNode*>(smem_raw);
+  unsigned* s_rmin = reinterpret_cast<unsigned*>(tab + n);
+  unsigned* s_rmax = s_rmin + n;
+  unsigned* h = s_rmax + n;  // [copy][node][bin][channel]
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int col = blockIdx.y;
+  const int64_t len = a.clen[col];
+  const int64_t i0 = len * (int64_t)blockIdx.x / gridDim.x, i1 = len * (int64_t)(blockIdx.x + 1) / gridDim.x;
+  if (i0 >= i1) return;
+  const int nbase = a.node_base;
+  for (int g = tid; g < n; g += THREADS) {
+    const h2ok_col_desc d = a.descs[(int64_t)(nbase + g) * a.cols + col];
+    CscNode t;
+    t.mn = d.min;
+    t.st = d.step;
+    t.nb = d.nbin;
+    if (d.nbin >= nbs) {
+      if (blockIdx.x == 0) atomicAdd(a.err, 1);
+      t.nb = 0;
+    }
+    t.m1 = a.mnode[2 * (nbase + g)];
+    t.m2 = a.mnode[2 * (nbase + g) + 1];
+    t.pad = 0;
+    tab[g] = t;
+    s_rmin[g] = kEncPosInf;
+    s_rmax[g] = kEncNegInf;
+  }
+  const int words = copies * n * nbs * 3;
+  for (int i = tid; i < words; i += THREADS) h[i] = (i % 3 == 0) ? 0u : kWyBias;
+  __syncthreads();
+  const unsigned hbase = (unsigned)__cvta_generic_to_shared(h) + (unsigned)((lane & (copies - 1)) * n * nbs) * 12u;
+  const uint2* __restrict__ nz = a.cptr[col];
+  const uint2* __restrict__ rec = a.rec;
+  for (int64_t ib = i0 + tid; ib < i1; ib += (int64_t)THREADS * U) {
+    uint2 e[U];
+    unsigned nd[U];
+    int w1[U], w2[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t i = ib + (int64_t)u * THREADS;
+      e[u] = i < i1 ? __ldg(nz + i) : make_uint2(0u, 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t i = ib + (int64_t)u * THREADS;
+      // a row in a leaf (node 0x3FF) and a list entry past the end both fall outside [0, n)
+      const uint2 rc = i < i1 ? __ldg(rec + e[u].x) : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+      nd[u] = i < i1 ? rec_node(rc.x, rc.y) - (unsigned)nbase : 0xFFFFFFFFu;
+      w1[u] = (int)rc.x >> 5;        // wyq, signed
+      w2[u] = (int)(rc.y >> 5);      // wyyq, unsigned
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (nd[u] >= (unsigned)n) continue;
+      const CscNode t = tab[nd[u]];
+      if (t.nb <= 0) continue;
+      const float x = __uint_as_float(e[u].y);
+      const int v1 = w1[u] - t.m1, v2 = w2[u] - t.m2;
+      const int b = bin_fast(x, t.mn, t.st, t.nb);
+      const unsigned addr = hbase + (unsigned)(((int)nd[u] * nbs + b) * 12);
+      sh_inc(addr);
+      const unsigned o1 = sh_add(addr + 4u, (unsigned)v1), o2 = sh_add(addr + 8u, (unsigned)v2);
+      const unsigned f1 = wrap_bit(o1, v1), f2 = wrap_bit(o2, v2);
+      if ((f1 | f2) >> 31)
+        eng_carry(a.acc, a.descs, nbase + (int)nd[u], a.cols, col, nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
+                  (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
+      if (x == x) {
+        const unsigned ex = enc_f32_bits(__float_as_uint(x));
+        if (ex < s_rmin[nd[u]]) atomicMin(&s_rmin[nd[u]], ex);
+        if (ex > s_rmax[nd[u]]) atomicMax(&s_rmax[nd[u]], ex);
+      }
+    }
+  }
+  __syncthreads();
+  // flush: copies added up, centring undone with the bin's own count
+  for (int t = tid; t < n * nbs; t += THREADS) {
+    const int g = t / nbs, b = t - g * nbs;
+    unsigned long long nc = 0;
+    long long n1 = 0, n2 = 0;
+    for (int cp = 0; cp < copies; cp++) {
+      const unsigned* w = h + ((cp * n + g) * nbs + b) * 3;
+      nc += w[0];
+      n1 += (long long)w[1] - (long long)kWyBias;
+      n2 += (long long)w[2] - (long long)kWyBias;
+    }
+    if (nc | (unsigned long long)n1 | (unsigned long long)n2) {
+      unsigned long long* gp = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(nbase + g) * a.cols + col) * nb1 + b) * 3;
+      const long long s1 = n1 + (long long)nc * tab[g].m1, s2 = n2 + (long long)nc * tab[g].m2;
+      if (nc) atomicAdd(gp, nc);
+      if (s1) atomicAdd(gp + 1, (unsigned long long)s1);
+      if (s2) atomicAdd(gp + 2, (unsigned long long)s2);
+    }
+  }
+  for (int g = tid; g < n; g += THREADS) {
+    if (s_rmin[g] != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)(nbase + g) * a.cols + col], s_rmin[g]);
+    if (s_rmax[g] != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)(nbase + g) * a.cols + col], s_rmax[g]);
+  }
+}
+
+// The zero cells of every tracked (node, column): totals of the node minus what the column's nonzeros added.
+__global__ void __launch_bounds__(256) eng_csc_zero_kernel(int n_nodes, int cols, const h2ok_col_desc* __restrict__ descs, int nb1,
+                                                           const unsigned long long* __restrict__ tot, int64_t* __restrict__ acc,
+                                                           uint32_t* __restrict__ min2_enc, uint32_t* __restrict__ maxin_enc) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t pair = (int64_t)blockIdx.x * 8 + warp;
+  if (pair >= (int64_t)n_nodes * cols) return;
+  const h2ok_col_desc d = descs[pair];
+  if (d.nbin <= 0) return;
+  const int g = (int)(pair / cols);
+  long long* cell = reinterpret_cast<long long*>(acc) + pair * nb1 * 3;
+  long long nc = 0, n1 = 0, n2 = 0;
+  for (int b = lane; b <= d.nbin; b += 32) {
+    nc += cell[3 * b];
+    n1 += cell[3 * b + 1];
+    n2 += cell[3 * b + 2];
+  }
+  for (int o = 16; o; o >>= 1) {
+    nc += __shfl_xor_sync(0xffffffffu, nc, o);
+    n1 += __shfl_xor_sync(0xffffffffu, n1, o);
+    n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+  }
+  if (lane != 0) return;
+  const long long zc = (long long)tot[3 * g] - nc;
+  if (zc <= 0) return;
+  const int bz = bin_of(0.0f, d.min, d.step, d.nbin);
+  cell[3 * bz] += zc;
+  cell[3 * bz + 1] += (long long)tot[3 * g + 1] - n1;
+  cell[3 * bz + 2] += (long long)tot[3 * g + 2] - n2;
+  const unsigned ez = enc_f32_bits(__float_as_uint(0.0f));
+  if (ez < min2_enc[pair]) min2_enc[pair] = ez;
+  if (ez > maxin_enc[pair]) maxin_enc[pair] = ez;
+}
+
+// ------------------------------------------------------------------------------------------------ a6 + regroup
+// Routing walks the rows in their ORIGINAL order (row -> node map nid16), not the node-grouped records: every access
+// is then a stream.  The value the split needs is not gathered from the row-major copy — a gather of one float per
+// row costs a 128-byte DRAM access each (ncu: 13.2 GB per level at 100M rows, profiles/r02_route_scatter_r01code_*) —
+// but decided from an 8-bit order-preserving code of the cell, kept column-major (code8, one byte per cell, written
+// once per data set): code(x) < code(splat) => x < splat, code(x) > code(splat) => x > splat, and only a row whose
+// code EQUALS the threshold's (~1/255 of a column's rows) reads its float and compares exactly as H2O does
+// (DecidedNode: x >= splat).  A warp of 32 consecutive rows reads one sector per distinct split column among its
+// rows, so a level streams (distinct split columns) x rows bytes at most.
+//
+// Regrouping is a stable-by-range multi-way partition in the same row order: every CTA owns one contiguous range of
+// rows in both kernels; eng_route_kernel counts its rows per child, eng_scan_kernel turns the [child][CTA] counts
+// into first positions, eng_scatter_kernel writes the next level's records {row, targets - child's offset} there.
+// Rows of a node stay ascending up to the order inside a 512-row tile — integer sums do not depend on it.
 constexpr int kRouteThreads = 512;
-constexpr unsigned kNoNid = 0xFFFFu;
+constexpr unsigned kNoNid = kNoNidConst;
 
 // order-preserving code of a non-NaN float: -0 counts as +0 so that the codes agree with float comparison
 __device__ __forceinline__ unsigned enc_key(float x) { return enc_f32_bits(__float_as_uint(__fadd_rn(x, 0.0f))); }
@@ -922,7 +910,7 @@ __device__ __forceinline__ int64_t route_per(int64_t rows, int G) {
 }
 
 __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
-    const float* __restrict__ XT, int64_t ldt, const SpSlot* __restrict__ slots, int nblk, const float* __restrict__ ovf,
+    const float* __restrict__ XT, int64_t ldt, const uint2* const* __restrict__ cptr, const int64_t* __restrict__ clen,
     const uint8_t* __restrict__ code8, int64_t ld8,
     const unsigned* __restrict__ thr, int64_t rows, int n_nodes, const h2ok_split* __restrict__ splits,
     const int32_t* __restrict__ child_ids, int gid_base, uint16_t* __restrict__ nid16, int32_t* __restrict__ leaf,
@@ -965,7 +953,7 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
           if (c == 255u) way = (t.na == H2OK_NA_LEFT) ? 0 : 1;
           else if (t.na == H2OK_NA_VS_REST) way = 0;
           else if (c != t.cs) way = c > t.cs ? 1 : 0;
-          else way = (XT ? XT[r * ldt + t.col] : sp_get(slots, nblk, ovf, r, t.col)) >= t.splat ? 1 : 0;  // code tie: the float decides
+          else way = (XT ? XT[r * ldt + t.col] : csc_get(cptr, clen, r, t.col)) >= t.splat ? 1 : 0;  // code tie: the float decides
           const int ch = way ? t.c1 : t.c0;
           if (ch < 0) leaf[r] = t.leaf0 + 1 + way;
           else next = (unsigned)ch;
@@ -1190,14 +1178,13 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
     if (err == cudaSuccess) err = cudaMalloc(p, bytes);
   };
   if (sparse) {
-    e.nblk = (cols + kSpCols - 1) / kSpCols;
-    // dense rows for the (row, block) pairs with more nonzeros than a slot holds: room for one pair in sixteen
-    const size_t cap = (size_t)rows * (size_t)e.nblk / 16 + 4096;
-    e.ovf_cap = cap > 0xFFFFFF00ull ? 0xFFFFFF00u : (unsigned)cap;
-    A(&e.slots, sizeof(SpSlot) * (size_t)rows * (size_t)e.nblk);
-    A((void**)&e.ovf, sizeof(float) * kSpCols * (size_t)e.ovf_cap);
-    A((void**)&e.ovf_count, sizeof(unsigned));
-    if (err == cudaSuccess) err = cudaMemset(e.ovf_count, 0, sizeof(unsigned));
+    A((void**)&e.csc_ptr, sizeof(uint2*) * (size_t)cols);
+    A((void**)&e.csc_len, sizeof(int64_t) * (size_t)cols);
+    A((void**)&e.node_tot, sizeof(unsigned long long) * 3 * kEngMaxNodes);
+    A((void**)&e.rec, sizeof(uint2) * (size_t)rows);
+    if (err == cudaSuccess) err = cudaMemset(e.csc_ptr, 0, sizeof(uint2*) * (size_t)cols);
+    if (err == cudaSuccess) err = cudaMemset(e.csc_len, 0, sizeof(int64_t) * (size_t)cols);
+    e.nnz = 0;
   } else {
     A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   }
@@ -1206,8 +1193,10 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
   A((void**)&e.cmin, sizeof(uint32_t) * (size_t)cols);
   A((void**)&e.cmax, sizeof(uint32_t) * (size_t)cols);
   for (int k = 0; k < 2; k++) {
-    A((void**)&e.gidx[k], sizeof(int32_t) * (size_t)rows);
-    A((void**)&e.gval[k], sizeof(uint2) * (size_t)rows);
+    if (!sparse) {  // sparse storage keeps no row records
+      A((void**)&e.gidx[k], sizeof(int32_t) * (size_t)rows);
+      A((void**)&e.gval[k], sizeof(uint2) * (size_t)rows);
+    }
     if (weighted) A((void**)&e.gw[k], sizeof(int32_t) * (size_t)rows);
     A((void**)&e.seg[k], sizeof(int32_t) * kSegInts);
     A((void**)&e.mnode[k], sizeof(int32_t) * 2 * kEngMaxNodes);
@@ -1217,9 +1206,7 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
   A((void**)&e.leaf, sizeof(int32_t) * (size_t)rows);
   A((void**)&e.err, sizeof(int32_t));
   A((void**)&e.na_flag, sizeof(int32_t));
-  A((void**)&e.load_err, sizeof(int32_t));
-  if (err == cudaSuccess) err = cudaMemset(e.load_err, 0, sizeof(int32_t));
-  e.load_checked = false;
+
   if (err == cudaSuccess) err = cudaMemset(e.err, 0, sizeof(int32_t));
   if (err == cudaSuccess) err = cudaMemset(e.na_flag, 0, sizeof(int32_t));
   e.na_known = false;
@@ -1231,12 +1218,15 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
 
 void engine_free(Engine& e) {
   cudaFree(e.XT); cudaFree(e.code8); cudaFree(e.thr); cudaFree(e.cmin); cudaFree(e.cmax);
-  cudaFree(e.slots); cudaFree(e.ovf); cudaFree(e.ovf_count);
-  e.slots = nullptr;
-  e.ovf = nullptr;
-  e.ovf_count = nullptr;
+  for (void* p : e.csc_blocks) cudaFree(p);
+  e.csc_blocks.clear();
+  cudaFree(e.csc_ptr); cudaFree(e.csc_len); cudaFree(e.node_tot); cudaFree(e.rec);
+  e.rec = nullptr;
+  e.csc_ptr = nullptr;
+  e.csc_len = nullptr;
+  e.node_tot = nullptr;
   e.sparse = false;
-  e.nblk = 0;
+  e.nnz = 0;
   e.cmin = e.cmax = nullptr;
   for (int k = 0; k < 2; k++) {
     cudaFree(e.gidx[k]); cudaFree(e.gval[k]); cudaFree(e.gw[k]); cudaFree(e.seg[k]); cudaFree(e.mnode[k]);
@@ -1244,8 +1234,7 @@ void engine_free(Engine& e) {
   }
   cudaFree(e.nid16); cudaFree(e.cta_cnt); cudaFree(e.leaf); cudaFree(e.err); cudaFree(e.na_flag);
   e.na_flag = nullptr;
-  cudaFree(e.load_err);
-  e.load_err = nullptr;
+
   e.XT = nullptr;
   e.code8 = nullptr;
   e.thr = nullptr;
@@ -1271,14 +1260,56 @@ cudaError_t engine_set_weighted(Engine& e, bool weighted) {
 
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s) {
   if (e.sparse) {
-    if (col0 % kSpCols) return cudaErrorInvalidValue;  // column blocks arrive whole (the last one may be short)
-    for (int c = 0; c < ncols; c += kSpCols) {
-      const int nc = ncols - c < kSpCols ? ncols - c : kSpCols;
-      eng_load_sparse_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(X + (int64_t)c * ld, ld, e.rows, nc, static_cast<SpSlot*>(e.slots),
-                                                               e.nblk, (col0 + c) / kSpCols, e.ovf, e.ovf_count, e.ovf_cap,
-                                                               e.load_err);
+    // count the nonzeros of every (column, chunk), lay the columns out one after the other in one allocation per
+    // block of columns, then compact (rows stay ascending inside a column).  One blocking round trip per block: this
+    // happens once per data set.
+    const int n_chunks = (int)((e.rows + kCscChunk - 1) / kCscChunk);
+    const size_t n_cnt = (size_t)ncols * n_chunks;
+    unsigned* d_cnt = nullptr;
+    int64_t* d_start = nullptr;
+    cudaError_t err = cudaMalloc((void**)&d_cnt, sizeof(unsigned) * n_cnt);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&d_start, sizeof(int64_t) * n_cnt);
+    std::vector<unsigned> h_cnt(n_cnt);
+    std::vector<int64_t> h_start(n_cnt), h_len(ncols);
+    std::vector<uint2*> h_ptr(ncols);
+    uint2* block = nullptr;
+    if (err == cudaSuccess) {
+      eng_csc_count_kernel<<<dim3((unsigned)n_chunks, (unsigned)ncols), 1024, 0, s>>>(X, ld, e.rows, n_chunks, d_cnt);
+      err = cudaMemcpyAsync(h_cnt.data(), d_cnt, sizeof(unsigned) * n_cnt, cudaMemcpyDeviceToHost, s);
     }
-    e.load_checked = false;
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+    int64_t total = 0;
+    if (err == cudaSuccess) {
+      for (int c = 0; c < ncols; c++) {
+        const int64_t first = total;
+        for (int k = 0; k < n_chunks; k++) {
+          h_start[(size_t)c * n_chunks + k] = total;
+          total += h_cnt[(size_t)c * n_chunks + k];
+        }
+        h_len[c] = total - first;
+      }
+      err = cudaMalloc((void**)&block, sizeof(uint2) * (size_t)(total > 0 ? total : 1));
+    }
+    if (err == cudaSuccess) {
+      e.csc_blocks.push_back(block);
+      int64_t off = 0;
+      for (int c = 0; c < ncols; c++) {
+        h_ptr[c] = block + off;
+        off += h_len[c];
+      }
+      e.nnz += total;
+      err = cudaMemcpyAsync(d_start, h_start.data(), sizeof(int64_t) * n_cnt, cudaMemcpyHostToDevice, s);
+    }
+    if (err == cudaSuccess) err = cudaMemcpyAsync(e.csc_ptr + col0, h_ptr.data(), sizeof(uint2*) * ncols, cudaMemcpyHostToDevice, s);
+    if (err == cudaSuccess) err = cudaMemcpyAsync(e.csc_len + col0, h_len.data(), sizeof(int64_t) * ncols, cudaMemcpyHostToDevice, s);
+    if (err == cudaSuccess) {
+      eng_csc_fill_kernel<<<dim3((unsigned)n_chunks, (unsigned)ncols), 1024, 0, s>>>(X, ld, e.rows, n_chunks, d_start, block);
+      err = cudaGetLastError();
+    }
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);  // the host vectors above are read by the copies
+    cudaFree(d_cnt);
+    cudaFree(d_start);
+    if (err != cudaSuccess) return err;
   } else {
     dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
     eng_load_kernel<<<grid, 256, 0, s>>>(X, ld, e.rows, col0, ncols, e.XT, e.ldt);
@@ -1347,37 +1378,60 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
   if (n_nodes < 1 || n_nodes >= kEngMaxNodes) return cudaErrorInvalidValue;
   const int nbs = level_nb1 > 0 && level_nb1 < nb1 ? level_nb1 : nb1;
   if (e.sparse) {
-    if ((size_t)kSpCols * nbs * 12 > (size_t)kHistSmemCap) return cudaErrorInvalidValue;
+    if (!e.wyq_rows) return cudaErrorInvalidValue;
     e.n_nodes = n_nodes;
-    SpHistArgs a{};
-    a.slots = static_cast<const SpSlot*>(e.slots);
-    a.nblk = e.nblk;
-    a.ovf = e.ovf;
-    a.cols = e.cols;
-    a.gidx = e.gidx[e.cur];
-    a.gval = e.gval[e.cur];
-    a.mnode = e.mnode[e.cur];
-    a.seg = e.seg[e.cur];
-    a.n_nodes = n_nodes;
-    a.descs = descs;
-    a.nb1 = nb1;
-    a.nbs = nbs;
-    a.copies = 1;
-    while (a.copies < 4 && (size_t)kSpCols * nbs * 12 * (a.copies * 2) <= (size_t)kHistSmemCap) a.copies *= 2;
-    a.acc = acc;
-    a.min2_enc = min2_enc;
-    a.maxin_enc = maxin_enc;
-    a.err = e.err;
+    // nodes per pass: descriptor table + range slots + at least one histogram copy per node must fit one CTA
+    const size_t per_node = sizeof(CscNode) + 8 + (size_t)nbs * 12;
+    // What a CTA takes when its histogram allows a choice: 56 KB.  More copies (112 KB) cut bank conflicts but leave the
+    // SM 30 KB of L1 for the row-record gathers: 14 ms per level against 8.5 ms on config 4 (32 nodes, 64 bins).
+    const size_t two_per_sm = 56 * 1024;
+    int group = (int)((size_t)kHistSmemCap / per_node);
+    if (group < 1) return cudaErrorInvalidValue;
+    if (group > n_nodes) group = n_nodes;
+    cudaError_t err = cudaMemsetAsync(e.node_tot, 0, sizeof(unsigned long long) * 3 * (size_t)n_nodes, s);
+    if (err != cudaSuccess) return err;
+    eng_node_totals_kernel<<<4 * e.sms, 512, sizeof(int) * 5 * (size_t)n_nodes, s>>>(e.rows, e.nid16, e.wyq_rows, e.wyyq_rows,
+                                                                                    n_nodes, e.node_tot, e.rec);
     static std::atomic<bool> attr_done[64];
     int dev = 0;
     cudaGetDevice(&dev);
     if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
-      cudaError_t ea = cudaFuncSetAttribute(eng_hist_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+      cudaError_t ea = cudaFuncSetAttribute(eng_hist_csc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
       if (ea != cudaSuccess) return ea;
       attr_done[dev & 63].store(true, std::memory_order_release);
     }
-    const dim3 grid((unsigned)e.sms, (unsigned)e.nblk);
-    eng_hist_sparse_kernel<<<grid, 1024, (size_t)a.copies * kSpCols * nbs * 12, s>>>(a);
+    CscHistArgs a{};
+    a.cptr = e.csc_ptr;
+    a.clen = e.csc_len;
+    a.cols = e.cols;
+    a.rec = e.rec;
+    a.mnode = e.mnode[e.cur];
+    a.descs = descs;
+    a.nb1 = nb1;
+    a.nbs = nbs;
+    a.acc = acc;
+    a.min2_enc = min2_enc;
+    a.maxin_enc = maxin_enc;
+    a.err = e.err;
+    // stretches of a column's nonzero list per CTA: about eight CTAs per SM over the whole grid
+    int chunks = (8 * e.sms + e.cols - 1) / e.cols;
+    chunks = chunks < 1 ? 1 : chunks;
+    a.chunks = chunks;
+    for (int base = 0; base < n_nodes; base += group) {
+      a.node_base = base;
+      a.n_nodes = n_nodes - base < group ? n_nodes - base : group;
+      // copies of the histogram (chosen by lane) spread the warp's atomics over more banks; as many as fit while two
+      // CTAs still share the SM, or one CTA's worth when even a single copy needs more than that
+      const size_t one = (size_t)a.n_nodes * (sizeof(CscNode) + 8 + (size_t)nbs * 12);
+      const size_t cap = one <= two_per_sm ? two_per_sm : (size_t)kHistSmemCap;
+      a.copies = 1;
+      while (a.copies < 8 && (size_t)a.n_nodes * (sizeof(CscNode) + 8 + (size_t)nbs * 12 * (a.copies * 2)) <= cap) a.copies *= 2;
+      const size_t smem = (size_t)a.n_nodes * (sizeof(CscNode) + 8 + (size_t)nbs * 12 * a.copies);
+      // four cells per thread in flight (two: 9.2 ms per level on config 4, four: 8.1, eight at one CTA per SM: 15.7)
+      eng_hist_csc_kernel<4><<<dim3((unsigned)chunks, (unsigned)e.cols), kCscThreads, smem, s>>>(a);
+    }
+    const int64_t pairs = (int64_t)n_nodes * e.cols;
+    eng_csc_zero_kernel<<<(unsigned)((pairs + 7) / 8), 256, 0, s>>>(n_nodes, e.cols, descs, nb1, e.node_tot, acc, min2_enc, maxin_enc);
     return cudaGetLastError();
   }
   const EngLayout lay = eng_layout(e.cols, nbs);
@@ -1436,14 +1490,14 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   const int G = e.route_ctas;
   const int n_slots = 2 * n_nodes < kEngMaxNodes ? 2 * n_nodes : kEngMaxNodes;  // child ids are < this
   const size_t rsmem = (size_t)n_nodes * sizeof(RouteNode) + (size_t)n_slots * sizeof(int);
-  eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, static_cast<const SpSlot*>(e.slots), e.nblk, e.ovf, e.code8, e.ld8,
-                                                   e.thr, e.rows, n_nodes, splits, child_ids,
+  eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, e.csc_ptr, e.csc_len, e.code8, e.ld8, e.thr, e.rows, n_nodes, splits,
+                                                   child_ids,
                                                    gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots);
   // every level but a tree's last: lay the children's records out for the next histogram pass
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.cta_cnt, G, n_nodes, child_ids, e.seg[nx], splits, e.scale_wy, e.scale_wyy,
                                      e.weighted ? nullptr : e.q_dev,
                                      e.mnode[e.cur], e.mnode[nx]);
-  if (regroup) {
+  if (regroup && !e.sparse) {
     const size_t ncp = (size_t)(n_slots + 1) & ~(size_t)1;
     const size_t ssmem = ncp * (4 * sizeof(int) + sizeof(int2)) +
                          (size_t)kScatTile * (sizeof(uint2) + sizeof(int) + sizeof(uint16_t) + (e.weighted ? sizeof(int) : 0));
@@ -1469,21 +1523,6 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   if (err != cudaSuccess) return err;
   e.cur = nx;
   e.n_nodes = 0;  // the caller says how many children there are (build_level / nid)
-  return cudaSuccess;
-}
-
-cudaError_t engine_check_load(Engine& e, cudaStream_t s, bool* too_dense) {
-  *too_dense = false;
-  if (!e.sparse) return cudaSuccess;
-  if (!e.load_checked) {
-    int flag = 0;
-    cudaError_t err = cudaMemcpyAsync(&flag, e.load_err, sizeof(int), cudaMemcpyDeviceToHost, s);
-    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
-    if (err != cudaSuccess) return err;
-    e.load_failed = flag != 0;
-    e.load_checked = true;
-  }
-  *too_dense = e.load_failed;
   return cudaSuccess;
 }
 

@@ -207,11 +207,6 @@ int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
   if (!L.have_tree) return fail(H2OK_ERR_STATE, "%s", "loop_level before loop_begin_tree");
   if (L.n_nodes < 1 || L.depth >= L.params.max_depth) return fail(H2OK_ERR_STATE, "%s", "loop_level: the tree is finished");
   CK(cudaSetDevice(c->device));
-  bool too_dense = false;
-  CK(engine_check_load(c->eng, c->stream, &too_dense));
-  if (too_dense)
-    return fail(H2OK_ERR_UNSUPPORTED, "%s", "sparse storage: more (row, block) pairs with over 12 nonzeros than the overflow store "
-                                            "holds (one pair in sixteen); create the shard without H2OK_TREE_SPARSE");
   const int n = L.n_nodes, R = c->comm_ranks;
   L.out = out;
   L.pairs = (int64_t)n * L.cols;
@@ -500,7 +495,6 @@ int32_t h2ok_hist_tree_load_synth(h2ok_ctx* c, int32_t shape, uint64_t seed, int
   const int cols = c->eng.cols;
   int64_t per = ((int64_t)512 << 20) / (4 * ld);  // columns per staging block (<= 512 MB)
   per = per < 1 ? 1 : (per > cols ? cols : per);
-  if (c->eng.sparse) per = per < 64 ? 64 : per / 64 * 64;  // sparse storage takes whole blocks of 64 columns
   CK(c->X.ensure((size_t)ld * per));
   for (int c0 = 0; c0 < cols; c0 += (int)per) {
     const int nc = cols - c0 < per ? cols - c0 : (int)per;

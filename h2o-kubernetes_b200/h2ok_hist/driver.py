@@ -231,8 +231,6 @@ class EngineShard(CudaShard):
     def _blocks(self):
         """Column blocks whose column-major staging copy stays under stage_bytes."""
         per = max(1, min(self.cols, self.stage_bytes // (4 * self.ld)))
-        if self.sparse:
-            per = max(64, per // 64 * 64)  # sparse storage takes whole blocks of 64 columns
         return [(c0, min(per, self.cols - c0)) for c0 in range(0, self.cols, per)]
 
     def _load_block(self, stage, c0, nc):

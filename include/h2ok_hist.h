@@ -274,12 +274,12 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
  * H2OK_MAX_BINS runs (64 columns per block up to 299 bins + NA, 32 up to 599, 16 beyond).
  *
  * H2OK_TREE_SPARSE (an input format beyond dense fp32; H2O keeps mostly-zero columns in sparse
- * chunks too): the shard is stored as one 64-byte slot per (row, block of 64 columns) with the block's nonzero cells —
- * up to 12 inline, denser (row, block) pairs in an overflow store sized for one pair in sixteen — instead of 256 bytes
- * of floats, and the histogram pass touches the nonzeros only; what the zero cells contribute follows exactly from the
- * node totals at the flush.  Same results bit for bit.  Unweighted trees, at most 299 bins + NA, column blocks loaded
- * in multiples of 64 columns; a matrix too dense for the overflow store makes the first level fail (H2OK_ERR_UNSUPPORTED).
- * Algorithmic bytes per level: nnz * 5 + rows * blocks * 4 (values, column bytes, counts) + rows * 8 + histogram. */
+ * chunks too): the shard is stored column by column as the list of its nonzero cells {row, value} — 8 bytes per
+ * nonzero instead of 4 bytes per cell — and the histogram pass streams those lists, every lane on a nonzero cell, with
+ * the row's node and targets looked up by row; what the zero cells contribute follows exactly from the node totals
+ * afterwards.  No row records are kept or regrouped.  Same results bit for bit, any density (it pays below ~25 %
+ * nonzeros).  Unweighted trees only.  Algorithmic bytes per level: nnz * 8 + rows * 10 (row -> node map and targets,
+ * once) + histogram. */
 int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t flags /*H2OK_TREE_**/);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
 /* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in

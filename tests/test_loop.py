@@ -125,15 +125,14 @@ def test_loop_config4_shape_matches_oracle(eshard, oracle):
 
 
 @pytest.mark.parametrize("rows,cols,nbins,depth,na", [(5, 3, 16, 3, 0), (4099, 70, 32, 5, 20), (60001, 130, 64, 6, 5),
-                                                      (30011, 64, 256, 5, 0), (20000, 200, 128, 4, 0)])
+                                                      (30011, 64, 256, 5, 0), (20000, 200, 128, 4, 0), (50001, 9, 256, 8, 10)])
 def test_sparse_storage_matches_oracle(sshard, oracle, rows, cols, nbins, depth, na):
-    """H2OK_TREE_SPARSE: nonzero-only storage and histogram pass, zeros accounted for at the flush — same bits as the
-    oracle at every level, on 90 %-zero data with NaNs, partly filled column blocks and (row, block) pairs that overflow
-    the 12 inline nonzeros."""
+    """H2OK_TREE_SPARSE: nonzero-only storage and histogram pass, zeros accounted for afterwards — same bits as the
+    oracle at every level, on 90 %-zero data with NaNs, dense stretches, and negative zeros."""
     X, y, _ = oracle.synth(abi.SHAPE_SPARSE, 700 + rows, 0, rows, cols, na_permille=na)
-    X[min(2, cols - 1), : rows // 2] = 1.5 + np.arange(rows // 2, dtype=np.float32) % 7  # a dense stretch: overflow slots
+    X[min(2, cols - 1), : rows // 2] = 1.5 + np.arange(rows // 2, dtype=np.float32) % 7  # a dense stretch of one column
     if cols > 64:
-        X[64:min(cols, 96), : rows // 40] += np.float32(0.25)  # a dense block for some rows (the store holds 1 pair in 16)
+        X[64:min(cols, 96), : rows // 3] += np.float32(0.25)  # a block of columns without zeros for a third of the rows
     X[0, :rows] = np.where(np.arange(rows) % 5 == 0, -0.0, X[0, :rows])  # negative zeros are zeros
     params = abi.Params.make(nbins=nbins, max_depth=depth, min_rows=1 if rows < 1000 else 5)
     check_tree(sshard, oracle, X, rows, y, None, params, host_out=(rows % 2 == 1))
@@ -141,30 +140,13 @@ def test_sparse_storage_matches_oracle(sshard, oracle, rows, cols, nbins, depth,
 
 
 def test_sparse_storage_all_zero_and_all_dense_columns(sshard, oracle):
-    rows, cols = 2001, 66
-    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 3, 0, rows, cols)  # no zeros at all: every (row, block) pair overflows
+    rows, cols = 9001, 66
+    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 3, 0, rows, cols)  # no zeros at all except the columns set below
     X[5, :rows] = 0.0
     X[65, :rows] = 0.0
     X[7, :rows] = np.where(np.arange(rows) % 2 == 0, 0.0, -1.0)
     levels = check_tree(sshard, oracle, X, rows, y, None, abi.Params.make(nbins=32, max_depth=4))
     assert len(levels) == 4
-
-
-def test_sparse_storage_reports_data_that_is_too_dense(sshard, oracle):
-    """A matrix without zeros does not fit the overflow store (one (row, block) pair in sixteen): a loud error."""
-    rows, cols = 40000, 64
-    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 3, 0, rows, cols)
-    sshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()))
-    torch.cuda.synchronize()
-    from h2ok_hist.driver import TreeLoop
-
-    from h2ok_hist import capi
-
-    loop = TreeLoop(sshard, abi.Params.make(nbins=32, max_depth=2))
-    loop.begin_tree()
-    with pytest.raises(capi.H2okError) as e:
-        loop.level()
-    assert e.value.code == abi.ERR_UNSUPPORTED and "overflow store" in str(e.value)
 
 
 def test_sparse_config4_shape_matches_oracle(sshard, oracle):
