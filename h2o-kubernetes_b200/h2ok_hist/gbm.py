@@ -23,11 +23,14 @@ def leaf_gamma(num, den, scale_num, scale_den):
 
 
 class GBMTrainer:
-    def __init__(self, driver, label, dist=abi.DIST_GAUSSIAN, learn_rate=0.1, n_classes=None):
-        """driver: a LevelDriver whose shard already holds X (prepare_data() done); label: device tensor [rows]
-        (multinomial: class ids 0..n_classes-1 as floats)."""
+    def __init__(self, driver, label, dist=abi.DIST_GAUSSIAN, learn_rate=0.1, n_classes=None, keep_levels=True):
+        """driver: a LevelDriver (prepare_data() done) or a TreeLoop (the level loop inside the library) whose shard
+        already holds X; label: device tensor [rows] (multinomial: class ids 0..n_classes-1 as floats).
+        keep_levels: copy every level's splits and child ids to the host (tests); off for timing runs."""
         self.drv, self.shard = driver, driver.shard
         self.lib = driver.lib
+        self.in_library = hasattr(driver, "done_level")
+        self.keep_levels = keep_levels
         self.dist, self.lr = dist, float(learn_rate)
         self.rows = self.shard.rows
         self.label = label
@@ -65,20 +68,32 @@ class GBMTrainer:
         """One tree on the targets in shard.y, its GammaPass and AddTreeContributions into f_out."""
         sh, rows = self.shard, self.rows
         levels = []
+        if self.in_library:  # one C call per level; the quantised targets live inside the context
+            def after(loop):
+                if self.keep_levels:
+                    lv = loop.done_level()
+                    levels.append((lv["splits"], lv["child_ids"]))
 
-        def keep(d, n, nch):
-            levels.append((d.shard.splits_np(n), d.shard.child_ids[: 2 * n].cpu().numpy().copy()))
+            self.drv.train_tree(after_level=after)
+            v = self.drv.view()
+            n_codes, q = 3 * v.gid_base, v.quant
+            p_wyq, p_wq = C.c_void_p(v.d_wyq), C.c_void_p(v.d_wq) if v.d_wq else None
+        else:
+            def keep(d, n, nch):
+                if self.keep_levels:
+                    levels.append((d.shard.splits_np(n), d.shard.child_ids[: 2 * n].cpu().numpy().copy()))
 
-        self.drv.train_tree(inspect=keep)
-        n_codes = 3 * self.drv.gid_base
-        q = sh.quant
+            self.drv.train_tree(inspect=keep)
+            n_codes, q = 3 * self.drv.gid_base, sh.quant
+            p_wyq, p_wq = _ptr(sh.wyq), _ptr(sh.wq)
         if den_scale is None:  # gaussian
-            denq, den_scale = (sh.wq, q.scale_w) if sh.weighted else (None, 1.0)
+            p_den, den_scale = (p_wq, q.scale_w) if sh.weighted else (None, 1.0)
+        else:
+            p_den = _ptr(denq)
         num = torch.zeros(n_codes, dtype=torch.int64, device=sh.device)
         den = torch.zeros(n_codes, dtype=torch.int64, device=sh.device)
         leaf = sh.leaf
-        self.lib.call("h2ok_hist_gbm_gamma_pass_dev", sh.ctx, _ptr(leaf), _ptr(sh.wyq), _ptr(denq), rows, n_codes,
-                      _ptr(num), _ptr(den))
+        self.lib.call("h2ok_hist_gbm_gamma_pass_dev", sh.ctx, _ptr(leaf), p_wyq, p_den, rows, n_codes, _ptr(num), _ptr(den))
         if _world() > 1:
             dist_.all_reduce(num)
             dist_.all_reduce(den)

@@ -231,3 +231,70 @@ def test_loop_synth_entry_points_need_no_torch_memory(lib, oracle):
         assert [int(x) for x in got] == oracle_lib.tree_checksum(levels, leaf)
     finally:
         lib.call("h2ok_hist_destroy", h)
+
+
+# ------------------------------------------------------------------------------------------------ a9 on the loop
+@pytest.mark.parametrize("sparse", [False, True])
+def test_multinomial_k10_on_the_loop_tracks_oracle(eshard, sshard, oracle, sparse):
+    """BASELINE config 4's trainer: 10-class multinomial GBM (ten trees per iteration on softmax residuals) through the
+    level loop inside the library, on dense and on sparse storage.  The first iteration starts from zero scores (exp is
+    exact on both sides): its ten trees and leaf values equal the oracle's bit for bit; later iterations go through
+    expf (device vs libm), so the check is the logloss trace to 1e-6."""
+    from h2ok_hist.driver import TreeLoop
+    from h2ok_hist.gbm import GBMTrainer
+
+    sh = sshard if sparse else eshard
+    rows, cols, K = 30000, 70, 10
+    X, y, _ = oracle.synth(abi.SHAPE_SPARSE, 5, 0, rows, cols, na_permille=0 if sparse else 5)
+    score = X[:K, :rows].T @ np.linspace(1.0, 2.0, K * K).reshape(K, K).astype(np.float32) + y[:rows, None] * 0.2
+    label = score.argmax(axis=1).astype(np.float32)
+    params = abi.Params.make(nbins=32, max_depth=4, min_rows=5)
+    sh.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(label))
+    loop = TreeLoop(sh, params)
+    tr = GBMTrainer(loop, torch.from_numpy(label).cuda(), abi.DIST_MULTINOMIAL, learn_rate=0.3, n_classes=K)
+    assert tr.init_f() == 0.0
+    ref = oracle_lib.OracleGBM(oracle, X, rows, label, None, params, abi.DIST_MULTINOMIAL, 0.3, n_classes=K)
+
+    def logloss(f):
+        z = f.astype(np.float64)
+        z = z - z.max(axis=0, keepdims=True)
+        logp = z - np.log(np.exp(z).sum(axis=0, keepdims=True))
+        return float(-logp[label.astype(np.int64), np.arange(rows)].mean())
+
+    trace = [tr.loss()]
+    assert trace[0] == pytest.approx(np.log(K), rel=1e-12)
+    for it in range(2):
+        gs = tr.step()
+        grs = ref.step()
+        torch.cuda.synchronize()
+        if it == 0:
+            for k in range(K):
+                assert gs[k].tobytes() == grs[k].tobytes(), f"class {k}: leaf values differ"
+                for (s_gpu, ids_gpu), (s_ref, ids_ref) in zip(tr.trees[k]["levels"], ref.trees[k]["levels"]):
+                    assert s_gpu.tobytes() == s_ref.tobytes() and np.array_equal(ids_gpu, ids_ref)
+            assert np.array_equal(tr.f[:, :rows].cpu().numpy(), ref.f)
+        trace.append(tr.loss())
+        assert trace[-1] == pytest.approx(logloss(ref.f), rel=1e-6)
+    assert all(b < a for a, b in zip(trace, trace[1:]))
+    assert len(tr.trees) == 2 * K
+
+
+def test_gaussian_on_the_loop_is_bit_exact(eshard, oracle):
+    from h2ok_hist.driver import TreeLoop
+    from h2ok_hist.gbm import GBMTrainer
+
+    rows, cols = 30011, 10
+    X, y, w = oracle.synth(abi.SHAPE_WIDE64, 321, 0, rows, cols, na_permille=10, weight_mode=1)
+    label = (y * 3 + 1).astype(np.float32)
+    params = abi.Params.make(nbins=64, max_depth=4, min_rows=5)
+    eshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(label), torch.from_numpy(w[:rows].copy()))
+    loop = TreeLoop(eshard, params)
+    tr = GBMTrainer(loop, torch.from_numpy(label).cuda(), abi.DIST_GAUSSIAN, learn_rate=0.3)
+    f0 = tr.init_f()
+    ref = oracle_lib.OracleGBM(oracle, X, rows, label, w[:rows].copy(), params, abi.DIST_GAUSSIAN, 0.3)
+    ref.init_f(f0)
+    for t in range(3):
+        g, gr = tr.step(), ref.step()
+        torch.cuda.synchronize()
+        assert g.tobytes() == gr.tobytes(), f"tree {t}: leaf values differ"
+        assert np.array_equal(tr.f.cpu().numpy(), ref.f), f"tree {t}: f differs"
