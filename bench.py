@@ -323,7 +323,7 @@ def run_gpu(args, wl):
     barrier()
 
     # ---- resident path: inputs in HBM when the timed region starts ------------------------------------
-    rec = []  # per timed step: (level, n_nodes, hist_ms, phase_ms)
+    rec = []  # per timed step: (level, n_nodes, hist_ms) — Python-stepped paths only; the library times its own loop
 
     def run_steps(n_steps, record):
         done = 0
@@ -332,8 +332,8 @@ def run_gpu(args, wl):
                 begin()
             lvl, n = loop.depth, loop.n_nodes
             loop.level()
-            if record:
-                rec.append((lvl, n, shard.last_hist_ms(), loop.phase_ms() if in_library else None))
+            if record and not in_library:
+                rec.append((lvl, n, shard.last_hist_ms()))
             done += 1
 
     def begin():
@@ -345,6 +345,8 @@ def run_gpu(args, wl):
     begin()
     run_steps(args.warmup, False)
     sampler = ClockSampler(local)
+    if in_library:
+        loop.reset_phase_stats()
     barrier()
     if rank == 0:
         sampler.start()
@@ -361,6 +363,7 @@ def run_gpu(args, wl):
     total_ms = float(ms.item())
     launches = shard.launches - launches0
     value = rows_total * cols * args.steps / (total_ms * 1e-3)
+    loop_stats = loop.phase_stats(reset=True) if in_library else None
 
     # result checksum: a full tree on the timed inputs, built right after the timed region.  Integer sums make every
     # tree on these inputs the same bits, whatever the number of ranks: the lines of a scaling run must agree.
@@ -372,31 +375,42 @@ def run_gpu(args, wl):
             loop.level()
         checksum = ["%016x" % c for c in loop.checksum(row0)]
 
-    # roofline of the dominant kernel: algorithmic bytes of THIS rank's launches / their device time
-    hist_ms = float(sum(r[2] for r in rec))
-    abytes = float(sum(algo_bytes_level(rows, cols, r[1], bins, sparse_nnz=nnz) for r in rec))
+    # roofline of the dominant kernel: algorithmic bytes of THIS rank's launches / their device time (CUDA events
+    # recorded inside the library around the histogram kernel of every timed level, read back after the timed region)
     peak, peak_src = measured_hbm_peak()
-    achieved = abytes / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
-    per_level = {}
-    for lvl, n, t, ph in rec:
-        per_level.setdefault(lvl, []).append((n, t, ph))
-    level_table = {}
-    for k, v in sorted(per_level.items()):
-        t = float(np.mean([x[1] for x in v]))
-        row = {"nodes": v[0][0], "hist_ms": round(t, 4),
-               "frac": round(algo_bytes_level(rows, cols, v[0][0], bins, sparse_nnz=nnz) / (t * 1e-3) / 1e9 / peak, 4)}
-        if v[0][2] is not None:
-            ph = np.mean([x[2] for x in v], axis=0)
-            row.update(reduce_ms=round(float(ph[1]), 4), search_ms=round(float(ph[2]), 4), route_ms=round(float(ph[3]), 4))
-        level_table[str(k)] = row
-    phases = None
-    if in_library and rec:
-        ph = np.mean([r[3] for r in rec], axis=0)
+    level_table, phases = {}, None
+    if in_library:
+        cnt, nodes, ms = loop_stats
+        hist_ms = float(ms[:, 0].sum())
+        abytes = float(sum(int(cnt[d]) * algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz) for d in range(len(cnt))))
+        for d in range(len(cnt)):
+            if cnt[d]:
+                t = float(ms[d, 0] / cnt[d])
+                level_table[str(d)] = {
+                    "nodes": int(nodes[d]), "hist_ms": round(t, 4),
+                    "frac": round(algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz) / (t * 1e-3) / 1e9 / peak, 4),
+                    "reduce_ms": round(float(ms[d, 2] / cnt[d]), 4), "search_ms": round(float(ms[d, 3] / cnt[d]), 4),
+                    "route_ms": round(float(ms[d, 4] / cnt[d]), 4)}
+        tot = ms.sum(axis=0) / max(1, int(cnt.sum()))
         step_ms = total_ms / args.steps
-        phases = {"hist_ms": round(float(ph[0]), 4), "reduce_ms": round(float(ph[1]), 4), "search_children_ms": round(float(ph[2]), 4),
-                  "route_regroup_ms": round(float(ph[3]), 4), "other_ms": round(float(step_ms - ph.sum()), 4),
-                  "note": "CUDA events inside the library around the phases of every timed level (this rank); other = "
-                          "per-tree set-up (absmax, quantise, root records) and gaps"}
+        phases = {"hist_kernel_ms": round(float(tot[0]), 4), "clear_and_hist_ms": round(float(tot[1]), 4),
+                  "reduce_ms": round(float(tot[2]), 4), "search_children_ms": round(float(tot[3]), 4),
+                  "route_regroup_ms": round(float(tot[4]), 4), "other_ms": round(float(step_ms - tot[1:].sum()), 4),
+                  "levels_timed": int(cnt.sum()),
+                  "note": "device time per level, CUDA events inside the library around the phases of every level of the "
+                          "timed region (this rank), read back afterwards; other = per-tree set-up (absmax, quantise, root "
+                          "records) and gaps"}
+    else:
+        hist_ms = float(sum(r[2] for r in rec))
+        abytes = float(sum(algo_bytes_level(rows, cols, r[1], bins) for r in rec))
+        per_level = {}
+        for lvl, n, t in rec:
+            per_level.setdefault(lvl, []).append((n, t))
+        for k, v in sorted(per_level.items()):
+            t = float(np.mean([x[1] for x in v]))
+            level_table[str(k)] = {"nodes": v[0][0], "hist_ms": round(t, 4),
+                                   "frac": round(algo_bytes_level(rows, cols, v[0][0], bins) / (t * 1e-3) / 1e9 / peak, 4)}
+    achieved = abytes / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
     whole_level_frac = abytes / (total_ms * 1e-3) / 1e9 / peak
 
     # ---- e2e: host buffers in, host buffers out, copies inside the timed region ---------------------------

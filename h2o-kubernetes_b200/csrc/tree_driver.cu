@@ -141,7 +141,20 @@ struct TreeLoop {
   size_t pairs_cap = 0, acc_pairs = 0;
   int32_t* h_nch = nullptr;                      // pinned
   cudaStream_t out_stream = nullptr;             // device -> host copies of a level's results
-  cudaEvent_t ev_ready = nullptr, ev_out = nullptr, ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_e = nullptr;
+  cudaEvent_t ev_ready = nullptr, ev_out = nullptr;
+  // phase timing (loop_set_options): a ring of event sets, read back sixteen levels later — by then they have long
+  // completed, so timing never makes the host wait for a level — and added up per tree depth
+  static constexpr int kRing = 16, kMaxDepth = 64;
+  struct EvSet {
+    cudaEvent_t a = nullptr, h0 = nullptr, h1 = nullptr, b = nullptr, c = nullptr, d = nullptr, e = nullptr;
+    int depth = 0;
+    bool used = false;
+  } ring[kRing];
+  int ring_pos = 0;
+  EvSet* cur_set = nullptr;
+  double ph_sum[kMaxDepth][5] = {};  // per depth: histogram kernel alone, clear + histogram, reduce, search + children, routing
+  int ph_cnt[kMaxDepth] = {};
+  int ph_nodes[kMaxDepth] = {};
   // targets of the current tree (device, owned)
   DevBuf<float> y, w;
   DevBuf<int32_t> wq, wyq, wyyq;
@@ -185,8 +198,11 @@ void loop_free(h2ok_ctx* c) {
   if (L->h_nch) cudaFreeHost(L->h_nch);
   if (L->h_q) cudaFreeHost(L->h_q);
   if (L->out_stream) cudaStreamDestroy(L->out_stream);
-  for (cudaEvent_t e : {L->ev_ready, L->ev_out, L->ev_a, L->ev_b, L->ev_c, L->ev_d, L->ev_e})
+  for (cudaEvent_t e : {L->ev_ready, L->ev_out})
     if (e) cudaEventDestroy(e);
+  for (auto& st : L->ring)
+    for (cudaEvent_t e : {st.a, st.h0, st.h1, st.b, st.c, st.d, st.e})
+      if (e) cudaEventDestroy(e);
   L->y.release(); L->w.release(); L->wq.release(); L->wyq.release(); L->wyyq.release(); L->absmax.release();
   delete L;
   c->loop = nullptr;
@@ -197,6 +213,23 @@ namespace {
 int32_t need_loop(h2ok_ctx* c, const char* who) {
   if (!c) return fail(H2OK_ERR_ARG, "%s: null context", who);
   if (!c->loop) return fail(H2OK_ERR_STATE, "%s before h2ok_hist_loop_create", who);
+  return H2OK_OK;
+}
+
+// one timed level's device times into the per-depth sums (its events completed long ago, or the caller has synchronised)
+int32_t drain_set(TreeLoop& L, TreeLoop::EvSet& st) {
+  float ms[5];
+  CK(cudaEventSynchronize(st.e));
+  CK(cudaEventElapsedTime(&ms[0], st.h0, st.h1));
+  CK(cudaEventElapsedTime(&ms[1], st.a, st.b));
+  CK(cudaEventElapsedTime(&ms[2], st.b, st.c));
+  CK(cudaEventElapsedTime(&ms[3], st.c, st.d));
+  CK(cudaEventElapsedTime(&ms[4], st.d, st.e));
+  if (st.depth < TreeLoop::kMaxDepth) {
+    for (int k = 0; k < 5; k++) L.ph_sum[st.depth][k] += ms[k];
+    L.ph_cnt[st.depth] += 1;
+  }
+  st.used = false;
   return H2OK_OK;
 }
 
@@ -217,7 +250,20 @@ int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
   if (L.p0 > L.pairs) L.p0 = L.pairs;
   L.last = L.depth + 1 >= L.params.max_depth;
   const size_t cell = (size_t)L.nb1 * 3;
-  if (L.phases_timed) CK(cudaEventRecord(L.ev_a, c->stream));
+  L.cur_set = nullptr;
+  if (L.phases_timed) {
+    TreeLoop::EvSet& st = L.ring[L.ring_pos];
+    L.ring_pos = (L.ring_pos + 1) % TreeLoop::kRing;
+    if (st.used) {
+      const int32_t rc = drain_set(L, st);
+      if (rc) return rc;
+    }
+    st.depth = L.depth;
+    st.used = true;
+    L.cur_set = &st;
+    if (L.depth < TreeLoop::kMaxDepth) L.ph_nodes[L.depth] = n;
+    CK(cudaEventRecord(st.a, c->stream));
+  }
   CK(cudaMemsetAsync(L.acc, 0, sizeof(int64_t) * cell * (size_t)(L.chunk * R), c->stream));
   CK(launch_init_enc(L.rng, L.rng + L.pairs_cap, L.pairs, c->stream));
   // H2O halves nbins_top_level per level (Split.nextLevelHistos: max(parent bins >> 1, nbins)): the shared histogram
@@ -231,10 +277,14 @@ int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
   c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * (c->eng.weighted ? 12.0 : 8.0) +
                         (double)L.pairs * cell * 8.0;
   CK(cudaEventRecord(c->ev0, c->stream));
+  if (L.cur_set) CK(cudaEventRecord(L.cur_set->h0, c->stream));
   CK(engine_build_level(c->eng, n, L.descs[L.cur], L.nb1, level_nb1, L.acc, L.rng, L.rng + L.pairs_cap, c->stream));
   CK(cudaEventRecord(c->ev1, c->stream));
   c->timed = true;
-  if (L.phases_timed) CK(cudaEventRecord(L.ev_b, c->stream));
+  if (L.cur_set) {
+    CK(cudaEventRecord(L.cur_set->h1, c->stream));
+    CK(cudaEventRecord(L.cur_set->b, c->stream));
+  }
   return H2OK_OK;
 }
 
@@ -261,7 +311,7 @@ int32_t level_reduce(h2ok_ctx* c) {
 int32_t level_search(h2ok_ctx* c) {
   TreeLoop& L = *c->loop;
   CK(cudaSetDevice(c->device));
-  if (L.phases_timed) CK(cudaEventRecord(L.ev_c, c->stream));
+  if (L.cur_set) CK(cudaEventRecord(L.cur_set->c, c->stream));
   CK(launch_split_points(nullptr, L.acc, nullptr, L.q_dev, L.descs[L.cur], L.p0, L.p1, L.nb1, L.params.min_rows,
                          L.params.min_split_improvement, L.cand, c->stream));
   if (L.checksum && L.p1 > L.p0) {
@@ -310,7 +360,7 @@ int32_t level_finish(h2ok_ctx* c) {
   if (out && (out->min2 || out->maxin))
     CK(launch_finalize(nullptr, L.rng, L.rng + L.pairs_cap, L.pairs, L.nb1, h2ok_quant{}, nullptr, L.rngf, L.rngf + L.pairs_cap,
                        c->stream));
-  if (L.phases_timed) CK(cudaEventRecord(L.ev_d, c->stream));
+  if (L.cur_set) CK(cudaEventRecord(L.cur_set->d, c->stream));
   // results to the host on their own stream, so that routing does not wait for the copies
   CK(cudaEventRecord(L.ev_ready, c->stream));
   CK(cudaStreamWaitEvent(L.out_stream, L.ev_ready, 0));
@@ -329,7 +379,7 @@ int32_t level_finish(h2ok_ctx* c) {
   }
   CK(cudaEventRecord(L.ev_out, L.out_stream));
   CK(engine_apply_splits(c->eng, L.splits, L.child_ids, L.gid_base, n, !L.last, c->stream));
-  if (L.phases_timed) CK(cudaEventRecord(L.ev_e, c->stream));
+  if (L.cur_set) CK(cudaEventRecord(L.cur_set->e, c->stream));
   c->stats.launches += L.last ? 6 : 9;
   return H2OK_OK;
 }
@@ -552,8 +602,9 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->out_stream, cudaStreamNonBlocking);
   for (cudaEvent_t* ev : {&L->ev_ready, &L->ev_out})
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
-  for (cudaEvent_t* ev : {&L->ev_a, &L->ev_b, &L->ev_c, &L->ev_d, &L->ev_e})
-    if (e == cudaSuccess) e = cudaEventCreate(ev);
+  for (auto& st : L->ring)
+    for (cudaEvent_t* ev : {&st.a, &st.h0, &st.h1, &st.b, &st.c, &st.d, &st.e})
+      if (e == cudaSuccess) e = cudaEventCreate(ev);
   if (e != cudaSuccess) {
     loop_free(c);
     return fail(H2OK_ERR_CUDA, "loop_create: %s", cudaGetErrorString(e));
@@ -719,18 +770,26 @@ int32_t h2ok_hist_loop_view(h2ok_ctx* c, h2ok_loop_view* v) {
   return H2OK_OK;
 }
 
-int32_t h2ok_hist_loop_phase_ms(h2ok_ctx* c, float* ms4) {
-  int32_t rc = need_loop(c, "loop_phase_ms");
+int32_t h2ok_hist_loop_phase_stats(h2ok_ctx* c, int32_t reset, int32_t max_depth, int32_t* count_out, int32_t* nodes_out,
+                                   float* ms_out) {
+  int32_t rc = need_loop(c, "loop_phase_stats");
   if (rc) return rc;
-  REQUIRE(ms4 != nullptr, "null pointer");
+  REQUIRE(max_depth >= 0 && max_depth <= TreeLoop::kMaxDepth, "max_depth outside [0, 64]");
+  REQUIRE(max_depth == 0 || (count_out && ms_out), "null pointer");
   TreeLoop& L = *c->loop;
-  if (!L.phases_timed || L.done_depth < 0) return fail(H2OK_ERR_STATE, "%s", "loop_phase_ms: no timed level (loop_set_options)");
   CK(cudaSetDevice(c->device));
-  CK(cudaEventSynchronize(L.ev_e));
-  CK(cudaEventElapsedTime(&ms4[0], L.ev_a, L.ev_b));  // clear + histogram pass
-  CK(cudaEventElapsedTime(&ms4[1], L.ev_b, L.ev_c));  // reduce over ranks
-  CK(cudaEventElapsedTime(&ms4[2], L.ev_c, L.ev_d));  // split search + gather + children
-  CK(cudaEventElapsedTime(&ms4[3], L.ev_d, L.ev_e));  // routing + regrouping
+  CK(cudaStreamSynchronize(c->stream));
+  for (auto& st : L.ring)
+    if (st.used && (rc = drain_set(L, st))) return rc;
+  for (int d = 0; d < max_depth; d++) {
+    count_out[d] = L.ph_cnt[d];
+    if (nodes_out) nodes_out[d] = L.ph_nodes[d];
+    for (int k = 0; k < 5; k++) ms_out[5 * d + k] = (float)L.ph_sum[d][k];
+  }
+  if (reset) {
+    memset(L.ph_sum, 0, sizeof(L.ph_sum));
+    memset(L.ph_cnt, 0, sizeof(L.ph_cnt));
+  }
   return H2OK_OK;
 }
 

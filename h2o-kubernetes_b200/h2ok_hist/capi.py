@@ -57,7 +57,7 @@ SIGNATURES = {
     "h2ok_hist_loop_begin_tree_synth": [vp, u64, i64, i32],
     "h2ok_hist_loop_level": [vp, pLO, C.POINTER(i32), C.POINTER(i32)],
     "h2ok_hist_loop_view": [vp, pLV],
-    "h2ok_hist_loop_phase_ms": [vp, vp],
+    "h2ok_hist_loop_phase_stats": [vp, i32, i32, vp, vp, vp],
     "h2ok_hist_loop_checksum": [vp, i64, vp],
     "h2ok_hist_group_create": [vp, i32, C.POINTER(vp)],
     "h2ok_hist_group_destroy": [vp],

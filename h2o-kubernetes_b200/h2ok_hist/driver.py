@@ -380,10 +380,15 @@ class TreeLoop:
         self.lib.call("h2ok_hist_loop_view", self.shard.ctx, C.byref(v))
         return v
 
-    def phase_ms(self):
-        out = (C.c_float * 4)()
-        self.lib.call("h2ok_hist_loop_phase_ms", self.shard.ctx, out)
-        return [float(x) for x in out]
+    def phase_stats(self, reset=False):
+        """Per tree depth: (levels timed, nodes, [hist kernel, clear + hist, reduce, search + children, routing] ms summed)."""
+        d = int(self.params.max_depth)
+        cnt, nodes, ms = np.zeros(d, np.int32), np.zeros(d, np.int32), np.zeros((d, 5), np.float32)
+        self.lib.call("h2ok_hist_loop_phase_stats", self.shard.ctx, 1 if reset else 0, d, abi.ptr(cnt), abi.ptr(nodes), abi.ptr(ms))
+        return cnt, nodes, ms
+
+    def reset_phase_stats(self):
+        self.lib.call("h2ok_hist_loop_phase_stats", self.shard.ctx, 1, 0, None, None, None)
 
     def checksum(self, row0=0):
         out = (C.c_uint64 * 3)()

@@ -339,7 +339,7 @@ int32_t h2ok_hist_loop_destroy(h2ok_ctx* ctx);
 int32_t h2ok_hist_loop_root_descs(h2ok_ctx* ctx, h2ok_col_desc* descs_out /*[cols], host*/);
 int32_t h2ok_hist_loop_set_reduce(h2ok_ctx* ctx, int32_t mode /*H2OK_REDUCE_**/);
 /* checksum != 0: keep the running result checksums of h2ok_hist_loop_checksum (one extra read of every level's
- * accumulators); time_phases != 0: bracket the phases of every level with CUDA events (h2ok_hist_loop_phase_ms). */
+ * accumulators); time_phases != 0: bracket the phases of every level with CUDA events (h2ok_hist_loop_phase_stats). */
 int32_t h2ok_hist_loop_set_options(h2ok_ctx* ctx, int32_t checksum, int32_t time_phases);
 /* New tree on targets y (and weights w, NULL: unweighted) in original row order: common fixed-point scales over all
  * ranks (chosen on the device: no host round trip), quantised targets, every row back at the root.  Asynchronous.
@@ -352,9 +352,13 @@ int32_t h2ok_hist_loop_begin_tree_synth(h2ok_ctx* ctx, uint64_t seed, int64_t ro
  * (0: the tree is finished; every row then has its leaf code). */
 int32_t h2ok_hist_loop_level(h2ok_ctx* ctx, const h2ok_level_out* out, int32_t* n_nodes_done, int32_t* n_children);
 int32_t h2ok_hist_loop_view(h2ok_ctx* ctx, h2ok_loop_view* view_out);
-/* Device milliseconds of the last level's phases: {clear + histogram pass, reduce over ranks, split search + candidate
- * gather + children, routing + regrouping}. */
-int32_t h2ok_hist_loop_phase_ms(h2ok_ctx* ctx, float* ms_out /*[4]*/);
+/* Device milliseconds of the timed levels since the last reset, added up per tree depth d < max_depth:
+ * count_out[d] levels of nodes_out[d] nodes, ms_out[5*d + k] with k = 0 the histogram kernel alone, 1 clear + histogram
+ * pass, 2 reduce over ranks, 3 split search + candidate gather + children, 4 routing + regrouping.  The events are read
+ * back many levels after they were recorded, so timing never holds the host up; this call synchronises the stream.
+ * nodes_out may be NULL; max_depth 0 with reset != 0 just clears the sums. */
+int32_t h2ok_hist_loop_phase_stats(h2ok_ctx* ctx, int32_t reset, int32_t max_depth, int32_t* count_out, int32_t* nodes_out,
+                                   float* ms_out);
 /* 64-bit checksums of the current tree so far, the same for any number of ranks: out[0] every level's reduced integer
  * accumulators, out[1] the splits {col, bin, na_dir, splat} of every node, out[2] the leaf code of every row.  Each is
  * sum(splitmix64(global index ^ salt) * value) mod 2^64 (tests/oracle_lib.py has the host restatement).  row0 = global

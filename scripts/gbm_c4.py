@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """BASELINE config 4 end to end: K-class (multinomial) GBM on synthetic 10M x 2000 sparse-ish columns, 64 bins —
-K one-class trees per iteration on softmax residuals through h2ok_hist.gbm.GBMTrainer (one GPU, or one rank per GPU
-under torchrun).  Prints one JSON line."""
+K one-class trees per iteration on softmax residuals through h2ok_hist.gbm.GBMTrainer on the level loop inside the
+library (one GPU, or one rank per GPU under torchrun).  --storage sparse (default): column lists of nonzeros
+(H2OK_TREE_SPARSE); dense: the row-wise engine on fp32, as round 1 ran it.  Prints one JSON line."""
 import argparse
 import ctypes as C
 import json
@@ -16,7 +17,7 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 from h2ok_hist import abi  # noqa: E402
-from h2ok_hist.driver import EngineShard, LevelDriver  # noqa: E402
+from h2ok_hist.driver import EngineShard, TreeLoop  # noqa: E402
 from h2ok_hist.gbm import GBMTrainer  # noqa: E402
 
 ap = argparse.ArgumentParser()
@@ -26,6 +27,7 @@ ap.add_argument("--classes", type=int, default=10)
 ap.add_argument("--iters", type=int, default=3)
 ap.add_argument("--depth", type=int, default=6)
 ap.add_argument("--bins", type=int, default=64)
+ap.add_argument("--storage", default="sparse", choices=["sparse", "dense"])
 a = ap.parse_args()
 world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -33,7 +35,8 @@ if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 row0 = a.rows * rank // world
 rows = a.rows * (rank + 1) // world - row0
-shard = EngineShard(local)
+shard = EngineShard(local, sparse=a.storage == "sparse")
+TreeLoop.join_ranks(shard)
 shard.set_data_synth(abi.SHAPE_SPARSE, 20261106, row0, rows, a.cols)
 
 
@@ -48,9 +51,8 @@ def column(c):
 score = torch.stack([column(c) for c in range(a.classes)])
 label = score.argmax(dim=0).float()
 del score
-drv = LevelDriver(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth))
-drv.prepare_data()
-tr = GBMTrainer(drv, label, abi.DIST_MULTINOMIAL, learn_rate=0.3, n_classes=a.classes)
+drv = TreeLoop(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth))
+tr = GBMTrainer(drv, label, abi.DIST_MULTINOMIAL, learn_rate=0.3, n_classes=a.classes, keep_levels=False)
 tr.init_f()
 ll0 = tr.loss()
 torch.cuda.synchronize()
@@ -63,11 +65,11 @@ for _ in range(a.iters):
     per_iter.append(time.perf_counter() - t1)
 sec = time.perf_counter() - t0
 ll = tr.loss()
-levels = sum(len(t["levels"]) for t in tr.trees)
+levels = len(tr.trees) * a.depth  # upper bound: a class tree may stop early
 if rank == 0:
     print(json.dumps({"workload": f"GBM multinomial {a.classes} classes, {a.iters} iterations ({len(tr.trees)} trees) depth {a.depth}, "
                                   f"{a.rows} x {a.cols}, {a.bins} bins",
-                      "n_gpus": world, "path": "engine", "seconds": sec, "s_per_iteration": sec / a.iters,
+                      "n_gpus": world, "path": "in-library loop, %s storage" % a.storage, "seconds": sec, "s_per_iteration": sec / a.iters,
                       "ms_per_tree": 1e3 * sec / len(tr.trees), "ms_per_level": 1e3 * sec / levels,
                       "cells_per_s_per_level": a.rows * a.cols * levels / sec,
                       "logloss_start": ll0, "logloss_end": ll}))

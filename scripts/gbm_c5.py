@@ -14,7 +14,7 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 from h2ok_hist import abi  # noqa: E402
-from h2ok_hist.driver import CudaShard, EngineShard, LevelDriver  # noqa: E402
+from h2ok_hist.driver import CudaShard, EngineShard, LevelDriver, TreeLoop  # noqa: E402
 from h2ok_hist.gbm import GBMTrainer  # noqa: E402
 
 ap = argparse.ArgumentParser()
@@ -32,6 +32,8 @@ if world > 1:
 row0 = a.rows * rank // world
 rows = a.rows * (rank + 1) // world - row0
 shard = (EngineShard if a.path == "engine" else CudaShard)(local)
+if a.path == "engine":
+    TreeLoop.join_ranks(shard)
 shard.set_data_synth(abi.SHAPE_WIDE64, 20261106, row0, rows, a.cols)
 # label = 1 if x0 + x2*x5 - x9 > tau; tau = the expression's median on a sample, so classes balance
 import ctypes as C  # noqa: E402
@@ -49,9 +51,12 @@ expr = column(0) + column(2) * column(5) - column(9)
 tau = expr[: min(rows, 1_000_000)].median()
 label = (expr > tau).float()
 del expr
-drv = LevelDriver(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth))
-drv.prepare_data()
-tr = GBMTrainer(drv, label, abi.DIST_BERNOULLI, learn_rate=0.1)
+if a.path == "engine":  # the level loop inside the library
+    drv = TreeLoop(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth))
+else:
+    drv = LevelDriver(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth))
+    drv.prepare_data()
+tr = GBMTrainer(drv, label, abi.DIST_BERNOULLI, learn_rate=0.1, keep_levels=False)
 tr.init_f()
 ll0 = tr.loss()
 torch.cuda.synchronize()
