@@ -39,6 +39,10 @@ WORKLOADS = {
     # of all ten = one "fused level" of SURVEY.md §8(d)); a step is one class-tree level, ten steps one fused level
     "c4": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, multinomial 10-class targets "
                     "(BASELINE config 4)", rows=10_000_000, cols=2000, bins=64, depth=6, shape=4, k=10, sparse=True),
+    # config 3's matrix binned ONCE against its root descriptors (255 global bins) and kept as one byte per cell
+    "c3-u8": dict(name="GBM histogram build 100M rows x 64 cols pre-binned to u8 codes (255 global bins + NA), depth 8 "
+                       "(BASELINE config 3's matrix, input format of SURVEY.md §8(f) row 4)", rows=100_000_000, cols=64, bins=255,
+                  depth=8, shape=3, u8=True),
     "c4-dense": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, 10-class targets, DENSE "
                           "fp32 storage (BASELINE config 4 as round 1 ran it)", rows=10_000_000, cols=2000, bins=64, depth=6,
                      shape=4, k=10),
@@ -47,12 +51,14 @@ CPU_SAMPLE_ROWS = 2_000_000
 CPU_SAMPLE_CELLS = 128_000_000  # and at most this many cells per level (2M rows x 64 columns; 64K rows x 2000)
 
 
-def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False, sparse_nnz=None):
+def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False, sparse_nnz=None, u8=False):
     """every fp32 cell once, nid + y (+ w) once per row, the fp64 histogram written once.
     Sparse storage (its own formula, include/h2ok_hist.h): 8 bytes per nonzero cell {row, value} instead of 4 bytes per
     cell, and 10 bytes per row (2-byte node + two 4-byte targets)."""
     if sparse_nnz is not None:
         return sparse_nnz * 8.0 + rows * 10.0 + n_nodes * cols * (bins + 1) * 3 * 8.0
+    if u8:  # pre-binned codes: one byte per cell
+        return rows * cols * 1.0 + rows * 8.0 + n_nodes * cols * (bins + 1) * 3 * 8.0
     return rows * cols * 4.0 + rows * (4.0 + 4.0 + (4.0 if weighted else 0.0)) + n_nodes * cols * (bins + 1) * 3 * 8.0
 
 
@@ -297,10 +303,14 @@ def run_gpu(args, wl):
     K = int(wl.get("k", 1))
     sparse = bool(wl.get("sparse")) and args.path != "stateless"
     nnz = rows * cols * (1.0 - 58982.0 / 65536.0) if sparse else None  # the generator zeroes a cell when hash16 < 58982
-    shard = CudaShard(local) if args.path == "stateless" else EngineShard(local, sparse=sparse)
+    u8 = bool(wl.get("u8")) and args.path != "stateless"
+    shard = CudaShard(local) if args.path == "stateless" else EngineShard(local, sparse=sparse, u8=u8)
     if in_library:
         TreeLoop.join_ranks(shard)  # the library's own NCCL communicator (h2ok_hist_comm_init)
-    shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
+    if u8:
+        shard.set_data_synth_prebinned(wl["shape"], SEED, row0, rows, cols, nbins=bins)
+    else:
+        shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
     # K class trees per boosting iteration: K target vectors (y_k = 2 u_k - 1 from their own hashes)
     ys = [shard.y]
     for k in range(1, K):
@@ -382,13 +392,13 @@ def run_gpu(args, wl):
     if in_library:
         cnt, nodes, ms = loop_stats
         hist_ms = float(ms[:, 0].sum())
-        abytes = float(sum(int(cnt[d]) * algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz) for d in range(len(cnt))))
+        abytes = float(sum(int(cnt[d]) * algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz, u8=u8) for d in range(len(cnt))))
         for d in range(len(cnt)):
             if cnt[d]:
                 t = float(ms[d, 0] / cnt[d])
                 level_table[str(d)] = {
                     "nodes": int(nodes[d]), "hist_ms": round(t, 4),
-                    "frac": round(algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz) / (t * 1e-3) / 1e9 / peak, 4),
+                    "frac": round(algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz, u8=u8) / (t * 1e-3) / 1e9 / peak, 4),
                     "reduce_ms": round(float(ms[d, 2] / cnt[d]), 4), "search_ms": round(float(ms[d, 3] / cnt[d]), 4),
                     "route_ms": round(float(ms[d, 4] / cnt[d]), 4)}
         tot = ms.sum(axis=0) / max(1, int(cnt.sum()))
@@ -424,7 +434,7 @@ def run_gpu(args, wl):
         if in_library:
             srows = cpu_sample_rows(wl)
             s2 = EngineShard(local, sparse=sparse)
-            s2.set_data_synth(wl["shape"], SEED, 0, srows, cols)
+            s2.set_data_synth(wl["shape"], SEED, 0, srows, cols)  # (u8 workloads: the slice check runs on the fp32 matrix)
             l2 = TreeLoop(s2, params, checksum=True)
             l2.train_tree()
             gpu_slice = l2.checksum(0)

@@ -324,14 +324,17 @@ int32_t h2ok_hist_synth_fill_cols_dev(h2ok_ctx* c, int32_t shape, uint64_t seed,
 int32_t h2ok_hist_tree_create(h2ok_ctx* c, int64_t rows, int32_t cols, int32_t flags) {
   REQUIRE(c != nullptr, "null context");
   REQUIRE(rows > 0 && cols > 0, "empty shard");
-  REQUIRE((flags & ~(H2OK_TREE_WEIGHTED | H2OK_TREE_SPARSE)) == 0, "unknown flag");
-  if ((flags & H2OK_TREE_WEIGHTED) && (flags & H2OK_TREE_SPARSE))
-    return fail(H2OK_ERR_UNSUPPORTED, "%s", "sparse storage takes unweighted trees only");
+  REQUIRE((flags & ~(H2OK_TREE_WEIGHTED | H2OK_TREE_SPARSE | H2OK_TREE_U8)) == 0, "unknown flag");
+  if ((flags & H2OK_TREE_WEIGHTED) && (flags & (H2OK_TREE_SPARSE | H2OK_TREE_U8)))
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "sparse and u8 storage take unweighted trees only");
+  if ((flags & H2OK_TREE_SPARSE) && (flags & H2OK_TREE_U8))
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "one storage format per shard");
   CK(cudaSetDevice(c->device));
   c->eng_ready = false;
   CK(cudaStreamSynchronize(c->stream));
   loop_free(c);
-  CK(engine_alloc(c->eng, rows, cols, (flags & H2OK_TREE_WEIGHTED) != 0, (flags & H2OK_TREE_SPARSE) != 0));
+  CK(engine_alloc(c->eng, rows, cols, (flags & H2OK_TREE_WEIGHTED) != 0, (flags & H2OK_TREE_SPARSE) != 0,
+                  (flags & H2OK_TREE_U8) != 0));
   c->eng_ready = true;
   return H2OK_OK;
 }
@@ -351,6 +354,30 @@ int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* c, int32_t col0, int32_t ncols, c
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_load_cols_dev before tree_create");
   REQUIRE(col0 >= 0 && ncols > 0 && col0 + ncols <= c->eng.cols && ld >= c->eng.rows, "column block outside the shard");
   CK(engine_load_cols(c->eng, col0, ncols, d_X, ld, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_tree_load_bins_dev(h2ok_ctx* c, int32_t col0, int32_t ncols, const uint8_t* d_bins, int64_t ld) {
+  REQUIRE(c && d_bins, "null pointer");
+  if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "tree_load_bins_dev before tree_create");
+  if (!c->eng.u8) return fail(H2OK_ERR_STATE, "%s", "tree_load_bins_dev needs a shard created with H2OK_TREE_U8");
+  REQUIRE(col0 >= 0 && ncols > 0 && col0 + ncols <= c->eng.cols && ld >= c->eng.rows, "column block outside the shard");
+  CK(engine_load_bins(c->eng, col0, ncols, d_bins, ld, c->stream));
+  return H2OK_OK;
+}
+
+int32_t h2ok_hist_prebin_dev(h2ok_ctx* c, const float* d_X, int64_t ld, int64_t rows, int32_t ncols, const h2ok_col_desc* descs,
+                             uint8_t* d_bins, int64_t ld_bins) {
+  REQUIRE(c && d_X && descs && d_bins, "null pointer");
+  REQUIRE(rows >= 0 && ncols > 0 && ld >= rows && ld_bins >= rows, "bad shape");
+  for (int32_t j = 0; j < ncols; j++)
+    if (descs[j].nbin > 255) return fail(H2OK_ERR_UNSUPPORTED, "%s", "prebin: a byte holds at most 255 bins (255 is the NA code)");
+  if (rows == 0) return H2OK_OK;
+  CK(cudaSetDevice(c->device));
+  CK(c->tmp_descs.ensure((size_t)ncols));
+  CK(cudaMemcpyAsync(c->tmp_descs.p, descs, sizeof(h2ok_col_desc) * (size_t)ncols, cudaMemcpyHostToDevice, c->stream));
+  CK(launch_prebin(d_X, ld, rows, ncols, c->tmp_descs.p, d_bins, ld_bins, c->stream));
+  CK(cudaStreamSynchronize(c->stream));  // descs is the caller's host memory
   return H2OK_OK;
 }
 

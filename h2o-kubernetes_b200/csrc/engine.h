@@ -40,6 +40,12 @@ struct Engine {
   int route_ctas = 0;  // CTAs of the routing / regrouping kernels (each owns one contiguous range of rows)
   bool weighted = false;
   float* XT = nullptr;       // [rows][ldt] row-major copy of the shard (dense storage)
+  // u8 storage instead (row_engine.cu "u8 storage"): pre-binned integer codes, one byte per cell, 255 = NA
+  bool u8 = false;
+  unsigned char* XB = nullptr;  // [rows][ldb] row-major codes (code8 holds the same codes column-major)
+  int64_t ldb = 0;
+  int32_t* load_err = nullptr;  // != 0: a cell loaded as fp32 was not a code (device)
+  bool load_checked = true, load_failed = false;  // host copy of it, read once after such a load
   // sparse storage instead (row_engine.cu "sparse storage"): per column the list of its nonzero cells {row, value}
   bool sparse = false;
   const uint2** csc_ptr = nullptr;   // [cols] device table of the columns' lists
@@ -74,7 +80,15 @@ struct Engine {
   int32_t* err = nullptr;               // (node, column) pairs that had more bins than a level's shared histogram held
 };
 
-cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool sparse = false);
+cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool sparse = false, bool u8 = false);
+// u8 storage: columns [col0, col0 + ncols) of a column-major block of codes (one byte per cell)
+cudaError_t engine_load_bins(Engine& e, int col0, int ncols, const unsigned char* B, int64_t ld, cudaStream_t s);
+// u8 storage: did every fp32 cell handed to engine_load_cols hold a code?  (one blocking read after such a load)
+cudaError_t engine_check_load(Engine& e, cudaStream_t s, bool* bad);
+// a2 as a pre-binning pass: codes of a column-major fp32 block against one (device) descriptor per column; NaN and
+// untracked columns give 255
+cudaError_t launch_prebin(const float* X, int64_t ld, int64_t rows, int ncols, const h2ok_col_desc* d_descs, unsigned char* B,
+                          int64_t ldb, cudaStream_t s);
 void engine_free(Engine& e);
 // switch the shard between unweighted and weighted trees (allocates the weight arrays the first time)
 cudaError_t engine_set_weighted(Engine& e, bool weighted);

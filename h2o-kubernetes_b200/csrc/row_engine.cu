@@ -122,6 +122,7 @@ __device__ __forceinline__ int seg_of(const int32_t* __restrict__ table, int n, 
 // ------------------------------------------------------------------------------------------------ histogram pass
 struct EngHistArgs {
   const float* XT;
+  const unsigned char* XB;  // u8 storage instead of XT: one byte per cell (an integer code, 255 = NA), row pitch ldt4
   int64_t ldt;
   unsigned ldt4;  // row pitch in bytes
   int cols;
@@ -170,12 +171,17 @@ __device__ __noinline__ void eng_carry(int64_t* acc, const h2ok_col_desc* __rest
   if (d2) carry_to_global(acc, cell, 2, d2);
 }
 
-template <int CPL> struct XVec;
-template <> struct XVec<1> { using type = float; };
-template <> struct XVec<2> { using type = float2; };
+template <int CPL, bool U8 = false> struct XVec;
+template <> struct XVec<1, false> { using type = float; };
+template <> struct XVec<2, false> { using type = float2; };
+template <> struct XVec<1, true> { using type = unsigned char; };
+template <> struct XVec<2, true> { using type = unsigned short; };
 
 __device__ __forceinline__ float xget(const float& v, int) { return v; }
 __device__ __forceinline__ float xget(const float2& v, int k) { return k ? v.y : v.x; }
+__device__ __forceinline__ int xcode(const unsigned char& v, int) { return (int)v; }
+__device__ __forceinline__ int xcode(const unsigned short& v, int k) { return k ? (int)(v >> 8) : (int)(v & 0xFFu); }
+
 
 // What a lane keeps in registers while it walks the rows of one node: the descriptors and running extremes of its CPL
 // columns.  A (node, column) that is not tracked gets a harmless 1-bin descriptor — its rows land in words that the
@@ -185,6 +191,7 @@ struct EngLane {
   double mn[CPL], st[CPL];
   int nb[CPL];
   float fmn[CPL], fmx[CPL];
+  int imn[CPL], icmn[CPL], icmx[CPL];  // u8 storage: integer lower bound of the bins, running extremes of the codes
 };
 
 // A signed value v (|v| < 2^31) was added to a word that held `old`; did the 32-bit word wrap?  Bit 31 of the result
@@ -204,9 +211,32 @@ __device__ constexpr unsigned kPark[4] = {0x3217u, 0x3270u, 0x3710u, 0x7210u};
 // v1 / v2 are the row's targets minus the run's centring offsets (see the kernel).
 // LPR = lanes per row (32, or 16 for levels whose histograms are too wide for 32 columns per block): a bin of one
 // column slot is 3 channels x LPR lanes x 4 bytes.
-template <int CPL, bool WEIGHTED, int U, int LPR, bool NA>
-__device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[CPL], const typename XVec<CPL>::type (&xv)[U],
-                                         const int (&w)[U], unsigned (&pa)[U * CPL]) {
+template <int CPL, bool WEIGHTED, int U, int LPR, bool NA, bool U8 = false>
+__device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[CPL],
+                                         const typename XVec<CPL, U8>::type (&xv)[U], const int (&w)[U],
+                                         unsigned (&pa)[U * CPL]) {
+  if constexpr (U8) {
+    // u8 storage: the cell IS an integer code and every descriptor has step 1 (DHistogram's integer rule: the range
+    // of a code column never exceeds nbins >= 255), so the bin is code - min, clamped: no fp64, no conversions.
+#pragma unroll
+    for (int j = 0; j < U; j++) {
+#pragma unroll
+      for (int k = 0; k < CPL; k++) {
+        const int code = xcode(xv[j], k);
+        int b = min(max(code - c.imn[k], 0), c.nb[k] - 1);
+        if (NA) {
+          const bool na = code == 255;
+          b = na ? c.nb[k] : b;
+          c.icmn[k] = na ? c.icmn[k] : min(c.icmn[k], code);
+          c.icmx[k] = na ? c.icmx[k] : max(c.icmx[k], code);
+        } else {
+          c.icmn[k] = min(c.icmn[k], code);
+          c.icmx[k] = max(c.icmx[k], code);
+        }
+        pa[j * CPL + k] = cell_addr(hb[k], (unsigned)b, 12u * LPR);
+      }
+    }
+  } else {
   float xs[U][CPL];
 #pragma unroll
   for (int j = 0; j < U; j++) {
@@ -232,6 +262,7 @@ __device__ __forceinline__ void eng_bins(EngLane<CPL>& c, const unsigned (&hb)[C
       c.fmn[k] = fminf(c.fmn[k], xs[U - 1][k]);
       c.fmx[k] = fmaxf(c.fmx[k], xs[U - 1][k]);
     }
+  }
   }
 }
 
@@ -296,10 +327,11 @@ struct EngCfg {
   static constexpr int U = WEIGHTED ? 4 / CPL : (CPL == 1 ? 6 : 4);  // 6, 4 (unweighted) or 4, 2 (weighted): even
 };
 
-template <int CPL, bool WEIGHTED, int LPR, bool NA>
+template <int CPL, bool WEIGHTED, int LPR, bool NA, bool U8 = false>
 __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_kernel(const __grid_constant__ EngHistArgs a) {
   static_assert(NA || !WEIGHTED, "zero-weight rows are turned into NaNs: weighted shards need the NA test");
-  using V = typename XVec<CPL>::type;
+  static_assert(!U8 || (!WEIGHTED && LPR == 32), "u8 storage: unweighted trees, 32 lanes per row");
+  using V = typename XVec<CPL, U8>::type;
   constexpr int THREADS = EngCfg<CPL, WEIGHTED>::threads, NW = THREADS / 32;
   constexpr int U = LPR == 16 && !WEIGHTED ? 4 : EngCfg<CPL, WEIGHTED>::U;  // (the 16-lane layout spills at eight rows)
   extern __shared__ __align__(16) unsigned h[];
@@ -328,7 +360,8 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
   }
   // lanes past the last column read the row's last CPL floats instead (never accumulated: their columns are untracked)
   const unsigned ldt4 = a.ldt4;  // row pitch in bytes: one IMAD.WIDE per row address
-  const char* xrow = reinterpret_cast<const char*>(a.XT + min(col_lane, (int)a.ldt - CPL));
+  const char* xrow = U8 ? reinterpret_cast<const char*>(a.XB + min(col_lane, (int)ldt4 - CPL))
+                        : reinterpret_cast<const char*>(a.XT + min(col_lane, (int)a.ldt - CPL));
   asm volatile("" : "+l"(xrow));  // kept in a register pair: rebuilt per batch it turns every row address into three instructions
   const int32_t* __restrict__ gidx = a.gidx;
   const uint2* __restrict__ gval = a.gval;
@@ -352,13 +385,18 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
       if (on && col < a.cols) {
         const h2ok_col_desc d = a.descs[(int64_t)node * a.cols + col];
         if (d.nbin >= nbs) atomicAdd(a.err, 1);  // the caller's level_bins hint was too small: counted, not accumulated
+        else if (U8 && d.nbin > 0 && !(d.step == 1.0 && d.min == (double)(int)d.min)) atomicAdd(a.err, 1);  // not a step-1 integer descriptor
         else if (d.nbin > 0) {
           tracked[k] = true;
           c.nb[k] = d.nbin;
           c.mn[k] = d.min;
           c.st[k] = d.step;
+          c.imn[k] = (int)d.min;
         }
       }
+      if (!tracked[k]) c.imn[k] = 0;
+      c.icmn[k] = 0x7fffffff;
+      c.icmx[k] = -1;
       c.fmn[k] = __int_as_float(0x7f800000);
       c.fmx[k] = __int_as_float(0xff800000);
     }
@@ -391,7 +429,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         w[0] = WEIGHTED ? __ldg(gw + q) : 1;
         unsigned pa[CPL];
         if (on) {
-          eng_bins<CPL, WEIGHTED, 1, LPR, NA>(c, hb, x, w, pa);
+          eng_bins<CPL, WEIGHTED, 1, LPR, NA, U8>(c, hb, x, w, pa);
           eng_accum<CPL, WEIGHTED, 1, LPR>(a, hb, node, col_lane, pa, v1, v2, w);
         }
       };
@@ -434,7 +472,7 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
 #pragma unroll
         for (int j = 0; j < U; j++) w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
         unsigned pa[U * CPL];
-        if (on) eng_bins<CPL, WEIGHTED, U, LPR, NA>(c, hb, x, w, pa);
+        if (on) eng_bins<CPL, WEIGHTED, U, LPR, NA, U8>(c, hb, x, w, pa);
         if (more) {
 #pragma unroll
           for (int j = 0; j < U; j++) prefetch_l2(row_addr(xrow, (unsigned)nx[j], ldt4));
@@ -447,6 +485,10 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
     // observed ranges: registers -> shared (integer min / max of the order-preserving encoding) -> global
 #pragma unroll
     for (int k = 0; k < CPL; k++) {
+      if (U8) {  // codes are small non-negative integers: exact as floats
+        c.fmn[k] = c.icmx[k] < 0 ? __int_as_float(0x7f800000) : (float)c.icmn[k];
+        c.fmx[k] = c.icmx[k] < 0 ? __int_as_float(0xff800000) : (float)c.icmx[k];
+      }
       if (tracked[k]) {
         atomicMin(&s_mn[k * 32 + lane], enc_f32_bits(__float_as_uint(c.fmn[k])));
         atomicMax(&s_mx[k * 32 + lane], enc_f32_bits(__float_as_uint(c.fmx[k])));
@@ -515,6 +557,84 @@ __device__ __forceinline__ int block_exscan_1024(int v, int* s_warp, int* total)
   *total = s_warp[32];
   __syncthreads();  // s_warp may be reused
   return ex;
+}
+
+// ------------------------------------------------------------------------------------------------ u8 storage
+// Pre-binned input: every cell is an integer code 0..254 (255 = NA), one byte.  The shard keeps
+// the codes twice, row-major for the histogram pass (64 B per row at 64 columns) and column-major for routing, which
+// compares the code itself with the threshold — exact, no float to fall back to.
+__global__ void __launch_bounds__(256) eng_load_u8_kernel(const unsigned char* __restrict__ B, int64_t ld, int64_t rows,
+                                                          int col0, int ncols, unsigned char* __restrict__ XB, int64_t ldb,
+                                                          unsigned char* __restrict__ code8, int64_t ld8,
+                                                          int* __restrict__ na_flag) {
+  __shared__ unsigned char t[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t r0 = (int64_t)blockIdx.x * 32;
+  const int c0 = blockIdx.y * 32;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int c = c0 + ty + i * 8;
+    const int64_t r = r0 + tx;
+    if (c < ncols && r < rows) {
+      const unsigned char v = B[(int64_t)c * ld + r];
+      t[ty + i * 8][tx] = v;
+      code8[(int64_t)(col0 + c) * ld8 + r] = v;
+      if (v == 255) *na_flag = 1;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int64_t r = r0 + ty + i * 8;
+    const int c = c0 + tx;
+    if (r < rows && c < ncols) XB[r * ldb + col0 + c] = t[tx][ty + i * 8];
+  }
+}
+
+// column ranges of a block of codes, as encoded floats (what DHistogram.initialHist reads)
+__global__ void __launch_bounds__(256) eng_u8_ranges_kernel(const unsigned char* __restrict__ B, int64_t ld, int64_t rows,
+                                                            uint32_t* __restrict__ mn, uint32_t* __restrict__ mx) {
+  const unsigned char* b = B + (int64_t)blockIdx.y * ld;
+  int lo = 256, hi = -1;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
+    const int v = b[r];
+    if (v != 255) {
+      lo = min(lo, v);
+      hi = max(hi, v);
+    }
+  }
+  lo = __reduce_min_sync(0xffffffffu, lo);
+  hi = __reduce_max_sync(0xffffffffu, hi);
+  if ((threadIdx.x & 31) == 0 && hi >= 0) {
+    atomicMin(&mn[blockIdx.y], enc_f32_bits(__float_as_uint((float)lo)));
+    atomicMax(&mx[blockIdx.y], enc_f32_bits(__float_as_uint((float)hi)));
+  }
+}
+
+// fp32 cells that already hold codes (0..254, NaN = NA) -> bytes; anything else is flagged
+__global__ void eng_f32_codes_kernel(const float* __restrict__ X, int64_t n, unsigned char* __restrict__ B, int* __restrict__ bad) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float x = X[i];
+  if (x != x) B[i] = 255;
+  else if (x >= 0.0f && x <= 254.0f && x == (float)(int)x) B[i] = (unsigned char)(int)x;
+  else {
+    B[i] = 255;
+    *bad = 1;
+  }
+}
+
+// a2 as a pre-binning pass: the code of every cell against its column's (root) descriptor
+__global__ void __launch_bounds__(256) eng_prebin_kernel(const float* __restrict__ X, int64_t ld, int64_t rows,
+                                                         const h2ok_col_desc* __restrict__ descs, unsigned char* __restrict__ B,
+                                                         int64_t ldb) {
+  const h2ok_col_desc d = descs[blockIdx.y];
+  const int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (r >= rows) return;
+  const float x = X[(int64_t)blockIdx.y * ld + r];
+  int b = 255;
+  if (x == x && d.nbin > 0) b = bin_of(x, d.min, d.step, d.nbin);
+  B[(int64_t)blockIdx.y * ldb + r] = (unsigned char)b;
 }
 
 // ------------------------------------------------------------------------------------------------ sparse storage
@@ -914,7 +1034,7 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
     const uint8_t* __restrict__ code8, int64_t ld8,
     const unsigned* __restrict__ thr, int64_t rows, int n_nodes, const h2ok_split* __restrict__ splits,
     const int32_t* __restrict__ child_ids, int gid_base, uint16_t* __restrict__ nid16, int32_t* __restrict__ leaf,
-    int32_t* __restrict__ cta_cnt, int n_slots) {
+    int32_t* __restrict__ cta_cnt, int n_slots, int exact_codes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RouteNode* tab = reinterpret_cast<RouteNode*>(smem_raw);
   int* s_cnt = reinterpret_cast<int*>(tab + n_nodes);
@@ -925,7 +1045,7 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
     t.col = (short)sp.col;
     t.na = (unsigned char)sp.na_dir;
     t.cs = 0;
-    if (sp.col >= 0 && sp.na_dir != H2OK_NA_VS_REST && sp.splat == sp.splat)
+    if (!exact_codes && sp.col >= 0 && sp.na_dir != H2OK_NA_VS_REST && sp.splat == sp.splat)
       t.cs = (unsigned char)code_of(thr + (int64_t)sp.col * 256, enc_key(sp.splat));
     t.c0 = (short)child_ids[2 * g];
     t.c1 = (short)child_ids[2 * g + 1];
@@ -952,6 +1072,7 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
           int way;
           if (c == 255u) way = (t.na == H2OK_NA_LEFT) ? 0 : 1;
           else if (t.na == H2OK_NA_VS_REST) way = 0;
+          else if (exact_codes) way = (float)c >= t.splat ? 1 : 0;  // u8 storage: the byte is the value
           else if (c != t.cs) way = c > t.cs ? 1 : 0;
           else way = (XT ? XT[r * ldt + t.col] : csc_get(cptr, clen, r, t.col)) >= t.splat ? 1 : 0;  // code tie: the float decides
           const int ch = way ? t.c1 : t.c0;
@@ -1157,10 +1278,12 @@ __global__ void eng_nid_kernel(const uint16_t* __restrict__ nid16, int64_t rows,
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ host side
-cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool sparse) {
+cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool sparse, bool u8) {
   engine_free(e);
-  if (sparse && weighted) return cudaErrorInvalidValue;
+  if ((sparse || u8) && weighted) return cudaErrorInvalidValue;
+  if (sparse && u8) return cudaErrorInvalidValue;
   e.sparse = sparse;
+  e.u8 = u8;
   if (rows >= (1ll << 31) - 4096) return cudaErrorInvalidValue;
   if (cols > 32767) return cudaErrorInvalidValue;  // the routing table keeps the split column in 16 bits
   e.rows = rows;
@@ -1185,6 +1308,12 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
     if (err == cudaSuccess) err = cudaMemset(e.csc_ptr, 0, sizeof(uint2*) * (size_t)cols);
     if (err == cudaSuccess) err = cudaMemset(e.csc_len, 0, sizeof(int64_t) * (size_t)cols);
     e.nnz = 0;
+  } else if (u8) {
+    e.ldb = ((int64_t)cols + 31) / 32 * 32;  // rows start on 32-byte sectors
+    A((void**)&e.XB, (size_t)rows * (size_t)e.ldb);
+    A((void**)&e.load_err, sizeof(int32_t));
+    if (err == cudaSuccess) err = cudaMemset(e.XB, 0, (size_t)rows * (size_t)e.ldb);
+    if (err == cudaSuccess) err = cudaMemset(e.load_err, 0, sizeof(int32_t));
   } else {
     A((void**)&e.XT, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   }
@@ -1211,13 +1340,17 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
   if (err == cudaSuccess) err = cudaMemset(e.na_flag, 0, sizeof(int32_t));
   e.na_known = false;
   e.has_na = true;
-  if (err == cudaSuccess && !sparse && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
+  if (err == cudaSuccess && !sparse && !u8 && e.ldt != cols) err = cudaMemset(e.XT, 0, sizeof(float) * (size_t)rows * (size_t)e.ldt);
   if (err != cudaSuccess) engine_free(e);
   return err;
 }
 
 void engine_free(Engine& e) {
   cudaFree(e.XT); cudaFree(e.code8); cudaFree(e.thr); cudaFree(e.cmin); cudaFree(e.cmax);
+  cudaFree(e.XB); cudaFree(e.load_err);
+  e.XB = nullptr;
+  e.load_err = nullptr;
+  e.u8 = false;
   for (void* p : e.csc_blocks) cudaFree(p);
   e.csc_blocks.clear();
   cudaFree(e.csc_ptr); cudaFree(e.csc_len); cudaFree(e.node_tot); cudaFree(e.rec);
@@ -1258,7 +1391,32 @@ cudaError_t engine_set_weighted(Engine& e, bool weighted) {
   return cudaSuccess;
 }
 
+cudaError_t engine_load_bins(Engine& e, int col0, int ncols, const unsigned char* B, int64_t ld, cudaStream_t s) {
+  if (!e.u8) return cudaErrorInvalidValue;
+  dim3 grid(nblk(e.rows, 32), nblk(ncols, 32));
+  eng_load_u8_kernel<<<grid, 256, 0, s>>>(B, ld, e.rows, col0, ncols, e.XB, e.ldb, e.code8, e.ld8, e.na_flag);
+  e.na_known = false;
+  cudaError_t err = launch_init_enc(e.cmin + col0, e.cmax + col0, ncols, s);
+  if (err != cudaSuccess) return err;
+  int64_t per = (e.rows + 255) / 256;
+  const unsigned bx = (unsigned)(per < 1 ? 1 : (per > 4 * e.sms ? 4 * e.sms : per));
+  eng_u8_ranges_kernel<<<dim3(bx, (unsigned)ncols), 256, 0, s>>>(B, ld, e.rows, e.cmin + col0, e.cmax + col0);
+  return cudaGetLastError();
+}
+
 cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int64_t ld, cudaStream_t s) {
+  if (e.u8) {  // fp32 cells that already hold codes (integers 0..254, NaN = NA): converted, anything else is flagged
+    unsigned char* tmp = nullptr;
+    cudaError_t err = cudaMalloc((void**)&tmp, (size_t)ld * ncols);
+    if (err != cudaSuccess) return err;
+    const int64_t n = ld * (int64_t)ncols;
+    eng_f32_codes_kernel<<<nblk(n, 256), 256, 0, s>>>(X, n, tmp, e.load_err);
+    e.load_checked = false;
+    err = engine_load_bins(e, col0, ncols, tmp, ld, s);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+    cudaFree(tmp);
+    return err;
+  }
   if (e.sparse) {
     // count the nonzeros of every (column, chunk), lay the columns out one after the other in one allocation per
     // block of columns, then compact (rows stay ascending inside a column).  One blocking round trip per block: this
@@ -1358,18 +1516,18 @@ int engine_max_nb1(int cols) {
   return kHistSmemCap / (16 * 12);
 }
 
-template <int CPL, bool W, int LPR, bool NA>
+template <int CPL, bool W, int LPR, bool NA, bool U8 = false>
 static cudaError_t launch_eng_hist(const EngHistArgs& a, dim3 grid, size_t smem, cudaStream_t s) {
   static std::atomic<bool> attr_done[64];  // per device, per instantiation (setting it twice is harmless)
   int dev = 0;
   cudaGetDevice(&dev);
   std::atomic<bool>& attr = attr_done[dev & 63];
   if (!attr.load(std::memory_order_acquire)) {
-    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W, LPR, NA>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+    cudaError_t e = cudaFuncSetAttribute(eng_hist_kernel<CPL, W, LPR, NA, U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
     if (e != cudaSuccess) return e;
     attr.store(true, std::memory_order_release);
   }
-  eng_hist_kernel<CPL, W, LPR, NA><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
+  eng_hist_kernel<CPL, W, LPR, NA, U8><<<grid, EngCfg<CPL, W>::threads, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -1434,13 +1592,15 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     eng_csc_zero_kernel<<<(unsigned)((pairs + 7) / 8), 256, 0, s>>>(n_nodes, e.cols, descs, nb1, e.node_tot, acc, min2_enc, maxin_enc);
     return cudaGetLastError();
   }
-  const EngLayout lay = eng_layout(e.cols, nbs);
+  EngLayout lay = eng_layout(e.cols, nbs);
+  if (e.u8 && lay.lpr == 16) lay = {0, 0};  // u8 storage runs the 32-lane layouts only (bins <= 599)
   if (!lay.cpl) return cudaErrorInvalidValue;
   e.n_nodes = n_nodes;
   EngHistArgs a{};
   a.XT = e.XT;
-  a.ldt = e.ldt;
-  a.ldt4 = (unsigned)(e.ldt * 4);
+  a.XB = e.XB;
+  a.ldt = e.u8 ? e.ldb : e.ldt;
+  a.ldt4 = e.u8 ? (unsigned)e.ldb : (unsigned)(e.ldt * 4);
   a.cols = e.cols;
   a.gidx = e.gidx[e.cur];
   a.gval = e.gval[e.cur];
@@ -1472,6 +1632,14 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     e.has_na = flag != 0;
     e.na_known = true;
   }
+  if (e.u8) {
+    if (e.has_na) {
+      if (lay.cpl == 2) return launch_eng_hist<2, false, 32, true, true>(a, grid, smem, s);
+      return launch_eng_hist<1, false, 32, true, true>(a, grid, smem, s);
+    }
+    if (lay.cpl == 2) return launch_eng_hist<2, false, 32, false, true>(a, grid, smem, s);
+    return launch_eng_hist<1, false, 32, false, true>(a, grid, smem, s);
+  }
   if (e.has_na) {
     if (lay.cpl == 2) return launch_eng_hist<2, false, 32, true>(a, grid, smem, s);
     if (lay.lpr == 32) return launch_eng_hist<1, false, 32, true>(a, grid, smem, s);
@@ -1492,7 +1660,7 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   const size_t rsmem = (size_t)n_nodes * sizeof(RouteNode) + (size_t)n_slots * sizeof(int);
   eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, e.csc_ptr, e.csc_len, e.code8, e.ld8, e.thr, e.rows, n_nodes, splits,
                                                    child_ids,
-                                                   gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots);
+                                                   gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots, e.u8 ? 1 : 0);
   // every level but a tree's last: lay the children's records out for the next histogram pass
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.cta_cnt, G, n_nodes, child_ids, e.seg[nx], splits, e.scale_wy, e.scale_wyy,
                                      e.weighted ? nullptr : e.q_dev,
@@ -1524,6 +1692,27 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   e.cur = nx;
   e.n_nodes = 0;  // the caller says how many children there are (build_level / nid)
   return cudaSuccess;
+}
+
+cudaError_t engine_check_load(Engine& e, cudaStream_t s, bool* bad) {
+  *bad = false;
+  if (!e.u8) return cudaSuccess;
+  if (!e.load_checked) {
+    int flag = 0;
+    cudaError_t err = cudaMemcpyAsync(&flag, e.load_err, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+    if (err != cudaSuccess) return err;
+    e.load_failed = flag != 0;
+    e.load_checked = true;
+  }
+  *bad = e.load_failed;
+  return cudaSuccess;
+}
+
+cudaError_t launch_prebin(const float* X, int64_t ld, int64_t rows, int ncols, const h2ok_col_desc* d_descs, unsigned char* B,
+                          int64_t ldb, cudaStream_t s) {
+  eng_prebin_kernel<<<dim3(nblk(rows, 256), (unsigned)ncols), 256, 0, s>>>(X, ld, rows, d_descs, B, ldb);
+  return cudaGetLastError();
 }
 
 cudaError_t engine_nid(Engine& e, int32_t* nid_rows, cudaStream_t s) {

@@ -240,6 +240,9 @@ int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
   if (!L.have_tree) return fail(H2OK_ERR_STATE, "%s", "loop_level before loop_begin_tree");
   if (L.n_nodes < 1 || L.depth >= L.params.max_depth) return fail(H2OK_ERR_STATE, "%s", "loop_level: the tree is finished");
   CK(cudaSetDevice(c->device));
+  bool bad_load = false;
+  CK(engine_check_load(c->eng, c->stream, &bad_load));
+  if (bad_load) return fail(H2OK_ERR_ARG, "%s", "u8 storage: a cell loaded from fp32 was not an integer code in [0, 254] or NaN");
   const int n = L.n_nodes, R = c->comm_ranks;
   L.out = out;
   L.pairs = (int64_t)n * L.cols;
@@ -420,7 +423,8 @@ int32_t begin_tree_local(h2ok_ctx* c, const float* d_y, const float* d_w) {
   const int64_t n = c->eng.rows;
   const size_t pad = (size_t)(n + 3) / 4 * 4;
   const bool weighted = d_w != nullptr;
-  if (weighted && c->eng.sparse) return fail(H2OK_ERR_UNSUPPORTED, "%s", "sparse storage takes unweighted trees only");
+  if (weighted && (c->eng.sparse || c->eng.u8))
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "sparse and u8 storage take unweighted trees only");
   if (weighted != c->eng.weighted) CK(engine_set_weighted(c->eng, weighted));
   CK(L.wyq.ensure(pad)); CK(L.wyyq.ensure(pad)); CK(L.absmax.ensure(3));
   if (weighted) CK(L.wq.ensure(pad));
@@ -566,6 +570,14 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
   const int cols = c->eng.cols;
   for (int j = 0; is_int && j < cols; j++)
     if (is_int[j] > 1) return fail(H2OK_ERR_UNSUPPORTED, "%s", "categorical columns (is_int == 2) are not supported");
+  if (c->eng.u8) {
+    // the cells are integer codes: every column is an integer column whose range never exceeds nbins, so that
+    // DHistogram's integer rule gives step-1 bins at every level (what the byte-wide histogram pass assumes)
+    if (params->nbins < 255 || params->nbins_top_level < 255)
+      return fail(H2OK_ERR_UNSUPPORTED, "%s", "u8 storage needs nbins >= 255 (one bin per code at every level)");
+    for (int j = 0; j < cols; j++)
+      if (!is_int || is_int[j] != 1) return fail(H2OK_ERR_ARG, "%s", "u8 storage: every column is an integer column (is_int == 1)");
+  }
   CK(cudaSetDevice(c->device));
   loop_free(c);
   TreeLoop* L = new TreeLoop();

@@ -13,7 +13,7 @@ NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT = 0, 1, 2, 3
 SHAPE_HIGGS28, SHAPE_WIDE64, SHAPE_SPARSE = 2, 3, 4
 DIST_GAUSSIAN, DIST_BERNOULLI, DIST_MULTINOMIAL = 0, 1, 2
 REDUCE_SCATTER, REDUCE_ALL = 0, 1
-TREE_WEIGHTED, TREE_SPARSE = 1, 2
+TREE_WEIGHTED, TREE_SPARSE, TREE_U8 = 1, 2, 4
 COMM_ID_BYTES = 128
 
 COL_DESC = np.dtype(

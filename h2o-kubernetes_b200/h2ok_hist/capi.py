@@ -38,6 +38,8 @@ SIGNATURES = {
     "h2ok_hist_tree_create": [vp, i64, i32, i32],
     "h2ok_hist_tree_load_cols_dev": [vp, i32, i32, vp, i64],
     "h2ok_hist_tree_destroy": [vp],
+    "h2ok_hist_tree_load_bins_dev": [vp, i32, i32, vp, i64],
+    "h2ok_hist_prebin_dev": [vp, vp, i64, i64, i32, vp, vp, i64],
     "h2ok_hist_tree_begin_dev": [vp, vp, vp, vp, vp],
     "h2ok_hist_tree_build_level_dev": [vp, i32, vp, i32, i32, vp, vp, vp],
     "h2ok_hist_tree_level_bins": [vp, i32],

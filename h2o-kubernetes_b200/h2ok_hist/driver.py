@@ -204,14 +204,15 @@ class EngineShard(CudaShard):
 
     stage_bytes = 2 << 30
 
-    def __init__(self, device=0, max_level_nodes=128, sparse=False):
-        """sparse: keep only the nonzero cells (H2OK_TREE_SPARSE) — for matrices that are mostly exact zeros."""
+    def __init__(self, device=0, max_level_nodes=128, sparse=False, u8=False):
+        """sparse: keep only the nonzero cells (H2OK_TREE_SPARSE) — for matrices that are mostly exact zeros.
+        u8: pre-binned input, one byte per cell (H2OK_TREE_U8); the cells are integer codes 0..254, NaN / 255 = NA."""
         super().__init__(device, max_level_nodes)
-        self.sparse = sparse
+        self.sparse, self.u8 = sparse, u8
 
     def _alloc_rows(self, rows, cols, weighted):
         self.rows, self.cols = rows, cols
-        flags = (abi.TREE_WEIGHTED if weighted else 0) | (abi.TREE_SPARSE if self.sparse else 0)
+        flags = (abi.TREE_WEIGHTED if weighted else 0) | (abi.TREE_SPARSE if self.sparse else 0) | (abi.TREE_U8 if self.u8 else 0)
         self.lib.call("h2ok_hist_tree_create", self.ctx, rows, cols, flags)
         n = (rows + 63) // 64 * 64
         self.ld = n
@@ -250,6 +251,41 @@ class EngineShard(CudaShard):
         self.lib.call("h2ok_hist_synth_fill_dev", self.ctx, shape, seed, row0, rows, cols, self.ld, na_permille,
                       weight_mode, None, _ptr(self.y), _ptr(self.w))
         torch.cuda.current_stream(self.device).synchronize()  # the staging buffer is released here
+
+    def set_data_synth_prebinned(self, shape, seed, row0, rows, cols, nbins=255, na_permille=0):
+        """u8 shards: the generator's fp32 columns, binned ONCE against their root descriptors (global bins from the
+        column ranges over all ranks, `nbins` <= 255 of them) by h2ok_hist_prebin_dev, loaded as codes.  Returns the
+        root descriptors the codes were made with."""
+        assert self.u8 and nbins <= 255
+        self._alloc_rows(rows, cols, False)
+        blocks = self._blocks()
+        stage = torch.empty((blocks[0][1], self.ld), dtype=torch.float32, device=self.device)
+        codes = torch.empty((blocks[0][1], self.ld), dtype=torch.uint8, device=self.device)
+        params = abi.Params.make(nbins=nbins)
+        descs = np.zeros(cols, abi.COL_DESC)
+        for c0, nc in blocks:
+            self.lib.call("h2ok_hist_synth_fill_cols_dev", self.ctx, shape, seed, row0, rows, c0, nc, self.ld, na_permille,
+                          _ptr(stage))
+            mn = torch.empty(nc, dtype=torch.int32, device=self.device)
+            mx = torch.empty(nc, dtype=torch.int32, device=self.device)
+            self.lib.call("h2ok_hist_col_ranges_dev", self.ctx, _ptr(stage), self.ld, rows, nc, _ptr(mn), _ptr(mx))
+            if _world() > 1:  # every rank must bin against the same global ranges
+                mn ^= _I32_SIGN
+                mx ^= _I32_SIGN
+                dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+                dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+                mn ^= _I32_SIGN
+                mx ^= _I32_SIGN
+            lo = abi.decode_f32(mn.cpu().numpy().view(np.uint32))
+            hi = abi.decode_f32(mx.cpu().numpy().view(np.uint32))
+            d = np.zeros(nc, abi.COL_DESC)
+            self.lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi), nc, C.byref(params), None, abi.ptr(d))
+            descs[c0:c0 + nc] = d
+            self.lib.call("h2ok_hist_prebin_dev", self.ctx, _ptr(stage), self.ld, rows, nc, abi.ptr(d), _ptr(codes), self.ld)
+            self.lib.call("h2ok_hist_tree_load_bins_dev", self.ctx, c0, nc, _ptr(codes), self.ld)
+        self.lib.call("h2ok_hist_synth_fill_dev", self.ctx, shape, seed, row0, rows, cols, self.ld, 0, 0, None, _ptr(self.y), None)
+        torch.cuda.current_stream(self.device).synchronize()
+        return descs
 
     def set_data_tensors(self, X, y, w=None):
         cols, rows = X.shape
@@ -306,6 +342,8 @@ class TreeLoop:
 
     def __init__(self, shard, params, is_int=None, reduce_mode=abi.REDUCE_SCATTER, checksum=False, time_phases=False):
         self.shard, self.params, self.lib = shard, params, shard.lib
+        if is_int is None and getattr(shard, "u8", False):
+            is_int = np.ones(shard.cols, np.int32)  # the cells of a u8 shard are integer codes
         self.is_int = None if is_int is None else np.ascontiguousarray(is_int, np.int32)
         self.max_bins = max(params.nbins, params.nbins_top_level)
         self.lib.call("h2ok_hist_loop_create", shard.ctx, C.byref(params), abi.ptr(self.is_int))

@@ -68,6 +68,7 @@ extern "C" {
 /* Flags of h2ok_hist_tree_create. */
 #define H2OK_TREE_WEIGHTED 1 /* trees with per-row weights (8 more bytes per row) */
 #define H2OK_TREE_SPARSE 2   /* store only the nonzero cells: for matrices that are mostly exact zeros (see below) */
+#define H2OK_TREE_U8 4       /* pre-binned input: one byte per cell, an integer code 0..254, 255 = NA (see below) */
 
 /* Synthetic shapes of SURVEY.md §8(d). */
 #define H2OK_SHAPE_HIGGS28 2 /* config 2: 28 HIGGS-shaped columns */
@@ -279,12 +280,28 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, 
  * the row's node and targets looked up by row; what the zero cells contribute follows exactly from the node totals
  * afterwards.  No row records are kept or regrouped.  Same results bit for bit, any density (it pays below ~25 %
  * nonzeros).  Unweighted trees only.  Algorithmic bytes per level: nnz * 8 + rows * 10 (row -> node map and targets,
- * once) + histogram. */
+ * once) + histogram.
+ *
+ * H2OK_TREE_U8 (pre-binned input, the other format of SURVEY.md §8(f) row 4): every cell is an integer code 0..254,
+ * 255 = NA — bins computed once (h2ok_hist_prebin_dev against the root descriptors, i.e. global bins as in H2O's
+ * histogram types with fixed split points) or supplied by the caller.  The shard keeps one byte per cell (64 B per
+ * row at 64 columns) and the trees are built on the CODES as integer columns (is_int == 1 for every column, nbins
+ * >= 255): DHistogram's integer rule then gives step-1 bins at every level, so the histogram pass bins with one
+ * integer subtraction — no fp64 — and routing compares the byte itself.  Results equal the standard path run on the
+ * code matrix, bit for bit.  Unweighted trees.  Algorithmic bytes per level: rows * cols * 1 + rows * 8 + histogram.
+ * Load with h2ok_hist_tree_load_bins_dev (or tree_load_cols_dev with fp32 cells that hold the codes). */
 int32_t h2ok_hist_tree_create(h2ok_ctx* ctx, int64_t rows, int32_t cols, int32_t flags /*H2OK_TREE_**/);
 int32_t h2ok_hist_tree_destroy(h2ok_ctx* ctx);
 /* columns [col0, col0 + ncols) from a column-major device block (column c at d_X + (c - col0) * ld), rows in
  * original order */
 int32_t h2ok_hist_tree_load_cols_dev(h2ok_ctx* ctx, int32_t col0, int32_t ncols, const float* d_X, int64_t ld);
+/* H2OK_TREE_U8 shards: columns [col0, col0 + ncols) from a column-major device block of codes (column c at
+ * d_bins + (c - col0) * ld, one byte per cell). */
+int32_t h2ok_hist_tree_load_bins_dev(h2ok_ctx* ctx, int32_t col0, int32_t ncols, const uint8_t* d_bins, int64_t ld);
+/* a2 as a pre-binning pass (DHistogram.bin once per cell): d_bins[c * ld_bins + r] = bin of d_X[c * ld + r] against
+ * descs[c] (HOST array, one descriptor per column, nbin <= 255), 255 for NaN and for untracked columns.  Synchronous. */
+int32_t h2ok_hist_prebin_dev(h2ok_ctx* ctx, const float* d_X, int64_t ld, int64_t rows, int32_t ncols,
+                             const h2ok_col_desc* descs, uint8_t* d_bins, int64_t ld_bins);
 /* new tree: per-row fixed-point targets in ORIGINAL row order (d_wq NULL when unweighted); all rows back at the root.
  * The target arrays are read again by every tree_apply_splits_dev of the tree: keep them valid and unchanged until
  * the tree is finished.

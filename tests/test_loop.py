@@ -172,6 +172,88 @@ def test_sparse_storage_rejects_weights(lib):
         lib.call("h2ok_hist_destroy", h)
 
 
+# ------------------------------------------------------------------------------------------------ u8 storage
+@pytest.fixture(scope="module")
+def ushard():
+    from h2ok_hist.driver import EngineShard
+
+    s = EngineShard(0, u8=True)
+    yield s
+    s.close()
+
+
+def codes_of(oracle, X, rows, nbins):
+    """The oracle's pre-binning: every column's cells against its root descriptor; NA -> NaN, codes as floats."""
+    root = oracle.root_descs(X, rows, abi.Params.make(nbins=nbins))
+    codes = np.full(X.shape, np.nan, np.float32)
+    for c in range(X.shape[0]):
+        if root[c]["nbin"] > 0:
+            b = oracle.bin_many(X[c, :rows], root[c]).astype(np.float32)
+            b[b == root[c]["nbin"]] = np.nan  # the NA bucket
+            codes[c, :rows] = b
+    return root, codes
+
+
+def test_prebin_matches_the_oracles_bins(ushard, oracle):
+    rows, cols = 70001, 9
+    X, _, _ = oracle.synth(abi.SHAPE_WIDE64, 11, 0, rows, cols, na_permille=20)
+    X[3, :rows] = 2.5  # a constant column: untracked, all NA codes
+    root, codes = codes_of(oracle, X, rows, 255)
+    dX = torch.from_numpy(X).cuda()
+    out = torch.full((cols, X.shape[1]), 7, dtype=torch.uint8, device="cuda")
+    ushard.lib.call("h2ok_hist_prebin_dev", ushard.ctx, C.c_void_p(dX.data_ptr()), X.shape[1], rows, cols, abi.ptr(root),
+                    C.c_void_p(out.data_ptr()), X.shape[1])
+    got = out[:, :rows].cpu().numpy()
+    want = np.where(np.isnan(codes[:, :rows]), 255, codes[:, :rows]).astype(np.uint8)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("rows,cols,depth,na,nbins_pre", [(7, 3, 3, 0, 255), (30011, 70, 6, 10, 255), (60001, 28, 7, 0, 200),
+                                                           (20000, 33, 5, 30, 64)])
+def test_u8_storage_matches_oracle_on_the_codes(ushard, oracle, rows, cols, depth, na, nbins_pre):
+    """H2OK_TREE_U8: trees on pre-binned codes equal the oracle run on the code matrix as integer columns, bit for bit —
+    histograms, ranges, splits, children, routing — whatever number of bins the codes were made with."""
+    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 40 + rows, 0, rows, cols, na_permille=na)
+    _, codes = codes_of(oracle, X, rows, nbins_pre)
+    params = abi.Params.make(nbins=255, max_depth=depth, min_rows=1 if rows < 1000 else 5)
+    check_tree(ushard, oracle, codes, rows, y, None, params, is_int=[1] * cols, host_out=(rows % 2 == 1))
+    assert ushard.stats().range_errors == 0
+
+
+def test_u8_storage_refuses_what_it_cannot_hold(ushard, oracle, lib):
+    from h2ok_hist import capi
+    from h2ok_hist.driver import TreeLoop
+
+    rows, cols = 5000, 4
+    X, y, _ = oracle.synth(abi.SHAPE_HIGGS28, 3, 0, rows, cols)
+    _, codes = codes_of(oracle, X, rows, 255)
+    ushard.set_data_tensors(torch.from_numpy(codes[:, :rows].copy()), torch.from_numpy(y[:rows].copy()))
+    with pytest.raises(capi.H2okError) as e:  # fewer bins than codes: step-1 bins are not guaranteed
+        TreeLoop(ushard, abi.Params.make(nbins=64, max_depth=3))
+    assert e.value.code == abi.ERR_UNSUPPORTED
+    with pytest.raises(capi.H2okError) as e:  # codes are integer columns
+        TreeLoop(ushard, abi.Params.make(nbins=255, max_depth=3), is_int=[0] * cols)
+    assert e.value.code == abi.ERR_ARG
+    ushard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(y[:rows].copy()))  # floats, not codes
+    loop = TreeLoop(ushard, abi.Params.make(nbins=255, max_depth=3))
+    loop.begin_tree()
+    with pytest.raises(capi.H2okError) as e:
+        loop.level()
+    assert e.value.code == abi.ERR_ARG and "code" in str(e.value)
+    h = C.c_void_p()
+    lib.call("h2ok_hist_create", 0, C.byref(h))
+    try:
+        with pytest.raises(capi.H2okError):
+            lib.call("h2ok_hist_tree_create", h, 100, 4, abi.TREE_U8 | abi.TREE_SPARSE)
+        lib.call("h2ok_hist_tree_create", h, 100, 4, 0)
+        buf = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+        with pytest.raises(capi.H2okError) as e:  # bins into a dense shard
+            lib.call("h2ok_hist_tree_load_bins_dev", h, 0, 4, C.c_void_p(buf.data_ptr()), 100)
+        assert e.value.code == abi.ERR_STATE
+    finally:
+        lib.call("h2ok_hist_destroy", h)
+
+
 def test_loop_rejects_wrong_call_order(lib):
     h = C.c_void_p()
     lib.call("h2ok_hist_create", 0, C.byref(h))
