@@ -126,8 +126,16 @@ struct TreeLoop {
   int reduce_mode = H2OK_REDUCE_SCATTER;
   // level buffers (device)
   h2ok_col_desc* descs[2] = {nullptr, nullptr};  // [max_nodes][cols], this level / the next
-  int64_t* acc = nullptr;                        // [pairs padded to a multiple of the ranks][nb1][3]
-  uint32_t* rng = nullptr;                       // [2][max_nodes * cols] encoded observed min | max
+  // accumulators and ranges are double buffered by level parity: the NEXT level's histogram pass is enqueued before
+  // the call returns (see enqueue_hist), while the level that just ran must stay readable (h2ok_hist_loop_view)
+  int64_t* acc2[2] = {nullptr, nullptr};         // [pairs padded to a multiple of the ranks][nb1][3]
+  uint32_t* rng2[2] = {nullptr, nullptr};        // [2][max_nodes * cols] encoded observed min | max
+  int64_t* acc = nullptr;                        // the current level's
+  uint32_t* rng = nullptr;
+  bool pre = false;                              // the current level's histogram pass is already in the stream
+
+  int64_t* done_acc = nullptr;                   // the level h2ok_hist_loop_view shows
+  uint32_t* done_rng = nullptr;
   PairCand* cand = nullptr;                      // [padded pairs]
   h2ok_split* splits = nullptr;                  // [max_nodes]
   int32_t* child_ids = nullptr;                  // [2 * max_nodes]
@@ -152,6 +160,7 @@ struct TreeLoop {
   } ring[kRing];
   int ring_pos = 0;
   EvSet* cur_set = nullptr;
+  EvSet* pre_set = nullptr;  // timing events of a histogram pass that was enqueued ahead (pre)
   double ph_sum[kMaxDepth][5] = {};  // per depth: histogram kernel alone, clear + histogram, reduce, search + children, routing
   int ph_cnt[kMaxDepth] = {};
   int ph_nodes[kMaxDepth] = {};
@@ -192,7 +201,11 @@ void loop_free(h2ok_ctx* c) {
   cudaStreamSynchronize(c->stream);
   if (L->out_stream) cudaStreamSynchronize(L->out_stream);
   for (int k = 0; k < 2; k++) cudaFree(L->descs[k]);
-  cudaFree(L->acc); cudaFree(L->rng); cudaFree(L->cand); cudaFree(L->splits); cudaFree(L->child_ids);
+  for (int k = 0; k < 2; k++) {
+    cudaFree(L->acc2[k]);
+    cudaFree(L->rng2[k]);
+  }
+  cudaFree(L->cand); cudaFree(L->splits); cudaFree(L->child_ids);
   cudaFree(L->n_children); cudaFree(L->tmp_descs); cudaFree(L->tmp_valid); cudaFree(L->hist); cudaFree(L->rngf);
   cudaFree(L->sums); cudaFree(L->sums_tmp); cudaFree(L->q_dev);
   if (L->h_nch) cudaFreeHost(L->h_nch);
@@ -235,6 +248,49 @@ int32_t drain_set(TreeLoop& L, TreeLoop::EvSet& st) {
 
 // ---- the phases of one level; a group of contexts (one host thread, several devices) runs each phase for every
 //      member before the next, with the NCCL calls of a phase inside one ncclGroupStart / ncclGroupEnd ---------------
+// Clear + histogram pass of level `depth` with at most n_bound nodes (descriptors in descs[cur]).  The pass takes the
+// exact node count from the engine's own node table on the device, so it can be enqueued for the NEXT level before the
+// host knows how many children there are: level_finish does that right behind routing, and the GPU never waits for
+// the host's round trip between two levels (on an eighth of the rows that round trip was 0.1 ms of a 1.4 ms level).
+int32_t enqueue_hist(h2ok_ctx* c, int n_bound, int depth, int cur) {
+  TreeLoop& L = *c->loop;
+  const int R = c->comm_ranks;
+  const size_t cell = (size_t)L.nb1 * 3;
+  const int64_t pairs = (int64_t)n_bound * L.cols, chunk = (pairs + R - 1) / R;
+  int64_t* acc = L.acc2[depth & 1];
+  uint32_t* rng = L.rng2[depth & 1];
+  L.cur_set = nullptr;
+  if (L.phases_timed) {
+    TreeLoop::EvSet& st = L.ring[L.ring_pos];
+    L.ring_pos = (L.ring_pos + 1) % TreeLoop::kRing;
+    if (st.used) {
+      const int32_t rc = drain_set(L, st);
+      if (rc) return rc;
+    }
+    st.depth = depth;
+    st.used = true;
+    L.cur_set = &st;
+    CK(cudaEventRecord(st.a, c->stream));
+  }
+  CK(cudaMemsetAsync(acc, 0, sizeof(int64_t) * cell * (size_t)(chunk * R), c->stream));
+  CK(launch_init_enc(rng, rng + L.pairs_cap, pairs, c->stream));
+  // H2O halves nbins_top_level per level (Split.nextLevelHistos: max(parent bins >> 1, nbins)): the shared histogram
+  // is sized for the level's widest one
+  int level_bins = L.params.nbins_top_level >> (depth < 30 ? depth : 30);
+  if (level_bins < L.params.nbins) level_bins = L.params.nbins;
+  const int level_nb1 = level_bins < L.max_bins ? level_bins + 1 : L.nb1;
+  CK(cudaEventRecord(c->ev0, c->stream));
+  if (L.cur_set) CK(cudaEventRecord(L.cur_set->h0, c->stream));
+  CK(engine_build_level(c->eng, n_bound, L.descs[cur], L.nb1, level_nb1, acc, rng, rng + L.pairs_cap, c->stream));
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->timed = true;
+  if (L.cur_set) {
+    CK(cudaEventRecord(L.cur_set->h1, c->stream));
+    CK(cudaEventRecord(L.cur_set->b, c->stream));
+  }
+  return H2OK_OK;
+}
+
 int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
   TreeLoop& L = *c->loop;
   if (!L.have_tree) return fail(H2OK_ERR_STATE, "%s", "loop_level before loop_begin_tree");
@@ -252,42 +308,20 @@ int32_t level_local(h2ok_ctx* c, const h2ok_level_out* out) {
   L.p1 = scatter ? (L.p0 + L.chunk < L.pairs ? L.p0 + L.chunk : L.pairs) : L.pairs;
   if (L.p0 > L.pairs) L.p0 = L.pairs;
   L.last = L.depth + 1 >= L.params.max_depth;
-  const size_t cell = (size_t)L.nb1 * 3;
-  L.cur_set = nullptr;
-  if (L.phases_timed) {
-    TreeLoop::EvSet& st = L.ring[L.ring_pos];
-    L.ring_pos = (L.ring_pos + 1) % TreeLoop::kRing;
-    if (st.used) {
-      const int32_t rc = drain_set(L, st);
-      if (rc) return rc;
-    }
-    st.depth = L.depth;
-    st.used = true;
-    L.cur_set = &st;
-    if (L.depth < TreeLoop::kMaxDepth) L.ph_nodes[L.depth] = n;
-    CK(cudaEventRecord(st.a, c->stream));
+  L.acc = L.acc2[L.depth & 1];
+  L.rng = L.rng2[L.depth & 1];
+  if (!L.pre) {  // (otherwise the pass was enqueued behind the previous level's routing)
+    const int32_t rc = enqueue_hist(c, n, L.depth, L.cur);
+    if (rc) return rc;
   }
-  CK(cudaMemsetAsync(L.acc, 0, sizeof(int64_t) * cell * (size_t)(L.chunk * R), c->stream));
-  CK(launch_init_enc(L.rng, L.rng + L.pairs_cap, L.pairs, c->stream));
-  // H2O halves nbins_top_level per level (Split.nextLevelHistos: max(parent bins >> 1, nbins)): the shared histogram
-  // is sized for the level's widest one
-  int level_bins = L.params.nbins_top_level >> (L.depth < 30 ? L.depth : 30);
-  if (level_bins < L.params.nbins) level_bins = L.params.nbins;
-  const int level_nb1 = level_bins < L.max_bins ? level_bins + 1 : L.nb1;
+  L.pre = false;
+  if (L.depth < TreeLoop::kMaxDepth) L.ph_nodes[L.depth] = n;
+  const size_t cell = (size_t)L.nb1 * 3;
   c->stats.passes = 1;
   c->stats.copies = 1;
   c->stats.launches = 3;
   c->stats.algo_bytes = (double)c->eng.rows * c->eng.cols * 4.0 + (double)c->eng.rows * (c->eng.weighted ? 12.0 : 8.0) +
                         (double)L.pairs * cell * 8.0;
-  CK(cudaEventRecord(c->ev0, c->stream));
-  if (L.cur_set) CK(cudaEventRecord(L.cur_set->h0, c->stream));
-  CK(engine_build_level(c->eng, n, L.descs[L.cur], L.nb1, level_nb1, L.acc, L.rng, L.rng + L.pairs_cap, c->stream));
-  CK(cudaEventRecord(c->ev1, c->stream));
-  c->timed = true;
-  if (L.cur_set) {
-    CK(cudaEventRecord(L.cur_set->h1, c->stream));
-    CK(cudaEventRecord(L.cur_set->b, c->stream));
-  }
   return H2OK_OK;
 }
 
@@ -383,6 +417,18 @@ int32_t level_finish(h2ok_ctx* c) {
   CK(cudaEventRecord(L.ev_out, L.out_stream));
   CK(engine_apply_splits(c->eng, L.splits, L.child_ids, L.gid_base, n, !L.last, c->stream));
   if (L.cur_set) CK(cudaEventRecord(L.cur_set->e, c->stream));
+  // the next level's histogram pass goes in right behind routing, with the node count bounded by twice this level's
+  // (the pass reads the exact count from the engine's node table).  Not for sparse storage, whose pass sizes its
+  // tables from the count.
+  if (!L.last && !c->eng.sparse) {
+    const int n_up = 2 * n < L.max_nodes ? 2 * n : L.max_nodes;
+    TreeLoop::EvSet* mine = L.cur_set;
+    const int32_t rc = enqueue_hist(c, n_up, L.depth + 1, nx);
+    if (rc) return rc;
+    L.pre_set = L.cur_set;
+    L.cur_set = mine;
+    L.pre = true;
+  }
   c->stats.launches += L.last ? 6 : 9;
   return H2OK_OK;
 }
@@ -401,6 +447,13 @@ int32_t level_wait(h2ok_ctx* c, int32_t* n_done, int32_t* n_children) {
                        cudaMemcpyDeviceToHost, L.out_stream));
     CK(cudaStreamSynchronize(L.out_stream));
   }
+  L.done_acc = L.acc;
+  L.done_rng = L.rng;
+  if (L.pre && nch == 0) {  // the tree ended early: the pass enqueued ahead found no node and did nothing
+    if (L.pre_set) L.pre_set->used = false;
+    L.pre = false;
+  }
+  L.cur_set = L.pre ? L.pre_set : nullptr;
   L.done_nodes = L.n_nodes;
   L.done_children = nch;
   L.done_depth = L.depth;
@@ -452,6 +505,8 @@ int32_t begin_tree_finish(h2ok_ctx* c) {
   CK(engine_begin_tree(c->eng, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, nullptr, c->stream, L.q_dev));
   CK(cudaMemcpyAsync(L.descs[0], L.root.data(), sizeof(h2ok_col_desc) * L.cols, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(L.sums, 0, 3 * sizeof(unsigned long long), c->stream));
+  if (L.pre && L.pre_set) L.pre_set->used = false;  // a tree abandoned half way: its pass enqueued ahead is void
+  L.pre = false;
   L.cur = 0;
   L.n_nodes = 1;
   L.depth = 0;
@@ -598,8 +653,10 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
     if (e == cudaSuccess) e = cudaMalloc(p, bytes);
   };
   for (int k = 0; k < 2; k++) A((void**)&L->descs[k], sizeof(h2ok_col_desc) * L->pairs_cap);
-  A((void**)&L->acc, sizeof(int64_t) * cell * L->acc_pairs);
-  A((void**)&L->rng, sizeof(uint32_t) * 2 * L->pairs_cap);
+  for (int k = 0; k < 2; k++) {
+    A((void**)&L->acc2[k], sizeof(int64_t) * cell * L->acc_pairs);
+    A((void**)&L->rng2[k], sizeof(uint32_t) * 2 * L->pairs_cap);
+  }
   A((void**)&L->cand, sizeof(PairCand) * L->acc_pairs);
   A((void**)&L->splits, sizeof(h2ok_split) * (size_t)L->max_nodes);
   A((void**)&L->child_ids, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
@@ -771,9 +828,9 @@ int32_t h2ok_hist_loop_view(h2ok_ctx* c, h2ok_loop_view* v) {
     v->done_pair0 = scatter ? (chunk * c->comm_rank < pairs ? chunk * c->comm_rank : pairs) : 0;
     v->done_pair1 = scatter ? (v->done_pair0 + chunk < pairs ? v->done_pair0 + chunk : pairs) : pairs;
     v->d_done_descs = L.descs[L.done_cur];
-    v->d_done_acc = L.acc;
-    v->d_done_min2_enc = L.rng;
-    v->d_done_maxin_enc = L.rng + L.pairs_cap;
+    v->d_done_acc = L.done_acc;
+    v->d_done_min2_enc = L.done_rng;
+    v->d_done_maxin_enc = L.done_rng + L.pairs_cap;
     v->d_done_splits = L.splits;
     v->d_done_child_ids = L.child_ids;
   } else {
