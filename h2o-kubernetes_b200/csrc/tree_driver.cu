@@ -140,6 +140,7 @@ struct TreeLoop {
   h2ok_split* splits = nullptr;                  // [max_nodes]
   int32_t* child_ids = nullptr;                  // [2 * max_nodes]
   int32_t* n_children = nullptr;                 // [1]
+  h2ok_col_desc* d_root = nullptr;               // [cols] the root descriptors, kept on the device
   h2ok_col_desc* tmp_descs = nullptr;            // [2 * max_nodes][cols] scratch of next_level
   int32_t* tmp_valid = nullptr;                  // [2 * max_nodes]
   double* hist = nullptr;                        // fp64 copy of acc, made only when a caller asks for it
@@ -205,7 +206,7 @@ void loop_free(h2ok_ctx* c) {
     cudaFree(L->acc2[k]);
     cudaFree(L->rng2[k]);
   }
-  cudaFree(L->cand); cudaFree(L->splits); cudaFree(L->child_ids);
+  cudaFree(L->cand); cudaFree(L->d_root); cudaFree(L->splits); cudaFree(L->child_ids);
   cudaFree(L->n_children); cudaFree(L->tmp_descs); cudaFree(L->tmp_valid); cudaFree(L->hist); cudaFree(L->rngf);
   cudaFree(L->sums); cudaFree(L->sums_tmp); cudaFree(L->q_dev);
   if (L->h_nch) cudaFreeHost(L->h_nch);
@@ -503,7 +504,8 @@ int32_t begin_tree_finish(h2ok_ctx* c) {
   CK(launch_quantize_rows_dev(L.tree_y, L.tree_w, n, weighted, L.q_dev, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, c->stream));
   CK(cudaMemsetAsync(c->eng.err, 0, sizeof(int32_t), c->stream));
   CK(engine_begin_tree(c->eng, weighted ? L.wq.p : nullptr, L.wyq.p, L.wyyq.p, nullptr, c->stream, L.q_dev));
-  CK(cudaMemcpyAsync(L.descs[0], L.root.data(), sizeof(h2ok_col_desc) * L.cols, cudaMemcpyHostToDevice, c->stream));
+  // (device to device: a copy from pageable host memory would make the host wait for the stream to drain first)
+  CK(cudaMemcpyAsync(L.descs[0], L.d_root, sizeof(h2ok_col_desc) * L.cols, cudaMemcpyDeviceToDevice, c->stream));
   CK(cudaMemsetAsync(L.sums, 0, 3 * sizeof(unsigned long long), c->stream));
   if (L.pre && L.pre_set) L.pre_set->used = false;  // a tree abandoned half way: its pass enqueued ahead is void
   L.pre = false;
@@ -658,6 +660,7 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
     A((void**)&L->rng2[k], sizeof(uint32_t) * 2 * L->pairs_cap);
   }
   A((void**)&L->cand, sizeof(PairCand) * L->acc_pairs);
+  A((void**)&L->d_root, sizeof(h2ok_col_desc) * (size_t)cols);
   A((void**)&L->splits, sizeof(h2ok_split) * (size_t)L->max_nodes);
   A((void**)&L->child_ids, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
   A((void**)&L->n_children, sizeof(int32_t));
@@ -706,8 +709,11 @@ static int32_t loop_make_root(h2ok_ctx* c) {
     memcpy(&hi[j], &b, 4);
   }
   L->root.resize(cols);
-  return h2ok_hist_root_descs_from_ranges(lo.data(), hi.data(), cols, &L->params, L->is_int.empty() ? nullptr : L->is_int.data(),
-                                          L->root.data());
+  const int32_t rc = h2ok_hist_root_descs_from_ranges(lo.data(), hi.data(), cols, &L->params,
+                                                      L->is_int.empty() ? nullptr : L->is_int.data(), L->root.data());
+  if (rc) return rc;
+  CK(cudaMemcpy(L->d_root, L->root.data(), sizeof(h2ok_col_desc) * cols, cudaMemcpyHostToDevice));
+  return H2OK_OK;
 }
 
 int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int) {
