@@ -490,21 +490,30 @@ int32_t h2ok_hist_apply_splits_dev(h2ok_ctx* c, const float* d_X, int64_t ld, in
 static constexpr int kUploadThreads = 4;
 static constexpr size_t kUploadChunk = (size_t)8 << 20;  // floats per chunk (32 MB)
 
-static cudaError_t upload_columns(int device, float* d_block, int64_t ld, const float* const* cols_host, int32_t ncols,
-                                  int64_t rows) {
+struct Uploader {  // lives for one h2ok_hist_set_data_host call: the pinned buffers are made once, not per block
   struct Worker {
     float* pin = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t free_ev = nullptr;
     cudaError_t err = cudaSuccess;
   } w[kUploadThreads];
-  cudaError_t err = cudaSuccess;
-  for (auto& x : w) {
-    if (err == cudaSuccess) err = cudaMallocHost((void**)&x.pin, kUploadChunk * sizeof(float));
-    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking);
-    if (err == cudaSuccess) err = cudaEventCreateWithFlags(&x.free_ev, cudaEventDisableTiming);
+  cudaError_t init() {
+    cudaError_t err = cudaSuccess;
+    for (auto& x : w) {
+      if (err == cudaSuccess) err = cudaMallocHost((void**)&x.pin, kUploadChunk * sizeof(float));
+      if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking);
+      if (err == cudaSuccess) err = cudaEventCreateWithFlags(&x.free_ev, cudaEventDisableTiming);
+    }
+    return err;
   }
-  if (err == cudaSuccess) {
+  ~Uploader() {
+    for (auto& x : w) {
+      if (x.free_ev) cudaEventDestroy(x.free_ev);
+      if (x.stream) cudaStreamDestroy(x.stream);
+      if (x.pin) cudaFreeHost(x.pin);
+    }
+  }
+  cudaError_t columns(int device, float* d_block, int64_t ld, const float* const* cols_host, int32_t ncols, int64_t rows) {
     const int64_t chunks_per_col = (rows + (int64_t)kUploadChunk - 1) / (int64_t)kUploadChunk;
     const int64_t items = chunks_per_col * ncols;
     std::vector<std::thread> pool;
@@ -525,15 +534,10 @@ static cudaError_t upload_columns(int device, float* d_block, int64_t ld, const 
       });
     for (auto& th : pool) th.join();
     for (auto& x : w)
-      if (err == cudaSuccess) err = x.err;
+      if (x.err != cudaSuccess) return x.err;
+    return cudaSuccess;
   }
-  for (auto& x : w) {
-    if (x.free_ev) cudaEventDestroy(x.free_ev);
-    if (x.stream) cudaStreamDestroy(x.stream);
-    if (x.pin) cudaFreeHost(x.pin);
-  }
-  return err;
-}
+};
 
 int32_t h2ok_hist_set_data_host(h2ok_ctx* c, const float* const* cols_host, int64_t rows, int32_t cols) {
   REQUIRE(c && cols_host, "null pointer");
@@ -545,14 +549,16 @@ int32_t h2ok_hist_set_data_host(h2ok_ctx* c, const float* const* cols_host, int6
   CK(engine_alloc(c->eng, rows, cols, false));
   c->eng_ready = true;
   const int64_t ld = (rows + 63) / 64 * 64;
-  int64_t per = ((int64_t)256 << 20) / (4 * ld);  // columns per staging block (<= 256 MB)
+  int64_t per = ((int64_t)1 << 30) / (4 * ld);  // columns per staging block (<= 1 GB)
   per = per < 1 ? 1 : (per > cols ? cols : per);
   CK(c->X.ensure((size_t)ld * per));
   CK(c->cmin.ensure(cols)); CK(c->cmax.ensure(cols));
+  Uploader up;
+  CK(up.init());
   for (int32_t c0 = 0; c0 < cols; c0 += (int32_t)per) {
     const int32_t nc = cols - c0 < per ? cols - c0 : (int32_t)per;
     CK(cudaStreamSynchronize(c->stream));  // the block is free again (the previous columns have been taken in)
-    CK(upload_columns(c->device, c->X.p, ld, cols_host + c0, nc, rows));
+    CK(up.columns(c->device, c->X.p, ld, cols_host + c0, nc, rows));
     CK(launch_col_ranges(c->X.p, ld, rows, nc, c->cmin.p + c0, c->cmax.p + c0, c->stream));
     CK(engine_load_cols(c->eng, c0, nc, c->X.p, ld, c->stream));
   }

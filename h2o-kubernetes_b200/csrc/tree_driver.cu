@@ -157,7 +157,8 @@ struct TreeLoop {
   struct EvSet {
     cudaEvent_t a = nullptr, h0 = nullptr, h1 = nullptr, b = nullptr, c = nullptr, d = nullptr, e = nullptr;
     int depth = 0;
-    bool used = false;
+    bool used = false;      // recorded (at least its first half) and not yet read back
+    bool complete = false;  // ... up to the end of routing: a pass enqueued ahead is only half a level
   } ring[kRing];
   int ring_pos = 0;
   EvSet* cur_set = nullptr;
@@ -264,12 +265,13 @@ int32_t enqueue_hist(h2ok_ctx* c, int n_bound, int depth, int cur) {
   if (L.phases_timed) {
     TreeLoop::EvSet& st = L.ring[L.ring_pos];
     L.ring_pos = (L.ring_pos + 1) % TreeLoop::kRing;
-    if (st.used) {
+    if (st.used && st.complete) {
       const int32_t rc = drain_set(L, st);
       if (rc) return rc;
     }
     st.depth = depth;
     st.used = true;
+    st.complete = false;
     L.cur_set = &st;
     CK(cudaEventRecord(st.a, c->stream));
   }
@@ -417,7 +419,10 @@ int32_t level_finish(h2ok_ctx* c) {
   }
   CK(cudaEventRecord(L.ev_out, L.out_stream));
   CK(engine_apply_splits(c->eng, L.splits, L.child_ids, L.gid_base, n, !L.last, c->stream));
-  if (L.cur_set) CK(cudaEventRecord(L.cur_set->e, c->stream));
+  if (L.cur_set) {
+    CK(cudaEventRecord(L.cur_set->e, c->stream));
+    L.cur_set->complete = true;
+  }
   // the next level's histogram pass goes in right behind routing, with the node count bounded by twice this level's
   // (the pass reads the exact count from the engine's node table).  Not for sparse storage, whose pass sizes its
   // tables from the count.
@@ -855,7 +860,7 @@ int32_t h2ok_hist_loop_phase_stats(h2ok_ctx* c, int32_t reset, int32_t max_depth
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->stream));
   for (auto& st : L.ring)
-    if (st.used && (rc = drain_set(L, st))) return rc;
+    if (st.used && st.complete && (rc = drain_set(L, st))) return rc;
   for (int d = 0; d < max_depth; d++) {
     count_out[d] = L.ph_cnt[d];
     if (nodes_out) nodes_out[d] = L.ph_nodes[d];
