@@ -35,10 +35,16 @@ WORKLOADS = {
                cols=64, bins=256, depth=8, shape=3),
     "c2": dict(name="GBM histogram build 1M rows x 28 cols (HIGGS-shaped), 256 bins, depth 6 (BASELINE config 2)",
                rows=1_000_000, cols=28, bins=256, depth=6, shape=2),
-    # config 4: the K = 10 class trees of one multinomial iteration, one after the other on the sparse storage (a level
-    # of all ten = one "fused level" of SURVEY.md §8(d)); a step is one class-tree level, ten steps one fused level
+    # config 4: the K = 10 class trees of one multinomial iteration, one after the other on the sparse storage (a step is
+    # one class-tree level; ten steps are one "fused level" of SURVEY.md §8(d), reported as config.fused_level_ms)
     "c4": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, multinomial 10-class targets "
-                    "(BASELINE config 4)", rows=10_000_000, cols=2000, bins=64, depth=6, shape=4, k=10, sparse=True),
+                    "(BASELINE config 4), class trees one after the other", rows=10_000_000, cols=2000, bins=64, depth=6,
+               shape=4, k=10, sparse=True),
+    # the same ten trees built in lockstep as a forest: a step is one level of ALL ten trees, value counts the ten
+    # class-tree levels in it.  Measured slower than "c4" (DESIGN.md §3.4), kept as the comparison.
+    "c4-forest": dict(name="GBM histogram build 10M rows x 2000 sparse-ish cols, 64 bins, depth 6, multinomial 10-class "
+                           "targets (BASELINE config 4), the ten class trees as one forest", rows=10_000_000, cols=2000,
+                      bins=64, depth=6, shape=4, k=10, sparse=True, forest=True),
     # config 3's matrix binned ONCE against its root descriptors (255 global bins) and kept as one byte per cell
     "c3-u8": dict(name="GBM histogram build 100M rows x 64 cols pre-binned to u8 codes (255 global bins + NA), depth 8 "
                        "(BASELINE config 3's matrix, input format of SURVEY.md §8(f) row 4)", rows=100_000_000, cols=64, bins=255,
@@ -51,12 +57,12 @@ CPU_SAMPLE_ROWS = 2_000_000
 CPU_SAMPLE_CELLS = 128_000_000  # and at most this many cells per level (2M rows x 64 columns; 64K rows x 2000)
 
 
-def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False, sparse_nnz=None, u8=False):
+def algo_bytes_level(rows, cols, n_nodes, bins, weighted=False, sparse_nnz=None, u8=False, trees=1):
     """every fp32 cell once, nid + y (+ w) once per row, the fp64 histogram written once.
     Sparse storage (its own formula, include/h2ok_hist.h): 8 bytes per nonzero cell {row, value} instead of 4 bytes per
     cell, and 10 bytes per row (2-byte node + two 4-byte targets)."""
-    if sparse_nnz is not None:
-        return sparse_nnz * 8.0 + rows * 10.0 + n_nodes * cols * (bins + 1) * 3 * 8.0
+    if sparse_nnz is not None:  # (a forest of `trees` class trees reads the cells once and `trees` row records per row)
+        return sparse_nnz * 8.0 + rows * 10.0 * trees + n_nodes * cols * (bins + 1) * 3 * 8.0
     if u8:  # pre-binned codes: one byte per cell
         return rows * cols * 1.0 + rows * 8.0 + n_nodes * cols * (bins + 1) * 3 * 8.0
     return rows * cols * 4.0 + rows * (4.0 + 4.0 + (4.0 if weighted else 0.0)) + n_nodes * cols * (bins + 1) * 3 * 8.0
@@ -311,13 +317,28 @@ def run_gpu(args, wl):
         shard.set_data_synth_prebinned(wl["shape"], SEED, row0, rows, cols, nbins=bins)
     else:
         shard.set_data_synth(wl["shape"], SEED, row0, rows, cols)
-    # K class trees per boosting iteration: K target vectors (y_k = 2 u_k - 1 from their own hashes)
-    ys = [shard.y]
-    for k in range(1, K):
-        yk = torch.empty_like(shard.y)
-        shard.lib.call("h2ok_hist_synth_fill_dev", shard.ctx, abi.SHAPE_HIGGS28, SEED + 7919 * k, row0, rows, cols, shard.ld, 0, 0,
-                       None, C.c_void_p(yk.data_ptr()), None)
-        ys.append(yk)
+    # K class trees per boosting iteration: K target vectors.  They are the residuals the first multinomial iteration
+    # sees, y_k = 1{label == k} - 1/K with label = the largest of the row's first K columns (what scripts/gbm_c4.py
+    # trains on), so that every class tree keeps splitting down to max_depth; independent noise targets (SURVEY.md
+    # §8(d)'s y_k = 2 u_k - 1) stop at the root under min_split_improvement and would time nine one-level trees.
+    forest = bool(wl.get("forest")) and in_library and K > 1
+    ys_all = torch.empty((K, shard.y.numel()), dtype=torch.float32, device=shard.y.device)
+    ys_all[0].copy_(shard.y)
+    if K > 1:
+        best = torch.full((rows,), -float("inf"), device=shard.y.device)
+        label = torch.zeros(rows, dtype=torch.int64, device=shard.y.device)
+        colbuf = torch.empty(shard.ld, dtype=torch.float32, device=shard.y.device)
+        for k in range(K):
+            shard.lib.call("h2ok_hist_synth_fill_cols_dev", shard.ctx, wl["shape"], SEED, row0, rows, k, 1, shard.ld, 0,
+                           C.c_void_p(colbuf.data_ptr()))
+            better = colbuf[:rows] > best
+            label[better] = k
+            best = torch.maximum(best, colbuf[:rows])
+        ys_all.zero_()
+        for k in range(K):
+            ys_all[k, :rows] = (label == k).float() - 1.0 / K
+        del best, label, colbuf
+    ys = [ys_all[k] for k in range(K)]
     tree_no = [0]
 
     def next_targets():
@@ -325,7 +346,7 @@ def run_gpu(args, wl):
         tree_no[0] += 1
         return y
     if in_library:
-        loop = TreeLoop(shard, params, checksum=True, time_phases=True)
+        loop = TreeLoop(shard, params, checksum=True, time_phases=True, forest=K if forest else 1)
     else:
         drv = LevelDriver(shard, params)
         drv.prepare_data()
@@ -347,7 +368,9 @@ def run_gpu(args, wl):
             done += 1
 
     def begin():
-        if in_library:
+        if forest:
+            loop.begin_forest(ys_all)
+        elif in_library:
             loop.begin_tree(y=next_targets())
         else:
             loop.begin_tree()
@@ -372,7 +395,8 @@ def run_gpu(args, wl):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     total_ms = float(ms.item())
     launches = shard.launches - launches0
-    value = rows_total * cols * args.steps / (total_ms * 1e-3)
+    trees_per_step = K if forest else 1  # a forest level is one level of each of its K class trees
+    value = rows_total * cols * trees_per_step * args.steps / (total_ms * 1e-3)
     loop_stats = loop.phase_stats(reset=True) if in_library else None
 
     # result checksum: a full tree on the timed inputs, built right after the timed region.  Integer sums make every
@@ -392,13 +416,13 @@ def run_gpu(args, wl):
     if in_library:
         cnt, nodes, ms = loop_stats
         hist_ms = float(ms[:, 0].sum())
-        abytes = float(sum(int(cnt[d]) * algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz, u8=u8) for d in range(len(cnt))))
+        abytes = float(sum(int(cnt[d]) * algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz, u8=u8, trees=trees_per_step) for d in range(len(cnt))))
         for d in range(len(cnt)):
             if cnt[d]:
                 t = float(ms[d, 0] / cnt[d])
                 level_table[str(d)] = {
                     "nodes": int(nodes[d]), "hist_ms": round(t, 4),
-                    "frac": round(algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz, u8=u8) / (t * 1e-3) / 1e9 / peak, 4),
+                    "frac": round(algo_bytes_level(rows, cols, int(nodes[d]), bins, sparse_nnz=nnz, u8=u8, trees=trees_per_step) / (t * 1e-3) / 1e9 / peak, 4),
                     "reduce_ms": round(float(ms[d, 2] / cnt[d]), 4), "search_ms": round(float(ms[d, 3] / cnt[d]), 4),
                     "route_ms": round(float(ms[d, 4] / cnt[d]), 4)}
         tot = ms.sum(axis=0) / max(1, int(cnt.sum()))
@@ -425,7 +449,7 @@ def run_gpu(args, wl):
 
     # ---- e2e: host buffers in, host buffers out, copies inside the timed region ---------------------------
     e2e = None
-    if not args.no_e2e and in_library:
+    if not args.no_e2e and in_library and not forest:
         e2e = run_e2e_loop(args, wl, shard, loop, world, rank, rows_total, rows, barrier)
 
     cpu = None
@@ -457,10 +481,12 @@ def run_gpu(args, wl):
                        "l2": "inputs larger than L2 (%.1f GB per GPU per level)" % (rows * cols * 4 / 1e9),
                        "per_level": level_table, "phases_ms": phases, "whole_level_frac": round(whole_level_frac, 4),
                        **({"k_classes": K, "storage": "sparse (H2OK_TREE_SPARSE)" if sparse else "dense fp32",
-                           "fused_level_ms": round(K * total_ms / args.steps, 3),
+                           "forest": forest,
+                           "fused_level_ms": round((1 if forest else K) * total_ms / args.steps, 3),
                            "fused_level_note": "one level of all K class trees = K steps; SURVEY.md §8(d)'s floor for it is one "
                                                "read of the DENSE matrix (80.8 GB): frac_of_dense_fused_floor compares with that",
-                           "frac_of_dense_fused_floor": round((rows * cols * 4.0 + K * rows * 8.0) / (K * total_ms / args.steps * 1e-3) / 1e9 / peak, 4)}
+                           "frac_of_dense_fused_floor": round((rows * cols * 4.0 + K * rows * 8.0) /
+                                                              ((1 if forest else K) * total_ms / args.steps * 1e-3) / 1e9 / peak, 4)}
                           if K > 1 else {})},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (NCU_TRAFFIC_BYTES_PER_CELL[args.path] * rows * cols / 1e9

@@ -30,6 +30,7 @@
 namespace h2ok {
 
 constexpr int kEngMaxNodes = 1024;  // >= H2OK_MAX_LEVEL_NODES + 1
+constexpr int kEngMaxClasses = 16;  // class trees a forest builds in lockstep
 
 struct Engine {
   int64_t rows = 0;  // rows of the shard
@@ -53,7 +54,12 @@ struct Engine {
   std::vector<void*> csc_blocks;     // the allocations behind them (one per loaded block of columns)
   int64_t nnz = 0;                   // nonzero cells of the shard
   unsigned long long* node_tot = nullptr;  // [kEngMaxNodes][3] rows / sum wyq / sum wyyq of every node of the level
-  uint2* rec = nullptr;              // [rows] {node, wyq, wyyq} of every row packed in 8 bytes, rebuilt per level
+  uint2* rec = nullptr;              // [rows][K] {node, wyq, wyyq} of every row packed in 8 bytes, rebuilt per level
+  // a forest (sparse storage): K class trees in lockstep.  nid16 / leaf are then [K][rows], the targets [K][ld_targets],
+  // q_dev [K], and every node of the flat list knows its class tree
+  int K = 1, K_alloc = 1;
+  int64_t ld_targets = 0;            // != 0: a forest is being built
+  unsigned char* node_class[2] = {nullptr, nullptr};
   uint8_t* code8 = nullptr;  // [cols][ld8] order-preserving 8-bit code of every cell (255 = NaN), for routing
   uint32_t* thr = nullptr;   // [cols][256] the codes' thresholds (encoded floats, ascending; unused = 0xFFFFFFFF)
   uint32_t* cmin = nullptr;  // [cols] encoded column minimum / maximum of the shard (NaN skipped), taken while loading
@@ -97,6 +103,10 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
 // new tree: every row at the root, records in row order.  q (may be NULL) gives the targets' fixed-point scales, from
 // which the children's centring offsets are derived; without it every node keeps the root's offsets.  The target
 // arrays are read again by every level's regrouping: they must stay valid and unchanged until the tree is finished.
+// a forest of K class trees on the sparse storage (wyq / wyyq: [K][ld] targets, q_dev: [K] scales on the device)
+cudaError_t engine_set_forest(Engine& e, int K);
+cudaError_t engine_begin_forest(Engine& e, int K, const int32_t* wyq, const int32_t* wyyq, int64_t ld, const h2ok_quant* q_dev,
+                                cudaStream_t s);
 // (q_dev: q in device memory instead — a tree then starts without a host round trip; q may be NULL with it)
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
                               const h2ok_quant* q, cudaStream_t s, const h2ok_quant* q_dev = nullptr);

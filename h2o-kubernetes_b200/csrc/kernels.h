@@ -66,10 +66,11 @@ struct PairCand {
 // pairs [pair0, pair1) of the flat [n_nodes * cols] list, from the fp64 histogram (hist != NULL) or straight from the
 // int64 accumulators with q's scales (hist == NULL); cand is indexed by pair
 // (q_dev != NULL: q's scales are read from device memory instead)
+// (node_class != NULL: a forest — q_dev is an array and node_class[node] picks the scales of the node's class tree)
 cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
                                 const h2ok_col_desc* descs,
                                 int64_t pair0, int64_t pair1, int nb1, double min_rows, double msi, PairCand* cand,
-                                cudaStream_t s);
+                                cudaStream_t s, const unsigned char* node_class = nullptr, int cols = 0);
 cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_split* splits, cudaStream_t s);
 // both steps over every pair; cand: [n_nodes * cols] scratch
 cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,

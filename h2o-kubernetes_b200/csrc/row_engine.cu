@@ -88,7 +88,8 @@ __global__ void __launch_bounds__(1024) eng_root_mean_kernel(int64_t rows, const
 __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_rows, const int32_t* __restrict__ wyq_rows,
                                  const int32_t* __restrict__ wyyq_rows, const int32_t* __restrict__ mnode,
                                  int32_t* __restrict__ gidx, uint2* __restrict__ gval, int32_t* __restrict__ gw,
-                                 int32_t* __restrict__ leaf, uint16_t* __restrict__ nid16, int32_t* __restrict__ seg) {
+                                 int32_t* __restrict__ leaf, uint16_t* __restrict__ nid16, int32_t* __restrict__ seg,
+                                 int root = 0) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0) {
     seg[0] = 0;
@@ -97,7 +98,7 @@ __global__ void eng_begin_kernel(int64_t rows, const int32_t* __restrict__ wq_ro
   }
   if (p >= rows) return;
   leaf[p] = -1;
-  nid16[p] = 0;
+  nid16[p] = (uint16_t)root;  // (a forest: class tree k starts at node k of the flat list)
   if (!gidx) return;  // sparse storage keeps no row records: the row -> node map is all it needs
   // zero-weight rows still travel down the tree (a6); the histogram pass skips them by weight
   gidx[p] = (int32_t)p;
@@ -718,7 +719,7 @@ __device__ __forceinline__ float csc_get(const uint2* const* __restrict__ cptr, 
 __global__ void __launch_bounds__(512) eng_node_totals_kernel(int64_t rows, const uint16_t* __restrict__ nid16,
                                                               const int32_t* __restrict__ wyq, const int32_t* __restrict__ wyyq,
                                                               int n_nodes, unsigned long long* __restrict__ tot,
-                                                              uint2* __restrict__ rec) {
+                                                              uint2* __restrict__ rec, int K, int k) {
   extern __shared__ int s_t[];  // [n_nodes][5]: rows, hi/lo of sum wyq, hi/lo of sum wyyq
   const unsigned lane = threadIdx.x & 31u;
   const int64_t per = ((rows + gridDim.x - 1) / gridDim.x + 511) / 512 * 512;
@@ -731,7 +732,8 @@ __global__ void __launch_bounds__(512) eng_node_totals_kernel(int64_t rows, cons
       const int64_t r = rb + threadIdx.x;
       const unsigned nd = r < re ? nid16[r] : kNoNidConst;
       const int a = nd != kNoNidConst ? wyq[r] : 0, b = nd != kNoNidConst ? wyyq[r] : 0;
-      if (r < re) rec[r] = rec_pack(a, b, nd != kNoNidConst && (int)nd < n_nodes ? nd : kNoNode);
+      // (a forest of K class trees keeps the K records of a row next to each other: rec[row][K])
+      if (r < re) rec[r * K + k] = rec_pack(a, b, nd != kNoNidConst && (int)nd < n_nodes ? nd : kNoNode);
       unsigned todo = __ballot_sync(0xffffffffu, nd != kNoNidConst);
       while (todo) {
         const int src = __ffs(todo) - 1;
@@ -762,19 +764,27 @@ __global__ void __launch_bounds__(512) eng_node_totals_kernel(int64_t rows, cons
   }
 }
 
-struct CscNode {  // what the pass needs of one node for one column, 32 bytes
-  double mn, st;
-  int nb;      // 0: (node, column) not tracked
-  int m1, m2;  // centring offsets of the node
-  int pad;
+// What the pass needs of one node for one column, 16 bytes = one shared-memory load per cell (the 32-byte entry it
+// replaces took two, 8 of the pass's ~30 LSU wavefronts per warp and cell).  The node minimum is a float whenever the
+// descriptor came from this library (column ranges, min2 / maxIn and split points are all floats); a caller's
+// descriptor with a minimum that is not sets kCscWide and the exact double is read from a side array.  The centring
+// offsets are kept to their top 10 bits: any offset is exact as long as the flush adds back the same one.
+struct CscNode {
+  double st;
+  float mn;
+  unsigned pk;  // nbin [10:0] (0: (node, column) not tracked) | kCscWide | m1 >> 17 [21:12] (signed) | m2 >> 17 [31:22]
 };
+constexpr unsigned kCscWide = 1u << 11;
+__device__ __forceinline__ int csc_m1(unsigned pk) { return (int)((int)(pk << 10) >> 22) * (1 << 17); }
+__device__ __forceinline__ int csc_m2(unsigned pk) { return (int)(pk >> 22) << 17; }
 
 struct CscHistArgs {
   const uint2* const* cptr;  // [cols] nonzeros of every column
   const int64_t* clen;       // [cols]
   int cols, chunks;
   int node_base;  // this launch covers nodes [node_base, node_base + n_nodes)
-  const uint2* rec;  // [rows] {node, wyq, wyyq} packed (rec_pack)
+  const uint2* rec;  // [rows][K] {node, wyq, wyyq} packed (rec_pack), the K class trees of a forest side by side
+  int K;
   const int32_t* mnode;
   int n_nodes;
   const h2ok_col_desc* descs;
@@ -790,48 +800,117 @@ struct CscHistArgs {
 // 18.6 ms per level on config 4, latency-bound.  Two CTAs share an SM whenever their histograms fit.
 constexpr int kCscThreads = 512;
 
+// The three parts the two passes below share: (1) node tables and zeroed histogram copies in shared memory, (2) one cell
+// of one node added in, (3) the copies added up and flushed.
+struct CscSmem {
+  CscNode* tab;
+  double* mn_wide;
+  unsigned *rmin, *rmax, *h;
+};
+constexpr size_t kCscNodeBytes = sizeof(CscNode) + 8 + 8;  // table entry, exact minimum, range slots
+
+__device__ __forceinline__ CscSmem csc_setup(const CscHistArgs& a, unsigned char* smem_raw, int col, int tid) {
+  const int n = a.n_nodes, nbs = a.nbs, nbase = a.node_base;
+  CscSmem m;
+  m.tab = reinterpret_cast<CscNode*>(smem_raw);
+  m.mn_wide = reinterpret_cast<double*>(m.tab + n);
+  m.rmin = reinterpret_cast<unsigned*>(m.mn_wide + n);
+  m.rmax = m.rmin + n;
+  m.h = m.rmax + n;  // [copy][node][bin][channel]
+  for (int g = tid; g < n; g += kCscThreads) {
+    const h2ok_col_desc d = a.descs[(int64_t)(nbase + g) * a.cols + col];
+    CscNode t;
+    t.mn = (float)d.min;
+    t.st = d.step;
+    unsigned nb = (unsigned)d.nbin;
+    if (d.nbin >= nbs || d.nbin > 1024) {
+      if (blockIdx.x == 0) atomicAdd(a.err, 1);
+      nb = 0;
+    }
+    if (d.nbin < 0) nb = 0;
+    const int m1 = a.mnode[2 * (nbase + g)], m2 = a.mnode[2 * (nbase + g) + 1];
+    t.pk = nb | ((double)t.mn != d.min ? kCscWide : 0u) | (((unsigned)(m1 >> 17) & 0x3FFu) << 12) | (((unsigned)m2 >> 17) << 22);
+    m.tab[g] = t;
+    m.mn_wide[g] = d.min;
+    m.rmin[g] = kEncPosInf;
+    m.rmax[g] = kEncNegInf;
+  }
+  const int words = a.copies * n * nbs * 3;
+  for (int i = tid; i < words; i += kCscThreads) m.h[i] = (i % 3 == 0) ? 0u : kWyBias;
+  __syncthreads();
+  return m;
+}
+
+// (rx, ry): the row's packed record for one tree; a row in a leaf (node 0x3FF) and the all-ones record of a list entry
+// past the end both fall outside [0, n)
+__device__ __forceinline__ void csc_cell(const CscHistArgs& a, const CscSmem& m, unsigned hbase, int col, unsigned rx, unsigned ry,
+                                         float x) {
+  const unsigned nd = rec_node(rx, ry) - (unsigned)a.node_base;
+  if (nd >= (unsigned)a.n_nodes) return;
+  const CscNode t = m.tab[nd];
+  const int nb = (int)(t.pk & 0x7FFu);
+  if (nb == 0) return;
+  const int v1 = ((int)rx >> 5) - csc_m1(t.pk), v2 = (int)(ry >> 5) - csc_m2(t.pk);  // wyq signed, wyyq unsigned
+  const double mn = (t.pk & kCscWide) ? m.mn_wide[nd] : (double)t.mn;
+  const int b = bin_fast(x, mn, t.st, nb);
+  const unsigned addr = hbase + (unsigned)(((int)nd * a.nbs + b) * 12);
+  sh_inc(addr);
+  const unsigned o1 = sh_add(addr + 4u, (unsigned)v1), o2 = sh_add(addr + 8u, (unsigned)v2);
+  const unsigned f1 = wrap_bit(o1, v1), f2 = wrap_bit(o2, v2);
+  if ((f1 | f2) >> 31)
+    eng_carry(a.acc, a.descs, a.node_base + (int)nd, a.cols, col, a.nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
+              (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
+  if (x == x) {
+    const unsigned ex = enc_f32_bits(__float_as_uint(x));
+    if (ex < m.rmin[nd]) atomicMin(&m.rmin[nd], ex);
+    if (ex > m.rmax[nd]) atomicMax(&m.rmax[nd], ex);
+  }
+}
+
+// copies added up, centring undone with the bin's own count
+__device__ __forceinline__ void csc_flush(const CscHistArgs& a, const CscSmem& m, int col, int tid) {
+  const int n = a.n_nodes, nbs = a.nbs, nbase = a.node_base;
+  __syncthreads();
+  for (int t = tid; t < n * nbs; t += kCscThreads) {
+    const int g = t / nbs, b = t - g * nbs;
+    unsigned long long nc = 0;
+    long long n1 = 0, n2 = 0;
+    for (int cp = 0; cp < a.copies; cp++) {
+      const unsigned* w = m.h + ((cp * n + g) * nbs + b) * 3;
+      nc += w[0];
+      n1 += (long long)w[1] - (long long)kWyBias;
+      n2 += (long long)w[2] - (long long)kWyBias;
+    }
+    if (nc | (unsigned long long)n1 | (unsigned long long)n2) {
+      unsigned long long* gp = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(nbase + g) * a.cols + col) * a.nb1 + b) * 3;
+      const long long s1 = n1 + (long long)nc * csc_m1(m.tab[g].pk), s2 = n2 + (long long)nc * csc_m2(m.tab[g].pk);
+      if (nc) atomicAdd(gp, nc);
+      if (s1) atomicAdd(gp + 1, (unsigned long long)s1);
+      if (s2) atomicAdd(gp + 2, (unsigned long long)s2);
+    }
+  }
+  for (int g = tid; g < n; g += kCscThreads) {
+    if (m.rmin[g] != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)(nbase + g) * a.cols + col], m.rmin[g]);
+    if (m.rmax[g] != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)(nbase + g) * a.cols + col], m.rmax[g]);
+  }
+}
+
+// One tree: U list entries per thread in flight, one 8-byte record gather each.
 template <int U>
 __global__ void __launch_bounds__(kCscThreads, U <= 4 ? 2 : 1) eng_hist_csc_kernel(const __grid_constant__ CscHistArgs a) {
   constexpr int THREADS = kCscThreads;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int n = a.n_nodes, nbs = a.nbs, copies = a.copies, nb1 = a.nb1;
-  CscNode* tab = reinterpret_cast<CscNode*>(smem_raw);
-  unsigned* s_rmin = reinterpret_cast<unsigned*>(tab + n);
-  unsigned* s_rmax = s_rmin + n;
-  unsigned* h = s_rmax + n;  // [copy][node][bin][channel]
   const int tid = threadIdx.x, lane = tid & 31;
   const int col = blockIdx.y;
   const int64_t len = a.clen[col];
   const int64_t i0 = len * (int64_t)blockIdx.x / gridDim.x, i1 = len * (int64_t)(blockIdx.x + 1) / gridDim.x;
   if (i0 >= i1) return;
-  const int nbase = a.node_base;
-  for (int g = tid; g < n; g += THREADS) {
-    const h2ok_col_desc d = a.descs[(int64_t)(nbase + g) * a.cols + col];
-    CscNode t;
-    t.mn = d.min;
-    t.st = d.step;
-    t.nb = d.nbin;
-    if (d.nbin >= nbs) {
-      if (blockIdx.x == 0) atomicAdd(a.err, 1);
-      t.nb = 0;
-    }
-    t.m1 = a.mnode[2 * (nbase + g)];
-    t.m2 = a.mnode[2 * (nbase + g) + 1];
-    t.pad = 0;
-    tab[g] = t;
-    s_rmin[g] = kEncPosInf;
-    s_rmax[g] = kEncNegInf;
-  }
-  const int words = copies * n * nbs * 3;
-  for (int i = tid; i < words; i += THREADS) h[i] = (i % 3 == 0) ? 0u : kWyBias;
-  __syncthreads();
-  const unsigned hbase = (unsigned)__cvta_generic_to_shared(h) + (unsigned)((lane & (copies - 1)) * n * nbs) * 12u;
+  const CscSmem m = csc_setup(a, smem_raw, col, tid);
+  const unsigned hbase = (unsigned)__cvta_generic_to_shared(m.h) + (unsigned)((lane & (a.copies - 1)) * a.n_nodes * a.nbs) * 12u;
   const uint2* __restrict__ nz = a.cptr[col];
   const uint2* __restrict__ rec = a.rec;
   for (int64_t ib = i0 + tid; ib < i1; ib += (int64_t)THREADS * U) {
-    uint2 e[U];
-    unsigned nd[U];
-    int w1[U], w2[U];
+    uint2 e[U], rc[U];
 #pragma unroll
     for (int u = 0; u < U; u++) {
       const int64_t i = ib + (int64_t)u * THREADS;
@@ -840,58 +919,55 @@ __global__ void __launch_bounds__(kCscThreads, U <= 4 ? 2 : 1) eng_hist_csc_kern
 #pragma unroll
     for (int u = 0; u < U; u++) {
       const int64_t i = ib + (int64_t)u * THREADS;
-      // a row in a leaf (node 0x3FF) and a list entry past the end both fall outside [0, n)
-      const uint2 rc = i < i1 ? __ldg(rec + e[u].x) : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
-      nd[u] = i < i1 ? rec_node(rc.x, rc.y) - (unsigned)nbase : 0xFFFFFFFFu;
-      w1[u] = (int)rc.x >> 5;        // wyq, signed
-      w2[u] = (int)(rc.y >> 5);      // wyyq, unsigned
+      rc[u] = i < i1 ? __ldg(rec + e[u].x) : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
     }
 #pragma unroll
+    for (int u = 0; u < U; u++) csc_cell(a, m, hbase, col, rc[u].x, rc[u].y, __uint_as_float(e[u].y));
+  }
+  csc_flush(a, m, col, tid);
+}
+
+// A forest of K class trees: a row's K records sit side by side (rec[row][K]) and every list entry is added into the
+// histograms of all K trees, so the column lists are streamed once per level of the whole forest.  Measured on config 4
+// (K = 10, all trees alive): 87 ms per level against 10 x 7.7 ms for the trees one after the other — no gain.  The pass
+// is bound by shared-memory wavefronts and issue slots of the per-(entry, tree) work (node table, binning, three
+// atomics, range), which a forest does not reduce; what it saves is the list stream (2 of ~30 wavefronts per warp and
+// tree) and what it loses is gather locality (a row's 80 bytes are a line of their own, the single tree's 8-byte
+// records share lines between neighbouring rows).  A variant where eight lanes fetch a row's line together and keep
+// the records they fetched (trees 2p, 2p + 1 of entry q) cut the gathers tenfold and still ran at 130-185 ms: 16 steps
+// of 20 live lanes per 32 entries instead of 10 steps of 32.  DESIGN.md §3.4.
+template <int U>
+__global__ void __launch_bounds__(kCscThreads, 2) eng_hist_csc_forest_kernel(const __grid_constant__ CscHistArgs a) {
+  constexpr int THREADS = kCscThreads;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int col = blockIdx.y;
+  const int64_t len = a.clen[col];
+  const int64_t i0 = len * (int64_t)blockIdx.x / gridDim.x, i1 = len * (int64_t)(blockIdx.x + 1) / gridDim.x;
+  if (i0 >= i1) return;
+  const CscSmem m = csc_setup(a, smem_raw, col, tid);
+  const unsigned hbase = (unsigned)__cvta_generic_to_shared(m.h) + (unsigned)((lane & (a.copies - 1)) * a.n_nodes * a.nbs) * 12u;
+  const uint2* __restrict__ nz = a.cptr[col];
+  const uint2* __restrict__ rec = a.rec;
+  const int K = a.K;
+  for (int64_t ib = i0 + tid; ib < i1; ib += (int64_t)THREADS * U) {
+    uint2 e[U], rc[U];
+#pragma unroll
     for (int u = 0; u < U; u++) {
-      if (nd[u] >= (unsigned)n) continue;
-      const CscNode t = tab[nd[u]];
-      if (t.nb <= 0) continue;
-      const float x = __uint_as_float(e[u].y);
-      const int v1 = w1[u] - t.m1, v2 = w2[u] - t.m2;
-      const int b = bin_fast(x, t.mn, t.st, t.nb);
-      const unsigned addr = hbase + (unsigned)(((int)nd[u] * nbs + b) * 12);
-      sh_inc(addr);
-      const unsigned o1 = sh_add(addr + 4u, (unsigned)v1), o2 = sh_add(addr + 8u, (unsigned)v2);
-      const unsigned f1 = wrap_bit(o1, v1), f2 = wrap_bit(o2, v2);
-      if ((f1 | f2) >> 31)
-        eng_carry(a.acc, a.descs, nbase + (int)nd[u], a.cols, col, nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
-                  (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
-      if (x == x) {
-        const unsigned ex = enc_f32_bits(__float_as_uint(x));
-        if (ex < s_rmin[nd[u]]) atomicMin(&s_rmin[nd[u]], ex);
-        if (ex > s_rmax[nd[u]]) atomicMax(&s_rmax[nd[u]], ex);
+      const int64_t i = ib + (int64_t)u * THREADS;
+      e[u] = i < i1 ? __ldg(nz + i) : make_uint2(0u, 0u);
+    }
+    for (int k = 0; k < K; k++) {
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int64_t i = ib + (int64_t)u * THREADS;
+        rc[u] = i < i1 ? __ldg(rec + (int64_t)e[u].x * K + k) : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
       }
+#pragma unroll
+      for (int u = 0; u < U; u++) csc_cell(a, m, hbase, col, rc[u].x, rc[u].y, __uint_as_float(e[u].y));
     }
   }
-  __syncthreads();
-  // flush: copies added up, centring undone with the bin's own count
-  for (int t = tid; t < n * nbs; t += THREADS) {
-    const int g = t / nbs, b = t - g * nbs;
-    unsigned long long nc = 0;
-    long long n1 = 0, n2 = 0;
-    for (int cp = 0; cp < copies; cp++) {
-      const unsigned* w = h + ((cp * n + g) * nbs + b) * 3;
-      nc += w[0];
-      n1 += (long long)w[1] - (long long)kWyBias;
-      n2 += (long long)w[2] - (long long)kWyBias;
-    }
-    if (nc | (unsigned long long)n1 | (unsigned long long)n2) {
-      unsigned long long* gp = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(nbase + g) * a.cols + col) * nb1 + b) * 3;
-      const long long s1 = n1 + (long long)nc * tab[g].m1, s2 = n2 + (long long)nc * tab[g].m2;
-      if (nc) atomicAdd(gp, nc);
-      if (s1) atomicAdd(gp + 1, (unsigned long long)s1);
-      if (s2) atomicAdd(gp + 2, (unsigned long long)s2);
-    }
-  }
-  for (int g = tid; g < n; g += THREADS) {
-    if (s_rmin[g] != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)(nbase + g) * a.cols + col], s_rmin[g]);
-    if (s_rmax[g] != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)(nbase + g) * a.cols + col], s_rmax[g]);
-  }
+  csc_flush(a, m, col, tid);
 }
 
 // The zero cells of every tracked (node, column): totals of the node minus what the column's nonzeros added.
@@ -1098,8 +1174,10 @@ __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ ct
                                                         const h2ok_split* __restrict__ splits, double scale_wy,
                                                         double scale_wyy, const h2ok_quant* __restrict__ q_dev,
                                                         const int32_t* __restrict__ mnode,
-                                                        int32_t* __restrict__ mnode_next) {
-  if (q_dev) {  // the tree's scales live on the device (no host round trip at tree start)
+                                                        int32_t* __restrict__ mnode_next,
+                                                        const unsigned char* __restrict__ node_class,
+                                                        unsigned char* __restrict__ node_class_next) {
+  if (q_dev && !node_class) {  // the tree's scales live on the device (no host round trip at tree start)
     scale_wy = q_dev->scale_wy;
     scale_wyy = q_dev->scale_wyy;
   }
@@ -1151,10 +1229,15 @@ __global__ void __launch_bounds__(1024) eng_scan_kernel(int32_t* __restrict__ ct
     // record, scaled like the targets; scale 0 (weighted shards) keeps every offset at 0
     const h2ok_split sp = splits[g];
     const int pm1 = mnode[2 * g], pm2 = mnode[2 * g + 1];
+    if (node_class) {  // a forest: every class tree has its own fixed-point scales; children stay in their parent's tree
+      scale_wy = q_dev[node_class[g]].scale_wy;
+      scale_wyy = q_dev[node_class[g]].scale_wyy;
+    }
 #pragma unroll
     for (int way = 0; way < 2; way++) {
       const int ch = child_ids[2 * g + way];
       if (ch < 0) continue;
+      if (node_class) node_class_next[ch] = node_class[g];
       const double pred = way ? sp.pred_right : sp.pred_left, se = way ? sp.se_right : sp.se_left;
       const double n = way ? sp.n_right : sp.n_left;
       int c1 = pm1, c2 = pm2;
@@ -1305,6 +1388,7 @@ cudaError_t engine_alloc(Engine& e, int64_t rows, int cols, bool weighted, bool 
     A((void**)&e.csc_len, sizeof(int64_t) * (size_t)cols);
     A((void**)&e.node_tot, sizeof(unsigned long long) * 3 * kEngMaxNodes);
     A((void**)&e.rec, sizeof(uint2) * (size_t)rows);
+    for (int k = 0; k < 2; k++) A((void**)&e.node_class[k], kEngMaxNodes);
     if (err == cudaSuccess) err = cudaMemset(e.csc_ptr, 0, sizeof(uint2*) * (size_t)cols);
     if (err == cudaSuccess) err = cudaMemset(e.csc_len, 0, sizeof(int64_t) * (size_t)cols);
     e.nnz = 0;
@@ -1354,7 +1438,11 @@ void engine_free(Engine& e) {
   for (void* p : e.csc_blocks) cudaFree(p);
   e.csc_blocks.clear();
   cudaFree(e.csc_ptr); cudaFree(e.csc_len); cudaFree(e.node_tot); cudaFree(e.rec);
+  cudaFree(e.node_class[0]); cudaFree(e.node_class[1]);
+  e.node_class[0] = e.node_class[1] = nullptr;
   e.rec = nullptr;
+  e.K = e.K_alloc = 1;
+  e.ld_targets = 0;
   e.csc_ptr = nullptr;
   e.csc_len = nullptr;
   e.node_tot = nullptr;
@@ -1483,8 +1571,60 @@ cudaError_t engine_load_cols(Engine& e, int col0, int ncols, const float* X, int
   return launch_col_ranges(X, ld, e.rows, ncols, e.cmin + col0, e.cmax + col0, s);  // DHistogram.initialHist reads them
 }
 
+// A forest: K class trees built in lockstep on the sparse storage (one pass over the column lists per level for all of
+// them).  Every row then sits in K nodes, one per tree; the node list of a level is flat, class after class.
+cudaError_t engine_set_forest(Engine& e, int K) {
+  if (!e.sparse || K < 1 || K > kEngMaxClasses) return cudaErrorInvalidValue;
+  if (K == e.K_alloc) {
+    e.K = K;
+    return cudaSuccess;
+  }
+  cudaFree(e.nid16); cudaFree(e.leaf); cudaFree(e.rec);
+  e.nid16 = nullptr;
+  e.leaf = nullptr;
+  e.rec = nullptr;
+  cudaError_t err = cudaMalloc((void**)&e.nid16, sizeof(uint16_t) * (size_t)e.rows * K);
+  if (err == cudaSuccess) err = cudaMalloc((void**)&e.leaf, sizeof(int32_t) * (size_t)e.rows * K);
+  if (err == cudaSuccess) err = cudaMalloc((void**)&e.rec, sizeof(uint2) * (size_t)e.rows * K);
+  if (err != cudaSuccess) return err;
+  e.K = e.K_alloc = K;
+  return cudaSuccess;
+}
+
+__global__ void eng_forest_classes_kernel(int K, unsigned char* __restrict__ node_class) {
+  if ((int)threadIdx.x < K) node_class[threadIdx.x] = (unsigned char)threadIdx.x;
+}
+
+// wyq / wyyq: [K][ld] the class trees' targets in original row order; q_dev: [K] their scales on the device
+cudaError_t engine_begin_forest(Engine& e, int K, const int32_t* wyq, const int32_t* wyyq, int64_t ld, const h2ok_quant* q_dev,
+                                cudaStream_t s) {
+  cudaError_t err = engine_set_forest(e, K);
+  if (err != cudaSuccess) return err;
+  e.cur = 0;
+  e.n_nodes = K;
+  e.scale_wy = e.scale_wyy = 0.0;
+  e.q_dev = q_dev;
+  e.wq_rows = nullptr;
+  e.wyq_rows = wyq;
+  e.wyyq_rows = wyyq;
+  e.ld_targets = ld;
+  for (int k = 0; k < K; k++) {
+    eng_root_mean_kernel<<<1, 1024, 0, s>>>(e.rows, wyq + k * ld, wyyq + k * ld, false, e.mnode[0] + 2 * k);
+    eng_begin_kernel<<<nblk(e.rows, 256), 256, 0, s>>>(e.rows, nullptr, wyq + k * ld, wyyq + k * ld, e.mnode[0] + 2 * k, nullptr,
+                                                       nullptr, nullptr, e.leaf + (int64_t)k * e.rows,
+                                                       e.nid16 + (int64_t)k * e.rows, e.seg[0], k);
+  }
+  eng_forest_classes_kernel<<<1, 32, 0, s>>>(K, e.node_class[0]);
+  return cudaGetLastError();
+}
+
 cudaError_t engine_begin_tree(Engine& e, const int32_t* wq_rows, const int32_t* wyq_rows, const int32_t* wyyq_rows,
                               const h2ok_quant* q, cudaStream_t s, const h2ok_quant* q_dev) {
+  if (e.sparse && e.K != 1) {
+    cudaError_t err = engine_set_forest(e, 1);
+    if (err != cudaSuccess) return err;
+  }
+  e.ld_targets = 0;
   e.q_dev = q_dev;
   e.cur = 0;
   e.n_nodes = 1;
@@ -1539,7 +1679,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     if (!e.wyq_rows) return cudaErrorInvalidValue;
     e.n_nodes = n_nodes;
     // nodes per pass: descriptor table + range slots + at least one histogram copy per node must fit one CTA
-    const size_t per_node = sizeof(CscNode) + 8 + (size_t)nbs * 12;
+    const size_t per_node = kCscNodeBytes + (size_t)nbs * 12;
     // What a CTA takes when its histogram allows a choice: 56 KB.  More copies (112 KB) cut bank conflicts but leave the
     // SM 30 KB of L1 for the row-record gathers: 14 ms per level against 8.5 ms on config 4 (32 nodes, 64 bins).
     const size_t two_per_sm = 56 * 1024;
@@ -1548,13 +1688,16 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     if (group > n_nodes) group = n_nodes;
     cudaError_t err = cudaMemsetAsync(e.node_tot, 0, sizeof(unsigned long long) * 3 * (size_t)n_nodes, s);
     if (err != cudaSuccess) return err;
-    eng_node_totals_kernel<<<4 * e.sms, 512, sizeof(int) * 5 * (size_t)n_nodes, s>>>(e.rows, e.nid16, e.wyq_rows, e.wyyq_rows,
-                                                                                    n_nodes, e.node_tot, e.rec);
+    for (int k = 0; k < e.K; k++)
+      eng_node_totals_kernel<<<4 * e.sms, 512, sizeof(int) * 5 * (size_t)n_nodes, s>>>(
+          e.rows, e.nid16 + (int64_t)k * e.rows, e.wyq_rows + (int64_t)k * e.ld_targets, e.wyyq_rows + (int64_t)k * e.ld_targets,
+          n_nodes, e.node_tot, e.rec, e.K, k);
     static std::atomic<bool> attr_done[64];
     int dev = 0;
     cudaGetDevice(&dev);
     if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
       cudaError_t ea = cudaFuncSetAttribute(eng_hist_csc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+      if (ea == cudaSuccess) ea = cudaFuncSetAttribute(eng_hist_csc_forest_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
       if (ea != cudaSuccess) return ea;
       attr_done[dev & 63].store(true, std::memory_order_release);
     }
@@ -1563,6 +1706,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     a.clen = e.csc_len;
     a.cols = e.cols;
     a.rec = e.rec;
+    a.K = e.K;
     a.mnode = e.mnode[e.cur];
     a.descs = descs;
     a.nb1 = nb1;
@@ -1580,13 +1724,16 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
       a.n_nodes = n_nodes - base < group ? n_nodes - base : group;
       // copies of the histogram (chosen by lane) spread the warp's atomics over more banks; as many as fit while two
       // CTAs still share the SM, or one CTA's worth when even a single copy needs more than that
-      const size_t one = (size_t)a.n_nodes * (sizeof(CscNode) + 8 + (size_t)nbs * 12);
-      const size_t cap = one <= two_per_sm ? two_per_sm : (size_t)kHistSmemCap;
+      const size_t one = (size_t)a.n_nodes * (kCscNodeBytes + (size_t)nbs * 12);
+      // (a level whose single copy is past that but under 100 KB keeps one copy, so that two CTAs still share the SM)
+      const size_t cap = one <= two_per_sm ? two_per_sm : (one <= 100 * 1024 ? one : (size_t)kHistSmemCap);
       a.copies = 1;
-      while (a.copies < 8 && (size_t)a.n_nodes * (sizeof(CscNode) + 8 + (size_t)nbs * 12 * (a.copies * 2)) <= cap) a.copies *= 2;
-      const size_t smem = (size_t)a.n_nodes * (sizeof(CscNode) + 8 + (size_t)nbs * 12 * a.copies);
+      while (a.copies < 8 && (size_t)a.n_nodes * (kCscNodeBytes + (size_t)nbs * 12 * (a.copies * 2)) <= cap) a.copies *= 2;
+      const size_t smem = (size_t)a.n_nodes * (kCscNodeBytes + (size_t)nbs * 12 * a.copies);
       // four cells per thread in flight (two: 9.2 ms per level on config 4, four: 8.1, eight at one CTA per SM: 15.7)
-      eng_hist_csc_kernel<4><<<dim3((unsigned)chunks, (unsigned)e.cols), kCscThreads, smem, s>>>(a);
+      const dim3 grid((unsigned)chunks, (unsigned)e.cols);
+      if (e.K == 1) eng_hist_csc_kernel<4><<<grid, kCscThreads, smem, s>>>(a);
+      else eng_hist_csc_forest_kernel<4><<<grid, kCscThreads, smem, s>>>(a);
     }
     const int64_t pairs = (int64_t)n_nodes * e.cols;
     eng_csc_zero_kernel<<<(unsigned)((pairs + 7) / 8), 256, 0, s>>>(n_nodes, e.cols, descs, nb1, e.node_tot, acc, min2_enc, maxin_enc);
@@ -1658,13 +1805,15 @@ cudaError_t engine_apply_splits(Engine& e, const h2ok_split* splits, const int32
   const int G = e.route_ctas;
   const int n_slots = 2 * n_nodes < kEngMaxNodes ? 2 * n_nodes : kEngMaxNodes;  // child ids are < this
   const size_t rsmem = (size_t)n_nodes * sizeof(RouteNode) + (size_t)n_slots * sizeof(int);
-  eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, e.csc_ptr, e.csc_len, e.code8, e.ld8, e.thr, e.rows, n_nodes, splits,
-                                                   child_ids,
-                                                   gid_base, e.nid16, e.leaf, e.cta_cnt, n_slots, e.u8 ? 1 : 0);
+  for (int k = 0; k < (e.sparse ? e.K : 1); k++)  // a forest routes every class tree's row -> node map with the same flat tables
+    eng_route_kernel<<<G, kRouteThreads, rsmem, s>>>(e.XT, e.ldt, e.csc_ptr, e.csc_len, e.code8, e.ld8, e.thr, e.rows, n_nodes, splits,
+                                                     child_ids, gid_base, e.nid16 + (int64_t)k * e.rows,
+                                                     e.leaf + (int64_t)k * e.rows, e.cta_cnt, n_slots, e.u8 ? 1 : 0);
   // every level but a tree's last: lay the children's records out for the next histogram pass
+  const bool forest = e.sparse && e.ld_targets != 0;
   eng_scan_kernel<<<1, 1024, 0, s>>>(e.cta_cnt, G, n_nodes, child_ids, e.seg[nx], splits, e.scale_wy, e.scale_wyy,
-                                     e.weighted ? nullptr : e.q_dev,
-                                     e.mnode[e.cur], e.mnode[nx]);
+                                     e.weighted ? nullptr : e.q_dev, e.mnode[e.cur], e.mnode[nx],
+                                     forest ? e.node_class[e.cur] : nullptr, forest ? e.node_class[nx] : nullptr);
   if (regroup && !e.sparse) {
     const size_t ncp = (size_t)(n_slots + 1) & ~(size_t)1;
     const size_t ssmem = ncp * (4 * sizeof(int) + sizeof(int2)) +

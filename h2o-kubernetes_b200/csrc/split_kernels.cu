@@ -239,6 +239,7 @@ __device__ float warp_splat(const V& vals, const h2ok_col_desc& d, int bin, int 
 // n_nodes may live on the device (n_dev != NULL): grids are then sized by an upper bound and surplus warps leave.
 template <class V>
 __global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, const h2ok_quant* __restrict__ q_dev,
+                                                                        const unsigned char* __restrict__ node_class, int cols,
                                                                         const h2ok_col_desc* __restrict__ descs,
                                                                         int64_t pair0, int64_t pair1, int nb1,
                                                                         double min_rows, double msi,
@@ -254,7 +255,8 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, 
   pc.key = pc.seL = pc.seR = pc.nL = pc.nR = pc.pL = pc.pR = pc.se_before = 0;
   if (d.nbin > 1) {
     V vals = base;
-    if (q_dev) vals.scales_from(q_dev);
+    // (a forest: the node's class tree has its own scales)
+    if (q_dev) vals.scales_from(node_class ? q_dev + node_class[pair / cols] : q_dev);
     vals.p += pair * nb1 * 3;
     Cand cand;
     double before;
@@ -493,12 +495,12 @@ __global__ void apply_splits_kernel(const float* __restrict__ X, int64_t ld, int
 
 cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
                                 const h2ok_col_desc* descs, int64_t pair0, int64_t pair1, int nb1, double min_rows,
-                                double msi, PairCand* cand, cudaStream_t s) {
+                                double msi, PairCand* cand, cudaStream_t s, const unsigned char* node_class, int cols) {
   if (pair1 <= pair0) return cudaSuccess;
   const unsigned grid = (unsigned)((pair1 - pair0 + kSplitWarps - 1) / kSplitWarps);
   if (hist) {
-    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, 0, s>>>(ValsF64{hist}, nullptr, descs, pair0, pair1, nb1, min_rows,
-                                                                   msi, cand);
+    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, 0, s>>>(ValsF64{hist}, nullptr, nullptr, 1, descs, pair0, pair1, nb1,
+                                                                   min_rows, msi, cand);
   } else {
     ValsAcc v{acc, {1.0, 1.0, 1.0}};
     if (!q_dev) {
@@ -506,7 +508,8 @@ cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2
       v.inv[1] = 1.0 / q->scale_wy;
       v.inv[2] = 1.0 / q->scale_wyy;
     }
-    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, 0, s>>>(v, q_dev, descs, pair0, pair1, nb1, min_rows, msi, cand);
+    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, 0, s>>>(v, q_dev, node_class, cols > 0 ? cols : 1, descs, pair0, pair1,
+                                                                   nb1, min_rows, msi, cand);
   }
   return cudaGetLastError();
 }

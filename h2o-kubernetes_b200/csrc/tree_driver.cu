@@ -123,6 +123,7 @@ struct TreeLoop {
   std::vector<int32_t> is_int;
   std::vector<h2ok_col_desc> root;
   int cols = 0, max_nodes = 0, max_bins = 0, nb1 = 0;
+  int forest = 1;  // class trees built in lockstep (h2ok_hist_loop_create_forest); 1: one tree
   int reduce_mode = H2OK_REDUCE_SCATTER;
   // level buffers (device)
   h2ok_col_desc* descs[2] = {nullptr, nullptr};  // [max_nodes][cols], this level / the next
@@ -174,6 +175,7 @@ struct TreeLoop {
   h2ok_quant* h_q = nullptr;    // pinned host copy (arrives with the first level's results)
   const float* tree_y = nullptr;  // the current tree's targets between the phases of loop_begin_tree
   const float* tree_w = nullptr;
+  int64_t tree_ld = 0;
   bool have_tree = false, checksum = false;
   // tree state
   int cur = 0, n_nodes = 0, depth = 0, gid_base = 0;
@@ -353,7 +355,8 @@ int32_t level_search(h2ok_ctx* c) {
   CK(cudaSetDevice(c->device));
   if (L.cur_set) CK(cudaEventRecord(L.cur_set->c, c->stream));
   CK(launch_split_points(nullptr, L.acc, nullptr, L.q_dev, L.descs[L.cur], L.p0, L.p1, L.nb1, L.params.min_rows,
-                         L.params.min_split_improvement, L.cand, c->stream));
+                         L.params.min_split_improvement, L.cand, c->stream,
+                         L.forest > 1 ? c->eng.node_class[c->eng.cur] : nullptr, L.cols));
   if (L.checksum && L.p1 > L.p0) {
     const int64_t cell = (int64_t)L.nb1 * 3, cnt = (L.p1 - L.p0) * cell;
     hash_i64_kernel<<<grid_for(cnt, 256, 1184), 256, 0, c->stream>>>(L.acc + L.p0 * cell, cnt, (uint64_t)(L.p0 * cell),
@@ -379,6 +382,8 @@ int32_t level_finish(h2ok_ctx* c) {
   CK(cudaSetDevice(c->device));
   const int n = L.n_nodes, nx = 1 - L.cur;
   const h2ok_level_out* out = L.out;
+  if (out && out->hist && L.forest > 1)
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "a forest level does not deliver the fp64 histogram (read the accumulators: loop_view)");
   CK(launch_best_col(L.cand, n, L.cols, L.splits, c->stream));
   if (L.last) {
     CK(cudaMemsetAsync(L.child_ids, 0xFF, sizeof(int32_t) * 2 * (size_t)n, c->stream));
@@ -478,6 +483,7 @@ int32_t level_wait(h2ok_ctx* c, int32_t* n_done, int32_t* n_children) {
 // a tree's start in three phases (a group runs each phase for all its members, the NCCL one inside a group call)
 int32_t begin_tree_local(h2ok_ctx* c, const float* d_y, const float* d_w) {
   TreeLoop& L = *c->loop;
+  if (L.forest > 1) return fail(H2OK_ERR_STATE, "%s", "this loop builds a forest: start its trees with loop_begin_forest_dev");
   CK(cudaSetDevice(c->device));
   const int64_t n = c->eng.rows;
   const size_t pad = (size_t)(n + 3) / 4 * 4;
@@ -529,14 +535,63 @@ int32_t begin_tree_common(h2ok_ctx* c, const float* d_y, const float* d_w) {
   return begin_tree_finish(c);
 }
 
+// K class trees in lockstep (sparse storage): d_y holds the K target vectors [K][ld_y]
+int32_t begin_forest_local(h2ok_ctx* c, const float* d_y, int64_t ld_y) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  if (!c->eng.sparse) return fail(H2OK_ERR_UNSUPPORTED, "%s", "a forest needs a shard created with H2OK_TREE_SPARSE");
+  const int K = L.forest;
+  const int64_t n = c->eng.rows;
+  const size_t pad = (size_t)(n + 3) / 4 * 4;
+  CK(L.wyq.ensure(pad * K)); CK(L.wyyq.ensure(pad * K)); CK(L.absmax.ensure(3 * (size_t)K));
+  L.tree_y = d_y;
+  L.tree_w = nullptr;
+  L.tree_ld = ld_y;
+  for (int k = 0; k < K; k++) CK(launch_target_absmax(d_y + (int64_t)k * ld_y, nullptr, n, L.absmax.p + 3 * k, c->stream));
+  return H2OK_OK;
+}
+int32_t begin_forest_reduce(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  if (c->comm_ranks > 1)
+    NK(nccl_api()->AllReduce(L.absmax.p, L.absmax.p, 3 * (size_t)L.forest, ncclFloat64, ncclMax, (ncclComm_t)c->comm, c->stream));
+  return H2OK_OK;
+}
+int32_t begin_forest_finish(h2ok_ctx* c) {
+  TreeLoop& L = *c->loop;
+  CK(cudaSetDevice(c->device));
+  const int K = L.forest;
+  const int64_t n = c->eng.rows;
+  const size_t pad = (size_t)(n + 3) / 4 * 4;
+  for (int k = 0; k < K; k++) {
+    CK(launch_choose_quant_dev(L.absmax.p + 3 * k, 0, 25, L.q_dev + k, c->stream));
+    CK(launch_quantize_rows_dev(L.tree_y + (int64_t)k * L.tree_ld, nullptr, n, false, L.q_dev + k, nullptr, L.wyq.p + pad * k,
+                                L.wyyq.p + pad * k, c->stream));
+    CK(cudaMemcpyAsync(L.descs[0] + (size_t)k * L.cols, L.d_root, sizeof(h2ok_col_desc) * L.cols, cudaMemcpyDeviceToDevice,
+                       c->stream));
+  }
+  CK(cudaMemcpyAsync(L.h_q, L.q_dev, sizeof(h2ok_quant) * (size_t)K, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemsetAsync(c->eng.err, 0, sizeof(int32_t), c->stream));
+  CK(engine_begin_forest(c->eng, K, L.wyq.p, L.wyyq.p, (int64_t)pad, L.q_dev, c->stream));
+  CK(cudaMemsetAsync(L.sums, 0, 3 * sizeof(unsigned long long), c->stream));
+  L.pre = false;
+  L.cur = 0;
+  L.n_nodes = K;
+  L.depth = 0;
+  L.gid_base = 0;
+  L.done_depth = -1;
+  L.have_tree = true;
+  return H2OK_OK;
+}
+
 // the checksum query in three phases
 int32_t checksum_local(h2ok_ctx* c, int64_t row0) {
   TreeLoop& L = *c->loop;
   if (!L.checksum) return fail(H2OK_ERR_STATE, "%s", "loop_checksum: switch the checksum on with loop_set_options first");
   CK(cudaSetDevice(c->device));
   CK(cudaMemsetAsync(L.sums + 2, 0, sizeof(unsigned long long), c->stream));
-  hash_i32_kernel<<<grid_for(c->eng.rows, 256, 1184), 256, 0, c->stream>>>(c->eng.leaf, c->eng.rows, (uint64_t)row0, kSaltLeaf,
-                                                                          L.sums + 2);
+  for (int k = 0; k < L.forest; k++)  // (a forest: every class tree's leaves, each under its own salt)
+    hash_i32_kernel<<<grid_for(c->eng.rows, 256, 1184), 256, 0, c->stream>>>(c->eng.leaf + (int64_t)k * c->eng.rows, c->eng.rows,
+                                                                            (uint64_t)row0, kSaltLeaf + 0x100ull * k, L.sums + 2);
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(L.sums_tmp, L.sums, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
   if (c->comm_ranks > 1 && c->comm_rank != 0) {
@@ -623,7 +678,7 @@ int32_t h2ok_hist_tree_load_synth(h2ok_ctx* c, int32_t shape, uint64_t seed, int
 }
 
 // ------------------------------------------------------------------------------------------------ the loop
-static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int) {
+static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int, int forest = 1) {
   REQUIRE(c && params, "null pointer");
   if (!c->eng_ready) return fail(H2OK_ERR_STATE, "%s", "loop_create before tree_create / the data is loaded");
   REQUIRE(params->max_depth >= 1 && params->nbins >= 1 && params->nbins_top_level >= 1, "bad params");
@@ -650,6 +705,14 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
   L->nb1 = max_bins + 1;
   if (is_int) L->is_int.assign(is_int, is_int + cols);
   int64_t mn = (int64_t)1 << (params->max_depth - 1 < 10 ? params->max_depth - 1 : 10);
+  L->forest = forest;
+  if (forest > 1) {
+    mn *= forest;  // the flat node list of a level holds every class tree's nodes
+    if (mn > H2OK_MAX_LEVEL_NODES) {
+      loop_free(c);
+      return fail(H2OK_ERR_UNSUPPORTED, "%s", "forest: n_trees * 2^(max_depth-1) must not exceed H2OK_MAX_LEVEL_NODES");
+    }
+  }
   L->max_nodes = (int)(mn < H2OK_MAX_LEVEL_NODES ? mn : H2OK_MAX_LEVEL_NODES);
   const int R = c->comm_ranks;
   L->pairs_cap = (size_t)L->max_nodes * cols;
@@ -673,9 +736,9 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
   A((void**)&L->tmp_valid, sizeof(int32_t) * 2 * (size_t)L->max_nodes);
   A((void**)&L->sums, 3 * sizeof(unsigned long long));
   A((void**)&L->sums_tmp, 3 * sizeof(unsigned long long));
-  A((void**)&L->q_dev, sizeof(h2ok_quant));
+  A((void**)&L->q_dev, sizeof(h2ok_quant) * (size_t)forest);
   if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_nch, sizeof(int32_t));
-  if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_q, sizeof(h2ok_quant));
+  if (e == cudaSuccess) e = cudaMallocHost((void**)&L->h_q, sizeof(h2ok_quant) * (size_t)forest);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->out_stream, cudaStreamNonBlocking);
   for (cudaEvent_t* ev : {&L->ev_ready, &L->ev_out})
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
@@ -726,6 +789,38 @@ int32_t h2ok_hist_loop_create(h2ok_ctx* c, const h2ok_params* params, const int3
   if (rc) return rc;
   if ((rc = loop_reduce_ranges(c))) return rc;
   return loop_make_root(c);
+}
+
+int32_t h2ok_hist_loop_create_forest(h2ok_ctx* c, const h2ok_params* params, const int32_t* is_int, int32_t n_trees) {
+  REQUIRE(c != nullptr, "null context");
+  REQUIRE(n_trees >= 1 && n_trees <= kEngMaxClasses, "n_trees outside [1, 16]");
+  if (n_trees > 1 && !(c->eng_ready && c->eng.sparse))
+    return fail(H2OK_ERR_UNSUPPORTED, "%s", "a forest needs a shard created with H2OK_TREE_SPARSE");
+  int32_t rc = loop_alloc(c, params, is_int, n_trees);
+  if (rc) return rc;
+  if ((rc = loop_reduce_ranges(c))) return rc;
+  return loop_make_root(c);
+}
+
+int32_t h2ok_hist_loop_begin_forest_dev(h2ok_ctx* c, const float* d_y, int64_t ld) {
+  int32_t rc = need_loop(c, "loop_begin_forest_dev");
+  if (rc) return rc;
+  REQUIRE(d_y != nullptr && ld >= c->eng.rows, "bad arguments");
+  if (c->loop->forest == 1) return begin_tree_common(c, d_y, nullptr);
+  if ((rc = begin_forest_local(c, d_y, ld))) return rc;
+  if ((rc = begin_forest_reduce(c))) return rc;
+  return begin_forest_finish(c);
+}
+
+int32_t h2ok_hist_loop_forest_quants(h2ok_ctx* c, h2ok_quant* out) {
+  int32_t rc = need_loop(c, "loop_forest_quants");
+  if (rc) return rc;
+  REQUIRE(out != nullptr, "null pointer");
+  if (!c->loop->have_tree) return fail(H2OK_ERR_STATE, "%s", "loop_forest_quants before a tree was begun");
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));  // the host copy of the scales travels behind the tree's set-up
+  memcpy(out, c->loop->h_q, sizeof(h2ok_quant) * (size_t)c->loop->forest);
+  return H2OK_OK;
 }
 
 int32_t h2ok_hist_loop_destroy(h2ok_ctx* c) {
@@ -821,6 +916,7 @@ int32_t h2ok_hist_loop_view(h2ok_ctx* c, h2ok_loop_view* v) {
   v->rank = c->comm_rank;
   v->n_ranks = c->comm_ranks;
   v->reduce_mode = L.reduce_mode;
+  v->n_trees = L.forest;
   CK(cudaStreamSynchronize(c->stream));  // the host copy of the scales is in flight until the tree's first level is done
   v->quant = *L.h_q;
   v->d_descs = L.descs[L.cur];

@@ -62,7 +62,7 @@ class LoopView(C.Structure):
                 ("max_nodes", C.c_int32), ("max_bins", C.c_int32), ("cols", C.c_int32), ("rank", C.c_int32),
                 ("n_ranks", C.c_int32), ("reduce_mode", C.c_int32),
                 ("done_depth", C.c_int32), ("done_nodes", C.c_int32), ("done_children", C.c_int32),
-                ("done_gid_base", C.c_int32), ("pad", C.c_int32),
+                ("done_gid_base", C.c_int32), ("n_trees", C.c_int32),
                 ("done_pair0", C.c_int64), ("done_pair1", C.c_int64), ("quant", Quant),
                 ("d_descs", C.c_void_p), ("d_wq", C.c_void_p), ("d_wyq", C.c_void_p), ("d_wyyq", C.c_void_p),
                 ("d_leaf", C.c_void_p), ("d_done_descs", C.c_void_p), ("d_done_acc", C.c_void_p),

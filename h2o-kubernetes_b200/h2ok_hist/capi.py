@@ -50,6 +50,9 @@ SIGNATURES = {
     "h2ok_hist_comm_unique_id": [vp],
     "h2ok_hist_comm_init": [vp, vp, i32, i32],
     "h2ok_hist_loop_create": [vp, pP, vp],
+    "h2ok_hist_loop_create_forest": [vp, pP, vp, i32],
+    "h2ok_hist_loop_begin_forest_dev": [vp, vp, i64],
+    "h2ok_hist_loop_forest_quants": [vp, vp],
     "h2ok_hist_loop_destroy": [vp],
     "h2ok_hist_loop_root_descs": [vp, vp],
     "h2ok_hist_loop_set_reduce": [vp, i32],

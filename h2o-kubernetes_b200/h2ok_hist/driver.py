@@ -340,13 +340,20 @@ class TreeLoop:
 
     shard: an EngineShard whose data is loaded.  Same results as LevelDriver, bit for bit."""
 
-    def __init__(self, shard, params, is_int=None, reduce_mode=abi.REDUCE_SCATTER, checksum=False, time_phases=False):
+    def __init__(self, shard, params, is_int=None, reduce_mode=abi.REDUCE_SCATTER, checksum=False, time_phases=False,
+                 forest=1):
+        """forest = K > 1: K trees on the same rows built in lockstep (the K class trees of a multinomial iteration) —
+        sparse shards only; start them with begin_forest(ys)."""
         self.shard, self.params, self.lib = shard, params, shard.lib
+        self.forest = int(forest)
         if is_int is None and getattr(shard, "u8", False):
             is_int = np.ones(shard.cols, np.int32)  # the cells of a u8 shard are integer codes
         self.is_int = None if is_int is None else np.ascontiguousarray(is_int, np.int32)
         self.max_bins = max(params.nbins, params.nbins_top_level)
-        self.lib.call("h2ok_hist_loop_create", shard.ctx, C.byref(params), abi.ptr(self.is_int))
+        if self.forest > 1:
+            self.lib.call("h2ok_hist_loop_create_forest", shard.ctx, C.byref(params), abi.ptr(self.is_int), self.forest)
+        else:
+            self.lib.call("h2ok_hist_loop_create", shard.ctx, C.byref(params), abi.ptr(self.is_int))
         self.lib.call("h2ok_hist_loop_set_reduce", shard.ctx, reduce_mode)
         self.lib.call("h2ok_hist_loop_set_options", shard.ctx, 1 if checksum else 0, 1 if time_phases else 0)
         self.n_nodes = 0
@@ -382,6 +389,19 @@ class TreeLoop:
         self.shard.launches += 5  # absmax, quantise, root mean, begin, + the library's own memsets do not count
         self.n_nodes, self.depth = 1, 0
 
+    def begin_forest(self, ys):
+        """ys: device tensor [forest, ld] — the trees' target vectors in original row order."""
+        assert ys.shape[0] == self.forest and ys.stride(1) == 1
+        self.lib.call("h2ok_hist_loop_begin_forest_dev", self.shard.ctx, _ptr(ys), ys.stride(0))
+        self.shard.launches += 5 * self.forest + 1
+        self.n_nodes, self.depth = self.forest, 0
+
+    def forest_quants(self):
+        """The fixed-point scales of the current forest's trees (list of abi.Quant)."""
+        out = (abi.Quant * self.forest)()
+        self.lib.call("h2ok_hist_loop_forest_quants", self.shard.ctx, out)
+        return list(out)
+
     def begin_tree_host(self, y_host, w_host=None):
         """y_host / w_host: host tensors or numpy arrays (fp32); the library copies them in."""
         p = lambda a: None if a is None else C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
@@ -395,7 +415,7 @@ class TreeLoop:
                       C.byref(nch))
         last = self.depth + 1 >= self.params.max_depth
         # init_enc, histogram pass, split points, bestCol, [children: descs + compact], route, scan, [scatter]
-        self.shard.launches += 6 if last else 9
+        self.shard.launches += (6 if last else 9) + 2 * (self.forest - 1)  # a forest: totals + routing per class tree
         self.depth += 1
         self.n_nodes = nch.value
         return done.value, nch.value

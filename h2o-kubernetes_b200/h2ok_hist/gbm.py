@@ -103,8 +103,45 @@ class GBMTrainer:
         sh.launches += 2
         return dict(levels=levels, gamma=gamma)
 
+    def _step_multinomial_forest(self):
+        """The K class trees of the iteration as ONE forest (h2ok_hist_loop_create_forest): every level streams the
+        sparse column lists once for all K trees.  Same trees, leaf values and scores as _step_multinomial."""
+        sh, rows, K = self.shard, self.rows, self.K
+        den_scale = 2.0**28
+        self.lib.call("h2ok_hist_gbm_residual_multi_dev", sh.ctx, K, _ptr(self.label), _ptr(self.f), self.ld, _ptr(sh.w),
+                      rows, den_scale, _ptr(self.res), _ptr(self.denq))
+        sh.launches += 1
+        self.drv.begin_forest(self.res)
+        while self.drv.n_nodes_left() > 0:
+            self.drv.level()
+        v = self.drv.view()
+        quants = self.drv.forest_quants()
+        n_codes = 3 * v.gid_base
+        pad = (rows + 3) // 4 * 4
+        out = []
+        nums = torch.zeros((K, n_codes), dtype=torch.int64, device=sh.device)
+        dens = torch.zeros((K, n_codes), dtype=torch.int64, device=sh.device)
+        for k in range(K):
+            self.lib.call("h2ok_hist_gbm_gamma_pass_dev", sh.ctx, C.c_void_p(v.d_leaf + 4 * k * rows),
+                          C.c_void_p(v.d_wyq + 4 * k * pad), _ptr(self.denq[k]), rows, n_codes, _ptr(nums[k]), _ptr(dens[k]))
+        if _world() > 1:
+            dist_.all_reduce(nums)
+            dist_.all_reduce(dens)
+        nums_h, dens_h = nums.cpu().numpy(), dens.cpu().numpy()
+        for k in range(K):
+            gamma = (K - 1.0) / K * leaf_gamma(nums_h[k], dens_h[k], quants[k].scale_wy, den_scale)
+            dg = torch.from_numpy(gamma).to(sh.device)
+            self.lib.call("h2ok_hist_gbm_add_gamma_dev", sh.ctx, C.c_void_p(v.d_leaf + 4 * k * rows), rows, _ptr(dg), n_codes,
+                          self.lr, _ptr(self.f[k]))
+            sh.launches += 2
+            self.trees.append(dict(levels=[], gamma=gamma, cls=k))
+            out.append(gamma)
+        return out
+
     def _step_multinomial(self):
         """K trees on the softmax residuals of the current scores (all residuals are taken before the first tree)."""
+        if getattr(self.drv, "forest", 1) == self.K and self.K > 1:
+            return self._step_multinomial_forest()
         sh, rows, K = self.shard, self.rows, self.K
         den_scale = 2.0**28
         self.lib.call("h2ok_hist_gbm_residual_multi_dev", sh.ctx, K, _ptr(self.label), _ptr(self.f), self.ld, _ptr(sh.w),

@@ -146,7 +146,10 @@ typedef struct h2ok_loop_view {
   int32_t depth, n_nodes, gid_base; /* the level the NEXT loop_level call will run; n_nodes == 0: tree finished */
   int32_t max_nodes, max_bins, cols, rank, n_ranks, reduce_mode;
   int32_t done_depth;               /* -1: no level has run since loop_begin_tree */
-  int32_t done_nodes, done_children, done_gid_base, pad;
+  int32_t done_nodes, done_children, done_gid_base;
+  int32_t n_trees; /* class trees built in lockstep (h2ok_hist_loop_create_forest); 1: one tree.  With n_trees = K > 1:
+                    * d_leaf is [K][rows], d_wyq / d_wyyq are [K][rows rounded up to 4], the node list of a level is flat
+                    * (class tree 0's nodes, then tree 1's ...) and leaf codes use the flat tree-wide node ids */
   int64_t done_pair0, done_pair1;   /* (node, column) pairs whose reduced sums this rank holds in d_done_acc */
   h2ok_quant quant;                 /* fixed-point scales of the current tree's targets */
   const h2ok_col_desc* d_descs;     /* [n_nodes][cols] descriptors of the next level */
@@ -352,6 +355,18 @@ int32_t h2ok_hist_comm_init(h2ok_ctx* ctx, const void* id /*[H2OK_COMM_ID_BYTES]
 /* Root descriptors from the column ranges of all ranks (DHistogram.initialHist), level buffers for
  * min(2^(max_depth-1), H2OK_MAX_LEVEL_NODES) nodes.  Collective when n_ranks > 1.  is_int: [cols] or NULL. */
 int32_t h2ok_hist_loop_create(h2ok_ctx* ctx, const h2ok_params* params, const int32_t* is_int);
+/* A forest: n_trees (<= 16) trees on the same rows built in lockstep — the K class trees of one multinomial iteration
+ * (GBM.buildNextKTrees builds K trees per iteration; BASELINE config 4 has K = 10).  H2OK_TREE_SPARSE shards only: the
+ * column lists are streamed ONCE per level for all the trees (every nonzero cell serves the K trees, whose row records
+ * sit side by side), which is SURVEY.md §8(d)'s "fused level".  Every tree has its own targets and fixed-point scales
+ * and equals the tree loop_begin_tree_* would have built alone, bit for bit; the level's node list is flat (tree 0's
+ * nodes, then tree 1's, ...), n_trees * 2^(max_depth-1) must not exceed H2OK_MAX_LEVEL_NODES.  h2ok_level_out.hist is
+ * not delivered for a forest. */
+int32_t h2ok_hist_loop_create_forest(h2ok_ctx* ctx, const h2ok_params* params, const int32_t* is_int, int32_t n_trees);
+/* New forest: d_y = the n_trees target vectors, [n_trees][ld] (device; read by work enqueued on the context's stream). */
+int32_t h2ok_hist_loop_begin_forest_dev(h2ok_ctx* ctx, const float* d_y, int64_t ld);
+/* The fixed-point scales of the current forest's trees (out: [n_trees], host); blocks until they have arrived. */
+int32_t h2ok_hist_loop_forest_quants(h2ok_ctx* ctx, h2ok_quant* out);
 int32_t h2ok_hist_loop_destroy(h2ok_ctx* ctx);
 int32_t h2ok_hist_loop_root_descs(h2ok_ctx* ctx, h2ok_col_desc* descs_out /*[cols], host*/);
 int32_t h2ok_hist_loop_set_reduce(h2ok_ctx* ctx, int32_t mode /*H2OK_REDUCE_**/);

@@ -28,6 +28,7 @@ ap.add_argument("--iters", type=int, default=3)
 ap.add_argument("--depth", type=int, default=6)
 ap.add_argument("--bins", type=int, default=64)
 ap.add_argument("--storage", default="sparse", choices=["sparse", "dense"])
+ap.add_argument("--forest", action="store_true", help="build the K class trees of an iteration in lockstep (sparse storage)")
 a = ap.parse_args()
 world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -51,7 +52,7 @@ def column(c):
 score = torch.stack([column(c) for c in range(a.classes)])
 label = score.argmax(dim=0).float()
 del score
-drv = TreeLoop(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth))
+drv = TreeLoop(shard, abi.Params.make(nbins=a.bins, max_depth=a.depth), forest=a.classes if a.forest else 1)
 tr = GBMTrainer(drv, label, abi.DIST_MULTINOMIAL, learn_rate=0.3, n_classes=a.classes, keep_levels=False)
 tr.init_f()
 ll0 = tr.loss()
@@ -69,7 +70,7 @@ levels = len(tr.trees) * a.depth  # upper bound: a class tree may stop early
 if rank == 0:
     print(json.dumps({"workload": f"GBM multinomial {a.classes} classes, {a.iters} iterations ({len(tr.trees)} trees) depth {a.depth}, "
                                   f"{a.rows} x {a.cols}, {a.bins} bins",
-                      "n_gpus": world, "path": "in-library loop, %s storage" % a.storage, "seconds": sec, "s_per_iteration": sec / a.iters,
+                      "n_gpus": world, "path": "in-library loop, %s storage%s" % (a.storage, ", class trees as one forest" if a.forest else ""), "seconds": sec, "s_per_iteration": sec / a.iters,
                       "ms_per_tree": 1e3 * sec / len(tr.trees), "ms_per_level": 1e3 * sec / levels,
                       "cells_per_s_per_level": a.rows * a.cols * levels / sec,
                       "logloss_start": ll0, "logloss_end": ll}))

@@ -361,6 +361,101 @@ def test_multinomial_k10_on_the_loop_tracks_oracle(eshard, sshard, oracle, spars
     assert len(tr.trees) == 2 * K
 
 
+def test_forest_equals_the_trees_built_one_by_one(sshard, oracle):
+    """h2ok_hist_loop_create_forest: K trees in lockstep on the sparse storage are, tree by tree, the trees the loop
+    builds alone — same splits at every node, same leaf for every row (up to the numbering of the nodes, which is flat
+    over the forest) — and hence the same result checksum parts per tree."""
+    from h2ok_hist.driver import TreeLoop
+
+    rows, cols, K = 40001, 130, 5
+    X, y, _ = oracle.synth(abi.SHAPE_SPARSE, 77, 0, rows, cols, na_permille=5)
+    ys = np.stack([np.roll(y[:rows], 17 * k) * (1.0 + 0.25 * k) + 0.1 * k * X[k % cols, :rows] for k in range(K)]).astype(np.float32)
+    params = abi.Params.make(nbins=32, max_depth=5, min_rows=5)
+    sshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(ys[0].copy()))
+    ld = (rows + 63) // 64 * 64
+    dys = torch.zeros((K, ld), dtype=torch.float32, device="cuda")
+    dys[:, :rows] = torch.from_numpy(ys)
+    alone = []
+    loop = TreeLoop(sshard, params)
+    for k in range(K):  # the trees one by one: per level the split records, at the end every row's leaf structure
+        loop.begin_tree(y=dys[k])
+        levels = []
+        while loop.n_nodes_left() > 0:
+            loop.level()
+            lv = loop.done_level()
+            levels.append((lv["splits"].copy(), lv["child_ids"].copy()))
+        alone.append((levels, sshard.leaf[:rows].cpu().numpy().copy()))
+    forest = TreeLoop(sshard, params, forest=K)
+    forest.begin_forest(dys)
+    flevels = []
+    while forest.n_nodes_left() > 0:
+        forest.level()
+        lv = forest.done_level()
+        flevels.append((lv["splits"].copy(), lv["child_ids"].copy(), lv["n"]))
+    v = forest.view()
+    assert v.n_trees == K
+    leaf_all = forest._dev_array(v.d_leaf, 4 * K * rows).view(np.int32).reshape(K, rows)
+    # walk the forest's flat levels class by class: the flat node list of a level is tree 0's nodes, then tree 1's, ...
+    counts = [1] * K
+    for d, (fs, fids, n) in enumerate(flevels):
+        assert n == sum(counts)
+        off, nxt = 0, []
+        for k in range(K):
+            if counts[k] == 0:
+                nxt.append(0)
+                continue
+            s_alone, ids_alone = alone[k][0][d]
+            mine = fs[off:off + counts[k]]
+            for name in ("col", "bin", "na_dir", "splat", "se_before", "se_left", "se_right", "n_left", "n_right",
+                         "pred_left", "pred_right"):
+                assert np.array_equal(mine[name], s_alone[name]), (d, k, name)
+            # same children exist (ids differ by the forest's flat numbering)
+            assert np.array_equal(fids[2 * off:2 * (off + counts[k])] >= 0, ids_alone >= 0)
+            nxt.append(int((ids_alone >= 0).sum()))
+            off += counts[k]
+        counts = nxt
+    # leaves: the partition of the rows must be the same (leaf codes are numbered differently)
+    for k in range(K):
+        a, b = alone[k][1], leaf_all[k]
+        assert (a >= 0).all() and (b >= 0).all()
+        pairs = np.unique(np.stack([a, b]), axis=1)
+        assert len(np.unique(pairs[0])) == pairs.shape[1] == len(np.unique(pairs[1]))  # a bijection between the codes
+
+
+def test_multinomial_k10_as_a_forest_tracks_oracle(sshard, oracle):
+    """The K = 10 trainer on the forest path: first iteration's scores bit-identical to the oracle's, logloss after."""
+    from h2ok_hist.driver import TreeLoop
+    from h2ok_hist.gbm import GBMTrainer
+
+    rows, cols, K = 30000, 70, 10
+    X, y, _ = oracle.synth(abi.SHAPE_SPARSE, 5, 0, rows, cols)
+    score = X[:K, :rows].T @ np.linspace(1.0, 2.0, K * K).reshape(K, K).astype(np.float32) + y[:rows, None] * 0.2
+    label = score.argmax(axis=1).astype(np.float32)
+    params = abi.Params.make(nbins=32, max_depth=4, min_rows=5)
+    sshard.set_data_tensors(torch.from_numpy(X[:, :rows].copy()), torch.from_numpy(label))
+    loop = TreeLoop(sshard, params, forest=K)
+    tr = GBMTrainer(loop, torch.from_numpy(label).cuda(), abi.DIST_MULTINOMIAL, learn_rate=0.3, n_classes=K)
+    tr.init_f()
+    ref = oracle_lib.OracleGBM(oracle, X, rows, label, None, params, abi.DIST_MULTINOMIAL, 0.3, n_classes=K)
+
+    def logloss(f):
+        z = f.astype(np.float64)
+        z = z - z.max(axis=0, keepdims=True)
+        logp = z - np.log(np.exp(z).sum(axis=0, keepdims=True))
+        return float(-logp[label.astype(np.int64), np.arange(rows)].mean())
+
+    trace = [tr.loss()]
+    for it in range(2):
+        tr.step()
+        ref.step()
+        torch.cuda.synchronize()
+        if it == 0:
+            assert np.array_equal(tr.f[:, :rows].cpu().numpy(), ref.f)
+        trace.append(tr.loss())
+        assert trace[-1] == pytest.approx(logloss(ref.f), rel=1e-6)
+    assert all(b < a for a, b in zip(trace, trace[1:]))
+
+
 def test_gaussian_on_the_loop_is_bit_exact(eshard, oracle):
     from h2ok_hist.driver import TreeLoop
     from h2ok_hist.gbm import GBMTrainer
