@@ -764,19 +764,19 @@ __global__ void __launch_bounds__(512) eng_node_totals_kernel(int64_t rows, cons
   }
 }
 
-// What the pass needs of one node for one column, 16 bytes = one shared-memory load per cell (the 32-byte entry it
-// replaces took two, 8 of the pass's ~30 LSU wavefronts per warp and cell).  The node minimum is a float whenever the
-// descriptor came from this library (column ranges, min2 / maxIn and split points are all floats); a caller's
-// descriptor with a minimum that is not sets kCscWide and the exact double is read from a side array.  The centring
-// offsets are kept to their top 10 bits: any offset is exact as long as the flush adds back the same one.
+// What the pass needs of one node for one column: two 16-byte shared-memory loads per cell.  The node minimum is a
+// float whenever the descriptor came from this library (column ranges, min2 / maxIn and split points are all floats);
+// a caller's descriptor with a minimum that is not sets kCscWide and the exact double is read from a side array.
 struct CscNode {
   double st;
   float mn;
-  unsigned pk;  // nbin [10:0] (0: (node, column) not tracked) | kCscWide | m1 >> 17 [21:12] (signed) | m2 >> 17 [31:22]
+  unsigned nbw;  // nbin (0: (node, column) not tracked) | kCscWide
 };
-constexpr unsigned kCscWide = 1u << 11;
-__device__ __forceinline__ int csc_m1(unsigned pk) { return (int)((int)(pk << 10) >> 22) * (1 << 17); }
-__device__ __forceinline__ int csc_m2(unsigned pk) { return (int)(pk >> 22) << 17; }
+struct CscNodeB {
+  int m1, m2;           // centring offsets of the node
+  unsigned rmin, rmax;  // observed range so far (order-preserving codes)
+};
+constexpr unsigned kCscWide = 1u << 31;
 
 struct CscHistArgs {
   const uint2* const* cptr;  // [cols] nonzeros of every column
@@ -795,50 +795,58 @@ struct CscHistArgs {
   int32_t* err;
 };
 
-// 512 threads, four nonzeros per thread in flight: the pass is a chain of dependent loads per cell (list entry, then the
-// row's node, then its targets), so throughput comes from independent chains — one cell per thread at a time ran at
-// 18.6 ms per level on config 4, latency-bound.  Two CTAs share an SM whenever their histograms fit.
+// 512 threads: the pass is a chain of dependent loads per cell (list entry, then the row's record), so throughput
+// comes from independent chains in flight — one cell per thread at a time ran at 18.6 ms per level on config 4,
+// latency-bound; four at a time 8.1.  Two CTAs share an SM whenever their histograms fit.
 constexpr int kCscThreads = 512;
 
 // The three parts the two passes below share: (1) node tables and zeroed histogram copies in shared memory, (2) one cell
 // of one node added in, (3) the copies added up and flushed.
 struct CscSmem {
   CscNode* tab;
+  CscNodeB* tab2;
   double* mn_wide;
-  unsigned *rmin, *rmax, *h;
+  unsigned* h;
 };
-constexpr size_t kCscNodeBytes = sizeof(CscNode) + 8 + 8;  // table entry, exact minimum, range slots
+constexpr size_t kCscNodeBytes = sizeof(CscNode) + sizeof(CscNodeB) + 8;  // two table entries, the exact minimum
 
 __device__ __forceinline__ CscSmem csc_setup(const CscHistArgs& a, unsigned char* smem_raw, int col, int tid) {
   const int n = a.n_nodes, nbs = a.nbs, nbase = a.node_base;
   CscSmem m;
   m.tab = reinterpret_cast<CscNode*>(smem_raw);
-  m.mn_wide = reinterpret_cast<double*>(m.tab + n);
-  m.rmin = reinterpret_cast<unsigned*>(m.mn_wide + n);
-  m.rmax = m.rmin + n;
-  m.h = m.rmax + n;  // [copy][node][bin][channel]
+  m.tab2 = reinterpret_cast<CscNodeB*>(m.tab + n);
+  m.mn_wide = reinterpret_cast<double*>(m.tab2 + n);
+  m.h = reinterpret_cast<unsigned*>(m.mn_wide + n);  // [copy][node][bin][channel]
   for (int g = tid; g < n; g += kCscThreads) {
     const h2ok_col_desc d = a.descs[(int64_t)(nbase + g) * a.cols + col];
     CscNode t;
     t.mn = (float)d.min;
     t.st = d.step;
-    unsigned nb = (unsigned)d.nbin;
-    if (d.nbin >= nbs || d.nbin > 1024) {
+    unsigned nb = d.nbin > 0 ? (unsigned)d.nbin : 0u;
+    if (d.nbin >= nbs) {
       if (blockIdx.x == 0) atomicAdd(a.err, 1);
       nb = 0;
     }
-    if (d.nbin < 0) nb = 0;
-    const int m1 = a.mnode[2 * (nbase + g)], m2 = a.mnode[2 * (nbase + g) + 1];
-    t.pk = nb | ((double)t.mn != d.min ? kCscWide : 0u) | (((unsigned)(m1 >> 17) & 0x3FFu) << 12) | (((unsigned)m2 >> 17) << 22);
+    t.nbw = nb | ((double)t.mn != d.min ? kCscWide : 0u);
     m.tab[g] = t;
+    CscNodeB t2;
+    t2.m1 = a.mnode[2 * (nbase + g)];
+    t2.m2 = a.mnode[2 * (nbase + g) + 1];
+    t2.rmin = kEncPosInf;
+    t2.rmax = kEncNegInf;
+    m.tab2[g] = t2;
     m.mn_wide[g] = d.min;
-    m.rmin[g] = kEncPosInf;
-    m.rmax[g] = kEncNegInf;
   }
   const int words = a.copies * n * nbs * 3;
   for (int i = tid; i < words; i += kCscThreads) m.h[i] = (i % 3 == 0) ? 0u : kWyBias;
   __syncthreads();
   return m;
+}
+
+// cold: the wrap of a shared word, with the launch arguments read here rather than kept ready in the hot loop
+__device__ __noinline__ void csc_carry(const CscHistArgs& a, int nd, int col, int b, unsigned f1, unsigned f2, int v1, int v2) {
+  eng_carry(a.acc, a.descs, a.node_base + nd, a.cols, col, a.nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
+            (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
 }
 
 // (rx, ry): the row's packed record for one tree; a row in a leaf (node 0x3FF) and the all-ones record of a list entry
@@ -848,22 +856,26 @@ __device__ __forceinline__ void csc_cell(const CscHistArgs& a, const CscSmem& m,
   const unsigned nd = rec_node(rx, ry) - (unsigned)a.node_base;
   if (nd >= (unsigned)a.n_nodes) return;
   const CscNode t = m.tab[nd];
-  const int nb = (int)(t.pk & 0x7FFu);
+  const CscNodeB t2 = m.tab2[nd];
+  const int nb = (int)(t.nbw & 0x7FFFFFFFu);
   if (nb == 0) return;
-  const int v1 = ((int)rx >> 5) - csc_m1(t.pk), v2 = (int)(ry >> 5) - csc_m2(t.pk);  // wyq signed, wyyq unsigned
-  const double mn = (t.pk & kCscWide) ? m.mn_wide[nd] : (double)t.mn;
+  const int v1 = ((int)rx >> 5) - t2.m1, v2 = (int)(ry >> 5) - t2.m2;  // wyq signed, wyyq unsigned
+  const double mn = (t.nbw & kCscWide) ? m.mn_wide[nd] : (double)t.mn;
   const int b = bin_fast(x, mn, t.st, nb);
   const unsigned addr = hbase + (unsigned)(((int)nd * a.nbs + b) * 12);
   sh_inc(addr);
   const unsigned o1 = sh_add(addr + 4u, (unsigned)v1), o2 = sh_add(addr + 8u, (unsigned)v2);
   const unsigned f1 = wrap_bit(o1, v1), f2 = wrap_bit(o2, v2);
-  if ((f1 | f2) >> 31)
-    eng_carry(a.acc, a.descs, a.node_base + (int)nd, a.cols, col, a.nb1, b, 0, (f1 >> 31) ? (v1 < 0 ? -1 : 1) : 0,
-              (f2 >> 31) ? (v2 < 0 ? -1 : 1) : 0);
-  if (x == x) {
-    const unsigned ex = enc_f32_bits(__float_as_uint(x));
-    if (ex < m.rmin[nd]) atomicMin(&m.rmin[nd], ex);
-    if (ex > m.rmax[nd]) atomicMax(&m.rmax[nd], ex);
+  if ((f1 | f2) >> 31) csc_carry(a, (int)nd, col, b, f1, f2, v1, v2);
+  // enc_f32_bits as one shift and one xor; a NaN's code lies outside [enc(-inf), enc(+inf)], so it is filtered by the
+  // same comparison that says "inside the range seen so far" only when that range is not empty: test it explicitly
+  const unsigned xb = __float_as_uint(x);
+  const unsigned ex = xb ^ ((unsigned)((int)xb >> 31) | 0x80000000u);
+  if ((ex < t2.rmin) | (ex > t2.rmax)) {
+    if (x == x) {
+      if (ex < t2.rmin) atomicMin(&m.tab2[nd].rmin, ex);
+      if (ex > t2.rmax) atomicMax(&m.tab2[nd].rmax, ex);
+    }
   }
 }
 
@@ -883,47 +895,74 @@ __device__ __forceinline__ void csc_flush(const CscHistArgs& a, const CscSmem& m
     }
     if (nc | (unsigned long long)n1 | (unsigned long long)n2) {
       unsigned long long* gp = reinterpret_cast<unsigned long long*>(a.acc) + (((int64_t)(nbase + g) * a.cols + col) * a.nb1 + b) * 3;
-      const long long s1 = n1 + (long long)nc * csc_m1(m.tab[g].pk), s2 = n2 + (long long)nc * csc_m2(m.tab[g].pk);
+      const long long s1 = n1 + (long long)nc * m.tab2[g].m1, s2 = n2 + (long long)nc * m.tab2[g].m2;
       if (nc) atomicAdd(gp, nc);
       if (s1) atomicAdd(gp + 1, (unsigned long long)s1);
       if (s2) atomicAdd(gp + 2, (unsigned long long)s2);
     }
   }
   for (int g = tid; g < n; g += kCscThreads) {
-    if (m.rmin[g] != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)(nbase + g) * a.cols + col], m.rmin[g]);
-    if (m.rmax[g] != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)(nbase + g) * a.cols + col], m.rmax[g]);
+    const CscNodeB t2 = m.tab2[g];
+    if (t2.rmin != kEncPosInf) atomicMin(&a.min2_enc[(int64_t)(nbase + g) * a.cols + col], t2.rmin);
+    if (t2.rmax != kEncNegInf) atomicMax(&a.maxin_enc[(int64_t)(nbase + g) * a.cols + col], t2.rmax);
   }
 }
 
-// One tree: U list entries per thread in flight, one 8-byte record gather each.
+// One tree.  U list entries per thread and batch, one 8-byte record gather each, and the loads of the next two batches
+// in flight while a batch is added in: a batch's list entries are fetched two iterations ahead and its row records one
+// iteration ahead, so neither latency sits on the chain.  Config 4, ms per level: four entries per thread without the
+// look-ahead 7.7, U = 1 / 2 / 4 with it 7.6 / 6.9 / 7.0.
 template <int U>
-__global__ void __launch_bounds__(kCscThreads, U <= 4 ? 2 : 1) eng_hist_csc_kernel(const __grid_constant__ CscHistArgs a) {
-  constexpr int THREADS = kCscThreads;
+__global__ void __launch_bounds__(kCscThreads, 2) eng_hist_csc_kernel(const __grid_constant__ CscHistArgs a) {
+  constexpr int THREADS = kCscThreads, STRIDE = THREADS * U;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31;
   const int col = blockIdx.y;
   const int64_t len = a.clen[col];
   const int64_t i0 = len * (int64_t)blockIdx.x / gridDim.x, i1 = len * (int64_t)(blockIdx.x + 1) / gridDim.x;
   if (i0 >= i1) return;
+  // (a list has fewer than 2^31 entries: 32-bit positions inside the CTA's stretch keep the loop's bookkeeping short —
+  // the pass is bound by issue slots, 79 % busy in profiles/r02_hist_csc_ncu_full.csv)
+  const int cnt = (int)(i1 - i0);
+  const uint2* __restrict__ nz = a.cptr[col] + i0;
+  const uint2* __restrict__ rec = a.rec;
+  const uint2 ones = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+  uint2 ea[U], eb[U], ra[U], rb[U];  // list entries of batches t + 1 / t + 2 and records of batches t / t + 1, by turns
+  float x0[U];
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    const int i = tid + u * THREADS;
+    const uint2 e = i < cnt ? __ldg(nz + i) : make_uint2(0u, 0u);
+    x0[u] = __uint_as_float(e.y);
+    ra[u] = i < cnt ? __ldg(rec + e.x) : ones;
+    ea[u] = i + STRIDE < cnt ? __ldg(nz + i + STRIDE) : make_uint2(0u, 0u);
+  }
   const CscSmem m = csc_setup(a, smem_raw, col, tid);
   const unsigned hbase = (unsigned)__cvta_generic_to_shared(m.h) + (unsigned)((lane & (a.copies - 1)) * a.n_nodes * a.nbs) * 12u;
-  const uint2* __restrict__ nz = a.cptr[col];
-  const uint2* __restrict__ rec = a.rec;
-  for (int64_t ib = i0 + tid; ib < i1; ib += (int64_t)THREADS * U) {
-    uint2 e[U], rc[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int64_t i = ib + (int64_t)u * THREADS;
-      e[u] = i < i1 ? __ldg(nz + i) : make_uint2(0u, 0u);
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int64_t i = ib + (int64_t)u * THREADS;
-      rc[u] = i < i1 ? __ldg(rec + e[u].x) : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) csc_cell(a, m, hbase, col, rc[u].x, rc[u].y, __uint_as_float(e[u].y));
+  // one batch: gather the next batch's records, fetch the entries of the one after, add this batch in.  Written twice
+  // with the buffers swapped so that nothing but the cell values moves between registers.
+#define H2OK_CSC_STEP(EA, EB, RA, RB, IB)                                                            \
+  {                                                                                                  \
+    _Pragma("unroll") for (int u = 0; u < U; u++) {                                                  \
+      const int i = (IB) + u * THREADS;                                                              \
+      RB[u] = i + STRIDE < cnt ? __ldg(rec + EA[u].x) : ones;                                        \
+      EB[u] = i + 2 * STRIDE < cnt ? __ldg(nz + i + 2 * STRIDE) : make_uint2(0u, 0u);                \
+    }                                                                                                \
+    _Pragma("unroll") for (int u = 0; u < U; u++) csc_cell(a, m, hbase, col, RA[u].x, RA[u].y, x0[u]); \
+    _Pragma("unroll") for (int u = 0; u < U; u++) x0[u] = __uint_as_float(EA[u].y);                  \
   }
+  // (a bit mask of the rows still in the tree, consulted before the record gather once most rows have left: slower,
+  // 7.4 ms against 6.0 on config 4's levels with a tenth of the rows live — the gather is not what those levels wait for)
+  // (two more variants for levels where most rows have left the tree, both measured on config 4's levels with a tenth
+  // of the rows live: live cells collected in a per-warp ring and added in 32 at a time, all lanes busy — 6.0 ms against
+  // 6.2; the mask and the ring say the same thing: those levels wait neither for the record gather nor for the issue
+  // slots of the per-cell code; an L2 prefetch of the list 2K / 8K / 32K entries ahead made every level slower, 7.7-7.9 ms
+  // per level against 7.1, so it is not the depth of the list stream either)
+  for (int ib = tid; ib < cnt; ib += 2 * STRIDE) {
+    H2OK_CSC_STEP(ea, eb, ra, rb, ib)
+    H2OK_CSC_STEP(eb, ea, rb, ra, ib + STRIDE)  // (past the end: every record is the all-ones one, nothing is added)
+  }
+#undef H2OK_CSC_STEP
   csc_flush(a, m, col, tid);
 }
 
@@ -1696,7 +1735,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     int dev = 0;
     cudaGetDevice(&dev);
     if (!attr_done[dev & 63].load(std::memory_order_acquire)) {
-      cudaError_t ea = cudaFuncSetAttribute(eng_hist_csc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
+      cudaError_t ea = cudaFuncSetAttribute(eng_hist_csc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
       if (ea == cudaSuccess) ea = cudaFuncSetAttribute(eng_hist_csc_forest_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemCap);
       if (ea != cudaSuccess) return ea;
       attr_done[dev & 63].store(true, std::memory_order_release);
@@ -1716,6 +1755,7 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
     a.maxin_enc = maxin_enc;
     a.err = e.err;
     // stretches of a column's nonzero list per CTA: about eight CTAs per SM over the whole grid
+    // (20 / 40 / 80 per SM: 7.2 / 7.1 / 7.4 ms per level on config 4 against 7.2)
     int chunks = (8 * e.sms + e.cols - 1) / e.cols;
     chunks = chunks < 1 ? 1 : chunks;
     a.chunks = chunks;
@@ -1730,9 +1770,8 @@ cudaError_t engine_build_level(Engine& e, int n_nodes, const h2ok_col_desc* desc
       a.copies = 1;
       while (a.copies < 8 && (size_t)a.n_nodes * (kCscNodeBytes + (size_t)nbs * 12 * (a.copies * 2)) <= cap) a.copies *= 2;
       const size_t smem = (size_t)a.n_nodes * (kCscNodeBytes + (size_t)nbs * 12 * a.copies);
-      // four cells per thread in flight (two: 9.2 ms per level on config 4, four: 8.1, eight at one CTA per SM: 15.7)
       const dim3 grid((unsigned)chunks, (unsigned)e.cols);
-      if (e.K == 1) eng_hist_csc_kernel<4><<<grid, kCscThreads, smem, s>>>(a);
+      if (e.K == 1) eng_hist_csc_kernel<2><<<grid, kCscThreads, smem, s>>>(a);
       else eng_hist_csc_forest_kernel<4><<<grid, kCscThreads, smem, s>>>(a);
     }
     const int64_t pairs = (int64_t)n_nodes * e.cols;
