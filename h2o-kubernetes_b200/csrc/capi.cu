@@ -61,7 +61,7 @@ static double pow2_scale(double absmax, int qbits) {
 extern "C" {
 
 const char* h2ok_last_error(void) { return g_err; }
-int32_t h2ok_hist_abi_version(void) { return 1; }
+int32_t h2ok_hist_abi_version(void) { return 2; }  // 2: h2ok_split carries equal + cat_bits
 
 int32_t h2ok_hist_create(int32_t device, h2ok_ctx** out) {
   REQUIRE(out != nullptr, "null out pointer");
@@ -606,7 +606,9 @@ int32_t h2ok_hist_root_descs_from_ranges(const float* col_min, const float* col_
   for (int j = 0; j < cols; j++) {
     float lo = col_min[j] + 0.0f, hi = col_max[j] + 0.0f;
     int ii = is_int ? is_int[j] : 0;
-    if (ii > 1) return fail(H2OK_ERR_UNSUPPORTED, "%s", "categorical columns (is_int == 2) are not supported");
+    if (ii < 0 || ii > 2) return fail(H2OK_ERR_ARG, "%s", "is_int: 0 real, 1 integer, 2 categorical");
+    if (ii == 2 && lo <= hi && (lo < 0.0f || hi >= (float)(32 * H2OK_CAT_WORDS)))
+      return fail(H2OK_ERR_UNSUPPORTED, "%s", "categorical columns hold the codes 0 .. 1023 (a split's bit set covers those)");
     h2ok_col_desc* o = &descs_out[j];
     memset(o, 0, sizeof(*o));
     o->is_int = ii;

@@ -118,6 +118,14 @@ __device__ __forceinline__ uint2 rec_pack(int wyq, int wyyq, unsigned node) {
   return make_uint2(((unsigned)wyq << 5) | (node & 31u), ((unsigned)wyyq << 5) | (node >> 5));
 }
 
+// a6 for a categorical split: the row's category code c = (int)x goes right when bit c is set; a code outside the set's
+// range follows the NAs (a category no training row had)
+__device__ __forceinline__ int cat_goes_right(const uint32_t* __restrict__ bits, float x, int na) {
+  const int c = (int)x;
+  if (c < 0 || c >= 32 * H2OK_CAT_WORDS) return na == H2OK_NA_LEFT ? 0 : 1;
+  return (int)((bits[c >> 5] >> (c & 31)) & 1u);
+}
+
 // wY words start mid-range so that sums hovering around zero never wrap
 constexpr unsigned kWyBias = 0x80000000u;
 

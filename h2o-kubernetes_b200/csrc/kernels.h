@@ -60,7 +60,7 @@ cudaError_t launch_finalize(const int64_t* acc, const uint32_t* mn, const uint32
 struct PairCand {
   double key;  // se_left + se_right
   double seL, seR, nL, nR, pL, pR, se_before;
-  int32_t bin, na, found;
+  int32_t bin, na, found;  // found: 0 none, 1 ranged split, 2 categorical split (bins sorted by mean response)
   float splat;
 };
 // pairs [pair0, pair1) of the flat [n_nodes * cols] list, from the fp64 histogram (hist != NULL) or straight from the
@@ -70,8 +70,16 @@ struct PairCand {
 cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
                                 const h2ok_col_desc* descs,
                                 int64_t pair0, int64_t pair1, int nb1, double min_rows, double msi, PairCand* cand,
-                                cudaStream_t s, const unsigned char* node_class = nullptr, int cols = 0);
+                                cudaStream_t s, const unsigned char* node_class = nullptr, int cols = 0,
+                                bool categorical = false);
 cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_split* splits, cudaStream_t s);
+// the bit sets of the level's categorical splits (found == 2 candidates that won their node), computed from the
+// histogram pairs [pair0, pair1) this rank holds: into the split records (bits == NULL) or into bits[n_nodes][32]
+// (zeros for nodes whose winning pair lies elsewhere), which launch_set_cat_bits copies into the records
+cudaError_t launch_cat_bits(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
+                            const h2ok_col_desc* descs, int n_nodes, int cols, int64_t pair0, int64_t pair1, int nb1,
+                            h2ok_split* splits, uint32_t* bits, cudaStream_t s, const unsigned char* node_class = nullptr);
+cudaError_t launch_set_cat_bits(const uint32_t* bits, int n_nodes, h2ok_split* splits, cudaStream_t s);
 // both steps over every pair; cand: [n_nodes * cols] scratch
 cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
                                double min_rows, double msi, PairCand* cand, h2ok_split* splits, cudaStream_t s);

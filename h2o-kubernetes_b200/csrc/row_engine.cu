@@ -1129,6 +1129,7 @@ __global__ void __launch_bounds__(256) eng_code_kernel(const float* __restrict__
   }
 }
 
+constexpr int kRouteBits = 0x80;  // RouteNode.na: the split is a categorical one (bit set in the split record)
 struct RouteNode {  // what routing needs of one node's split, 16 bytes
   float splat;
   short col;          // < 0: the node does not split
@@ -1158,9 +1159,9 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
     RouteNode t;
     t.splat = sp.splat;
     t.col = (short)sp.col;
-    t.na = (unsigned char)sp.na_dir;
+    t.na = (unsigned char)(sp.na_dir | (sp.col >= 0 && sp.equal >= 2 ? kRouteBits : 0));
     t.cs = 0;
-    if (!exact_codes && sp.col >= 0 && sp.na_dir != H2OK_NA_VS_REST && sp.splat == sp.splat)
+    if (!exact_codes && sp.col >= 0 && sp.equal < 2 && sp.na_dir != H2OK_NA_VS_REST && sp.splat == sp.splat)
       t.cs = (unsigned char)code_of(thr + (int64_t)sp.col * 256, enc_key(sp.splat));
     t.c0 = (short)child_ids[2 * g];
     t.c1 = (short)child_ids[2 * g + 1];
@@ -1185,8 +1186,12 @@ __global__ void __launch_bounds__(kRouteThreads, 4) eng_route_kernel(
         } else {
           const unsigned c = code8[(int64_t)t.col * ld8 + r];
           int way;
-          if (c == 255u) way = (t.na == H2OK_NA_LEFT) ? 0 : 1;
-          else if (t.na == H2OK_NA_VS_REST) way = 0;
+          const int na = t.na & ~kRouteBits;
+          if (c == 255u) way = (na == H2OK_NA_LEFT) ? 0 : 1;
+          else if (na == H2OK_NA_VS_REST) way = 0;
+          else if (t.na & kRouteBits)  // a categorical split: the row's category against the split's bit set
+            way = cat_goes_right(splits[n].cat_bits,
+                                 exact_codes ? (float)c : (XT ? XT[r * ldt + t.col] : csc_get(cptr, clen, r, t.col)), na);
           else if (exact_codes) way = (float)c >= t.splat ? 1 : 0;  // u8 storage: the byte is the value
           else if (c != t.cs) way = c > t.cs ? 1 : 0;
           else way = (XT ? XT[r * ldt + t.col] : csc_get(cptr, clen, r, t.col)) >= t.splat ? 1 : 0;  // code tie: the float decides

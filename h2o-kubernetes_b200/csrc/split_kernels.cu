@@ -73,6 +73,67 @@ struct ValsAcc {
   }
 };
 
+// A categorical column's bins in the order of their mean response (DTree.findBestSplitPoint sorts them and then scans
+// the sorted copy like any ordered column); the NA bucket keeps its place behind the last bin.
+template <class V>
+struct ValsPerm {
+  V v;
+  const unsigned short* idx;
+  int nb;
+  __device__ __forceinline__ double operator()(int b, int ch) const { return v(b < nb ? (int)idx[b] : b, ch); }
+};
+
+// Which columns are sorted: categorical, one category per bin, four categories or more (with three the ordered scan
+// already tries two of the three partitions; H2O-3's own threshold as recalled — oracle/hist_oracle.c cat_sorted()).
+__device__ __forceinline__ bool cat_sorted(const h2ok_col_desc& d) { return d.is_int == 2 && d.step == 1.0 && d.nbin >= 4; }
+
+// idx[rank] = bin, ranks by (mean response, bin) ascending — a stable sort, done by counting: bin i's rank is the
+// number of bins that come before it.  An empty bin's mean is -DBL_MAX (they come first).
+template <class V>
+__device__ void warp_sort_bins(const V& vals, int nb, int lane, double* avg, unsigned short* idx) {
+  for (int b = lane; b < nb; b += 32) {
+    const double w = vals(b, 0);
+    avg[b] = w == 0 ? -1.7976931348623157e308 : __ddiv_rn(vals(b, 1), w);
+  }
+  __syncwarp();
+  for (int i = lane; i < nb; i += 32) {
+    const double a = avg[i];
+    int r = 0;
+    for (int j = 0; j < nb; j++) {
+      const double aj = avg[j];
+      r += (aj < a || (aj == a && j < i)) ? 1 : 0;
+    }
+    idx[r < nb ? r : nb - 1] = (unsigned short)i;
+  }
+  __syncwarp();
+}
+
+// The IcedBitSet of a categorical split: the categories of the sorted positions [bin, nb) go right.  A category the
+// node has not seen (empty bin) goes where most of the seen categories went, left on a tie (as recalled).
+template <class V>
+__device__ void warp_cat_bits(const V& vals, const h2ok_col_desc& d, const unsigned short* idx, int bin, int lane,
+                              unsigned* bits /* [H2OK_CAT_WORDS], shared */) {
+  bits[lane] = 0;
+  __syncwarp();
+  int nl = 0, nr = 0;
+  for (int i = lane; i < d.nbin; i += 32)
+    if (vals((int)idx[i], 0) != 0) {
+      if (i >= bin) nr++;
+      else nl++;
+    }
+  nl = __reduce_add_sync(kFull, nl);
+  nr = __reduce_add_sync(kFull, nr);
+  const bool empties_left = nl >= nr;
+  const int off = (int)d.min;
+  for (int i = lane; i < d.nbin; i += 32) {
+    const int b = (int)idx[i];
+    const bool right = vals(b, 0) != 0 ? i >= bin : !empties_left;
+    const int c = b + off;
+    if (right && c >= 0 && c < 32 * H2OK_CAT_WORDS) atomicOr(&bits[c >> 5], 1u << (c & 31));
+  }
+  __syncwarp();
+}
+
 // One warp evaluates one (node, column).  Returns found != 0 in every lane and the winning candidate in `out`.
 template <class V>
 __device__ int warp_best_split_point(const V& vals, int nbins, double min_rows, double msi, int lane,
@@ -243,7 +304,7 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, 
                                                                         const h2ok_col_desc* __restrict__ descs,
                                                                         int64_t pair0, int64_t pair1, int nb1,
                                                                         double min_rows, double msi,
-                                                                        PairCand* __restrict__ out) {
+                                                                        PairCand* __restrict__ out, int cat_smem) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t pair = pair0 + (int64_t)blockIdx.x * kSplitWarps + warp;
   if (pair >= pair1) return;
@@ -260,7 +321,23 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_points_kernel(V base, 
     vals.p += pair * nb1 * 3;
     Cand cand;
     double before;
-    if (warp_best_split_point(vals, d.nbin, min_rows, msi, lane, cand, before)) {
+    if (cat_smem && cat_sorted(d)) {
+      extern __shared__ __align__(16) unsigned char sort_smem[];
+      double* avg = reinterpret_cast<double*>(sort_smem) + (size_t)warp * nb1;
+      unsigned short* idx = reinterpret_cast<unsigned short*>(reinterpret_cast<double*>(sort_smem) + (size_t)kSplitWarps * nb1) +
+                            (size_t)warp * nb1;
+      warp_sort_bins(vals, d.nbin, lane, avg, idx);
+      const ValsPerm<V> pv{vals, idx, d.nbin};
+      if (warp_best_split_point(pv, d.nbin, min_rows, msi, lane, cand, before)) {
+        pc.found = cand.na == H2OK_NA_VS_REST ? 1 : 2;  // (all non-NA rows on one side: no bit set is needed)
+        pc.key = cand.key;
+        pc.seL = cand.seL; pc.seR = cand.seR; pc.nL = cand.nL; pc.nR = cand.nR; pc.pL = cand.pL; pc.pR = cand.pR;
+        pc.se_before = before;
+        pc.bin = cand.bin;
+        pc.na = cand.na;
+        pc.splat = cand.na == H2OK_NA_VS_REST ? -1.0f : 0.0f;
+      }
+    } else if (warp_best_split_point(vals, d.nbin, min_rows, msi, lane, cand, before)) {
       pc.found = 1;
       pc.key = cand.key;
       pc.seL = cand.seL; pc.seR = cand.seR; pc.nL = cand.nL; pc.nR = cand.nR; pc.pL = cand.pL; pc.pR = cand.pR;
@@ -303,6 +380,8 @@ __global__ void __launch_bounds__(kSplitWarps * 32) best_col_kernel(const PairCa
   out.na_dir = 0;
   out.splat = 0.0f;
   out.se_before = out.se_left = out.se_right = out.n_left = out.n_right = out.pred_left = out.pred_right = 0;
+  out.equal = out.pad = 0;
+  for (int w = 0; w < H2OK_CAT_WORDS; w++) out.cat_bits[w] = 0;  // (filled in by cat_bits_kernel)
   if (bc != 0x7fffffff) {
     const PairCand p = cand[(int64_t)g * cols + bc];
     out.col = bc;
@@ -316,8 +395,52 @@ __global__ void __launch_bounds__(kSplitWarps * 32) best_col_kernel(const PairCa
     out.n_right = p.nR;
     out.pred_left = p.pL;
     out.pred_right = p.pR;
+    out.equal = p.found == 2 ? 2 : 0;
   }
   splits[g] = out;
+}
+
+// The bit sets of the level's categorical splits, one warp per node: the winning column's bins are sorted again and the
+// set is written into the split record — or, when this rank holds only the pairs [pair0, pair1) of the reduced
+// histogram, into bits[node] (zeros for the nodes whose winner another rank holds; the ranks' arrays are then summed).
+template <class V>
+__global__ void __launch_bounds__(kSplitWarps * 32) cat_bits_kernel(V base, const h2ok_quant* __restrict__ q_dev,
+                                                                    const unsigned char* __restrict__ node_class, int cols,
+                                                                    const h2ok_col_desc* __restrict__ descs, int n_nodes,
+                                                                    int64_t pair0, int64_t pair1, int nb1,
+                                                                    h2ok_split* __restrict__ splits, uint32_t* __restrict__ bits) {
+  extern __shared__ __align__(16) unsigned char sort_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x * kSplitWarps + warp;
+  if (g >= n_nodes) return;
+  double* avg = reinterpret_cast<double*>(sort_smem) + (size_t)warp * nb1;
+  unsigned short* idx = reinterpret_cast<unsigned short*>(reinterpret_cast<double*>(sort_smem) + (size_t)kSplitWarps * nb1) +
+                        (size_t)warp * nb1;
+  unsigned* wbits = reinterpret_cast<unsigned*>(reinterpret_cast<unsigned short*>(reinterpret_cast<double*>(sort_smem) +
+                                                                                   (size_t)kSplitWarps * nb1) +
+                                                (size_t)kSplitWarps * (nb1 + (nb1 & 1))) + warp * H2OK_CAT_WORDS;
+  const int col = splits[g].col, bin = splits[g].bin;
+  const bool cat = col >= 0 && splits[g].equal == 2;
+  const int64_t pair = (int64_t)g * cols + (cat ? col : 0);
+  unsigned word = 0;
+  if (cat && pair >= pair0 && pair < pair1) {
+    const h2ok_col_desc d = descs[pair];
+    V vals = base;
+    if (q_dev) vals.scales_from(node_class ? q_dev + node_class[g] : q_dev);
+    vals.p += pair * nb1 * 3;
+    warp_sort_bins(vals, d.nbin, lane, avg, idx);
+    warp_cat_bits(vals, d, idx, bin, lane, wbits);
+    word = wbits[lane];
+  }
+  if (bits) bits[(int64_t)g * H2OK_CAT_WORDS + lane] = word;
+  else if (cat) splits[g].cat_bits[lane] = word;
+}
+
+__global__ void set_cat_bits_kernel(const uint32_t* __restrict__ bits, int n_nodes, h2ok_split* __restrict__ splits) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_nodes * H2OK_CAT_WORDS) return;
+  const int g = i / H2OK_CAT_WORDS;
+  if (splits[g].col >= 0 && splits[g].equal == 2) splits[g].cat_bits[i % H2OK_CAT_WORDS] = bits[i];
 }
 
 // ---- a8 ---------------------------------------------------------------------------------------------------
@@ -404,6 +527,8 @@ __global__ void next_level_descs_kernel(const h2ok_split* __restrict__ splits, c
       if (s.col == j) {
         if (s.na_dir == H2OK_NA_VS_REST) {
           if (way == 1) ok = false;
+        } else if (s.equal >= 2) {
+          // a set of categories on each side: nothing is known about either side's range (Split.nextLevelHistos case 2 / 3)
         } else {
           double split = (double)s.splat;
           if (h.is_int > 0) split = (double)(float)ceil(split);
@@ -485,6 +610,7 @@ __global__ void apply_splits_kernel(const float* __restrict__ X, int64_t ld, int
   int way;
   if (d != d) way = (na == H2OK_NA_LEFT) ? 0 : 1;
   else if (na == H2OK_NA_VS_REST) way = 0;
+  else if (splits[g].equal >= 2) way = cat_goes_right(splits[g].cat_bits, d, na);
   else way = d >= splat ? 1 : 0;
   const int ch = child_ids[2 * g + way];
   nid[r] = ch;
@@ -493,14 +619,25 @@ __global__ void apply_splits_kernel(const float* __restrict__ X, int64_t ld, int
 
 }  // namespace
 
+// shared memory of the categorical sort: per warp nb1 means, nb1 bin indices (and a bit set in cat_bits_kernel)
+static size_t cat_smem_bytes(int nb1) {
+  return (size_t)kSplitWarps * ((size_t)nb1 * 8 + (size_t)(nb1 + (nb1 & 1)) * 2 + H2OK_CAT_WORDS * 4);
+}
+
 cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
                                 const h2ok_col_desc* descs, int64_t pair0, int64_t pair1, int nb1, double min_rows,
-                                double msi, PairCand* cand, cudaStream_t s, const unsigned char* node_class, int cols) {
+                                double msi, PairCand* cand, cudaStream_t s, const unsigned char* node_class, int cols,
+                                bool categorical) {
   if (pair1 <= pair0) return cudaSuccess;
   const unsigned grid = (unsigned)((pair1 - pair0 + kSplitWarps - 1) / kSplitWarps);
+  const size_t smem = categorical ? cat_smem_bytes(nb1) : 0;
   if (hist) {
-    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, 0, s>>>(ValsF64{hist}, nullptr, nullptr, 1, descs, pair0, pair1, nb1,
-                                                                   min_rows, msi, cand);
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(split_points_kernel<ValsF64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    split_points_kernel<ValsF64><<<grid, kSplitWarps * 32, smem, s>>>(ValsF64{hist}, nullptr, nullptr, 1, descs, pair0, pair1, nb1,
+                                                                      min_rows, msi, cand, categorical ? 1 : 0);
   } else {
     ValsAcc v{acc, {1.0, 1.0, 1.0}};
     if (!q_dev) {
@@ -508,9 +645,48 @@ cudaError_t launch_split_points(const double* hist, const int64_t* acc, const h2
       v.inv[1] = 1.0 / q->scale_wy;
       v.inv[2] = 1.0 / q->scale_wyy;
     }
-    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, 0, s>>>(v, q_dev, node_class, cols > 0 ? cols : 1, descs, pair0, pair1,
-                                                                   nb1, min_rows, msi, cand);
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(split_points_kernel<ValsAcc>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    split_points_kernel<ValsAcc><<<grid, kSplitWarps * 32, smem, s>>>(v, q_dev, node_class, cols > 0 ? cols : 1, descs, pair0,
+                                                                      pair1, nb1, min_rows, msi, cand, categorical ? 1 : 0);
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_cat_bits(const double* hist, const int64_t* acc, const h2ok_quant* q, const h2ok_quant* q_dev,
+                            const h2ok_col_desc* descs, int n_nodes, int cols, int64_t pair0, int64_t pair1, int nb1,
+                            h2ok_split* splits, uint32_t* bits, cudaStream_t s, const unsigned char* node_class) {
+  const unsigned grid = (unsigned)((n_nodes + kSplitWarps - 1) / kSplitWarps);
+  const size_t smem = cat_smem_bytes(nb1);
+  if (hist) {
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(cat_bits_kernel<ValsF64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    cat_bits_kernel<ValsF64><<<grid, kSplitWarps * 32, smem, s>>>(ValsF64{hist}, nullptr, nullptr, cols, descs, n_nodes, pair0,
+                                                                  pair1, nb1, splits, bits);
+  } else {
+    ValsAcc v{acc, {1.0, 1.0, 1.0}};
+    if (!q_dev) {
+      v.inv[0] = 1.0 / q->scale_w;
+      v.inv[1] = 1.0 / q->scale_wy;
+      v.inv[2] = 1.0 / q->scale_wyy;
+    }
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(cat_bits_kernel<ValsAcc>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    cat_bits_kernel<ValsAcc><<<grid, kSplitWarps * 32, smem, s>>>(v, q_dev, node_class, cols, descs, n_nodes, pair0, pair1, nb1,
+                                                                  splits, bits);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_set_cat_bits(const uint32_t* bits, int n_nodes, h2ok_split* splits, cudaStream_t s) {
+  const int n = n_nodes * H2OK_CAT_WORDS;
+  set_cat_bits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(bits, n_nodes, splits);
   return cudaGetLastError();
 }
 
@@ -519,12 +695,16 @@ cudaError_t launch_best_col(const PairCand* cand, int n_nodes, int cols, h2ok_sp
   return cudaGetLastError();
 }
 
+// (the caller's descriptors live on the device: the categorical sort's shared memory is always asked for here)
 cudaError_t launch_find_splits(const double* hist, const h2ok_col_desc* descs, int n_nodes, int cols, int nb1,
                                double min_rows, double msi, PairCand* cand, h2ok_split* splits, cudaStream_t s) {
-  cudaError_t e = launch_split_points(hist, nullptr, nullptr, nullptr, descs, 0, (int64_t)n_nodes * cols, nb1, min_rows, msi,
-                                      cand, s);
+  const int64_t pairs = (int64_t)n_nodes * cols;
+  cudaError_t e = launch_split_points(hist, nullptr, nullptr, nullptr, descs, 0, pairs, nb1, min_rows, msi, cand, s, nullptr, 0,
+                                      true);
   if (e != cudaSuccess) return e;
-  return launch_best_col(cand, n_nodes, cols, splits, s);
+  e = launch_best_col(cand, n_nodes, cols, splits, s);
+  if (e != cudaSuccess) return e;
+  return launch_cat_bits(hist, nullptr, nullptr, nullptr, descs, n_nodes, cols, 0, pairs, nb1, splits, nullptr, s, nullptr);
 }
 
 static cudaError_t next_level_any(bool enc, const h2ok_split* splits, const h2ok_col_desc* descs, const void* min2,

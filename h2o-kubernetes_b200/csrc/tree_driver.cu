@@ -103,6 +103,9 @@ __global__ void hash_splits_kernel(const h2ok_split* __restrict__ sp, int n, int
     s += splitmix64((b + 1) ^ salt) * (unsigned long long)(long long)t.bin;
     s += splitmix64((b + 2) ^ salt) * (unsigned long long)(long long)t.na_dir;
     s += splitmix64((b + 3) ^ salt) * (unsigned long long)__float_as_uint(t.splat);
+    if (t.col >= 0 && t.equal == 2)  // a categorical split: its bit set, word by word
+      for (int w = 0; w < H2OK_CAT_WORDS; w++)
+        s += splitmix64((b + 1) ^ salt ^ ((uint64_t)(w + 1) << 32)) * (unsigned long long)t.cat_bits[w];
   }
   s = warp_add_u64(s);
   if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
@@ -125,6 +128,7 @@ struct TreeLoop {
   int cols = 0, max_nodes = 0, max_bins = 0, nb1 = 0;
   int forest = 1;  // class trees built in lockstep (h2ok_hist_loop_create_forest); 1: one tree
   int reduce_mode = H2OK_REDUCE_SCATTER;
+  bool has_cat = false;  // some column is categorical: the split search sorts its bins and splits carry bit sets
   // level buffers (device)
   h2ok_col_desc* descs[2] = {nullptr, nullptr};  // [max_nodes][cols], this level / the next
   // accumulators and ranges are double buffered by level parity: the NEXT level's histogram pass is enqueued before
@@ -356,7 +360,7 @@ int32_t level_search(h2ok_ctx* c) {
   if (L.cur_set) CK(cudaEventRecord(L.cur_set->c, c->stream));
   CK(launch_split_points(nullptr, L.acc, nullptr, L.q_dev, L.descs[L.cur], L.p0, L.p1, L.nb1, L.params.min_rows,
                          L.params.min_split_improvement, L.cand, c->stream,
-                         L.forest > 1 ? c->eng.node_class[c->eng.cur] : nullptr, L.cols));
+                         L.forest > 1 ? c->eng.node_class[c->eng.cur] : nullptr, L.cols, L.has_cat));
   if (L.checksum && L.p1 > L.p0) {
     const int64_t cell = (int64_t)L.nb1 * 3, cnt = (L.p1 - L.p0) * cell;
     hash_i64_kernel<<<grid_for(cnt, 256, 1184), 256, 0, c->stream>>>(L.acc + L.p0 * cell, cnt, (uint64_t)(L.p0 * cell),
@@ -385,6 +389,9 @@ int32_t level_finish(h2ok_ctx* c) {
   if (out && out->hist && L.forest > 1)
     return fail(H2OK_ERR_UNSUPPORTED, "%s", "a forest level does not deliver the fp64 histogram (read the accumulators: loop_view)");
   CK(launch_best_col(L.cand, n, L.cols, L.splits, c->stream));
+  if (L.has_cat)  // (reduce mode ALL: every rank holds every pair)
+    CK(launch_cat_bits(nullptr, L.acc, nullptr, L.q_dev, L.descs[L.cur], n, L.cols, 0, (int64_t)n * L.cols, L.nb1, L.splits,
+                       nullptr, c->stream, L.forest > 1 ? c->eng.node_class[c->eng.cur] : nullptr));
   if (L.last) {
     CK(cudaMemsetAsync(L.child_ids, 0xFF, sizeof(int32_t) * 2 * (size_t)n, c->stream));
     CK(cudaMemsetAsync(L.n_children, 0, sizeof(int32_t), c->stream));
@@ -685,15 +692,19 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
   const int max_bins = params->nbins > params->nbins_top_level ? params->nbins : params->nbins_top_level;
   if (max_bins > H2OK_MAX_BINS) return fail(H2OK_ERR_UNSUPPORTED, "%s", "bins outside [1, H2OK_MAX_BINS]");
   const int cols = c->eng.cols;
-  for (int j = 0; is_int && j < cols; j++)
-    if (is_int[j] > 1) return fail(H2OK_ERR_UNSUPPORTED, "%s", "categorical columns (is_int == 2) are not supported");
+  bool has_cat = false;
+  for (int j = 0; is_int && j < cols; j++) {
+    if (is_int[j] < 0 || is_int[j] > 2) return fail(H2OK_ERR_ARG, "%s", "is_int: 0 real, 1 integer, 2 categorical");
+    has_cat = has_cat || is_int[j] == 2;
+  }
   if (c->eng.u8) {
     // the cells are integer codes: every column is an integer column whose range never exceeds nbins, so that
     // DHistogram's integer rule gives step-1 bins at every level (what the byte-wide histogram pass assumes)
     if (params->nbins < 255 || params->nbins_top_level < 255)
       return fail(H2OK_ERR_UNSUPPORTED, "%s", "u8 storage needs nbins >= 255 (one bin per code at every level)");
     for (int j = 0; j < cols; j++)
-      if (!is_int || is_int[j] != 1) return fail(H2OK_ERR_ARG, "%s", "u8 storage: every column is an integer column (is_int == 1)");
+      if (!is_int || is_int[j] < 1)
+        return fail(H2OK_ERR_ARG, "%s", "u8 storage: every column is an integer or categorical column (is_int 1 or 2)");
   }
   CK(cudaSetDevice(c->device));
   loop_free(c);
@@ -704,6 +715,10 @@ static int32_t loop_alloc(h2ok_ctx* c, const h2ok_params* params, const int32_t*
   L->max_bins = max_bins;
   L->nb1 = max_bins + 1;
   if (is_int) L->is_int.assign(is_int, is_int + cols);
+  L->has_cat = has_cat;
+  // a categorical split's bit set is worked out from the winning column's reduced histogram, which under
+  // H2OK_REDUCE_SCATTER only one rank holds: such loops reduce with an all-reduce, every rank then has every pair
+  if (has_cat) L->reduce_mode = H2OK_REDUCE_ALL;
   int64_t mn = (int64_t)1 << (params->max_depth - 1 < 10 ? params->max_depth - 1 : 10);
   L->forest = forest;
   if (forest > 1) {
@@ -841,7 +856,7 @@ int32_t h2ok_hist_loop_set_reduce(h2ok_ctx* c, int32_t mode) {
   int32_t rc = need_loop(c, "loop_set_reduce");
   if (rc) return rc;
   REQUIRE(mode == H2OK_REDUCE_SCATTER || mode == H2OK_REDUCE_ALL, "unknown reduce mode");
-  c->loop->reduce_mode = mode;
+  c->loop->reduce_mode = c->loop->has_cat ? H2OK_REDUCE_ALL : mode;  // (categorical columns: see loop_alloc)
   return H2OK_OK;
 }
 

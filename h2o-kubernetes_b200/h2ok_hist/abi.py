@@ -24,10 +24,12 @@ SPLIT = np.dtype(
         ("col", "<i4"), ("bin", "<i4"), ("na_dir", "<i4"), ("splat", "<f4"),
         ("se_before", "<f8"), ("se_left", "<f8"), ("se_right", "<f8"),
         ("n_left", "<f8"), ("n_right", "<f8"), ("pred_left", "<f8"), ("pred_right", "<f8"),
+        ("equal", "<i4"), ("pad", "<i4"), ("cat_bits", "<u4", (32,)),
     ],
     align=True,
 )
-assert COL_DESC.itemsize == 32 and SPLIT.itemsize == 72
+CAT_WORDS = 32
+assert COL_DESC.itemsize == 32 and SPLIT.itemsize == 208
 
 
 class Quant(C.Structure):

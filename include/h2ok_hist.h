@@ -41,7 +41,7 @@ extern "C" {
 #define H2OK_ERR_ARG 1         /* bad argument (null, size, alignment) */
 #define H2OK_ERR_CUDA 2        /* a CUDA call failed; message has the CUDA error string */
 #define H2OK_ERR_STATE 3       /* call sequence violated (e.g. build_level before set_data) */
-#define H2OK_ERR_UNSUPPORTED 4 /* categorical columns, > H2OK_MAX_BINS bins, ... */
+#define H2OK_ERR_UNSUPPORTED 4 /* > H2OK_MAX_BINS bins, category codes past 1023, ... */
 
 #define H2OK_MAX_BINS 1024
 #define H2OK_MAX_LEVEL_NODES 1023 /* node indices travel in 10 bits of the packed row records */
@@ -85,10 +85,15 @@ typedef struct h2ok_col_desc {
   double maxex;   /* exclusive upper bound (_maxEx) */
   double step;    /* _step: nbin/(maxex-min), or 1.0 for integer columns with few values */
   int32_t nbin;   /* _nbin <= max_bins */
-  int32_t is_int; /* _isInt: 0 real, 1 integer; 2 (categorical) is rejected */
+  int32_t is_int; /* _isInt: 0 real, 1 integer, 2 categorical (integer codes 0 .. 1023, at most nbins of them) */
 } h2ok_col_desc;
 
-/* a7 — DTree.Split as chosen by UndecidedNode.bestCol.  col < 0: the node does not split. */
+/* a7 — DTree.Split as chosen by UndecidedNode.bestCol.  col < 0: the node does not split.
+ * equal == 0: a ranged split, x >= splat goes right.  equal == 2: a categorical split (DTree.Split._equal 2 / 3 with its
+ * IcedBitSet): the column is categorical (h2ok_col_desc.is_int == 2), `bin` is the cut position in the order of the
+ * bins sorted by mean response, splat is unused, and a row whose category code is c goes right when bit c of cat_bits
+ * is set (word c / 32, bit c % 32).  NaN follows na_dir either way. */
+#define H2OK_CAT_WORDS 32 /* category codes 0 .. 1023 */
 typedef struct h2ok_split {
   int32_t col;
   int32_t bin;    /* bins [0,bin) left, [bin,nbin) right */
@@ -97,6 +102,9 @@ typedef struct h2ok_split {
   double se_before, se_left, se_right;
   double n_left, n_right;       /* weighted row counts */
   double pred_left, pred_right; /* wY/w of each side */
+  int32_t equal;
+  int32_t pad;
+  uint32_t cat_bits[H2OK_CAT_WORDS];
 } h2ok_split;
 
 /* Fixed-point scales for the integer accumulators.  All three are powers of two so that the

@@ -498,10 +498,48 @@ static float split_splat(const double* vals, const h2ok_col_desc* d, int32_t bin
   return (float)((lo + hi) / 2.0);
 }
 
+/* [H2O-3 DTree.findBestSplitPoint, categorical part, recalled]: a categorical column with one category per bin and
+ * at least four bins is scanned in the order of its bins' mean response (idxs sorted by avgs; empty bins carry
+ * -Double.MAX_VALUE and come first; the sort is stable), which finds the best two-set partition for a squared-error
+ * criterion.  The split then carries a bit set instead of a threshold. */
+static int cat_sorted(const h2ok_col_desc* d) { return d->is_int == 2 && d->step == 1.0 && d->nbin >= 4; }
+
+static void sort_bins_by_mean(const double* vals, int32_t nb, int32_t* idx) {
+  double* avg = (double*)malloc(sizeof(double) * (size_t)nb);
+  for (int32_t b = 0; b < nb; b++) avg[b] = vals[3 * b] == 0 ? -DBL_MAX : vals[3 * b + 1] / vals[3 * b];
+  for (int32_t i = 0; i < nb; i++) { /* rank by counting: (mean, bin) ascending */
+    int32_t r = 0;
+    for (int32_t j = 0; j < nb; j++) r += (avg[j] < avg[i] || (avg[j] == avg[i] && j < i)) ? 1 : 0;
+    idx[r < nb ? r : nb - 1] = i;
+  }
+  free(avg);
+}
+
+/* [IcedBitSet of DTree.Split, recalled]: the categories at the sorted positions [bin, nb) go right; a category the node
+ * has not seen goes where most of the seen ones went (left on a tie). */
+static void cat_bits(const double* vals, const h2ok_col_desc* d, const int32_t* idx, int32_t bin, uint32_t* bits) {
+  int nl = 0, nr = 0;
+  for (int32_t i = 0; i < d->nbin; i++)
+    if (vals[3 * idx[i]] != 0) {
+      if (i >= bin) nr++;
+      else nl++;
+    }
+  int empties_left = nl >= nr;
+  int off = (int)d->min;
+  for (int w = 0; w < H2OK_CAT_WORDS; w++) bits[w] = 0;
+  for (int32_t i = 0; i < d->nbin; i++) {
+    int right = vals[3 * idx[i]] != 0 ? i >= bin : !empties_left;
+    int c = idx[i] + off;
+    if (right && c >= 0 && c < 32 * H2OK_CAT_WORDS) bits[c >> 5] |= 1u << (c & 31);
+  }
+}
+
 void h2ok_oracle_find_splits(const double* hist, const h2ok_col_desc* descs, int32_t n_nodes, int32_t cols,
                              int32_t max_bins, double min_rows, double msi, h2ok_split* splits) {
   int32_t nb1 = max_bins + 1;
   double* scratch = (double*)malloc(sizeof(double) * 6 * (size_t)(nb1 + 1));
+  double* sorted = (double*)malloc(sizeof(double) * 3 * (size_t)nb1);
+  int32_t* idx = (int32_t*)malloc(sizeof(int32_t) * (size_t)nb1);
   for (int32_t g = 0; g < n_nodes; g++) {
     h2ok_split* s = &splits[g];
     memset(s, 0, sizeof(*s));
@@ -511,7 +549,16 @@ void h2ok_oracle_find_splits(const double* hist, const h2ok_col_desc* descs, int
       const h2ok_col_desc* d = &descs[(int64_t)g * cols + c];
       if (d->nbin <= 1) continue;
       const double* vals = hist + ((int64_t)g * cols + c) * nb1 * 3;
-      col_split cs = best_split_point(vals, d->nbin, min_rows, msi, scratch);
+      const int cat = cat_sorted(d);
+      const double* scan = vals;
+      if (cat) { /* a sorted copy; the NA bucket stays behind the last bin */
+        sort_bins_by_mean(vals, d->nbin, idx);
+        for (int32_t b = 0; b < d->nbin; b++)
+          for (int ch = 0; ch < 3; ch++) sorted[3 * b + ch] = vals[3 * idx[b] + ch];
+        for (int ch = 0; ch < 3; ch++) sorted[3 * d->nbin + ch] = vals[3 * d->nbin + ch];
+        scan = sorted;
+      }
+      col_split cs = best_split_point(scan, d->nbin, min_rows, msi, scratch);
       if (!cs.found) continue;
       double se = cs.se_l + cs.se_r;
       if (s->col < 0 || se < best_se) { /* bestCol: strictly smaller se() wins, first column on ties */
@@ -519,7 +566,15 @@ void h2ok_oracle_find_splits(const double* hist, const h2ok_col_desc* descs, int
         s->col = c;
         s->bin = cs.bin;
         s->na_dir = cs.na_dir;
-        s->splat = split_splat(vals, d, cs.bin, cs.na_dir);
+        s->equal = 0;
+        memset(s->cat_bits, 0, sizeof(s->cat_bits));
+        if (cat && cs.na_dir != H2OK_NA_VS_REST) {
+          s->equal = 2;
+          s->splat = 0.0f;
+          cat_bits(vals, d, idx, cs.bin, s->cat_bits);
+        } else {
+          s->splat = cat ? -1.0f : split_splat(vals, d, cs.bin, cs.na_dir);
+        }
         s->se_before = cs.se_before;
         s->se_left = cs.se_l;
         s->se_right = cs.se_r;
@@ -530,6 +585,8 @@ void h2ok_oracle_find_splits(const double* hist, const h2ok_col_desc* descs, int
       }
     }
   }
+  free(idx);
+  free(sorted);
   free(scratch);
 }
 
@@ -575,6 +632,8 @@ void h2ok_oracle_next_level(const h2ok_split* splits, const h2ok_col_desc* descs
         if (s->col == j) {
           if (s->na_dir == H2OK_NA_VS_REST) {
             if (way == 1) continue; /* the NA child has nothing but NAs in this column */
+          } else if (s->equal >= 2) {
+            /* [Split.nextLevelHistos case 2 / 3]: a set of categories each side, no tighter bounds */
           } else {
             double split = (double)s->splat;
             if (h->is_int > 0) split = (double)(float)ceil(split);
@@ -614,7 +673,11 @@ void h2ok_oracle_apply_splits(const float* X, int64_t ld, int64_t rows, const h2
     int way;
     if (isnan(d)) way = (s->na_dir == H2OK_NA_LEFT) ? 0 : 1;
     else if (s->na_dir == H2OK_NA_VS_REST) way = 0;
-    else way = d >= s->splat ? 1 : 0;
+    else if (s->equal >= 2) { /* [DecidedNode with a bit set]: the row's category; one outside the set's range follows the NAs */
+      int c = (int)d;
+      if (c < 0 || c >= 32 * H2OK_CAT_WORDS) way = (s->na_dir == H2OK_NA_LEFT) ? 0 : 1;
+      else way = (int)((s->cat_bits[c >> 5] >> (c & 31)) & 1u);
+    } else way = d >= s->splat ? 1 : 0;
     int32_t ch = child_ids[2 * g + way];
     nid[r] = ch;
     if (ch < 0 && leaf) leaf[r] = (gid_base + g) * 3 + 1 + way;

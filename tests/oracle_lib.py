@@ -291,6 +291,13 @@ def tree_checksum(levels, leaf, row0=0):
         f = np.stack([sp["col"].astype(np.int64), sp["bin"].astype(np.int64), sp["na_dir"].astype(np.int64),
                       sp["splat"].view(np.uint32).astype(np.int64)], axis=1)
         split_sum = (split_sum + _hash_sum(f, 4 * lv["gid_base"], SALT_SPLIT)) & 0xFFFFFFFFFFFFFFFF
+        if "equal" in sp.dtype.names:  # categorical splits: their bit sets, word by word
+            with np.errstate(over="ignore"):
+                for g in np.nonzero((sp["col"] >= 0) & (sp["equal"] == 2))[0]:
+                    b = np.uint64(4 * (lv["gid_base"] + int(g)) + 1)
+                    w = np.arange(1, 33, dtype=np.uint64) << np.uint64(32)
+                    h = splitmix64_np(b ^ np.uint64(SALT_SPLIT) ^ w) * sp["cat_bits"][g].astype(np.uint64)
+                    split_sum = (split_sum + int(np.sum(h, dtype=np.uint64))) & 0xFFFFFFFFFFFFFFFF
     return [acc_sum, split_sum, _hash_sum(np.asarray(leaf, np.int32).astype(np.int64), row0, SALT_LEAF)]
 
 

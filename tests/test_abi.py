@@ -32,7 +32,7 @@ def test_library_loads_and_exports_every_declared_symbol():
         assert hasattr(lib.cdll, n), f"{n} declared in h2ok_hist.h but not exported"
     bound = set(capi.SIGNATURES) | {"h2ok_last_error"}
     assert set(names) == bound, set(names) ^ bound
-    assert lib.cdll.h2ok_hist_abi_version() == 1
+    assert lib.cdll.h2ok_hist_abi_version() == 2
 
 
 def test_struct_layouts_match_header(tmp_path):
@@ -85,10 +85,20 @@ def test_host_helpers_need_no_gpu(oracle):
     qo = abi.Quant()
     oracle.lib.h2ok_oracle_choose_quant(abi.ptr(m), 1, 25, C.byref(qo))
     assert (q.scale_w, q.scale_wy, q.scale_wyy) == (qo.scale_w, qo.scale_wy, qo.scale_wyy) == (2.0**24, 2.0**25, 2.0**23)
-    ii[1] = 2
+    # a categorical column (is_int == 2) is binned like an integer column; its codes must fit a split's bit set
+    ii[2] = 2
+    lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi), 4, C.byref(p), abi.ptr(ii), abi.ptr(out))
+    assert out["nbin"].tolist() == [16, 0, 3, 0] and out["is_int"].tolist() == [0, 0, 2, 0]
+    assert out.tobytes() == oracle.root_descs(X, 8, p, ii).tobytes()
+    hi2 = hi.copy()
+    hi2[2] = 1024.0
+    with pytest.raises(capi.H2okError) as e:
+        lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi2), 4, C.byref(p), abi.ptr(ii), abi.ptr(out))
+    assert e.value.code == abi.ERR_UNSUPPORTED and "categorical" in str(e.value)
+    ii[2] = 3
     with pytest.raises(capi.H2okError) as e:
         lib.call("h2ok_hist_root_descs_from_ranges", abi.ptr(lo), abi.ptr(hi), 4, C.byref(p), abi.ptr(ii), abi.ptr(out))
-    assert e.value.code == abi.ERR_UNSUPPORTED and "categorical" in str(e.value)
+    assert e.value.code == abi.ERR_ARG
 
 
 def test_fails_loudly_without_a_device():

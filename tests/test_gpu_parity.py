@@ -356,6 +356,38 @@ def test_find_splits_on_real_histograms_bit_exact(shard, oracle, weight_mode, na
         assert (want["col"] >= 0).any()
 
 
+
+def test_find_splits_categorical_bit_exact(shard, oracle):
+    """a7 on categorical columns (is_int == 2): the bins sorted by mean response, the scan, the bit set of the winning
+    split — the whole h2ok_split record byte for byte against the oracle, next to real and integer columns."""
+    from test_oracle import desc
+
+    rng = np.random.default_rng(11)
+    n_nodes, cols = 7, 5
+    for nb, k_lo, k_hi in [(16, 4, 16), (64, 3, 64), (1024, 200, 1024)]:
+        hist = np.zeros((n_nodes, cols, nb + 1, 3))
+        descs = np.zeros((n_nodes, cols), abi.COL_DESC)
+        for g in range(n_nodes):
+            for c in range(cols):
+                k = int(rng.integers(k_lo, k_hi + 1))
+                cnt = rng.integers(0, 40, k).astype(np.float64)
+                cnt[rng.random(k) < 0.2] = 0  # unseen categories
+                mean = rng.integers(-16, 17, k) / 8.0
+                hist[g, c, :k, 0] = cnt
+                hist[g, c, :k, 1] = cnt * mean
+                hist[g, c, :k, 2] = cnt * mean * mean + cnt * rng.integers(0, 4, k) / 8.0
+                if (g + c) % 3 == 0:
+                    hist[g, c, nb] = (12, 3.5, 9.25)  # NAs
+                off = float(rng.integers(0, 1024 - k + 1))
+                descs[g, c] = desc(off, off + k, 1.0, k, is_int=2 if c != 1 else 1)
+        descs[2, 3] = desc(0.0, 3.0, 1.0, 3, is_int=2)  # three categories: ordered scan
+        descs[3, 0]["nbin"] = 0
+        for min_rows, msi in [(1.0, 0.0), (10.0, 1e-5), (60.0, 1e-5)]:
+            want = oracle.find_splits(hist, descs, min_rows, msi)
+            got = gpu_find_splits(shard, hist, descs, min_rows, msi)
+            assert got.tobytes() == want.tobytes(), (nb, min_rows, got, want)
+            assert (want["equal"] == 2).any()
+
 def run_tree_both(shard, oracle, X, rows, y, w, params, is_int=None):
     """LevelDriver on the GPU vs the oracle's fixed-point level loop: every level's accumulators, descriptors,
     splits, child ids and row map must be identical."""

@@ -172,6 +172,48 @@ def test_sparse_storage_rejects_weights(lib):
         lib.call("h2ok_hist_destroy", h)
 
 
+
+# ------------------------------------------------------------------------------------------------ categorical columns
+def categorical_case(oracle, rows, cols, seed, na):
+    """Columns 1, 3 and 5 become categorical (codes 0..k-1, k = 5, 37, 300), and the target depends on membership in
+    scattered sets of categories, so the winning splits are bit-set splits; column 4 is an integer column."""
+    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, seed, 0, rows, cols, na_permille=na)
+    rng = np.random.default_rng(seed)
+    is_int = [0] * cols
+    yy = y[:rows].astype(np.float64) * 0.2
+    for c, k in ((1, 5), (3, 37), (5, 300)):
+        if c >= cols:
+            continue
+        codes = rng.integers(0, k, rows).astype(np.float32)
+        nan = np.isnan(X[c, :rows])
+        X[c, :rows] = np.where(nan, np.nan, codes)
+        member = rng.random(k) < 0.5
+        yy += np.where(nan, 0.0, member[codes.astype(np.int64)] * (1.0 + c))
+        is_int[c] = 2
+    if cols > 4:
+        X[4, :rows] = np.floor(X[4, :rows] * 3)
+        is_int[4] = 1
+    y[:rows] = yy.astype(np.float32)
+    return X, y, is_int
+
+
+@pytest.mark.parametrize("rows,cols,nbins,depth,na", [(4099, 6, 64, 5, 0), (60001, 9, 512, 6, 20), (30011, 40, 1024, 5, 5)])
+def test_loop_categorical_columns_match_oracle(eshard, oracle, rows, cols, nbins, depth, na):
+    """is_int == 2: the split search sorts the categories by mean response, the split carries a bit set, rows are routed
+    by their category, children keep the parent's range of the split column — every level against the oracle."""
+    X, y, is_int = categorical_case(oracle, rows, cols, 900 + rows, na)
+    params = abi.Params.make(nbins=nbins, max_depth=depth, min_rows=5)
+    levels = check_tree(eshard, oracle, X, rows, y, None, params, is_int=is_int, host_out=True)
+    assert any((lv["splits"]["equal"] == 2).any() for lv in levels)
+
+
+def test_sparse_storage_categorical_columns(sshard, oracle):
+    rows, cols = 30011, 70
+    X, y, is_int = categorical_case(oracle, rows, cols, 77, 10)
+    X[6:, :rows] = np.where(np.arange(rows)[None, :] % 7 < 5, 0.0, X[6:, :rows])  # the other columns mostly zero
+    levels = check_tree(sshard, oracle, X, rows, y, None, abi.Params.make(nbins=512, max_depth=5, min_rows=5), is_int=is_int)
+    assert any((lv["splits"]["equal"] == 2).any() for lv in levels)
+
 # ------------------------------------------------------------------------------------------------ u8 storage
 @pytest.fixture(scope="module")
 def ushard():
@@ -219,6 +261,22 @@ def test_u8_storage_matches_oracle_on_the_codes(ushard, oracle, rows, cols, dept
     check_tree(ushard, oracle, codes, rows, y, None, params, is_int=[1] * cols, host_out=(rows % 2 == 1))
     assert ushard.stats().range_errors == 0
 
+
+
+def test_u8_storage_categorical_columns(ushard, oracle):
+    """Codes of a categorical column are category ids: the same bit-set splits on the byte-wide storage."""
+    rows, cols = 30011, 8
+    X, y, _ = oracle.synth(abi.SHAPE_WIDE64, 55, 0, rows, cols, na_permille=10)
+    _, codes = codes_of(oracle, X, rows, 200)
+    rng = np.random.default_rng(3)
+    cat = rng.integers(0, 150, rows)
+    member = rng.random(150) < 0.5
+    codes[2, :rows] = cat
+    y[:rows] = (y[:rows] * 0.1 + member[cat] * 2.0).astype(np.float32)
+    is_int = [1] * cols
+    is_int[2] = 2
+    levels = check_tree(ushard, oracle, codes, rows, y, None, abi.Params.make(nbins=255, max_depth=5, min_rows=5), is_int=is_int)
+    assert any((lv["splits"]["equal"] == 2).any() for lv in levels)
 
 def test_u8_storage_refuses_what_it_cannot_hold(ushard, oracle, lib):
     from h2ok_hist import capi

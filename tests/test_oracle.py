@@ -466,3 +466,82 @@ def test_gbm_multinomial_residuals_paper_case(oracle):
     assert res[:, 3] == pytest.approx([-0.5, 0.75, -0.25], abs=1e-6)
     assert abs(float(res[:, 3].astype(np.float64).sum())) < 1e-6
     assert den[:, 3] == pytest.approx([0.25 * 2**28, 0.1875 * 2**28, 0.1875 * 2**28], rel=1e-5)
+
+
+# ---------------------------------------------------------------- categorical columns (is_int == 2)
+def _bits_set(sp):
+    return {32 * w + b for w in range(32) for b in range(32) if (int(sp["cat_bits"][w]) >> b) & 1}
+
+
+def test_categorical_split_paper_case(oracle):
+    # six categories (codes 3..8) whose means alternate: no threshold separates them, the sorted scan does
+    cnt = [10, 10, 10, 10, 10, 10]
+    ys = [0, 10, 0, 10, 0, 10]
+    h = hist_from(cnt, ys, ys)
+    d = np.array([[desc(3.0, 9.0, 1.0, 6, is_int=2)]], abi.COL_DESC)
+    s = oracle.find_splits(h, d, 10.0, 1e-5)[0]
+    assert s["col"] == 0 and s["equal"] == 2 and s["bin"] == 3
+    assert s["se_left"] == 0 and s["se_right"] == 0 and s["pred_left"] == 0 and s["pred_right"] == 1
+    assert _bits_set(s) == {4, 6, 8}  # the categories with mean 1 go right
+    # the same column as an ordinary integer column: an ordered split, far worse
+    d1 = np.array([[desc(3.0, 9.0, 1.0, 6, is_int=1)]], abi.COL_DESC)
+    s1 = oracle.find_splits(h, d1, 10.0, 1e-5)[0]
+    assert s1["equal"] == 0 and s1["se_left"] + s1["se_right"] > 10
+    # fewer than four bins: ordered scan (no bit set)
+    h3 = hist_from(cnt[:3], ys[:3], ys[:3])
+    d3 = np.array([[desc(3.0, 6.0, 1.0, 3, is_int=2)]], abi.COL_DESC)
+    assert oracle.find_splits(h3, d3, 10.0, 1e-5)[0]["equal"] == 0
+    # unseen categories (empty bins) follow the majority of the seen ones; ties go left
+    h = hist_from([10, 0, 10, 10, 0, 10], [0, 0, 10, 10, 0, 10], [0, 0, 10, 10, 0, 10])
+    s = oracle.find_splits(h, d, 10.0, 1e-5)[0]
+    assert s["equal"] == 2 and _bits_set(s) == {5, 6, 8} | {4, 7}  # one seen category left, three right: empties right
+    h = hist_from([10, 0, 10, 10, 0, 10], [0, 0, 0, 10, 0, 10], [0, 0, 0, 10, 0, 10])
+    assert _bits_set(oracle.find_splits(h, d, 10.0, 1e-5)[0]) == {6, 8}  # two each: empties left
+
+
+def test_categorical_sorted_scan_finds_the_best_partition(oracle):
+    """The property the sort is there for: for squared error, the best of all 2^(k-1) - 1 two-set partitions of k
+    categories is a cut of the categories sorted by mean.  Brute force over every partition, several random cases."""
+    rng = np.random.default_rng(5)
+    for case in range(20):
+        k = int(rng.integers(4, 9))
+        cnt = rng.integers(1, 20, k).astype(np.float64)
+        mean = rng.integers(-8, 9, k) / 4.0
+        ys = cnt * mean
+        yys = cnt * mean * mean + rng.integers(0, 5, k) / 4.0
+        h = hist_from(cnt, ys, yys)
+        d = np.array([[desc(0.0, float(k), 1.0, k, is_int=2)]], abi.COL_DESC)
+        s = oracle.find_splits(h, d, 1.0, 0.0)[0]
+
+        def se(mask):
+            w, wy, wyy = cnt[mask].sum(), ys[mask].sum(), yys[mask].sum()
+            return wyy - wy * wy / w
+
+        best = min(se(np.array([(m >> i) & 1 == 1 for i in range(k)])) + se(np.array([(m >> i) & 1 == 0 for i in range(k)]))
+                   for m in range(1, 2 ** k - 1))
+        if s["col"] < 0:
+            continue
+        assert s["equal"] == 2
+        assert abs((s["se_left"] + s["se_right"]) - best) <= 1e-9 * max(1.0, abs(best))
+        right = np.array([i in _bits_set(s) for i in range(k)])
+        assert abs(se(right) - s["se_right"]) <= 1e-9 * max(1.0, s["se_right"]) and cnt[right].sum() == s["n_right"]
+
+
+def test_categorical_next_level_and_routing(oracle):
+    p = abi.Params.make(nbins=8, min_rows=1.0)
+    descs = np.array([[desc(0.0, 6.0, 1.0, 6, is_int=2)]], abi.COL_DESC)
+    sp = np.zeros(1, abi.SPLIT)
+    sp[0]["col"], sp[0]["equal"], sp[0]["na_dir"] = 0, 2, abi.NA_LEFT
+    sp[0]["n_left"] = sp[0]["n_right"] = 10
+    sp[0]["se_left"] = sp[0]["se_right"] = 1.0
+    sp[0]["cat_bits"][0] = (1 << 1) | (1 << 4)
+    # both children keep the parent's observed range of the split column: nothing narrower is known
+    child, ids, n = oracle.next_level(sp, descs, np.array([[0.0]], np.float32), np.array([[5.0]], np.float32), p)
+    assert n == 2
+    for k in (0, 1):
+        assert child[k, 0]["min"] == 0.0 and child[k, 0]["maxex"] == 6.0 and child[k, 0]["nbin"] == 6 and child[k, 0]["is_int"] == 2
+    X = np.array([[0, 1, 2, 4, np.nan, 2000.0, -3.0, 5]], np.float32)
+    nid = np.zeros(8, np.int32)
+    leaf = np.full(8, -1, np.int32)
+    oracle.apply_splits(X, 8, sp, np.array([0, 1], np.int32), 0, nid, leaf)
+    assert nid.tolist() == [0, 1, 0, 1, 0, 0, 0, 0]  # NaN and codes outside 0..1023 follow na_dir (left)
