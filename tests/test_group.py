@@ -88,6 +88,55 @@ def test_group_of_all_gpus_is_bit_identical_to_one(lib, mode):
             assert a[k].tobytes() == b[k].tobytes(), k
 
 
+
+def group_tree_host(lib, n_dev, X, rows, y, params, is_int):
+    """One tree over n_dev devices on the caller's columns (h2ok_hist_group_set_data_host / begin_tree_host)."""
+    cols = X.shape[0]
+    devs = (C.c_int32 * n_dev)(*range(n_dev))
+    g = C.c_void_p()
+    lib.call("h2ok_hist_group_create", devs, n_dev, C.byref(g))
+    try:
+        ptrs = (C.c_void_p * cols)(*[X[c].ctypes.data for c in range(cols)])
+        lib.call("h2ok_hist_group_set_data_host", g, ptrs, rows, cols)
+        ii = np.asarray(is_int, np.int32)
+        lib.call("h2ok_hist_group_loop_create", g, C.byref(params), abi.ptr(ii))
+        lib.call("h2ok_hist_group_set_options", g, abi.REDUCE_SCATTER, 1, 0)  # (categorical columns: ALL is used anyway)
+        lib.call("h2ok_hist_group_begin_tree_host", g, abi.ptr(y), None)
+        splits = []
+        n, nch = 1, C.c_int32(1)
+        while nch.value > 0 and len(splits) < params.max_depth:
+            sp = np.zeros(n, abi.SPLIT)
+            out = abi.LevelOut(None, None, None, C.c_void_p(sp.ctypes.data), None, None)
+            done = C.c_int32()
+            lib.call("h2ok_hist_group_level", g, C.byref(out), C.byref(done), C.byref(nch))
+            splits.append(sp)
+            n = nch.value
+        sums = (C.c_uint64 * 3)()
+        lib.call("h2ok_hist_group_checksum", g, sums)
+        return [int(x) for x in sums], splits
+    finally:
+        lib.call("h2ok_hist_group_destroy", g)
+
+
+def test_group_categorical_columns_match_the_oracle_on_every_device_count(lib, oracle):
+    """Bit-set splits through the group API: one device against the oracle, and all the box's devices against one."""
+    from test_loop import categorical_case
+
+    rows, cols = 80021, 9
+    X, y, is_int = categorical_case(oracle, rows, cols, 4242, 10)
+    X = np.ascontiguousarray(X[:, :rows])
+    y = np.ascontiguousarray(y[:rows])
+    params = abi.Params.make(nbins=512, max_depth=6, min_rows=5)
+    ref, _, leaf, _ = oracle_lib.train_tree_q(oracle, X, rows, y, None, params, is_int)
+    want = oracle_lib.tree_checksum(ref, leaf)
+    assert any((lv["splits"]["equal"] == 2).any() for lv in ref)
+    for n in sorted({1, torch.cuda.device_count()}):
+        sums, splits = group_tree_host(lib, n, X, rows, y, params, is_int)
+        assert sums == want, n
+        assert len(splits) == len(ref)
+        for got, lv in zip(splits, ref):
+            assert got.tobytes() == lv["splits"].tobytes()
+
 def test_h2ok_bench_binary_runs_and_agrees_with_the_library(lib):
     rows, cols = 200_000, 28
     out = subprocess.run([deploy.BENCH_BINARY, "--shape", "c2", "--rows", str(rows), "--bins", "64", "--depth", "5", "--trees", "2"],
