@@ -346,7 +346,8 @@ def run_gpu(args, wl):
         tree_no[0] += 1
         return y
     if in_library:
-        loop = TreeLoop(shard, params, checksum=True, time_phases=True, forest=K if forest else 1)
+        # (the checksum's hash kernels run only for the tree built after the timed region, see below)
+        loop = TreeLoop(shard, params, checksum=False, time_phases=True, forest=K if forest else 1)
     else:
         drv = LevelDriver(shard, params)
         drv.prepare_data()
@@ -404,10 +405,12 @@ def run_gpu(args, wl):
     checksum = None
     if in_library:
         tree_no[0] = 0
+        loop.set_options(checksum=True)
         begin()
         while loop.n_nodes_left() > 0:
             loop.level()
         checksum = ["%016x" % c for c in loop.checksum(row0)]
+        loop.set_options(checksum=False)
 
     # roofline of the dominant kernel: algorithmic bytes of THIS rank's launches / their device time (CUDA events
     # recorded inside the library around the histogram kernel of every timed level, read back after the timed region)

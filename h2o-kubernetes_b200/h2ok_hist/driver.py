@@ -355,9 +355,19 @@ class TreeLoop:
         else:
             self.lib.call("h2ok_hist_loop_create", shard.ctx, C.byref(params), abi.ptr(self.is_int))
         self.lib.call("h2ok_hist_loop_set_reduce", shard.ctx, reduce_mode)
-        self.lib.call("h2ok_hist_loop_set_options", shard.ctx, 1 if checksum else 0, 1 if time_phases else 0)
+        self.time_phases = bool(time_phases)
+        self.set_options(checksum=checksum)
         self.n_nodes = 0
         self.depth = 0
+
+    def set_options(self, checksum=None, time_phases=None):
+        """Switch the result checksum (three hash kernels per level) / the per-phase event timing on or off; takes
+        effect with the next tree."""
+        if checksum is not None:
+            self.checksum_on = bool(checksum)
+        if time_phases is not None:
+            self.time_phases = bool(time_phases)
+        self.lib.call("h2ok_hist_loop_set_options", self.shard.ctx, 1 if self.checksum_on else 0, 1 if self.time_phases else 0)
 
     @staticmethod
     def join_ranks(shard):
