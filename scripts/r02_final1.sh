@@ -2,7 +2,7 @@
 # final round-2 evidence on one GPU: the default bench line (with CPU baseline and e2e), the other workloads
 mkdir -p gpurun_out
 timeout 900 python bench.py > gpurun_out/r02_bench_c3_n1.json 2> gpurun_out/b1.err; tail -3 gpurun_out/b1.err
-for wl in c2 c4 c3-u8; do
+for wl in c2 c4 c4-forest c3-u8; do
 timeout 900 python bench.py --steps 30 --warmup 8 --no-cpu --workload $wl > gpurun_out/r02_bench_${wl}_n1.json 2> gpurun_out/b_$wl.err; tail -3 gpurun_out/b_$wl.err
 done
 timeout 900 python bench.py --impl reference --steps 8 --warmup 3 > gpurun_out/r02_bench_reference_arm.json 2> gpurun_out/bref.err; tail -3 gpurun_out/bref.err
