@@ -474,10 +474,16 @@ __global__ void __launch_bounds__(EngCfg<CPL, WEIGHTED>::threads, 1) eng_hist_ke
         for (int j = 0; j < U; j++) w[j] = WEIGHTED ? __ldg(gw + p + j) : 1;
         unsigned pa[U * CPL];
         if (on) eng_bins<CPL, WEIGHTED, U, LPR, NA, U8>(c, hb, x, w, pa);
+        // The two warp barriers are there for ptxas, not for the threads: without them it starts a cell's atomics as
+        // soon as that cell's bin is known and threads the prefetches through the atomics, i.e. it undoes the phases
+        // (all bins, then the prefetches, then all atomics back to back).  Memory operations do not move across a
+        // barrier; the arithmetic still does.  100M x 64: 6.2-6.3 ms per level against 6.3-6.65 (same box, same run).
+        __syncwarp();
         if (more) {
 #pragma unroll
           for (int j = 0; j < U; j++) prefetch_l2(row_addr(xrow, (unsigned)nx[j], ldt4));
         }
+        __syncwarp();
         if (on) eng_accum<CPL, WEIGHTED, U, LPR>(a, hb, node, col_lane, pa, v1, v2, w);
       }
       for (; p < send; p++) one_row(p);  // the run's last, partial batch
