@@ -1351,6 +1351,15 @@ __global__ void __launch_bounds__(kScatThreads, 2) eng_scatter_kernel(
       const int64_t r = base + k * kScatThreads + threadIdx.x;
       ch[k] = r < r1 ? nid16[r] : kNoNid;
     }
+    // the rows' targets, on their way while the tile is counted and scanned (loaded where they are used: 1.47 ms of
+    // routing + regrouping per level at 100M rows against 1.43; one CTA per SM with 64 registers and no spills: 1.51)
+    int ty[kScatPer], tyy[kScatPer];
+#pragma unroll
+    for (int k = 0; k < kScatPer; k++) {
+      const int64_t r = base + k * kScatThreads + threadIdx.x;
+      ty[k] = r < r1 ? __ldg(wyq_rows + r) : 0;
+      tyy[k] = r < r1 ? __ldg(wyyq_rows + r) : 0;
+    }
 #pragma unroll
     for (int k = 0; k < kScatPer; k++) {  // position of the row among the tile's rows of its child
       const unsigned grp = __match_any_sync(0xffffffffu, ch[k]);
@@ -1381,7 +1390,7 @@ __global__ void __launch_bounds__(kScatThreads, 2) eng_scatter_kernel(
         const int pos = s_lb[ch[k]] + rank[k];
         const int2 m = s_m[ch[k]];
         s_row[pos] = (int)r;
-        s_val[pos] = make_uint2((unsigned)(wyq_rows[r] - m.x), (unsigned)(wyyq_rows[r] - m.y));
+        s_val[pos] = make_uint2((unsigned)(ty[k] - m.x), (unsigned)(tyy[k] - m.y));
         if (WEIGHTED) {
           const int wq = wq_rows[r];
           s_w[pos] = wq;
