@@ -22,6 +22,38 @@ pub struct H2okParams {
     pub min_split_improvement: f64,
 }
 
+/// `h2ok_split` (ABI version 2, 208 bytes): DTree.Split as chosen for one node.  `equal == 2`: a categorical split,
+/// category c goes right when bit c of `cat_bits` is set; otherwise `x >= splat` goes right.  NaN follows `na_dir`.
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct H2okSplit {
+    pub col: i32,
+    pub bin: i32,
+    pub na_dir: i32,
+    pub splat: f32,
+    pub se_before: f64,
+    pub se_left: f64,
+    pub se_right: f64,
+    pub n_left: f64,
+    pub n_right: f64,
+    pub pred_left: f64,
+    pub pred_right: f64,
+    pub equal: i32,
+    pub pad: i32,
+    pub cat_bits: [u32; 32],
+}
+
+/// `h2ok_level_out`: host buffers `h2ok_hist_group_level` fills for the level it ran (any pointer may be null).
+#[repr(C)]
+pub struct H2okLevelOut {
+    pub hist: *mut f64,
+    pub min2: *mut f32,
+    pub maxin: *mut f32,
+    pub splits: *mut H2okSplit,
+    pub child_descs: *mut u8, // h2ok_col_desc[n_children][cols], 32 bytes each
+    pub child_ids: *mut i32,
+}
+
 pub const H2OK_SHAPE_HIGGS28: i32 = 2;
 pub const H2OK_SHAPE_WIDE64: i32 = 3;
 pub const H2OK_SHAPE_SPARSE: i32 = 4;
@@ -35,7 +67,7 @@ extern "C" {
     fn h2ok_hist_group_loop_create(group: *mut H2okGroup, params: *const H2okParams, is_int: *const i32) -> i32;
     fn h2ok_hist_group_set_options(group: *mut H2okGroup, reduce_mode: i32, checksum: i32, time_phases: i32) -> i32;
     fn h2ok_hist_group_begin_tree_synth(group: *mut H2okGroup, seed: u64, weight_mode: i32) -> i32;
-    fn h2ok_hist_group_level(group: *mut H2okGroup, out: *const u8, n_nodes_done: *mut i32, n_children: *mut i32) -> i32;
+    fn h2ok_hist_group_level(group: *mut H2okGroup, out: *const H2okLevelOut, n_nodes_done: *mut i32, n_children: *mut i32) -> i32;
     fn h2ok_hist_group_checksum(group: *mut H2okGroup, out3: *mut u64) -> i32;
     fn h2ok_hist_group_hist_ms(group: *mut H2okGroup, ms_out: *mut c_float) -> i32;
     fn h2ok_hist_group_sync(group: *mut H2okGroup) -> i32;
